@@ -1,0 +1,124 @@
+/*
+ * b200rt.h — C ABI of libb200rt.so, the B200 (sm_100a) render path.
+ *
+ * This is the drop-in boundary for ONE path of peter-seres/python-ray-tracer: the numba kernel launch
+ *
+ *     render[blockspergrid, threadsperblock](pixel_loc, result, camera_origin, camera_rotation,
+ *                                            spheres, lights, planes, amb, lamb, refl, refl_depth, aliasing)
+ *
+ * (reference src/main.py:41-42,46-47; kernel src/ray_tracing/kernels.py:6-73 and everything it inlines:
+ * src/ray_tracing/trace.py:7-133, intersections.py:6-68, common.py:5-120).  The reference has no FFI; the
+ * binding a maintainer adds is the ctypes stub shown in INTEGRATION.md (python-ray-tracer_b200/b200rt/_lib.py).
+ *
+ * Plain pointers and sizes only; no torch / numba types.  All device buffers are caller-owned.
+ * Every entry point returns 0 on success, <0 for argument errors (B200RT_E_*), >0 for a cudaError_t.
+ * b200rt_last_error() returns a thread-local human-readable message for the last failure.
+ */
+#ifndef B200RT_H
+#define B200RT_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200RT_VERSION 1
+
+#if defined(__GNUC__)
+#define B200RT_API __attribute__((visibility("default")))
+#else
+#define B200RT_API
+#endif
+
+/* argument errors */
+#define B200RT_E_NULL        (-1)   /* args == NULL or a required pointer is NULL          */
+#define B200RT_E_STRUCT_SIZE (-2)   /* args->struct_size != sizeof(b200rt_args)            */
+#define B200RT_E_SHAPE       (-3)   /* W/H/S/L/Pl/x range out of bounds                    */
+#define B200RT_E_DEPTH       (-4)   /* refl_depth < 0 or > B200RT_MAX_DEPTH                */
+#define B200RT_E_DEVICE      (-5)   /* no such CUDA device / not an sm_100 device           */
+#define B200RT_E_NOMEM       (-6)   /* scratch allocation failed                            */
+
+#define B200RT_MAX_DEPTH 64
+
+/* flags */
+#define B200RT_F_SCENE_ON_HOST   0x1u  /* spheres/lights/planes point to HOST memory (b200rt_render only; implied by _host) */
+#define B200RT_F_NO_FILTER       0x2u  /* debug: run the exact sphere test on every sphere (must give bit-identical output) */
+#define B200RT_F_UNSWAP_GB       0x4u  /* write channels as R,G,B instead of the reference's R,B,G wiring (common.py:60-63) */
+
+/*
+ * Closed form of Camera.generate_pixel_locations() (reference src/scene/camera.py:18-26), evaluated the way
+ * numpy.mgrid does (index*step + start):
+ *     pixel_loc[0][x][y] = f          pixel_loc[1][x][y] = x*sy + ar          pixel_loc[2][x][y] = y*sz + 1.0
+ * Used when args->pixel_loc == NULL, so no 24*W*H-byte array has to exist (796 MB at 7680x4320).
+ */
+typedef struct b200rt_grid {
+    double f, ar, sy, sz;
+} b200rt_grid;
+
+/* Ray = one get_intersection query (reference trace.py:53 closest-hit, trace.py:92 shadow). */
+typedef struct b200rt_stats {
+    uint64_t primary;   /* first query of every sample (kernels.py:26,56 -> trace.py:120 -> :53) */
+    uint64_t shadow;    /* one per light per hit-trace (trace.py:92)                              */
+    uint64_t bounce;    /* first query of every reflection trace (trace.py:128 -> :53)            */
+    uint64_t slow_path; /* thread-level entries into the exact sphere test (diagnostic)           */
+    float    kernel_ms[4]; /* device time: [0] total, [1] closest-hit kernels, [2] shadow kernels, [3] everything else */
+} b200rt_stats;
+
+typedef struct b200rt_args {
+    uint32_t struct_size;          /* = sizeof(b200rt_args)                                                     */
+    uint32_t flags;                /* B200RT_F_*                                                                */
+    int32_t  device;               /* CUDA device ordinal                                                       */
+    int32_t  reserved0;
+    void*    stream;               /* cudaStream_t (NULL = default stream); the launch is asynchronous on it    */
+
+    /* kernels.py:7 argument 1: pixel_loc float64 (3,W,H) C-order, DEVICE pointer; NULL -> use `grid`.          */
+    const double* pixel_loc;
+    b200rt_grid   grid;
+    /* argument 2: result uint8 (3,W,H) C-order, indexed [channel][x][y] (kernels.py:71-73); DEVICE pointer.    */
+    uint8_t* result;
+    int32_t  W, H;                 /* = pixel_loc.shape[1], pixel_loc.shape[2]                                   */
+    int32_t  x_begin, x_end;       /* column tile [x_begin, x_end) along array axis 1; whole frame = [0, W)     */
+
+    double   cam_origin[3];        /* argument 3: camera_origin (src/scene/camera.py:14-16)                      */
+    double   cam_rot[9];           /* argument 4: camera_rotation, row-major 3x3 (src/scene/rotation.py:34-43)   */
+
+    const float* spheres; int32_t S;   /* argument 5: float32 (7,S): rows Cx,Cy,Cz,r,R,G,B (src/scene/scene.py:17-23,69-76) */
+    const float* lights;  int32_t L;   /* argument 6: float32 (3,L)                       (scene.py:32-36,87-94)            */
+    const float* planes;  int32_t Pl;  /* argument 7: float32 (9,Pl): ox,oy,oz,nx,ny,nz,R,G,B (scene.py:47-53,78-85)        */
+
+    double   amb, lamb, refl;      /* arguments 8-10 (src/main.py:11)                                            */
+    int64_t  refl_depth;           /* argument 11                                                                */
+    int32_t  aliasing;             /* argument 12 (bool)                                                         */
+    int32_t  reserved1;
+
+    b200rt_stats* stats;           /* optional HOST pointer; non-NULL makes the call synchronous and fills it    */
+} b200rt_args;
+
+B200RT_API int         b200rt_version(void);
+B200RT_API const char* b200rt_last_error(void);
+B200RT_API uint32_t    b200rt_args_size(void);
+
+/* Render tile [x_begin,x_end) of the frame into the DEVICE buffer args->result.  Asynchronous on args->stream
+ * unless args->stats != NULL.  Replaces the numba launch at reference src/main.py:41-42. */
+B200RT_API int b200rt_render(const b200rt_args* args);
+
+/* Same call with HOST buffers: args->pixel_loc (nullable), args->result, spheres/lights/planes are host
+ * pointers.  Stages the inputs, renders, copies the tile of `result` back and synchronises — the
+ * to_device / launch / copy_to_host sequence of reference src/main.py:19-51 in one call. */
+B200RT_API int b200rt_render_host(const b200rt_args* args);
+
+/* Measured FP32 CUDA-core throughput of `device` (dependent-chain-free FFMA / FFMA2 loops), TFLOP/s, and the
+ * SM clock (MHz) derived from clock64()/globaltimer during the probe.  Used as the roofline denominator. */
+B200RT_API int b200rt_fp32_probe(int device, double* ffma_tflops, double* ffma2_tflops, double* sm_mhz);
+
+B200RT_API int b200rt_device_count(void);
+B200RT_API int b200rt_sm_count(int device);
+/* Free the per-device scratch (packed scene, ray queues).  Safe to call at any time between renders. */
+B200RT_API int b200rt_shutdown(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200RT_H */

@@ -37,14 +37,19 @@ def _import_reference():
     return cuda, ray_tracing
 
 
-def padded_pixel_loc(pixel_loc: np.ndarray) -> np.ndarray:
-    """(3,W,H) -> (3,W+1,H+1) reproducing GPU flat-wrap reads; past-the-end elements are 0.0."""
+def padded_pixel_loc(pixel_loc: np.ndarray, x_lo=0, x_hi=None, y_lo=0, y_hi=None) -> np.ndarray:
+    """pad[c,x,y] = flat[c*W*H + x*H + y] for x in [x_lo, x_hi], y in [y_lo, y_hi] (inclusive; defaults
+    0..W and 0..H, i.e. shape (3,W+1,H+1)).  Reproduces GPU flat-wrap reads; past-the-end elements are 0.0."""
     _, W, H = pixel_loc.shape
-    flat = np.concatenate([np.ascontiguousarray(pixel_loc, dtype=np.float64).ravel(), np.zeros(H + 2)])
-    c = np.arange(3)[:, None, None]
-    x = np.arange(W + 1)[None, :, None]
-    y = np.arange(H + 1)[None, None, :]
-    return flat[c * W * H + x * H + y]
+    x_hi = W if x_hi is None else x_hi
+    y_hi = H if y_hi is None else y_hi
+    flat = np.ascontiguousarray(pixel_loc, dtype=np.float64).reshape(-1)
+    c = np.arange(3, dtype=np.int64)[:, None, None]
+    x = np.arange(x_lo, x_hi + 1, dtype=np.int64)[None, :, None]
+    y = np.arange(y_lo, y_hi + 1, dtype=np.int64)[None, None, :]
+    idx = c * W * H + x * H + y
+    ok = idx < flat.size
+    return np.where(ok, flat[np.minimum(idx, flat.size - 1)], 0.0)
 
 
 def _largest_divisor(n: int, cap: int) -> int:
@@ -86,15 +91,17 @@ def render_reference_sim(pixel_loc, cam_origin, cam_rotation, spheres, lights, p
     _, W, H = pixel_loc.shape
     x0, x1 = x_range if x_range is not None else (0, W)
     y0, y1 = y_range if y_range is not None else (0, H)
-    pad = padded_pixel_loc(pixel_loc)
     hy = 1 if y0 > 0 else 0
+    hx0 = 1 if x0 > 0 else 0
+    pad = padded_pixel_loc(pixel_loc, x0 - hx0, x1, y0 - hy, y1)   # region + halo only
+    px0 = x0 - hx0                                                 # pad's x origin in frame coordinates
     amb, lamb, refl = float(amb), float(lamb), float(refl)
     refl_depth, aliasing = int(refl_depth), bool(aliasing)
     jobs, spans = [], []
     for xa in range(x0, x1, cols_per_job):
         xb = min(xa + cols_per_job, x1)
         hx = 1 if xa > 0 else 0
-        tile = np.ascontiguousarray(pad[:, xa - hx: xb + 1, y0 - hy: y1 + 1])
+        tile = np.ascontiguousarray(pad[:, xa - hx - px0: xb + 1 - px0, :])
         jobs.append((tile, hx, hy, np.asarray(cam_origin), np.asarray(cam_rotation),
                      np.asarray(spheres), np.asarray(lights), np.asarray(planes),
                      amb, lamb, refl, refl_depth, aliasing))

@@ -1,0 +1,103 @@
+"""Convenience front ends over the C ABI: whole-frame and tiled renders from host data.
+
+`render_host` is the to_device / launch / copy_to_host sequence of reference src/main.py:19-51 as ONE call
+into libb200rt (b200rt_render_host): host buffers in, host uint8 (3,W,H) out.  Pure ctypes + numpy.
+"""
+import ctypes as C
+import numpy as np
+from . import _lib
+
+
+def _fill_common(a, W, H, cam_origin, cam_rotation, spheres, lights, planes, amb, lamb, refl, refl_depth, aliasing,
+                 device, flags, tile):
+    a.struct_size = C.sizeof(_lib.Args)
+    a.flags = flags
+    a.device = int(device)
+    a.W, a.H = int(W), int(H)
+    a.x_begin, a.x_end = (0, W) if tile is None else (int(tile[0]), int(tile[1]))
+    co = np.ascontiguousarray(cam_origin, dtype=np.float64).ravel()
+    cr = np.ascontiguousarray(cam_rotation, dtype=np.float64).ravel()
+    if co.size != 3 or cr.size != 9:
+        raise ValueError("camera_origin must have 3 elements and camera_rotation 9")
+    for i in range(3):
+        a.cam_origin[i] = co[i]
+    for i in range(9):
+        a.cam_rot[i] = cr[i]
+    for name, arr, rows in (("spheres", spheres, 7), ("lights", lights, 3), ("planes", planes, 9)):
+        if arr.ndim != 2 or arr.shape[0] != rows:
+            raise ValueError(f"{name} must have shape ({rows}, N), got {arr.shape}")
+    a.spheres, a.S = (spheres.ctypes.data if spheres.size else None), spheres.shape[1]
+    a.lights, a.L = (lights.ctypes.data if lights.size else None), lights.shape[1]
+    a.planes, a.Pl = (planes.ctypes.data if planes.size else None), planes.shape[1]
+    a.amb, a.lamb, a.refl = float(amb), float(lamb), float(refl)
+    a.refl_depth, a.aliasing = int(refl_depth), int(bool(aliasing))
+
+
+def render_host(pixel_loc, cam_origin, cam_rotation, spheres, lights, planes, amb, lamb, refl, refl_depth, aliasing,
+                *, grid=None, shape=None, out=None, device=0, tile=None, flags=0, stats=False):
+    """Host arrays in, host uint8 (3,W,H) out, through b200rt_render_host.
+
+    pixel_loc: float64 (3,W,H) host array, or None with grid=(f, ar, sy, sz) and shape=(W, H).
+    Returns `out` (or (out, stats_dict) when stats=True).  Only the tile's columns are written.
+    """
+    L = _lib.lib()
+    a = _lib.Args()
+    if pixel_loc is not None and getattr(pixel_loc, "grid", None) is not None and grid is None:
+        grid, shape, pixel_loc = pixel_loc.grid, pixel_loc.shape[1:], None
+    keep = []
+    if pixel_loc is not None:
+        pl = np.ascontiguousarray(pixel_loc, dtype=np.float64)
+        if pl.ndim != 3 or pl.shape[0] != 3:
+            raise ValueError(f"pixel_loc must have shape (3, W, H), got {pl.shape}")
+        W, H = pl.shape[1:]
+        a.pixel_loc = pl.ctypes.data
+        keep.append(pl)
+    else:
+        if grid is None or shape is None:
+            raise ValueError("either pixel_loc or grid+shape is required")
+        W, H = shape
+        a.pixel_loc = None
+        a.grid = _lib.Grid(*[float(v) for v in grid])
+    sp = np.ascontiguousarray(spheres, dtype=np.float32)
+    li = np.ascontiguousarray(lights, dtype=np.float32)
+    pn = np.ascontiguousarray(planes, dtype=np.float32)
+    keep += [sp, li, pn]
+    _fill_common(a, W, H, cam_origin, cam_rotation, sp, li, pn, amb, lamb, refl, refl_depth, aliasing, device, flags, tile)
+    if out is None:
+        out = np.zeros((3, W, H), dtype=np.uint8)
+    if out.shape != (3, W, H) or out.dtype != np.uint8 or not out.flags.c_contiguous:
+        raise ValueError("out must be a C-contiguous uint8 array of shape (3, W, H)")
+    a.result = out.ctypes.data
+    st = _lib.Stats() if stats else None
+    a.stats = C.pointer(st) if st is not None else None
+    _lib.check(L.b200rt_render_host(C.byref(a)))
+    return (out, st.as_dict()) if stats else out
+
+
+def render_frame(scene, camera, amb=0.0, lamb=0.6, refl=0.3, refl_depth=2, aliasing=True, **kw):
+    """Scene + Camera -> uint8 (3,W,H) host array (channel wiring as the reference stores it: R,B,G)."""
+    spheres, lights, planes = scene.generate_scene()
+    W, H = camera.resolution
+    return render_host(None, camera.position, camera.rotation, spheres, lights, planes, amb, lamb, refl, refl_depth,
+                       aliasing, grid=camera.grid(), shape=(W, H), **kw)
+
+
+def render_batch(scene, cameras, amb=0.0, lamb=0.6, refl=0.3, refl_depth=2, aliasing=True, devices=(0,), **kw):
+    """Camera-pose batch: frame k renders on devices[k % len(devices)] (frame sharding)."""
+    from concurrent.futures import ThreadPoolExecutor
+    devices = list(devices)
+
+    def one(k):
+        return render_frame(scene, cameras[k], amb, lamb, refl, refl_depth, aliasing, device=devices[k % len(devices)], **kw)
+
+    if len(devices) == 1:
+        return [one(k) for k in range(len(cameras))]
+    with ThreadPoolExecutor(len(devices)) as ex:       # ctypes releases the GIL; one in-flight frame per device
+        return list(ex.map(one, range(len(cameras))))
+
+
+def fp32_probe(device=0):
+    """Measured FP32 CUDA-core peak of the device: dict(ffma_tflops, ffma2_tflops, sm_mhz)."""
+    f1, f2, mhz = C.c_double(), C.c_double(), C.c_double()
+    _lib.check(_lib.lib().b200rt_fp32_probe(int(device), C.byref(f1), C.byref(f2), C.byref(mhz)))
+    return dict(ffma_tflops=f1.value, ffma2_tflops=f2.value, sm_mhz=mhz.value)

@@ -1,0 +1,831 @@
+// b200rt.cu — hand-written CUDA (sm_100a) implementation of the python-ray-tracer `render` hot path and its C ABI.
+//
+// Design (DESIGN.md has the long form): a device-side WAVEFRONT.  One frame tile is a set of independent
+// paths (1 or 9 samples per pixel).  Each reflection depth runs
+//     k_closest   brute-force closest hit of every live ray         (reference trace.py:7-41, called at :53)
+//     k_setup     hit point, normal, bias; compacts the hit list    (trace.py:56-83)
+//     k_shadow    any-hit query of (hit, light) pairs               (trace.py:86-96)
+//     k_shade     Lambert terms, weighted accumulate, reflection    (trace.py:99-110, :123-131)
+// over dense, compacted ray queues, so the two intersection kernels — >99 % of the work at S=1024 — run with
+// every lane busy regardless of how many paths have died.  k_raygen (kernels.py:16-23,32-55) feeds the first
+// queue, k_resolve (kernels.py:58-73) sums the samples in reference order, quantises and writes the framebuffer
+// with vector stores.  Queue lengths live in device memory; nothing synchronises with the host.
+//
+// Numerics: FP32 for intersection and shading (IEEE div/sqrt, explicit FMAs — rt_math.cuh); primary-ray
+// generation in FP64 from the reference's float64 pixel grid, rounded once to FP32.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <math.h>
+#include <mutex>
+#include <vector>
+#include <string>
+#include <algorithm>
+#include "../../include/b200rt.h"
+#include "rt_math.cuh"
+
+namespace b200rt {
+
+// ------------------------------------------------------------------------------------------------
+// Device-side scene (packed once per launch by k_pack from the reference's SoA arrays)
+// ------------------------------------------------------------------------------------------------
+struct SceneDev {
+    const float4* sphA;    // [Spad] (Cx, Cy, Cz, r^2 - |C|^2)  filter operands; padding entries never pass
+    const float4* sphB;    // [S]    (Cx, Cy, Cz, r^2)          exact-test operands; r^2 = float32 r*r (intersections.py:21)
+    const float4* sphCol;  // [S]    (R, G, B, 0)
+    const float4* plO;     // [Pl]   plane point
+    const float4* plN;     // [Pl]   stored normal (used un-renormalised by the intersection, intersections.py:52)
+    const float4* plNu;    // [Pl]   float32 re-normalised normal (common.py:104-110)
+    const float4* plCol;   // [Pl]
+    const float4* lights;  // [L]
+    const float*  cmax;    // [1]    max |C| over spheres (filter error bound)
+    int S, Spad, Pl, L;
+};
+
+// (7,S) / (9,Pl) / (3,L) float32 SoA  ->  packed float4 arrays.  One thread per object.
+__global__ void k_pack(const float* __restrict__ spheres, int S, int Spad,
+                       const float* __restrict__ planes, int Pl,
+                       const float* __restrict__ lights, int L,
+                       float4* sphA, float4* sphB, float4* sphCol,
+                       float4* plO, float4* plN, float4* plNu, float4* plCol, float4* lightsOut, float* cmax) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < Spad) {
+        if (i < S) {
+            float cx = spheres[0 * S + i], cy = spheres[1 * S + i], cz = spheres[2 * S + i], r = spheres[3 * S + i];
+            float r2 = __fmul_rn(r, r);                                   // float32 product, intersections.py:21
+            double cc = (double)cx * cx + (double)cy * cy + (double)cz * cz;
+            sphA[i] = make_float4(cx, cy, cz, (float)((double)r2 - cc));
+            sphB[i] = make_float4(cx, cy, cz, r2);
+            sphCol[i] = make_float4(spheres[4 * S + i], spheres[5 * S + i], spheres[6 * S + i], 0.f);
+            // scene bound for the filter margin: max |C| (atomicMax on the bit pattern of a non-negative float)
+            atomicMax(reinterpret_cast<int*>(cmax), __float_as_int((float)sqrt(cc) * 1.0000002f));
+        } else {
+            sphA[i] = make_float4(0.f, 0.f, 0.f, -3.0e38f);               // padding: q = -3e38 never reaches a threshold
+        }
+    }
+    if (i < Pl) {
+        plO[i] = make_float4(planes[0 * Pl + i], planes[1 * Pl + i], planes[2 * Pl + i], 0.f);
+        float nx = planes[3 * Pl + i], ny = planes[4 * Pl + i], nz = planes[5 * Pl + i];
+        plN[i] = make_float4(nx, ny, nz, 0.f);
+        // common.py:104-110 + :28-32 evaluated in float32, left to right, no contraction
+        float nn = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(nx, nx), __fmul_rn(ny, ny)), __fmul_rn(nz, nz)));
+        plNu[i] = make_float4(__fdiv_rn(nx, nn), __fdiv_rn(ny, nn), __fdiv_rn(nz, nn), 0.f);
+        plCol[i] = make_float4(planes[6 * Pl + i], planes[7 * Pl + i], planes[8 * Pl + i], 0.f);
+    }
+    if (i < L) lightsOut[i] = make_float4(lights[0 * L + i], lights[1 * L + i], lights[2 * L + i], 0.f);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Frame / tile description shared by k_raygen and k_resolve
+// ------------------------------------------------------------------------------------------------
+struct FrameDev {
+    const double* pixel_loc;       // (3,W,H) or nullptr
+    double gf, gar, gsy, gsz;      // affine grid (camera.py:18-26)
+    double ox, oy, oz;             // camera origin
+    double rot[9];                 // camera rotation, row-major
+    int W, H;
+    int x0, x1;                    // chunk columns [x0, x1)
+    int ns;                        // samples per pixel slot: 1 or 9
+    uint32_t npix;                 // (x1-x0)*H
+};
+
+// pixel_loc[c, x, y] with the GPU's unchecked C-order flat addressing: elements past the end
+// of the buffer are defined as 0.0.
+__device__ __forceinline__ double pl_at(const FrameDev& f, int c, int x, int y) {
+    const long long W = f.W, H = f.H;
+    long long flat = (long long)c * W * H + (long long)x * H + y;
+    if (flat < 0 || flat >= 3 * W * H) return 0.0;
+    if (f.pixel_loc) return f.pixel_loc[flat];
+    int cc = (int)(flat / (W * H)); long long rem = flat - (long long)cc * W * H;
+    int xx = (int)(rem / H), yy = (int)(rem - (long long)xx * H);
+    if (cc == 0) return f.gf;
+    if (cc == 1) return __dadd_rn(__dmul_rn((double)xx, f.gsy), f.gar);
+    return __dadd_rn(__dmul_rn((double)yy, f.gsz), 1.0);
+}
+
+// AA neighbour order of kernels.py:32-53: left, right, top(y+1), bot(y-1), topleft, topright, bottomleft, bottomright
+__constant__ int c_dx[9] = { 0, -1, +1, 0, 0, -1, +1, -1, +1 };
+__constant__ int c_dy[9] = { 0, 0, 0, +1, -1, +1, +1, -1, -1 };
+
+// One thread per (sample k, pixel p) slot.  Primary ray in FP64 (kernels.py:19-23 / :43-55), rounded to FP32,
+// appended to the ray queue.  Slots that the reference never samples (AA border: x == 0 or y == 0) are skipped.
+__global__ void k_raygen(FrameDev f, float4* __restrict__ rayO, float4* __restrict__ rayD, uint32_t* n_live) {
+    const uint32_t nslots = f.npix * (uint32_t)f.ns;
+    for (uint32_t base = blockIdx.x * blockDim.x; base < nslots; base += gridDim.x * blockDim.x) {
+        uint32_t slot = base + threadIdx.x;
+        bool valid = slot < nslots;
+        float4 o = make_float4(0, 0, 0, 0), d = make_float4(0, 0, 0, 0);
+        if (valid) {
+            uint32_t k = slot / f.npix, p = slot - k * f.npix;
+            int x = f.x0 + (int)(p / (uint32_t)f.H), y = (int)(p % (uint32_t)f.H);
+            if (k > 0 && !(x >= 1 && y >= 1)) valid = false;          // kernels.py:29
+            if (valid) {
+                double px = pl_at(f, 0, x, y), py = pl_at(f, 1, x, y), pz = pl_at(f, 2, x, y);
+                if (k > 0) {                                          // kernels.py:43-50  0.5*P + 0.5*P'
+                    int xn = x + c_dx[k], yn = y + c_dy[k];
+                    px = __dadd_rn(__dmul_rn(0.5, px), __dmul_rn(0.5, pl_at(f, 0, xn, yn)));
+                    py = __dadd_rn(__dmul_rn(0.5, py), __dmul_rn(0.5, pl_at(f, 1, xn, yn)));
+                    pz = __dadd_rn(__dmul_rn(0.5, pz), __dmul_rn(0.5, pl_at(f, 2, xn, yn)));
+                }
+                // matmul (common.py:40-49) then normalize (common.py:28-32), float64
+                double bx = f.rot[0] * px + f.rot[1] * py + f.rot[2] * pz;
+                double by = f.rot[3] * px + f.rot[4] * py + f.rot[5] * pz;
+                double bz = f.rot[6] * px + f.rot[7] * py + f.rot[8] * pz;
+                double n = sqrt(bx * bx + by * by + bz * bz);
+                d = make_float4((float)(bx / n), (float)(by / n), (float)(bz / n), 0.f);
+                o = make_float4((float)f.ox, (float)f.oy, (float)f.oz, __uint_as_float(slot));
+            }
+        }
+        uint32_t pos = warp_append(valid, n_live);
+        if (valid) { rayO[pos] = o; rayD[pos] = d; }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// The hot kernel: brute-force intersection of a dense ray queue against all spheres and planes.
+// ------------------------------------------------------------------------------------------------
+constexpr int kThreads = 256;            // threads per CTA
+constexpr int kRays    = 4;              // rays per thread (ILP; one broadcast LDS.128 feeds 4 tests)
+constexpr int kGroup   = kThreads * kRays;
+constexpr int kChunkS  = 4096;           // spheres staged in shared memory per pass (64 KB + 16 KB)
+
+struct QueueDev {
+    // closest-hit input: ray queue (O.xyz, slot) / (D.xyz, -)
+    const float4* rayO; const float4* rayD;
+    // shadow input: hit records
+    const float4* hP;                    // (biased hit point, slot)
+    const uint32_t* n_in;                // number of rays (closest) or number of hit records (shadow)
+    uint32_t* work;                      // dynamic group counter (zeroed before the launch)
+    float* hit_t; int* hit_id;           // closest-hit output, queue order
+    uint8_t* occl;                       // shadow output, [light][hit]
+    unsigned long long* slow;            // diagnostic: thread-level slow-path entries (may be null)
+};
+
+// Per ray, per sphere the loop evaluates the discriminant of intersections.py:23 in expanded form
+//     disc = b^2 - c,  b = (C-O).D = C.D - O.D,  c = |C-O|^2 - r^2 = (|C|^2 - r^2) - 2 C.O + |O|^2
+//     q = b^2 + 2 C.O + (r^2 - |C|^2)   and   disc >= 0  <=>  q >= |O|^2
+// = 7 FFMA per test with per-ray constants (D, 2O, -O.D) and one float4 per sphere.  The expanded form
+// cancels badly in FP32, so it is used ONLY as a conservative filter: q >= |O|^2 - margin, with margin a
+// rigorous bound on its rounding error (64 * 2^-24 * (max|C| + |O|)^2).  Spheres that pass
+// (a few per ray out of S) go through sphere_exact() — the robust form — which alone decides hit/miss and t.
+// With B200RT_F_NO_FILTER every sphere takes the exact test; outputs must be bit-identical (tested).
+template <bool ANY, bool NOFILTER>
+__global__ void __launch_bounds__(kThreads, 2)
+k_intersect(SceneDev sc, QueueDev q) {
+    extern __shared__ float4 s_sph[];                        // [chunk] filter operands
+    float* s_r2 = reinterpret_cast<float*>(s_sph + min(sc.Spad, kChunkS));   // [chunk] r^2 for the exact test
+    __shared__ uint32_t s_group;
+
+    const uint32_t n_in = *q.n_in;
+    const uint32_t n = ANY ? n_in * (uint32_t)sc.L : n_in;
+    const uint32_t ngroups = (n + kGroup - 1) / kGroup;
+    const float cmax = *sc.cmax;
+    int staged = -1;                                          // sphere chunk currently in shared memory
+    uint32_t slow_cnt = 0;                                    // thread-level entries into the exact test
+
+    for (;;) {
+        __syncthreads();                                      // protects s_group and the staged chunk
+        if (threadIdx.x == 0) s_group = atomicAdd(q.work, 1u);
+        __syncthreads();
+        const uint32_t g = s_group;
+        if (g >= ngroups) break;
+
+        // ---- load / build this thread's rays ----
+        float dx[kRays], dy[kRays], dz[kRays], o2x[kRays], o2y[kRays], o2z[kRays], nod[kRays], thr[kRays];
+        float best[kRays]; int bid[kRays];
+#pragma unroll
+        for (int r = 0; r < kRays; ++r) {
+            const uint32_t i = g * kGroup + r * kThreads + threadIdx.x;
+            V3 O = mk(0.f, 0.f, 0.f), D = mk(0.f, 0.f, 0.f);
+            const bool active = i < n;
+            if (active) {
+                if (ANY) {
+                    const uint32_t j = i / n_in, h = i - j * n_in;
+                    const float4 p = q.hP[h]; const float4 l = __ldg(&sc.lights[j]);
+                    O = mk(p.x, p.y, p.z);
+                    D = normalize3(sub3(mk(l.x, l.y, l.z), O));            // common.py:84-91
+                } else {
+                    const float4 o = q.rayO[i], d = q.rayD[i];
+                    O = mk(o.x, o.y, o.z); D = mk(d.x, d.y, d.z);
+                }
+            }
+            dx[r] = D.x; dy[r] = D.y; dz[r] = D.z;
+            o2x[r] = 2.f * O.x; o2y[r] = 2.f * O.y; o2z[r] = 2.f * O.z;
+            nod[r] = -dot3(O, D);
+            const float oo = dot3(O, O);
+            const float A = cmax + __fsqrt_rn(oo);
+            const float margin = fmaf(3.8146973e-6f /* 64 * 2^-24 */, A * A, 1e-12f);
+            thr[r] = active ? (oo - margin) : __int_as_float(0x7f800000);
+            best[r] = kTMax; bid[r] = -1;
+        }
+
+        // ---- spheres, staged chunk by chunk ----
+        for (int c0 = 0; c0 < sc.Spad; c0 += kChunkS) {
+            const int cnt = min(kChunkS, sc.Spad - c0);
+            if (staged != c0) {
+                __syncthreads();
+                for (int s = threadIdx.x; s < cnt; s += kThreads) {
+                    s_sph[s] = sc.sphA[c0 + s];
+                    s_r2[s] = (c0 + s < sc.S) ? sc.sphB[c0 + s].w : 0.f;
+                }
+                staged = c0;
+                __syncthreads();
+            }
+#pragma unroll 2
+            for (int s = 0; s < cnt; s += 2) {
+                const float4 a0 = s_sph[s], a1 = s_sph[s + 1];
+                bool p0[kRays], p1[kRays]; bool any = false;
+#pragma unroll
+                for (int r = 0; r < kRays; ++r) {
+                    if (NOFILTER) { p0[r] = thr[r] < 3e38f && (c0 + s < sc.S); p1[r] = thr[r] < 3e38f && (c0 + s + 1 < sc.S); }
+                    else {
+                        const float b0 = fmaf(a0.x, dx[r], fmaf(a0.y, dy[r], fmaf(a0.z, dz[r], nod[r])));
+                        const float b1 = fmaf(a1.x, dx[r], fmaf(a1.y, dy[r], fmaf(a1.z, dz[r], nod[r])));
+                        const float q0 = fmaf(b0, b0, fmaf(a0.x, o2x[r], fmaf(a0.y, o2y[r], fmaf(a0.z, o2z[r], a0.w))));
+                        const float q1 = fmaf(b1, b1, fmaf(a1.x, o2x[r], fmaf(a1.y, o2y[r], fmaf(a1.z, o2z[r], a1.w))));
+                        p0[r] = q0 >= thr[r]; p1[r] = q1 >= thr[r];
+                    }
+                    any |= p0[r] | p1[r];
+                }
+                if (any) {                                                // rare: a few spheres per ray
+                    slow_cnt++;
+#pragma unroll
+                    for (int r = 0; r < kRays; ++r) {
+                        const V3 O = mk(0.5f * o2x[r], 0.5f * o2y[r], 0.5f * o2z[r]);   // exact
+                        const V3 D = mk(dx[r], dy[r], dz[r]);
+                        if (p0[r]) {
+                            const float t = sphere_exact(O, D, a0.x, a0.y, a0.z, s_r2[s]);
+                            if (ANY) { if (t > 0.f && t < kTMax) { bid[r] = 0; thr[r] = __int_as_float(0x7f800000); } }
+                            else if (t > 0.f && t < best[r]) { best[r] = t; bid[r] = c0 + s; }    // trace.py:26-29
+                        }
+                        if (p1[r]) {
+                            const float t = sphere_exact(O, D, a1.x, a1.y, a1.z, s_r2[s + 1]);
+                            if (ANY) { if (t > 0.f && t < kTMax) { bid[r] = 0; thr[r] = __int_as_float(0x7f800000); } }
+                            else if (t > 0.f && t < best[r]) { best[r] = t; bid[r] = c0 + s + 1; }
+                        }
+                    }
+                }
+            }
+        }
+
+        // ---- planes (trace.py:32-39), then write back ----
+#pragma unroll
+        for (int r = 0; r < kRays; ++r) {
+            const uint32_t i = g * kGroup + r * kThreads + threadIdx.x;
+            if (i >= n) continue;
+            const V3 O = mk(0.5f * o2x[r], 0.5f * o2y[r], 0.5f * o2z[r]);
+            const V3 D = mk(dx[r], dy[r], dz[r]);
+            if (ANY) {
+                bool occluded = bid[r] >= 0;
+                for (int p = 0; p < sc.Pl && !occluded; ++p) {
+                    const float t = plane_exact(O, D, __ldg(&sc.plO[p]), __ldg(&sc.plN[p]));
+                    occluded = (t > 0.f && t < kTMax);
+                }
+                q.occl[i] = occluded ? 1 : 0;
+            } else {
+                for (int p = 0; p < sc.Pl; ++p) {
+                    const float t = plane_exact(O, D, __ldg(&sc.plO[p]), __ldg(&sc.plN[p]));
+                    if (t > 0.f && t < best[r]) { best[r] = t; bid[r] = sc.S + p; }
+                }
+                q.hit_t[i] = best[r]; q.hit_id[i] = bid[r];
+            }
+        }
+    }
+    if (q.slow) {
+        const uint32_t tot = __reduce_add_sync(0xffffffffu, slow_cnt);
+        if (lane_id() == 0 && tot) atomicAdd(q.slow, (unsigned long long)tot);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Per-hit shading kernels (trace.py:56-110, :123-131) — <1 % of the work at S=1024
+// ------------------------------------------------------------------------------------------------
+struct ShadeDev {
+    float4* rayO; float4* rayD;          // ray queue (read by k_setup, rewritten by k_shade)
+    const float* hit_t; const int* hit_id;
+    float4* hP; float4* hN; float4* hD;  // hit records: (biased P, slot) (N, id) (incoming D, -)
+    const uint8_t* occl;                 // [light][hit]
+    float* accR; float* accG; float* accB;   // per-slot colour accumulators
+    const uint32_t* n_live;              // rays in the queue (k_setup input)
+    uint32_t* n_hit;                     // hit records (k_setup output, k_shade input)
+    uint32_t* n_next;                    // next ray queue length (k_shade output)
+    float amb, lamb, weight;             // weight = refl^depth_index (1 for the primary trace), trace.py:131
+    int emit_reflection;                 // 0 on the last depth
+};
+
+// trace.py:56-83: miss -> path ends; hit -> P = O + tD, colour/normal by object type, P += BIAS*N.
+__global__ void k_setup(SceneDev sc, ShadeDev s) {
+    const uint32_t n = *s.n_live;
+    for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {
+        const uint32_t i = base + threadIdx.x;
+        bool hit = false; float4 o, d; float t = 0.f; int id = -1;
+        if (i < n) { id = s.hit_id[i]; hit = id >= 0; }
+        V3 Pb = mk(0, 0, 0), N = mk(0, 0, 0);
+        if (hit) {
+            o = s.rayO[i]; d = s.rayD[i]; t = s.hit_t[i];
+            const V3 P = madd3(mk(o.x, o.y, o.z), t, mk(d.x, d.y, d.z));            // trace.py:60
+            if (id < sc.S) { const float4 c = __ldg(&sc.sphB[id]); N = normalize3(sub3(P, mk(c.x, c.y, c.z))); }   // common.py:94-101
+            else           { const float4 nu = __ldg(&sc.plNu[id - sc.S]); N = mk(nu.x, nu.y, nu.z); }             // common.py:104-110
+            Pb = madd3(P, kBias, N);                                                 // trace.py:82-83
+        }
+        const uint32_t h = warp_append(hit, s.n_hit);
+        if (hit) {
+            s.hP[h] = make_float4(Pb.x, Pb.y, Pb.z, o.w);
+            s.hN[h] = make_float4(N.x, N.y, N.z, __int_as_float(id));
+            s.hD[h] = make_float4(d.x, d.y, d.z, 0.f);
+        }
+    }
+}
+
+// trace.py:77,86-110 and the accumulate of trace.py:131: RGB_trace = amb*col + sum_j [visible_j && k_j>0] k_j*col,
+// acc[slot] += weight * RGB_trace; then the reflection ray (common.py:113-120) re-queued at the same index.
+__global__ void k_shade(SceneDev sc, ShadeDev s) {
+    const uint32_t n = *s.n_hit;
+    if (blockIdx.x == 0 && threadIdx.x == 0) *s.n_next = s.emit_reflection ? n : 0u;
+    for (uint32_t h = blockIdx.x * blockDim.x + threadIdx.x; h < n; h += gridDim.x * blockDim.x) {
+        const float4 p = s.hP[h], nn = s.hN[h], dd = s.hD[h];
+        const V3 Pb = mk(p.x, p.y, p.z), N = mk(nn.x, nn.y, nn.z), D = mk(dd.x, dd.y, dd.z);
+        const int id = __float_as_int(nn.w);
+        const uint32_t slot = __float_as_uint(p.w);
+        const float4 col = (id < sc.S) ? __ldg(&sc.sphCol[id]) : __ldg(&sc.plCol[id - sc.S]);
+        float r = __fmul_rn(s.amb, col.x), g = __fmul_rn(s.amb, col.y), b = __fmul_rn(s.amb, col.z);   // trace.py:77
+        for (int j = 0; j < sc.L; ++j) {                                                               // trace.py:86
+            if (s.occl[(size_t)j * n + h]) continue;                                                   // :95-96
+            const float4 l = __ldg(&sc.lights[j]);
+            const V3 Lv = normalize3(sub3(mk(l.x, l.y, l.z), Pb));                                     // :89
+            const float k = __fmul_rn(s.lamb, dot3(Lv, N));                                            // :99
+            if (k > 0.f) { r = fmaf(k, col.x, r); g = fmaf(k, col.y, g); b = fmaf(k, col.z, b); }      // :101-102
+        }
+        s.accR[slot] = fmaf(s.weight, r, s.accR[slot]);                                                // :131
+        s.accG[slot] = fmaf(s.weight, g, s.accG[slot]);
+        s.accB[slot] = fmaf(s.weight, b, s.accB[slot]);
+        if (s.emit_reflection) {
+            const float dn = dot3(D, N);
+            const V3 R = normalize3(madd3(D, -2.0f * dn, N));                                          // common.py:113-120
+            const V3 O2 = madd3(Pb, kBias, R);                                                         // trace.py:110
+            s.rayO[h] = make_float4(O2.x, O2.y, O2.z, p.w);
+            s.rayD[h] = make_float4(R.x, R.y, R.z, 0.f);
+        }
+    }
+}
+
+// kernels.py:58-73: sum the samples in reference order with the G/B cross-wiring (F6), /9, quantise with
+// round-half-even, swap G/B on output (F5), and store VEC pixels (consecutive y = contiguous bytes) per thread.
+template <int VEC>
+__global__ void k_resolve(FrameDev f, const float* __restrict__ accR, const float* __restrict__ accG,
+                          const float* __restrict__ accB, uint8_t* __restrict__ result, int aliasing, int unswap) {
+    const uint32_t nvec = f.npix / VEC;
+    const size_t WH = (size_t)f.W * f.H;
+    for (uint32_t v = blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += gridDim.x * blockDim.x) {
+        uint32_t out0[VEC], out1[VEC], out2[VEC];
+#pragma unroll
+        for (int e = 0; e < VEC; ++e) {
+            const uint32_t p = v * VEC + e;
+            const int x = f.x0 + (int)(p / (uint32_t)f.H), y = (int)(p % (uint32_t)f.H);
+            float R = accR[p], G = accG[p], B = accB[p];
+            if (aliasing && x >= 1 && y >= 1) {                                        // kernels.py:29
+                for (int k = 1; k < 9; ++k) {
+                    const size_t sl = (size_t)k * f.npix + p;
+                    R = __fadd_rn(R, accR[sl]); G = __fadd_rn(G, accB[sl]); B = __fadd_rn(B, accG[sl]);   // :58-60
+                }
+                R = __fdiv_rn(R, 9.0f); G = __fdiv_rn(G, 9.0f); B = __fdiv_rn(B, 9.0f);                  // :63-65
+            }
+            out0[e] = clip_color(R);
+            out1[e] = unswap ? clip_color(G) : clip_color(B);                           // common.py:60-63
+            out2[e] = unswap ? clip_color(B) : clip_color(G);
+        }
+        const size_t o = (size_t)f.x0 * f.H + (size_t)v * VEC;
+        uint8_t* d0 = result + o; uint8_t* d1 = result + WH + o; uint8_t* d2 = result + 2 * WH + o;
+        if constexpr (VEC == 1) { d0[0] = (uint8_t)out0[0]; d1[0] = (uint8_t)out1[0]; d2[0] = (uint8_t)out2[0]; }
+        else {
+            uint32_t w0[VEC / 4], w1[VEC / 4], w2[VEC / 4];
+#pragma unroll
+            for (int e = 0; e < VEC / 4; ++e) {
+                w0[e] = out0[4 * e] | (out0[4 * e + 1] << 8) | (out0[4 * e + 2] << 16) | (out0[4 * e + 3] << 24);
+                w1[e] = out1[4 * e] | (out1[4 * e + 1] << 8) | (out1[4 * e + 2] << 16) | (out1[4 * e + 3] << 24);
+                w2[e] = out2[4 * e] | (out2[4 * e + 1] << 8) | (out2[4 * e + 2] << 16) | (out2[4 * e + 3] << 24);
+            }
+            if constexpr (VEC == 16) {
+                *reinterpret_cast<uint4*>(d0) = make_uint4(w0[0], w0[1], w0[2], w0[3]);
+                *reinterpret_cast<uint4*>(d1) = make_uint4(w1[0], w1[1], w1[2], w1[3]);
+                *reinterpret_cast<uint4*>(d2) = make_uint4(w2[0], w2[1], w2[2], w2[3]);
+            } else {
+                *reinterpret_cast<uint32_t*>(d0) = w0[0];
+                *reinterpret_cast<uint32_t*>(d1) = w1[0];
+                *reinterpret_cast<uint32_t*>(d2) = w2[0];
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// FP32 CUDA-core peak probe (roofline denominator): independent FFMA / FFMA2 chains, no memory traffic
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_probe_ffma(float* out, int iters, unsigned long long* clk) {
+    float a[8]; const float m = 1.0000001f, c = 1e-9f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) a[i] = (float)(threadIdx.x + i);
+    unsigned long long t0 = 0, g0 = 0;
+    if (blockIdx.x == 0 && threadIdx.x == 0) { asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g0)); t0 = clock64(); }
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int u = 0; u < 16; ++u)
+#pragma unroll
+            for (int i = 0; i < 8; ++i) a[i] = fmaf(a[i], m, c);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        unsigned long long t1 = clock64(), g1; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g1));
+        clk[0] = t1 - t0; clk[1] = g1 - g0;
+    }
+    float s = 0; for (int i = 0; i < 8; ++i) s += a[i];
+    if (s == 12345.678f) out[0] = s;
+}
+__global__ void __launch_bounds__(256) k_probe_ffma2(float* out, int iters) {
+    unsigned long long a[8], m, c;
+    { float2 mm = make_float2(1.0000001f, 1.0000002f), cc = make_float2(1e-9f, 2e-9f);
+      m = *reinterpret_cast<unsigned long long*>(&mm); c = *reinterpret_cast<unsigned long long*>(&cc); }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { float2 v = make_float2((float)(threadIdx.x + i), (float)i); a[i] = *reinterpret_cast<unsigned long long*>(&v); }
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int u = 0; u < 16; ++u)
+#pragma unroll
+            for (int i = 0; i < 8; ++i) asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(a[i]) : "l"(m), "l"(c));
+    }
+    float s = 0; for (int i = 0; i < 8; ++i) { float2 v = *reinterpret_cast<float2*>(&a[i]); s += v.x + v.y; }
+    if (s == 12345.678f) out[0] = s;
+}
+
+}  // namespace b200rt
+
+// ================================================================================================
+// Host side: per-device context, scratch management, launch sequence, C ABI
+// ================================================================================================
+using namespace b200rt;
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string& msg) { g_err = msg; return code; }
+static int cuda_fail(cudaError_t e, const char* what) {
+    g_err = std::string(what) + ": " + cudaGetErrorName(e) + " (" + cudaGetErrorString(e) + ")";
+    cudaGetLastError();
+    return (int)e;
+}
+#define CK(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return cuda_fail(e__, #call); } while (0)
+
+namespace {
+
+struct Buf {
+    void* p = nullptr; size_t cap = 0;
+    cudaError_t ensure(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) { cudaError_t e = cudaFree(p); p = nullptr; cap = 0; if (e != cudaSuccess) return e; }   // cudaFree waits for the device
+        size_t want = bytes + bytes / 8;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e != cudaSuccess) { cudaGetLastError(); e = cudaMalloc(&p, bytes); want = bytes; }
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct DevCtx {
+    std::mutex mu;
+    bool init = false;
+    int sm_count = 0;
+    int isect_blocks_per_sm = 2;
+    Buf sphA, sphB, sphCol, plO, plN, plNu, plCol, lights, cmax;   // packed scene
+    Buf stage;                                                     // host-scene / host-pixel_loc staging
+    Buf rayO, rayD, hitT, hitId, hP, hN, hD, acc, occl, ctr, slow; // wavefront state
+    Buf hostResult, hostPixelLoc;                                  // b200rt_render_host device copies
+    cudaEvent_t done = nullptr; bool has_done = false;
+    void release_all() {
+        Buf* all[] = { &sphA, &sphB, &sphCol, &plO, &plN, &plNu, &plCol, &lights, &cmax, &stage, &rayO, &rayD, &hitT, &hitId,
+                       &hP, &hN, &hD, &acc, &occl, &ctr, &slow, &hostResult, &hostPixelLoc };
+        for (Buf* b : all) b->release();
+        if (done) { cudaEventDestroy(done); done = nullptr; } has_done = false; init = false;
+    }
+};
+
+constexpr int kMaxDevices = 64;
+DevCtx g_ctx[kMaxDevices];
+
+size_t isect_smem_bytes(int Spad) { return (size_t)std::min(Spad, kChunkS) * (sizeof(float4) + sizeof(float)); }
+
+size_t max_paths_per_chunk() {
+    const char* e = getenv("B200RT_MAX_PATHS");
+    if (e) { long long v = atoll(e); if (v >= 1024) return (size_t)v; }
+    return (size_t)48 << 20;
+}
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+struct Timer {            // stats mode only: per-class device time from event pairs
+    bool on = false; cudaStream_t st = nullptr;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev[3];
+    void begin(int cls) { if (!on) return; cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b); cudaEventRecord(a, st); ev[cls].push_back({a, b}); }
+    void end(int cls) { if (!on) return; cudaEventRecord(ev[cls].back().second, st); }
+    float total(int cls) { float s = 0; for (auto& p : ev[cls]) { float ms = 0; cudaEventElapsedTime(&ms, p.first, p.second); s += ms; cudaEventDestroy(p.first); cudaEventDestroy(p.second); } ev[cls].clear(); return s; }
+};
+
+int validate(const b200rt_args* a) {
+    if (!a) return fail(B200RT_E_NULL, "args is NULL");
+    if (a->struct_size != sizeof(b200rt_args)) return fail(B200RT_E_STRUCT_SIZE, "args->struct_size does not match this library (version skew)");
+    if (!a->result) return fail(B200RT_E_NULL, "args->result is NULL");
+    if (a->W <= 0 || a->H <= 0) return fail(B200RT_E_SHAPE, "W and H must be positive");
+    if ((long long)a->W * a->H > (1ll << 31)) return fail(B200RT_E_SHAPE, "W*H too large");
+    if (a->x_begin < 0 || a->x_end > a->W || a->x_begin > a->x_end) return fail(B200RT_E_SHAPE, "column tile [x_begin,x_end) outside [0,W)");
+    if (a->S < 0 || a->L < 0 || a->Pl < 0) return fail(B200RT_E_SHAPE, "negative object count");
+    if ((a->S > 0 && !a->spheres) || (a->L > 0 && !a->lights) || (a->Pl > 0 && !a->planes)) return fail(B200RT_E_NULL, "scene array pointer is NULL");
+    if (a->refl_depth < 0 || a->refl_depth > B200RT_MAX_DEPTH) return fail(B200RT_E_DEPTH, "refl_depth out of range");
+    int ndev = 0; if (cudaGetDeviceCount(&ndev) != cudaSuccess || a->device < 0 || a->device >= ndev || a->device >= kMaxDevices) { cudaGetLastError(); return fail(B200RT_E_DEVICE, "no such CUDA device"); }
+    return 0;
+}
+
+template <bool ANY>
+int launch_intersect(DevCtx& c, const SceneDev& sc, const QueueDev& q, bool nofilter, cudaStream_t st) {
+    const size_t smem = isect_smem_bytes(sc.Spad);
+    const int grid = c.sm_count * c.isect_blocks_per_sm;
+    if (nofilter) k_intersect<ANY, true><<<grid, kThreads, smem, st>>>(sc, q);
+    else          k_intersect<ANY, false><<<grid, kThreads, smem, st>>>(sc, q);
+    CK(cudaGetLastError());
+    return 0;
+}
+
+int init_ctx(DevCtx& c, int device) {
+    if (c.init) return 0;
+    cudaDeviceProp prop; CK(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) return fail(B200RT_E_DEVICE, "libb200rt is built for sm_100a (B200) only; device is sm_" + std::to_string(prop.major * 10 + prop.minor));
+    c.sm_count = prop.multiProcessorCount;
+    const int smem_max = (int)isect_smem_bytes(kChunkS);
+    CK(cudaFuncSetAttribute(k_intersect<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
+    CK(cudaFuncSetAttribute(k_intersect<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
+    CK(cudaFuncSetAttribute(k_intersect<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
+    CK(cudaFuncSetAttribute(k_intersect<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
+    CK(cudaEventCreateWithFlags(&c.done, cudaEventDisableTiming));
+    c.init = true;
+    return 0;
+}
+
+}  // namespace
+
+namespace {
+
+// The launch sequence.  `a` has DEVICE pointers for pixel_loc/result; scene pointers are host or device per flags.
+int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
+    const bool stats = a->stats != nullptr;
+    const int S = a->S, L = a->L, Pl = a->Pl;
+    const int Spad = std::max(4, (S + 3) & ~3);
+    const int depth = (int)a->refl_depth;
+    const int ns = a->aliasing ? 9 : 1;
+    const int W = a->W, H = a->H;
+    const int ncols = a->x_end - a->x_begin;
+    if (ncols == 0) { if (stats) memset(a->stats, 0, sizeof(*a->stats)); return 0; }
+
+    if (c.has_done) CK(cudaStreamWaitEvent(st, c.done, 0));      // serialise users of the shared scratch
+
+    // ---- scene: stage (if on host) and pack ----
+    CK(c.sphA.ensure(sizeof(float4) * Spad)); CK(c.sphB.ensure(sizeof(float4) * std::max(S, 1))); CK(c.sphCol.ensure(sizeof(float4) * std::max(S, 1)));
+    CK(c.plO.ensure(sizeof(float4) * std::max(Pl, 1))); CK(c.plN.ensure(sizeof(float4) * std::max(Pl, 1)));
+    CK(c.plNu.ensure(sizeof(float4) * std::max(Pl, 1))); CK(c.plCol.ensure(sizeof(float4) * std::max(Pl, 1)));
+    CK(c.lights.ensure(sizeof(float4) * std::max(L, 1))); CK(c.cmax.ensure(sizeof(float)));
+    const float *d_sph = a->spheres, *d_lig = a->lights, *d_pla = a->planes;
+    if (a->flags & B200RT_F_SCENE_ON_HOST) {
+        const size_t nS = (size_t)7 * S, nL = (size_t)3 * L, nP = (size_t)9 * Pl;
+        CK(c.stage.ensure(sizeof(float) * std::max<size_t>(nS + nL + nP, 1)));
+        float* sg = c.stage.as<float>();
+        if (nS) CK(cudaMemcpyAsync(sg, a->spheres, sizeof(float) * nS, cudaMemcpyHostToDevice, st));
+        if (nL) CK(cudaMemcpyAsync(sg + nS, a->lights, sizeof(float) * nL, cudaMemcpyHostToDevice, st));
+        if (nP) CK(cudaMemcpyAsync(sg + nS + nL, a->planes, sizeof(float) * nP, cudaMemcpyHostToDevice, st));
+        d_sph = sg; d_lig = sg + nS; d_pla = sg + nS + nL;
+    }
+    CK(cudaMemsetAsync(c.cmax.p, 0, sizeof(float), st));
+    {
+        const int nobj = std::max(std::max(Spad, Pl), L);
+        k_pack<<<(nobj + 255) / 256, 256, 0, st>>>(d_sph, S, Spad, d_pla, Pl, d_lig, L, c.sphA.as<float4>(), c.sphB.as<float4>(),
+                                                   c.sphCol.as<float4>(), c.plO.as<float4>(), c.plN.as<float4>(), c.plNu.as<float4>(),
+                                                   c.plCol.as<float4>(), c.lights.as<float4>(), c.cmax.as<float>());
+        CK(cudaGetLastError());
+    }
+    SceneDev sc{ c.sphA.as<float4>(), c.sphB.as<float4>(), c.sphCol.as<float4>(), c.plO.as<float4>(), c.plN.as<float4>(),
+                 c.plNu.as<float4>(), c.plCol.as<float4>(), c.lights.as<float4>(), c.cmax.as<float>(), S, Spad, Pl, L };
+
+    // ---- chunking: whole columns, <= max_paths slots per chunk ----
+    const size_t per_col = (size_t)ns * H;
+    size_t cols_per_chunk = std::max<size_t>(1, max_paths_per_chunk() / per_col);
+    cols_per_chunk = std::min<size_t>(cols_per_chunk, (size_t)ncols);
+    const int nchunks = (int)((ncols + cols_per_chunk - 1) / cols_per_chunk);
+    const size_t cap = cols_per_chunk * per_col;                 // slots per chunk
+    CK(c.rayO.ensure(sizeof(float4) * cap)); CK(c.rayD.ensure(sizeof(float4) * cap));
+    CK(c.hitT.ensure(sizeof(float) * cap)); CK(c.hitId.ensure(sizeof(int) * cap));
+    CK(c.hP.ensure(sizeof(float4) * cap)); CK(c.hN.ensure(sizeof(float4) * cap)); CK(c.hD.ensure(sizeof(float4) * cap));
+    CK(c.acc.ensure(sizeof(float) * 3 * cap)); CK(c.occl.ensure(std::max<size_t>(cap * (size_t)L, 1)));
+    const int ctr_stride = 4 * (depth + 2);
+    CK(c.ctr.ensure(sizeof(uint32_t) * (size_t)ctr_stride * nchunks)); CK(c.slow.ensure(sizeof(unsigned long long)));
+    CK(cudaMemsetAsync(c.ctr.p, 0, sizeof(uint32_t) * (size_t)ctr_stride * nchunks, st));
+    CK(cudaMemsetAsync(c.slow.p, 0, sizeof(unsigned long long), st));
+
+    {   // persistent grid for the intersection kernels
+        int nb = 0; CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_intersect<false, false>, kThreads, isect_smem_bytes(Spad)));
+        c.isect_blocks_per_sm = std::max(1, nb);
+    }
+    const bool nofilter = (a->flags & B200RT_F_NO_FILTER) != 0;
+    const int small_grid = c.sm_count * 8;
+    Timer tm; tm.on = stats; tm.st = st;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    if (stats) { CK(cudaEventCreate(&ev0)); CK(cudaEventCreate(&ev1)); CK(cudaEventRecord(ev0, st)); }
+
+    std::vector<float> wts(depth + 1);
+    for (int d = 0; d <= depth; ++d) wts[d] = d == 0 ? 1.0f : (float)pow(a->refl, (double)d);     // trace.py:131 refl ** (i+1)
+
+    for (int ch = 0; ch < nchunks; ++ch) {
+        FrameDev f{};
+        f.pixel_loc = a->pixel_loc; f.gf = a->grid.f; f.gar = a->grid.ar; f.gsy = a->grid.sy; f.gsz = a->grid.sz;
+        f.ox = a->cam_origin[0]; f.oy = a->cam_origin[1]; f.oz = a->cam_origin[2];
+        for (int i = 0; i < 9; ++i) f.rot[i] = a->cam_rot[i];
+        f.W = W; f.H = H; f.ns = ns;
+        f.x0 = a->x_begin + (int)(ch * cols_per_chunk); f.x1 = std::min(a->x_end, f.x0 + (int)cols_per_chunk);
+        f.npix = (uint32_t)(f.x1 - f.x0) * (uint32_t)H;
+        const size_t nslots = (size_t)f.npix * ns;
+        uint32_t* ctr = c.ctr.as<uint32_t>() + (size_t)ch * ctr_stride;
+        float* accR = c.acc.as<float>(); float* accG = accR + cap; float* accB = accG + cap;
+
+        tm.begin(2);
+        CK(cudaMemsetAsync(accR, 0, sizeof(float) * nslots, st));
+        CK(cudaMemsetAsync(accG, 0, sizeof(float) * nslots, st));
+        CK(cudaMemsetAsync(accB, 0, sizeof(float) * nslots, st));
+        k_raygen<<<(int)std::min<size_t>((nslots + 255) / 256, (size_t)small_grid), 256, 0, st>>>(f, c.rayO.as<float4>(), c.rayD.as<float4>(), ctr + 0);
+        CK(cudaGetLastError());
+        tm.end(2);
+
+        for (int d = 0; d <= depth; ++d) {
+            uint32_t* cd = ctr + 4 * d;             // [0] n_live, [1] n_hit, [2] work(closest), [3] work(shadow)
+            QueueDev q{};
+            q.rayO = c.rayO.as<float4>(); q.rayD = c.rayD.as<float4>(); q.hP = c.hP.as<float4>();
+            q.hit_t = c.hitT.as<float>(); q.hit_id = c.hitId.as<int>(); q.occl = c.occl.as<uint8_t>();
+            q.slow = stats ? c.slow.as<unsigned long long>() : nullptr;
+            ShadeDev s{};
+            s.rayO = c.rayO.as<float4>(); s.rayD = c.rayD.as<float4>(); s.hit_t = c.hitT.as<float>(); s.hit_id = c.hitId.as<int>();
+            s.hP = c.hP.as<float4>(); s.hN = c.hN.as<float4>(); s.hD = c.hD.as<float4>(); s.occl = c.occl.as<uint8_t>();
+            s.accR = accR; s.accG = accG; s.accB = accB;
+            s.n_live = cd + 0; s.n_hit = cd + 1; s.n_next = cd + 4;
+            s.amb = (float)a->amb; s.lamb = (float)a->lamb; s.weight = wts[d]; s.emit_reflection = d < depth;
+
+            tm.begin(0);
+            q.n_in = cd + 0; q.work = cd + 2;
+            { int rc = launch_intersect<false>(c, sc, q, nofilter, st); if (rc) return rc; }
+            tm.end(0);
+            tm.begin(2);
+            k_setup<<<small_grid, 256, 0, st>>>(sc, s); CK(cudaGetLastError());
+            tm.end(2);
+            if (L > 0) {
+                tm.begin(1);
+                q.n_in = cd + 1; q.work = cd + 3;
+                { int rc = launch_intersect<true>(c, sc, q, nofilter, st); if (rc) return rc; }
+                tm.end(1);
+            }
+            tm.begin(2);
+            k_shade<<<small_grid, 256, 0, st>>>(sc, s); CK(cudaGetLastError());
+            tm.end(2);
+        }
+
+        tm.begin(2);
+        const int unswap = (a->flags & B200RT_F_UNSWAP_GB) ? 1 : 0;
+        const size_t tile_off = (size_t)f.x0 * H;
+        const bool al16 = (H % 16 == 0) && (((uintptr_t)a->result + tile_off) % 16 == 0) && (((size_t)W * H) % 16 == 0);
+        const bool al4 = (H % 4 == 0) && (((uintptr_t)a->result + tile_off) % 4 == 0) && (((size_t)W * H) % 4 == 0);
+        if (al16)      k_resolve<16><<<std::min<int>((f.npix / 16 + 255) / 256, small_grid), 256, 0, st>>>(f, accR, accG, accB, a->result, a->aliasing, unswap);
+        else if (al4)  k_resolve<4><<<std::min<int>((f.npix / 4 + 255) / 256, small_grid), 256, 0, st>>>(f, accR, accG, accB, a->result, a->aliasing, unswap);
+        else           k_resolve<1><<<std::min<int>((f.npix + 255) / 256, small_grid), 256, 0, st>>>(f, accR, accG, accB, a->result, a->aliasing, unswap);
+        CK(cudaGetLastError());
+        tm.end(2);
+    }
+    CK(cudaEventRecord(c.done, st)); c.has_done = true;
+
+    if (stats) {
+        CK(cudaEventRecord(ev1, st));
+        CK(cudaStreamSynchronize(st));
+        std::vector<uint32_t> h((size_t)ctr_stride * nchunks);
+        CK(cudaMemcpy(h.data(), c.ctr.p, sizeof(uint32_t) * h.size(), cudaMemcpyDeviceToHost));
+        b200rt_stats out{}; 
+        for (int ch = 0; ch < nchunks; ++ch)
+            for (int d = 0; d <= depth; ++d) {
+                const uint32_t* cd = h.data() + (size_t)ch * ctr_stride + 4 * d;
+                if (d == 0) out.primary += cd[0]; else out.bounce += cd[0];
+                out.shadow += (uint64_t)cd[1] * (uint64_t)L;
+            }
+        unsigned long long slow = 0; CK(cudaMemcpy(&slow, c.slow.p, sizeof(slow), cudaMemcpyDeviceToHost));
+        out.slow_path = slow;
+        CK(cudaEventElapsedTime(&out.kernel_ms[0], ev0, ev1));
+        out.kernel_ms[1] = tm.total(0); out.kernel_ms[2] = tm.total(1); out.kernel_ms[3] = tm.total(2);
+        cudaEventDestroy(ev0); cudaEventDestroy(ev1);
+        *a->stats = out;
+    }
+    return 0;
+}
+
+}  // namespace
+
+// ================================================================================================
+// C ABI (include/b200rt.h)
+// ================================================================================================
+extern "C" {
+
+B200RT_API int b200rt_version(void) { return B200RT_VERSION; }
+B200RT_API const char* b200rt_last_error(void) { return g_err.c_str(); }
+B200RT_API uint32_t b200rt_args_size(void) { return (uint32_t)sizeof(b200rt_args); }
+
+B200RT_API int b200rt_device_count(void) {
+    int n = 0; if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; } return n;
+}
+B200RT_API int b200rt_sm_count(int device) {
+    int n = 0; if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) { cudaGetLastError(); return 0; } return n;
+}
+
+B200RT_API int b200rt_render(const b200rt_args* a) {
+    if (int rc = validate(a)) return rc;
+    DeviceGuard guard(a->device);
+    DevCtx& c = g_ctx[a->device];
+    std::lock_guard<std::mutex> lock(c.mu);
+    if (int rc = init_ctx(c, a->device)) return rc;
+    return render_device(c, a, (cudaStream_t)a->stream);
+}
+
+B200RT_API int b200rt_render_host(const b200rt_args* a) {
+    if (int rc = validate(a)) return rc;
+    DeviceGuard guard(a->device);
+    DevCtx& c = g_ctx[a->device];
+    std::lock_guard<std::mutex> lock(c.mu);
+    if (int rc = init_ctx(c, a->device)) return rc;
+    cudaStream_t st = (cudaStream_t)a->stream;
+    const size_t WH = (size_t)a->W * a->H;
+    b200rt_args d = *a;
+    d.flags |= B200RT_F_SCENE_ON_HOST;
+    if (a->pixel_loc) {                                           // reference src/main.py:29
+        CK(c.hostPixelLoc.ensure(sizeof(double) * 3 * WH));
+        if (c.has_done) CK(cudaStreamWaitEvent(st, c.done, 0));
+        CK(cudaMemcpyAsync(c.hostPixelLoc.p, a->pixel_loc, sizeof(double) * 3 * WH, cudaMemcpyHostToDevice, st));
+        d.pixel_loc = c.hostPixelLoc.as<double>();
+    }
+    CK(c.hostResult.ensure(3 * WH));                              // src/main.py:32 (only the tile is written / read back)
+    d.result = c.hostResult.as<uint8_t>();
+    if (int rc = render_device(c, &d, st)) return rc;
+    const size_t off = (size_t)a->x_begin * a->H, len = (size_t)(a->x_end - a->x_begin) * a->H;
+    if (len) {
+        if (len == WH) CK(cudaMemcpyAsync(a->result, d.result, 3 * WH, cudaMemcpyDeviceToHost, st));      // src/main.py:51
+        else for (int ch = 0; ch < 3; ++ch)
+            CK(cudaMemcpyAsync(a->result + ch * WH + off, d.result + ch * WH + off, len, cudaMemcpyDeviceToHost, st));
+    }
+    CK(cudaStreamSynchronize(st));
+    return 0;
+}
+
+B200RT_API int b200rt_fp32_probe(int device, double* ffma_tflops, double* ffma2_tflops, double* sm_mhz) {
+    int ndev = b200rt_device_count();
+    if (device < 0 || device >= ndev) return fail(B200RT_E_DEVICE, "no such CUDA device");
+    DeviceGuard guard(device);
+    int sms = b200rt_sm_count(device);
+    float* out = nullptr; unsigned long long* clk = nullptr;
+    CK(cudaMalloc(&out, 64)); CK(cudaMalloc(&clk, 16));
+    cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    const int grid = sms * 8, iters = 4096;                      // 8 CTAs x 256 threads per SM = full occupancy
+    const double fma_per_thread = (double)iters * 16 * 8;
+    double best1 = 0, best2 = 0, mhz = 0;
+    for (int rep = 0; rep < 5; ++rep) {
+        float ms = 0;
+        CK(cudaEventRecord(e0)); k_probe_ffma<<<grid, 256>>>(out, iters, clk); CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1));
+        CK(cudaEventElapsedTime(&ms, e0, e1));
+        double tf = 2.0 * fma_per_thread * grid * 256 / (ms * 1e-3) / 1e12; 
+        unsigned long long hc[2]; CK(cudaMemcpy(hc, clk, 16, cudaMemcpyDeviceToHost));
+        if (tf > best1) { best1 = tf; if (hc[1]) mhz = (double)hc[0] / (double)hc[1] * 1e3; }
+        CK(cudaEventRecord(e0)); k_probe_ffma2<<<grid, 256>>>(out, iters); CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1));
+        CK(cudaEventElapsedTime(&ms, e0, e1));
+        tf = 2.0 * 2.0 * fma_per_thread * grid * 256 / (ms * 1e-3) / 1e12;
+        if (tf > best2) best2 = tf;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(out); cudaFree(clk);
+    if (ffma_tflops) *ffma_tflops = best1;
+    if (ffma2_tflops) *ffma2_tflops = best2;
+    if (sm_mhz) *sm_mhz = mhz;
+    return 0;
+}
+
+B200RT_API int b200rt_shutdown(void) {
+    int ndev = b200rt_device_count();
+    for (int dev = 0; dev < ndev && dev < kMaxDevices; ++dev) {
+        DevCtx& c = g_ctx[dev];
+        std::lock_guard<std::mutex> lock(c.mu);
+        if (!c.init) continue;
+        DeviceGuard guard(dev);
+        cudaDeviceSynchronize();
+        c.release_all();
+    }
+    return 0;
+}
+
+}  // extern "C"

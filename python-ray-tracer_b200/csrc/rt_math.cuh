@@ -1,0 +1,83 @@
+// rt_math.cuh — FP32 device math of the render path, written with explicit rounding intrinsics so that
+// every kernel that inlines these helpers performs bit-identical arithmetic (no compiler-chosen FMA
+// contraction; IEEE div/sqrt — the reference kernel is compiled without fast-math).
+//
+// Reference semantics restated here (all under /root/reference/src/ray_tracing/):
+//   common.py:10-49   linear_comb / vector_difference / normalize / dot / matmul
+//   common.py:52-63   clip_color / clip_color_vector (round-half-even, R,B,G wiring)
+//   intersections.py:6-68  ray-sphere / ray-plane
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b200rt {
+
+constexpr float kBias  = 0.0002f;   // trace.py:82
+constexpr float kEps   = 0.001f;    // intersections.py:46
+constexpr float kTMax  = 999.0f;    // trace.py:17
+
+struct V3 { float x, y, z; };
+
+__device__ __forceinline__ V3 mk(float x, float y, float z) { V3 v; v.x = x; v.y = y; v.z = z; return v; }
+__device__ __forceinline__ float dot3(V3 a, V3 b) {
+    return fmaf(a.x, b.x, fmaf(a.y, b.y, __fmul_rn(a.z, b.z)));
+}
+__device__ __forceinline__ V3 sub3(V3 a, V3 b) { return mk(__fsub_rn(a.x, b.x), __fsub_rn(a.y, b.y), __fsub_rn(a.z, b.z)); }
+// a + s*b
+__device__ __forceinline__ V3 madd3(V3 a, float s, V3 b) { return mk(fmaf(s, b.x, a.x), fmaf(s, b.y, a.y), fmaf(s, b.z, a.z)); }
+// common.py:28-32 — divide by the norm (IEEE sqrt + div), no zero guard
+__device__ __forceinline__ V3 normalize3(V3 v) {
+    float n = __fsqrt_rn(dot3(v, v));
+    return mk(__fdiv_rn(v.x, n), __fdiv_rn(v.y, n), __fdiv_rn(v.z, n));
+}
+
+// common.py:52-57: min(max(0, int(round(c))), 255) with round-half-to-even (cvt.rni), SURVEY F4
+__device__ __forceinline__ uint32_t clip_color(float c) {
+    int v = __float2int_rn(c);          // NaN -> 0, saturates at INT_MIN/INT_MAX
+    v = max(0, min(255, v));
+    return (uint32_t)v;
+}
+
+// Exact (robust) FP32 ray-sphere test, unit direction.  Restates intersections.py:6-38 with a == 1:
+//   reference  t = (-b -/+ sqrt(b^2 - 4c)) / 2,  b = 2 (O-C).D,  c = |O-C|^2 - r^2
+// evaluated as tc = (C-O).D, disc = r^2 - |(C-O) - tc D|^2 (perpendicular-distance form: no catastrophic
+// cancellation between b^2 and c when the origin is far from a small sphere), t = tc -/+ sqrt(disc).
+// Returns t > 0 (near root if positive, else far root if positive — origin inside the sphere), or -1.
+__device__ __forceinline__ float sphere_exact(V3 O, V3 D, float cx, float cy, float cz, float r2) {
+    V3 Lc = mk(__fsub_rn(cx, O.x), __fsub_rn(cy, O.y), __fsub_rn(cz, O.z));
+    float tc = dot3(Lc, D);
+    V3 v = mk(fmaf(-tc, D.x, Lc.x), fmaf(-tc, D.y, Lc.y), fmaf(-tc, D.z, Lc.z));
+    float disc = __fsub_rn(r2, dot3(v, v));
+    if (!(disc >= 0.0f)) return -1.0f;                 // intersections.py:25-26
+    float sq = __fsqrt_rn(disc);
+    float t = __fsub_rn(tc, sq);                       // :28-31
+    if (t > 0.0f) return t;
+    t = __fadd_rn(tc, sq);                             // :33-36
+    return (t > 0.0f) ? t : -1.0f;
+}
+
+// intersections.py:41-68.  (ox,oy,oz) plane point, (nx,ny,nz) stored normal (not re-normalised here).
+__device__ __forceinline__ float plane_exact(V3 O, V3 D, float4 po, float4 pn) {
+    V3 n = mk(pn.x, pn.y, pn.z);
+    float denom = dot3(D, n);
+    if (fabsf(denom) < kEps) return -1.0f;
+    V3 LP = mk(__fsub_rn(po.x, O.x), __fsub_rn(po.y, O.y), __fsub_rn(po.z, O.z));
+    float t = __fdiv_rn(dot3(LP, n), denom);
+    return (t > 0.0f) ? t : -1.0f;
+}
+
+__device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
+
+// Warp-aggregated append: returns this lane's slot in a queue whose length lives at *counter.
+__device__ __forceinline__ uint32_t warp_append(bool valid, uint32_t* counter) {
+    uint32_t mask = __ballot_sync(0xffffffffu, valid);
+    uint32_t base = 0;
+    if (mask) {
+        int leader = __ffs(mask) - 1;
+        if ((int)lane_id() == leader) base = atomicAdd(counter, (uint32_t)__popc(mask));
+        base = __shfl_sync(0xffffffffu, base, leader);
+    }
+    return base + __popc(mask & ((1u << lane_id()) - 1u));
+}
+
+}  // namespace b200rt
