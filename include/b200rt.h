@@ -93,6 +93,11 @@ typedef struct b200rt_args {
     int32_t  aliasing;             /* argument 12 (bool)                                                         */
     int32_t  reserved1;
 
+    /* Multi-GPU interleaving: when strip_width > 0 the tile [x_begin,x_end) is cut into strips of
+     * strip_width columns and only strips i with i % strip_world == strip_rank are rendered (one wavefront for
+     * all of them).  strip_width == 0 renders the whole tile.  Pixels outside the selected strips are untouched. */
+    int32_t  strip_width, strip_rank, strip_world, reserved2;
+
     b200rt_stats* stats;           /* optional HOST pointer; non-NULL makes the call synchronous and fills it    */
 } b200rt_args;
 

@@ -35,6 +35,7 @@ class Args(C.Structure):
         ("planes", C.c_void_p), ("Pl", C.c_int32),
         ("amb", C.c_double), ("lamb", C.c_double), ("refl", C.c_double),
         ("refl_depth", C.c_int64), ("aliasing", C.c_int32), ("reserved1", C.c_int32),
+        ("strip_width", C.c_int32), ("strip_rank", C.c_int32), ("strip_world", C.c_int32), ("reserved2", C.c_int32),
         ("stats", C.POINTER(Stats)),
     ]
 

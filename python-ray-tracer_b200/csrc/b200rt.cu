@@ -85,10 +85,19 @@ struct FrameDev {
     double ox, oy, oz;             // camera origin
     double rot[9];                 // camera rotation, row-major
     int W, H;
-    int x0, x1;                    // chunk columns [x0, x1)
+    int x0, x1;                    // chunk LOCAL columns [x0, x1) (local = index among the columns this call renders)
+    int xb;                        // tile origin: global x of local column 0
+    int sw, srank, sworld;         // interleaved strips (sw == 0: contiguous tile)
     int ns;                        // samples per pixel slot: 1 or 9
     uint32_t npix;                 // (x1-x0)*H
 };
+
+// local column -> global x (array axis 1)
+__device__ __forceinline__ int col_x(const FrameDev& f, int lc) {
+    if (f.sw <= 0) return f.xb + lc;
+    const int s = lc / f.sw;
+    return f.xb + (s * f.sworld + f.srank) * f.sw + (lc - s * f.sw);
+}
 
 // pixel_loc[c, x, y] with the GPU's unchecked C-order flat addressing: elements past the end
 // of the buffer are defined as 0.0.
@@ -118,7 +127,7 @@ __global__ void k_raygen(FrameDev f, float4* __restrict__ rayO, float4* __restri
         float4 o = make_float4(0, 0, 0, 0), d = make_float4(0, 0, 0, 0);
         if (valid) {
             uint32_t k = slot / f.npix, p = slot - k * f.npix;
-            int x = f.x0 + (int)(p / (uint32_t)f.H), y = (int)(p % (uint32_t)f.H);
+            int x = col_x(f, f.x0 + (int)(p / (uint32_t)f.H)), y = (int)(p % (uint32_t)f.H);
             if (k > 0 && !(x >= 1 && y >= 1)) valid = false;          // kernels.py:29
             if (valid) {
                 double px = pl_at(f, 0, x, y), py = pl_at(f, 1, x, y), pz = pl_at(f, 2, x, y);
@@ -382,7 +391,7 @@ __global__ void k_resolve(FrameDev f, const float* __restrict__ accR, const floa
 #pragma unroll
         for (int e = 0; e < VEC; ++e) {
             const uint32_t p = v * VEC + e;
-            const int x = f.x0 + (int)(p / (uint32_t)f.H), y = (int)(p % (uint32_t)f.H);
+            const int x = col_x(f, f.x0 + (int)(p / (uint32_t)f.H)), y = (int)(p % (uint32_t)f.H);
             float R = accR[p], G = accG[p], B = accB[p];
             if (aliasing && x >= 1 && y >= 1) {                                        // kernels.py:29
                 for (int k = 1; k < 9; ++k) {
@@ -395,7 +404,8 @@ __global__ void k_resolve(FrameDev f, const float* __restrict__ accR, const floa
             out1[e] = unswap ? clip_color(G) : clip_color(B);                           // common.py:60-63
             out2[e] = unswap ? clip_color(B) : clip_color(G);
         }
-        const size_t o = (size_t)f.x0 * f.H + (size_t)v * VEC;
+        const uint32_t p0 = v * VEC;                                  // H % VEC == 0: a vector never straddles columns
+        const size_t o = (size_t)col_x(f, f.x0 + (int)(p0 / (uint32_t)f.H)) * f.H + (p0 % (uint32_t)f.H);
         uint8_t* d0 = result + o; uint8_t* d1 = result + WH + o; uint8_t* d2 = result + 2 * WH + o;
         if constexpr (VEC == 1) { d0[0] = (uint8_t)out0[0]; d1[0] = (uint8_t)out1[0]; d2[0] = (uint8_t)out2[0]; }
         else {
@@ -540,6 +550,8 @@ int validate(const b200rt_args* a) {
     if (a->W <= 0 || a->H <= 0) return fail(B200RT_E_SHAPE, "W and H must be positive");
     if ((long long)a->W * a->H > (1ll << 31)) return fail(B200RT_E_SHAPE, "W*H too large");
     if (a->x_begin < 0 || a->x_end > a->W || a->x_begin > a->x_end) return fail(B200RT_E_SHAPE, "column tile [x_begin,x_end) outside [0,W)");
+    if (a->strip_width < 0 || (a->strip_width > 0 && (a->strip_world <= 0 || a->strip_rank < 0 || a->strip_rank >= a->strip_world)))
+        return fail(B200RT_E_SHAPE, "bad strip_width/strip_rank/strip_world");
     if (a->S < 0 || a->L < 0 || a->Pl < 0) return fail(B200RT_E_SHAPE, "negative object count");
     if ((a->S > 0 && !a->spheres) || (a->L > 0 && !a->lights) || (a->Pl > 0 && !a->planes)) return fail(B200RT_E_NULL, "scene array pointer is NULL");
     if (a->refl_depth < 0 || a->refl_depth > B200RT_MAX_DEPTH) return fail(B200RT_E_DEPTH, "refl_depth out of range");
@@ -584,7 +596,13 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     const int depth = (int)a->refl_depth;
     const int ns = a->aliasing ? 9 : 1;
     const int W = a->W, H = a->H;
-    const int ncols = a->x_end - a->x_begin;
+    const int span = a->x_end - a->x_begin;
+    int ncols = span;                                            // columns this call renders
+    if (a->strip_width > 0) {
+        const int sw = a->strip_width, period = sw * a->strip_world;
+        const int full = span / period, rem = span % period;
+        ncols = full * sw + std::max(0, std::min(sw, rem - a->strip_rank * sw));
+    }
     if (ncols == 0) { if (stats) memset(a->stats, 0, sizeof(*a->stats)); return 0; }
 
     if (c.has_done) CK(cudaStreamWaitEvent(st, c.done, 0));      // serialise users of the shared scratch
@@ -649,7 +667,8 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         f.ox = a->cam_origin[0]; f.oy = a->cam_origin[1]; f.oz = a->cam_origin[2];
         for (int i = 0; i < 9; ++i) f.rot[i] = a->cam_rot[i];
         f.W = W; f.H = H; f.ns = ns;
-        f.x0 = a->x_begin + (int)(ch * cols_per_chunk); f.x1 = std::min(a->x_end, f.x0 + (int)cols_per_chunk);
+        f.x0 = (int)(ch * cols_per_chunk); f.x1 = std::min(ncols, f.x0 + (int)cols_per_chunk);
+        f.xb = a->x_begin; f.sw = a->strip_width; f.srank = a->strip_rank; f.sworld = a->strip_world;
         f.npix = (uint32_t)(f.x1 - f.x0) * (uint32_t)H;
         const size_t nslots = (size_t)f.npix * ns;
         uint32_t* ctr = c.ctr.as<uint32_t>() + (size_t)ch * ctr_stride;
@@ -696,9 +715,8 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
 
         tm.begin(2);
         const int unswap = (a->flags & B200RT_F_UNSWAP_GB) ? 1 : 0;
-        const size_t tile_off = (size_t)f.x0 * H;
-        const bool al16 = (H % 16 == 0) && (((uintptr_t)a->result + tile_off) % 16 == 0) && (((size_t)W * H) % 16 == 0);
-        const bool al4 = (H % 4 == 0) && (((uintptr_t)a->result + tile_off) % 4 == 0) && (((size_t)W * H) % 4 == 0);
+        const bool al16 = (H % 16 == 0) && (((uintptr_t)a->result) % 16 == 0);     // every column start is then 16-byte aligned
+        const bool al4 = (H % 4 == 0) && (((uintptr_t)a->result) % 4 == 0);
         if (al16)      k_resolve<16><<<std::min<int>((f.npix / 16 + 255) / 256, small_grid), 256, 0, st>>>(f, accR, accG, accB, a->result, a->aliasing, unswap);
         else if (al4)  k_resolve<4><<<std::min<int>((f.npix / 4 + 255) / 256, small_grid), 256, 0, st>>>(f, accR, accG, accB, a->result, a->aliasing, unswap);
         else           k_resolve<1><<<std::min<int>((f.npix + 255) / 256, small_grid), 256, 0, st>>>(f, accR, accG, accB, a->result, a->aliasing, unswap);
@@ -775,11 +793,16 @@ B200RT_API int b200rt_render_host(const b200rt_args* a) {
     CK(c.hostResult.ensure(3 * WH));                              // src/main.py:32 (only the tile is written / read back)
     d.result = c.hostResult.as<uint8_t>();
     if (int rc = render_device(c, &d, st)) return rc;
-    const size_t off = (size_t)a->x_begin * a->H, len = (size_t)(a->x_end - a->x_begin) * a->H;
-    if (len) {
-        if (len == WH) CK(cudaMemcpyAsync(a->result, d.result, 3 * WH, cudaMemcpyDeviceToHost, st));      // src/main.py:51
-        else for (int ch = 0; ch < 3; ++ch)
-            CK(cudaMemcpyAsync(a->result + ch * WH + off, d.result + ch * WH + off, len, cudaMemcpyDeviceToHost, st));
+    const int sw = a->strip_width > 0 ? a->strip_width : std::max(1, a->x_end - a->x_begin);
+    const int world = a->strip_width > 0 ? a->strip_world : 1, srank = a->strip_width > 0 ? a->strip_rank : 0;
+    if (a->x_end - a->x_begin == a->W && world == 1) {
+        CK(cudaMemcpyAsync(a->result, d.result, 3 * WH, cudaMemcpyDeviceToHost, st));                     // src/main.py:51
+    } else {
+        for (int xs = a->x_begin + srank * sw; xs < a->x_end; xs += sw * world) {                          // each rendered strip
+            const size_t off = (size_t)xs * a->H, len = (size_t)(std::min(a->x_end, xs + sw) - xs) * a->H;
+            for (int ch = 0; ch < 3; ++ch)
+                CK(cudaMemcpyAsync(a->result + ch * WH + off, d.result + ch * WH + off, len, cudaMemcpyDeviceToHost, st));
+        }
     }
     CK(cudaStreamSynchronize(st));
     return 0;
