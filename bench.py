@@ -32,11 +32,7 @@ for p in (ROOT, os.path.join(ROOT, "python-ray-tracer_b200")):
 
 import numpy as np  # noqa: E402
 
-STRIP = 32           # columns per interleaved strip
-
-
-def strips_for_rank(W, rank, world):
-    return [(x0, min(W, x0 + STRIP)) for i, x0 in enumerate(range(0, W, STRIP)) if i % world == rank]
+STRIP = 16           # columns per interleaved strip (multi-GPU load balance)
 
 
 class ClockSampler(threading.Thread):
@@ -101,3 +97,181 @@ def oracle_sample(w, seconds_target=15.0, threads=0):
     t, rays = run(nx2, ny2)
     return dict(value=rays / t / 1e6, unit="Mrays/s", cores=cores, kind="port",
                 sample=f"{nx2}x{ny2} px window at ({x0},{y0}) of the {W}x{H} frame, {rays} rays in {t:.1f} s", seconds=t)
+
+
+def run_reference(args, w):
+    """--impl reference: the CPU port of the reference path on all host threads, bounded sample per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    per_step = max(2.0, min(20.0, 60.0 / max(1, args.steps + args.warmup)))
+    res = None
+    vals = []
+    for i in range(args.warmup + args.steps):
+        res = oracle_sample(w, seconds_target=per_step)
+        if i >= args.warmup:
+            vals.append(res)
+    rays = sum(float(v["value"]) * v["seconds"] for v in vals)
+    secs = sum(v["seconds"] for v in vals)
+    value = rays / secs
+    cam = w["cameras"][0]
+    line = {"impl": "reference", "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / max(1, len(vals)),
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": w["label"], "resolution": list(cam.resolution)},
+            "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": res["cores"], "kind": "port", "sample": res["sample"]},
+            "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args, w):
+    import torch
+    import torch.distributed as dist
+    from b200rt import _lib, render_host, fp32_probe
+    from b200rt.ray_tracing import render
+    from b200rt.workloads import flops_per_ray
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier(device_ids=[local])
+        torch.cuda.synchronize()
+
+    cams = w["cameras"]
+    cam = cams[0]
+    W, H = cam.resolution
+    sp_h, li_h, pl_h = w["scene"].generate_scene()
+    S, L, Pl = sp_h.shape[1], li_h.shape[1], pl_h.shape[1]
+    spheres, lights, planes = [torch.from_numpy(a).to(dev) for a in (sp_h, li_h, pl_h)]
+    result = torch.zeros((3, W, H), dtype=torch.uint8, device=dev)
+    strips = (STRIP, rank, world) if world > 1 else None
+    shade = (w["amb"], w["lamb"], w["refl"], w["refl_depth"], w["aliasing"])
+    stream = torch.cuda.current_stream(dev)
+
+    from b200rt.cuda import pixel_grid
+    grids = [pixel_grid(c, local) for c in cams]               # closed-form pixel grid: no 24*W*H-byte array
+
+    def frame(k=0, stats=False):
+        c = cams[k % len(cams)]
+        ln = render.configure(stream=stream, strips=strips, stats=stats)
+        ln(grids[k % len(cams)], result, c.position, c.rotation, spheres, lights, planes, *shade)
+        return ln.stats
+
+    # one instrumented frame: ray counts (deterministic) and per-kernel-class device time
+    st = frame(0, stats=True)
+    rays_rank = torch.tensor([st["primary"], st["shadow"], st["bounce"]], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(rays_rank)
+    rays_total = float(rays_rank.sum().item())
+    for i in range(args.warmup):
+        frame(i)
+    sampler = ClockSampler(local); sampler.start()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for i in range(args.steps):
+        frame(i)
+    e1.record(stream)
+    barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_step = float(ms.item()) / args.steps
+    sampler.stop_flag = True; sampler.join(timeout=2)
+
+    # kernel-class times of an instrumented frame after warm-up (dominant kernel = k_intersect, both variants)
+    st2 = frame(0, stats=True)
+    isect_ms = st2["ms_closest"] + st2["ms_shadow"]
+    rays_this_rank = st2["rays"]
+
+    # end to end: host buffers through b200rt_render_host, copies inside the timed region; N>1: + NCCL gather of strips
+    host_out = np.zeros((3, W, H), dtype=np.uint8)
+    h2d = sp_h.nbytes + li_h.nbytes + pl_h.nbytes
+    ncols_rank = sum(min(W, x0 + STRIP) - x0 for i, x0 in enumerate(range(0, W, STRIP)) if i % world == rank) if world > 1 else W
+    d2h = 3 * ncols_rank * H
+
+    def frame_e2e(k=0):
+        c = cams[k % len(cams)]
+        render_host(None, c.position, c.rotation, sp_h, li_h, pl_h, *shade, grid=c.grid(), shape=(W, H), out=host_out,
+                    device=local, strips=strips)
+
+    frame_e2e(0)
+    barrier()
+    t0 = time.perf_counter()
+    n_e2e = max(1, min(args.steps, 5))
+    for i in range(n_e2e):
+        frame_e2e(i)
+    barrier()
+    e2e_ms = torch.tensor([(time.perf_counter() - t0) * 1e3 / n_e2e], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
+    e2e_ms = float(e2e_ms.item())
+
+    if rank == 0:
+        probe = fp32_probe(local)
+        sms = _lib.lib().b200rt_sm_count(local)
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
+        sm_max = float(peaks.get("sm_max_mhz", 1965.0))
+        nominal_tf = 2.0 * 128 * sms * sm_max * 1e6 / 1e12
+        fpr = flops_per_ray(S, Pl)
+        ach_tf = rays_this_rank * fpr / (isect_ms * 1e-3) / 1e12
+        clocks = sampler.summary()
+        depth = w["refl_depth"]
+        launches_per_frame = 2 + (depth + 1) * (3 + (1 if L > 0 else 0)) + 1        # pack, raygen, per depth closest/setup/shadow/shade, resolve
+        line = {
+            "metric": "Mrays/s", "value": rays_total / (ms_step * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": w["label"], "resolution": [W, H], "spheres": S, "planes": Pl, "lights": L,
+                       "refl_depth": depth, "aliasing": bool(w["aliasing"]), "rays_per_frame": rays_total,
+                       "rays_per_pixel": rays_total / (W * H), "parallelism": f"column strips of {STRIP} interleaved over {world} GPU(s)" if world > 1 else "1 GPU, whole frame",
+                       "l2": "working set (ray queues, ~100 B/path x %.1f M paths) exceeds the 126 MB L2; no flush needed" % (W * H * (9 if w["aliasing"] else 1) / world / 1e6)},
+            "e2e": {"value": rays_total / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": e2e_ms,
+                    "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
+            "gpu_launches": int(launches_per_frame * args.steps),
+            "clocks": clocks,
+            "roofline": {"bound": "fp32", "kernel": "k_intersect (closest + shadow)", "achieved": ach_tf, "peak": nominal_tf,
+                         "unit": "TFLOP/s", "frac": ach_tf / nominal_tf, "traffic": None,
+                         "peak_def": f"2 FLOP x 128 lanes x {sms} SMs x {sm_max:.0f} MHz (nominal max clock; MEASURED_PEAKS has no FP32 entry)",
+                         "peak_measured_ffma": probe["ffma_tflops"], "peak_measured_ffma2": probe["ffma2_tflops"],
+                         "probe_sm_mhz": probe["sm_mhz"], "frac_of_measured_ffma": ach_tf / max(probe["ffma_tflops"], 1e-9),
+                         "algorithmic_flops_per_ray": fpr, "kernel_ms_per_frame": isect_ms, "kernel_share_of_frame": isect_ms / st2["ms_total"],
+                         "slow_path_entries_per_ray": st2["slow_path"] / max(1, rays_this_rank),
+                         "framebuffer_write_gbs": 3.0 * W * H / world / (st2["ms_total"] * 1e-3) / 1e9,
+                         "hbm_peak_gbs": peaks.get("hbm_gbs")},
+        }
+        if world == 1 and not args.no_cpu:
+            cb = oracle_sample(w, seconds_target=12.0)
+            line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier(device_ids=[local])
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c4")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    from b200rt.workloads import workload
+    w = workload(args.workload)
+    if args.impl == "reference":
+        run_reference(args, w)
+    else:
+        run_ours(args, w)
+
+
+if __name__ == "__main__":
+    main()

@@ -9,12 +9,14 @@ from . import _lib
 
 
 def _fill_common(a, W, H, cam_origin, cam_rotation, spheres, lights, planes, amb, lamb, refl, refl_depth, aliasing,
-                 device, flags, tile):
+                 device, flags, tile, strips=None):
     a.struct_size = C.sizeof(_lib.Args)
     a.flags = flags
     a.device = int(device)
     a.W, a.H = int(W), int(H)
     a.x_begin, a.x_end = (0, W) if tile is None else (int(tile[0]), int(tile[1]))
+    if strips is not None:                       # (strip_width, rank, world): interleaved column strips of this tile
+        a.strip_width, a.strip_rank, a.strip_world = [int(v) for v in strips]
     co = np.ascontiguousarray(cam_origin, dtype=np.float64).ravel()
     cr = np.ascontiguousarray(cam_rotation, dtype=np.float64).ravel()
     if co.size != 3 or cr.size != 9:
@@ -34,7 +36,7 @@ def _fill_common(a, W, H, cam_origin, cam_rotation, spheres, lights, planes, amb
 
 
 def render_host(pixel_loc, cam_origin, cam_rotation, spheres, lights, planes, amb, lamb, refl, refl_depth, aliasing,
-                *, grid=None, shape=None, out=None, device=0, tile=None, flags=0, stats=False):
+                *, grid=None, shape=None, out=None, device=0, tile=None, strips=None, flags=0, stats=False):
     """Host arrays in, host uint8 (3,W,H) out, through b200rt_render_host.
 
     pixel_loc: float64 (3,W,H) host array, or None with grid=(f, ar, sy, sz) and shape=(W, H).
@@ -62,7 +64,7 @@ def render_host(pixel_loc, cam_origin, cam_rotation, spheres, lights, planes, am
     li = np.ascontiguousarray(lights, dtype=np.float32)
     pn = np.ascontiguousarray(planes, dtype=np.float32)
     keep += [sp, li, pn]
-    _fill_common(a, W, H, cam_origin, cam_rotation, sp, li, pn, amb, lamb, refl, refl_depth, aliasing, device, flags, tile)
+    _fill_common(a, W, H, cam_origin, cam_rotation, sp, li, pn, amb, lamb, refl, refl_depth, aliasing, device, flags, tile, strips)
     if out is None:
         out = np.zeros((3, W, H), dtype=np.uint8)
     if out.shape != (3, W, H) or out.dtype != np.uint8 or not out.flags.c_contiguous:

@@ -85,6 +85,25 @@ def to_device(ary, device=None, stream=None):
     return DeviceArray(t, host_small=small, shape=host.shape, dtype=host.dtype, device=dev)
 
 
+def pixel_grid(camera, device=None):
+    """Device-side stand-in for to_device(camera.generate_pixel_locations()) that never materialises the
+    24*W*H-byte array: carries only the closed form (f, ar, sy, sz).  render() accepts it as `pixel_loc`."""
+    W, H = camera.resolution
+    dev = 0 if device is None else int(device)
+    return DeviceArray(None, grid=tuple(camera.grid()), shape=(3, W, H), dtype=np.float64, device=dev,
+                       lazy_host=_LazyGrid(camera))
+
+
+class _LazyGrid:
+    """np.array(lazy) materialises the grid only if somebody really asks for the data."""
+
+    def __init__(self, camera):
+        self._camera = camera
+
+    def __array__(self, dtype=None, copy=None):
+        return np.array(self._camera.generate_pixel_locations(), dtype=dtype or np.float64)
+
+
 def device_array(shape, dtype=np.float64, device=None):
     torch = _torch()
     dev = torch.cuda.current_device() if device is None else int(device)

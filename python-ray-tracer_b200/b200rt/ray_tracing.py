@@ -60,8 +60,8 @@ def _device_index(x, default):
 
 
 class _Launch:
-    def __init__(self, stream=None, flags=0, stats=False, tile=None):
-        self.stream, self.flags, self.want_stats, self.tile = stream, flags, stats, tile
+    def __init__(self, stream=None, flags=0, stats=False, tile=None, strips=None):
+        self.stream, self.flags, self.want_stats, self.tile, self.strips = stream, flags, stats, tile, strips
         self.stats = None
 
     def __call__(self, pixel_loc, result, camera_origin, camera_rotation, spheres, lights, planes,
@@ -114,6 +114,8 @@ class _Launch:
         a.result = rt.data_ptr()
         a.W, a.H = W, H
         a.x_begin, a.x_end = (0, W) if self.tile is None else (int(self.tile[0]), int(self.tile[1]))
+        if self.strips is not None:
+            a.strip_width, a.strip_rank, a.strip_world = [int(v) for v in self.strips]
         co = _small_host(camera_origin, np.float64).ravel()
         cr = _small_host(camera_rotation, np.float64).ravel()
         for i in range(3):
@@ -149,9 +151,10 @@ class _Render:
             stream = cfg[2]
         return _Launch(stream=stream)
 
-    def configure(self, stream=None, flags=0, stats=False, tile=None):
-        """Library-specific launcher: explicit stream, B200RT_F_* flags, ray statistics, column tile."""
-        return _Launch(stream=stream, flags=flags, stats=stats, tile=tile)
+    def configure(self, stream=None, flags=0, stats=False, tile=None, strips=None):
+        """Library-specific launcher: explicit stream, B200RT_F_* flags, ray statistics, column tile,
+        interleaved strips (strip_width, rank, world) for multi-GPU sharding."""
+        return _Launch(stream=stream, flags=flags, stats=stats, tile=tile, strips=strips)
 
     def __call__(self, *args, **kw):
         raise TypeError("render is a kernel: launch it as render[blockspergrid, threadsperblock](...)")
