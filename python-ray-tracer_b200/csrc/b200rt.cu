@@ -39,7 +39,7 @@ struct SceneDev {
     const float4* plNu;    // [Pl]   float32 re-normalised normal (common.py:104-110)
     const float4* plCol;   // [Pl]
     const float4* lights;  // [L]
-    const float*  cmax;    // [1]    max |C| over spheres (filter error bound)
+    const float*  cmax;    // [2]    max |C|, max r over spheres (filter error bounds)
     int S, Spad, Pl, L;
 };
 
@@ -60,6 +60,7 @@ __global__ void k_pack(const float* __restrict__ spheres, int S, int Spad,
             sphCol[i] = make_float4(spheres[4 * S + i], spheres[5 * S + i], spheres[6 * S + i], 0.f);
             // scene bound for the filter margin: max |C| (atomicMax on the bit pattern of a non-negative float)
             atomicMax(reinterpret_cast<int*>(cmax), __float_as_int((float)sqrt(cc) * 1.0000002f));
+            atomicMax(reinterpret_cast<int*>(cmax) + 1, __float_as_int(fabsf(r)));          // bounds[1] = max r
         } else {
             sphA[i] = make_float4(0.f, 0.f, 0.f, -3.0e38f);               // padding: q = -3e38 never reaches a threshold
         }
@@ -146,7 +147,7 @@ __global__ void k_raygen(FrameDev f, float4* __restrict__ rayO, float4* __restri
                 o = make_float4((float)f.ox, (float)f.oy, (float)f.oz, __uint_as_float(slot));
             }
         }
-        uint32_t pos = warp_append(valid, n_live);
+        uint32_t pos = block_append(valid, n_live);
         if (valid) { rayO[pos] = o; rayD[pos] = d; }
     }
 }
@@ -308,6 +309,268 @@ k_intersect(SceneDev sc, QueueDev q) {
 }
 
 // ------------------------------------------------------------------------------------------------
+// The production intersection kernel: the same conservative filter issued as packed FFMA2 (two rays per
+// instruction), plus a 4-FFMA "pivot" form for rays whose line passes through a point shared by the group.
+// ------------------------------------------------------------------------------------------------
+// FFMA2 (fma.rn.f32x2) performs two IEEE FP32 FMAs in one issue slot: the FP32 pipe stays at its 128 FMA/clk/SM
+// while the warp scheduler has every other slot free for the compare / LDS / loop instructions, which is what
+// capped the scalar kernel at ~50 % of the FMA pipe (profiles/r01_v1_summary.md).  Lane .x/.y of every packed
+// value are two different RAYS; the sphere operand is the same in both lanes and is staged pre-duplicated in
+// shared memory, so one broadcast LDS.128 pair delivers register pairs that feed FFMA2 directly.
+//
+// Pivot form.  disc(line, sphere) does not depend on which point of the line is used as origin.  All primary
+// rays start at the camera, and every shadow ray towards light j lies (to within the rounding of its direction)
+// on a line through that light, so with the pivot V as origin
+//     c = |C-V|^2 - r^2   is a per-(pivot, sphere) constant    ->  q = b^2 + (r^2 - |C-V|^2),  b = C.D - V.D
+// = 4 FFMA per (ray, sphere) instead of 7.  k_pivot tabulates (Cx,Cy,Cz, r^2-|C-V|^2) per pivot in float64-
+// rounded-once form.  As before the filter only SELECTS candidates (q >= -margin, margin bounds its own rounding,
+// the exact test's rounding and the distance between the true ray line and the pivot); sphere_exact() on the
+// real ray decides.  B200RT_F_NO_FILTER output must stay bit-identical (tests/test_gpu_parity.py).
+constexpr int kChunk2 = 2048;            // spheres staged per pass: 64 KB duplicated operands + 8 KB r^2
+
+struct PivotDev {
+    const float4* tab;                   // [(L+1)][Spad]  (Cx, Cy, Cz, r^2 - |C - V_j|^2); j < L lights, j == L camera
+    const float4* piv;                   // [(L+1)]        pivot positions (float32)
+    const float*  bounds;                // [2]            max |C|, max r
+};
+
+// One thread per (pivot j, sphere s).
+__global__ void k_pivot(SceneDev sc, float cox, float coy, float coz, float4* tab, float4* piv) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = i / sc.Spad, s = i - j * sc.Spad;
+    if (j > sc.L) return;
+    float4 v = (j < sc.L) ? sc.lights[j] : make_float4(cox, coy, coz, 0.f);
+    if (s == 0) piv[j] = v;
+    if (s < sc.S) {
+        const float4 c = sc.sphB[s];
+        const double ex = (double)c.x - v.x, ey = (double)c.y - v.y, ez = (double)c.z - v.z;
+        tab[i] = make_float4(c.x, c.y, c.z, (float)((double)c.w - (ex * ex + ey * ey + ez * ez)));
+    } else {
+        tab[i] = make_float4(0.f, 0.f, 0.f, -3.0e38f);
+    }
+}
+
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+    float d; asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c)); return d;   // FMNMX3 (sm_100+)
+}
+
+// MODE 0: closest hit, arbitrary rays (bounces)            7 FFMA / test
+// MODE 1: closest hit, rays from the camera pivot (primary) 4 FFMA / test
+// MODE 2: any hit, shadow rays of light j = group / groups_per_light   4 FFMA / test
+// NP = ray PAIRS per thread.
+// Work distribution: the sphere chunk [c0, c0+cnt) of the table is staged once per CTA (per light phase for
+// shadow rays); after that every WARP claims groups of 32*NR consecutive rays from a global counter on its own —
+// no CTA-wide barrier inside the ray loop, so a warp that spends time in the exact test never stalls the others.
+// Shadow kernels walk the lights in a per-CTA rotated order (phase ph -> light (blockIdx.x + ph) % L).
+// S > kChunk2: one launch per sphere chunk; running (t, id) / occlusion state is carried in the output arrays.
+template <int MODE, int NP>
+__global__ void __launch_bounds__(kThreads, 2)
+k_isect2(SceneDev sc, QueueDev q, PivotDev pv, int c0) {
+    constexpr bool ANY = (MODE == 2), PIV = (MODE != 0);
+    constexpr int NR = 2 * NP, GW = 32 * NR;                  // rays per thread / per warp group
+    constexpr int NO = PIV ? 1 : NP;                          // 2*O operands exist only in the 7-FFMA form
+    extern __shared__ float4 s_dup[];                         // [2*cnt]: (x,x,y,y) (z,z,w,w) per sphere
+    const int cnt = min(kChunk2, sc.Spad - c0);               // multiple of 4
+    float* s_r2 = reinterpret_cast<float*>(s_dup + 2 * cnt);
+    const bool first = (c0 == 0), last = (c0 + cnt >= sc.Spad);
+
+    const uint32_t n_in = *q.n_in;
+    const uint32_t ngroups = (n_in + GW - 1) / GW;            // per light for ANY
+    const float cmax = pv.bounds[0], rmax = pv.bounds[1];
+    const float kInf = __int_as_float(0x7f800000);
+    const int nphase = ANY ? sc.L : 1;
+    const uint32_t lane = lane_id();
+    uint32_t slow_cnt = 0;
+
+    for (int ph = 0; ph < nphase; ++ph) {
+        const int j = ANY ? (int)((blockIdx.x + (uint32_t)ph) % (uint32_t)sc.L) : sc.L;     // pivot of this phase
+        const float4* tab = (PIV ? pv.tab + (size_t)j * sc.Spad : sc.sphA) + c0;
+        if (ph > 0) __syncthreads();
+        for (int s = threadIdx.x; s < cnt; s += kThreads) {
+            const float4 a = tab[s];
+            s_dup[2 * s] = make_float4(a.x, a.x, a.y, a.y);
+            s_dup[2 * s + 1] = make_float4(a.z, a.z, a.w, a.w);
+            s_r2[s] = (c0 + s < sc.S) ? sc.sphB[c0 + s].w : 0.f;
+        }
+        __syncthreads();
+        V3 Vp = mk(0.f, 0.f, 0.f);
+        if (PIV) { const float4 v = __ldg(&pv.piv[j]); Vp = mk(v.x, v.y, v.z); }
+        uint32_t* work = q.work + (ANY ? j : 0);
+
+        for (;;) {
+            uint32_t g = 0;
+            if (lane == 0) g = atomicAdd(work, 1u);
+            g = __shfl_sync(0xffffffffu, g, 0);
+            if (g >= ngroups) break;
+            // A thread owns NR CONSECUTIVE queue entries (neighbouring pixels): they pass the filter at the same
+            // spheres, so one slow-path entry serves all of them.
+            const uint32_t i0 = g * (uint32_t)GW + lane * NR;
+
+            // ---- per-ray constants, packed two rays per register pair ----
+            float2 dx[NP], dy[NP], dz[NP], nod[NP], o2x[NO], o2y[NO], o2z[NO];
+            float thr[NR], best[ANY ? 1 : NR]; int bid[NR];
+#pragma unroll
+            for (int r = 0; r < NR; ++r) {
+                const uint32_t i = i0 + r;
+                bool active = i < n_in;
+                V3 O = mk(0.f, 0.f, 0.f), D = mk(0.f, 0.f, 0.f);
+                float th = kInf, no = 0.f;
+                bid[r] = -1;
+                if (!ANY) best[r] = kTMax;
+                if (active && !first) {                           // running state of the earlier sphere chunks
+                    if (ANY) { if (q.occl[(size_t)j * n_in + i]) { bid[r] = 0; active = false; } }
+                    else     { best[r] = q.hit_t[i]; bid[r] = q.hit_id[i]; }
+                }
+                if (active) {
+                    if (MODE == 2) {
+                        const float4 p = q.hP[i];
+                        O = mk(p.x, p.y, p.z);
+                        const V3 d = sub3(Vp, O);                                   // common.py:84-91
+                        const float nrm = __fsqrt_rn(dot3(d, d));
+                        D = mk(__fdiv_rn(d.x, nrm), __fdiv_rn(d.y, nrm), __fdiv_rn(d.z, nrm));
+                        const float A = cmax + __fsqrt_rn(dot3(Vp, Vp)), B = cmax + __fsqrt_rn(dot3(O, O));
+                        const float e = nrm * 9.5367432e-7f;                        // 2^-20 |V-P|: ray line vs pivot
+                        th = -(fmaf(3.8146973e-6f, fmaf(A, A, B * B), fmaf(4.f * e, rmax, 16.f * e * e)) + 1e-12f);
+                        no = -dot3(Vp, D);
+                    } else {
+                        const float4 o = q.rayO[i], d = q.rayD[i];
+                        O = mk(o.x, o.y, o.z); D = mk(d.x, d.y, d.z);
+                        const float oo = dot3(O, O);
+                        const float A = cmax + __fsqrt_rn(oo);
+                        const float margin = fmaf(3.8146973e-6f /* 64 * 2^-24 */, A * A, 1e-12f);
+                        if (MODE == 1) { th = -2.f * margin; no = -dot3(Vp, D); }   // O == Vp for every primary ray
+                        else           { th = oo - margin;   no = -dot3(O, D); }
+                    }
+                }
+                const int p = r >> 1;
+                if (r & 1) { dx[p].y = D.x; dy[p].y = D.y; dz[p].y = D.z; nod[p].y = no; }
+                else       { dx[p].x = D.x; dy[p].x = D.y; dz[p].x = D.z; nod[p].x = no; }
+                if (!PIV) {
+                    if (r & 1) { o2x[p].y = 2.f * O.x; o2y[p].y = 2.f * O.y; o2z[p].y = 2.f * O.z; }
+                    else       { o2x[p].x = 2.f * O.x; o2y[p].x = 2.f * O.y; o2z[p].x = 2.f * O.z; }
+                }
+                thr[r] = th;
+            }
+            float thr_t = thr[0];                             // PIV: loosest threshold of this thread's rays
+#pragma unroll
+            for (int r = 1; r < NR; ++r) thr_t = fminf(thr_t, thr[r]);
+
+            // q of ray pair p against the sphere whose duplicated operands are (ax, ay, az, aw)
+            auto qpair = [&](int p, float2 ax, float2 ay, float2 az, float2 aw) -> float2 {
+                const float2 b = ffma2(ax, dx[p], ffma2(ay, dy[p], ffma2(az, dz[p], nod[p])));
+                if (PIV) return ffma2(b, b, aw);
+                return ffma2(b, b, ffma2(ax, o2x[PIV ? 0 : p], ffma2(ay, o2y[PIV ? 0 : p], ffma2(az, o2z[PIV ? 0 : p], aw))));
+            };
+
+            // -- candidates in spheres sb, sb+1 (rare): recompute q per sphere, the exact test decides --
+            auto slow2 = [&](int sb) {
+                slow_cnt++;
+#pragma unroll 1
+                for (int k = 0; k < 2; ++k) {
+                    const float4 u = s_dup[2 * (sb + k)], w = s_dup[2 * (sb + k) + 1];
+                    const float r2 = s_r2[sb + k];
+#pragma unroll
+                    for (int r = 0; r < NR; ++r) {
+                        const int p = r >> 1;
+                        const float2 qv = qpair(p, make_float2(u.x, u.y), make_float2(u.z, u.w), make_float2(w.x, w.y), make_float2(w.z, w.w));
+                        if (!(((r & 1) ? qv.y : qv.x) >= thr[r])) continue;
+                        const V3 D = (r & 1) ? mk(dx[p].y, dy[p].y, dz[p].y) : mk(dx[p].x, dy[p].x, dz[p].x);
+                        V3 O;
+                        if (MODE == 0)      O = (r & 1) ? mk(0.5f * o2x[PIV ? 0 : p].y, 0.5f * o2y[PIV ? 0 : p].y, 0.5f * o2z[PIV ? 0 : p].y)
+                                                        : mk(0.5f * o2x[PIV ? 0 : p].x, 0.5f * o2y[PIV ? 0 : p].x, 0.5f * o2z[PIV ? 0 : p].x);   // exact
+                        else if (MODE == 1) O = Vp;
+                        else { const float4 hp = q.hP[i0 + r]; O = mk(hp.x, hp.y, hp.z); }
+                        const float t = sphere_exact(O, D, u.x, u.z, w.x, r2);
+                        if (ANY) {
+                            if (t > 0.f && t < kTMax) {           // occluded: retire the lane (b = 0 -> q = r^2 - |C-V|^2)
+                                bid[r] = 0; thr[r] = kInf;
+                                if (r & 1) { dx[p].y = 0.f; dy[p].y = 0.f; dz[p].y = 0.f; nod[p].y = 0.f; }
+                                else       { dx[p].x = 0.f; dy[p].x = 0.f; dz[p].x = 0.f; nod[p].x = 0.f; }
+                            }
+                        } else if (t > 0.f && t < best[r]) { best[r] = t; bid[r] = c0 + sb + k; }   // trace.py:26-29
+                    }
+                }
+            };
+
+            // ---- spheres: scan two spheres x NR rays per step.  The candidate decision of a step is taken one
+            // step LATER (software pipelining): the vote/branch then never waits on the FMA pipe, and the next
+            // step's FFMA2s issue back to back.  Candidates are still handled in sphere order (tie-break). ----
+            float m_prev = -3.0e38f; bool any_prev = false;
+            int s = 0;
+            for (;;) {
+                bool found = false;
+#pragma unroll 2
+                for (; s < cnt; s += 2) {
+                    const float4 u0 = s_dup[2 * s], w0 = s_dup[2 * s + 1], u1 = s_dup[2 * s + 2], w1 = s_dup[2 * s + 3];
+                    const bool fire = __any_sync(0xffffffffu, PIV ? (m_prev >= thr_t) : any_prev);   // step s-2
+                    if (PIV) {                   // one threshold per thread: max of the 4*NP q values against it
+                        float m = -3.0e38f;
+#pragma unroll
+                        for (int p = 0; p < NP; ++p) {
+                            const float2 q0 = qpair(p, make_float2(u0.x, u0.y), make_float2(u0.z, u0.w), make_float2(w0.x, w0.y), make_float2(w0.z, w0.w));
+                            const float2 q1 = qpair(p, make_float2(u1.x, u1.y), make_float2(u1.z, u1.w), make_float2(w1.x, w1.y), make_float2(w1.z, w1.w));
+                            m = fmax3(m, q0.x, q0.y); m = fmax3(m, q1.x, q1.y);
+                        }
+                        m_prev = m;
+                    } else {
+                        bool any = false;
+#pragma unroll
+                        for (int p = 0; p < NP; ++p) {
+                            const float2 q0 = qpair(p, make_float2(u0.x, u0.y), make_float2(u0.z, u0.w), make_float2(w0.x, w0.y), make_float2(w0.z, w0.w));
+                            const float2 q1 = qpair(p, make_float2(u1.x, u1.y), make_float2(u1.z, u1.w), make_float2(w1.x, w1.y), make_float2(w1.z, w1.w));
+                            any |= (q0.x >= thr[2 * p]) | (q0.y >= thr[2 * p + 1]) | (q1.x >= thr[2 * p]) | (q1.y >= thr[2 * p + 1]);
+                        }
+                        any_prev = any;
+                    }
+                    if (fire) { found = true; break; }
+                }
+                if (found) { slow2(s - 2); s += 2; continue; }            // step s is computed and pending
+                if (__any_sync(0xffffffffu, PIV ? (m_prev >= thr_t) : any_prev)) slow2(cnt - 2);   // flush the last step
+                break;
+            }
+
+            // ---- planes after the last sphere chunk (trace.py:32-39), then write back ----
+#pragma unroll
+            for (int r = 0; r < NR; ++r) {
+                const uint32_t i = i0 + r;
+                if (i >= n_in) continue;
+                const int p = r >> 1;
+                if (ANY) {
+                    bool occluded = bid[r] >= 0;
+                    if (last && !occluded && sc.Pl > 0) {
+                        const float4 hp = q.hP[i]; const V3 O = mk(hp.x, hp.y, hp.z);
+                        const V3 D = (r & 1) ? mk(dx[p].y, dy[p].y, dz[p].y) : mk(dx[p].x, dy[p].x, dz[p].x);
+                        for (int pl = 0; pl < sc.Pl && !occluded; ++pl) {
+                            const float t = plane_exact(O, D, __ldg(&sc.plO[pl]), __ldg(&sc.plN[pl]));
+                            occluded = (t > 0.f && t < kTMax);
+                        }
+                    }
+                    q.occl[(size_t)j * n_in + i] = occluded ? 1 : 0;
+                } else {
+                    if (last) {
+                        const V3 D = (r & 1) ? mk(dx[p].y, dy[p].y, dz[p].y) : mk(dx[p].x, dy[p].x, dz[p].x);
+                        V3 O;
+                        if (MODE == 0)      O = (r & 1) ? mk(0.5f * o2x[PIV ? 0 : p].y, 0.5f * o2y[PIV ? 0 : p].y, 0.5f * o2z[PIV ? 0 : p].y)
+                                                        : mk(0.5f * o2x[PIV ? 0 : p].x, 0.5f * o2y[PIV ? 0 : p].x, 0.5f * o2z[PIV ? 0 : p].x);
+                        else                O = Vp;
+                        for (int pl = 0; pl < sc.Pl; ++pl) {
+                            const float t = plane_exact(O, D, __ldg(&sc.plO[pl]), __ldg(&sc.plN[pl]));
+                            if (t > 0.f && t < best[r]) { best[r] = t; bid[r] = sc.S + pl; }
+                        }
+                    }
+                    q.hit_t[i] = best[r]; q.hit_id[i] = bid[r];
+                }
+            }
+        }
+    }
+    if (q.slow) {
+        const uint32_t tot = __reduce_add_sync(0xffffffffu, slow_cnt);
+        if (lane == 0 && tot) atomicAdd(q.slow, (unsigned long long)tot);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // Per-hit shading kernels (trace.py:56-110, :123-131) — <1 % of the work at S=1024
 // ------------------------------------------------------------------------------------------------
 struct ShadeDev {
@@ -338,7 +601,7 @@ __global__ void k_setup(SceneDev sc, ShadeDev s) {
             else           { const float4 nu = __ldg(&sc.plNu[id - sc.S]); N = mk(nu.x, nu.y, nu.z); }             // common.py:104-110
             Pb = madd3(P, kBias, N);                                                 // trace.py:82-83
         }
-        const uint32_t h = warp_append(hit, s.n_hit);
+        const uint32_t h = block_append(hit, s.n_hit);
         if (hit) {
             s.hP[h] = make_float4(Pb.x, Pb.y, Pb.z, o.w);
             s.hN[h] = make_float4(N.x, N.y, N.z, __int_as_float(id));
@@ -505,14 +768,16 @@ struct DevCtx {
     bool init = false;
     int sm_count = 0;
     int isect_blocks_per_sm = 2;
+    int force_np = 0; bool no_pivot = false;                       // tuning overrides (env B200RT_NP, B200RT_NO_PIVOT)
     Buf sphA, sphB, sphCol, plO, plN, plNu, plCol, lights, cmax;   // packed scene
+    Buf pivTab, pivPos;                                            // pivot tables (k_pivot)
     Buf stage;                                                     // host-scene / host-pixel_loc staging
-    Buf rayO, rayD, hitT, hitId, hP, hN, hD, acc, occl, ctr, slow; // wavefront state
+    Buf rayO, rayD, hitT, hitId, hP, hN, hD, acc, occl, ctr, work, slow; // wavefront state
     Buf hostResult, hostPixelLoc;                                  // b200rt_render_host device copies
     cudaEvent_t done = nullptr; bool has_done = false;
     void release_all() {
-        Buf* all[] = { &sphA, &sphB, &sphCol, &plO, &plN, &plNu, &plCol, &lights, &cmax, &stage, &rayO, &rayD, &hitT, &hitId,
-                       &hP, &hN, &hD, &acc, &occl, &ctr, &slow, &hostResult, &hostPixelLoc };
+        Buf* all[] = { &sphA, &sphB, &sphCol, &plO, &plN, &plNu, &plCol, &lights, &cmax, &pivTab, &pivPos, &stage, &rayO, &rayD, &hitT, &hitId,
+                       &hP, &hN, &hD, &acc, &occl, &ctr, &work, &slow, &hostResult, &hostPixelLoc };
         for (Buf* b : all) b->release();
         if (done) { cudaEventDestroy(done); done = nullptr; } has_done = false; init = false;
     }
@@ -563,9 +828,35 @@ template <bool ANY>
 int launch_intersect(DevCtx& c, const SceneDev& sc, const QueueDev& q, bool nofilter, cudaStream_t st) {
     const size_t smem = isect_smem_bytes(sc.Spad);
     const int grid = c.sm_count * c.isect_blocks_per_sm;
-    if (nofilter) k_intersect<ANY, true><<<grid, kThreads, smem, st>>>(sc, q);
-    else          k_intersect<ANY, false><<<grid, kThreads, smem, st>>>(sc, q);
+    (void)nofilter;                                   // the scalar kernel is kept as the exact-test-on-everything debug path
+    k_intersect<ANY, true><<<grid, kThreads, smem, st>>>(sc, q);
     CK(cudaGetLastError());
+    return 0;
+}
+
+size_t isect2_smem_bytes(int Spad) { return (size_t)std::min(Spad, kChunk2) * (2 * sizeof(float4) + sizeof(float)); }
+
+// Rays per thread of the production kernel: 8 (4 pairs) for big queues, fewer for small ones (more groups than warps).
+// One launch per sphere chunk; `work` points at (L+1) zeroed counters per chunk.
+template <int MODE>
+int launch_isect2(DevCtx& c, const SceneDev& sc, QueueDev q, const PivotDev& pv, size_t max_rays, uint32_t* work, cudaStream_t st) {
+    const size_t smem = isect2_smem_bytes(sc.Spad);
+    const int grid = c.sm_count * 2;
+    const size_t warps = (size_t)grid * (kThreads / 32);
+    const int np = c.force_np ? c.force_np : (max_rays >= warps * 256 * 4 ? 4 : (max_rays >= warps * 128 * 4 ? 2 : 1));
+    for (int c0 = 0, k = 0; c0 < sc.Spad; c0 += kChunk2, ++k) {
+        q.work = work + (size_t)k * (sc.L + 1);
+        if (np == 4)      k_isect2<MODE, 4><<<grid, kThreads, smem, st>>>(sc, q, pv, c0);
+        else if (np == 2) k_isect2<MODE, 2><<<grid, kThreads, smem, st>>>(sc, q, pv, c0);
+        else              k_isect2<MODE, 1><<<grid, kThreads, smem, st>>>(sc, q, pv, c0);
+        CK(cudaGetLastError());
+    }
+    return 0;
+}
+
+template <int MODE, int NP>
+int set_isect2_attr() {
+    CK(cudaFuncSetAttribute(k_isect2<MODE, NP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)isect2_smem_bytes(kChunk2)));
     return 0;
 }
 
@@ -575,10 +866,13 @@ int init_ctx(DevCtx& c, int device) {
     if (prop.major != 10) return fail(B200RT_E_DEVICE, "libb200rt is built for sm_100a (B200) only; device is sm_" + std::to_string(prop.major * 10 + prop.minor));
     c.sm_count = prop.multiProcessorCount;
     const int smem_max = (int)isect_smem_bytes(kChunkS);
-    CK(cudaFuncSetAttribute(k_intersect<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
-    CK(cudaFuncSetAttribute(k_intersect<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
     CK(cudaFuncSetAttribute(k_intersect<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
     CK(cudaFuncSetAttribute(k_intersect<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
+    if (int rc = set_isect2_attr<0, 1>()) return rc; if (int rc = set_isect2_attr<0, 2>()) return rc; if (int rc = set_isect2_attr<0, 4>()) return rc;
+    if (int rc = set_isect2_attr<1, 1>()) return rc; if (int rc = set_isect2_attr<1, 2>()) return rc; if (int rc = set_isect2_attr<1, 4>()) return rc;
+    if (int rc = set_isect2_attr<2, 1>()) return rc; if (int rc = set_isect2_attr<2, 2>()) return rc; if (int rc = set_isect2_attr<2, 4>()) return rc;
+    { const char* e = getenv("B200RT_NP"); c.force_np = e ? atoi(e) : 0; if (c.force_np != 1 && c.force_np != 2 && c.force_np != 4) c.force_np = 0; }
+    { const char* e = getenv("B200RT_NO_PIVOT"); c.no_pivot = e && atoi(e) != 0; }
     CK(cudaEventCreateWithFlags(&c.done, cudaEventDisableTiming));
     c.init = true;
     return 0;
@@ -611,7 +905,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     CK(c.sphA.ensure(sizeof(float4) * Spad)); CK(c.sphB.ensure(sizeof(float4) * std::max(S, 1))); CK(c.sphCol.ensure(sizeof(float4) * std::max(S, 1)));
     CK(c.plO.ensure(sizeof(float4) * std::max(Pl, 1))); CK(c.plN.ensure(sizeof(float4) * std::max(Pl, 1)));
     CK(c.plNu.ensure(sizeof(float4) * std::max(Pl, 1))); CK(c.plCol.ensure(sizeof(float4) * std::max(Pl, 1)));
-    CK(c.lights.ensure(sizeof(float4) * std::max(L, 1))); CK(c.cmax.ensure(sizeof(float)));
+    CK(c.lights.ensure(sizeof(float4) * std::max(L, 1))); CK(c.cmax.ensure(2 * sizeof(float)));
     const float *d_sph = a->spheres, *d_lig = a->lights, *d_pla = a->planes;
     if (a->flags & B200RT_F_SCENE_ON_HOST) {
         const size_t nS = (size_t)7 * S, nL = (size_t)3 * L, nP = (size_t)9 * Pl;
@@ -622,7 +916,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         if (nP) CK(cudaMemcpyAsync(sg + nS + nL, a->planes, sizeof(float) * nP, cudaMemcpyHostToDevice, st));
         d_sph = sg; d_lig = sg + nS; d_pla = sg + nS + nL;
     }
-    CK(cudaMemsetAsync(c.cmax.p, 0, sizeof(float), st));
+    CK(cudaMemsetAsync(c.cmax.p, 0, 2 * sizeof(float), st));
     {
         const int nobj = std::max(std::max(Spad, Pl), L);
         k_pack<<<(nobj + 255) / 256, 256, 0, st>>>(d_sph, S, Spad, d_pla, Pl, d_lig, L, c.sphA.as<float4>(), c.sphB.as<float4>(),
@@ -632,6 +926,14 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     }
     SceneDev sc{ c.sphA.as<float4>(), c.sphB.as<float4>(), c.sphCol.as<float4>(), c.plO.as<float4>(), c.plN.as<float4>(),
                  c.plNu.as<float4>(), c.plCol.as<float4>(), c.lights.as<float4>(), c.cmax.as<float>(), S, Spad, Pl, L };
+    CK(c.pivTab.ensure(sizeof(float4) * (size_t)(L + 1) * Spad)); CK(c.pivPos.ensure(sizeof(float4) * (L + 1)));
+    {
+        const int n = (L + 1) * Spad;
+        k_pivot<<<(n + 255) / 256, 256, 0, st>>>(sc, (float)a->cam_origin[0], (float)a->cam_origin[1], (float)a->cam_origin[2],
+                                                 c.pivTab.as<float4>(), c.pivPos.as<float4>());
+        CK(cudaGetLastError());
+    }
+    const PivotDev pv{ c.pivTab.as<float4>(), c.pivPos.as<float4>(), c.cmax.as<float>() };
 
     // ---- chunking: whole columns, <= max_paths slots per chunk ----
     const size_t per_col = (size_t)ns * H;
@@ -646,10 +948,15 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     const int ctr_stride = 4 * (depth + 2);
     CK(c.ctr.ensure(sizeof(uint32_t) * (size_t)ctr_stride * nchunks)); CK(c.slow.ensure(sizeof(unsigned long long)));
     CK(cudaMemsetAsync(c.ctr.p, 0, sizeof(uint32_t) * (size_t)ctr_stride * nchunks, st));
+    const int nsch = (Spad + kChunk2 - 1) / kChunk2;             // sphere chunks = k_isect2 launches per query kernel
+    const size_t work_per_depth = (size_t)2 * nsch * (L + 1);    // closest + shadow
+    const size_t work_n = work_per_depth * (depth + 1) * nchunks;
+    CK(c.work.ensure(sizeof(uint32_t) * work_n));
+    CK(cudaMemsetAsync(c.work.p, 0, sizeof(uint32_t) * work_n, st));
     CK(cudaMemsetAsync(c.slow.p, 0, sizeof(unsigned long long), st));
 
     {   // persistent grid for the intersection kernels
-        int nb = 0; CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_intersect<false, false>, kThreads, isect_smem_bytes(Spad)));
+        int nb = 0; CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_intersect<false, true>, kThreads, isect_smem_bytes(Spad)));
         c.isect_blocks_per_sm = std::max(1, nb);
     }
     const bool nofilter = (a->flags & B200RT_F_NO_FILTER) != 0;
@@ -683,7 +990,8 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         tm.end(2);
 
         for (int d = 0; d <= depth; ++d) {
-            uint32_t* cd = ctr + 4 * d;             // [0] n_live, [1] n_hit, [2] work(closest), [3] work(shadow)
+            uint32_t* cd = ctr + 4 * d;             // [0] n_live, [1] n_hit, [2] work(closest), [3] work(shadow)  (scalar debug kernels)
+            uint32_t* wk = c.work.as<uint32_t>() + ((size_t)ch * (depth + 1) + d) * work_per_depth;      // k_isect2 group counters
             QueueDev q{};
             q.rayO = c.rayO.as<float4>(); q.rayD = c.rayD.as<float4>(); q.hP = c.hP.as<float4>();
             q.hit_t = c.hitT.as<float>(); q.hit_id = c.hitId.as<int>(); q.occl = c.occl.as<uint8_t>();
@@ -697,7 +1005,13 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
 
             tm.begin(0);
             q.n_in = cd + 0; q.work = cd + 2;
-            { int rc = launch_intersect<false>(c, sc, q, nofilter, st); if (rc) return rc; }
+            {
+                int rc;
+                if (nofilter)                     rc = launch_intersect<false>(c, sc, q, true, st);
+                else if (d == 0 && !c.no_pivot)   rc = launch_isect2<1>(c, sc, q, pv, nslots, wk, st);
+                else                              rc = launch_isect2<0>(c, sc, q, pv, nslots, wk, st);
+                if (rc) return rc;
+            }
             tm.end(0);
             tm.begin(2);
             k_setup<<<small_grid, 256, 0, st>>>(sc, s); CK(cudaGetLastError());
@@ -705,7 +1019,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             if (L > 0) {
                 tm.begin(1);
                 q.n_in = cd + 1; q.work = cd + 3;
-                { int rc = launch_intersect<true>(c, sc, q, nofilter, st); if (rc) return rc; }
+                { int rc = nofilter ? launch_intersect<true>(c, sc, q, true, st) : launch_isect2<2>(c, sc, q, pv, nslots, wk + (size_t)nsch * (L + 1), st); if (rc) return rc; }
                 tm.end(1);
             }
             tm.begin(2);

@@ -80,4 +80,28 @@ __device__ __forceinline__ uint32_t warp_append(bool valid, uint32_t* counter) {
     return base + __popc(mask & ((1u << lane_id()) - 1u));
 }
 
+
+// CTA-aggregated append for 256-thread CTAs whose threads hold CONSECUTIVE items: the CTA's valid items land in one
+// contiguous, order-preserving run of the queue (one atomic per CTA).  Keeps neighbouring pixels neighbouring in
+// the ray queues, which is what makes a warp's rays pass the sphere filter at the same spheres.
+// Must be called by every thread of the CTA (contains __syncthreads()).
+__device__ __forceinline__ uint32_t block_append(bool valid, uint32_t* counter) {
+    __shared__ uint32_t s_cnt[8];
+    __shared__ uint32_t s_base;
+    const uint32_t mask = __ballot_sync(0xffffffffu, valid);
+    const uint32_t wid = threadIdx.x >> 5;
+    if (lane_id() == 0) s_cnt[wid] = (uint32_t)__popc(mask);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t total = 0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) { const uint32_t t = s_cnt[w]; s_cnt[w] = total; total += t; }
+        s_base = total ? atomicAdd(counter, total) : 0u;
+    }
+    __syncthreads();
+    const uint32_t pos = s_base + s_cnt[wid] + (uint32_t)__popc(mask & ((1u << lane_id()) - 1u));
+    __syncthreads();                                   // s_cnt / s_base are reused by the caller's next iteration
+    return pos;
+}
+
 }  // namespace b200rt
