@@ -224,7 +224,7 @@ def run_ours(args, w):
         ach_tf = rays_this_rank * fpr / (isect_ms * 1e-3) / 1e12
         clocks = sampler.summary()
         depth = w["refl_depth"]
-        launches_per_frame = 3 + (depth + 1) * (3 + (1 if L > 0 else 0)) + 1        # pack, pivot, raygen, per depth closest/setup/shadow/shade, resolve
+        launches_per_frame = 3 + (depth + 1) * (3 + L) + 1        # pack, pivot, raygen, per depth closest/setup/shadow/shade, resolve
         line = {
             "metric": "Mrays/s", "value": rays_total / (ms_step * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
@@ -237,13 +237,13 @@ def run_ours(args, w):
                     "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
             "gpu_launches": int(launches_per_frame * args.steps),
             "clocks": clocks,
-            "roofline": {"bound": "fp32", "kernel": "k_isect2 (closest + shadow)", "achieved": ach_tf, "peak": nominal_tf,
+            "roofline": {"bound": "fp32", "kernel": "k_isect3 (closest + shadow)", "achieved": ach_tf, "peak": nominal_tf,
                          "unit": "TFLOP/s", "frac": ach_tf / nominal_tf, "traffic": None,
                          "peak_def": f"2 FLOP x 128 lanes x {sms} SMs x {sm_max:.0f} MHz (nominal max clock; MEASURED_PEAKS has no FP32 entry)",
                          "peak_measured_ffma": probe["ffma_tflops"], "peak_measured_ffma2": probe["ffma2_tflops"],
                          "probe_sm_mhz": probe["sm_mhz"], "frac_of_measured_ffma": ach_tf / max(probe["ffma_tflops"], 1e-9),
                          "algorithmic_flops_per_ray": fpr, "kernel_ms_per_frame": isect_ms, "kernel_ms_closest": st2["ms_closest"], "kernel_ms_shadow": st2["ms_shadow"], "other_ms": st2["ms_other"], "kernel_share_of_frame": isect_ms / st2["ms_total"],
-                         "slow_path_entries_per_ray": st2["slow_path"] / max(1, rays_this_rank),
+                         "slow_path_entries_per_ray": st2["slow_path"] / max(1, rays_this_rank), "exact_tests_per_ray": st2["exact_tests"] / max(1, rays_this_rank),
                          "framebuffer_write_gbs": 3.0 * W * H / world / (st2["ms_total"] * 1e-3) / 1e9,
                          "hbm_peak_gbs": peaks.get("hbm_gbs")},
         }

@@ -62,7 +62,8 @@ typedef struct b200rt_stats {
     uint64_t primary;   /* first query of every sample (kernels.py:26,56 -> trace.py:120 -> :53) */
     uint64_t shadow;    /* one per light per hit-trace (trace.py:92)                              */
     uint64_t bounce;    /* first query of every reflection trace (trace.py:128 -> :53)            */
-    uint64_t slow_path; /* thread-level entries into the exact sphere test (diagnostic)           */
+    uint64_t slow_path; /* thread-level entries into the candidate handler (diagnostic)           */
+    uint64_t exact_tests; /* exact (robust) ray-sphere tests run on filter candidates (diagnostic)  */
     float    kernel_ms[4]; /* device time: [0] total, [1] closest-hit kernels, [2] shadow kernels, [3] everything else */
 } b200rt_stats;
 

@@ -309,264 +309,317 @@ k_intersect(SceneDev sc, QueueDev q) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// The production intersection kernel: the same conservative filter issued as packed FFMA2 (two rays per
-// instruction), plus a 4-FFMA "pivot" form for rays whose line passes through a point shared by the group.
+// The production intersection kernel (k_isect3)
 // ------------------------------------------------------------------------------------------------
-// FFMA2 (fma.rn.f32x2) performs two IEEE FP32 FMAs in one issue slot: the FP32 pipe stays at its 128 FMA/clk/SM
-// while the warp scheduler has every other slot free for the compare / LDS / loop instructions, which is what
-// capped the scalar kernel at ~50 % of the FMA pipe (profiles/r01_v1_summary.md).  Lane .x/.y of every packed
-// value are two different RAYS; the sphere operand is the same in both lanes and is staged pre-duplicated in
-// shared memory, so one broadcast LDS.128 pair delivers register pairs that feed FFMA2 directly.
+// What bounds this loop on B200 is not the FP32 pipe but the register file: measured (tools/ffma2_probe*.cu) an
+// SMSP sustains ~1.75 register-operand reads per lane-cycle, every FFMA2 that reads two register pairs costs 2.3
+// cycles, and a 3-input ALU op (FMNMX3) costs as much as an FFMA2 when its operands all come from registers.  So the
+// loop is organised to read as few vector registers as possible:
+//   * packed FFMA2 (fma.rn.f32x2): two IEEE FP32 FMAs per instruction.  The two lanes of every packed value are two
+//     SPHERES (2i, 2i+1) tested against the same ray;
+//   * the sphere operands are warp-uniform, so they never touch the vector register file: the table of the launch
+//     lives in constant memory and reaches the FMA pipe as UNIFORM-register pairs (LDCU.128 -> FFMA2 ..., URx.F32x2);
+//   * the ray operands are 32-bit registers in FFMA2's broadcast form (R.F32): 1 register read instead of a pair.
+// Per (ray, sphere pair) the 4-FFMA pivot form reads 2+3+3+2 registers + 3 for the max — the probe's V7 variant runs
+// this at 2.32 cycles/FFMA2 = 64 TFLOP/s executed, 86 % of the nominal FP32 peak, FMA-pipe bound.
 //
-// Pivot form.  disc(line, sphere) does not depend on which point of the line is used as origin.  All primary
-// rays start at the camera, and every shadow ray towards light j lies (to within the rounding of its direction)
-// on a line through that light, so with the pivot V as origin
-//     c = |C-V|^2 - r^2   is a per-(pivot, sphere) constant    ->  q = b^2 + (r^2 - |C-V|^2),  b = C.D - V.D
-// = 4 FFMA per (ray, sphere) instead of 7.  k_pivot tabulates (Cx,Cy,Cz, r^2-|C-V|^2) per pivot in float64-
-// rounded-once form.  As before the filter only SELECTS candidates (q >= -margin, margin bounds its own rounding,
-// the exact test's rounding and the distance between the true ray line and the pivot); sphere_exact() on the
-// real ray decides.  B200RT_F_NO_FILTER output must stay bit-identical (tests/test_gpu_parity.py).
-constexpr int kChunk2 = 2048;            // spheres staged per pass: 64 KB duplicated operands + 8 KB r^2
+// Filter algebra (unchanged from the scalar kernel, see k_intersect): disc >= 0 <=> q >= thr.
+//   MODE 0 (any ray, bounces):     q = b^2 + 2 C.O + (r^2 - |C|^2) - (|O|^2 - margin)          8 FFMA2 / 2 tests
+//   MODE 1/2 (pivot V on the line): q = b^2 + (r^2 - |C-V|^2),  b = C.D - V.D,  thr = -margin   4 FFMA2 / 2 tests
+// Pivot form: disc(line, sphere) does not depend on which point of the line is the origin.  All primary rays start
+// at the camera and every shadow ray towards light j lies (to within the rounding of its direction) on a line through
+// that light, so c = |C-V|^2 - r^2 is a per-(pivot, sphere) constant tabulated once per frame by k_pivot in float64-
+// rounded-once form.  The filter only SELECTS candidates (margin bounds its own rounding, the exact test's rounding
+// and the distance between the true ray line and the pivot); sphere_exact() on the real ray decides, so the output is
+// bit-identical to running the exact test on every sphere (B200RT_F_NO_FILTER, tests/test_gpu_parity.py).
+constexpr int kTabCap = 3584;            // float4 entries of the constant-memory table = 3584 spheres (56 KB)
+__constant__ float4 c_tab[kTabCap + 2 * 4]; // per sphere pair i: [2i] = (cx0,cx1,cy0,cy1)  [2i+1] = (cz0,cz1,k0,k1); + prefetch overrun
 
 struct PivotDev {
-    const float4* tab;                   // [(L+1)][Spad]  (Cx, Cy, Cz, r^2 - |C - V_j|^2); j < L lights, j == L camera
-    const float4* piv;                   // [(L+1)]        pivot positions (float32)
-    const float*  bounds;                // [2]            max |C|, max r
+    const float4* tab;                   // [(L+2)][Spad] pair layout; table j < L: light j, j == L: camera, j == L+1: origin-free
+    const float4* piv;                   // [(L+1)]       pivot positions (float32)
+    const float*  bounds;                // [2]           max |C|, max r
 };
 
-// One thread per (pivot j, sphere s).
+// One thread per (table j, sphere pair i): k = r^2 - |C-V_j|^2 (j <= L) or r^2 - |C|^2 (j == L+1), float64 rounded once.
 __global__ void k_pivot(SceneDev sc, float cox, float coy, float coz, float4* tab, float4* piv) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    const int j = i / sc.Spad, s = i - j * sc.Spad;
-    if (j > sc.L) return;
-    float4 v = (j < sc.L) ? sc.lights[j] : make_float4(cox, coy, coz, 0.f);
-    if (s == 0) piv[j] = v;
-    if (s < sc.S) {
-        const float4 c = sc.sphB[s];
-        const double ex = (double)c.x - v.x, ey = (double)c.y - v.y, ez = (double)c.z - v.z;
-        tab[i] = make_float4(c.x, c.y, c.z, (float)((double)c.w - (ex * ex + ey * ey + ez * ez)));
-    } else {
-        tab[i] = make_float4(0.f, 0.f, 0.f, -3.0e38f);
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int npair = sc.Spad / 2;
+    const int j = idx / npair, i = idx - j * npair;
+    if (j > sc.L + 1) return;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (j < sc.L) v = sc.lights[j]; else if (j == sc.L) v = make_float4(cox, coy, coz, 0.f);
+    if (i == 0 && j <= sc.L) piv[j] = v;
+    float c[2][4];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const int s = 2 * i + h;
+        if (s < sc.S) {
+            const float4 sp = sc.sphB[s];
+            const double ex = (double)sp.x - v.x, ey = (double)sp.y - v.y, ez = (double)sp.z - v.z;
+            c[h][0] = sp.x; c[h][1] = sp.y; c[h][2] = sp.z; c[h][3] = (float)((double)sp.w - (ex * ex + ey * ey + ez * ez));
+        } else { c[h][0] = c[h][1] = c[h][2] = 0.f; c[h][3] = -3.0e38f; }     // padding never reaches a threshold
     }
+    float4* o = tab + ((size_t)j * npair + i) * 2;
+    o[0] = make_float4(c[0][0], c[1][0], c[0][1], c[1][1]);
+    o[1] = make_float4(c[0][2], c[1][2], c[0][3], c[1][3]);
 }
 
 __device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
+__device__ __forceinline__ float2 bc(float a) { return make_float2(a, a); }       // FFMA2 broadcast operand (R.F32 / UR.F32)
 __device__ __forceinline__ float fmax3(float a, float b, float c) {
     float d; asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c)); return d;   // FMNMX3 (sm_100+)
 }
 
-// MODE 0: closest hit, arbitrary rays (bounces)            7 FFMA / test
-// MODE 1: closest hit, rays from the camera pivot (primary) 4 FFMA / test
-// MODE 2: any hit, shadow rays of light j = group / groups_per_light   4 FFMA / test
-// NP = ray PAIRS per thread.
-// Work distribution: the sphere chunk [c0, c0+cnt) of the table is staged once per CTA (per light phase for
-// shadow rays); after that every WARP claims groups of 32*NR consecutive rays from a global counter on its own —
-// no CTA-wide barrier inside the ray loop, so a warp that spends time in the exact test never stalls the others.
-// Shadow kernels walk the lights in a per-CTA rotated order (phase ph -> light (blockIdx.x + ph) % L).
-// S > kChunk2: one launch per sphere chunk; running (t, id) / occlusion state is carried in the output arrays.
-template <int MODE, int NP>
-__global__ void __launch_bounds__(kThreads, 2)
-k_isect2(SceneDev sc, QueueDev q, PivotDev pv, int c0) {
-    constexpr bool ANY = (MODE == 2), PIV = (MODE != 0);
-    constexpr int NR = 2 * NP, GW = 32 * NR;                  // rays per thread / per warp group
-    constexpr int NO = PIV ? 1 : NP;                          // 2*O operands exist only in the 7-FFMA form
-    extern __shared__ float4 s_dup[];                         // [2*cnt]: (x,x,y,y) (z,z,w,w) per sphere
-    const int cnt = min(kChunk2, sc.Spad - c0);               // multiple of 4
-    float* s_r2 = reinterpret_cast<float*>(s_dup + 2 * cnt);
-    const bool first = (c0 == 0), last = (c0 + cnt >= sc.Spad);
+// MODE 0: closest hit, arbitrary rays (bounces)   MODE 1: closest hit, camera pivot (primary)   MODE 2: any hit, shadow
+// rays of light j.  NR = rays per thread.  The launch covers the sphere chunk [c0, c0+cnt) (cnt % 8 == 0) whose table
+// the host copied to c_tab[tb ...].  Work distribution: every WARP claims groups of 32*NR consecutive rays from a
+// global counter (one per light) — no CTA-wide barrier anywhere.  One launch per (light, sphere chunk); with more than
+// one chunk the running (t, id) / occlusion state is carried in the output arrays.
+//
+// Candidates (filter passes, ~1.5 per ray out of S) are not tested where they are found: a warp appends them to its
+// own shared-memory queue and runs the exact test over the queue with all 32 lanes busy ("flush"), when the queue
+// fills and at the end of the group.  Results meet in shared memory: closest hit = atomicMin on the packed key
+// (float bits of t << 32 | sphere id) — min t, and on equal t the lowest index, which is the reference's tie-break
+// (first object wins, trace.py:26; planes have ids >= S and so lose ties against spheres, trace.py:36).
+constexpr int KP = 4;                    // sphere pairs per scan step (8 spheres)
+constexpr int kQCap = 1024;              // candidate queue entries per warp
+constexpr int kQFlush = kQCap - 32 * 16; // flush before an append (<= 16 per lane) could overflow
+constexpr unsigned long long kNoHit = ((unsigned long long)0x4479c000u << 32) | 0xffffffffu;   // (999.0f, id -1)
 
+struct IsectSmem {
+    uint32_t q[kThreads / 32][kQCap];
+    unsigned long long key[kThreads / 32][32 * 8];     // per ray of the warp's group: packed closest hit / occlusion flag
+};
+
+template <int MODE, int NR>
+__global__ void __launch_bounds__(kThreads, NR == 8 ? 2 : 3)
+k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
+    constexpr bool ANY = (MODE == 2), PIV = (MODE != 0);
+    constexpr int GW = 32 * NR;                               // rays per warp group
+    constexpr int NO = PIV ? 1 : NR;                          // 2*O operands exist only in the 8-FFMA2 form
+    extern __shared__ __align__(16) unsigned char s_raw[];
+    IsectSmem& sm = *reinterpret_cast<IsectSmem*>(s_raw);
+    const bool first = (c0 == 0), last = (c0 + cnt >= sc.Spad);
     const uint32_t n_in = *q.n_in;
-    const uint32_t ngroups = (n_in + GW - 1) / GW;            // per light for ANY
+    const uint32_t ngroups = (n_in + GW - 1) / GW;
     const float cmax = pv.bounds[0], rmax = pv.bounds[1];
     const float kInf = __int_as_float(0x7f800000);
-    const int nphase = ANY ? sc.L : 1;
-    const uint32_t lane = lane_id();
-    uint32_t slow_cnt = 0;
+    const uint32_t lane = lane_id(), wid = threadIdx.x >> 5;
+    const int npair = cnt >> 1;
+    uint32_t* sq = sm.q[wid];
+    unsigned long long* skey = sm.key[wid];
+    uint32_t slow_cnt = 0, exact_cnt = 0;
+    // j: pivot of this launch (light index for ANY, camera = L for MODE 1); its table is c_tab[tb + 2*pair + {0,1}].
+    // tb is a kernel parameter so that the table index provably lives in uniform registers (LDCU -> UR operands).
+    V3 Vp = mk(0.f, 0.f, 0.f);
+    if (PIV) { const float4 v = __ldg(&pv.piv[j]); Vp = mk(v.x, v.y, v.z); }
+    uint32_t* work = q.work + (ANY ? j : 0);
 
-    for (int ph = 0; ph < nphase; ++ph) {
-        const int j = ANY ? (int)((blockIdx.x + (uint32_t)ph) % (uint32_t)sc.L) : sc.L;     // pivot of this phase
-        const float4* tab = (PIV ? pv.tab + (size_t)j * sc.Spad : sc.sphA) + c0;
-        if (ph > 0) __syncthreads();
-        for (int s = threadIdx.x; s < cnt; s += kThreads) {
-            const float4 a = tab[s];
-            s_dup[2 * s] = make_float4(a.x, a.x, a.y, a.y);
-            s_dup[2 * s + 1] = make_float4(a.z, a.z, a.w, a.w);
-            s_r2[s] = (c0 + s < sc.S) ? sc.sphB[c0 + s].w : 0.f;
-        }
-        __syncthreads();
-        V3 Vp = mk(0.f, 0.f, 0.f);
-        if (PIV) { const float4 v = __ldg(&pv.piv[j]); Vp = mk(v.x, v.y, v.z); }
-        uint32_t* work = q.work + (ANY ? j : 0);
+    for (;;) {
+        uint32_t g = 0;
+        if (lane == 0) g = atomicAdd(work, 1u);
+        g = __shfl_sync(0xffffffffu, g, 0);
+        if (g >= ngroups) break;
+        // A thread owns NR CONSECUTIVE queue entries (neighbouring pixels): they pass the filter at the same spheres.
+        const uint32_t gbase = g * (uint32_t)GW, i0 = gbase + lane * NR;
 
-        for (;;) {
-            uint32_t g = 0;
-            if (lane == 0) g = atomicAdd(work, 1u);
-            g = __shfl_sync(0xffffffffu, g, 0);
-            if (g >= ngroups) break;
-            // A thread owns NR CONSECUTIVE queue entries (neighbouring pixels): they pass the filter at the same
-            // spheres, so one slow-path entry serves all of them.
-            const uint32_t i0 = g * (uint32_t)GW + lane * NR;
-
-            // ---- per-ray constants, packed two rays per register pair ----
-            float2 dx[NP], dy[NP], dz[NP], nod[NP], o2x[NO], o2y[NO], o2z[NO];
-            float thr[NR], best[ANY ? 1 : NR]; int bid[NR];
+        // ---- per-ray constants (32-bit registers, broadcast operands of FFMA2) ----
+        float dx[NR], dy[NR], dz[NR], nod[NR], o2x[NO], o2y[NO], o2z[NO], nthr[NO], thr[PIV ? NR : 1];
 #pragma unroll
-            for (int r = 0; r < NR; ++r) {
-                const uint32_t i = i0 + r;
-                bool active = i < n_in;
-                V3 O = mk(0.f, 0.f, 0.f), D = mk(0.f, 0.f, 0.f);
-                float th = kInf, no = 0.f;
-                bid[r] = -1;
-                if (!ANY) best[r] = kTMax;
-                if (active && !first) {                           // running state of the earlier sphere chunks
-                    if (ANY) { if (q.occl[(size_t)j * n_in + i]) { bid[r] = 0; active = false; } }
-                    else     { best[r] = q.hit_t[i]; bid[r] = q.hit_id[i]; }
-                }
-                if (active) {
-                    if (MODE == 2) {
-                        const float4 p = q.hP[i];
-                        O = mk(p.x, p.y, p.z);
-                        const V3 d = sub3(Vp, O);                                   // common.py:84-91
-                        const float nrm = __fsqrt_rn(dot3(d, d));
-                        D = mk(__fdiv_rn(d.x, nrm), __fdiv_rn(d.y, nrm), __fdiv_rn(d.z, nrm));
-                        const float A = cmax + __fsqrt_rn(dot3(Vp, Vp)), B = cmax + __fsqrt_rn(dot3(O, O));
-                        const float e = nrm * 9.5367432e-7f;                        // 2^-20 |V-P|: ray line vs pivot
-                        th = -(fmaf(3.8146973e-6f, fmaf(A, A, B * B), fmaf(4.f * e, rmax, 16.f * e * e)) + 1e-12f);
-                        no = -dot3(Vp, D);
-                    } else {
-                        const float4 o = q.rayO[i], d = q.rayD[i];
-                        O = mk(o.x, o.y, o.z); D = mk(d.x, d.y, d.z);
-                        const float oo = dot3(O, O);
-                        const float A = cmax + __fsqrt_rn(oo);
-                        const float margin = fmaf(3.8146973e-6f /* 64 * 2^-24 */, A * A, 1e-12f);
-                        if (MODE == 1) { th = -2.f * margin; no = -dot3(Vp, D); }   // O == Vp for every primary ray
-                        else           { th = oo - margin;   no = -dot3(O, D); }
-                    }
-                }
-                const int p = r >> 1;
-                if (r & 1) { dx[p].y = D.x; dy[p].y = D.y; dz[p].y = D.z; nod[p].y = no; }
-                else       { dx[p].x = D.x; dy[p].x = D.y; dz[p].x = D.z; nod[p].x = no; }
-                if (!PIV) {
-                    if (r & 1) { o2x[p].y = 2.f * O.x; o2y[p].y = 2.f * O.y; o2z[p].y = 2.f * O.z; }
-                    else       { o2x[p].x = 2.f * O.x; o2y[p].x = 2.f * O.y; o2z[p].x = 2.f * O.z; }
-                }
-                thr[r] = th;
+        for (int r = 0; r < NR; ++r) {
+            const uint32_t i = i0 + r;
+            bool active = i < n_in;
+            V3 O = mk(0.f, 0.f, 0.f), D = mk(0.f, 0.f, 0.f);
+            float th = kInf, no = 0.f;
+            unsigned long long key0 = ANY ? 0ull : kNoHit;
+            if (active && !first) {                               // running state of the earlier sphere chunks
+                if (ANY) { if (q.occl[(size_t)j * n_in + i]) { key0 = 1ull; active = false; } }
+                else     { key0 = ((unsigned long long)__float_as_uint(q.hit_t[i]) << 32) | (uint32_t)q.hit_id[i]; }
             }
-            float thr_t = thr[0];                             // PIV: loosest threshold of this thread's rays
-#pragma unroll
-            for (int r = 1; r < NR; ++r) thr_t = fminf(thr_t, thr[r]);
-
-            // q of ray pair p against the sphere whose duplicated operands are (ax, ay, az, aw)
-            auto qpair = [&](int p, float2 ax, float2 ay, float2 az, float2 aw) -> float2 {
-                const float2 b = ffma2(ax, dx[p], ffma2(ay, dy[p], ffma2(az, dz[p], nod[p])));
-                if (PIV) return ffma2(b, b, aw);
-                return ffma2(b, b, ffma2(ax, o2x[PIV ? 0 : p], ffma2(ay, o2y[PIV ? 0 : p], ffma2(az, o2z[PIV ? 0 : p], aw))));
-            };
-
-            // -- candidates in spheres sb, sb+1 (rare): recompute q per sphere, the exact test decides --
-            auto slow2 = [&](int sb) {
-                slow_cnt++;
-#pragma unroll 1
-                for (int k = 0; k < 2; ++k) {
-                    const float4 u = s_dup[2 * (sb + k)], w = s_dup[2 * (sb + k) + 1];
-                    const float r2 = s_r2[sb + k];
-#pragma unroll
-                    for (int r = 0; r < NR; ++r) {
-                        const int p = r >> 1;
-                        const float2 qv = qpair(p, make_float2(u.x, u.y), make_float2(u.z, u.w), make_float2(w.x, w.y), make_float2(w.z, w.w));
-                        if (!(((r & 1) ? qv.y : qv.x) >= thr[r])) continue;
-                        const V3 D = (r & 1) ? mk(dx[p].y, dy[p].y, dz[p].y) : mk(dx[p].x, dy[p].x, dz[p].x);
-                        V3 O;
-                        if (MODE == 0)      O = (r & 1) ? mk(0.5f * o2x[PIV ? 0 : p].y, 0.5f * o2y[PIV ? 0 : p].y, 0.5f * o2z[PIV ? 0 : p].y)
-                                                        : mk(0.5f * o2x[PIV ? 0 : p].x, 0.5f * o2y[PIV ? 0 : p].x, 0.5f * o2z[PIV ? 0 : p].x);   // exact
-                        else if (MODE == 1) O = Vp;
-                        else { const float4 hp = q.hP[i0 + r]; O = mk(hp.x, hp.y, hp.z); }
-                        const float t = sphere_exact(O, D, u.x, u.z, w.x, r2);
-                        if (ANY) {
-                            if (t > 0.f && t < kTMax) {           // occluded: retire the lane (b = 0 -> q = r^2 - |C-V|^2)
-                                bid[r] = 0; thr[r] = kInf;
-                                if (r & 1) { dx[p].y = 0.f; dy[p].y = 0.f; dz[p].y = 0.f; nod[p].y = 0.f; }
-                                else       { dx[p].x = 0.f; dy[p].x = 0.f; dz[p].x = 0.f; nod[p].x = 0.f; }
-                            }
-                        } else if (t > 0.f && t < best[r]) { best[r] = t; bid[r] = c0 + sb + k; }   // trace.py:26-29
-                    }
-                }
-            };
-
-            // ---- spheres: scan two spheres x NR rays per step.  The candidate decision of a step is taken one
-            // step LATER (software pipelining): the vote/branch then never waits on the FMA pipe, and the next
-            // step's FFMA2s issue back to back.  Candidates are still handled in sphere order (tie-break). ----
-            float m_prev = -3.0e38f; bool any_prev = false;
-            int s = 0;
-            for (;;) {
-                bool found = false;
-#pragma unroll 2
-                for (; s < cnt; s += 2) {
-                    const float4 u0 = s_dup[2 * s], w0 = s_dup[2 * s + 1], u1 = s_dup[2 * s + 2], w1 = s_dup[2 * s + 3];
-                    const bool fire = __any_sync(0xffffffffu, PIV ? (m_prev >= thr_t) : any_prev);   // step s-2
-                    if (PIV) {                   // one threshold per thread: max of the 4*NP q values against it
-                        float m = -3.0e38f;
-#pragma unroll
-                        for (int p = 0; p < NP; ++p) {
-                            const float2 q0 = qpair(p, make_float2(u0.x, u0.y), make_float2(u0.z, u0.w), make_float2(w0.x, w0.y), make_float2(w0.z, w0.w));
-                            const float2 q1 = qpair(p, make_float2(u1.x, u1.y), make_float2(u1.z, u1.w), make_float2(w1.x, w1.y), make_float2(w1.z, w1.w));
-                            m = fmax3(m, q0.x, q0.y); m = fmax3(m, q1.x, q1.y);
-                        }
-                        m_prev = m;
-                    } else {
-                        bool any = false;
-#pragma unroll
-                        for (int p = 0; p < NP; ++p) {
-                            const float2 q0 = qpair(p, make_float2(u0.x, u0.y), make_float2(u0.z, u0.w), make_float2(w0.x, w0.y), make_float2(w0.z, w0.w));
-                            const float2 q1 = qpair(p, make_float2(u1.x, u1.y), make_float2(u1.z, u1.w), make_float2(w1.x, w1.y), make_float2(w1.z, w1.w));
-                            any |= (q0.x >= thr[2 * p]) | (q0.y >= thr[2 * p + 1]) | (q1.x >= thr[2 * p]) | (q1.y >= thr[2 * p + 1]);
-                        }
-                        any_prev = any;
-                    }
-                    if (fire) { found = true; break; }
-                }
-                if (found) { slow2(s - 2); s += 2; continue; }            // step s is computed and pending
-                if (__any_sync(0xffffffffu, PIV ? (m_prev >= thr_t) : any_prev)) slow2(cnt - 2);   // flush the last step
-                break;
-            }
-
-            // ---- planes after the last sphere chunk (trace.py:32-39), then write back ----
-#pragma unroll
-            for (int r = 0; r < NR; ++r) {
-                const uint32_t i = i0 + r;
-                if (i >= n_in) continue;
-                const int p = r >> 1;
-                if (ANY) {
-                    bool occluded = bid[r] >= 0;
-                    if (last && !occluded && sc.Pl > 0) {
-                        const float4 hp = q.hP[i]; const V3 O = mk(hp.x, hp.y, hp.z);
-                        const V3 D = (r & 1) ? mk(dx[p].y, dy[p].y, dz[p].y) : mk(dx[p].x, dy[p].x, dz[p].x);
-                        for (int pl = 0; pl < sc.Pl && !occluded; ++pl) {
-                            const float t = plane_exact(O, D, __ldg(&sc.plO[pl]), __ldg(&sc.plN[pl]));
-                            occluded = (t > 0.f && t < kTMax);
-                        }
-                    }
-                    q.occl[(size_t)j * n_in + i] = occluded ? 1 : 0;
+            skey[lane * NR + r] = key0;
+            if (active) {
+                if (MODE == 2) {
+                    const float4 p = q.hP[i];
+                    O = mk(p.x, p.y, p.z);
+                    const V3 d = sub3(Vp, O);                                   // common.py:84-91
+                    const float nrm = __fsqrt_rn(dot3(d, d));
+                    D = mk(__fdiv_rn(d.x, nrm), __fdiv_rn(d.y, nrm), __fdiv_rn(d.z, nrm));
+                    const float A = cmax + __fsqrt_rn(dot3(Vp, Vp)), B = cmax + __fsqrt_rn(dot3(O, O));
+                    const float e = nrm * 9.5367432e-7f;                        // 2^-20 |V-P|: ray line vs pivot
+                    th = -(fmaf(3.8146973e-6f, fmaf(A, A, B * B), fmaf(4.f * e, rmax, 16.f * e * e)) + 1e-12f);
+                    no = -dot3(Vp, D);
                 } else {
-                    if (last) {
-                        const V3 D = (r & 1) ? mk(dx[p].y, dy[p].y, dz[p].y) : mk(dx[p].x, dy[p].x, dz[p].x);
-                        V3 O;
-                        if (MODE == 0)      O = (r & 1) ? mk(0.5f * o2x[PIV ? 0 : p].y, 0.5f * o2y[PIV ? 0 : p].y, 0.5f * o2z[PIV ? 0 : p].y)
-                                                        : mk(0.5f * o2x[PIV ? 0 : p].x, 0.5f * o2y[PIV ? 0 : p].x, 0.5f * o2z[PIV ? 0 : p].x);
-                        else                O = Vp;
-                        for (int pl = 0; pl < sc.Pl; ++pl) {
-                            const float t = plane_exact(O, D, __ldg(&sc.plO[pl]), __ldg(&sc.plN[pl]));
-                            if (t > 0.f && t < best[r]) { best[r] = t; bid[r] = sc.S + pl; }
-                        }
-                    }
-                    q.hit_t[i] = best[r]; q.hit_id[i] = bid[r];
+                    const float4 o = q.rayO[i], d = q.rayD[i];
+                    O = mk(o.x, o.y, o.z); D = mk(d.x, d.y, d.z);
+                    const float oo = dot3(O, O);
+                    const float A = cmax + __fsqrt_rn(oo);
+                    const float margin = fmaf(3.8146973e-6f /* 64 * 2^-24 */, A * A, 1e-12f);
+                    if (MODE == 1) { th = -2.f * margin; no = -dot3(Vp, D); }   // O == Vp for every primary ray
+                    else           { th = oo - margin;   no = -dot3(O, D); }
                 }
             }
+            dx[r] = D.x; dy[r] = D.y; dz[r] = D.z; nod[r] = no;
+            // MODE 0: the per-ray threshold is folded into q (q' = q - thr, one more FFMA2): candidates are q' >= 0
+            // (an inactive ray has thr = +inf, so its q' is -inf and never qualifies).
+            if (!PIV) { o2x[r] = 2.f * O.x; o2y[r] = 2.f * O.y; o2z[r] = 2.f * O.z; nthr[r] = -th; }
+            else      thr[PIV ? r : 0] = th;
         }
+        float thr_t = 0.f;                                    // one scan threshold per thread: the loosest of its rays
+        if (PIV) {
+            thr_t = thr[0];
+#pragma unroll
+            for (int r = 1; r < NR; ++r) thr_t = fminf(thr_t, thr[PIV ? r : 0]);
+        }
+        uint32_t qcnt = 0;                                    // candidates waiting in this warp's queue (warp-uniform)
+
+        // q (minus thr in MODE 0) of ray r against sphere pair (u, w): lanes .x/.y = spheres 2i / 2i+1
+        auto qray = [&](int r, const float4& u, const float4& w) -> float2 {
+            const float2 b = ffma2(make_float2(u.x, u.y), bc(dx[r]), ffma2(make_float2(u.z, u.w), bc(dy[r]),
+                                   ffma2(make_float2(w.x, w.y), bc(dz[r]), bc(nod[r]))));
+            if (PIV) return ffma2(b, b, make_float2(w.z, w.w));
+            const int ro = PIV ? 0 : r;
+            const float2 t = ffma2(make_float2(u.x, u.y), bc(o2x[ro]), ffma2(make_float2(u.z, u.w), bc(o2y[ro]),
+                                   ffma2(make_float2(w.x, w.y), bc(o2z[ro]), ffma2(make_float2(w.z, w.w), bc(1.0f), bc(nthr[ro])))));
+            return ffma2(b, b, t);
+        };
+
+        // -- exact tests over the queue, one candidate per lane per iteration (dense) --
+        auto flush = [&]() {
+            __syncwarp();
+            for (uint32_t idx = lane; idx < qcnt; idx += 32) {
+                const uint32_t item = sq[idx];
+                const uint32_t rl = item & 255u; const int sid = c0 + (int)(item >> 8);
+                const uint32_t i = gbase + rl;
+                V3 O, D;                                       // the ray, re-read (bit-identical to the setup above)
+                if (MODE == 2) { const float4 hp = q.hP[i]; O = mk(hp.x, hp.y, hp.z); D = normalize3(sub3(Vp, O)); }
+                else {
+                    const float4 d = q.rayD[i]; D = mk(d.x, d.y, d.z);
+                    if (MODE == 1) O = Vp; else { const float4 o = q.rayO[i]; O = mk(o.x, o.y, o.z); }
+                }
+                const float4 sp = __ldg(&sc.sphB[sid]);
+                const float t = sphere_exact(O, D, sp.x, sp.y, sp.z, sp.w);
+                if (t > 0.f && t < kTMax) {                                                   // trace.py:26-29
+                    if (ANY) skey[rl] = 1ull;
+                    else     atomicMin(&skey[rl], ((unsigned long long)__float_as_uint(t) << 32) | (uint32_t)sid);
+                }
+            }
+            exact_cnt += (qcnt + 31 - lane) / 32;
+            __syncwarp();
+            qcnt = 0;
+        };
+
+        // -- candidates in sphere pair `pair` (rare): recompute q per ray, append the passing (ray, sphere)
+        // combinations to the warp's queue (warp prefix sum of the per-lane counts) --
+        auto slow_pair = [&](int pair) {
+            const float4 u = c_tab[tb + 2 * pair], w = c_tab[tb + 2 * pair + 1];
+            uint32_t cand = 0;
+#pragma unroll
+            for (int r = 0; r < NR; ++r) {
+                const float2 qv = qray(r, u, w);
+                const float lim = PIV ? thr[PIV ? r : 0] : 0.f;
+                if (qv.x >= lim) cand |= 1u << (2 * r);
+                if (qv.y >= lim) cand |= 2u << (2 * r);
+            }
+            if (c0 + 2 * pair + 1 >= sc.S) cand &= (c0 + 2 * pair >= sc.S) ? 0u : 0x55555555u;     // padding spheres
+            const uint32_t n = (uint32_t)__popc(cand);
+            uint32_t x = n;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, d); if ((int)lane >= d) x += y; }
+            uint32_t pos = qcnt + x - n;
+            qcnt += __shfl_sync(0xffffffffu, x, 31);
+            while (cand) {
+                const int bit = __ffs(cand) - 1;
+                cand &= cand - 1;
+                sq[pos++] = (lane * NR + (uint32_t)(bit >> 1)) | ((uint32_t)(2 * pair + (bit & 1)) << 8);
+            }
+            if (qcnt > (uint32_t)kQFlush) flush();
+        };
+        auto slow_step = [&](int pb, const float (&mk4)[KP]) {        // pairs pb .. pb+KP-1, per-pair maxima mk4
+            slow_cnt++;
+#pragma unroll 1
+            for (int k = 0; k < KP; ++k) {
+                float mv = mk4[0];
+#pragma unroll
+                for (int kk = 1; kk < KP; ++kk) mv = (k == kk) ? mk4[kk] : mv;
+                if (__any_sync(0xffffffffu, mv >= thr_t)) slow_pair(pb + k);
+            }
+        };
+
+        // ---- scan: KP sphere pairs x NR rays per step, pair-major; the uniform registers of a pair are refilled
+        // for the NEXT step as soon as the pair is done (rolling prefetch: LDCU latency never reaches the FMA pipe).
+        // The candidate decision of a step is taken one step LATER (software pipelining): the vote/branch never
+        // waits on the FMA pipe. ----
+        float mprev[KP];
+        float4 u[KP], w[KP];
+#pragma unroll
+        for (int k = 0; k < KP; ++k) { mprev[k] = -3.0e38f; u[k] = c_tab[tb + 2 * k]; w[k] = c_tab[tb + 2 * k + 1]; }
+        int pb = 0;                                                   // first pair of the step being computed
+        for (;;) {
+            bool found = false;
+            for (; pb < npair; pb += KP) {
+                const float mall = fmaxf(fmaxf(mprev[0], mprev[1]), fmaxf(mprev[2], mprev[3]));
+                const bool fire = __any_sync(0xffffffffu, mall >= thr_t);       // step pb-KP
+                float mk4[KP];
+#pragma unroll
+                for (int k = 0; k < KP; ++k) {
+                    float m = -3.0e38f;
+#pragma unroll
+                    for (int r = 0; r < NR; ++r) { const float2 qv = qray(r, u[k], w[k]); m = fmax3(m, qv.x, qv.y); }
+                    mk4[k] = m;
+                    u[k] = c_tab[tb + 2 * (pb + KP + k)]; w[k] = c_tab[tb + 2 * (pb + KP + k) + 1];   // next step (c_tab is over-allocated)
+                }
+                if (fire) {                                           // handle step pb-KP first, keep this step pending
+                    slow_step(pb - KP, mprev);
+#pragma unroll
+                    for (int k = 0; k < KP; ++k) mprev[k] = mk4[k];
+                    found = true; pb += KP; break;
+                }
+#pragma unroll
+                for (int k = 0; k < KP; ++k) mprev[k] = mk4[k];
+            }
+            if (found) continue;
+            const float mall = fmaxf(fmaxf(mprev[0], mprev[1]), fmaxf(mprev[2], mprev[3]));
+            if (__any_sync(0xffffffffu, mall >= thr_t)) slow_step(npair - KP, mprev);            // flush the last step
+            break;
+        }
+        flush();
+
+        // ---- planes after the last sphere chunk (trace.py:32-39), then write back ----
+#pragma unroll
+        for (int r = 0; r < NR; ++r) {
+            const uint32_t i = i0 + r;
+            if (i >= n_in) continue;
+            const unsigned long long key = skey[lane * NR + r];
+            if (ANY) {
+                bool occluded = key != 0ull;
+                if (last && !occluded && sc.Pl > 0) {
+                    const float4 hp = q.hP[i]; const V3 O = mk(hp.x, hp.y, hp.z);
+                    const V3 D = mk(dx[r], dy[r], dz[r]);
+                    for (int pl = 0; pl < sc.Pl && !occluded; ++pl) {
+                        const float t = plane_exact(O, D, __ldg(&sc.plO[pl]), __ldg(&sc.plN[pl]));
+                        occluded = (t > 0.f && t < kTMax);
+                    }
+                }
+                q.occl[(size_t)j * n_in + i] = occluded ? 1 : 0;
+            } else {
+                float best = __uint_as_float((uint32_t)(key >> 32)); int bid = (int)(uint32_t)key;
+                if (last) {
+                    const V3 D = mk(dx[r], dy[r], dz[r]);
+                    const V3 O = (MODE == 0) ? mk(0.5f * o2x[PIV ? 0 : r], 0.5f * o2y[PIV ? 0 : r], 0.5f * o2z[PIV ? 0 : r]) : Vp;
+                    for (int pl = 0; pl < sc.Pl; ++pl) {
+                        const float t = plane_exact(O, D, __ldg(&sc.plO[pl]), __ldg(&sc.plN[pl]));
+                        if (t > 0.f && t < best) { best = t; bid = sc.S + pl; }
+                    }
+                }
+                q.hit_t[i] = best; q.hit_id[i] = bid;
+            }
+        }
+        __syncwarp();                                         // keys are re-initialised by the next group's setup
     }
     if (q.slow) {
-        const uint32_t tot = __reduce_add_sync(0xffffffffu, slow_cnt);
-        if (lane == 0 && tot) atomicAdd(q.slow, (unsigned long long)tot);
+        const uint32_t tot = __reduce_add_sync(0xffffffffu, slow_cnt), tot2 = __reduce_add_sync(0xffffffffu, exact_cnt);
+        if (lane == 0 && tot) { atomicAdd(q.slow, (unsigned long long)tot); atomicAdd(q.slow + 1, (unsigned long long)tot2); }
     }
 }
 
@@ -768,7 +821,7 @@ struct DevCtx {
     bool init = false;
     int sm_count = 0;
     int isect_blocks_per_sm = 2;
-    int force_np = 0; bool no_pivot = false;                       // tuning overrides (env B200RT_NP, B200RT_NO_PIVOT)
+    int force_nr = 0, force_nr0 = 0; bool no_pivot = false;                       // tuning overrides (env B200RT_NR, B200RT_NO_PIVOT)
     Buf sphA, sphB, sphCol, plO, plN, plNu, plCol, lights, cmax;   // packed scene
     Buf pivTab, pivPos;                                            // pivot tables (k_pivot)
     Buf stage;                                                     // host-scene / host-pixel_loc staging
@@ -834,29 +887,47 @@ int launch_intersect(DevCtx& c, const SceneDev& sc, const QueueDev& q, bool nofi
     return 0;
 }
 
-size_t isect2_smem_bytes(int Spad) { return (size_t)std::min(Spad, kChunk2) * (2 * sizeof(float4) + sizeof(float)); }
-
-// Rays per thread of the production kernel: 8 (4 pairs) for big queues, fewer for small ones (more groups than warps).
-// One launch per sphere chunk; `work` points at (L+1) zeroed counters per chunk.
-template <int MODE>
-int launch_isect2(DevCtx& c, const SceneDev& sc, QueueDev q, const PivotDev& pv, size_t max_rays, uint32_t* work, cudaStream_t st) {
-    const size_t smem = isect2_smem_bytes(sc.Spad);
-    const int grid = c.sm_count * 2;
-    const size_t warps = (size_t)grid * (kThreads / 32);
-    const int np = c.force_np ? c.force_np : (max_rays >= warps * 256 * 4 ? 4 : (max_rays >= warps * 128 * 4 ? 2 : 1));
-    for (int c0 = 0, k = 0; c0 < sc.Spad; c0 += kChunk2, ++k) {
-        q.work = work + (size_t)k * (sc.L + 1);
-        if (np == 4)      k_isect2<MODE, 4><<<grid, kThreads, smem, st>>>(sc, q, pv, c0);
-        else if (np == 2) k_isect2<MODE, 2><<<grid, kThreads, smem, st>>>(sc, q, pv, c0);
-        else              k_isect2<MODE, 1><<<grid, kThreads, smem, st>>>(sc, q, pv, c0);
-        CK(cudaGetLastError());
-    }
+constexpr size_t isect3_smem(int) { return sizeof(IsectSmem); }
+template <int MODE> int set_isect3_attr() {
+    CK(cudaFuncSetAttribute(k_isect3<MODE, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IsectSmem)));
+    CK(cudaFuncSetAttribute(k_isect3<MODE, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IsectSmem)));
+    CK(cudaFuncSetAttribute(k_isect3<MODE, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IsectSmem)));
     return 0;
 }
 
-template <int MODE, int NP>
-int set_isect2_attr() {
-    CK(cudaFuncSetAttribute(k_isect2<MODE, NP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)isect2_smem_bytes(kChunk2)));
+// k_isect3 launches for one query kernel (closest hit of a ray queue, or the shadow query of a hit list).
+// The constant-memory table holds kTabCap spheres: a launch covers one sphere chunk and, for shadow rays, as many
+// lights as fit beside each other.  `work` points at nsch*(L+1) zeroed group counters.
+// Rays per thread: 8 for big queues, fewer for small ones (more groups than warps).
+template <int MODE>
+int launch_isect3(DevCtx& c, const SceneDev& sc, QueueDev q, const PivotDev& pv, size_t max_rays, uint32_t* work, cudaStream_t st) {
+    const size_t warps = (size_t)c.sm_count * 2 * (kThreads / 32);
+    int nr = c.force_nr ? c.force_nr : (max_rays >= warps * 256 * 4 ? 8 : (max_rays >= warps * 128 * 4 ? 4 : 2));
+    if (MODE == 0 && c.force_nr0) nr = c.force_nr0;             // (measured: 8 rays/thread wins for the 8-FFMA2 form too, despite a 60-byte spill)
+    const int grid = c.sm_count * (nr == 8 ? 2 : 3);
+    const int L = sc.L;
+    const int chunk = std::min(sc.Spad, kTabCap);
+    const int lp = (MODE == 2 && sc.Spad <= kTabCap) ? std::max(1, kTabCap / sc.Spad) : 1;      // light tables resident at once
+    const int nlights = (MODE == 2) ? L : 1;
+    for (int c0 = 0, k = 0; c0 < sc.Spad; c0 += chunk, ++k) {
+        const int cnt = std::min(chunk, sc.Spad - c0);
+        q.work = work + (size_t)k * (L + 1);
+        for (int j0 = 0; j0 < nlights; j0 += lp) {
+            const int nj = std::min(lp, nlights - j0);
+            for (int jj = 0; jj < nj; ++jj) {
+                const int tj = (MODE == 2) ? j0 + jj : (MODE == 1 ? L : L + 1);
+                CK(cudaMemcpyToSymbolAsync(c_tab, pv.tab + (size_t)tj * sc.Spad + c0, sizeof(float4) * cnt,
+                                           sizeof(float4) * (size_t)jj * cnt, cudaMemcpyDeviceToDevice, st));
+            }
+            for (int jj = 0; jj < nj; ++jj) {
+                const int j = (MODE == 2) ? j0 + jj : L, tb = jj * cnt;
+                if (nr == 8)      k_isect3<MODE, 8><<<grid, kThreads, isect3_smem(8), st>>>(sc, q, pv, c0, cnt, j, tb);
+                else if (nr == 4) k_isect3<MODE, 4><<<grid, kThreads, isect3_smem(4), st>>>(sc, q, pv, c0, cnt, j, tb);
+                else              k_isect3<MODE, 2><<<grid, kThreads, isect3_smem(2), st>>>(sc, q, pv, c0, cnt, j, tb);
+                CK(cudaGetLastError());
+            }
+        }
+    }
     return 0;
 }
 
@@ -868,10 +939,9 @@ int init_ctx(DevCtx& c, int device) {
     const int smem_max = (int)isect_smem_bytes(kChunkS);
     CK(cudaFuncSetAttribute(k_intersect<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
     CK(cudaFuncSetAttribute(k_intersect<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
-    if (int rc = set_isect2_attr<0, 1>()) return rc; if (int rc = set_isect2_attr<0, 2>()) return rc; if (int rc = set_isect2_attr<0, 4>()) return rc;
-    if (int rc = set_isect2_attr<1, 1>()) return rc; if (int rc = set_isect2_attr<1, 2>()) return rc; if (int rc = set_isect2_attr<1, 4>()) return rc;
-    if (int rc = set_isect2_attr<2, 1>()) return rc; if (int rc = set_isect2_attr<2, 2>()) return rc; if (int rc = set_isect2_attr<2, 4>()) return rc;
-    { const char* e = getenv("B200RT_NP"); c.force_np = e ? atoi(e) : 0; if (c.force_np != 1 && c.force_np != 2 && c.force_np != 4) c.force_np = 0; }
+    if (int rc = set_isect3_attr<0>()) return rc; if (int rc = set_isect3_attr<1>()) return rc; if (int rc = set_isect3_attr<2>()) return rc;
+    { const char* e = getenv("B200RT_NR"); c.force_nr = e ? atoi(e) : 0; if (c.force_nr != 2 && c.force_nr != 4 && c.force_nr != 8) c.force_nr = 0; }
+    { const char* e = getenv("B200RT_NR0"); c.force_nr0 = e ? atoi(e) : 0; if (c.force_nr0 != 2 && c.force_nr0 != 4 && c.force_nr0 != 8) c.force_nr0 = 0; }
     { const char* e = getenv("B200RT_NO_PIVOT"); c.no_pivot = e && atoi(e) != 0; }
     CK(cudaEventCreateWithFlags(&c.done, cudaEventDisableTiming));
     c.init = true;
@@ -886,7 +956,7 @@ namespace {
 int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     const bool stats = a->stats != nullptr;
     const int S = a->S, L = a->L, Pl = a->Pl;
-    const int Spad = std::max(4, (S + 3) & ~3);
+    const int Spad = std::max(8, (S + 7) & ~7);               // k_isect3 scans 8 spheres per step
     const int depth = (int)a->refl_depth;
     const int ns = a->aliasing ? 9 : 1;
     const int W = a->W, H = a->H;
@@ -926,9 +996,9 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     }
     SceneDev sc{ c.sphA.as<float4>(), c.sphB.as<float4>(), c.sphCol.as<float4>(), c.plO.as<float4>(), c.plN.as<float4>(),
                  c.plNu.as<float4>(), c.plCol.as<float4>(), c.lights.as<float4>(), c.cmax.as<float>(), S, Spad, Pl, L };
-    CK(c.pivTab.ensure(sizeof(float4) * (size_t)(L + 1) * Spad)); CK(c.pivPos.ensure(sizeof(float4) * (L + 1)));
+    CK(c.pivTab.ensure(sizeof(float4) * (size_t)(L + 2) * Spad)); CK(c.pivPos.ensure(sizeof(float4) * (L + 1)));
     {
-        const int n = (L + 1) * Spad;
+        const int n = (L + 2) * (Spad / 2);
         k_pivot<<<(n + 255) / 256, 256, 0, st>>>(sc, (float)a->cam_origin[0], (float)a->cam_origin[1], (float)a->cam_origin[2],
                                                  c.pivTab.as<float4>(), c.pivPos.as<float4>());
         CK(cudaGetLastError());
@@ -946,14 +1016,14 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     CK(c.hP.ensure(sizeof(float4) * cap)); CK(c.hN.ensure(sizeof(float4) * cap)); CK(c.hD.ensure(sizeof(float4) * cap));
     CK(c.acc.ensure(sizeof(float) * 3 * cap)); CK(c.occl.ensure(std::max<size_t>(cap * (size_t)L, 1)));
     const int ctr_stride = 4 * (depth + 2);
-    CK(c.ctr.ensure(sizeof(uint32_t) * (size_t)ctr_stride * nchunks)); CK(c.slow.ensure(sizeof(unsigned long long)));
+    CK(c.ctr.ensure(sizeof(uint32_t) * (size_t)ctr_stride * nchunks)); CK(c.slow.ensure(2 * sizeof(unsigned long long)));
     CK(cudaMemsetAsync(c.ctr.p, 0, sizeof(uint32_t) * (size_t)ctr_stride * nchunks, st));
-    const int nsch = (Spad + kChunk2 - 1) / kChunk2;             // sphere chunks = k_isect2 launches per query kernel
+    const int nsch = (Spad + kTabCap - 1) / kTabCap;             // sphere chunks of the constant-memory table
     const size_t work_per_depth = (size_t)2 * nsch * (L + 1);    // closest + shadow
     const size_t work_n = work_per_depth * (depth + 1) * nchunks;
     CK(c.work.ensure(sizeof(uint32_t) * work_n));
     CK(cudaMemsetAsync(c.work.p, 0, sizeof(uint32_t) * work_n, st));
-    CK(cudaMemsetAsync(c.slow.p, 0, sizeof(unsigned long long), st));
+    CK(cudaMemsetAsync(c.slow.p, 0, 2 * sizeof(unsigned long long), st));
 
     {   // persistent grid for the intersection kernels
         int nb = 0; CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_intersect<false, true>, kThreads, isect_smem_bytes(Spad)));
@@ -991,7 +1061,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
 
         for (int d = 0; d <= depth; ++d) {
             uint32_t* cd = ctr + 4 * d;             // [0] n_live, [1] n_hit, [2] work(closest), [3] work(shadow)  (scalar debug kernels)
-            uint32_t* wk = c.work.as<uint32_t>() + ((size_t)ch * (depth + 1) + d) * work_per_depth;      // k_isect2 group counters
+            uint32_t* wk = c.work.as<uint32_t>() + ((size_t)ch * (depth + 1) + d) * work_per_depth;      // k_isect3 group counters
             QueueDev q{};
             q.rayO = c.rayO.as<float4>(); q.rayD = c.rayD.as<float4>(); q.hP = c.hP.as<float4>();
             q.hit_t = c.hitT.as<float>(); q.hit_id = c.hitId.as<int>(); q.occl = c.occl.as<uint8_t>();
@@ -1008,8 +1078,8 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             {
                 int rc;
                 if (nofilter)                     rc = launch_intersect<false>(c, sc, q, true, st);
-                else if (d == 0 && !c.no_pivot)   rc = launch_isect2<1>(c, sc, q, pv, nslots, wk, st);
-                else                              rc = launch_isect2<0>(c, sc, q, pv, nslots, wk, st);
+                else if (d == 0 && !c.no_pivot)   rc = launch_isect3<1>(c, sc, q, pv, nslots, wk, st);
+                else                              rc = launch_isect3<0>(c, sc, q, pv, nslots, wk, st);
                 if (rc) return rc;
             }
             tm.end(0);
@@ -1019,7 +1089,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             if (L > 0) {
                 tm.begin(1);
                 q.n_in = cd + 1; q.work = cd + 3;
-                { int rc = nofilter ? launch_intersect<true>(c, sc, q, true, st) : launch_isect2<2>(c, sc, q, pv, nslots, wk + (size_t)nsch * (L + 1), st); if (rc) return rc; }
+                { int rc = nofilter ? launch_intersect<true>(c, sc, q, true, st) : launch_isect3<2>(c, sc, q, pv, nslots, wk + (size_t)nsch * (L + 1), st); if (rc) return rc; }
                 tm.end(1);
             }
             tm.begin(2);
@@ -1051,8 +1121,8 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
                 if (d == 0) out.primary += cd[0]; else out.bounce += cd[0];
                 out.shadow += (uint64_t)cd[1] * (uint64_t)L;
             }
-        unsigned long long slow = 0; CK(cudaMemcpy(&slow, c.slow.p, sizeof(slow), cudaMemcpyDeviceToHost));
-        out.slow_path = slow;
+        unsigned long long slow[2] = {0, 0}; CK(cudaMemcpy(slow, c.slow.p, sizeof(slow), cudaMemcpyDeviceToHost));
+        out.slow_path = slow[0]; out.exact_tests = slow[1];
         CK(cudaEventElapsedTime(&out.kernel_ms[0], ev0, ev1));
         out.kernel_ms[1] = tm.total(0); out.kernel_ms[2] = tm.total(1); out.kernel_ms[3] = tm.total(2);
         cudaEventDestroy(ev0); cudaEventDestroy(ev1);

@@ -147,3 +147,52 @@ def test_full_size_c4_crops_vs_oracle(oracle):
         tot["n"] += rep["n"]; tot["n_bad"] += rep["n_bad"]; tot["max"] = max(tot["max"], rep["max"]); tot["bad"] += rep["bad"][:5]
     print("c4 full-size crops", tot)
     assert tot["n_bad"] <= _budget(tot["n"]), tot
+
+
+def _synthetic(S, L, Pl, W, H, depth, aa, seed):
+    """Random scene in front of the main.py camera, packed (7,S)/(3,L)/(9,Pl) float32 like Scene.generate_scene()."""
+    from b200rt.scene import Camera
+    rng = np.random.default_rng(seed)
+    sp = np.zeros((7, S), np.float32)
+    if S:
+        sp[0] = rng.uniform(0.5, 9.0, S); sp[1] = rng.uniform(-3.5, 3.5, S); sp[3] = rng.uniform(0.03, 0.25, S)
+        sp[2] = sp[3] + rng.uniform(0.0, 1.5, S); sp[4:7] = rng.integers(40, 256, (3, S))
+    li = np.zeros((3, L), np.float32)
+    if L:
+        li[0] = rng.uniform(-2, 8, L); li[1] = rng.uniform(-4, 4, L); li[2] = rng.uniform(3, 7, L)
+    pl = np.zeros((9, Pl), np.float32)
+    for p in range(Pl):
+        pl[:, p] = [5, 0, -0.1 * p, 0, 0, 1, 128, 128, 128]
+    cam = Camera(resolution=(W, H), position=[-2, 0, 2.0], euler=[0, -30, 0])
+    return dict(W=W, H=H, grid=np.array(cam.grid()), cam_origin=cam.position, cam_rotation=cam.rotation, spheres=sp, lights=li,
+                planes=pl, amb=0.05, lamb=0.6, refl=0.3, refl_depth=depth, aliasing=aa)
+
+
+@pytest.mark.parametrize("S,L,Pl", [(4001, 2, 1),      # more spheres than the constant-memory table: two sphere chunks per query
+                                    (2000, 5, 1),      # light tables do not fit side by side: one upload per light
+                                    (13, 17, 2),       # many lights, odd sphere count (padding pair half empty)
+                                    (1, 1, 0), (0, 2, 1), (7, 0, 1)])
+def test_launch_plans_vs_oracle_and_unfiltered(oracle, S, L, Pl):
+    from b200rt import _lib
+    g = _synthetic(S, L, Pl, 96, 64, 2, False, seed=S * 31 + L)
+    got = _cuda(g)
+    assert np.array_equal(got, _cuda(g, flags=_lib.F_NO_FILTER)), "filter/pivot path differs from exact-test-on-everything"
+    ref = oracle.render(None, *_args(g), grid=g["grid"], shape=(96, 64))
+    rep = parity_report(got, ref)
+    print((S, L, Pl), rep)
+    assert rep["n_bad"] <= _budget(rep["n"]), rep
+    _, st = _cuda(g, stats=True)
+    _, cnt = oracle.render(None, *_args(g), grid=g["grid"], shape=(96, 64), want_counts=True)
+    assert st["primary"] == int(cnt[0])
+    assert abs(st["shadow"] - int(cnt[1])) <= max(3, 2e-3 * int(cnt[1])) and abs(st["bounce"] - int(cnt[2])) <= max(3, 2e-3 * int(cnt[2]))
+
+
+def test_small_queue_variants_bit_identical():
+    """Rays-per-thread variants of k_isect3 (chosen by queue size, forced here through the tile width) agree."""
+    g = load_golden("c4_small")
+    whole = _cuda(g)
+    W = int(g["W"])
+    out = np.zeros_like(whole)
+    from b200rt import render_host
+    render_host(None, *_args(g), grid=g["grid"], shape=(W, int(g["H"])), tile=(0, 3), out=out)     # tiny queue -> NR=2
+    assert np.array_equal(out[:, :3], whole[:, :3])
