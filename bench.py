@@ -194,7 +194,8 @@ def run_ours(args, w):
     # end to end: host buffers through b200rt_render_host, copies inside the timed region; N>1: + NCCL gather of strips
     host_out = np.zeros((3, W, H), dtype=np.uint8)
     h2d = sp_h.nbytes + li_h.nbytes + pl_h.nbytes
-    ncols_rank = sum(min(W, x0 + STRIP) - x0 for i, x0 in enumerate(range(0, W, STRIP)) if i % world == rank) if world > 1 else W
+    from b200rt.sharding import columns_of_rank
+    ncols_rank = len(columns_of_rank(W, rank, world, STRIP))
     d2h = 3 * ncols_rank * H
 
     def frame_e2e(k=0):
@@ -221,6 +222,11 @@ def run_ours(args, w):
         sm_max = float(peaks.get("sm_max_mhz", 1965.0))
         nominal_tf = 2.0 * 128 * sms * sm_max * 1e6 / 1e12
         fpr = flops_per_ray(S, Pl)
+        traffic, traffic_src = None, None          # ncu dram bytes of the k_isect3 launches of one frame (committed capture, 1 GPU, C4)
+        tp = os.path.join(ROOT, "profiles", "r01_v3_traffic.json")
+        if os.path.exists(tp) and args.workload == "c4" and world == 1:
+            tj = json.load(open(tp))
+            traffic, traffic_src = tj["traffic_bytes_per_frame"], "profiles/r01_v3_traffic.json (ncu dram__bytes_read+write, 16 k_isect3 launches of one frame)"
         ach_tf = rays_this_rank * fpr / (isect_ms * 1e-3) / 1e12
         clocks = sampler.summary()
         depth = w["refl_depth"]
@@ -238,7 +244,8 @@ def run_ours(args, w):
             "gpu_launches": int(launches_per_frame * args.steps),
             "clocks": clocks,
             "roofline": {"bound": "fp32", "kernel": "k_isect3 (closest + shadow)", "achieved": ach_tf, "peak": nominal_tf,
-                         "unit": "TFLOP/s", "frac": ach_tf / nominal_tf, "traffic": None,
+                         "unit": "TFLOP/s", "frac": ach_tf / nominal_tf, "traffic": traffic, "traffic_source": traffic_src,
+                         "algorithmic_bytes_per_frame": int(rays_this_rank * 40),
                          "peak_def": f"2 FLOP x 128 lanes x {sms} SMs x {sm_max:.0f} MHz (nominal max clock; MEASURED_PEAKS has no FP32 entry)",
                          "peak_measured_ffma": probe["ffma_tflops"], "peak_measured_ffma2": probe["ffma2_tflops"],
                          "probe_sm_mhz": probe["sm_mhz"], "frac_of_measured_ffma": ach_tf / max(probe["ffma_tflops"], 1e-9),

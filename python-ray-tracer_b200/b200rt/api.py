@@ -76,18 +76,43 @@ def render_host(pixel_loc, cam_origin, cam_rotation, spheres, lights, planes, am
     return (out, st.as_dict()) if stats else out
 
 
-def render_frame(scene, camera, amb=0.0, lamb=0.6, refl=0.3, refl_depth=2, aliasing=True, **kw):
-    """Scene + Camera -> uint8 (3,W,H) host array (channel wiring as the reference stores it: R,B,G)."""
+def render_frame(scene, camera, amb=0.0, lamb=0.6, refl=0.3, refl_depth=2, aliasing=True, devices=None, strip=None, **kw):
+    """Scene + Camera -> uint8 (3,W,H) host array (channel wiring as the reference stores it: R,B,G).
+
+    devices=[d0, d1, ...]: the frame is cut into interleaved column strips (sharding.strip_ranges), device i renders
+    strips s % N == i, and every device copies its strips straight into the one host array (direct D2H gather,
+    SURVEY §8(e)); one host thread per device (ctypes releases the GIL).  Output is bit-identical to one device."""
     spheres, lights, planes = scene.generate_scene()
     W, H = camera.resolution
-    return render_host(None, camera.position, camera.rotation, spheres, lights, planes, amb, lamb, refl, refl_depth,
-                       aliasing, grid=camera.grid(), shape=(W, H), **kw)
+    common = (None, camera.position, camera.rotation, spheres, lights, planes, amb, lamb, refl, refl_depth, aliasing)
+    if not devices or len(devices) == 1:
+        if devices:
+            kw["device"] = devices[0]
+        return render_host(*common, grid=camera.grid(), shape=(W, H), **kw)
+    from concurrent.futures import ThreadPoolExecutor
+    from .sharding import DEFAULT_STRIP
+    out = kw.pop("out", None)
+    if out is None:
+        out = np.zeros((3, W, H), dtype=np.uint8)
+    n = len(devices)
+    sw = strip or DEFAULT_STRIP
+
+    def one(i):
+        return render_host(*common, grid=camera.grid(), shape=(W, H), out=out, device=devices[i], strips=(sw, i, n), **kw)
+
+    with ThreadPoolExecutor(n) as ex:
+        res = list(ex.map(one, range(n)))
+    if kw.get("stats"):
+        tot = {k: sum(r[1][k] for r in res) for k in ("primary", "shadow", "bounce", "rays", "slow_path", "exact_tests")}
+        tot["ms_total"] = max(r[1]["ms_total"] for r in res)
+        return out, tot
+    return out
 
 
 def render_batch(scene, cameras, amb=0.0, lamb=0.6, refl=0.3, refl_depth=2, aliasing=True, devices=(0,), **kw):
     """Camera-pose batch: frame k renders on devices[k % len(devices)] (frame sharding)."""
     from concurrent.futures import ThreadPoolExecutor
-    devices = list(devices)
+    devices = list(devices)                          # frame k -> devices[k % N]  (sharding.frames_of_rank)
 
     def one(k):
         return render_frame(scene, cameras[k], amb, lamb, refl, refl_depth, aliasing, device=devices[k % len(devices)], **kw)
