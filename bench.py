@@ -99,11 +99,27 @@ def oracle_sample(w, seconds_target=15.0, threads=0):
                 sample=f"{nx2}x{ny2} px window at ({x0},{y0}) of the {W}x{H} frame, {rays} rays in {t:.1f} s", seconds=t)
 
 
+def workload_config(w, world, rays_total=None):
+    """The `config` object shared by both arms."""
+    cam = w["cameras"][0]
+    W, H = cam.resolution
+    sp, li, pl = w["scene"].generate_scene()
+    cfg = {"workload": w["label"], "resolution": [W, H], "spheres": sp.shape[1], "planes": pl.shape[1], "lights": li.shape[1],
+           "refl_depth": w["refl_depth"], "aliasing": bool(w["aliasing"]),
+           "parallelism": f"column strips of {STRIP} interleaved over {world} GPU(s)" if world > 1 else "1 GPU, whole frame",
+           "l2": "working set (ray queues, ~100 B/path x %.1f M paths) exceeds the 126 MB L2; no flush needed" % (W * H * (9 if w["aliasing"] else 1) / world / 1e6)}
+    if rays_total is not None:
+        cfg["rays_per_frame"] = rays_total
+        cfg["rays_per_pixel"] = rays_total / (W * H)
+    return cfg
+
+
 def run_reference(args, w):
     """--impl reference: the CPU port of the reference path on all host threads, bounded sample per step."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    os.environ["OMP_NUM_THREADS"] = str(os.cpu_count())          # torchrun pins it to 1; this arm is the all-host-threads CPU run
     per_step = max(2.0, min(20.0, 60.0 / max(1, args.steps + args.warmup)))
     res = None
     vals = []
@@ -118,7 +134,7 @@ def run_reference(args, w):
     line = {"impl": "reference", "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / max(1, len(vals)),
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": w["label"], "resolution": list(cam.resolution)},
+            "config": workload_config(w, args.gpus),
             "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": res["cores"], "kind": "port", "sample": res["sample"]},
             "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
@@ -192,7 +208,7 @@ def run_ours(args, w):
     rays_this_rank = st2["rays"]
 
     # end to end: host buffers through b200rt_render_host, copies inside the timed region; N>1: + NCCL gather of strips
-    host_out = np.zeros((3, W, H), dtype=np.uint8)
+    host_out = torch.zeros((3, W, H), dtype=torch.uint8).pin_memory().numpy()      # pinned: the D2H of the framebuffer is a DMA
     h2d = sp_h.nbytes + li_h.nbytes + pl_h.nbytes
     from b200rt.sharding import columns_of_rank
     ncols_rank = len(columns_of_rank(W, rank, world, STRIP))
@@ -235,10 +251,7 @@ def run_ours(args, w):
             "metric": "Mrays/s", "value": rays_total / (ms_step * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": w["label"], "resolution": [W, H], "spheres": S, "planes": Pl, "lights": L,
-                       "refl_depth": depth, "aliasing": bool(w["aliasing"]), "rays_per_frame": rays_total,
-                       "rays_per_pixel": rays_total / (W * H), "parallelism": f"column strips of {STRIP} interleaved over {world} GPU(s)" if world > 1 else "1 GPU, whole frame",
-                       "l2": "working set (ray queues, ~100 B/path x %.1f M paths) exceeds the 126 MB L2; no flush needed" % (W * H * (9 if w["aliasing"] else 1) / world / 1e6)},
+            "config": workload_config(w, world, rays_total),
             "e2e": {"value": rays_total / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": e2e_ms,
                     "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
             "gpu_launches": int(launches_per_frame * args.steps),
@@ -250,11 +263,12 @@ def run_ours(args, w):
                          "peak_measured_ffma": probe["ffma_tflops"], "peak_measured_ffma2": probe["ffma2_tflops"],
                          "probe_sm_mhz": probe["sm_mhz"], "frac_of_measured_ffma": ach_tf / max(probe["ffma_tflops"], 1e-9),
                          "algorithmic_flops_per_ray": fpr, "kernel_ms_per_frame": isect_ms, "kernel_ms_closest": st2["ms_closest"], "kernel_ms_shadow": st2["ms_shadow"], "other_ms": st2["ms_other"], "kernel_share_of_frame": isect_ms / st2["ms_total"],
-                         "slow_path_entries_per_ray": st2["slow_path"] / max(1, rays_this_rank), "exact_tests_per_ray": st2["exact_tests"] / max(1, rays_this_rank),
+                         "slow_path_entries_per_ray": st2["slow_path"] / max(1, rays_this_rank), "exact_tests_per_ray": st2["exact_tests"] / max(1, rays_this_rank), "shadow_queries_traced_fraction": st2["shadow_traced"] / max(1, st2["shadow"]),
                          "framebuffer_write_gbs": 3.0 * W * H / world / (st2["ms_total"] * 1e-3) / 1e9,
                          "hbm_peak_gbs": peaks.get("hbm_gbs")},
         }
         if world == 1 and not args.no_cpu:
+            os.environ.setdefault("OMP_NUM_THREADS", str(os.cpu_count()))
             cb = oracle_sample(w, seconds_target=12.0)
             line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
         print(json.dumps(line), flush=True)

@@ -64,6 +64,8 @@ typedef struct b200rt_stats {
     uint64_t bounce;    /* first query of every reflection trace (trace.py:128 -> :53)            */
     uint64_t slow_path; /* thread-level entries into the candidate handler (diagnostic)           */
     uint64_t exact_tests; /* exact (robust) ray-sphere tests run on filter candidates (diagnostic)  */
+    uint64_t shadow_traced; /* shadow queries actually traced: (hit, light) pairs with lamb*(Lv.N) > 0; the others are
+                               queries whose answer the reference computes and then ignores (trace.py:92-102)     */
     float    kernel_ms[4]; /* device time: [0] total, [1] closest-hit kernels, [2] shadow kernels, [3] everything else */
 } b200rt_stats;
 

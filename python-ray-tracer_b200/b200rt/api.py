@@ -103,7 +103,7 @@ def render_frame(scene, camera, amb=0.0, lamb=0.6, refl=0.3, refl_depth=2, alias
     with ThreadPoolExecutor(n) as ex:
         res = list(ex.map(one, range(n)))
     if kw.get("stats"):
-        tot = {k: sum(r[1][k] for r in res) for k in ("primary", "shadow", "bounce", "rays", "slow_path", "exact_tests")}
+        tot = {k: sum(r[1][k] for r in res) for k in ("primary", "shadow", "bounce", "rays", "slow_path", "exact_tests", "shadow_traced")}
         tot["ms_total"] = max(r[1]["ms_total"] for r in res)
         return out, tot
     return out

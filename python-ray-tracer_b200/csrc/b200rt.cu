@@ -169,6 +169,8 @@ struct QueueDev {
     uint32_t* work;                      // dynamic group counter (zeroed before the launch)
     float* hit_t; int* hit_id;           // closest-hit output, queue order
     uint8_t* occl;                       // shadow output, [light][hit]
+    const uint32_t* shidx; size_t shcap; // k_isect3 shadow input: per light the hit records whose Lambert term can be non-zero
+    const uint32_t* n_tot;               // k_isect3 shadow: number of hit records (row length of occl)
     unsigned long long* slow;            // diagnostic: thread-level slow-path entries (may be null)
 };
 
@@ -401,7 +403,9 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
     extern __shared__ __align__(16) unsigned char s_raw[];
     IsectSmem& sm = *reinterpret_cast<IsectSmem*>(s_raw);
     const bool first = (c0 == 0), last = (c0 + cnt >= sc.Spad);
-    const uint32_t n_in = *q.n_in;
+    const uint32_t n_in = q.n_in[ANY ? j : 0];                // shadow: length of light j's list
+    const uint32_t n_tot = ANY ? *q.n_tot : 0u;
+    const uint32_t* shl = ANY ? q.shidx + (size_t)j * q.shcap : nullptr;      // list entry -> hit record
     const uint32_t ngroups = (n_in + GW - 1) / GW;
     const float cmax = pv.bounds[0], rmax = pv.bounds[1];
     const float kInf = __int_as_float(0x7f800000);
@@ -433,14 +437,16 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
             V3 O = mk(0.f, 0.f, 0.f), D = mk(0.f, 0.f, 0.f);
             float th = kInf, no = 0.f;
             unsigned long long key0 = ANY ? 0ull : kNoHit;
+            uint32_t hrec = 0;
+            if (ANY && active) hrec = shl[i];
             if (active && !first) {                               // running state of the earlier sphere chunks
-                if (ANY) { if (q.occl[(size_t)j * n_in + i]) { key0 = 1ull; active = false; } }
+                if (ANY) { if (q.occl[(size_t)j * n_tot + hrec]) { key0 = 1ull; active = false; } }
                 else     { key0 = ((unsigned long long)__float_as_uint(q.hit_t[i]) << 32) | (uint32_t)q.hit_id[i]; }
             }
             skey[lane * NR + r] = key0;
             if (active) {
                 if (MODE == 2) {
-                    const float4 p = q.hP[i];
+                    const float4 p = q.hP[hrec];
                     O = mk(p.x, p.y, p.z);
                     const V3 d = sub3(Vp, O);                                   // common.py:84-91
                     const float nrm = __fsqrt_rn(dot3(d, d));
@@ -492,7 +498,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
                 const uint32_t rl = item & 255u; const int sid = c0 + (int)(item >> 8);
                 const uint32_t i = gbase + rl;
                 V3 O, D;                                       // the ray, re-read (bit-identical to the setup above)
-                if (MODE == 2) { const float4 hp = q.hP[i]; O = mk(hp.x, hp.y, hp.z); D = normalize3(sub3(Vp, O)); }
+                if (MODE == 2) { const float4 hp = q.hP[shl[i]]; O = mk(hp.x, hp.y, hp.z); D = normalize3(sub3(Vp, O)); }
                 else {
                     const float4 d = q.rayD[i]; D = mk(d.x, d.y, d.z);
                     if (MODE == 1) O = Vp; else { const float4 o = q.rayO[i]; O = mk(o.x, o.y, o.z); }
@@ -593,15 +599,16 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
             const unsigned long long key = skey[lane * NR + r];
             if (ANY) {
                 bool occluded = key != 0ull;
+                const uint32_t hrec = shl[i];
                 if (last && !occluded && sc.Pl > 0) {
-                    const float4 hp = q.hP[i]; const V3 O = mk(hp.x, hp.y, hp.z);
+                    const float4 hp = q.hP[hrec]; const V3 O = mk(hp.x, hp.y, hp.z);
                     const V3 D = mk(dx[r], dy[r], dz[r]);
                     for (int pl = 0; pl < sc.Pl && !occluded; ++pl) {
                         const float t = plane_exact(O, D, __ldg(&sc.plO[pl]), __ldg(&sc.plN[pl]));
                         occluded = (t > 0.f && t < kTMax);
                     }
                 }
-                q.occl[(size_t)j * n_in + i] = occluded ? 1 : 0;
+                q.occl[(size_t)j * n_tot + hrec] = occluded ? 1 : 0;
             } else {
                 float best = __uint_as_float((uint32_t)(key >> 32)); int bid = (int)(uint32_t)key;
                 if (last) {
@@ -634,6 +641,7 @@ struct ShadeDev {
     float* accR; float* accG; float* accB;   // per-slot colour accumulators
     const uint32_t* n_live;              // rays in the queue (k_setup input)
     uint32_t* n_hit;                     // hit records (k_setup output, k_shade input)
+    uint32_t* shidx; size_t shcap; uint32_t* n_sh;   // per light: list of hit records to shadow-test, and its length (k_setup output)
     uint32_t* n_next;                    // next ray queue length (k_shade output)
     float amb, lamb, weight;             // weight = refl^depth_index (1 for the primary trace), trace.py:131
     int emit_reflection;                 // 0 on the last depth
@@ -654,7 +662,30 @@ __global__ void k_setup(SceneDev sc, ShadeDev s) {
             else           { const float4 nu = __ldg(&sc.plNu[id - sc.S]); N = mk(nu.x, nu.y, nu.z); }             // common.py:104-110
             Pb = madd3(P, kBias, N);                                                 // trace.py:82-83
         }
-        const uint32_t h = block_append(hit, s.n_hit);
+        // The reference runs the shadow query first and then drops the light when k = lamb * (Lv.N) <= 0
+        // (trace.py:92-102): for those (hit, light) pairs the query's answer is never used, so only pairs with k > 0
+        // go on light j's list.  k is computed exactly as k_shade computes it, so both kernels take the same decision.
+        // One multi-queue append per pass: queue 0 = the hit list (first pass), the others = lights' lists
+        // (n_hit and n_sh[] are adjacent counters).
+        uint32_t h = 0;
+        for (int j0 = 0, first = 1; first || j0 < sc.L; first = 0) {
+            const int nl = min(first ? 7 : 8, sc.L - j0), sh = first ? 1 : 0;
+            uint32_t flags = (first && hit) ? 1u : 0u;
+            if (hit) {
+                for (int jj = 0; jj < nl; ++jj) {
+                    const float4 l = __ldg(&sc.lights[j0 + jj]);
+                    const V3 Lv = normalize3(sub3(mk(l.x, l.y, l.z), Pb));
+                    if (__fmul_rn(s.lamb, dot3(Lv, N)) > 0.f) flags |= 1u << (jj + sh);
+                }
+            }
+            uint32_t pos[8];
+            block_append8(flags, nl + sh, first ? s.n_hit : s.n_sh + j0, pos);
+            if (first) h = pos[0];
+#pragma unroll
+            for (int jj = 0; jj < 8; ++jj)
+                if (jj >= sh && ((flags >> jj) & 1u)) s.shidx[(size_t)(j0 + jj - sh) * s.shcap + pos[jj]] = h;
+            j0 += nl;
+        }
         if (hit) {
             s.hP[h] = make_float4(Pb.x, Pb.y, Pb.z, o.w);
             s.hN[h] = make_float4(N.x, N.y, N.z, __int_as_float(id));
@@ -676,11 +707,12 @@ __global__ void k_shade(SceneDev sc, ShadeDev s) {
         const float4 col = (id < sc.S) ? __ldg(&sc.sphCol[id]) : __ldg(&sc.plCol[id - sc.S]);
         float r = __fmul_rn(s.amb, col.x), g = __fmul_rn(s.amb, col.y), b = __fmul_rn(s.amb, col.z);   // trace.py:77
         for (int j = 0; j < sc.L; ++j) {                                                               // trace.py:86
-            if (s.occl[(size_t)j * n + h]) continue;                                                   // :95-96
             const float4 l = __ldg(&sc.lights[j]);
             const V3 Lv = normalize3(sub3(mk(l.x, l.y, l.z), Pb));                                     // :89
             const float k = __fmul_rn(s.lamb, dot3(Lv, N));                                            // :99
-            if (k > 0.f) { r = fmaf(k, col.x, r); g = fmaf(k, col.y, g); b = fmaf(k, col.z, b); }      // :101-102
+            if (!(k > 0.f)) continue;                                                                  // :101 (no shadow query was made)
+            if (s.occl[(size_t)j * n + h]) continue;                                                   // :95-96
+            r = fmaf(k, col.x, r); g = fmaf(k, col.y, g); b = fmaf(k, col.z, b);                       // :102
         }
         s.accR[slot] = fmaf(s.weight, r, s.accR[slot]);                                                // :131
         s.accG[slot] = fmaf(s.weight, g, s.accG[slot]);
@@ -825,12 +857,12 @@ struct DevCtx {
     Buf sphA, sphB, sphCol, plO, plN, plNu, plCol, lights, cmax;   // packed scene
     Buf pivTab, pivPos;                                            // pivot tables (k_pivot)
     Buf stage;                                                     // host-scene / host-pixel_loc staging
-    Buf rayO, rayD, hitT, hitId, hP, hN, hD, acc, occl, ctr, work, slow; // wavefront state
+    Buf rayO, rayD, hitT, hitId, hP, hN, hD, acc, occl, shidx, ctr, work, slow; // wavefront state
     Buf hostResult, hostPixelLoc;                                  // b200rt_render_host device copies
     cudaEvent_t done = nullptr; bool has_done = false;
     void release_all() {
         Buf* all[] = { &sphA, &sphB, &sphCol, &plO, &plN, &plNu, &plCol, &lights, &cmax, &pivTab, &pivPos, &stage, &rayO, &rayD, &hitT, &hitId,
-                       &hP, &hN, &hD, &acc, &occl, &ctr, &work, &slow, &hostResult, &hostPixelLoc };
+                       &hP, &hN, &hD, &acc, &occl, &shidx, &ctr, &work, &slow, &hostResult, &hostPixelLoc };
         for (Buf* b : all) b->release();
         if (done) { cudaEventDestroy(done); done = nullptr; } has_done = false; init = false;
     }
@@ -1015,7 +1047,9 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     CK(c.hitT.ensure(sizeof(float) * cap)); CK(c.hitId.ensure(sizeof(int) * cap));
     CK(c.hP.ensure(sizeof(float4) * cap)); CK(c.hN.ensure(sizeof(float4) * cap)); CK(c.hD.ensure(sizeof(float4) * cap));
     CK(c.acc.ensure(sizeof(float) * 3 * cap)); CK(c.occl.ensure(std::max<size_t>(cap * (size_t)L, 1)));
-    const int ctr_stride = 4 * (depth + 2);
+    CK(c.shidx.ensure(sizeof(uint32_t) * std::max<size_t>(cap * (size_t)L, 1)));
+    const int cps = 4 + L;                                       // counters per depth: n_live, n_hit, 2 debug work counters, n_sh[L]
+    const int ctr_stride = cps * (depth + 2);
     CK(c.ctr.ensure(sizeof(uint32_t) * (size_t)ctr_stride * nchunks)); CK(c.slow.ensure(2 * sizeof(unsigned long long)));
     CK(cudaMemsetAsync(c.ctr.p, 0, sizeof(uint32_t) * (size_t)ctr_stride * nchunks, st));
     const int nsch = (Spad + kTabCap - 1) / kTabCap;             // sphere chunks of the constant-memory table
@@ -1060,7 +1094,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         tm.end(2);
 
         for (int d = 0; d <= depth; ++d) {
-            uint32_t* cd = ctr + 4 * d;             // [0] n_live, [1] n_hit, [2] work(closest), [3] work(shadow)  (scalar debug kernels)
+            uint32_t* cd = ctr + cps * d;           // [0] n_live, [1] work(closest), [2] work(shadow) (scalar debug kernels), [3] n_hit, [4+j] n_sh[j]
             uint32_t* wk = c.work.as<uint32_t>() + ((size_t)ch * (depth + 1) + d) * work_per_depth;      // k_isect3 group counters
             QueueDev q{};
             q.rayO = c.rayO.as<float4>(); q.rayD = c.rayD.as<float4>(); q.hP = c.hP.as<float4>();
@@ -1070,11 +1104,13 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             s.rayO = c.rayO.as<float4>(); s.rayD = c.rayD.as<float4>(); s.hit_t = c.hitT.as<float>(); s.hit_id = c.hitId.as<int>();
             s.hP = c.hP.as<float4>(); s.hN = c.hN.as<float4>(); s.hD = c.hD.as<float4>(); s.occl = c.occl.as<uint8_t>();
             s.accR = accR; s.accG = accG; s.accB = accB;
-            s.n_live = cd + 0; s.n_hit = cd + 1; s.n_next = cd + 4;
+            s.n_live = cd + 0; s.n_hit = cd + 3; s.n_next = cd + cps;
+            s.shidx = c.shidx.as<uint32_t>(); s.shcap = cap; s.n_sh = cd + 4;
+            q.shidx = c.shidx.as<uint32_t>(); q.shcap = cap; q.n_tot = cd + 3;
             s.amb = (float)a->amb; s.lamb = (float)a->lamb; s.weight = wts[d]; s.emit_reflection = d < depth;
 
             tm.begin(0);
-            q.n_in = cd + 0; q.work = cd + 2;
+            q.n_in = cd + 0; q.work = cd + 1;
             {
                 int rc;
                 if (nofilter)                     rc = launch_intersect<false>(c, sc, q, true, st);
@@ -1088,7 +1124,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             tm.end(2);
             if (L > 0) {
                 tm.begin(1);
-                q.n_in = cd + 1; q.work = cd + 3;
+                q.n_in = nofilter ? cd + 3 : cd + 4; q.work = cd + 2;        // k_isect3: per-light list lengths n_sh[j]
                 { int rc = nofilter ? launch_intersect<true>(c, sc, q, true, st) : launch_isect3<2>(c, sc, q, pv, nslots, wk + (size_t)nsch * (L + 1), st); if (rc) return rc; }
                 tm.end(1);
             }
@@ -1117,9 +1153,10 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         b200rt_stats out{}; 
         for (int ch = 0; ch < nchunks; ++ch)
             for (int d = 0; d <= depth; ++d) {
-                const uint32_t* cd = h.data() + (size_t)ch * ctr_stride + 4 * d;
+                const uint32_t* cd = h.data() + (size_t)ch * ctr_stride + cps * d;
+                for (int j = 0; j < L; ++j) out.shadow_traced += cd[4 + j];
                 if (d == 0) out.primary += cd[0]; else out.bounce += cd[0];
-                out.shadow += (uint64_t)cd[1] * (uint64_t)L;
+                out.shadow += (uint64_t)cd[3] * (uint64_t)L;
             }
         unsigned long long slow[2] = {0, 0}; CK(cudaMemcpy(slow, c.slow.p, sizeof(slow), cudaMemcpyDeviceToHost));
         out.slow_path = slow[0]; out.exact_tests = slow[1];

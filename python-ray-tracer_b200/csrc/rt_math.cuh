@@ -104,4 +104,31 @@ __device__ __forceinline__ uint32_t block_append(bool valid, uint32_t* counter) 
     return pos;
 }
 
+
+// block_append for up to 8 queues at once (bit j of `flags` = this item goes on queue j; counters[j] = its length):
+// one pair of barriers for all of them.  pos[j] is valid where bit j is set.
+__device__ __forceinline__ void block_append8(uint32_t flags, int nq, uint32_t* counters, uint32_t (&pos)[8]) {
+    __shared__ uint32_t s_cnt8[8][8];      // [queue][warp]
+    __shared__ uint32_t s_base8[8];
+    const uint32_t wid = threadIdx.x >> 5, lt = (1u << lane_id()) - 1u;
+    uint32_t mask[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        mask[j] = (j < nq) ? __ballot_sync(0xffffffffu, (flags >> j) & 1u) : 0u;
+        if (j < nq && lane_id() == 0) s_cnt8[j][wid] = (uint32_t)__popc(mask[j]);
+    }
+    __syncthreads();
+    if ((int)threadIdx.x < nq) {
+        const int j = threadIdx.x;
+        uint32_t total = 0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) { const uint32_t t = s_cnt8[j][w]; s_cnt8[j][w] = total; total += t; }
+        s_base8[j] = total ? atomicAdd(counters + j, total) : 0u;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < 8; ++j) pos[j] = (j < nq) ? s_base8[j] + s_cnt8[j][wid] + (uint32_t)__popc(mask[j] & lt) : 0u;
+    __syncthreads();
+}
+
 }  // namespace b200rt
