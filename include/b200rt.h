@@ -117,9 +117,23 @@ B200RT_API int b200rt_render(const b200rt_args* args);
  * to_device / launch / copy_to_host sequence of reference src/main.py:19-51 in one call. */
 B200RT_API int b200rt_render_host(const b200rt_args* args);
 
+/* Camera-pose batch with HOST buffers (the caller of the path for animations; BASELINE config 5): `args` as for
+ * b200rt_render_host (its cam_origin/cam_rot are ignored; result must be non-NULL, e.g. = results), cam_origins float64 (n,3), cam_rots float64 (n,9) row-major,
+ * results uint8 (n,3,W,H).  The scene is staged once; frame k's D2H copy overlaps frame k+1's render.  Synchronous. */
+B200RT_API int b200rt_render_batch_host(const b200rt_args* args, int n_frames, const double* cam_origins, const double* cam_rots,
+                                        uint8_t* results);
+
 /* Measured FP32 CUDA-core throughput of `device` (dependent-chain-free FFMA / FFMA2 loops), TFLOP/s, and the
  * SM clock (MHz) derived from clock64()/globaltimer during the probe.  Used as the roofline denominator. */
 B200RT_API int b200rt_fp32_probe(int device, double* ffma_tflops, double* ffma2_tflops, double* sm_mhz);
+
+/* Presentation step, reference src/viewer/image.py:7-19 (convert_array_to_image): planar uint8 (3,W,H) indexed
+ * [c][x][y]  ->  interleaved RGB8 image of H rows x W pixels, out[y][x][c] = in[c][x][y] (what `mirror(rotate(270))`
+ * yields for the square frames the reference renders; non-square frames come out whole instead of cropped).
+ * flags: B200RT_F_UNSWAP_GB writes R,G,B instead of the stored R,B,G.  Device pointers; asynchronous on `stream`. */
+B200RT_API int b200rt_to_image(int device, void* stream, const uint8_t* planar, uint8_t* rgb, int W, int H, uint32_t flags);
+/* Same with HOST buffers (stages, transposes on the device, copies back, synchronises). */
+B200RT_API int b200rt_to_image_host(int device, const uint8_t* planar, uint8_t* rgb, int W, int H, uint32_t flags);
 
 B200RT_API int b200rt_device_count(void);
 B200RT_API int b200rt_sm_count(int device);

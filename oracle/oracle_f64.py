@@ -179,3 +179,14 @@ def sample(O, D, spheres, lights, planes, amb, lamb, refl, refl_depth, numpy_wea
 
 def clip_color(c):
     return int(lib().oracle_clip_color(float(c)))
+
+
+def convert_array_to_image_array(x):
+    """numpy restatement of reference src/viewer/image.py:7-19 for SQUARE input: stack (3,W,H) -> (W,H,3), cast to
+    uint8, then mirror(rotate(270)) == transpose of the first two axes.  Returns the (H, W, 3) uint8 array the PIL image
+    holds.  (Pinned by tests/golden/viewer_square.npz, generated with the reference's own function.)"""
+    import numpy as np
+    y = np.zeros((x.shape[1], x.shape[2], 3))
+    for i in range(3):
+        y[:, :, i] = x[i, :, :]
+    return np.ascontiguousarray(y.astype(np.uint8).transpose(1, 0, 2))

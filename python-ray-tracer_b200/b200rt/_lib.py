@@ -57,8 +57,11 @@ def lib():
         L.b200rt_args_size.restype = C.c_uint32
         L.b200rt_render.argtypes = [C.POINTER(Args)]; L.b200rt_render.restype = C.c_int
         L.b200rt_render_host.argtypes = [C.POINTER(Args)]; L.b200rt_render_host.restype = C.c_int
+        L.b200rt_render_batch_host.argtypes = [C.POINTER(Args), C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]; L.b200rt_render_batch_host.restype = C.c_int
         L.b200rt_fp32_probe.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.b200rt_fp32_probe.restype = C.c_int
+        L.b200rt_to_image.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint32]; L.b200rt_to_image.restype = C.c_int
+        L.b200rt_to_image_host.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint32]; L.b200rt_to_image_host.restype = C.c_int
         L.b200rt_device_count.restype = C.c_int
         L.b200rt_sm_count.argtypes = [C.c_int]; L.b200rt_sm_count.restype = C.c_int
         L.b200rt_shutdown.restype = C.c_int

@@ -109,18 +109,48 @@ def render_frame(scene, camera, amb=0.0, lamb=0.6, refl=0.3, refl_depth=2, alias
     return out
 
 
-def render_batch(scene, cameras, amb=0.0, lamb=0.6, refl=0.3, refl_depth=2, aliasing=True, devices=(0,), **kw):
-    """Camera-pose batch: frame k renders on devices[k % len(devices)] (frame sharding)."""
+def render_batch(scene, cameras, amb=0.0, lamb=0.6, refl=0.3, refl_depth=2, aliasing=True, devices=(0,), out=None, flags=0):
+    """Camera-pose batch: frame k renders on devices[k % N] (sharding.frames_of_rank); per device ONE
+    call into b200rt_render_batch_host (scene staged once, D2H of frame k overlapped with the render of frame k+1).
+    All cameras must share the resolution.  Returns uint8 (n, 3, W, H)."""
     from concurrent.futures import ThreadPoolExecutor
-    devices = list(devices)                          # frame k -> devices[k % N]  (sharding.frames_of_rank)
+    from .sharding import frames_of_rank
+    devices = list(devices)
+    n = len(cameras)
+    W, H = cameras[0].resolution
+    if any(tuple(c.resolution) != (W, H) for c in cameras):
+        raise ValueError("all cameras of a batch must have the same resolution")
+    sp, li, pn = [np.ascontiguousarray(a, dtype=np.float32) for a in scene.generate_scene()]
+    if out is None:
+        out = np.zeros((n, 3, W, H), dtype=np.uint8)
+    if out.shape != (n, 3, W, H) or out.dtype != np.uint8 or not out.flags.c_contiguous:
+        raise ValueError("out must be a C-contiguous uint8 array of shape (n, 3, W, H)")
+    L = _lib.lib()
 
-    def one(k):
-        return render_frame(scene, cameras[k], amb, lamb, refl, refl_depth, aliasing, device=devices[k % len(devices)], **kw)
+    def one(i):
+        ks = frames_of_rank(n, i, len(devices))
+        if not ks:
+            return
+        a = _lib.Args()
+        a.pixel_loc = None
+        a.grid = _lib.Grid(*[float(v) for v in cameras[0].grid()])
+        _fill_common(a, W, H, cameras[0].position, cameras[0].rotation, sp, li, pn, amb, lamb, refl, refl_depth, aliasing,
+                     devices[i], flags, None)
+        org = np.ascontiguousarray([np.asarray(cameras[k].position, dtype=np.float64).ravel() for k in ks])
+        rot = np.ascontiguousarray([np.asarray(cameras[k].rotation, dtype=np.float64).ravel() for k in ks])
+        contiguous = len(devices) == 1
+        res = out if contiguous else np.zeros((len(ks), 3, W, H), dtype=np.uint8)
+        a.result = res.ctypes.data                      # (validated as non-NULL; the batch writes through `results`)
+        _lib.check(L.b200rt_render_batch_host(C.byref(a), len(ks), org.ctypes.data, rot.ctypes.data, res.ctypes.data))
+        if not contiguous:
+            out[ks] = res
 
     if len(devices) == 1:
-        return [one(k) for k in range(len(cameras))]
-    with ThreadPoolExecutor(len(devices)) as ex:       # ctypes releases the GIL; one in-flight frame per device
-        return list(ex.map(one, range(len(cameras))))
+        one(0)
+    else:
+        with ThreadPoolExecutor(len(devices)) as ex:           # ctypes releases the GIL; one batch in flight per device
+            list(ex.map(one, range(len(devices))))
+    return out
 
 
 def fp32_probe(device=0):

@@ -80,6 +80,14 @@ class Scene:
     def generate_scene(self):
         return self.get_spheres(), self.get_lights(), self.get_planes()
 
+    @classmethod
+    def from_arrays(cls, sphere_centers=None, sphere_radii=None, sphere_colors=None, light_positions=None,
+                    plane_points=None, plane_normals=None, plane_colors=None) -> "PackedScene":
+        """Vectorised packing: (N,3) / (N,) arrays in, the same float32 (7,S)/(3,L)/(9,P) bytes out as
+        building N dataclass objects and calling get_spheres()/get_lights()/get_planes() (scene.py:69-94), without the
+        per-object Python loop."""
+        return PackedScene(sphere_centers, sphere_radii, sphere_colors, light_positions, plane_points, plane_normals, plane_colors)
+
     @staticmethod
     def default_scene() -> "Scene":
         """The demo scene of reference scene.py:99-115: 3 lights, 6 spheres, 1 grey floor plane."""
@@ -89,3 +97,40 @@ class Scene:
                    Sphere([-1.7, -0.5, 0.3], 0.3, GREEN), Sphere([-2.0, 1.31, 1.3], 1.3, RED)]
         planes = [Plane([5, 0, 0], [0, 0, 1], GREY)]
         return Scene(lights, spheres, planes)
+
+
+class PackedScene:
+    """A scene held as packed arrays: quacks like Scene for the render path (generate_scene / get_*)."""
+
+    def __init__(self, sphere_centers=None, sphere_radii=None, sphere_colors=None, light_positions=None,
+                 plane_points=None, plane_normals=None, plane_colors=None):
+        def mat(a, cols):
+            a = np.zeros((0, cols)) if a is None else np.asarray(a, dtype=np.float64)
+            return a.reshape(-1, cols)
+        c, col = mat(sphere_centers, 3), mat(sphere_colors, 3)
+        r = np.zeros(0) if sphere_radii is None else np.asarray(sphere_radii, dtype=np.float64).ravel()
+        if not (len(c) == len(r) == len(col)):
+            raise ValueError("sphere_centers, sphere_radii and sphere_colors must have the same length")
+        self._spheres = np.zeros((7, len(c)), dtype=np.float32)
+        self._spheres[0:3] = c.T; self._spheres[3] = r; self._spheres[4:7] = col.T
+        li = mat(light_positions, 3)
+        self._lights = np.ascontiguousarray(li.T, dtype=np.float32)
+        po, pn, pc = mat(plane_points, 3), mat(plane_normals, 3), mat(plane_colors, 3)
+        if not (len(po) == len(pn) == len(pc)):
+            raise ValueError("plane_points, plane_normals and plane_colors must have the same length")
+        self._planes = np.zeros((9, len(po)), dtype=np.float32)
+        if len(po):
+            nrm = np.array([np.linalg.norm(v) for v in pn])        # same routine per vector as Plane.to_array (scene.py:50-51)
+            self._planes[0:3] = po.T; self._planes[3:6] = (pn / nrm[:, None]).T; self._planes[6:9] = pc.T
+
+    def get_spheres(self) -> np.ndarray:
+        return self._spheres.copy()
+
+    def get_planes(self) -> np.ndarray:
+        return self._planes.copy()
+
+    def get_lights(self) -> np.ndarray:
+        return self._lights.copy()
+
+    def generate_scene(self):
+        return self.get_spheres(), self.get_lights(), self.get_planes()

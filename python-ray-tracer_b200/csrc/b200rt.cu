@@ -403,9 +403,10 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
     extern __shared__ __align__(16) unsigned char s_raw[];
     IsectSmem& sm = *reinterpret_cast<IsectSmem*>(s_raw);
     const bool first = (c0 == 0), last = (c0 + cnt >= sc.Spad);
-    const uint32_t n_in = q.n_in[ANY ? j : 0];                // shadow: length of light j's list
+    const bool lists = ANY && q.shidx != nullptr;             // shadow: per-light lists (else every hit record, identity map)
     const uint32_t n_tot = ANY ? *q.n_tot : 0u;
-    const uint32_t* shl = ANY ? q.shidx + (size_t)j * q.shcap : nullptr;      // list entry -> hit record
+    const uint32_t n_in = ANY ? (lists ? q.n_in[j] : n_tot) : q.n_in[0];
+    const uint32_t* shl = lists ? q.shidx + (size_t)j * q.shcap : nullptr;    // list entry -> hit record
     const uint32_t ngroups = (n_in + GW - 1) / GW;
     const float cmax = pv.bounds[0], rmax = pv.bounds[1];
     const float kInf = __int_as_float(0x7f800000);
@@ -438,7 +439,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
             float th = kInf, no = 0.f;
             unsigned long long key0 = ANY ? 0ull : kNoHit;
             uint32_t hrec = 0;
-            if (ANY && active) hrec = shl[i];
+            if (ANY && active) hrec = shl ? shl[i] : i;
             if (active && !first) {                               // running state of the earlier sphere chunks
                 if (ANY) { if (q.occl[(size_t)j * n_tot + hrec]) { key0 = 1ull; active = false; } }
                 else     { key0 = ((unsigned long long)__float_as_uint(q.hit_t[i]) << 32) | (uint32_t)q.hit_id[i]; }
@@ -498,7 +499,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
                 const uint32_t rl = item & 255u; const int sid = c0 + (int)(item >> 8);
                 const uint32_t i = gbase + rl;
                 V3 O, D;                                       // the ray, re-read (bit-identical to the setup above)
-                if (MODE == 2) { const float4 hp = q.hP[shl[i]]; O = mk(hp.x, hp.y, hp.z); D = normalize3(sub3(Vp, O)); }
+                if (MODE == 2) { const float4 hp = q.hP[shl ? shl[i] : i]; O = mk(hp.x, hp.y, hp.z); D = normalize3(sub3(Vp, O)); }
                 else {
                     const float4 d = q.rayD[i]; D = mk(d.x, d.y, d.z);
                     if (MODE == 1) O = Vp; else { const float4 o = q.rayO[i]; O = mk(o.x, o.y, o.z); }
@@ -599,7 +600,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
             const unsigned long long key = skey[lane * NR + r];
             if (ANY) {
                 bool occluded = key != 0ull;
-                const uint32_t hrec = shl[i];
+                const uint32_t hrec = shl ? shl[i] : i;
                 if (last && !occluded && sc.Pl > 0) {
                     const float4 hp = q.hP[hrec]; const V3 O = mk(hp.x, hp.y, hp.z);
                     const V3 D = mk(dx[r], dy[r], dz[r]);
@@ -668,7 +669,8 @@ __global__ void k_setup(SceneDev sc, ShadeDev s) {
         // One multi-queue append per pass: queue 0 = the hit list (first pass), the others = lights' lists
         // (n_hit and n_sh[] are adjacent counters).
         uint32_t h = 0;
-        for (int j0 = 0, first = 1; first || j0 < sc.L; first = 0) {
+        if (!s.shidx) h = block_append(hit, s.n_hit);             // dense shadow layout (small scenes): hit list only
+        else for (int j0 = 0, first = 1; first || j0 < sc.L; first = 0) {
             const int nl = min(first ? 7 : 8, sc.L - j0), sh = first ? 1 : 0;
             uint32_t flags = (first && hit) ? 1u : 0u;
             if (hit) {
@@ -707,11 +709,12 @@ __global__ void k_shade(SceneDev sc, ShadeDev s) {
         const float4 col = (id < sc.S) ? __ldg(&sc.sphCol[id]) : __ldg(&sc.plCol[id - sc.S]);
         float r = __fmul_rn(s.amb, col.x), g = __fmul_rn(s.amb, col.y), b = __fmul_rn(s.amb, col.z);   // trace.py:77
         for (int j = 0; j < sc.L; ++j) {                                                               // trace.py:86
+            if (!s.shidx && s.occl[(size_t)j * n + h]) continue;                                       // :95-96 (dense layout)
             const float4 l = __ldg(&sc.lights[j]);
             const V3 Lv = normalize3(sub3(mk(l.x, l.y, l.z), Pb));                                     // :89
             const float k = __fmul_rn(s.lamb, dot3(Lv, N));                                            // :99
-            if (!(k > 0.f)) continue;                                                                  // :101 (no shadow query was made)
-            if (s.occl[(size_t)j * n + h]) continue;                                                   // :95-96
+            if (!(k > 0.f)) continue;                                                                  // :101 (lists: no shadow query was made)
+            if (s.shidx && s.occl[(size_t)j * n + h]) continue;                                        // :95-96
             r = fmaf(k, col.x, r); g = fmaf(k, col.y, g); b = fmaf(k, col.z, b);                       // :102
         }
         s.accR[slot] = fmaf(s.weight, r, s.accR[slot]);                                                // :131
@@ -815,6 +818,58 @@ __global__ void __launch_bounds__(256) k_probe_ffma2(float* out, int iters) {
     if (s == 12345.678f) out[0] = s;
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// Presentation step: the array transform of reference src/viewer/image.py:7-19.
+// convert_array_to_image stacks (3,W,H) -> (W,H,3), and `ImageOps.mirror(im.rotate(270))` is a transpose for
+// square input, i.e. out[y][x][c] = in[c][x][y]: planar, y-contiguous  ->  interleaved RGB8 rows, x-contiguous.
+// 64x64 tiles through shared memory: 4-byte loads along y, 4-byte stores along x.
+// ------------------------------------------------------------------------------------------------
+constexpr int kImgTile = 64;
+__global__ void __launch_bounds__(256) k_to_image(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int W, int H, int unswap, int vec) {
+    __shared__ uint8_t tile[3][kImgTile][kImgTile + 4];                 // [c][x][y]
+    const int x0 = blockIdx.x * kImgTile, y0 = blockIdx.y * kImgTile;
+    const size_t WH = (size_t)W * H;
+    const bool full = vec && (x0 + kImgTile <= W) && (y0 + kImgTile <= H);
+    if (full) {
+        for (int i = threadIdx.x; i < 3 * kImgTile * (kImgTile / 4); i += 256) {
+            const int c = i / (kImgTile * (kImgTile / 4)), rem = i - c * (kImgTile * (kImgTile / 4));
+            const int xx = rem / (kImgTile / 4), y4 = rem - xx * (kImgTile / 4);
+            const uint32_t v = *reinterpret_cast<const uint32_t*>(in + c * WH + (size_t)(x0 + xx) * H + y0 + 4 * y4);
+            *reinterpret_cast<uint32_t*>(&tile[c][xx][4 * y4]) = v;
+        }
+    } else {
+        for (int i = threadIdx.x; i < 3 * kImgTile * kImgTile; i += 256) {
+            const int c = i / (kImgTile * kImgTile), rem = i - c * (kImgTile * kImgTile);
+            const int xx = rem / kImgTile, yy = rem - xx * kImgTile;
+            if (x0 + xx < W && y0 + yy < H) tile[c][xx][yy] = in[c * WH + (size_t)(x0 + xx) * H + y0 + yy];
+        }
+    }
+    __syncthreads();
+    const int c1 = unswap ? 2 : 1, c2 = unswap ? 1 : 2;               // stored order is R,B,G (common.py:60-63); unswap -> R,G,B
+    if (full) {
+        constexpr int kWords = kImgTile * 3 / 4;                       // 48 words per output row of the tile
+        for (int i = threadIdx.x; i < kImgTile * kWords; i += 256) {
+            const int yy = i / kWords, wd = i - yy * kWords;
+            uint32_t v = 0;
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                const int byte = 4 * wd + b, xx = byte / 3, ch = byte - 3 * xx;
+                const int c = ch == 0 ? 0 : (ch == 1 ? c1 : c2);
+                v |= (uint32_t)tile[c][xx][yy] << (8 * b);
+            }
+            *reinterpret_cast<uint32_t*>(out + ((size_t)(y0 + yy) * W + x0) * 3 + 4 * wd) = v;
+        }
+    } else {
+        for (int i = threadIdx.x; i < kImgTile * kImgTile * 3; i += 256) {
+            const int yy = i / (kImgTile * 3), rem = i - yy * (kImgTile * 3);
+            const int xx = rem / 3, ch = rem - 3 * xx;
+            const int c = ch == 0 ? 0 : (ch == 1 ? c1 : c2);
+            if (x0 + xx < W && y0 + yy < H) out[((size_t)(y0 + yy) * W + x0 + xx) * 3 + ch] = tile[c][xx][yy];
+        }
+    }
+}
+
 }  // namespace b200rt
 
 // ================================================================================================
@@ -858,13 +913,16 @@ struct DevCtx {
     Buf pivTab, pivPos;                                            // pivot tables (k_pivot)
     Buf stage;                                                     // host-scene / host-pixel_loc staging
     Buf rayO, rayD, hitT, hitId, hP, hN, hD, acc, occl, shidx, ctr, work, slow; // wavefront state
-    Buf hostResult, hostPixelLoc;                                  // b200rt_render_host device copies
+    Buf batchScene;                                                // b200rt_render_batch_host: the scene, staged once
+    cudaStream_t copyStream = nullptr; cudaEvent_t evRender[2] = {nullptr, nullptr}, evCopy[2] = {nullptr, nullptr};
+    Buf hostResult, hostPixelLoc, imgOut;                          // b200rt_render_host / b200rt_to_image_host device copies
     cudaEvent_t done = nullptr; bool has_done = false;
     void release_all() {
         Buf* all[] = { &sphA, &sphB, &sphCol, &plO, &plN, &plNu, &plCol, &lights, &cmax, &pivTab, &pivPos, &stage, &rayO, &rayD, &hitT, &hitId,
-                       &hP, &hN, &hD, &acc, &occl, &shidx, &ctr, &work, &slow, &hostResult, &hostPixelLoc };
+                       &hP, &hN, &hD, &acc, &occl, &shidx, &ctr, &work, &slow, &hostResult, &hostPixelLoc, &imgOut, &batchScene };
         for (Buf* b : all) b->release();
         if (done) { cudaEventDestroy(done); done = nullptr; } has_done = false; init = false;
+        if (copyStream) { cudaStreamDestroy(copyStream); copyStream = nullptr; for (int i = 0; i < 2; ++i) { cudaEventDestroy(evRender[i]); cudaEventDestroy(evCopy[i]); } }
     }
 };
 
@@ -1047,7 +1105,10 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     CK(c.hitT.ensure(sizeof(float) * cap)); CK(c.hitId.ensure(sizeof(int) * cap));
     CK(c.hP.ensure(sizeof(float4) * cap)); CK(c.hN.ensure(sizeof(float4) * cap)); CK(c.hD.ensure(sizeof(float4) * cap));
     CK(c.acc.ensure(sizeof(float) * 3 * cap)); CK(c.occl.ensure(std::max<size_t>(cap * (size_t)L, 1)));
-    CK(c.shidx.ensure(sizeof(uint32_t) * std::max<size_t>(cap * (size_t)L, 1)));
+    // Per-light shadow lists pay off when a query is expensive (many spheres); for tiny scenes the dense [light][hit]
+    // layout is cheaper than building the lists.
+    const bool use_lists = S >= 32 && !(a->flags & B200RT_F_NO_FILTER);
+    if (use_lists) CK(c.shidx.ensure(sizeof(uint32_t) * std::max<size_t>(cap * (size_t)L, 1)));
     const int cps = 4 + L;                                       // counters per depth: n_live, n_hit, 2 debug work counters, n_sh[L]
     const int ctr_stride = cps * (depth + 2);
     CK(c.ctr.ensure(sizeof(uint32_t) * (size_t)ctr_stride * nchunks)); CK(c.slow.ensure(2 * sizeof(unsigned long long)));
@@ -1105,8 +1166,8 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             s.hP = c.hP.as<float4>(); s.hN = c.hN.as<float4>(); s.hD = c.hD.as<float4>(); s.occl = c.occl.as<uint8_t>();
             s.accR = accR; s.accG = accG; s.accB = accB;
             s.n_live = cd + 0; s.n_hit = cd + 3; s.n_next = cd + cps;
-            s.shidx = c.shidx.as<uint32_t>(); s.shcap = cap; s.n_sh = cd + 4;
-            q.shidx = c.shidx.as<uint32_t>(); q.shcap = cap; q.n_tot = cd + 3;
+            s.shidx = use_lists ? c.shidx.as<uint32_t>() : nullptr; s.shcap = cap; s.n_sh = cd + 4;
+            q.shidx = s.shidx; q.shcap = cap; q.n_tot = cd + 3;
             s.amb = (float)a->amb; s.lamb = (float)a->lamb; s.weight = wts[d]; s.emit_reflection = d < depth;
 
             tm.begin(0);
@@ -1154,7 +1215,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         for (int ch = 0; ch < nchunks; ++ch)
             for (int d = 0; d <= depth; ++d) {
                 const uint32_t* cd = h.data() + (size_t)ch * ctr_stride + cps * d;
-                for (int j = 0; j < L; ++j) out.shadow_traced += cd[4 + j];
+                if (use_lists) { for (int j = 0; j < L; ++j) out.shadow_traced += cd[4 + j]; } else out.shadow_traced += (uint64_t)cd[3] * (uint64_t)L;
                 if (d == 0) out.primary += cd[0]; else out.bounce += cd[0];
                 out.shadow += (uint64_t)cd[3] * (uint64_t)L;
             }
@@ -1229,6 +1290,58 @@ B200RT_API int b200rt_render_host(const b200rt_args* a) {
     return 0;
 }
 
+// Camera-pose batch (BASELINE config 5): the scene is staged once, frame k renders into one of two
+// device framebuffers while frame k-1's D2H copy runs on a second stream.
+B200RT_API int b200rt_render_batch_host(const b200rt_args* a, int n_frames, const double* cam_origins, const double* cam_rots,
+                                        uint8_t* results) {
+    if (int rc = validate(a)) return rc;
+    if (n_frames < 0 || (n_frames > 0 && (!cam_origins || !cam_rots || !results))) return fail(B200RT_E_NULL, "batch arrays are NULL");
+    if (a->x_begin != 0 || a->x_end != a->W || a->strip_width != 0) return fail(B200RT_E_SHAPE, "batch rendering takes whole frames");
+    DeviceGuard guard(a->device);
+    DevCtx& c = g_ctx[a->device];
+    std::lock_guard<std::mutex> lock(c.mu);
+    if (int rc = init_ctx(c, a->device)) return rc;
+    cudaStream_t st = (cudaStream_t)a->stream;
+    const size_t WH = (size_t)a->W * a->H, fb = 3 * WH;
+    if (!c.copyStream) {
+        CK(cudaStreamCreateWithFlags(&c.copyStream, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; ++i) { CK(cudaEventCreateWithFlags(&c.evRender[i], cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&c.evCopy[i], cudaEventDisableTiming)); }
+    }
+    CK(c.hostResult.ensure(2 * fb));
+    b200rt_args d = *a;
+    d.stats = nullptr;
+    // scene: stage once, then treat as device-resident
+    const size_t nS = (size_t)7 * a->S, nL = (size_t)3 * a->L, nP = (size_t)9 * a->Pl;
+    CK(c.batchScene.ensure(sizeof(float) * std::max<size_t>(nS + nL + nP, 1)));
+    float* sg = c.batchScene.as<float>();
+    if (c.has_done) CK(cudaStreamWaitEvent(st, c.done, 0));
+    if (nS) CK(cudaMemcpyAsync(sg, a->spheres, sizeof(float) * nS, cudaMemcpyHostToDevice, st));
+    if (nL) CK(cudaMemcpyAsync(sg + nS, a->lights, sizeof(float) * nL, cudaMemcpyHostToDevice, st));
+    if (nP) CK(cudaMemcpyAsync(sg + nS + nL, a->planes, sizeof(float) * nP, cudaMemcpyHostToDevice, st));
+    d.spheres = sg; d.lights = sg + nS; d.planes = sg + nS + nL;
+    d.flags &= ~B200RT_F_SCENE_ON_HOST;
+    if (a->pixel_loc) {
+        CK(c.hostPixelLoc.ensure(sizeof(double) * 3 * WH));
+        CK(cudaMemcpyAsync(c.hostPixelLoc.p, a->pixel_loc, sizeof(double) * 3 * WH, cudaMemcpyHostToDevice, st));
+        d.pixel_loc = c.hostPixelLoc.as<double>();
+    }
+    for (int k = 0; k < n_frames; ++k) {
+        const int b = k & 1;
+        for (int i = 0; i < 3; ++i) d.cam_origin[i] = cam_origins[3 * k + i];
+        for (int i = 0; i < 9; ++i) d.cam_rot[i] = cam_rots[9 * k + i];
+        d.result = c.hostResult.as<uint8_t>() + (size_t)b * fb;
+        if (k >= 2) CK(cudaStreamWaitEvent(st, c.evCopy[b], 0));                 // frame k-2 has left this framebuffer
+        if (int rc = render_device(c, &d, st)) return rc;
+        CK(cudaEventRecord(c.evRender[b], st));
+        CK(cudaStreamWaitEvent(c.copyStream, c.evRender[b], 0));
+        CK(cudaMemcpyAsync(results + (size_t)k * fb, d.result, fb, cudaMemcpyDeviceToHost, c.copyStream));
+        CK(cudaEventRecord(c.evCopy[b], c.copyStream));
+    }
+    CK(cudaStreamSynchronize(st));
+    CK(cudaStreamSynchronize(c.copyStream));
+    return 0;
+}
+
 B200RT_API int b200rt_fp32_probe(int device, double* ffma_tflops, double* ffma2_tflops, double* sm_mhz) {
     int ndev = b200rt_device_count();
     if (device < 0 || device >= ndev) return fail(B200RT_E_DEVICE, "no such CUDA device");
@@ -1256,6 +1369,38 @@ B200RT_API int b200rt_fp32_probe(int device, double* ffma_tflops, double* ffma2_
     if (ffma_tflops) *ffma_tflops = best1;
     if (ffma2_tflops) *ffma2_tflops = best2;
     if (sm_mhz) *sm_mhz = mhz;
+    return 0;
+}
+
+B200RT_API int b200rt_to_image(int device, void* stream, const uint8_t* planar, uint8_t* rgb, int W, int H, uint32_t flags) {
+    if (!planar || !rgb) return fail(B200RT_E_NULL, "planar / rgb pointer is NULL");
+    if (W <= 0 || H <= 0) return fail(B200RT_E_SHAPE, "W and H must be positive");
+    int ndev = b200rt_device_count();
+    if (device < 0 || device >= ndev) return fail(B200RT_E_DEVICE, "no such CUDA device");
+    DeviceGuard guard(device);
+    const int vec = (W % 4 == 0) && (H % 4 == 0) && ((uintptr_t)planar % 4 == 0) && ((uintptr_t)rgb % 4 == 0);
+    dim3 grid((W + kImgTile - 1) / kImgTile, (H + kImgTile - 1) / kImgTile);
+    k_to_image<<<grid, 256, 0, (cudaStream_t)stream>>>(planar, rgb, W, H, (flags & B200RT_F_UNSWAP_GB) ? 1 : 0, vec);
+    CK(cudaGetLastError());
+    return 0;
+}
+
+B200RT_API int b200rt_to_image_host(int device, const uint8_t* planar, uint8_t* rgb, int W, int H, uint32_t flags) {
+    if (!planar || !rgb) return fail(B200RT_E_NULL, "planar / rgb pointer is NULL");
+    if (W <= 0 || H <= 0) return fail(B200RT_E_SHAPE, "W and H must be positive");
+    int ndev = b200rt_device_count();
+    if (device < 0 || device >= ndev || device >= kMaxDevices) return fail(B200RT_E_DEVICE, "no such CUDA device");
+    DeviceGuard guard(device);
+    DevCtx& c = g_ctx[device];
+    std::lock_guard<std::mutex> lock(c.mu);
+    if (int rc = init_ctx(c, device)) return rc;
+    const size_t n = (size_t)3 * W * H;
+    CK(c.hostResult.ensure(n)); CK(c.imgOut.ensure(n));
+    if (c.has_done) CK(cudaStreamWaitEvent(nullptr, c.done, 0));
+    CK(cudaMemcpyAsync(c.hostResult.p, planar, n, cudaMemcpyHostToDevice, nullptr));
+    if (int rc = b200rt_to_image(device, nullptr, c.hostResult.as<uint8_t>(), c.imgOut.as<uint8_t>(), W, H, flags)) return rc;
+    CK(cudaMemcpyAsync(rgb, c.imgOut.p, n, cudaMemcpyDeviceToHost, nullptr));
+    CK(cudaStreamSynchronize(nullptr));
     return 0;
 }
 

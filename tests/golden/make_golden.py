@@ -242,3 +242,17 @@ def main():
 
 if __name__ == "__main__":
     main()
+
+
+def viewer_golden():
+    """tests/golden/viewer_square.npz: the reference's convert_array_to_image (src/viewer/image.py:7-19) on random
+    square uint8 arrays.  Run with:  python -c "import make_golden as m; m.viewer_golden()"  (needs /root/reference)."""
+    sys.path.insert(0, "/root/reference/src")
+    from viewer import convert_array_to_image
+    rng = np.random.default_rng(7)
+    out = {}
+    for n in (96, 130):
+        x = rng.integers(0, 256, (3, n, n), dtype=np.uint8)
+        out[f"x_{n}"] = x
+        out[f"img_{n}"] = np.asarray(convert_array_to_image(x))
+    np.savez_compressed(os.path.join(os.path.dirname(os.path.abspath(__file__)), "viewer_square.npz"), **out)

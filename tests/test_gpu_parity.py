@@ -196,3 +196,18 @@ def test_small_queue_variants_bit_identical():
     from b200rt import render_host
     render_host(None, *_args(g), grid=g["grid"], shape=(W, int(g["H"])), tile=(0, 3), out=out)     # tiny queue -> NR=2
     assert np.array_equal(out[:, :3], whole[:, :3])
+
+
+def test_batch_equals_single_frames():
+    """b200rt_render_batch_host (scene staged once, double-buffered D2H) == frame-by-frame renders."""
+    from b200rt import render_batch, render_frame
+    from b200rt.scene import Scene
+    from b200rt.workloads import c5_camera
+    scene = Scene.default_scene()
+    cams = [c5_camera(k, res=(192, 108)) for k in (0, 7, 23, 40, 63)]
+    got = render_batch(scene, cams, 0.0, 0.6, 0.3, 2, False)
+    assert got.shape == (5, 3, 192, 108)
+    for k, cam in enumerate(cams):
+        assert np.array_equal(got[k], render_frame(scene, cam, 0.0, 0.6, 0.3, 2, False)), k
+    two = render_batch(scene, cams, 0.0, 0.6, 0.3, 2, False, devices=[0, 0])      # two host threads, one device
+    assert np.array_equal(two, got)

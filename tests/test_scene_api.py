@@ -88,3 +88,21 @@ def test_against_reference_package_in_place():
     sb = Scene([Light([1, 2, 3])], [Sphere([0.1, 0.2, 0.3], 0.7, [1, 2, 3])], [Plane([0, 0, 1], [1, 2, 3], [9, 8, 7])])
     for x, y in zip(sa.generate_scene(), sb.generate_scene()):
         assert np.array_equal(x, y) and x.dtype == y.dtype
+
+
+def test_from_arrays_packs_the_same_bytes_as_the_object_path():
+    """vectorised packing == per-object to_array() packing, byte for byte."""
+    from b200rt.scene import Scene, Sphere, Light, Plane
+    rng = np.random.default_rng(11)
+    n = 500
+    c = rng.uniform(-20, 20, (n, 3)); r = rng.uniform(0.05, 2, n); col = rng.integers(0, 256, (n, 3))
+    li = rng.uniform(-5, 5, (4, 3))
+    po = rng.uniform(-5, 5, (3, 3)); pn = rng.normal(size=(3, 3)); pc = rng.integers(0, 256, (3, 3))
+    a = Scene([Light(list(v)) for v in li], [Sphere(list(c[i]), r[i], list(col[i])) for i in range(n)],
+              [Plane(list(po[i]), list(pn[i]), list(pc[i])) for i in range(3)])
+    b = Scene.from_arrays(c, r, col, li, po, pn, pc)
+    for x, y in zip(a.generate_scene(), b.generate_scene()):
+        assert x.dtype == y.dtype == np.float32 and x.shape == y.shape
+        assert x.tobytes() == y.tobytes()
+    e = Scene.from_arrays()
+    assert [v.shape for v in e.generate_scene()] == [(7, 0), (3, 0), (9, 0)]
