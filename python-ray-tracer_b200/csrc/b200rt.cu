@@ -114,13 +114,16 @@ __device__ __forceinline__ double pl_at(const FrameDev& f, int c, int x, int y) 
     return __dadd_rn(__dmul_rn((double)yy, f.gsz), 1.0);
 }
 
+constexpr unsigned long long kNoHitKey = ((unsigned long long)0x4479c000u << 32) | 0xffffffffu;   // (t = 999.0f, id = -1)
+
 // AA neighbour order of kernels.py:32-53: left, right, top(y+1), bot(y-1), topleft, topright, bottomleft, bottomright
 __constant__ int c_dx[9] = { 0, -1, +1, 0, 0, -1, +1, -1, +1 };
 __constant__ int c_dy[9] = { 0, 0, 0, +1, -1, +1, +1, -1, -1 };
 
 // One thread per (sample k, pixel p) slot.  Primary ray in FP64 (kernels.py:19-23 / :43-55), rounded to FP32,
 // appended to the ray queue.  Slots that the reference never samples (AA border: x == 0 or y == 0) are skipped.
-__global__ void k_raygen(FrameDev f, float4* __restrict__ rayO, float4* __restrict__ rayD, uint32_t* n_live) {
+__global__ void k_raygen(FrameDev f, float4* __restrict__ rayO, float4* __restrict__ rayD, unsigned long long* __restrict__ hit,
+                         uint32_t* n_live) {
     const uint32_t nslots = f.npix * (uint32_t)f.ns;
     for (uint32_t base = blockIdx.x * blockDim.x; base < nslots; base += gridDim.x * blockDim.x) {
         uint32_t slot = base + threadIdx.x;
@@ -148,7 +151,7 @@ __global__ void k_raygen(FrameDev f, float4* __restrict__ rayO, float4* __restri
             }
         }
         uint32_t pos = block_append(valid, n_live);
-        if (valid) { rayO[pos] = o; rayD[pos] = d; }
+        if (valid) { rayO[pos] = o; rayD[pos] = d; hit[pos] = kNoHitKey; }
     }
 }
 
@@ -167,8 +170,8 @@ struct QueueDev {
     const float4* hP;                    // (biased hit point, slot)
     const uint32_t* n_in;                // number of rays (closest) or number of hit records (shadow)
     uint32_t* work;                      // dynamic group counter (zeroed before the launch)
-    float* hit_t; int* hit_id;           // closest-hit output, queue order
-    uint8_t* occl;                       // shadow output, [light][hit]
+    unsigned long long* hit;             // closest-hit output, queue order: (float bits of t) << 32 | id; pre-set to kNoHit
+    uint8_t* occl; size_t ocap;          // shadow output, [light][hit] with row stride ocap; pre-set to 0 (k_isect3 stores only 1s)
     const uint32_t* shidx; size_t shcap; // k_isect3 shadow input: per light the hit records whose Lambert term can be non-zero
     const uint32_t* n_tot;               // k_isect3 shadow: number of hit records (row length of occl)
     unsigned long long* slow;            // diagnostic: thread-level slow-path entries (may be null)
@@ -294,13 +297,13 @@ k_intersect(SceneDev sc, QueueDev q) {
                     const float t = plane_exact(O, D, __ldg(&sc.plO[p]), __ldg(&sc.plN[p]));
                     occluded = (t > 0.f && t < kTMax);
                 }
-                q.occl[i] = occluded ? 1 : 0;
+                q.occl[(size_t)(i / n_in) * q.ocap + (i % n_in)] = occluded ? 1 : 0;
             } else {
                 for (int p = 0; p < sc.Pl; ++p) {
                     const float t = plane_exact(O, D, __ldg(&sc.plO[p]), __ldg(&sc.plN[p]));
                     if (t > 0.f && t < best[r]) { best[r] = t; bid[r] = sc.S + p; }
                 }
-                q.hit_t[i] = best[r]; q.hit_id[i] = bid[r];
+                q.hit[i] = ((unsigned long long)__float_as_uint(best[r]) << 32) | (uint32_t)bid[r];
             }
         }
     }
@@ -387,11 +390,12 @@ __device__ __forceinline__ float fmax3(float a, float b, float c) {
 constexpr int KP = 4;                    // sphere pairs per scan step (8 spheres)
 constexpr int kQCap = 1024;              // candidate queue entries per warp
 constexpr int kQFlush = kQCap - 32 * 16; // flush before an append (<= 16 per lane) could overflow
-constexpr unsigned long long kNoHit = ((unsigned long long)0x4479c000u << 32) | 0xffffffffu;   // (999.0f, id -1)
+constexpr unsigned long long kNoHit = kNoHitKey;                                                 // (999.0f, id -1)
 
 struct IsectSmem {
     uint32_t q[kThreads / 32][kQCap];
-    unsigned long long key[kThreads / 32][32 * 8];     // per ray of the warp's group: packed closest hit / occlusion flag
+    uint32_t kt[kThreads / 32][32 * 8];                // per ray of the warp's group: float bits of the closest t / occlusion flag
+    uint32_t ki[kThreads / 32][32 * 8];                // ... and the id of the closest object
 };
 
 template <int MODE, int NR>
@@ -408,12 +412,12 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
     const uint32_t n_in = ANY ? (lists ? q.n_in[j] : n_tot) : q.n_in[0];
     const uint32_t* shl = lists ? q.shidx + (size_t)j * q.shcap : nullptr;    // list entry -> hit record
     const uint32_t ngroups = (n_in + GW - 1) / GW;
+    const int npair = cnt >> 1;
     const float cmax = pv.bounds[0], rmax = pv.bounds[1];
     const float kInf = __int_as_float(0x7f800000);
     const uint32_t lane = lane_id(), wid = threadIdx.x >> 5;
-    const int npair = cnt >> 1;
     uint32_t* sq = sm.q[wid];
-    unsigned long long* skey = sm.key[wid];
+    uint32_t* skt = sm.kt[wid]; uint32_t* ski = sm.ki[wid];
     uint32_t slow_cnt = 0, exact_cnt = 0;
     // j: pivot of this launch (light index for ANY, camera = L for MODE 1); its table is c_tab[tb + 2*pair + {0,1}].
     // tb is a kernel parameter so that the table index provably lives in uniform registers (LDCU -> UR operands).
@@ -421,11 +425,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
     if (PIV) { const float4 v = __ldg(&pv.piv[j]); Vp = mk(v.x, v.y, v.z); }
     uint32_t* work = q.work + (ANY ? j : 0);
 
-    for (;;) {
-        uint32_t g = 0;
-        if (lane == 0) g = atomicAdd(work, 1u);
-        g = __shfl_sync(0xffffffffu, g, 0);
-        if (g >= ngroups) break;
+    auto run_group = [&](const uint32_t g) {
         // A thread owns NR CONSECUTIVE queue entries (neighbouring pixels): they pass the filter at the same spheres.
         const uint32_t gbase = g * (uint32_t)GW, i0 = gbase + lane * NR;
 
@@ -440,11 +440,10 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
             unsigned long long key0 = ANY ? 0ull : kNoHit;
             uint32_t hrec = 0;
             if (ANY && active) hrec = shl ? shl[i] : i;
-            if (active && !first) {                               // running state of the earlier sphere chunks
-                if (ANY) { if (q.occl[(size_t)j * n_tot + hrec]) { key0 = 1ull; active = false; } }
-                else     { key0 = ((unsigned long long)__float_as_uint(q.hit_t[i]) << 32) | (uint32_t)q.hit_id[i]; }
+            if (ANY && active && !first) {                        // occluded by a sphere of an earlier chunk: done
+                if (q.occl[(size_t)j * q.ocap + hrec]) { key0 = 1ull; active = false; }
             }
-            skey[lane * NR + r] = key0;
+            skt[lane * NR + r] = (uint32_t)(key0 >> 32) | (ANY ? (uint32_t)key0 : 0u); ski[lane * NR + r] = 0xffffffffu;
             if (active) {
                 if (MODE == 2) {
                     const float4 p = q.hP[hrec];
@@ -492,23 +491,35 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
         };
 
         // -- exact tests over the queue, one candidate per lane per iteration (dense) --
+        // The closest hit of a ray is the minimum over its candidates of (t, id) — smallest t, lowest id on a tie
+        // (trace.py:26).  Two native 32-bit shared atomics instead of a 64-bit atomicMin: the latter is a CAS loop, and
+        // with a divergent loop inside the scan ptxas no longer keeps the table operands in uniform registers.
         auto flush = [&]() {
             __syncwarp();
-            for (uint32_t idx = lane; idx < qcnt; idx += 32) {
-                const uint32_t item = sq[idx];
-                const uint32_t rl = item & 255u; const int sid = c0 + (int)(item >> 8);
-                const uint32_t i = gbase + rl;
-                V3 O, D;                                       // the ray, re-read (bit-identical to the setup above)
-                if (MODE == 2) { const float4 hp = q.hP[shl ? shl[i] : i]; O = mk(hp.x, hp.y, hp.z); D = normalize3(sub3(Vp, O)); }
-                else {
-                    const float4 d = q.rayD[i]; D = mk(d.x, d.y, d.z);
-                    if (MODE == 1) O = Vp; else { const float4 o = q.rayO[i]; O = mk(o.x, o.y, o.z); }
+            for (uint32_t base = 0; base < qcnt; base += 32) {                // warp-uniform trip count
+                const uint32_t idx = base + lane;
+                bool hit = false; uint32_t rl = 0, tbits = 0; int sid = 0;
+                if (idx < qcnt) {
+                    const uint32_t item = sq[idx];
+                    rl = item & 255u; sid = c0 + (int)(item >> 8);
+                    const uint32_t i = gbase + rl;
+                    V3 O, D;                                   // the ray, re-read (bit-identical to the setup above)
+                    if (MODE == 2) { const float4 hp = q.hP[shl ? shl[i] : i]; O = mk(hp.x, hp.y, hp.z); D = normalize3(sub3(Vp, O)); }
+                    else {
+                        const float4 d = q.rayD[i]; D = mk(d.x, d.y, d.z);
+                        if (MODE == 1) O = Vp; else { const float4 o = q.rayO[i]; O = mk(o.x, o.y, o.z); }
+                    }
+                    const float4 sp = __ldg(&sc.sphB[sid]);
+                    const float t = sphere_exact(O, D, sp.x, sp.y, sp.z, sp.w);
+                    hit = t > 0.f && t < kTMax;                                               // trace.py:26-29
+                    tbits = __float_as_uint(t);
                 }
-                const float4 sp = __ldg(&sc.sphB[sid]);
-                const float t = sphere_exact(O, D, sp.x, sp.y, sp.z, sp.w);
-                if (t > 0.f && t < kTMax) {                                                   // trace.py:26-29
-                    if (ANY) skey[rl] = 1ull;
-                    else     atomicMin(&skey[rl], ((unsigned long long)__float_as_uint(t) << 32) | (uint32_t)sid);
+                if (ANY) { if (hit) skt[rl] = 1u; __syncwarp(); }
+                else {
+                    if (hit && tbits < atomicMin(&skt[rl], tbits)) ski[rl] = 0xffffffffu;     // new minimum t: forget the old id
+                    __syncwarp();
+                    if (hit && skt[rl] == tbits) atomicMin(&ski[rl], (uint32_t)sid);
+                    __syncwarp();
                 }
             }
             exact_cnt += (qcnt + 31 - lane) / 32;
@@ -597,9 +608,9 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
         for (int r = 0; r < NR; ++r) {
             const uint32_t i = i0 + r;
             if (i >= n_in) continue;
-            const unsigned long long key = skey[lane * NR + r];
+            const unsigned long long key = ((unsigned long long)skt[lane * NR + r] << 32) | ski[lane * NR + r];
             if (ANY) {
-                bool occluded = key != 0ull;
+                bool occluded = (key >> 32) != 0ull;
                 const uint32_t hrec = shl ? shl[i] : i;
                 if (last && !occluded && sc.Pl > 0) {
                     const float4 hp = q.hP[hrec]; const V3 O = mk(hp.x, hp.y, hp.z);
@@ -609,7 +620,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
                         occluded = (t > 0.f && t < kTMax);
                     }
                 }
-                q.occl[(size_t)j * n_tot + hrec] = occluded ? 1 : 0;
+                if (occluded) q.occl[(size_t)j * q.ocap + hrec] = 1;
             } else {
                 float best = __uint_as_float((uint32_t)(key >> 32)); int bid = (int)(uint32_t)key;
                 if (last) {
@@ -620,10 +631,18 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
                         if (t > 0.f && t < best) { best = t; bid = sc.S + pl; }
                     }
                 }
-                q.hit_t[i] = best; q.hit_id[i] = bid;
+                if (bid >= 0) atomicMin(&q.hit[i], ((unsigned long long)__float_as_uint(best) << 32) | (uint32_t)bid);
             }
         }
         __syncwarp();                                         // keys are re-initialised by the next group's setup
+    };
+
+    for (;;) {
+        uint32_t g = 0;
+        if (lane == 0) g = atomicAdd(work, 1u);
+        g = __shfl_sync(0xffffffffu, g, 0);
+        if (g >= ngroups) break;
+        run_group(g);
     }
     if (q.slow) {
         const uint32_t tot = __reduce_add_sync(0xffffffffu, slow_cnt), tot2 = __reduce_add_sync(0xffffffffu, exact_cnt);
@@ -636,9 +655,9 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
 // ------------------------------------------------------------------------------------------------
 struct ShadeDev {
     float4* rayO; float4* rayD;          // ray queue (read by k_setup, rewritten by k_shade)
-    const float* hit_t; const int* hit_id;
+    unsigned long long* hit;             // packed closest hit per ray (read by k_setup; k_shade pre-sets it for the next depth)
     float4* hP; float4* hN; float4* hD;  // hit records: (biased P, slot) (N, id) (incoming D, -)
-    const uint8_t* occl;                 // [light][hit]
+    uint8_t* occl; size_t ocap;          // [light][hit], row stride ocap (zeroed by k_setup, set by the shadow query)
     float* accR; float* accG; float* accB;   // per-slot colour accumulators
     const uint32_t* n_live;              // rays in the queue (k_setup input)
     uint32_t* n_hit;                     // hit records (k_setup output, k_shade input)
@@ -654,10 +673,10 @@ __global__ void k_setup(SceneDev sc, ShadeDev s) {
     for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {
         const uint32_t i = base + threadIdx.x;
         bool hit = false; float4 o, d; float t = 0.f; int id = -1;
-        if (i < n) { id = s.hit_id[i]; hit = id >= 0; }
+        if (i < n) { const unsigned long long key = s.hit[i]; id = (int)(uint32_t)key; t = __uint_as_float((uint32_t)(key >> 32)); hit = id >= 0; }
         V3 Pb = mk(0, 0, 0), N = mk(0, 0, 0);
         if (hit) {
-            o = s.rayO[i]; d = s.rayD[i]; t = s.hit_t[i];
+            o = s.rayO[i]; d = s.rayD[i];
             const V3 P = madd3(mk(o.x, o.y, o.z), t, mk(d.x, d.y, d.z));            // trace.py:60
             if (id < sc.S) { const float4 c = __ldg(&sc.sphB[id]); N = normalize3(sub3(P, mk(c.x, c.y, c.z))); }   // common.py:94-101
             else           { const float4 nu = __ldg(&sc.plNu[id - sc.S]); N = mk(nu.x, nu.y, nu.z); }             // common.py:104-110
@@ -692,6 +711,7 @@ __global__ void k_setup(SceneDev sc, ShadeDev s) {
             s.hP[h] = make_float4(Pb.x, Pb.y, Pb.z, o.w);
             s.hN[h] = make_float4(N.x, N.y, N.z, __int_as_float(id));
             s.hD[h] = make_float4(d.x, d.y, d.z, 0.f);
+            for (int j = 0; j < sc.L; ++j) s.occl[(size_t)j * s.ocap + h] = 0;
         }
     }
 }
@@ -709,12 +729,12 @@ __global__ void k_shade(SceneDev sc, ShadeDev s) {
         const float4 col = (id < sc.S) ? __ldg(&sc.sphCol[id]) : __ldg(&sc.plCol[id - sc.S]);
         float r = __fmul_rn(s.amb, col.x), g = __fmul_rn(s.amb, col.y), b = __fmul_rn(s.amb, col.z);   // trace.py:77
         for (int j = 0; j < sc.L; ++j) {                                                               // trace.py:86
-            if (!s.shidx && s.occl[(size_t)j * n + h]) continue;                                       // :95-96 (dense layout)
+            if (!s.shidx && s.occl[(size_t)j * s.ocap + h]) continue;                                       // :95-96 (dense layout)
             const float4 l = __ldg(&sc.lights[j]);
             const V3 Lv = normalize3(sub3(mk(l.x, l.y, l.z), Pb));                                     // :89
             const float k = __fmul_rn(s.lamb, dot3(Lv, N));                                            // :99
             if (!(k > 0.f)) continue;                                                                  // :101 (lists: no shadow query was made)
-            if (s.shidx && s.occl[(size_t)j * n + h]) continue;                                        // :95-96
+            if (s.shidx && s.occl[(size_t)j * s.ocap + h]) continue;                                       // :95-96
             r = fmaf(k, col.x, r); g = fmaf(k, col.y, g); b = fmaf(k, col.z, b);                       // :102
         }
         s.accR[slot] = fmaf(s.weight, r, s.accR[slot]);                                                // :131
@@ -726,6 +746,7 @@ __global__ void k_shade(SceneDev sc, ShadeDev s) {
             const V3 O2 = madd3(Pb, kBias, R);                                                         // trace.py:110
             s.rayO[h] = make_float4(O2.x, O2.y, O2.z, p.w);
             s.rayD[h] = make_float4(R.x, R.y, R.z, 0.f);
+            s.hit[h] = kNoHit;
         }
     }
 }
@@ -912,13 +933,13 @@ struct DevCtx {
     Buf sphA, sphB, sphCol, plO, plN, plNu, plCol, lights, cmax;   // packed scene
     Buf pivTab, pivPos;                                            // pivot tables (k_pivot)
     Buf stage;                                                     // host-scene / host-pixel_loc staging
-    Buf rayO, rayD, hitT, hitId, hP, hN, hD, acc, occl, shidx, ctr, work, slow; // wavefront state
+    Buf rayO, rayD, hitKey, hP, hN, hD, acc, occl, shidx, ctr, work, slow; // wavefront state
     Buf batchScene;                                                // b200rt_render_batch_host: the scene, staged once
     cudaStream_t copyStream = nullptr; cudaEvent_t evRender[2] = {nullptr, nullptr}, evCopy[2] = {nullptr, nullptr};
     Buf hostResult, hostPixelLoc, imgOut;                          // b200rt_render_host / b200rt_to_image_host device copies
     cudaEvent_t done = nullptr; bool has_done = false;
     void release_all() {
-        Buf* all[] = { &sphA, &sphB, &sphCol, &plO, &plN, &plNu, &plCol, &lights, &cmax, &pivTab, &pivPos, &stage, &rayO, &rayD, &hitT, &hitId,
+        Buf* all[] = { &sphA, &sphB, &sphCol, &plO, &plN, &plNu, &plCol, &lights, &cmax, &pivTab, &pivPos, &stage, &rayO, &rayD, &hitKey,
                        &hP, &hN, &hD, &acc, &occl, &shidx, &ctr, &work, &slow, &hostResult, &hostPixelLoc, &imgOut, &batchScene };
         for (Buf* b : all) b->release();
         if (done) { cudaEventDestroy(done); done = nullptr; } has_done = false; init = false;
@@ -1102,7 +1123,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     const int nchunks = (int)((ncols + cols_per_chunk - 1) / cols_per_chunk);
     const size_t cap = cols_per_chunk * per_col;                 // slots per chunk
     CK(c.rayO.ensure(sizeof(float4) * cap)); CK(c.rayD.ensure(sizeof(float4) * cap));
-    CK(c.hitT.ensure(sizeof(float) * cap)); CK(c.hitId.ensure(sizeof(int) * cap));
+    CK(c.hitKey.ensure(sizeof(unsigned long long) * cap));
     CK(c.hP.ensure(sizeof(float4) * cap)); CK(c.hN.ensure(sizeof(float4) * cap)); CK(c.hD.ensure(sizeof(float4) * cap));
     CK(c.acc.ensure(sizeof(float) * 3 * cap)); CK(c.occl.ensure(std::max<size_t>(cap * (size_t)L, 1)));
     // Per-light shadow lists pay off when a query is expensive (many spheres); for tiny scenes the dense [light][hit]
@@ -1150,7 +1171,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         CK(cudaMemsetAsync(accR, 0, sizeof(float) * nslots, st));
         CK(cudaMemsetAsync(accG, 0, sizeof(float) * nslots, st));
         CK(cudaMemsetAsync(accB, 0, sizeof(float) * nslots, st));
-        k_raygen<<<(int)std::min<size_t>((nslots + 255) / 256, (size_t)small_grid), 256, 0, st>>>(f, c.rayO.as<float4>(), c.rayD.as<float4>(), ctr + 0);
+        k_raygen<<<(int)std::min<size_t>((nslots + 255) / 256, (size_t)small_grid), 256, 0, st>>>(f, c.rayO.as<float4>(), c.rayD.as<float4>(), c.hitKey.as<unsigned long long>(), ctr + 0);
         CK(cudaGetLastError());
         tm.end(2);
 
@@ -1159,11 +1180,11 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             uint32_t* wk = c.work.as<uint32_t>() + ((size_t)ch * (depth + 1) + d) * work_per_depth;      // k_isect3 group counters
             QueueDev q{};
             q.rayO = c.rayO.as<float4>(); q.rayD = c.rayD.as<float4>(); q.hP = c.hP.as<float4>();
-            q.hit_t = c.hitT.as<float>(); q.hit_id = c.hitId.as<int>(); q.occl = c.occl.as<uint8_t>();
+            q.hit = c.hitKey.as<unsigned long long>(); q.occl = c.occl.as<uint8_t>(); q.ocap = cap;
             q.slow = stats ? c.slow.as<unsigned long long>() : nullptr;
             ShadeDev s{};
-            s.rayO = c.rayO.as<float4>(); s.rayD = c.rayD.as<float4>(); s.hit_t = c.hitT.as<float>(); s.hit_id = c.hitId.as<int>();
-            s.hP = c.hP.as<float4>(); s.hN = c.hN.as<float4>(); s.hD = c.hD.as<float4>(); s.occl = c.occl.as<uint8_t>();
+            s.rayO = c.rayO.as<float4>(); s.rayD = c.rayD.as<float4>(); s.hit = c.hitKey.as<unsigned long long>();
+            s.hP = c.hP.as<float4>(); s.hN = c.hN.as<float4>(); s.hD = c.hD.as<float4>(); s.occl = c.occl.as<uint8_t>(); s.ocap = cap;
             s.accR = accR; s.accG = accG; s.accB = accB;
             s.n_live = cd + 0; s.n_hit = cd + 3; s.n_next = cd + cps;
             s.shidx = use_lists ? c.shidx.as<uint32_t>() : nullptr; s.shcap = cap; s.n_sh = cd + 4;

@@ -1,0 +1,19 @@
+# A/B of prebuilt libraries under tools/ab/*.so on one workload: bash tools/gpu_ab.sh [workload] [steps]
+cd $GRAFT_REPO_ROOT
+mkdir -p gpurun_out
+WL=${1:-c4}; ST=${2:-5}
+cp python-ray-tracer_b200/b200rt/libb200rt.so /tmp/orig.so
+for f in tools/ab/*.so; do
+  n=$(basename $f .so)
+  cp $f python-ray-tracer_b200/b200rt/libb200rt.so; touch python-ray-tracer_b200/b200rt/libb200rt.so
+  timeout 300 python bench.py --workload $WL --steps $ST --warmup 3 --no-cpu > gpurun_out/ab_$n.json 2> gpurun_out/ab_$n.err
+  python - $n <<'PY'
+import json,sys
+n=sys.argv[1]
+try:
+    d=json.loads(open('gpurun_out/ab_%s.json'%n).read().strip().splitlines()[-1]); r=d['roofline']
+    print(n, 'ms', round(d['ms_per_step'],3), 'closest', round(r['kernel_ms_closest'],3), 'shadow', round(r['kernel_ms_shadow'],3), 'other', round(r['other_ms'],3), 'e2e', round(d['e2e']['ms_per_step'],3))
+except Exception as e: print(n, 'ERR', e, open('gpurun_out/ab_%s.err'%n).read()[-600:])
+PY
+done
+cp /tmp/orig.so python-ray-tracer_b200/b200rt/libb200rt.so
