@@ -12,6 +12,9 @@ NVCC_FLAGS = ["-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-O3",
               "-shared", "-Xcompiler", "-fPIC,-fvisibility=hidden"]
 
 
+SOURCES = ["b200rt.cu", "isect_shadow.cu"]       # two CUDA modules on purpose: two constant banks (csrc/isect3.cuh)
+
+
 def needs_build() -> bool:
     if not os.path.exists(LIB_PATH):
         return True
@@ -24,6 +27,6 @@ def needs_build() -> bool:
 def build(force: bool = False, verbose: bool = False) -> str:
     if force or needs_build():
         cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + \
-              ["-o", LIB_PATH, os.path.join(SRC_DIR, "b200rt.cu")]
+              ["--threads", "2", "-o", LIB_PATH] + [os.path.join(SRC_DIR, f) for f in SOURCES]
         subprocess.check_call(cmd)
     return LIB_PATH

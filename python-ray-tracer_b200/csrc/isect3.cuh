@@ -1,0 +1,435 @@
+// isect3.cuh — the production intersection kernel k_isect3 (brute-force closest-hit / any-hit queries of a ray queue
+// against all spheres and planes; reference trace.py:7-41, intersections.py:6-68) and its launcher.
+//
+// Included by TWO translation units on purpose: b200rt.cu instantiates the closest-hit modes (0, 1) and
+// isect_shadow.cu the shadow mode (2).  Without relocatable device code every .cu file is its own CUDA module with its
+// own 64 KB constant bank, so the closest-hit tables (camera pivot + origin-free) and the lights' tables are resident
+// at the same time: for scenes up to kTabCap/L spheres nothing is uploaded between launches, and closest-hit and
+// shadow launches of different depths are independent of each other (they run on two streams, see render_device).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <algorithm>
+#include "rt_math.cuh"
+
+namespace b200rt {
+
+// ------------------------------------------------------------------------------------------------
+// Device-side scene (packed once per launch by k_pack from the reference's SoA arrays)
+// ------------------------------------------------------------------------------------------------
+struct SceneDev {
+    const float4* sphA;    // [Spad] (Cx, Cy, Cz, r^2 - |C|^2)  filter operands; padding entries never pass
+    const float4* sphB;    // [S]    (Cx, Cy, Cz, r^2)          exact-test operands; r^2 = float32 r*r (intersections.py:21)
+    const float4* sphCol;  // [S]    (R, G, B, 0)
+    const float4* plO;     // [Pl]   plane point
+    const float4* plN;     // [Pl]   stored normal (used un-renormalised by the intersection, intersections.py:52)
+    const float4* plNu;    // [Pl]   float32 re-normalised normal (common.py:104-110)
+    const float4* plCol;   // [Pl]
+    const float4* lights;  // [L]
+    const float*  cmax;    // [2]    max |C|, max r over spheres (filter error bounds)
+    int S, Spad, Pl, L;
+};
+
+constexpr unsigned long long kNoHitKey = ((unsigned long long)0x4479c000u << 32) | 0xffffffffu;   // (t = 999.0f, id = -1)
+constexpr int kThreads = 256;            // threads per CTA
+
+struct QueueDev {
+    // closest-hit input: ray queue (O.xyz, slot) / (D.xyz, -)
+    const float4* rayO; const float4* rayD;
+    // shadow input: hit records
+    const float4* hP;                    // (biased hit point, slot)
+    const uint32_t* n_in;                // number of rays (closest) or number of hit records (shadow)
+    uint32_t* work;                      // dynamic group counter (zeroed before the launch)
+    unsigned long long* hit;             // closest-hit output, queue order: (float bits of t) << 32 | id; pre-set to kNoHit
+    uint8_t* occl; size_t ocap;          // shadow output, [light][hit] with row stride ocap; pre-set to 0 (k_isect3 stores only 1s)
+    const uint32_t* shidx; size_t shcap; // k_isect3 shadow input: per light the hit records whose Lambert term can be non-zero
+    const uint32_t* n_tot;               // k_isect3 shadow: number of hit records (row length of occl)
+    unsigned long long* slow;            // diagnostic: thread-level slow-path entries (may be null)
+};
+
+// ------------------------------------------------------------------------------------------------
+// The production intersection kernel (k_isect3)
+// ------------------------------------------------------------------------------------------------
+// What bounds this loop on B200 is not the FP32 pipe but the register file: measured (tools/ffma2_probe*.cu) an
+// SMSP sustains ~1.75 register-operand reads per lane-cycle, every FFMA2 that reads two register pairs costs 2.3
+// cycles, and a 3-input ALU op (FMNMX3) costs as much as an FFMA2 when its operands all come from registers.  So the
+// loop is organised to read as few vector registers as possible:
+//   * packed FFMA2 (fma.rn.f32x2): two IEEE FP32 FMAs per instruction.  The two lanes of every packed value are two
+//     SPHERES (2i, 2i+1) tested against the same ray;
+//   * the sphere operands are warp-uniform, so they never touch the vector register file: the table of the launch
+//     lives in constant memory and reaches the FMA pipe as UNIFORM-register pairs (LDCU.128 -> FFMA2 ..., URx.F32x2);
+//   * the ray operands are 32-bit registers in FFMA2's broadcast form (R.F32): 1 register read instead of a pair.
+// Per (ray, sphere pair) the 4-FFMA pivot form reads 2+3+3+2 registers + 3 for the max — the probe's V7 variant runs
+// this at 2.32 cycles/FFMA2 = 64 TFLOP/s executed, 86 % of the nominal FP32 peak, FMA-pipe bound.
+//
+// Filter algebra (unchanged from the scalar kernel, see k_intersect): disc >= 0 <=> q >= thr.
+//   MODE 0 (any ray, bounces):     q = b^2 + 2 C.O + (r^2 - |C|^2) - (|O|^2 - margin)          8 FFMA2 / 2 tests
+//   MODE 1/2 (pivot V on the line): q = b^2 + (r^2 - |C-V|^2),  b = C.D - V.D,  thr = -margin   4 FFMA2 / 2 tests
+// Pivot form: disc(line, sphere) does not depend on which point of the line is the origin.  All primary rays start
+// at the camera and every shadow ray towards light j lies (to within the rounding of its direction) on a line through
+// that light, so c = |C-V|^2 - r^2 is a per-(pivot, sphere) constant tabulated once per frame by k_pivot in float64-
+// rounded-once form.  The filter only SELECTS candidates (margin bounds its own rounding, the exact test's rounding
+// and the distance between the true ray line and the pivot); sphere_exact() on the real ray decides, so the output is
+// bit-identical to running the exact test on every sphere (B200RT_F_NO_FILTER, tests/test_gpu_parity.py).
+constexpr int kTabCap = 3584;            // float4 entries of the constant-memory table = 3584 spheres (56 KB)
+static __constant__ float4 c_tab[kTabCap + 2 * 4]; // per sphere pair i: [2i] = (cx0,cx1,cy0,cy1)  [2i+1] = (cz0,cz1,k0,k1); + prefetch overrun
+
+struct PivotDev {
+    const float4* tab;                   // [(L+2)][Spad] pair layout; table j < L: light j, j == L: camera, j == L+1: origin-free
+    const float4* piv;                   // [(L+1)]       pivot positions (float32)
+    const float*  bounds;                // [2]           max |C|, max r
+};
+
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
+__device__ __forceinline__ float2 bc(float a) { return make_float2(a, a); }       // FFMA2 broadcast operand (R.F32 / UR.F32)
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+    float d; asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c)); return d;   // FMNMX3 (sm_100+)
+}
+
+// MODE 0: closest hit, arbitrary rays (bounces)   MODE 1: closest hit, camera pivot (primary)   MODE 2: any hit, shadow
+// rays of light j.  NR = rays per thread.  The launch covers the sphere chunk [c0, c0+cnt) (cnt % 8 == 0) whose table
+// the host copied to c_tab[tb ...].  Work distribution: every WARP claims groups of 32*NR consecutive rays from a
+// global counter (one per light) — no CTA-wide barrier anywhere.  One launch per (light, sphere chunk); with more than
+// one chunk the running (t, id) / occlusion state is carried in the output arrays.
+//
+// Candidates (filter passes, ~1.5 per ray out of S) are not tested where they are found: a warp appends them to its
+// own shared-memory queue and runs the exact test over the queue with all 32 lanes busy ("flush"), when the queue
+// fills and at the end of the group.  Results meet in shared memory: closest hit = atomicMin on the packed key
+// (float bits of t << 32 | sphere id) — min t, and on equal t the lowest index, which is the reference's tie-break
+// (first object wins, trace.py:26; planes have ids >= S and so lose ties against spheres, trace.py:36).
+constexpr int KP = 4;                    // sphere pairs per scan step (8 spheres)
+constexpr int kQCap = 1024;              // candidate queue entries per warp
+constexpr int kQFlush = kQCap - 32 * 16; // flush before an append (<= 16 per lane) could overflow
+constexpr unsigned long long kNoHit = kNoHitKey;                                                 // (999.0f, id -1)
+
+struct IsectSmem {
+    uint32_t q[kThreads / 32][kQCap];
+    uint32_t kt[kThreads / 32][32 * 8];                // per ray of the warp's group: float bits of the closest t / occlusion flag
+    uint32_t ki[kThreads / 32][32 * 8];                // ... and the id of the closest object
+};
+
+template <int MODE, int NR>
+__global__ void __launch_bounds__(kThreads, NR == 8 ? 2 : 3)
+k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
+    constexpr bool ANY = (MODE == 2), PIV = (MODE != 0);
+    constexpr int GW = 32 * NR;                               // rays per warp group
+    constexpr int NO = PIV ? 1 : NR;                          // 2*O operands exist only in the 8-FFMA2 form
+    extern __shared__ __align__(16) unsigned char s_raw[];
+    IsectSmem& sm = *reinterpret_cast<IsectSmem*>(s_raw);
+    const bool first = (c0 == 0), last = (c0 + cnt >= sc.Spad);
+    const bool lists = ANY && q.shidx != nullptr;             // shadow: per-light lists (else every hit record, identity map)
+    const uint32_t n_tot = ANY ? *q.n_tot : 0u;
+    const uint32_t n_in = ANY ? (lists ? q.n_in[j] : n_tot) : q.n_in[0];
+    const uint32_t* shl = lists ? q.shidx + (size_t)j * q.shcap : nullptr;    // list entry -> hit record
+    const uint32_t ngroups = (n_in + GW - 1) / GW;
+    const int npair = cnt >> 1;
+    const float cmax = pv.bounds[0], rmax = pv.bounds[1];
+    const float kInf = __int_as_float(0x7f800000);
+    const uint32_t lane = lane_id(), wid = threadIdx.x >> 5;
+    uint32_t* sq = sm.q[wid];
+    uint32_t* skt = sm.kt[wid]; uint32_t* ski = sm.ki[wid];
+    uint32_t slow_cnt = 0, exact_cnt = 0;
+    // j: pivot of this launch (light index for ANY, camera = L for MODE 1); its table is c_tab[tb + 2*pair + {0,1}].
+    // tb is a kernel parameter so that the table index provably lives in uniform registers (LDCU -> UR operands).
+    V3 Vp = mk(0.f, 0.f, 0.f);
+    if (PIV) { const float4 v = __ldg(&pv.piv[j]); Vp = mk(v.x, v.y, v.z); }
+    uint32_t* work = q.work + (ANY ? j : 0);
+
+    auto run_group = [&](const uint32_t g) {
+        // A thread owns NR CONSECUTIVE queue entries (neighbouring pixels): they pass the filter at the same spheres.
+        const uint32_t gbase = g * (uint32_t)GW, i0 = gbase + lane * NR;
+
+        // ---- per-ray constants (32-bit registers, broadcast operands of FFMA2) ----
+        float dx[NR], dy[NR], dz[NR], nod[NR], o2x[NO], o2y[NO], o2z[NO], nthr[NO], thr[PIV ? NR : 1];
+#pragma unroll
+        for (int r = 0; r < NR; ++r) {
+            const uint32_t i = i0 + r;
+            bool active = i < n_in;
+            V3 O = mk(0.f, 0.f, 0.f), D = mk(0.f, 0.f, 0.f);
+            float th = kInf, no = 0.f;
+            unsigned long long key0 = ANY ? 0ull : kNoHit;
+            uint32_t hrec = 0;
+            if (ANY && active) hrec = shl ? shl[i] : i;
+            if (ANY && active && !first) {                        // occluded by a sphere of an earlier chunk: done
+                if (q.occl[(size_t)j * q.ocap + hrec]) { key0 = 1ull; active = false; }
+            }
+            skt[lane * NR + r] = (uint32_t)(key0 >> 32) | (ANY ? (uint32_t)key0 : 0u); ski[lane * NR + r] = 0xffffffffu;
+            if (active) {
+                if (MODE == 2) {
+                    const float4 p = q.hP[hrec];
+                    O = mk(p.x, p.y, p.z);
+                    const V3 d = sub3(Vp, O);                                   // common.py:84-91
+                    const float nrm = __fsqrt_rn(dot3(d, d));
+                    D = mk(__fdiv_rn(d.x, nrm), __fdiv_rn(d.y, nrm), __fdiv_rn(d.z, nrm));
+                    const float A = cmax + __fsqrt_rn(dot3(Vp, Vp)), B = cmax + __fsqrt_rn(dot3(O, O));
+                    const float e = nrm * 9.5367432e-7f;                        // 2^-20 |V-P|: ray line vs pivot
+                    th = -(fmaf(3.8146973e-6f, fmaf(A, A, B * B), fmaf(4.f * e, rmax, 16.f * e * e)) + 1e-12f);
+                    no = -dot3(Vp, D);
+                } else {
+                    const float4 o = q.rayO[i], d = q.rayD[i];
+                    O = mk(o.x, o.y, o.z); D = mk(d.x, d.y, d.z);
+                    const float oo = dot3(O, O);
+                    const float A = cmax + __fsqrt_rn(oo);
+                    const float margin = fmaf(3.8146973e-6f /* 64 * 2^-24 */, A * A, 1e-12f);
+                    if (MODE == 1) { th = -2.f * margin; no = -dot3(Vp, D); }   // O == Vp for every primary ray
+                    else           { th = oo - margin;   no = -dot3(O, D); }
+                }
+            }
+            dx[r] = D.x; dy[r] = D.y; dz[r] = D.z; nod[r] = no;
+            // MODE 0: the per-ray threshold is folded into q (q' = q - thr, one more FFMA2): candidates are q' >= 0
+            // (an inactive ray has thr = +inf, so its q' is -inf and never qualifies).
+            if (!PIV) { o2x[r] = 2.f * O.x; o2y[r] = 2.f * O.y; o2z[r] = 2.f * O.z; nthr[r] = -th; }
+            else      thr[PIV ? r : 0] = th;
+        }
+        float thr_t = 0.f;                                    // one scan threshold per thread: the loosest of its rays
+        if (PIV) {
+            thr_t = thr[0];
+#pragma unroll
+            for (int r = 1; r < NR; ++r) thr_t = fminf(thr_t, thr[PIV ? r : 0]);
+        }
+        uint32_t qcnt = 0;                                    // candidates waiting in this warp's queue (warp-uniform)
+
+        // q (minus thr in MODE 0) of ray r against sphere pair (u, w): lanes .x/.y = spheres 2i / 2i+1
+        auto qray = [&](int r, const float4& u, const float4& w) -> float2 {
+            const float2 b = ffma2(make_float2(u.x, u.y), bc(dx[r]), ffma2(make_float2(u.z, u.w), bc(dy[r]),
+                                   ffma2(make_float2(w.x, w.y), bc(dz[r]), bc(nod[r]))));
+            if (PIV) return ffma2(b, b, make_float2(w.z, w.w));
+            const int ro = PIV ? 0 : r;
+            const float2 t = ffma2(make_float2(u.x, u.y), bc(o2x[ro]), ffma2(make_float2(u.z, u.w), bc(o2y[ro]),
+                                   ffma2(make_float2(w.x, w.y), bc(o2z[ro]), ffma2(make_float2(w.z, w.w), bc(1.0f), bc(nthr[ro])))));
+            return ffma2(b, b, t);
+        };
+
+        // -- exact tests over the queue, one candidate per lane per iteration (dense) --
+        // The closest hit of a ray is the minimum over its candidates of (t, id) — smallest t, lowest id on a tie
+        // (trace.py:26).  Two native 32-bit shared atomics instead of a 64-bit atomicMin: the latter is a CAS loop, and
+        // with a divergent loop inside the scan ptxas no longer keeps the table operands in uniform registers.
+        auto flush = [&]() {
+            __syncwarp();
+            for (uint32_t base = 0; base < qcnt; base += 32) {                // warp-uniform trip count
+                const uint32_t idx = base + lane;
+                bool hit = false; uint32_t rl = 0, tbits = 0; int sid = 0;
+                if (idx < qcnt) {
+                    const uint32_t item = sq[idx];
+                    rl = item & 255u; sid = c0 + (int)(item >> 8);
+                    const uint32_t i = gbase + rl;
+                    V3 O, D;                                   // the ray, re-read (bit-identical to the setup above)
+                    if (MODE == 2) { const float4 hp = q.hP[shl ? shl[i] : i]; O = mk(hp.x, hp.y, hp.z); D = normalize3(sub3(Vp, O)); }
+                    else {
+                        const float4 d = q.rayD[i]; D = mk(d.x, d.y, d.z);
+                        if (MODE == 1) O = Vp; else { const float4 o = q.rayO[i]; O = mk(o.x, o.y, o.z); }
+                    }
+                    const float4 sp = __ldg(&sc.sphB[sid]);
+                    const float t = sphere_exact(O, D, sp.x, sp.y, sp.z, sp.w);
+                    hit = t > 0.f && t < kTMax;                                               // trace.py:26-29
+                    tbits = __float_as_uint(t);
+                }
+                if (ANY) { if (hit) skt[rl] = 1u; __syncwarp(); }
+                else {
+                    if (hit && tbits < atomicMin(&skt[rl], tbits)) ski[rl] = 0xffffffffu;     // new minimum t: forget the old id
+                    __syncwarp();
+                    if (hit && skt[rl] == tbits) atomicMin(&ski[rl], (uint32_t)sid);
+                    __syncwarp();
+                }
+            }
+            exact_cnt += (qcnt + 31 - lane) / 32;
+            __syncwarp();
+            qcnt = 0;
+        };
+
+        // -- candidates in sphere pair `pair` (rare): recompute q per ray, append the passing (ray, sphere)
+        // combinations to the warp's queue (warp prefix sum of the per-lane counts) --
+        auto slow_pair = [&](int pair) {
+            const float4 u = c_tab[tb + 2 * pair], w = c_tab[tb + 2 * pair + 1];
+            uint32_t cand = 0;
+#pragma unroll
+            for (int r = 0; r < NR; ++r) {
+                const float2 qv = qray(r, u, w);
+                const float lim = PIV ? thr[PIV ? r : 0] : 0.f;
+                if (qv.x >= lim) cand |= 1u << (2 * r);
+                if (qv.y >= lim) cand |= 2u << (2 * r);
+            }
+            if (c0 + 2 * pair + 1 >= sc.S) cand &= (c0 + 2 * pair >= sc.S) ? 0u : 0x55555555u;     // padding spheres
+            const uint32_t n = (uint32_t)__popc(cand);
+            uint32_t x = n;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, d); if ((int)lane >= d) x += y; }
+            uint32_t pos = qcnt + x - n;
+            qcnt += __shfl_sync(0xffffffffu, x, 31);
+            while (cand) {
+                const int bit = __ffs(cand) - 1;
+                cand &= cand - 1;
+                sq[pos++] = (lane * NR + (uint32_t)(bit >> 1)) | ((uint32_t)(2 * pair + (bit & 1)) << 8);
+            }
+            if (qcnt > (uint32_t)kQFlush) flush();
+        };
+        auto slow_step = [&](int pb, const float (&mk4)[KP]) {        // pairs pb .. pb+KP-1, per-pair maxima mk4
+            slow_cnt++;
+#pragma unroll 1
+            for (int k = 0; k < KP; ++k) {
+                float mv = mk4[0];
+#pragma unroll
+                for (int kk = 1; kk < KP; ++kk) mv = (k == kk) ? mk4[kk] : mv;
+                if (__any_sync(0xffffffffu, mv >= thr_t)) slow_pair(pb + k);
+            }
+        };
+
+        // ---- scan: KP sphere pairs x NR rays per step, pair-major; the uniform registers of a pair are refilled
+        // for the NEXT step as soon as the pair is done (rolling prefetch: LDCU latency never reaches the FMA pipe).
+        // The candidate decision of a step is taken one step LATER (software pipelining): the vote/branch never
+        // waits on the FMA pipe. ----
+        float mprev[KP];
+        float4 u[KP], w[KP];
+#pragma unroll
+        for (int k = 0; k < KP; ++k) { mprev[k] = -3.0e38f; u[k] = c_tab[tb + 2 * k]; w[k] = c_tab[tb + 2 * k + 1]; }
+        int pb = 0;                                                   // first pair of the step being computed
+        for (;;) {
+            bool found = false;
+            for (; pb < npair; pb += KP) {
+                const float mall = fmaxf(fmaxf(mprev[0], mprev[1]), fmaxf(mprev[2], mprev[3]));
+                const bool fire = __any_sync(0xffffffffu, mall >= thr_t);       // step pb-KP
+                float mk4[KP];
+#pragma unroll
+                for (int k = 0; k < KP; ++k) {
+                    float m = -3.0e38f;
+#pragma unroll
+                    for (int r = 0; r < NR; ++r) { const float2 qv = qray(r, u[k], w[k]); m = fmax3(m, qv.x, qv.y); }
+                    mk4[k] = m;
+                    u[k] = c_tab[tb + 2 * (pb + KP + k)]; w[k] = c_tab[tb + 2 * (pb + KP + k) + 1];   // next step (c_tab is over-allocated)
+                }
+                if (fire) {                                           // handle step pb-KP first, keep this step pending
+                    slow_step(pb - KP, mprev);
+#pragma unroll
+                    for (int k = 0; k < KP; ++k) mprev[k] = mk4[k];
+                    found = true; pb += KP; break;
+                }
+#pragma unroll
+                for (int k = 0; k < KP; ++k) mprev[k] = mk4[k];
+            }
+            if (found) continue;
+            const float mall = fmaxf(fmaxf(mprev[0], mprev[1]), fmaxf(mprev[2], mprev[3]));
+            if (__any_sync(0xffffffffu, mall >= thr_t)) slow_step(npair - KP, mprev);            // flush the last step
+            break;
+        }
+        flush();
+
+        // ---- planes after the last sphere chunk (trace.py:32-39), then write back ----
+#pragma unroll
+        for (int r = 0; r < NR; ++r) {
+            const uint32_t i = i0 + r;
+            if (i >= n_in) continue;
+            const unsigned long long key = ((unsigned long long)skt[lane * NR + r] << 32) | ski[lane * NR + r];
+            if (ANY) {
+                bool occluded = (key >> 32) != 0ull;
+                const uint32_t hrec = shl ? shl[i] : i;
+                if (last && !occluded && sc.Pl > 0) {
+                    const float4 hp = q.hP[hrec]; const V3 O = mk(hp.x, hp.y, hp.z);
+                    const V3 D = mk(dx[r], dy[r], dz[r]);
+                    for (int pl = 0; pl < sc.Pl && !occluded; ++pl) {
+                        const float t = plane_exact(O, D, __ldg(&sc.plO[pl]), __ldg(&sc.plN[pl]));
+                        occluded = (t > 0.f && t < kTMax);
+                    }
+                }
+                if (occluded) q.occl[(size_t)j * q.ocap + hrec] = 1;
+            } else {
+                float best = __uint_as_float((uint32_t)(key >> 32)); int bid = (int)(uint32_t)key;
+                if (last) {
+                    const V3 D = mk(dx[r], dy[r], dz[r]);
+                    const V3 O = (MODE == 0) ? mk(0.5f * o2x[PIV ? 0 : r], 0.5f * o2y[PIV ? 0 : r], 0.5f * o2z[PIV ? 0 : r]) : Vp;
+                    for (int pl = 0; pl < sc.Pl; ++pl) {
+                        const float t = plane_exact(O, D, __ldg(&sc.plO[pl]), __ldg(&sc.plN[pl]));
+                        if (t > 0.f && t < best) { best = t; bid = sc.S + pl; }
+                    }
+                }
+                if (bid >= 0) atomicMin(&q.hit[i], ((unsigned long long)__float_as_uint(best) << 32) | (uint32_t)bid);
+            }
+        }
+        __syncwarp();                                         // keys are re-initialised by the next group's setup
+    };
+
+    for (;;) {
+        uint32_t g = 0;
+        if (lane == 0) g = atomicAdd(work, 1u);
+        g = __shfl_sync(0xffffffffu, g, 0);
+        if (g >= ngroups) break;
+        run_group(g);
+    }
+    if (q.slow) {
+        const uint32_t tot = __reduce_add_sync(0xffffffffu, slow_cnt), tot2 = __reduce_add_sync(0xffffffffu, exact_cnt);
+        if (lane == 0 && tot) { atomicAdd(q.slow, (unsigned long long)tot); atomicAdd(q.slow + 1, (unsigned long long)tot2); }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Host side: table residency and launches (per translation unit = per constant bank)
+// ------------------------------------------------------------------------------------------------
+struct IsectCfg { int sm_count; int force_nr; int force_nr0; };
+
+template <int MODE> static cudaError_t isect3_set_attr() {
+    cudaError_t e;
+    if ((e = cudaFuncSetAttribute(k_isect3<MODE, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IsectSmem))) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_isect3<MODE, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IsectSmem))) != cudaSuccess) return e;
+    return cudaFuncSetAttribute(k_isect3<MODE, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IsectSmem));
+}
+
+// Whole tables tabs[0..n) (each Spad entries) into slots 0..n-1 of THIS module's c_tab: done once per frame when
+// n * Spad <= kTabCap, after which launches pass resident = true and nothing is copied between them.
+static inline cudaError_t isect3_upload_resident(const PivotDev& pv, int Spad, const int* tabs, int n, cudaStream_t st) {
+    for (int k = 0; k < n; ++k) {
+        cudaError_t e = cudaMemcpyToSymbolAsync(c_tab, pv.tab + (size_t)tabs[k] * Spad, sizeof(float4) * Spad,
+                                                sizeof(float4) * (size_t)k * Spad, cudaMemcpyDeviceToDevice, st);
+        if (e != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
+// k_isect3 launches for one query (closest hit of a ray queue, or the shadow query of the hit lists): one launch per
+// (sphere chunk, light).  resident: slot convention of isect3_upload_resident — closest-hit module: slot 0 = camera
+// pivot (MODE 1), slot 1 = origin-free (MODE 0); shadow module: slot j = light j.  Otherwise the tables a launch needs
+// are copied in front of it (as many lights beside each other as fit).  `work` points at nsch*(L+1) zeroed group
+// counters.  Rays per thread: 8 for big queues, fewer for small ones (more groups than warps).
+template <int MODE>
+static cudaError_t isect3_launch(const IsectCfg& cfg, const SceneDev& sc, QueueDev q, const PivotDev& pv, size_t max_rays,
+                          uint32_t* work, bool resident, cudaStream_t st) {
+    const size_t warps = (size_t)cfg.sm_count * 2 * (kThreads / 32);
+    int nr = cfg.force_nr ? cfg.force_nr : (max_rays >= warps * 256 * 4 ? 8 : (max_rays >= warps * 128 * 4 ? 4 : 2));
+    if (MODE == 0 && cfg.force_nr0) nr = cfg.force_nr0;         // (measured: 8 rays/thread wins for the 8-FFMA2 form too)
+    const int grid = cfg.sm_count * (nr == 8 ? 2 : 3);
+    const int L = sc.L;
+    const int chunk = std::min(sc.Spad, kTabCap);
+    const int lp = (MODE == 2 && sc.Spad <= kTabCap) ? std::max(1, kTabCap / sc.Spad) : 1;      // light tables beside each other
+    const int nlights = (MODE == 2) ? L : 1;
+    cudaError_t e;
+    for (int c0 = 0, k = 0; c0 < sc.Spad; c0 += chunk, ++k) {
+        const int cnt = std::min(chunk, sc.Spad - c0);
+        q.work = work + (size_t)k * (L + 1);
+        for (int j0 = 0; j0 < nlights; j0 += lp) {
+            const int nj = std::min(lp, nlights - j0);
+            if (!resident)
+                for (int jj = 0; jj < nj; ++jj) {
+                    const int tj = (MODE == 2) ? j0 + jj : (MODE == 1 ? L : L + 1);
+                    e = cudaMemcpyToSymbolAsync(c_tab, pv.tab + (size_t)tj * sc.Spad + c0, sizeof(float4) * cnt,
+                                                sizeof(float4) * (size_t)jj * cnt, cudaMemcpyDeviceToDevice, st);
+                    if (e != cudaSuccess) return e;
+                }
+            for (int jj = 0; jj < nj; ++jj) {
+                const int j = (MODE == 2) ? j0 + jj : L;
+                const int slot = resident ? (MODE == 2 ? j : (MODE == 1 ? 0 : 1)) : jj;
+                const int tb = slot * cnt;
+                if (nr == 8)      k_isect3<MODE, 8><<<grid, kThreads, sizeof(IsectSmem), st>>>(sc, q, pv, c0, cnt, j, tb);
+                else if (nr == 4) k_isect3<MODE, 4><<<grid, kThreads, sizeof(IsectSmem), st>>>(sc, q, pv, c0, cnt, j, tb);
+                else              k_isect3<MODE, 2><<<grid, kThreads, sizeof(IsectSmem), st>>>(sc, q, pv, c0, cnt, j, tb);
+                if ((e = cudaGetLastError()) != cudaSuccess) return e;
+            }
+        }
+    }
+    return cudaSuccess;
+}
+
+// The shadow mode lives in isect_shadow.cu (its own module / constant bank):
+cudaError_t shadow_set_attr();
+cudaError_t shadow_upload_resident(const PivotDev& pv, int Spad, int L, cudaStream_t st);
+cudaError_t shadow_launch(const IsectCfg& cfg, const SceneDev& sc, const QueueDev& q, const PivotDev& pv, size_t max_rays,
+                          uint32_t* work, bool resident, cudaStream_t st);
+
+}  // namespace b200rt

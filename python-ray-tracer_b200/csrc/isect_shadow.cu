@@ -1,0 +1,22 @@
+// isect_shadow.cu — the shadow-query instantiations of k_isect3 (MODE 2: any hit towards light j, reference
+// trace.py:86-96).  A separate translation unit = a separate CUDA module with its own constant bank: the lights'
+// pivot tables stay resident here while the closest-hit tables stay resident in b200rt.cu's bank (see isect3.cuh).
+#include "isect3.cuh"
+#include <vector>
+
+namespace b200rt {
+
+cudaError_t shadow_set_attr() { return isect3_set_attr<2>(); }
+
+cudaError_t shadow_upload_resident(const PivotDev& pv, int Spad, int L, cudaStream_t st) {
+    std::vector<int> tabs(L);
+    for (int j = 0; j < L; ++j) tabs[j] = j;                 // slot j = light j
+    return isect3_upload_resident(pv, Spad, tabs.data(), L, st);
+}
+
+cudaError_t shadow_launch(const IsectCfg& cfg, const SceneDev& sc, const QueueDev& q, const PivotDev& pv, size_t max_rays,
+                          uint32_t* work, bool resident, cudaStream_t st) {
+    return isect3_launch<2>(cfg, sc, q, pv, max_rays, work, resident, st);
+}
+
+}  // namespace b200rt
