@@ -168,6 +168,9 @@ def run_ours(args, w):
     spheres, lights, planes = [torch.from_numpy(a).to(dev) for a in (sp_h, li_h, pl_h)]
     result = torch.zeros((3, W, H), dtype=torch.uint8, device=dev)
     strips = (STRIP, rank, world) if world > 1 else None
+    emu = int(os.environ.get("B200RT_EMULATE_WORLD", "0"))      # tuning aid: render rank 0's share of an N-GPU frame on one GPU
+    if world == 1 and emu > 1:
+        strips = (STRIP, 0, emu)
     shade = (w["amb"], w["lamb"], w["refl"], w["refl_depth"], w["aliasing"])
     stream = torch.cuda.current_stream(dev)
 

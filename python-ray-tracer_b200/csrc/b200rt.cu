@@ -312,21 +312,23 @@ __global__ void k_pivot(SceneDev sc, float cox, float coy, float coz, float4* ta
 // Per-hit shading kernels (trace.py:56-110, :123-131) — <1 % of the work at S=1024
 // ------------------------------------------------------------------------------------------------
 struct ShadeDev {
-    float4* rayO; float4* rayD;          // ray queue (read by k_setup, rewritten by k_shade)
-    unsigned long long* hit;             // packed closest hit per ray (read by k_setup; k_shade pre-sets it for the next depth)
-    float4* hP; float4* hN; float4* hD;  // hit records: (biased P, slot) (N, id) (incoming D, -)
+    const float4* rayO; const float4* rayD;      // this depth's ray queue (k_setup input)
+    const unsigned long long* hit;               // packed closest hit per ray (k_setup input)
+    float4* rayO2; float4* rayD2; unsigned long long* hit2;   // next depth's ray queue (k_setup output; hit2 pre-set to "no hit")
+    float4* hP; float4* hN;              // hit records: (biased P, slot) (N, id)
     uint8_t* occl; size_t ocap;          // [light][hit], row stride ocap (zeroed by k_setup, set by the shadow query)
     float* accR; float* accG; float* accB;   // per-slot colour accumulators
     const uint32_t* n_live;              // rays in the queue (k_setup input)
     uint32_t* n_hit;                     // hit records (k_setup output, k_shade input)
     uint32_t* shidx; size_t shcap; uint32_t* n_sh;   // per light: list of hit records to shadow-test, and its length (k_setup output)
-    uint32_t* n_next;                    // next ray queue length (k_shade output)
     float amb, lamb, weight;             // weight = refl^depth_index (1 for the primary trace), trace.py:131
-    int emit_reflection;                 // 0 on the last depth
+    int emit_reflection;                 // 0 on the last depth (k_setup)
+    unsigned long long* tl;              // diagnostic timeline slot (may be null)
 };
 
 // trace.py:56-83: miss -> path ends; hit -> P = O + tD, colour/normal by object type, P += BIAS*N.
 __global__ void k_setup(SceneDev sc, ShadeDev s) {
+    if (s.tl && threadIdx.x == 0) atomicMin(s.tl, globaltimer_ns());
     const uint32_t n = *s.n_live;
     for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {
         const uint32_t i = base + threadIdx.x;
@@ -368,45 +370,47 @@ __global__ void k_setup(SceneDev sc, ShadeDev s) {
         if (hit) {
             s.hP[h] = make_float4(Pb.x, Pb.y, Pb.z, o.w);
             s.hN[h] = make_float4(N.x, N.y, N.z, __int_as_float(id));
-            s.hD[h] = make_float4(d.x, d.y, d.z, 0.f);
             for (int j = 0; j < sc.L; ++j) s.occl[(size_t)j * s.ocap + h] = 0;
+            if (s.emit_reflection) {                 // the bounce ray does not depend on the shadow queries: queue it now,
+                const V3 D = mk(d.x, d.y, d.z);      // the next closest-hit launch runs beside this depth's shadow launches
+                const float dn = dot3(D, N);
+                const V3 R = normalize3(madd3(D, -2.0f * dn, N));                              // common.py:113-120
+                const V3 O2 = madd3(Pb, kBias, R);                                             // trace.py:110
+                s.rayO2[h] = make_float4(O2.x, O2.y, O2.z, o.w);                               // the hit list IS the next queue
+                s.rayD2[h] = make_float4(R.x, R.y, R.z, 0.f);
+                s.hit2[h] = kNoHit;
+            }
         }
     }
+    if (s.tl && threadIdx.x == 0) atomicMax(s.tl + 1, globaltimer_ns());
 }
 
-// trace.py:77,86-110 and the accumulate of trace.py:131: RGB_trace = amb*col + sum_j [visible_j && k_j>0] k_j*col,
-// acc[slot] += weight * RGB_trace; then the reflection ray (common.py:113-120) re-queued at the same index.
+// trace.py:77,86-102 and the accumulate of trace.py:131: RGB_trace = amb*col + sum_j [visible_j && k_j>0] k_j*col,
+// acc[slot] += weight * RGB_trace.  (The reflection ray of trace.py:104-110 was queued by k_setup.)
 __global__ void k_shade(SceneDev sc, ShadeDev s) {
+    if (s.tl && threadIdx.x == 0) atomicMin(s.tl, globaltimer_ns());
     const uint32_t n = *s.n_hit;
-    if (blockIdx.x == 0 && threadIdx.x == 0) *s.n_next = s.emit_reflection ? n : 0u;
     for (uint32_t h = blockIdx.x * blockDim.x + threadIdx.x; h < n; h += gridDim.x * blockDim.x) {
-        const float4 p = s.hP[h], nn = s.hN[h], dd = s.hD[h];
-        const V3 Pb = mk(p.x, p.y, p.z), N = mk(nn.x, nn.y, nn.z), D = mk(dd.x, dd.y, dd.z);
+        const float4 p = s.hP[h], nn = s.hN[h];
+        const V3 Pb = mk(p.x, p.y, p.z), N = mk(nn.x, nn.y, nn.z);
         const int id = __float_as_int(nn.w);
         const uint32_t slot = __float_as_uint(p.w);
         const float4 col = (id < sc.S) ? __ldg(&sc.sphCol[id]) : __ldg(&sc.plCol[id - sc.S]);
         float r = __fmul_rn(s.amb, col.x), g = __fmul_rn(s.amb, col.y), b = __fmul_rn(s.amb, col.z);   // trace.py:77
         for (int j = 0; j < sc.L; ++j) {                                                               // trace.py:86
-            if (!s.shidx && s.occl[(size_t)j * s.ocap + h]) continue;                                       // :95-96 (dense layout)
+            if (!s.shidx && s.occl[(size_t)j * s.ocap + h]) continue;                                  // :95-96 (dense layout)
             const float4 l = __ldg(&sc.lights[j]);
             const V3 Lv = normalize3(sub3(mk(l.x, l.y, l.z), Pb));                                     // :89
             const float k = __fmul_rn(s.lamb, dot3(Lv, N));                                            // :99
             if (!(k > 0.f)) continue;                                                                  // :101 (lists: no shadow query was made)
-            if (s.shidx && s.occl[(size_t)j * s.ocap + h]) continue;                                       // :95-96
+            if (s.shidx && s.occl[(size_t)j * s.ocap + h]) continue;                                   // :95-96
             r = fmaf(k, col.x, r); g = fmaf(k, col.y, g); b = fmaf(k, col.z, b);                       // :102
         }
         s.accR[slot] = fmaf(s.weight, r, s.accR[slot]);                                                // :131
         s.accG[slot] = fmaf(s.weight, g, s.accG[slot]);
         s.accB[slot] = fmaf(s.weight, b, s.accB[slot]);
-        if (s.emit_reflection) {
-            const float dn = dot3(D, N);
-            const V3 R = normalize3(madd3(D, -2.0f * dn, N));                                          // common.py:113-120
-            const V3 O2 = madd3(Pb, kBias, R);                                                         // trace.py:110
-            s.rayO[h] = make_float4(O2.x, O2.y, O2.z, p.w);
-            s.rayD[h] = make_float4(R.x, R.y, R.z, 0.f);
-            s.hit[h] = kNoHit;
-        }
     }
+    if (s.tl && threadIdx.x == 0) atomicMax(s.tl + 1, globaltimer_ns());
 }
 
 // kernels.py:58-73: sum the samples in reference order with the G/B cross-wiring (F6), /9, quantise with
@@ -582,25 +586,42 @@ struct Buf {
     template <class T> T* as() const { return reinterpret_cast<T*>(p); }
 };
 
+constexpr int kSets = 4;      // depths whose hit records are alive at once
+constexpr int kSide = 4;      // shadow streams
+
 struct DevCtx {
     std::mutex mu;
     bool init = false;
     int sm_count = 0;
     int isect_blocks_per_sm = 2;
-    int force_nr = 0, force_nr0 = 0; bool no_pivot = false;                       // tuning overrides (env B200RT_NR, B200RT_NO_PIVOT)
+    int force_nr = 0, force_nr0 = 0; bool no_pivot = false, no_conc = false;                       // tuning overrides (env B200RT_NR, B200RT_NO_PIVOT)
     Buf sphA, sphB, sphCol, plO, plN, plNu, plCol, lights, cmax;   // packed scene
     Buf pivTab, pivPos;                                            // pivot tables (k_pivot)
     Buf stage;                                                     // host-scene / host-pixel_loc staging
-    Buf rayO, rayD, hitKey, hP, hN, hD, acc, occl, shidx, ctr, work, slow; // wavefront state
+    Buf rayO[2], rayD[2], hitKey[2];                               // ray queues, double-buffered by depth parity
+    Buf hP[kSets], hN[kSets], occl[kSets], shidx[kSets];           // hit records / shadow state: ring of kSets depths
+    Buf acc, ctr, work, slow, tl;
+    bool timeline = false;                                        // env B200RT_TIMELINE: per-launch first-start / last-end (globaltimer) to stderr
+    // internal streams (see the launch sequence in render_device): the dependent chain at high priority, one stream per
+    // light (up to kSide) for the shadow queries, one for the shading
+    cudaStream_t chainStream = nullptr, lightStream[kSide] = {}, shadeStream = nullptr;
+    cudaEvent_t evFork = nullptr, evJoin = nullptr, evSetup[kSets] = {}, evShade[kSets] = {}, evLight[kSide] = {};
     Buf batchScene;                                                // b200rt_render_batch_host: the scene, staged once
     cudaStream_t copyStream = nullptr; cudaEvent_t evRender[2] = {nullptr, nullptr}, evCopy[2] = {nullptr, nullptr};
     Buf hostResult, hostPixelLoc, imgOut;                          // b200rt_render_host / b200rt_to_image_host device copies
     cudaEvent_t done = nullptr; bool has_done = false;
     void release_all() {
-        Buf* all[] = { &sphA, &sphB, &sphCol, &plO, &plN, &plNu, &plCol, &lights, &cmax, &pivTab, &pivPos, &stage, &rayO, &rayD, &hitKey,
-                       &hP, &hN, &hD, &acc, &occl, &shidx, &ctr, &work, &slow, &hostResult, &hostPixelLoc, &imgOut, &batchScene };
+        Buf* all[] = { &sphA, &sphB, &sphCol, &plO, &plN, &plNu, &plCol, &lights, &cmax, &pivTab, &pivPos, &stage, &rayO[0], &rayO[1], &rayD[0], &rayD[1], &hitKey[0], &hitKey[1],
+                       &acc, &tl, &ctr, &work, &slow, &hostResult, &hostPixelLoc, &imgOut, &batchScene };
         for (Buf* b : all) b->release();
+        for (int i = 0; i < kSets; ++i) { hP[i].release(); hN[i].release(); occl[i].release(); shidx[i].release(); }
         if (done) { cudaEventDestroy(done); done = nullptr; } has_done = false; init = false;
+        if (chainStream) {
+            cudaStreamDestroy(chainStream); chainStream = nullptr; cudaStreamDestroy(shadeStream);
+            for (int i = 0; i < kSide; ++i) { cudaStreamDestroy(lightStream[i]); cudaEventDestroy(evLight[i]); }
+            for (int i = 0; i < kSets; ++i) { cudaEventDestroy(evSetup[i]); cudaEventDestroy(evShade[i]); }
+            cudaEventDestroy(evFork); cudaEventDestroy(evJoin);
+        }
         if (copyStream) { cudaStreamDestroy(copyStream); copyStream = nullptr; for (int i = 0; i < 2; ++i) { cudaEventDestroy(evRender[i]); cudaEventDestroy(evCopy[i]); } }
     }
 };
@@ -668,7 +689,17 @@ int init_ctx(DevCtx& c, int device) {
     { const char* e = getenv("B200RT_NR"); c.force_nr = e ? atoi(e) : 0; if (c.force_nr != 2 && c.force_nr != 4 && c.force_nr != 8) c.force_nr = 0; }
     { const char* e = getenv("B200RT_NR0"); c.force_nr0 = e ? atoi(e) : 0; if (c.force_nr0 != 2 && c.force_nr0 != 4 && c.force_nr0 != 8) c.force_nr0 = 0; }
     { const char* e = getenv("B200RT_NO_PIVOT"); c.no_pivot = e && atoi(e) != 0; }
+    { const char* e = getenv("B200RT_NO_CONCURRENCY"); c.no_conc = e && atoi(e) != 0; }
+    { const char* e = getenv("B200RT_TIMELINE"); c.timeline = e && atoi(e) != 0; }
     CK(cudaEventCreateWithFlags(&c.done, cudaEventDisableTiming));
+    {
+        int lo = 0, hi = 0; CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));         // hi = greatest priority (numerically lowest)
+        CK(cudaStreamCreateWithPriority(&c.chainStream, cudaStreamNonBlocking, hi));
+        CK(cudaStreamCreateWithPriority(&c.shadeStream, cudaStreamNonBlocking, hi));
+        for (int i = 0; i < kSide; ++i) { CK(cudaStreamCreateWithPriority(&c.lightStream[i], cudaStreamNonBlocking, lo)); CK(cudaEventCreateWithFlags(&c.evLight[i], cudaEventDisableTiming)); }
+        for (int i = 0; i < kSets; ++i) { CK(cudaEventCreateWithFlags(&c.evSetup[i], cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&c.evShade[i], cudaEventDisableTiming)); }
+        CK(cudaEventCreateWithFlags(&c.evFork, cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&c.evJoin, cudaEventDisableTiming));
+    }
     c.init = true;
     return 0;
 }
@@ -743,14 +774,20 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     cols_per_chunk = std::min<size_t>(cols_per_chunk, (size_t)ncols);
     const int nchunks = (int)((ncols + cols_per_chunk - 1) / cols_per_chunk);
     const size_t cap = cols_per_chunk * per_col;                 // slots per chunk
-    CK(c.rayO.ensure(sizeof(float4) * cap)); CK(c.rayD.ensure(sizeof(float4) * cap));
-    CK(c.hitKey.ensure(sizeof(unsigned long long) * cap));
-    CK(c.hP.ensure(sizeof(float4) * cap)); CK(c.hN.ensure(sizeof(float4) * cap)); CK(c.hD.ensure(sizeof(float4) * cap));
-    CK(c.acc.ensure(sizeof(float) * 3 * cap)); CK(c.occl.ensure(std::max<size_t>(cap * (size_t)L, 1)));
+    const bool use_lists = S >= 32 && !(a->flags & B200RT_F_NO_FILTER);
+    for (int b = 0; b < 2; ++b) {                                // depth d: ray queue d & 1 (see the launch sequence below)
+        CK(c.rayO[b].ensure(sizeof(float4) * cap)); CK(c.rayD[b].ensure(sizeof(float4) * cap));
+        CK(c.hitKey[b].ensure(sizeof(unsigned long long) * cap));
+    }
+    const int nsets = std::min(kSets, depth + 1);                // depth d: hit-record set d % nsets
+    for (int b = 0; b < nsets; ++b) {
+        CK(c.hP[b].ensure(sizeof(float4) * cap)); CK(c.hN[b].ensure(sizeof(float4) * cap));
+        CK(c.occl[b].ensure(std::max<size_t>(cap * (size_t)L, 1)));
+        if (use_lists) CK(c.shidx[b].ensure(sizeof(uint32_t) * std::max<size_t>(cap * (size_t)L, 1)));
+    }
+    CK(c.acc.ensure(sizeof(float) * 3 * cap));
     // Per-light shadow lists pay off when a query is expensive (many spheres); for tiny scenes the dense [light][hit]
     // layout is cheaper than building the lists.
-    const bool use_lists = S >= 32 && !(a->flags & B200RT_F_NO_FILTER);
-    if (use_lists) CK(c.shidx.ensure(sizeof(uint32_t) * std::max<size_t>(cap * (size_t)L, 1)));
     const int cps = 4 + L;                                       // counters per depth: n_live, n_hit, 2 debug work counters, n_sh[L]
     const int ctr_stride = cps * (depth + 2);
     CK(c.ctr.ensure(sizeof(uint32_t) * (size_t)ctr_stride * nchunks)); CK(c.slow.ensure(2 * sizeof(unsigned long long)));
@@ -768,6 +805,18 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     }
     const int small_grid = c.sm_count * 8;
     Timer tm; tm.on = stats; tm.st = st;
+    unsigned long long* tlb = nullptr; int tln = 0; std::vector<std::string> tlname;
+    if (c.timeline) {
+        CK(c.tl.ensure(sizeof(unsigned long long) * 2 * 1024)); tlb = c.tl.as<unsigned long long>();
+        std::vector<unsigned long long> init(2048); for (int i = 0; i < 1024; ++i) { init[2 * i] = ~0ull; init[2 * i + 1] = 0; }
+        CK(cudaMemcpyAsync(tlb, init.data(), sizeof(unsigned long long) * 2048, cudaMemcpyHostToDevice, st)); CK(cudaStreamSynchronize(st));
+    }
+    auto tl_mark = [&](const char* nm, int d, int from) { for (int i = from; i < tln; ++i) tlname.push_back(std::string(nm) + " d" + std::to_string(d) + (tln - from > 1 ? " j" + std::to_string(i - from) : "")); };
+    // concurrency needs launches that do not touch shared constant memory
+    const bool conc = !stats && !nofilter && S >= 64 && closest_res && (L == 0 || shadow_res) && !c.no_conc;
+    cudaStream_t cs = conc ? c.chainStream : st, ss = conc ? c.shadeStream : st;
+    const int nls = std::max(1, std::min(L, kSide));
+    if (conc) { CK(cudaEventRecord(c.evFork, st)); CK(cudaStreamWaitEvent(cs, c.evFork, 0)); }
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     if (stats) { CK(cudaEventCreate(&ev0)); CK(cudaEventCreate(&ev1)); CK(cudaEventRecord(ev0, st)); }
 
@@ -788,63 +837,96 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         float* accR = c.acc.as<float>(); float* accG = accR + cap; float* accB = accG + cap;
 
         tm.begin(2);
-        CK(cudaMemsetAsync(accR, 0, sizeof(float) * nslots, st));
-        CK(cudaMemsetAsync(accG, 0, sizeof(float) * nslots, st));
-        CK(cudaMemsetAsync(accB, 0, sizeof(float) * nslots, st));
-        k_raygen<<<(int)std::min<size_t>((nslots + 255) / 256, (size_t)small_grid), 256, 0, st>>>(f, c.rayO.as<float4>(), c.rayD.as<float4>(), c.hitKey.as<unsigned long long>(), ctr + 0);
+        CK(cudaMemsetAsync(accR, 0, sizeof(float) * nslots, cs));
+        CK(cudaMemsetAsync(accG, 0, sizeof(float) * nslots, cs));
+        CK(cudaMemsetAsync(accB, 0, sizeof(float) * nslots, cs));
+        k_raygen<<<(int)std::min<size_t>((nslots + 255) / 256, (size_t)small_grid), 256, 0, cs>>>(f, c.rayO[0].as<float4>(), c.rayD[0].as<float4>(), c.hitKey[0].as<unsigned long long>(), ctr + 0);
         CK(cudaGetLastError());
         tm.end(2);
 
+        // Launch sequence.  The dependent chain closest(d) -> setup(d) -> closest(d+1) ... runs on `cs`; the shadow
+        // query of light j of every depth on `ls[j % nls]`; the shading of every depth on `ss`.  setup(d) feeds the
+        // shadow queries and the shading of depth d, and only the final resolve consumes the shading.  Why: a k_isect3
+        // launch ends with warps idling for up to one ray group's time, and with few groups per warp (deep bounces, one
+        // GPU of eight) those tails were >10 % of the frame; independent launches pending on other streams back-fill
+        // them, and the chain's high priority keeps the critical path moving.  Ray queues alternate between two
+        // buffers; the hit records of depth d live in set d % nsets, so setup(d + nsets) waits for shade(d).  With
+        // tables that are not resident, the debug kernels, small scenes or stats (per-class timing) everything runs
+        // on `st`.
         for (int d = 0; d <= depth; ++d) {
-            uint32_t* cd = ctr + cps * d;           // [0] n_live, [1] work(closest), [2] work(shadow) (scalar debug kernels), [3] n_hit, [4+j] n_sh[j]
+            const int b = d & 1, hs = d % nsets;
+            uint32_t* cd = ctr + cps * d;           // [0] n_live (d == 0), [1] work(closest), [2] work(shadow) (scalar debug kernels), [3] n_hit, [4+j] n_sh[j]
+            uint32_t* n_live = d == 0 ? ctr + 0 : ctr + cps * (d - 1) + 3;       // the hit list of depth d-1 is the ray queue of depth d
             uint32_t* wk = c.work.as<uint32_t>() + ((size_t)ch * (depth + 1) + d) * work_per_depth;      // k_isect3 group counters
             QueueDev q{};
-            q.rayO = c.rayO.as<float4>(); q.rayD = c.rayD.as<float4>(); q.hP = c.hP.as<float4>();
-            q.hit = c.hitKey.as<unsigned long long>(); q.occl = c.occl.as<uint8_t>(); q.ocap = cap;
+            q.rayO = c.rayO[b].as<float4>(); q.rayD = c.rayD[b].as<float4>(); q.hP = c.hP[hs].as<float4>();
+            q.hit = c.hitKey[b].as<unsigned long long>(); q.occl = c.occl[hs].as<uint8_t>(); q.ocap = cap;
             q.slow = stats ? c.slow.as<unsigned long long>() : nullptr;
             ShadeDev s{};
-            s.rayO = c.rayO.as<float4>(); s.rayD = c.rayD.as<float4>(); s.hit = c.hitKey.as<unsigned long long>();
-            s.hP = c.hP.as<float4>(); s.hN = c.hN.as<float4>(); s.hD = c.hD.as<float4>(); s.occl = c.occl.as<uint8_t>(); s.ocap = cap;
+            s.rayO = q.rayO; s.rayD = q.rayD; s.hit = q.hit;
+            s.rayO2 = c.rayO[b ^ 1].as<float4>(); s.rayD2 = c.rayD[b ^ 1].as<float4>(); s.hit2 = c.hitKey[b ^ 1].as<unsigned long long>();
+            s.hP = c.hP[hs].as<float4>(); s.hN = c.hN[hs].as<float4>(); s.occl = c.occl[hs].as<uint8_t>(); s.ocap = cap;
             s.accR = accR; s.accG = accG; s.accB = accB;
-            s.n_live = cd + 0; s.n_hit = cd + 3; s.n_next = cd + cps;
-            s.shidx = use_lists ? c.shidx.as<uint32_t>() : nullptr; s.shcap = cap; s.n_sh = cd + 4;
+            s.n_live = n_live; s.n_hit = cd + 3;
+            s.shidx = use_lists ? c.shidx[hs].as<uint32_t>() : nullptr; s.shcap = cap; s.n_sh = cd + 4;
             q.shidx = s.shidx; q.shcap = cap; q.n_tot = cd + 3;
             s.amb = (float)a->amb; s.lamb = (float)a->lamb; s.weight = wts[d]; s.emit_reflection = d < depth;
 
             tm.begin(0);
-            q.n_in = cd + 0; q.work = cd + 1;
-            {
-                if (nofilter)                     { if (int rc = launch_intersect<false>(c, sc, q, true, st)) return rc; }
-                else if (d == 0 && !c.no_pivot)   CK(isect3_launch<1>(icfg, sc, q, pv, nslots, wk, closest_res, st));
-                else                              CK(isect3_launch<0>(icfg, sc, q, pv, nslots, wk, closest_res, st));
-            }
+            q.n_in = n_live; q.work = cd + 1;
+            if (nofilter)                     { if (int rc = launch_intersect<false>(c, sc, q, true, cs)) return rc; }
+            else if (d == 0 && !c.no_pivot)   { const int f0 = tln; CK(isect3_launch<1>(icfg, sc, q, pv, nslots, wk, closest_res, cs, tlb, &tln)); tl_mark("closest<1>", d, f0); }
+            else                              { const int f0 = tln; CK(isect3_launch<0>(icfg, sc, q, pv, nslots, wk, closest_res, cs, tlb, &tln)); tl_mark("closest<0>", d, f0); }
             tm.end(0);
             tm.begin(2);
-            k_setup<<<small_grid, 256, 0, st>>>(sc, s); CK(cudaGetLastError());
+            if (conc && d >= nsets) CK(cudaStreamWaitEvent(cs, c.evShade[hs], 0));        // set hs is free again
+            if (tlb) { s.tl = tlb + 2 * (size_t)tln++; tlname.push_back("setup d" + std::to_string(d)); }
+            k_setup<<<small_grid, 256, 0, cs>>>(sc, s); CK(cudaGetLastError());
+            if (conc) CK(cudaEventRecord(c.evSetup[hs], cs));
             tm.end(2);
             if (L > 0) {
                 tm.begin(1);
                 q.n_in = nofilter ? cd + 3 : cd + 4; q.work = cd + 2;        // k_isect3: per-light list lengths n_sh[j]
-                if (nofilter) { if (int rc = launch_intersect<true>(c, sc, q, true, st)) return rc; }
-                else CK(shadow_launch(icfg, sc, q, pv, nslots, wk + (size_t)nsch * (L + 1), shadow_res, st));
+                uint32_t* wks = wk + (size_t)nsch * (L + 1);
+                if (nofilter) { if (int rc = launch_intersect<true>(c, sc, q, true, cs)) return rc; }
+                else if (!conc) { const int f0 = tln; CK(shadow_launch(icfg, sc, q, pv, nslots, wks, shadow_res, cs, tlb, &tln)); tl_mark("shadow", d, f0); }
+                else {
+                    for (int k = 0; k < nls; ++k) CK(cudaStreamWaitEvent(c.lightStream[k], c.evSetup[hs], 0));
+                    for (int j = 0; j < L; ++j) {
+                        const int f0 = tln;
+                        CK(shadow_launch(icfg, sc, q, pv, nslots, wks, true, c.lightStream[j % nls], tlb, &tln, j, j + 1));
+                        if (tlb) tlname.push_back("shadow d" + std::to_string(d) + " j" + std::to_string(j)); (void)f0;
+                    }
+                    for (int k = 0; k < nls; ++k) { CK(cudaEventRecord(c.evLight[k], c.lightStream[k])); CK(cudaStreamWaitEvent(ss, c.evLight[k], 0)); }
+                }
                 tm.end(1);
-            }
+            } else if (conc) CK(cudaStreamWaitEvent(ss, c.evSetup[hs], 0));
             tm.begin(2);
-            k_shade<<<small_grid, 256, 0, st>>>(sc, s); CK(cudaGetLastError());
+            if (tlb) { s.tl = tlb + 2 * (size_t)tln++; tlname.push_back("shade d" + std::to_string(d)); }
+            k_shade<<<small_grid, 256, 0, ss>>>(sc, s); CK(cudaGetLastError());
+            if (conc) CK(cudaEventRecord(c.evShade[hs], ss));
             tm.end(2);
         }
+        if (conc) CK(cudaStreamWaitEvent(cs, c.evShade[depth % nsets], 0));               // (ss is in order: every depth is shaded)
 
         tm.begin(2);
         const int unswap = (a->flags & B200RT_F_UNSWAP_GB) ? 1 : 0;
         const bool al16 = (H % 16 == 0) && (((uintptr_t)a->result) % 16 == 0);     // every column start is then 16-byte aligned
         const bool al4 = (H % 4 == 0) && (((uintptr_t)a->result) % 4 == 0);
-        if (al16)      k_resolve<16><<<std::min<int>((f.npix / 16 + 255) / 256, small_grid), 256, 0, st>>>(f, accR, accG, accB, a->result, a->aliasing, unswap);
-        else if (al4)  k_resolve<4><<<std::min<int>((f.npix / 4 + 255) / 256, small_grid), 256, 0, st>>>(f, accR, accG, accB, a->result, a->aliasing, unswap);
-        else           k_resolve<1><<<std::min<int>((f.npix + 255) / 256, small_grid), 256, 0, st>>>(f, accR, accG, accB, a->result, a->aliasing, unswap);
+        if (al16)      k_resolve<16><<<std::min<int>((f.npix / 16 + 255) / 256, small_grid), 256, 0, cs>>>(f, accR, accG, accB, a->result, a->aliasing, unswap);
+        else if (al4)  k_resolve<4><<<std::min<int>((f.npix / 4 + 255) / 256, small_grid), 256, 0, cs>>>(f, accR, accG, accB, a->result, a->aliasing, unswap);
+        else           k_resolve<1><<<std::min<int>((f.npix + 255) / 256, small_grid), 256, 0, cs>>>(f, accR, accG, accB, a->result, a->aliasing, unswap);
         CK(cudaGetLastError());
         tm.end(2);
     }
+    if (conc) { CK(cudaEventRecord(c.evJoin, cs)); CK(cudaStreamWaitEvent(st, c.evJoin, 0)); }
     CK(cudaEventRecord(c.done, st)); c.has_done = true;
+    if (tlb) {
+        CK(cudaStreamSynchronize(st));
+        std::vector<unsigned long long> h(2 * (size_t)tln); CK(cudaMemcpy(h.data(), tlb, sizeof(unsigned long long) * h.size(), cudaMemcpyDeviceToHost));
+        unsigned long long t0 = ~0ull; for (int i = 0; i < tln; ++i) t0 = std::min(t0, h[2 * i]);
+        for (int i = 0; i < tln; ++i) fprintf(stderr, "[b200rt timeline] %-16s start %9.1f us  end %9.1f us  dur %8.1f us\n", tlname[i].c_str(), (h[2 * i] - t0) * 1e-3, (h[2 * i + 1] - t0) * 1e-3, (h[2 * i + 1] - h[2 * i]) * 1e-3);
+    }
 
     if (stats) {
         CK(cudaEventRecord(ev1, st));
@@ -856,7 +938,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             for (int d = 0; d <= depth; ++d) {
                 const uint32_t* cd = h.data() + (size_t)ch * ctr_stride + cps * d;
                 if (use_lists) { for (int j = 0; j < L; ++j) out.shadow_traced += cd[4 + j]; } else out.shadow_traced += (uint64_t)cd[3] * (uint64_t)L;
-                if (d == 0) out.primary += cd[0]; else out.bounce += cd[0];
+                if (d == 0) out.primary += cd[0]; else out.bounce += (cd - cps)[3];       // queue of depth d = hit list of depth d-1
                 out.shadow += (uint64_t)cd[3] * (uint64_t)L;
             }
         unsigned long long slow[2] = {0, 0}; CK(cudaMemcpy(slow, c.slow.p, sizeof(slow), cudaMemcpyDeviceToHost));

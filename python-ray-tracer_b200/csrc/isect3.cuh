@@ -45,6 +45,7 @@ struct QueueDev {
     const uint32_t* shidx; size_t shcap; // k_isect3 shadow input: per light the hit records whose Lambert term can be non-zero
     const uint32_t* n_tot;               // k_isect3 shadow: number of hit records (row length of occl)
     unsigned long long* slow;            // diagnostic: thread-level slow-path entries (may be null)
+    unsigned long long* tl;              // diagnostic (B200RT_TIMELINE): [0] first CTA start, [1] last CTA end, globaltimer ns (may be null)
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -80,6 +81,7 @@ struct PivotDev {
     const float*  bounds;                // [2]           max |C|, max r
 };
 
+__device__ __forceinline__ unsigned long long globaltimer_ns() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 __device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
 __device__ __forceinline__ float2 bc(float a) { return make_float2(a, a); }       // FFMA2 broadcast operand (R.F32 / UR.F32)
 __device__ __forceinline__ float fmax3(float a, float b, float c) {
@@ -116,6 +118,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
     constexpr int NO = PIV ? 1 : NR;                          // 2*O operands exist only in the 8-FFMA2 form
     extern __shared__ __align__(16) unsigned char s_raw[];
     IsectSmem& sm = *reinterpret_cast<IsectSmem*>(s_raw);
+    if (q.tl && threadIdx.x == 0) atomicMin(q.tl, globaltimer_ns());
     const bool first = (c0 == 0), last = (c0 + cnt >= sc.Spad);
     const bool lists = ANY && q.shidx != nullptr;             // shadow: per-light lists (else every hit record, identity map)
     const uint32_t n_tot = ANY ? *q.n_tot : 0u;
@@ -354,6 +357,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
         if (g >= ngroups) break;
         run_group(g);
     }
+    if (q.tl && threadIdx.x == 0) atomicMax(q.tl + 1, globaltimer_ns());
     if (q.slow) {
         const uint32_t tot = __reduce_add_sync(0xffffffffu, slow_cnt), tot2 = __reduce_add_sync(0xffffffffu, exact_cnt);
         if (lane == 0 && tot) { atomicAdd(q.slow, (unsigned long long)tot); atomicAdd(q.slow + 1, (unsigned long long)tot2); }
@@ -390,7 +394,8 @@ static inline cudaError_t isect3_upload_resident(const PivotDev& pv, int Spad, c
 // counters.  Rays per thread: 8 for big queues, fewer for small ones (more groups than warps).
 template <int MODE>
 static cudaError_t isect3_launch(const IsectCfg& cfg, const SceneDev& sc, QueueDev q, const PivotDev& pv, size_t max_rays,
-                          uint32_t* work, bool resident, cudaStream_t st) {
+                          uint32_t* work, bool resident, cudaStream_t st, unsigned long long* tlbase = nullptr, int* tlnext = nullptr,
+                          int jb = 0, int je = -1) {                // [jb, je): lights of this call (MODE 2; default all)
     const size_t warps = (size_t)cfg.sm_count * 2 * (kThreads / 32);
     int nr = cfg.force_nr ? cfg.force_nr : (max_rays >= warps * 256 * 4 ? 8 : (max_rays >= warps * 128 * 4 ? 4 : 2));
     if (MODE == 0 && cfg.force_nr0) nr = cfg.force_nr0;         // (measured: 8 rays/thread wins for the 8-FFMA2 form too)
@@ -398,13 +403,13 @@ static cudaError_t isect3_launch(const IsectCfg& cfg, const SceneDev& sc, QueueD
     const int L = sc.L;
     const int chunk = std::min(sc.Spad, kTabCap);
     const int lp = (MODE == 2 && sc.Spad <= kTabCap) ? std::max(1, kTabCap / sc.Spad) : 1;      // light tables beside each other
-    const int nlights = (MODE == 2) ? L : 1;
+    const int jbeg = (MODE == 2) ? jb : 0, jend = (MODE == 2) ? (je < 0 ? L : je) : 1;
     cudaError_t e;
     for (int c0 = 0, k = 0; c0 < sc.Spad; c0 += chunk, ++k) {
         const int cnt = std::min(chunk, sc.Spad - c0);
         q.work = work + (size_t)k * (L + 1);
-        for (int j0 = 0; j0 < nlights; j0 += lp) {
-            const int nj = std::min(lp, nlights - j0);
+        for (int j0 = jbeg; j0 < jend; j0 += lp) {
+            const int nj = std::min(lp, jend - j0);
             if (!resident)
                 for (int jj = 0; jj < nj; ++jj) {
                     const int tj = (MODE == 2) ? j0 + jj : (MODE == 1 ? L : L + 1);
@@ -416,6 +421,7 @@ static cudaError_t isect3_launch(const IsectCfg& cfg, const SceneDev& sc, QueueD
                 const int j = (MODE == 2) ? j0 + jj : L;
                 const int slot = resident ? (MODE == 2 ? j : (MODE == 1 ? 0 : 1)) : jj;
                 const int tb = slot * cnt;
+                if (tlbase) q.tl = tlbase + 2 * (size_t)((*tlnext)++);
                 if (nr == 8)      k_isect3<MODE, 8><<<grid, kThreads, sizeof(IsectSmem), st>>>(sc, q, pv, c0, cnt, j, tb);
                 else if (nr == 4) k_isect3<MODE, 4><<<grid, kThreads, sizeof(IsectSmem), st>>>(sc, q, pv, c0, cnt, j, tb);
                 else              k_isect3<MODE, 2><<<grid, kThreads, sizeof(IsectSmem), st>>>(sc, q, pv, c0, cnt, j, tb);
@@ -430,6 +436,7 @@ static cudaError_t isect3_launch(const IsectCfg& cfg, const SceneDev& sc, QueueD
 cudaError_t shadow_set_attr();
 cudaError_t shadow_upload_resident(const PivotDev& pv, int Spad, int L, cudaStream_t st);
 cudaError_t shadow_launch(const IsectCfg& cfg, const SceneDev& sc, const QueueDev& q, const PivotDev& pv, size_t max_rays,
-                          uint32_t* work, bool resident, cudaStream_t st);
+                          uint32_t* work, bool resident, cudaStream_t st, unsigned long long* tlbase = nullptr, int* tlnext = nullptr,
+                          int jb = 0, int je = -1);
 
 }  // namespace b200rt

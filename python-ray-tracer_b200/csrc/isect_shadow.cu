@@ -15,8 +15,8 @@ cudaError_t shadow_upload_resident(const PivotDev& pv, int Spad, int L, cudaStre
 }
 
 cudaError_t shadow_launch(const IsectCfg& cfg, const SceneDev& sc, const QueueDev& q, const PivotDev& pv, size_t max_rays,
-                          uint32_t* work, bool resident, cudaStream_t st) {
-    return isect3_launch<2>(cfg, sc, q, pv, max_rays, work, resident, st);
+                          uint32_t* work, bool resident, cudaStream_t st, unsigned long long* tlbase, int* tlnext, int jb, int je) {
+    return isect3_launch<2>(cfg, sc, q, pv, max_rays, work, resident, st, tlbase, tlnext, jb, je);
 }
 
 }  // namespace b200rt

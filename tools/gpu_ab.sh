@@ -6,7 +6,7 @@ cp python-ray-tracer_b200/b200rt/libb200rt.so /tmp/orig.so
 for f in tools/ab/*.so; do
   n=$(basename $f .so)
   cp $f python-ray-tracer_b200/b200rt/libb200rt.so; touch python-ray-tracer_b200/b200rt/libb200rt.so
-  timeout 300 python bench.py --workload $WL --steps $ST --warmup 3 --no-cpu > gpurun_out/ab_$n.json 2> gpurun_out/ab_$n.err
+  timeout 300 env B200RT_EMULATE_WORLD=${3:-0} python bench.py --workload $WL --steps $ST --warmup 3 --no-cpu > gpurun_out/ab_$n.json 2> gpurun_out/ab_$n.err
   python - $n <<'PY'
 import json,sys
 n=sys.argv[1]
