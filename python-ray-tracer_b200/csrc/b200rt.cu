@@ -283,8 +283,31 @@ k_intersect(SceneDev sc, QueueDev q) {
     }
 }
 
-// One thread per (table j, sphere pair i): k = r^2 - |C-V_j|^2 (j <= L) or r^2 - |C|^2 (j == L+1), float64 rounded once.
-__global__ void k_pivot(SceneDev sc, float cox, float coy, float coz, float4* tab, float4* piv) {
+// Order of light j's table: spheres by decreasing solid angle seen from the light, ~ r^2 / |C - V_j|^2 — the likelier
+// occluders come first, so most occluded shadow rays are finished after the first pass over a fraction of the spheres
+// (C4: half of all shadow rays are occluded, 90 % of those by one of the first 120-350 spheres of 1024).  Any order
+// gives the same image: a shadow query only asks WHETHER something is hit (trace.py:92-96).  One thread per
+// (light j, sphere s): rank by counting (S is a few thousand at most); padding entries go last.
+__global__ void k_rank(SceneDev sc, int* perm) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = idx / sc.Spad, s = idx - j * sc.Spad;
+    if (j >= sc.L) return;
+    const float4 v = sc.lights[j];
+    auto key = [&](int t) -> float {
+        if (t >= sc.S) return -1.f;
+        const float4 sp = sc.sphB[t];
+        const float ex = sp.x - v.x, ey = sp.y - v.y, ez = sp.z - v.z;
+        return sp.w / fmaxf(ex * ex + ey * ey + ez * ez, 1e-30f);
+    };
+    const float ks = key(s);
+    int rank = 0;
+    for (int t = 0; t < sc.Spad; ++t) { const float kt = key(t); rank += (kt > ks || (kt == ks && t < s)) ? 1 : 0; }
+    perm[(size_t)j * sc.Spad + rank] = s;
+}
+
+// One thread per (table j, pair i of table positions): k = r^2 - |C-V_j|^2 (j <= L) or r^2 - |C|^2 (j == L+1), float64
+// rounded once.  Light tables (j < L) are in k_rank's order, the two closest-hit tables in array order (ids matter there).
+__global__ void k_pivot(SceneDev sc, float cox, float coy, float coz, const int* perm, float4* tab, float4* piv) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     const int npair = sc.Spad / 2;
     const int j = idx / npair, i = idx - j * npair;
@@ -295,7 +318,7 @@ __global__ void k_pivot(SceneDev sc, float cox, float coy, float coz, float4* ta
     float c[2][4];
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
-        const int s = 2 * i + h;
+        const int s = (j < sc.L) ? perm[(size_t)j * sc.Spad + 2 * i + h] : 2 * i + h;
         if (s < sc.S) {
             const float4 sp = sc.sphB[s];
             const double ex = (double)sp.x - v.x, ey = (double)sp.y - v.y, ez = (double)sp.z - v.z;
@@ -596,10 +619,10 @@ struct DevCtx {
     int isect_blocks_per_sm = 2;
     int force_nr = 0, force_nr0 = 0; bool no_pivot = false, no_conc = false;                       // tuning overrides (env B200RT_NR, B200RT_NO_PIVOT)
     Buf sphA, sphB, sphCol, plO, plN, plNu, plCol, lights, cmax;   // packed scene
-    Buf pivTab, pivPos;                                            // pivot tables (k_pivot)
+    Buf pivTab, pivPos, pivPerm;                                   // pivot tables (k_pivot), light-table order (k_rank)
     Buf stage;                                                     // host-scene / host-pixel_loc staging
     Buf rayO[2], rayD[2], hitKey[2];                               // ray queues, double-buffered by depth parity
-    Buf hP[kSets], hN[kSets], occl[kSets], shidx[kSets];           // hit records / shadow state: ring of kSets depths
+    Buf hP[kSets], hN[kSets], occl[kSets], shidx[kSets], shidx2[kSets];   // hit records / shadow state: ring of kSets depths
     Buf acc, ctr, work, slow, tl;
     bool timeline = false;                                        // env B200RT_TIMELINE: per-launch first-start / last-end (globaltimer) to stderr
     // internal streams (see the launch sequence in render_device): the dependent chain at high priority, one stream per
@@ -611,10 +634,10 @@ struct DevCtx {
     Buf hostResult, hostPixelLoc, imgOut;                          // b200rt_render_host / b200rt_to_image_host device copies
     cudaEvent_t done = nullptr; bool has_done = false;
     void release_all() {
-        Buf* all[] = { &sphA, &sphB, &sphCol, &plO, &plN, &plNu, &plCol, &lights, &cmax, &pivTab, &pivPos, &stage, &rayO[0], &rayO[1], &rayD[0], &rayD[1], &hitKey[0], &hitKey[1],
+        Buf* all[] = { &sphA, &sphB, &sphCol, &plO, &plN, &plNu, &plCol, &lights, &cmax, &pivTab, &pivPos, &pivPerm, &stage, &rayO[0], &rayO[1], &rayD[0], &rayD[1], &hitKey[0], &hitKey[1],
                        &acc, &tl, &ctr, &work, &slow, &hostResult, &hostPixelLoc, &imgOut, &batchScene };
         for (Buf* b : all) b->release();
-        for (int i = 0; i < kSets; ++i) { hP[i].release(); hN[i].release(); occl[i].release(); shidx[i].release(); }
+        for (int i = 0; i < kSets; ++i) { hP[i].release(); hN[i].release(); occl[i].release(); shidx[i].release(); shidx2[i].release(); }
         if (done) { cudaEventDestroy(done); done = nullptr; } has_done = false; init = false;
         if (chainStream) {
             cudaStreamDestroy(chainStream); chainStream = nullptr; cudaStreamDestroy(shadeStream);
@@ -755,11 +778,13 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     CK(c.pivTab.ensure(sizeof(float4) * (size_t)(L + 2) * Spad)); CK(c.pivPos.ensure(sizeof(float4) * (L + 1)));
     {
         const int n = (L + 2) * (Spad / 2);
+        CK(c.pivPerm.ensure(sizeof(int) * std::max<size_t>((size_t)L * Spad, 1)));
+        if (L > 0) { k_rank<<<(L * Spad + 255) / 256, 256, 0, st>>>(sc, c.pivPerm.as<int>()); CK(cudaGetLastError()); }
         k_pivot<<<(n + 255) / 256, 256, 0, st>>>(sc, (float)a->cam_origin[0], (float)a->cam_origin[1], (float)a->cam_origin[2],
-                                                 c.pivTab.as<float4>(), c.pivPos.as<float4>());
+                                                 c.pivPerm.as<int>(), c.pivTab.as<float4>(), c.pivPos.as<float4>());
         CK(cudaGetLastError());
     }
-    const PivotDev pv{ c.pivTab.as<float4>(), c.pivPos.as<float4>(), c.cmax.as<float>() };
+    const PivotDev pv{ c.pivTab.as<float4>(), c.pivPos.as<float4>(), c.cmax.as<float>(), c.pivPerm.as<int>() };
     // Constant-memory residency (isect3.cuh): the closest-hit module holds the camera-pivot and origin-free tables,
     // the shadow module one table per light.  When they fit they are uploaded once per frame.
     const bool nofilter = (a->flags & B200RT_F_NO_FILTER) != 0;
@@ -783,7 +808,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     for (int b = 0; b < nsets; ++b) {
         CK(c.hP[b].ensure(sizeof(float4) * cap)); CK(c.hN[b].ensure(sizeof(float4) * cap));
         CK(c.occl[b].ensure(std::max<size_t>(cap * (size_t)L, 1)));
-        if (use_lists) CK(c.shidx[b].ensure(sizeof(uint32_t) * std::max<size_t>(cap * (size_t)L, 1)));
+        if (use_lists) { CK(c.shidx[b].ensure(sizeof(uint32_t) * std::max<size_t>(cap * (size_t)L, 1))); CK(c.shidx2[b].ensure(sizeof(uint32_t) * std::max<size_t>(cap * (size_t)L, 1))); }
     }
     CK(c.acc.ensure(sizeof(float) * 3 * cap));
     // Per-light shadow lists pay off when a query is expensive (many spheres); for tiny scenes the dense [light][hit]
@@ -793,7 +818,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     CK(c.ctr.ensure(sizeof(uint32_t) * (size_t)ctr_stride * nchunks)); CK(c.slow.ensure(2 * sizeof(unsigned long long)));
     CK(cudaMemsetAsync(c.ctr.p, 0, sizeof(uint32_t) * (size_t)ctr_stride * nchunks, st));
     const int nsch = (Spad + kTabCap - 1) / kTabCap;             // sphere chunks of the constant-memory table
-    const size_t work_per_depth = (size_t)2 * nsch * (L + 1);    // closest + shadow
+    const size_t work_per_depth = (size_t)nsch + (size_t)2 * L * kMaxPass;   // closest: per chunk; shadow: per (light, pass) group counter + survivor counter
     const size_t work_n = work_per_depth * (depth + 1) * nchunks;
     CK(c.work.ensure(sizeof(uint32_t) * work_n));
     CK(cudaMemsetAsync(c.work.p, 0, sizeof(uint32_t) * work_n, st));
@@ -869,14 +894,13 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             s.accR = accR; s.accG = accG; s.accB = accB;
             s.n_live = n_live; s.n_hit = cd + 3;
             s.shidx = use_lists ? c.shidx[hs].as<uint32_t>() : nullptr; s.shcap = cap; s.n_sh = cd + 4;
-            q.shidx = s.shidx; q.shcap = cap; q.n_tot = cd + 3;
             s.amb = (float)a->amb; s.lamb = (float)a->lamb; s.weight = wts[d]; s.emit_reflection = d < depth;
 
             tm.begin(0);
             q.n_in = n_live; q.work = cd + 1;
             if (nofilter)                     { if (int rc = launch_intersect<false>(c, sc, q, true, cs)) return rc; }
-            else if (d == 0 && !c.no_pivot)   { const int f0 = tln; CK(isect3_launch<1>(icfg, sc, q, pv, nslots, wk, closest_res, cs, tlb, &tln)); tl_mark("closest<1>", d, f0); }
-            else                              { const int f0 = tln; CK(isect3_launch<0>(icfg, sc, q, pv, nslots, wk, closest_res, cs, tlb, &tln)); tl_mark("closest<0>", d, f0); }
+            else if (d == 0 && !c.no_pivot)   { const int f0 = tln; CK(isect3_launch_closest<1>(icfg, sc, q, pv, nslots, wk, closest_res, cs, tlb, &tln)); tl_mark("closest<1>", d, f0); }
+            else                              { const int f0 = tln; CK(isect3_launch_closest<0>(icfg, sc, q, pv, nslots, wk, closest_res, cs, tlb, &tln)); tl_mark("closest<0>", d, f0); }
             tm.end(0);
             tm.begin(2);
             if (conc && d >= nsets) CK(cudaStreamWaitEvent(cs, c.evShade[hs], 0));        // set hs is free again
@@ -886,18 +910,19 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             tm.end(2);
             if (L > 0) {
                 tm.begin(1);
-                q.n_in = nofilter ? cd + 3 : cd + 4; q.work = cd + 2;        // k_isect3: per-light list lengths n_sh[j]
-                uint32_t* wks = wk + (size_t)nsch * (L + 1);
-                if (nofilter) { if (int rc = launch_intersect<true>(c, sc, q, true, cs)) return rc; }
-                else if (!conc) { const int f0 = tln; CK(shadow_launch(icfg, sc, q, pv, nslots, wks, shadow_res, cs, tlb, &tln)); tl_mark("shadow", d, f0); }
+                if (nofilter) { q.n_in = cd + 3; q.work = cd + 2; if (int rc = launch_intersect<true>(c, sc, q, true, cs)) return rc; }
                 else {
-                    for (int k = 0; k < nls; ++k) CK(cudaStreamWaitEvent(c.lightStream[k], c.evSetup[hs], 0));
+                    ShadowPlan sp{};
+                    sp.list0 = s.shidx; sp.list1 = use_lists ? c.shidx2[hs].as<uint32_t>() : nullptr; sp.cap = cap;
+                    sp.n0 = use_lists ? cd + 4 : cd + 3; sp.n0_stride = use_lists ? 1 : 0;      // per-light list lengths n_sh[j], or the hit count
+                    sp.work = wk + nsch; sp.npass = wk + nsch + (size_t)L * kMaxPass;
+                    if (conc) for (int k = 0; k < nls; ++k) CK(cudaStreamWaitEvent(c.lightStream[k], c.evSetup[hs], 0));
                     for (int j = 0; j < L; ++j) {
                         const int f0 = tln;
-                        CK(shadow_launch(icfg, sc, q, pv, nslots, wks, true, c.lightStream[j % nls], tlb, &tln, j, j + 1));
-                        if (tlb) tlname.push_back("shadow d" + std::to_string(d) + " j" + std::to_string(j)); (void)f0;
+                        CK(shadow_launch_light(icfg, sc, q, pv, nslots, sp, j, shadow_res, conc ? c.lightStream[j % nls] : cs, tlb, &tln));
+                        for (int k = f0; k < tln; ++k) tlname.push_back("shadow d" + std::to_string(d) + " j" + std::to_string(j) + " p" + std::to_string(k - f0));
                     }
-                    for (int k = 0; k < nls; ++k) { CK(cudaEventRecord(c.evLight[k], c.lightStream[k])); CK(cudaStreamWaitEvent(ss, c.evLight[k], 0)); }
+                    if (conc) for (int k = 0; k < nls; ++k) { CK(cudaEventRecord(c.evLight[k], c.lightStream[k])); CK(cudaStreamWaitEvent(ss, c.evLight[k], 0)); }
                 }
                 tm.end(1);
             } else if (conc) CK(cudaStreamWaitEvent(ss, c.evSetup[hs], 0));
@@ -1002,10 +1027,17 @@ B200RT_API int b200rt_render_host(const b200rt_args* a) {
     if (a->x_end - a->x_begin == a->W && world == 1) {
         CK(cudaMemcpyAsync(a->result, d.result, 3 * WH, cudaMemcpyDeviceToHost, st));                     // src/main.py:51
     } else {
-        for (int xs = a->x_begin + srank * sw; xs < a->x_end; xs += sw * world) {                          // each rendered strip
-            const size_t off = (size_t)xs * a->H, len = (size_t)(std::min(a->x_end, xs + sw) - xs) * a->H;
-            for (int ch = 0; ch < 3; ++ch)
-                CK(cudaMemcpyAsync(a->result + ch * WH + off, d.result + ch * WH + off, len, cudaMemcpyDeviceToHost, st));
+        // The rendered strips of one channel are equally spaced byte ranges (sw*H bytes every sw*world*H): one 2-D
+        // copy per channel for the full-width strips, plus the clipped last strip if there is one.
+        const int x0 = a->x_begin + srank * sw, period = sw * world;
+        int nfull = 0, xlast = -1;
+        for (int xs = x0; xs < a->x_end; xs += period) { if (xs + sw <= a->x_end) ++nfull; else xlast = xs; }
+        for (int ch = 0; ch < 3; ++ch) {
+            const size_t off = ch * WH + (size_t)x0 * a->H;
+            if (nfull) CK(cudaMemcpy2DAsync(a->result + off, (size_t)period * a->H, d.result + off, (size_t)period * a->H,
+                                            (size_t)sw * a->H, nfull, cudaMemcpyDeviceToHost, st));
+            if (xlast >= 0) CK(cudaMemcpyAsync(a->result + ch * WH + (size_t)xlast * a->H, d.result + ch * WH + (size_t)xlast * a->H,
+                                               (size_t)(a->x_end - xlast) * a->H, cudaMemcpyDeviceToHost, st));
         }
     }
     CK(cudaStreamSynchronize(st));

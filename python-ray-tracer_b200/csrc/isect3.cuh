@@ -38,12 +38,16 @@ struct QueueDev {
     const float4* rayO; const float4* rayD;
     // shadow input: hit records
     const float4* hP;                    // (biased hit point, slot)
-    const uint32_t* n_in;                // number of rays (closest) or number of hit records (shadow)
+    const uint32_t* n_in;                // number of rays (closest) / entries of in_list or hit records (shadow)
     uint32_t* work;                      // dynamic group counter (zeroed before the launch)
     unsigned long long* hit;             // closest-hit output, queue order: (float bits of t) << 32 | id; pre-set to kNoHit
     uint8_t* occl; size_t ocap;          // shadow output, [light][hit] with row stride ocap; pre-set to 0 (k_isect3 stores only 1s)
-    const uint32_t* shidx; size_t shcap; // k_isect3 shadow input: per light the hit records whose Lambert term can be non-zero
-    const uint32_t* n_tot;               // k_isect3 shadow: number of hit records (row length of occl)
+    const uint32_t* in_list;             // k_isect3 shadow input: hit records to query for this light (null: every hit record, identity map)
+    // k_isect3 shadow passes: a query scans the light's table (spheres sorted by decreasing solid angle seen from the
+    // light) in several launches over consecutive ranges; rays found occluded are done, the others are appended to
+    // out_list (hit-record indices, counter out_n) = the next pass's input.  Null on the last pass.
+    uint32_t* out_list; uint32_t* out_n;
+    int last;                            // this launch covers the end of the sphere array: planes are tested here (set by the launcher)
     unsigned long long* slow;            // diagnostic: thread-level slow-path entries (may be null)
     unsigned long long* tl;              // diagnostic (B200RT_TIMELINE): [0] first CTA start, [1] last CTA end, globaltimer ns (may be null)
 };
@@ -79,6 +83,7 @@ struct PivotDev {
     const float4* tab;                   // [(L+2)][Spad] pair layout; table j < L: light j, j == L: camera, j == L+1: origin-free
     const float4* piv;                   // [(L+1)]       pivot positions (float32)
     const float*  bounds;                // [2]           max |C|, max r
+    const int*    perm;                  // [L][Spad]     light tables only: table position -> sphere index (k_rank), or null
 };
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
@@ -119,11 +124,9 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
     extern __shared__ __align__(16) unsigned char s_raw[];
     IsectSmem& sm = *reinterpret_cast<IsectSmem*>(s_raw);
     if (q.tl && threadIdx.x == 0) atomicMin(q.tl, globaltimer_ns());
-    const bool first = (c0 == 0), last = (c0 + cnt >= sc.Spad);
-    const bool lists = ANY && q.shidx != nullptr;             // shadow: per-light lists (else every hit record, identity map)
-    const uint32_t n_tot = ANY ? *q.n_tot : 0u;
-    const uint32_t n_in = ANY ? (lists ? q.n_in[j] : n_tot) : q.n_in[0];
-    const uint32_t* shl = lists ? q.shidx + (size_t)j * q.shcap : nullptr;    // list entry -> hit record
+    const bool last = q.last != 0;
+    const uint32_t n_in = *q.n_in;
+    const uint32_t* shl = ANY ? q.in_list : nullptr;          // list entry -> hit record
     const uint32_t ngroups = (n_in + GW - 1) / GW;
     const int npair = cnt >> 1;
     const float cmax = pv.bounds[0], rmax = pv.bounds[1];
@@ -136,7 +139,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
     // tb is a kernel parameter so that the table index provably lives in uniform registers (LDCU -> UR operands).
     V3 Vp = mk(0.f, 0.f, 0.f);
     if (PIV) { const float4 v = __ldg(&pv.piv[j]); Vp = mk(v.x, v.y, v.z); }
-    uint32_t* work = q.work + (ANY ? j : 0);
+    uint32_t* work = q.work;
 
     auto run_group = [&](const uint32_t g) {
         // A thread owns NR CONSECUTIVE queue entries (neighbouring pixels): they pass the filter at the same spheres.
@@ -153,9 +156,6 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
             unsigned long long key0 = ANY ? 0ull : kNoHit;
             uint32_t hrec = 0;
             if (ANY && active) hrec = shl ? shl[i] : i;
-            if (ANY && active && !first) {                        // occluded by a sphere of an earlier chunk: done
-                if (q.occl[(size_t)j * q.ocap + hrec]) { key0 = 1ull; active = false; }
-            }
             skt[lane * NR + r] = (uint32_t)(key0 >> 32) | (ANY ? (uint32_t)key0 : 0u); ski[lane * NR + r] = 0xffffffffu;
             if (active) {
                 if (MODE == 2) {
@@ -215,6 +215,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
                 if (idx < qcnt) {
                     const uint32_t item = sq[idx];
                     rl = item & 255u; sid = c0 + (int)(item >> 8);
+                    if (ANY && pv.perm) sid = __ldg(&pv.perm[(size_t)j * sc.Spad + sid]);          // sorted table position -> sphere
                     const uint32_t i = gbase + rl;
                     V3 O, D;                                   // the ray, re-read (bit-identical to the setup above)
                     if (MODE == 2) { const float4 hp = q.hP[shl ? shl[i] : i]; O = mk(hp.x, hp.y, hp.z); D = normalize3(sub3(Vp, O)); }
@@ -317,6 +318,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
         flush();
 
         // ---- planes after the last sphere chunk (trace.py:32-39), then write back ----
+        uint32_t surv = 0;                                     // ANY: this thread's rays that are still unoccluded
 #pragma unroll
         for (int r = 0; r < NR; ++r) {
             const uint32_t i = i0 + r;
@@ -333,7 +335,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
                         occluded = (t > 0.f && t < kTMax);
                     }
                 }
-                if (occluded) q.occl[(size_t)j * q.ocap + hrec] = 1;
+                if (occluded) q.occl[(size_t)j * q.ocap + hrec] = 1; else surv |= 1u << r;
             } else {
                 float best = __uint_as_float((uint32_t)(key >> 32)); int bid = (int)(uint32_t)key;
                 if (last) {
@@ -346,6 +348,18 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
                 }
                 if (bid >= 0) atomicMin(&q.hit[i], ((unsigned long long)__float_as_uint(best) << 32) | (uint32_t)bid);
             }
+        }
+        if (ANY && q.out_list) {                              // survivors -> next pass's list, group order kept
+            const uint32_t n = (uint32_t)__popc(surv);
+            uint32_t x = n;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, d); if ((int)lane >= d) x += y; }
+            uint32_t base = 0;
+            if (lane == 31) base = atomicAdd(q.out_n, x);
+            uint32_t pos = __shfl_sync(0xffffffffu, base, 31) + x - n;
+#pragma unroll
+            for (int r = 0; r < NR; ++r)
+                if ((surv >> r) & 1u) q.out_list[pos++] = shl ? shl[i0 + r] : i0 + r;
         }
         __syncwarp();                                         // keys are re-initialised by the next group's setup
     };
@@ -387,47 +401,88 @@ static inline cudaError_t isect3_upload_resident(const PivotDev& pv, int Spad, c
     return cudaSuccess;
 }
 
-// k_isect3 launches for one query (closest hit of a ray queue, or the shadow query of the hit lists): one launch per
-// (sphere chunk, light).  resident: slot convention of isect3_upload_resident — closest-hit module: slot 0 = camera
-// pivot (MODE 1), slot 1 = origin-free (MODE 0); shadow module: slot j = light j.  Otherwise the tables a launch needs
-// are copied in front of it (as many lights beside each other as fit).  `work` points at nsch*(L+1) zeroed group
-// counters.  Rays per thread: 8 for big queues, fewer for small ones (more groups than warps).
+// Rays per thread: 8 for big queues, fewer for small ones (more groups than warps).
 template <int MODE>
-static cudaError_t isect3_launch(const IsectCfg& cfg, const SceneDev& sc, QueueDev q, const PivotDev& pv, size_t max_rays,
-                          uint32_t* work, bool resident, cudaStream_t st, unsigned long long* tlbase = nullptr, int* tlnext = nullptr,
-                          int jb = 0, int je = -1) {                // [jb, je): lights of this call (MODE 2; default all)
+static cudaError_t isect3_launch_one(const IsectCfg& cfg, const SceneDev& sc, const QueueDev& q, const PivotDev& pv, size_t max_rays,
+                                     int c0, int cnt, int j, int tb, cudaStream_t st) {
     const size_t warps = (size_t)cfg.sm_count * 2 * (kThreads / 32);
     int nr = cfg.force_nr ? cfg.force_nr : (max_rays >= warps * 256 * 4 ? 8 : (max_rays >= warps * 128 * 4 ? 4 : 2));
     if (MODE == 0 && cfg.force_nr0) nr = cfg.force_nr0;         // (measured: 8 rays/thread wins for the 8-FFMA2 form too)
     const int grid = cfg.sm_count * (nr == 8 ? 2 : 3);
-    const int L = sc.L;
-    const int chunk = std::min(sc.Spad, kTabCap);
-    const int lp = (MODE == 2 && sc.Spad <= kTabCap) ? std::max(1, kTabCap / sc.Spad) : 1;      // light tables beside each other
-    const int jbeg = (MODE == 2) ? jb : 0, jend = (MODE == 2) ? (je < 0 ? L : je) : 1;
+    if (nr == 8)      k_isect3<MODE, 8><<<grid, kThreads, sizeof(IsectSmem), st>>>(sc, q, pv, c0, cnt, j, tb);
+    else if (nr == 4) k_isect3<MODE, 4><<<grid, kThreads, sizeof(IsectSmem), st>>>(sc, q, pv, c0, cnt, j, tb);
+    else              k_isect3<MODE, 2><<<grid, kThreads, sizeof(IsectSmem), st>>>(sc, q, pv, c0, cnt, j, tb);
+    return cudaGetLastError();
+}
+
+// Closest hit of a ray queue (MODE 0: origin-free table L+1, MODE 1: camera-pivot table L): one launch per sphere
+// chunk of the constant table; chunks meet in q.hit (atomicMin).  resident (isect3_upload_resident with tabs = {L, L+1}):
+// slot 0 = camera pivot, slot 1 = origin-free; otherwise the chunk's table is copied in front of its launch.
+// `work`: one zeroed group counter per chunk.
+template <int MODE>
+static cudaError_t isect3_launch_closest(const IsectCfg& cfg, const SceneDev& sc, QueueDev q, const PivotDev& pv, size_t max_rays,
+                                         uint32_t* work, bool resident, cudaStream_t st, unsigned long long* tlbase = nullptr, int* tlnext = nullptr) {
+    static_assert(MODE == 0 || MODE == 1, "closest-hit modes");
+    const int L = sc.L, chunk = std::min(sc.Spad, kTabCap), tj = (MODE == 1) ? L : L + 1;
     cudaError_t e;
     for (int c0 = 0, k = 0; c0 < sc.Spad; c0 += chunk, ++k) {
         const int cnt = std::min(chunk, sc.Spad - c0);
-        q.work = work + (size_t)k * (L + 1);
-        for (int j0 = jbeg; j0 < jend; j0 += lp) {
-            const int nj = std::min(lp, jend - j0);
-            if (!resident)
-                for (int jj = 0; jj < nj; ++jj) {
-                    const int tj = (MODE == 2) ? j0 + jj : (MODE == 1 ? L : L + 1);
-                    e = cudaMemcpyToSymbolAsync(c_tab, pv.tab + (size_t)tj * sc.Spad + c0, sizeof(float4) * cnt,
-                                                sizeof(float4) * (size_t)jj * cnt, cudaMemcpyDeviceToDevice, st);
-                    if (e != cudaSuccess) return e;
-                }
-            for (int jj = 0; jj < nj; ++jj) {
-                const int j = (MODE == 2) ? j0 + jj : L;
-                const int slot = resident ? (MODE == 2 ? j : (MODE == 1 ? 0 : 1)) : jj;
-                const int tb = slot * cnt;
-                if (tlbase) q.tl = tlbase + 2 * (size_t)((*tlnext)++);
-                if (nr == 8)      k_isect3<MODE, 8><<<grid, kThreads, sizeof(IsectSmem), st>>>(sc, q, pv, c0, cnt, j, tb);
-                else if (nr == 4) k_isect3<MODE, 4><<<grid, kThreads, sizeof(IsectSmem), st>>>(sc, q, pv, c0, cnt, j, tb);
-                else              k_isect3<MODE, 2><<<grid, kThreads, sizeof(IsectSmem), st>>>(sc, q, pv, c0, cnt, j, tb);
-                if ((e = cudaGetLastError()) != cudaSuccess) return e;
-            }
-        }
+        if (!resident && (e = cudaMemcpyToSymbolAsync(c_tab, pv.tab + (size_t)tj * sc.Spad + c0, sizeof(float4) * cnt, 0,
+                                                      cudaMemcpyDeviceToDevice, st)) != cudaSuccess) return e;
+        q.work = work + k; q.last = (c0 + cnt >= sc.Spad) ? 1 : 0;
+        if (tlbase) q.tl = tlbase + 2 * (size_t)((*tlnext)++);
+        if ((e = isect3_launch_one<MODE>(cfg, sc, q, pv, max_rays, c0, cnt, L, resident ? (MODE == 1 ? 0 : sc.Spad) : 0, st)) != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
+// ---- shadow queries: passes over the light's sorted table with compaction of the survivors ----
+constexpr int kMaxPass = 32;
+constexpr int kPass0 = 128, kPass1 = 256;          // first two ranges; the rest in chunks of the constant table
+
+struct ShadowPlan {                                  // one depth's shadow state (device pointers)
+    uint32_t* list0; uint32_t* list1; size_t cap;    // [L][cap] k_setup's lists (null: dense layout, every hit record) and the second buffer
+    const uint32_t* n0; int n0_stride;               // list lengths from k_setup: n0[j * n0_stride]  (dense: the hit count, stride 0)
+    uint32_t* npass; uint32_t* work;                 // [L][kMaxPass] zeroed: survivor counters, group counters
+};
+
+// Sphere ranges [c0, c0+cnt) of the passes.  Small scenes: one pass.  (resident or not, a pass fits the constant table.)
+static inline int shadow_passes(int Spad, int (*ranges)[2]) {
+    int n = 0, c0 = 0;
+    const int first[2] = { kPass0, kPass1 };
+    if (Spad > 2 * kPass0)
+        for (int k = 0; k < 2 && Spad - c0 > first[k] + kPass0; ++k) { ranges[n][0] = c0; ranges[n][1] = first[k]; c0 += first[k]; ++n; }
+    while (c0 < Spad) {
+        if (n == kMaxPass) return -1;
+        const int cnt = std::min(kTabCap, Spad - c0);
+        ranges[n][0] = c0; ranges[n][1] = cnt; c0 += cnt; ++n;
+    }
+    return n;
+}
+
+// Light j's shadow query (MODE 2).  resident: slot j of this module's c_tab holds the whole sorted table of light j.
+template <int MODE>
+static cudaError_t isect3_launch_shadow_light(const IsectCfg& cfg, const SceneDev& sc, QueueDev q, const PivotDev& pv, size_t max_rays,
+                                              const ShadowPlan& sp, int j, bool resident, cudaStream_t st,
+                                              unsigned long long* tlbase = nullptr, int* tlnext = nullptr) {
+    static_assert(MODE == 2, "shadow mode");
+    int ranges[kMaxPass][2];
+    const int np = shadow_passes(sc.Spad, ranges);
+    if (np < 0 || (np > 1 && !sp.list0)) return cudaErrorInvalidValue;
+    const uint32_t* in = sp.list0 ? sp.list0 + (size_t)j * sp.cap : nullptr;
+    const uint32_t* n_in = sp.n0 + (size_t)j * sp.n0_stride;
+    cudaError_t e;
+    for (int p = 0; p < np; ++p) {
+        const int c0 = ranges[p][0], cnt = ranges[p][1];
+        const bool lastp = (p == np - 1);
+        q.in_list = in; q.n_in = n_in; q.work = sp.work + (size_t)j * kMaxPass + p; q.last = lastp ? 1 : 0;
+        q.out_list = lastp ? nullptr : ((p & 1) ? sp.list0 : sp.list1) + (size_t)j * sp.cap;
+        q.out_n = lastp ? nullptr : sp.npass + (size_t)j * kMaxPass + p;
+        if (!resident && (e = cudaMemcpyToSymbolAsync(c_tab, pv.tab + (size_t)j * sc.Spad + c0, sizeof(float4) * cnt, 0,
+                                                      cudaMemcpyDeviceToDevice, st)) != cudaSuccess) return e;
+        if (tlbase) q.tl = tlbase + 2 * (size_t)((*tlnext)++);
+        if ((e = isect3_launch_one<MODE>(cfg, sc, q, pv, max_rays, c0, cnt, j, resident ? j * sc.Spad + c0 : 0, st)) != cudaSuccess) return e;
+        in = q.out_list; n_in = q.out_n;
     }
     return cudaSuccess;
 }
@@ -435,8 +490,8 @@ static cudaError_t isect3_launch(const IsectCfg& cfg, const SceneDev& sc, QueueD
 // The shadow mode lives in isect_shadow.cu (its own module / constant bank):
 cudaError_t shadow_set_attr();
 cudaError_t shadow_upload_resident(const PivotDev& pv, int Spad, int L, cudaStream_t st);
-cudaError_t shadow_launch(const IsectCfg& cfg, const SceneDev& sc, const QueueDev& q, const PivotDev& pv, size_t max_rays,
-                          uint32_t* work, bool resident, cudaStream_t st, unsigned long long* tlbase = nullptr, int* tlnext = nullptr,
-                          int jb = 0, int je = -1);
+cudaError_t shadow_launch_light(const IsectCfg& cfg, const SceneDev& sc, const QueueDev& q, const PivotDev& pv, size_t max_rays,
+                                const ShadowPlan& sp, int j, bool resident, cudaStream_t st,
+                                unsigned long long* tlbase = nullptr, int* tlnext = nullptr);
 
 }  // namespace b200rt

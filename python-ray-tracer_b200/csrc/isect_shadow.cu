@@ -14,9 +14,9 @@ cudaError_t shadow_upload_resident(const PivotDev& pv, int Spad, int L, cudaStre
     return isect3_upload_resident(pv, Spad, tabs.data(), L, st);
 }
 
-cudaError_t shadow_launch(const IsectCfg& cfg, const SceneDev& sc, const QueueDev& q, const PivotDev& pv, size_t max_rays,
-                          uint32_t* work, bool resident, cudaStream_t st, unsigned long long* tlbase, int* tlnext, int jb, int je) {
-    return isect3_launch<2>(cfg, sc, q, pv, max_rays, work, resident, st, tlbase, tlnext, jb, je);
+cudaError_t shadow_launch_light(const IsectCfg& cfg, const SceneDev& sc, const QueueDev& q, const PivotDev& pv, size_t max_rays,
+                                const ShadowPlan& sp, int j, bool resident, cudaStream_t st, unsigned long long* tlbase, int* tlnext) {
+    return isect3_launch_shadow_light<2>(cfg, sc, q, pv, max_rays, sp, j, resident, st, tlbase, tlnext);
 }
 
 }  // namespace b200rt
