@@ -355,11 +355,13 @@ __global__ void k_setup(SceneDev sc, ShadeDev s) {
     const uint32_t n = *s.n_live;
     for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {
         const uint32_t i = base + threadIdx.x;
-        bool hit = false; float4 o, d; float t = 0.f; int id = -1;
-        if (i < n) { const unsigned long long key = s.hit[i]; id = (int)(uint32_t)key; t = __uint_as_float((uint32_t)(key >> 32)); hit = id >= 0; }
+        bool hit = false; float4 o = make_float4(0, 0, 0, 0), d = o; float t = 0.f; int id = -1;
+        if (i < n) {                                 // the three loads go out together (the ray is read even if it missed)
+            const unsigned long long key = s.hit[i]; o = s.rayO[i]; d = s.rayD[i];
+            id = (int)(uint32_t)key; t = __uint_as_float((uint32_t)(key >> 32)); hit = id >= 0;
+        }
         V3 Pb = mk(0, 0, 0), N = mk(0, 0, 0);
         if (hit) {
-            o = s.rayO[i]; d = s.rayD[i];
             const V3 P = madd3(mk(o.x, o.y, o.z), t, mk(d.x, d.y, d.z));            // trace.py:60
             if (id < sc.S) { const float4 c = __ldg(&sc.sphB[id]); N = normalize3(sub3(P, mk(c.x, c.y, c.z))); }   // common.py:94-101
             else           { const float4 nu = __ldg(&sc.plNu[id - sc.S]); N = mk(nu.x, nu.y, nu.z); }             // common.py:104-110
@@ -410,28 +412,35 @@ __global__ void k_setup(SceneDev sc, ShadeDev s) {
 
 // trace.py:77,86-102 and the accumulate of trace.py:131: RGB_trace = amb*col + sum_j [visible_j && k_j>0] k_j*col,
 // acc[slot] += weight * RGB_trace.  (The reflection ray of trace.py:104-110 was queued by k_setup.)
-__global__ void k_shade(SceneDev sc, ShadeDev s) {
+__global__ void __launch_bounds__(256) k_shade(SceneDev sc, ShadeDev s) {
     if (s.tl && threadIdx.x == 0) atomicMin(s.tl, globaltimer_ns());
     const uint32_t n = *s.n_hit;
     for (uint32_t h = blockIdx.x * blockDim.x + threadIdx.x; h < n; h += gridDim.x * blockDim.x) {
+        // Latency-bound kernel: every load whose address is known is issued before the arithmetic — the accumulators,
+        // and the occlusion flags of the first 8 lights as one bit mask (a flag that was never written by a shadow
+        // query is only looked at when k > 0 fails first, so reading it early is harmless).
         const float4 p = s.hP[h], nn = s.hN[h];
+        const uint32_t slot = __float_as_uint(p.w);
+        const float ar = s.accR[slot], ag = s.accG[slot], ab = s.accB[slot];
+        uint32_t occ8 = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) if (j < sc.L && s.occl[(size_t)j * s.ocap + h]) occ8 |= 1u << j;
         const V3 Pb = mk(p.x, p.y, p.z), N = mk(nn.x, nn.y, nn.z);
         const int id = __float_as_int(nn.w);
-        const uint32_t slot = __float_as_uint(p.w);
         const float4 col = (id < sc.S) ? __ldg(&sc.sphCol[id]) : __ldg(&sc.plCol[id - sc.S]);
         float r = __fmul_rn(s.amb, col.x), g = __fmul_rn(s.amb, col.y), b = __fmul_rn(s.amb, col.z);   // trace.py:77
         for (int j = 0; j < sc.L; ++j) {                                                               // trace.py:86
-            if (!s.shidx && s.occl[(size_t)j * s.ocap + h]) continue;                                  // :95-96 (dense layout)
+            const bool occluded = j < 8 ? ((occ8 >> j) & 1u) != 0u : s.occl[(size_t)j * s.ocap + h] != 0;     // :95-96
+            if (occluded) continue;
             const float4 l = __ldg(&sc.lights[j]);
             const V3 Lv = normalize3(sub3(mk(l.x, l.y, l.z), Pb));                                     // :89
             const float k = __fmul_rn(s.lamb, dot3(Lv, N));                                            // :99
-            if (!(k > 0.f)) continue;                                                                  // :101 (lists: no shadow query was made)
-            if (s.shidx && s.occl[(size_t)j * s.ocap + h]) continue;                                   // :95-96
+            if (!(k > 0.f)) continue;                                                                  // :101
             r = fmaf(k, col.x, r); g = fmaf(k, col.y, g); b = fmaf(k, col.z, b);                       // :102
         }
-        s.accR[slot] = fmaf(s.weight, r, s.accR[slot]);                                                // :131
-        s.accG[slot] = fmaf(s.weight, g, s.accG[slot]);
-        s.accB[slot] = fmaf(s.weight, b, s.accB[slot]);
+        s.accR[slot] = fmaf(s.weight, r, ar);                                                          // :131
+        s.accG[slot] = fmaf(s.weight, g, ag);
+        s.accB[slot] = fmaf(s.weight, b, ab);
     }
     if (s.tl && threadIdx.x == 0) atomicMax(s.tl + 1, globaltimer_ns());
 }
@@ -624,6 +633,7 @@ struct DevCtx {
     Buf rayO[2], rayD[2], hitKey[2];                               // ray queues, double-buffered by depth parity
     Buf hP[kSets], hN[kSets], occl[kSets], shidx[kSets], shidx2[kSets];   // hit records / shadow state: ring of kSets depths
     Buf acc, ctr, work, slow, tl;
+    int npre = 2, pre[6] = {128, 256, 0, 0, 0, 0};                  // leading shadow passes (env B200RT_PASSES=a,b,...; multiples of 8)
     bool timeline = false;                                        // env B200RT_TIMELINE: per-launch first-start / last-end (globaltimer) to stderr
     // internal streams (see the launch sequence in render_device): the dependent chain at high priority, one stream per
     // light (up to kSide) for the shadow queries, one for the shading
@@ -714,6 +724,10 @@ int init_ctx(DevCtx& c, int device) {
     { const char* e = getenv("B200RT_NO_PIVOT"); c.no_pivot = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_NO_CONCURRENCY"); c.no_conc = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_TIMELINE"); c.timeline = e && atoi(e) != 0; }
+    if (const char* e = getenv("B200RT_PASSES")) {
+        c.npre = 0;
+        for (const char* p = e; *p && c.npre < 6; ) { const int v = atoi(p) & ~7; if (v >= 8) c.pre[c.npre++] = v; while (*p && *p != ',') ++p; if (*p == ',') ++p; }
+    }
     CK(cudaEventCreateWithFlags(&c.done, cudaEventDisableTiming));
     {
         int lo = 0, hi = 0; CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));         // hi = greatest priority (numerically lowest)
@@ -791,7 +805,8 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     const bool closest_res = !nofilter && 2 * Spad <= kTabCap, shadow_res = !nofilter && L > 0 && L * Spad <= kTabCap;
     if (closest_res) { const int tabs[2] = { L, L + 1 }; CK(isect3_upload_resident(pv, Spad, tabs, 2, st)); }
     if (shadow_res) CK(shadow_upload_resident(pv, Spad, L, st));
-    const IsectCfg icfg{ c.sm_count, c.force_nr, c.force_nr0 };
+    IsectCfg icfg{ c.sm_count, c.force_nr, c.force_nr0, c.npre, {0, 0, 0, 0, 0, 0} };
+    for (int k = 0; k < c.npre; ++k) icfg.pre[k] = c.pre[k];
 
     // ---- chunking: whole columns, <= max_paths slots per chunk ----
     const size_t per_col = (size_t)ns * H;

@@ -381,7 +381,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
 // ------------------------------------------------------------------------------------------------
 // Host side: table residency and launches (per translation unit = per constant bank)
 // ------------------------------------------------------------------------------------------------
-struct IsectCfg { int sm_count; int force_nr; int force_nr0; };
+struct IsectCfg { int sm_count; int force_nr; int force_nr0; int npre; int pre[6]; };   // pre: sizes of the leading shadow passes
 
 template <int MODE> static cudaError_t isect3_set_attr() {
     cudaError_t e;
@@ -438,7 +438,6 @@ static cudaError_t isect3_launch_closest(const IsectCfg& cfg, const SceneDev& sc
 
 // ---- shadow queries: passes over the light's sorted table with compaction of the survivors ----
 constexpr int kMaxPass = 32;
-constexpr int kPass0 = 128, kPass1 = 256;          // first two ranges; the rest in chunks of the constant table
 
 struct ShadowPlan {                                  // one depth's shadow state (device pointers)
     uint32_t* list0; uint32_t* list1; size_t cap;    // [L][cap] k_setup's lists (null: dense layout, every hit record) and the second buffer
@@ -447,11 +446,9 @@ struct ShadowPlan {                                  // one depth's shadow state
 };
 
 // Sphere ranges [c0, c0+cnt) of the passes.  Small scenes: one pass.  (resident or not, a pass fits the constant table.)
-static inline int shadow_passes(int Spad, int (*ranges)[2]) {
+static inline int shadow_passes(const IsectCfg& cfg, int Spad, int (*ranges)[2]) {
     int n = 0, c0 = 0;
-    const int first[2] = { kPass0, kPass1 };
-    if (Spad > 2 * kPass0)
-        for (int k = 0; k < 2 && Spad - c0 > first[k] + kPass0; ++k) { ranges[n][0] = c0; ranges[n][1] = first[k]; c0 += first[k]; ++n; }
+    for (int k = 0; k < cfg.npre && Spad - c0 >= 2 * cfg.pre[k]; ++k) { ranges[n][0] = c0; ranges[n][1] = cfg.pre[k]; c0 += cfg.pre[k]; ++n; }
     while (c0 < Spad) {
         if (n == kMaxPass) return -1;
         const int cnt = std::min(kTabCap, Spad - c0);
@@ -467,7 +464,7 @@ static cudaError_t isect3_launch_shadow_light(const IsectCfg& cfg, const SceneDe
                                               unsigned long long* tlbase = nullptr, int* tlnext = nullptr) {
     static_assert(MODE == 2, "shadow mode");
     int ranges[kMaxPass][2];
-    const int np = shadow_passes(sc.Spad, ranges);
+    const int np = shadow_passes(cfg, sc.Spad, ranges);
     if (np < 0 || (np > 1 && !sp.list0)) return cudaErrorInvalidValue;
     const uint32_t* in = sp.list0 ? sp.list0 + (size_t)j * sp.cap : nullptr;
     const uint32_t* n_in = sp.n0 + (size_t)j * sp.n0_stride;
