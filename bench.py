@@ -282,6 +282,11 @@ def run_ours(args, w):
                          "probe_sm_mhz": probe["sm_mhz"], "frac_of_measured_ffma": ach_tf / max(probe["ffma_tflops"], 1e-9),
                          "algorithmic_flops_per_ray": fpr, "kernel_ms_per_frame": isect_ms, "kernel_ms_closest": st2["ms_closest"], "kernel_ms_shadow": st2["ms_shadow"], "other_ms": st2["ms_other"], "kernel_share_of_frame": isect_ms / st2["ms_total"],
                          "slow_path_entries_per_ray": st2["slow_path"] / max(1, rays_this_rank), "exact_tests_per_ray": st2["exact_tests"] / max(1, rays_this_rank), "shadow_queries_traced_fraction": st2["shadow_traced"] / max(1, st2["shadow"]),
+                         # work actually executed (the early-out shadow passes and the culled shadow queries skip tests):
+                         "executed_sphere_tests": st2["tests_pivot"] + st2["tests_general"], "canonical_sphere_tests": rays_this_rank * S,
+                         "executed_tflops": (8.0 * st2["tests_pivot"] + 16.0 * st2["tests_general"]) / (isect_ms * 1e-3) / 1e12,
+                         "executed_frac": (8.0 * st2["tests_pivot"] + 16.0 * st2["tests_general"]) / (isect_ms * 1e-3) / 1e12 / nominal_tf,
+                         "frac_note": "frac = canonical brute-force FLOPs (16 per ray-sphere test, SURVEY 8d) / kernel time / peak; it exceeds the FMA-pipe utilisation because the kernel executes 8 FLOP per test in the pivot form and skips tests that cannot change the image (executed_frac = FLOPs actually issued / peak)",
                          "framebuffer_write_gbs": 3.0 * W * H / world / (st2["ms_total"] * 1e-3) / 1e9,
                          "hbm_peak_gbs": peaks.get("hbm_gbs")},
         }

@@ -66,6 +66,8 @@ typedef struct b200rt_stats {
     uint64_t exact_tests; /* exact (robust) ray-sphere tests run on filter candidates (diagnostic)  */
     uint64_t shadow_traced; /* shadow queries actually traced: (hit, light) pairs with lamb*(Lv.N) > 0; the others are
                                queries whose answer the reference computes and then ignores (trace.py:92-102)     */
+    uint64_t tests_pivot;   /* (ray, sphere) filter tests EXECUTED in the 4-FMA pivot form (primary + shadow passes; padding included) */
+    uint64_t tests_general; /* ... in the 8-FMA origin-free form (bounce rays).  Canonical brute force would be rays * S.          */
     float    kernel_ms[4]; /* device time: [0] total, [1] closest-hit kernels, [2] shadow kernels, [3] everything else */
 } b200rt_stats;
 

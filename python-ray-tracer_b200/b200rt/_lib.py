@@ -13,12 +13,12 @@ class Grid(C.Structure):
 
 
 class Stats(C.Structure):
-    _fields_ = [("primary", C.c_uint64), ("shadow", C.c_uint64), ("bounce", C.c_uint64), ("slow_path", C.c_uint64), ("exact_tests", C.c_uint64), ("shadow_traced", C.c_uint64),
+    _fields_ = [("primary", C.c_uint64), ("shadow", C.c_uint64), ("bounce", C.c_uint64), ("slow_path", C.c_uint64), ("exact_tests", C.c_uint64), ("shadow_traced", C.c_uint64), ("tests_pivot", C.c_uint64), ("tests_general", C.c_uint64),
                 ("kernel_ms", C.c_float * 4)]
 
     def as_dict(self):
         return dict(primary=int(self.primary), shadow=int(self.shadow), bounce=int(self.bounce),
-                    rays=int(self.primary + self.shadow + self.bounce), slow_path=int(self.slow_path), exact_tests=int(self.exact_tests), shadow_traced=int(self.shadow_traced),
+                    rays=int(self.primary + self.shadow + self.bounce), slow_path=int(self.slow_path), exact_tests=int(self.exact_tests), shadow_traced=int(self.shadow_traced), tests_pivot=int(self.tests_pivot), tests_general=int(self.tests_general),
                     ms_total=float(self.kernel_ms[0]), ms_closest=float(self.kernel_ms[1]),
                     ms_shadow=float(self.kernel_ms[2]), ms_other=float(self.kernel_ms[3]))
 

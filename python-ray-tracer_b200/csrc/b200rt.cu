@@ -981,6 +981,21 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
                 if (d == 0) out.primary += cd[0]; else out.bounce += (cd - cps)[3];       // queue of depth d = hit list of depth d-1
                 out.shadow += (uint64_t)cd[3] * (uint64_t)L;
             }
+        // executed filter tests: closest hit = queue length x Spad; shadow = sum over passes of (pass input length x pass range)
+        if (!nofilter) {
+            std::vector<uint32_t> hw(work_n); CK(cudaMemcpy(hw.data(), c.work.p, sizeof(uint32_t) * work_n, cudaMemcpyDeviceToHost));
+            int ranges[kMaxPass][2]; const int np = shadow_passes(icfg, Spad, ranges);
+            for (int ch = 0; ch < nchunks; ++ch)
+                for (int d = 0; d <= depth; ++d) {
+                    const uint32_t* cd = h.data() + (size_t)ch * ctr_stride + cps * d;
+                    const uint64_t nq = d == 0 ? cd[0] : (cd - cps)[3];
+                    if (d == 0 && !c.no_pivot) out.tests_pivot += nq * (uint64_t)Spad; else out.tests_general += nq * (uint64_t)Spad;
+                    const uint32_t* npass = hw.data() + ((size_t)ch * (depth + 1) + d) * work_per_depth + nsch + (size_t)L * kMaxPass;
+                    for (int j = 0; j < L; ++j)
+                        for (int p = 0; p < np; ++p)
+                            out.tests_pivot += (uint64_t)(p == 0 ? (use_lists ? cd[4 + j] : cd[3]) : npass[(size_t)j * kMaxPass + p - 1]) * (uint64_t)ranges[p][1];
+                }
+        }
         unsigned long long slow[2] = {0, 0}; CK(cudaMemcpy(slow, c.slow.p, sizeof(slow), cudaMemcpyDeviceToHost));
         out.slow_path = slow[0]; out.exact_tests = slow[1];
         CK(cudaEventElapsedTime(&out.kernel_ms[0], ev0, ev1));
