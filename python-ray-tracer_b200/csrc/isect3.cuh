@@ -105,15 +105,19 @@ __device__ __forceinline__ float fmax3(float a, float b, float c) {
 // (float bits of t << 32 | sphere id) — min t, and on equal t the lowest index, which is the reference's tie-break
 // (first object wins, trace.py:26; planes have ids >= S and so lose ties against spheres, trace.py:36).
 constexpr int KP = 4;                    // sphere pairs per scan step (8 spheres)
-constexpr int kQCap = 1024;              // candidate queue entries per warp
+constexpr int kQCap = 768;               // candidate queue entries per warp
 constexpr int kQFlush = kQCap - 32 * 16; // flush before an append (<= 16 per lane) could overflow
 constexpr unsigned long long kNoHit = kNoHitKey;                                                 // (999.0f, id -1)
 
-struct IsectSmem {
-    uint32_t q[kThreads / 32][kQCap];
-    uint32_t kt[kThreads / 32][32 * 8];                // per ray of the warp's group: float bits of the closest t / occlusion flag
-    uint32_t ki[kThreads / 32][32 * 8];                // ... and the id of the closest object
+template <int NR> struct IsectWarpSmem {               // per warp (no CTA-level cooperation anywhere in k_isect3)
+    float4 d[32 * NR];                                 // per ray of the group: D.xyz, -V.D (or -O.D)
+    float4 o[32 * NR];                                 // MODE 0: 2*O.xyz, -thr   MODE 2: O.xyz, hit-record index (bits)
+    float thr[32 * NR];                                // pivot modes: the ray's filter threshold
+    uint32_t kt[32 * NR];                              // float bits of the closest t / occlusion flag
+    uint32_t ki[32 * NR];                              // ... and the id of the closest object
+    uint32_t q[kQCap];                                 // candidate queue
 };
+template <int NR> struct IsectSmem { IsectWarpSmem<NR> w[kThreads / 32]; };   // NR = 8: 14 KB per warp, 112 KB per CTA, 2 CTAs per SM
 
 template <int MODE, int NR>
 __global__ void __launch_bounds__(kThreads, NR == 8 ? 2 : 3)
@@ -122,7 +126,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
     constexpr int GW = 32 * NR;                               // rays per warp group
     constexpr int NO = PIV ? 1 : NR;                          // 2*O operands exist only in the 8-FFMA2 form
     extern __shared__ __align__(16) unsigned char s_raw[];
-    IsectSmem& sm = *reinterpret_cast<IsectSmem*>(s_raw);
+    IsectSmem<NR>& sm = *reinterpret_cast<IsectSmem<NR>*>(s_raw);
     if (q.tl && threadIdx.x == 0) atomicMin(q.tl, globaltimer_ns());
     const bool last = q.last != 0;
     const uint32_t n_in = *q.n_in;
@@ -132,8 +136,9 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
     const float cmax = pv.bounds[0], rmax = pv.bounds[1];
     const float kInf = __int_as_float(0x7f800000);
     const uint32_t lane = lane_id(), wid = threadIdx.x >> 5;
-    uint32_t* sq = sm.q[wid];
-    uint32_t* skt = sm.kt[wid]; uint32_t* ski = sm.ki[wid];
+    IsectWarpSmem<NR>& ws = sm.w[wid];
+    uint32_t* sq = ws.q;
+    uint32_t* skt = ws.kt; uint32_t* ski = ws.ki;
     uint32_t slow_cnt = 0, exact_cnt = 0;
     // j: pivot of this launch (light index for ANY, camera = L for MODE 1); its table is c_tab[tb + 2*pair + {0,1}].
     // tb is a kernel parameter so that the table index provably lives in uniform registers (LDCU -> UR operands).
@@ -142,23 +147,22 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
     uint32_t* work = q.work;
 
     auto run_group = [&](const uint32_t g) {
-        // A thread owns NR CONSECUTIVE queue entries (neighbouring pixels): they pass the filter at the same spheres.
-        const uint32_t gbase = g * (uint32_t)GW, i0 = gbase + lane * NR;
+        const uint32_t gbase = g * (uint32_t)GW;
 
-        // ---- per-ray constants (32-bit registers, broadcast operands of FFMA2) ----
-        float dx[NR], dy[NR], dz[NR], nod[NR], o2x[NO], o2y[NO], o2z[NO], nthr[NO], thr[PIV ? NR : 1];
-#pragma unroll
-        for (int r = 0; r < NR; ++r) {
-            const uint32_t i = i0 + r;
-            bool active = i < n_in;
+        // ---- per-ray constants.  Computed ray by ray by ONE copy of the code (iteration k: ray k*32 + lane of the
+        // group) and staged in shared memory: unrolled over the thread's rays this prologue was a third of the
+        // kernel's instructions and its instruction-cache misses showed in short launches.  The staged copy also
+        // serves the exact tests and the write-back, which therefore read no ray data from global memory. ----
+#pragma unroll 1
+        for (int k = 0; k < NR; ++k) {
+            const uint32_t rl = (uint32_t)k * 32u + lane, i = gbase + rl;
+            const bool active = i < n_in;
             V3 O = mk(0.f, 0.f, 0.f), D = mk(0.f, 0.f, 0.f);
             float th = kInf, no = 0.f;
-            unsigned long long key0 = ANY ? 0ull : kNoHit;
             uint32_t hrec = 0;
-            if (ANY && active) hrec = shl ? shl[i] : i;
-            skt[lane * NR + r] = (uint32_t)(key0 >> 32) | (ANY ? (uint32_t)key0 : 0u); ski[lane * NR + r] = 0xffffffffu;
             if (active) {
                 if (MODE == 2) {
+                    hrec = shl ? shl[i] : i;
                     const float4 p = q.hP[hrec];
                     O = mk(p.x, p.y, p.z);
                     const V3 d = sub3(Vp, O);                                   // common.py:84-91
@@ -178,11 +182,22 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
                     else           { th = oo - margin;   no = -dot3(O, D); }
                 }
             }
-            dx[r] = D.x; dy[r] = D.y; dz[r] = D.z; nod[r] = no;
+            ws.d[rl] = make_float4(D.x, D.y, D.z, no);
             // MODE 0: the per-ray threshold is folded into q (q' = q - thr, one more FFMA2): candidates are q' >= 0
             // (an inactive ray has thr = +inf, so its q' is -inf and never qualifies).
-            if (!PIV) { o2x[r] = 2.f * O.x; o2y[r] = 2.f * O.y; o2z[r] = 2.f * O.z; nthr[r] = -th; }
-            else      thr[PIV ? r : 0] = th;
+            if (MODE == 0) ws.o[rl] = make_float4(2.f * O.x, 2.f * O.y, 2.f * O.z, -th);
+            if (MODE == 2) ws.o[rl] = make_float4(O.x, O.y, O.z, __uint_as_float(hrec));
+            if (PIV) ws.thr[rl] = th;
+            skt[rl] = ANY ? 0u : (uint32_t)(kNoHit >> 32); ski[rl] = 0xffffffffu;
+        }
+        // the thread's rays r = 0..NR-1 are rays r*32 + lane (32-bit registers, broadcast operands of FFMA2)
+        float dx[NR], dy[NR], dz[NR], nod[NR], o2x[NO], o2y[NO], o2z[NO], nthr[NO], thr[PIV ? NR : 1];
+#pragma unroll
+        for (int r = 0; r < NR; ++r) {
+            const float4 d = ws.d[r * 32 + lane];
+            dx[r] = d.x; dy[r] = d.y; dz[r] = d.z; nod[r] = d.w;
+            if (!PIV) { const float4 o = ws.o[r * 32 + lane]; o2x[PIV ? 0 : r] = o.x; o2y[PIV ? 0 : r] = o.y; o2z[PIV ? 0 : r] = o.z; nthr[PIV ? 0 : r] = o.w; }
+            else      thr[PIV ? r : 0] = ws.thr[r * 32 + lane];
         }
         float thr_t = 0.f;                                    // one scan threshold per thread: the loosest of its rays
         if (PIV) {
@@ -216,13 +231,10 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
                     const uint32_t item = sq[idx];
                     rl = item & 255u; sid = c0 + (int)(item >> 8);
                     if (ANY && pv.perm) sid = __ldg(&pv.perm[(size_t)j * sc.Spad + sid]);          // sorted table position -> sphere
-                    const uint32_t i = gbase + rl;
-                    V3 O, D;                                   // the ray, re-read (bit-identical to the setup above)
-                    if (MODE == 2) { const float4 hp = q.hP[shl ? shl[i] : i]; O = mk(hp.x, hp.y, hp.z); D = normalize3(sub3(Vp, O)); }
-                    else {
-                        const float4 d = q.rayD[i]; D = mk(d.x, d.y, d.z);
-                        if (MODE == 1) O = Vp; else { const float4 o = q.rayO[i]; O = mk(o.x, o.y, o.z); }
-                    }
+                    const float4 dd = ws.d[rl];                // the ray as staged by the prologue (2*O halves exactly)
+                    const V3 D = mk(dd.x, dd.y, dd.z);
+                    V3 O = Vp;
+                    if (MODE != 1) { const float4 oo = ws.o[rl]; O = (MODE == 0) ? mk(0.5f * oo.x, 0.5f * oo.y, 0.5f * oo.z) : mk(oo.x, oo.y, oo.z); }
                     const float4 sp = __ldg(&sc.sphB[sid]);
                     const float t = sphere_exact(O, D, sp.x, sp.y, sp.z, sp.w);
                     hit = t > 0.f && t < kTMax;                                               // trace.py:26-29
@@ -263,7 +275,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
             while (cand) {
                 const int bit = __ffs(cand) - 1;
                 cand &= cand - 1;
-                sq[pos++] = (lane * NR + (uint32_t)(bit >> 1)) | ((uint32_t)(2 * pair + (bit & 1)) << 8);
+                sq[pos++] = ((uint32_t)(bit >> 1) * 32u + lane) | ((uint32_t)(2 * pair + (bit & 1)) << 8);
             }
             if (qcnt > (uint32_t)kQFlush) flush();
         };
@@ -317,30 +329,30 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
         }
         flush();
 
-        // ---- planes after the last sphere chunk (trace.py:32-39), then write back ----
-        uint32_t surv = 0;                                     // ANY: this thread's rays that are still unoccluded
-#pragma unroll
-        for (int r = 0; r < NR; ++r) {
-            const uint32_t i = i0 + r;
+        // ---- planes after the last sphere chunk (trace.py:32-39), then write back (one code copy, ray k*32 + lane) ----
+        uint32_t surv = 0;                                     // ANY: bit k = ray k*32 + lane is still unoccluded
+#pragma unroll 1
+        for (int k = 0; k < NR; ++k) {
+            const uint32_t rl = (uint32_t)k * 32u + lane, i = gbase + rl;
             if (i >= n_in) continue;
-            const unsigned long long key = ((unsigned long long)skt[lane * NR + r] << 32) | ski[lane * NR + r];
+            const float4 dd = ws.d[rl];
+            const V3 D = mk(dd.x, dd.y, dd.z);
             if (ANY) {
-                bool occluded = (key >> 32) != 0ull;
-                const uint32_t hrec = shl ? shl[i] : i;
+                bool occluded = skt[rl] != 0u;
+                const float4 oo = ws.o[rl];
                 if (last && !occluded && sc.Pl > 0) {
-                    const float4 hp = q.hP[hrec]; const V3 O = mk(hp.x, hp.y, hp.z);
-                    const V3 D = mk(dx[r], dy[r], dz[r]);
+                    const V3 O = mk(oo.x, oo.y, oo.z);
                     for (int pl = 0; pl < sc.Pl && !occluded; ++pl) {
                         const float t = plane_exact(O, D, __ldg(&sc.plO[pl]), __ldg(&sc.plN[pl]));
                         occluded = (t > 0.f && t < kTMax);
                     }
                 }
-                if (occluded) q.occl[(size_t)j * q.ocap + hrec] = 1; else surv |= 1u << r;
+                if (occluded) q.occl[(size_t)j * q.ocap + __float_as_uint(oo.w)] = 1; else surv |= 1u << k;
             } else {
-                float best = __uint_as_float((uint32_t)(key >> 32)); int bid = (int)(uint32_t)key;
+                float best = __uint_as_float(skt[rl]); int bid = (int)ski[rl];
                 if (last) {
-                    const V3 D = mk(dx[r], dy[r], dz[r]);
-                    const V3 O = (MODE == 0) ? mk(0.5f * o2x[PIV ? 0 : r], 0.5f * o2y[PIV ? 0 : r], 0.5f * o2z[PIV ? 0 : r]) : Vp;
+                    V3 O = Vp;
+                    if (MODE == 0) { const float4 oo = ws.o[rl]; O = mk(0.5f * oo.x, 0.5f * oo.y, 0.5f * oo.z); }
                     for (int pl = 0; pl < sc.Pl; ++pl) {
                         const float t = plane_exact(O, D, __ldg(&sc.plO[pl]), __ldg(&sc.plN[pl]));
                         if (t > 0.f && t < best) { best = t; bid = sc.S + pl; }
@@ -349,17 +361,18 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
                 if (bid >= 0) atomicMin(&q.hit[i], ((unsigned long long)__float_as_uint(best) << 32) | (uint32_t)bid);
             }
         }
-        if (ANY && q.out_list) {                              // survivors -> next pass's list, group order kept
-            const uint32_t n = (uint32_t)__popc(surv);
-            uint32_t x = n;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, d); if ((int)lane >= d) x += y; }
+        if (ANY && q.out_list) {                              // survivors -> next pass's list, in queue order
+            const uint32_t total = __reduce_add_sync(0xffffffffu, (uint32_t)__popc(surv));
             uint32_t base = 0;
-            if (lane == 31) base = atomicAdd(q.out_n, x);
-            uint32_t pos = __shfl_sync(0xffffffffu, base, 31) + x - n;
-#pragma unroll
-            for (int r = 0; r < NR; ++r)
-                if ((surv >> r) & 1u) q.out_list[pos++] = shl ? shl[i0 + r] : i0 + r;
+            if (lane == 0 && total) base = atomicAdd(q.out_n, total);
+            base = __shfl_sync(0xffffffffu, base, 0);
+#pragma unroll 1
+            for (int k = 0; k < NR; ++k) {
+                const bool sv = (surv >> k) & 1u;
+                const uint32_t bal = __ballot_sync(0xffffffffu, sv);
+                if (sv) q.out_list[base + (uint32_t)__popc(bal & ((1u << lane) - 1u))] = __float_as_uint(ws.o[(uint32_t)k * 32u + lane].w);
+                base += (uint32_t)__popc(bal);
+            }
         }
         __syncwarp();                                         // keys are re-initialised by the next group's setup
     };
@@ -385,9 +398,9 @@ struct IsectCfg { int sm_count; int force_nr; int force_nr0; int npre; int pre[6
 
 template <int MODE> static cudaError_t isect3_set_attr() {
     cudaError_t e;
-    if ((e = cudaFuncSetAttribute(k_isect3<MODE, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IsectSmem))) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(k_isect3<MODE, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IsectSmem))) != cudaSuccess) return e;
-    return cudaFuncSetAttribute(k_isect3<MODE, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IsectSmem));
+    if ((e = cudaFuncSetAttribute(k_isect3<MODE, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IsectSmem<8>))) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_isect3<MODE, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IsectSmem<4>))) != cudaSuccess) return e;
+    return cudaFuncSetAttribute(k_isect3<MODE, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IsectSmem<2>));
 }
 
 // Whole tables tabs[0..n) (each Spad entries) into slots 0..n-1 of THIS module's c_tab: done once per frame when
@@ -409,9 +422,9 @@ static cudaError_t isect3_launch_one(const IsectCfg& cfg, const SceneDev& sc, co
     int nr = cfg.force_nr ? cfg.force_nr : (max_rays >= warps * 256 * 4 ? 8 : (max_rays >= warps * 128 * 4 ? 4 : 2));
     if (MODE == 0 && cfg.force_nr0) nr = cfg.force_nr0;         // (measured: 8 rays/thread wins for the 8-FFMA2 form too)
     const int grid = cfg.sm_count * (nr == 8 ? 2 : 3);
-    if (nr == 8)      k_isect3<MODE, 8><<<grid, kThreads, sizeof(IsectSmem), st>>>(sc, q, pv, c0, cnt, j, tb);
-    else if (nr == 4) k_isect3<MODE, 4><<<grid, kThreads, sizeof(IsectSmem), st>>>(sc, q, pv, c0, cnt, j, tb);
-    else              k_isect3<MODE, 2><<<grid, kThreads, sizeof(IsectSmem), st>>>(sc, q, pv, c0, cnt, j, tb);
+    if (nr == 8)      k_isect3<MODE, 8><<<grid, kThreads, sizeof(IsectSmem<8>), st>>>(sc, q, pv, c0, cnt, j, tb);
+    else if (nr == 4) k_isect3<MODE, 4><<<grid, kThreads, sizeof(IsectSmem<4>), st>>>(sc, q, pv, c0, cnt, j, tb);
+    else              k_isect3<MODE, 2><<<grid, kThreads, sizeof(IsectSmem<2>), st>>>(sc, q, pv, c0, cnt, j, tb);
     return cudaGetLastError();
 }
 
