@@ -46,6 +46,7 @@ extern "C" {
 #define B200RT_F_SCENE_ON_HOST   0x1u  /* spheres/lights/planes point to HOST memory (b200rt_render only; implied by _host) */
 #define B200RT_F_NO_FILTER       0x2u  /* debug: run the exact sphere test on every sphere (must give bit-identical output) */
 #define B200RT_F_UNSWAP_GB       0x4u  /* write channels as R,G,B instead of the reference's R,B,G wiring (common.py:60-63) */
+#define B200RT_F_NO_CULL         0x8u  /* k_isect3 scans every sphere for every ray group (no beam culling); the image is the same */
 
 /*
  * Closed form of Camera.generate_pixel_locations() (reference src/scene/camera.py:18-26), evaluated the way

@@ -76,6 +76,7 @@ struct FrameDev {
     int sw, srank, sworld;         // interleaved strips (sw == 0: contiguous tile)
     int ns;                        // samples per pixel slot: 1 or 9
     uint32_t npix;                 // (x1-x0)*H
+    int tiled;                     // pixel slots in 16x16 tiles (H and the chunk's column count are multiples of 16), else column-major
 };
 
 // local column -> global x (array axis 1)
@@ -83,6 +84,16 @@ __device__ __forceinline__ int col_x(const FrameDev& f, int lc) {
     if (f.sw <= 0) return f.xb + lc;
     const int s = lc / f.sw;
     return f.xb + (s * f.sworld + f.srank) * f.sw + (lc - s * f.sw);
+}
+
+// Pixel slot p of the chunk -> (local column, y).  Tiled order: a ray group of 256 consecutive slots is a 16x16 pixel
+// tile, i.e. a narrow beam (the filter's candidates are shared by the whole group and k_isect3's beam culling is tight).
+__device__ __forceinline__ void slot_pixel(const FrameDev& f, uint32_t p, int& lc, int& y) {
+    if (f.tiled) {
+        const uint32_t tile = p >> 8, in = p & 255u, tiles_y = (uint32_t)f.H >> 4;
+        const uint32_t tx = tile / tiles_y, ty = tile - tx * tiles_y;
+        lc = (int)(tx * 16u + (in >> 4)); y = (int)(ty * 16u + (in & 15u));
+    } else { lc = (int)(p / (uint32_t)f.H); y = (int)(p % (uint32_t)f.H); }
 }
 
 // pixel_loc[c, x, y] with the GPU's unchecked C-order flat addressing: elements past the end
@@ -115,7 +126,8 @@ __global__ void k_raygen(FrameDev f, float4* __restrict__ rayO, float4* __restri
         float4 o = make_float4(0, 0, 0, 0), d = make_float4(0, 0, 0, 0);
         if (valid) {
             uint32_t k = slot / f.npix, p = slot - k * f.npix;
-            int x = col_x(f, f.x0 + (int)(p / (uint32_t)f.H)), y = (int)(p % (uint32_t)f.H);
+            int lc, y; slot_pixel(f, p, lc, y);
+            int x = col_x(f, f.x0 + lc);
             if (k > 0 && !(x >= 1 && y >= 1)) valid = false;          // kernels.py:29
             if (valid) {
                 double px = pl_at(f, 0, x, y), py = pl_at(f, 1, x, y), pz = pl_at(f, 2, x, y);
@@ -307,7 +319,7 @@ __global__ void k_rank(SceneDev sc, int* perm) {
 
 // One thread per (table j, pair i of table positions): k = r^2 - |C-V_j|^2 (j <= L) or r^2 - |C|^2 (j == L+1), float64
 // rounded once.  Light tables (j < L) are in k_rank's order, the two closest-hit tables in array order (ids matter there).
-__global__ void k_pivot(SceneDev sc, float cox, float coy, float coz, const int* perm, float4* tab, float4* piv) {
+__global__ void k_pivot(SceneDev sc, float cox, float coy, float coz, const int* perm, float4* tab, float4* piv, float* rad) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     const int npair = sc.Spad / 2;
     const int j = idx / npair, i = idx - j * npair;
@@ -323,7 +335,8 @@ __global__ void k_pivot(SceneDev sc, float cox, float coy, float coz, const int*
             const float4 sp = sc.sphB[s];
             const double ex = (double)sp.x - v.x, ey = (double)sp.y - v.y, ez = (double)sp.z - v.z;
             c[h][0] = sp.x; c[h][1] = sp.y; c[h][2] = sp.z; c[h][3] = (float)((double)sp.w - (ex * ex + ey * ey + ez * ez));
-        } else { c[h][0] = c[h][1] = c[h][2] = 0.f; c[h][3] = -3.0e38f; }     // padding never reaches a threshold
+            rad[(size_t)j * sc.Spad + 2 * i + h] = __fsqrt_ru(sp.w);              // radius, rounded up (beam culling)
+        } else { c[h][0] = c[h][1] = c[h][2] = 0.f; c[h][3] = -3.0e38f; rad[(size_t)j * sc.Spad + 2 * i + h] = 0.f; }     // padding never reaches a threshold
     }
     float4* o = tab + ((size_t)j * npair + i) * 2;
     o[0] = make_float4(c[0][0], c[1][0], c[0][1], c[1][1]);
@@ -457,7 +470,8 @@ __global__ void k_resolve(FrameDev f, const float* __restrict__ accR, const floa
 #pragma unroll
         for (int e = 0; e < VEC; ++e) {
             const uint32_t p = v * VEC + e;
-            const int x = col_x(f, f.x0 + (int)(p / (uint32_t)f.H)), y = (int)(p % (uint32_t)f.H);
+            int lc, y; slot_pixel(f, p, lc, y);
+            const int x = col_x(f, f.x0 + lc);
             float R = accR[p], G = accG[p], B = accB[p];
             if (aliasing && x >= 1 && y >= 1) {                                        // kernels.py:29
                 for (int k = 1; k < 9; ++k) {
@@ -471,7 +485,8 @@ __global__ void k_resolve(FrameDev f, const float* __restrict__ accR, const floa
             out2[e] = unswap ? clip_color(B) : clip_color(G);
         }
         const uint32_t p0 = v * VEC;                                  // H % VEC == 0: a vector never straddles columns
-        const size_t o = (size_t)col_x(f, f.x0 + (int)(p0 / (uint32_t)f.H)) * f.H + (p0 % (uint32_t)f.H);
+        int lc0, y0; slot_pixel(f, p0, lc0, y0);
+        const size_t o = (size_t)col_x(f, f.x0 + lc0) * f.H + (size_t)y0;
         uint8_t* d0 = result + o; uint8_t* d1 = result + WH + o; uint8_t* d2 = result + 2 * WH + o;
         if constexpr (VEC == 1) { d0[0] = (uint8_t)out0[0]; d1[0] = (uint8_t)out1[0]; d2[0] = (uint8_t)out2[0]; }
         else {
@@ -626,9 +641,9 @@ struct DevCtx {
     bool init = false;
     int sm_count = 0;
     int isect_blocks_per_sm = 2;
-    int force_nr = 0, force_nr0 = 0; bool no_pivot = false, no_conc = false;                       // tuning overrides (env B200RT_NR, B200RT_NO_PIVOT)
+    int force_nr = 0, force_nr0 = 0; bool no_pivot = false, no_conc = false, no_cull = false;                       // tuning overrides (env B200RT_NR, B200RT_NO_PIVOT)
     Buf sphA, sphB, sphCol, plO, plN, plNu, plCol, lights, cmax;   // packed scene
-    Buf pivTab, pivPos, pivPerm;                                   // pivot tables (k_pivot), light-table order (k_rank)
+    Buf pivTab, pivPos, pivPerm, pivRad;                                   // pivot tables (k_pivot), light-table order (k_rank)
     Buf stage;                                                     // host-scene / host-pixel_loc staging
     Buf rayO[2], rayD[2], hitKey[2];                               // ray queues, double-buffered by depth parity
     Buf hP[kSets], hN[kSets], occl[kSets], shidx[kSets], shidx2[kSets];   // hit records / shadow state: ring of kSets depths
@@ -644,7 +659,7 @@ struct DevCtx {
     Buf hostResult, hostPixelLoc, imgOut;                          // b200rt_render_host / b200rt_to_image_host device copies
     cudaEvent_t done = nullptr; bool has_done = false;
     void release_all() {
-        Buf* all[] = { &sphA, &sphB, &sphCol, &plO, &plN, &plNu, &plCol, &lights, &cmax, &pivTab, &pivPos, &pivPerm, &stage, &rayO[0], &rayO[1], &rayD[0], &rayD[1], &hitKey[0], &hitKey[1],
+        Buf* all[] = { &sphA, &sphB, &sphCol, &plO, &plN, &plNu, &plCol, &lights, &cmax, &pivTab, &pivPos, &pivPerm, &pivRad, &stage, &rayO[0], &rayO[1], &rayD[0], &rayD[1], &hitKey[0], &hitKey[1],
                        &acc, &tl, &ctr, &work, &slow, &hostResult, &hostPixelLoc, &imgOut, &batchScene };
         for (Buf* b : all) b->release();
         for (int i = 0; i < kSets; ++i) { hP[i].release(); hN[i].release(); occl[i].release(); shidx[i].release(); shidx2[i].release(); }
@@ -723,6 +738,7 @@ int init_ctx(DevCtx& c, int device) {
     { const char* e = getenv("B200RT_NR0"); c.force_nr0 = e ? atoi(e) : 0; if (c.force_nr0 != 2 && c.force_nr0 != 4 && c.force_nr0 != 8) c.force_nr0 = 0; }
     { const char* e = getenv("B200RT_NO_PIVOT"); c.no_pivot = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_NO_CONCURRENCY"); c.no_conc = e && atoi(e) != 0; }
+    { const char* e = getenv("B200RT_NO_CULL"); c.no_cull = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_TIMELINE"); c.timeline = e && atoi(e) != 0; }
     if (const char* e = getenv("B200RT_PASSES")) {
         c.npre = 0;
@@ -792,13 +808,14 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     CK(c.pivTab.ensure(sizeof(float4) * (size_t)(L + 2) * Spad)); CK(c.pivPos.ensure(sizeof(float4) * (L + 1)));
     {
         const int n = (L + 2) * (Spad / 2);
-        CK(c.pivPerm.ensure(sizeof(int) * std::max<size_t>((size_t)L * Spad, 1)));
+        CK(c.pivPerm.ensure(sizeof(int) * std::max<size_t>((size_t)L * Spad, 1))); CK(c.pivRad.ensure(sizeof(float) * (size_t)(L + 2) * Spad));
         if (L > 0) { k_rank<<<(L * Spad + 255) / 256, 256, 0, st>>>(sc, c.pivPerm.as<int>()); CK(cudaGetLastError()); }
         k_pivot<<<(n + 255) / 256, 256, 0, st>>>(sc, (float)a->cam_origin[0], (float)a->cam_origin[1], (float)a->cam_origin[2],
-                                                 c.pivPerm.as<int>(), c.pivTab.as<float4>(), c.pivPos.as<float4>());
+                                                 c.pivPerm.as<int>(), c.pivTab.as<float4>(), c.pivPos.as<float4>(), c.pivRad.as<float>());
         CK(cudaGetLastError());
     }
-    const PivotDev pv{ c.pivTab.as<float4>(), c.pivPos.as<float4>(), c.cmax.as<float>(), c.pivPerm.as<int>() };
+    const bool cull = !(a->flags & B200RT_F_NO_CULL) && !c.no_cull;
+    const PivotDev pv{ c.pivTab.as<float4>(), c.pivPos.as<float4>(), c.cmax.as<float>(), c.pivPerm.as<int>(), cull ? c.pivRad.as<float>() : nullptr };
     // Constant-memory residency (isect3.cuh): the closest-hit module holds the camera-pivot and origin-free tables,
     // the shadow module one table per light.  When they fit they are uploaded once per frame.
     const bool nofilter = (a->flags & B200RT_F_NO_FILTER) != 0;
@@ -812,6 +829,8 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     const size_t per_col = (size_t)ns * H;
     size_t cols_per_chunk = std::max<size_t>(1, max_paths_per_chunk() / per_col);
     cols_per_chunk = std::min<size_t>(cols_per_chunk, (size_t)ncols);
+    const bool tiled = (H % 16 == 0) && (ncols % 16 == 0) && (cols_per_chunk >= 16);
+    if (tiled) cols_per_chunk &= ~(size_t)15;
     const int nchunks = (int)((ncols + cols_per_chunk - 1) / cols_per_chunk);
     const size_t cap = cols_per_chunk * per_col;                 // slots per chunk
     const bool use_lists = S >= 32 && !(a->flags & B200RT_F_NO_FILTER);
@@ -830,14 +849,14 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     // layout is cheaper than building the lists.
     const int cps = 4 + L;                                       // counters per depth: n_live, n_hit, 2 debug work counters, n_sh[L]
     const int ctr_stride = cps * (depth + 2);
-    CK(c.ctr.ensure(sizeof(uint32_t) * (size_t)ctr_stride * nchunks)); CK(c.slow.ensure(2 * sizeof(unsigned long long)));
+    CK(c.ctr.ensure(sizeof(uint32_t) * (size_t)ctr_stride * nchunks)); CK(c.slow.ensure(4 * sizeof(unsigned long long)));
     CK(cudaMemsetAsync(c.ctr.p, 0, sizeof(uint32_t) * (size_t)ctr_stride * nchunks, st));
     const int nsch = (Spad + kTabCap - 1) / kTabCap;             // sphere chunks of the constant-memory table
     const size_t work_per_depth = (size_t)nsch + (size_t)2 * L * kMaxPass;   // closest: per chunk; shadow: per (light, pass) group counter + survivor counter
     const size_t work_n = work_per_depth * (depth + 1) * nchunks;
     CK(c.work.ensure(sizeof(uint32_t) * work_n));
     CK(cudaMemsetAsync(c.work.p, 0, sizeof(uint32_t) * work_n, st));
-    CK(cudaMemsetAsync(c.slow.p, 0, 2 * sizeof(unsigned long long), st));
+    CK(cudaMemsetAsync(c.slow.p, 0, 4 * sizeof(unsigned long long), st));
 
     {   // persistent grid for the intersection kernels
         int nb = 0; CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_intersect<false, true>, kThreads, isect_smem_bytes(Spad)));
@@ -871,7 +890,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         f.W = W; f.H = H; f.ns = ns;
         f.x0 = (int)(ch * cols_per_chunk); f.x1 = std::min(ncols, f.x0 + (int)cols_per_chunk);
         f.xb = a->x_begin; f.sw = a->strip_width; f.srank = a->strip_rank; f.sworld = a->strip_world;
-        f.npix = (uint32_t)(f.x1 - f.x0) * (uint32_t)H;
+        f.npix = (uint32_t)(f.x1 - f.x0) * (uint32_t)H; f.tiled = tiled ? 1 : 0;
         const size_t nslots = (size_t)f.npix * ns;
         uint32_t* ctr = c.ctr.as<uint32_t>() + (size_t)ch * ctr_stride;
         float* accR = c.acc.as<float>(); float* accG = accR + cap; float* accB = accG + cap;
@@ -981,23 +1000,8 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
                 if (d == 0) out.primary += cd[0]; else out.bounce += (cd - cps)[3];       // queue of depth d = hit list of depth d-1
                 out.shadow += (uint64_t)cd[3] * (uint64_t)L;
             }
-        // executed filter tests: closest hit = queue length x Spad; shadow = sum over passes of (pass input length x pass range)
-        if (!nofilter) {
-            std::vector<uint32_t> hw(work_n); CK(cudaMemcpy(hw.data(), c.work.p, sizeof(uint32_t) * work_n, cudaMemcpyDeviceToHost));
-            int ranges[kMaxPass][2]; const int np = shadow_passes(icfg, Spad, ranges);
-            for (int ch = 0; ch < nchunks; ++ch)
-                for (int d = 0; d <= depth; ++d) {
-                    const uint32_t* cd = h.data() + (size_t)ch * ctr_stride + cps * d;
-                    const uint64_t nq = d == 0 ? cd[0] : (cd - cps)[3];
-                    if (d == 0 && !c.no_pivot) out.tests_pivot += nq * (uint64_t)Spad; else out.tests_general += nq * (uint64_t)Spad;
-                    const uint32_t* npass = hw.data() + ((size_t)ch * (depth + 1) + d) * work_per_depth + nsch + (size_t)L * kMaxPass;
-                    for (int j = 0; j < L; ++j)
-                        for (int p = 0; p < np; ++p)
-                            out.tests_pivot += (uint64_t)(p == 0 ? (use_lists ? cd[4 + j] : cd[3]) : npass[(size_t)j * kMaxPass + p - 1]) * (uint64_t)ranges[p][1];
-                }
-        }
-        unsigned long long slow[2] = {0, 0}; CK(cudaMemcpy(slow, c.slow.p, sizeof(slow), cudaMemcpyDeviceToHost));
-        out.slow_path = slow[0]; out.exact_tests = slow[1];
+        unsigned long long slow[4] = {0, 0, 0, 0}; CK(cudaMemcpy(slow, c.slow.p, sizeof(slow), cudaMemcpyDeviceToHost));
+        out.slow_path = slow[0]; out.exact_tests = slow[1]; out.tests_pivot = slow[2]; out.tests_general = slow[3];   // counted by k_isect3
         CK(cudaEventElapsedTime(&out.kernel_ms[0], ev0, ev1));
         out.kernel_ms[1] = tm.total(0); out.kernel_ms[2] = tm.total(1); out.kernel_ms[3] = tm.total(2);
         cudaEventDestroy(ev0); cudaEventDestroy(ev1);

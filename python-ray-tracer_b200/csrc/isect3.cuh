@@ -84,6 +84,7 @@ struct PivotDev {
     const float4* piv;                   // [(L+1)]       pivot positions (float32)
     const float*  bounds;                // [2]           max |C|, max r
     const int*    perm;                  // [L][Spad]     light tables only: table position -> sphere index (k_rank), or null
+    const float*  rad;                   // [(L+2)][Spad] radius of the sphere at each table position (beam culling), or null = no culling
 };
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
@@ -140,6 +141,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
     uint32_t* sq = ws.q;
     uint32_t* skt = ws.kt; uint32_t* ski = ws.ki;
     uint32_t slow_cnt = 0, exact_cnt = 0;
+    unsigned long long tests_cnt = 0;                         // diagnostic: filter tests executed by this thread's rays (padding and inactive rays included)
     // j: pivot of this launch (light index for ANY, camera = L for MODE 1); its table is c_tab[tb + 2*pair + {0,1}].
     // tb is a kernel parameter so that the table index provably lives in uniform registers (LDCU -> UR operands).
     V3 Vp = mk(0.f, 0.f, 0.f);
@@ -290,6 +292,116 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
             }
         };
 
+        // ---- beam culling.  The group's rays lie in a "beam": origins within ro of their centroid Oc, directions
+        // within kap of their mean Dc, so the point at parameter t of any of them is within ro + kap*t of Oc + t*Dc.  A
+        // sphere that stays clear of that swept cone for all t >= 0 cannot be hit by any ray of the group and needs no
+        // test at all — for primary rays, shadow rays towards a light and rays reflected off a plane the beam of 256
+        // neighbouring rays is narrow and most of the scene is outside it.  The test is conservative (radius inflated by
+        // the exact test's rounding bound), so the image does not change; B200RT_F_NO_CULL switches it off.  Survivors
+        // are listed per PAIR of table positions and scanned through the list (operands from the constant table with a
+        // computed index instead of uniform registers); wide beams and poor cull rates take the dense scan. ----
+        int ns = -1, nsr = 0;                                 // ns >= 0: sparse scan over slist[0..ns), the first nsr entries real
+        uint16_t* slist = reinterpret_cast<uint16_t*>(MODE == 2 ? (void*)ws.ki : MODE == 0 ? (void*)ws.thr : (void*)ws.o);   // 1 KB free in every mode
+        if (pv.rad && npair <= 32 * NR * 2 && npair >= 64) {
+            float ax = 0.f, ay = 0.f, az = 0.f, bx = 0.f, by = 0.f, bz = 0.f, na = 0.f;
+#pragma unroll
+            for (int r = 0; r < NR; ++r) {
+                if (gbase + (uint32_t)r * 32u + lane >= n_in) continue;
+                na += 1.f; bx += dx[r]; by += dy[r]; bz += dz[r];
+                if (MODE == 0) { ax += 0.5f * o2x[PIV ? 0 : r]; ay += 0.5f * o2y[PIV ? 0 : r]; az += 0.5f * o2z[PIV ? 0 : r]; }
+                if (MODE == 2) { const float4 oo = ws.o[r * 32 + lane]; ax += oo.x; ay += oo.y; az += oo.z; }
+            }
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) {
+                na += __shfl_xor_sync(0xffffffffu, na, d);
+                bx += __shfl_xor_sync(0xffffffffu, bx, d); by += __shfl_xor_sync(0xffffffffu, by, d); bz += __shfl_xor_sync(0xffffffffu, bz, d);
+                if (MODE != 1) { ax += __shfl_xor_sync(0xffffffffu, ax, d); ay += __shfl_xor_sync(0xffffffffu, ay, d); az += __shfl_xor_sync(0xffffffffu, az, d); }
+            }
+            const float bn = __fsqrt_rn(bx * bx + by * by + bz * bz);
+            if (__all_sync(0xffffffffu, bn > 0.25f * na)) {    // (mean direction well defined; na >= 1 in a claimed group; votes keep the control flow provably uniform)
+                const float ib = 1.f / bn, ia = 1.f / na;
+                const V3 Dc = mk(bx * ib, by * ib, bz * ib);
+                const V3 Oc = (MODE == 1) ? Vp : mk(ax * ia, ay * ia, az * ia);
+                float ro2 = 0.f, kap2 = 0.f;
+#pragma unroll
+                for (int r = 0; r < NR; ++r) {
+                    if (gbase + (uint32_t)r * 32u + lane >= n_in) continue;
+                    const float ex = dx[r] - Dc.x, ey = dy[r] - Dc.y, ez = dz[r] - Dc.z;
+                    kap2 = fmaxf(kap2, ex * ex + ey * ey + ez * ez);
+                    if (MODE == 0) { const float fx = 0.5f * o2x[PIV ? 0 : r] - Oc.x, fy = 0.5f * o2y[PIV ? 0 : r] - Oc.y, fz = 0.5f * o2z[PIV ? 0 : r] - Oc.z; ro2 = fmaxf(ro2, fx * fx + fy * fy + fz * fz); }
+                    if (MODE == 2) { const float4 oo = ws.o[r * 32 + lane]; const float fx = oo.x - Oc.x, fy = oo.y - Oc.y, fz = oo.z - Oc.z; ro2 = fmaxf(ro2, fx * fx + fy * fy + fz * fz); }
+                }
+#pragma unroll
+                for (int d = 16; d > 0; d >>= 1) { ro2 = fmaxf(ro2, __shfl_xor_sync(0xffffffffu, ro2, d)); kap2 = fmaxf(kap2, __shfl_xor_sync(0xffffffffu, kap2, d)); }
+                const float kap = __fsqrt_rn(kap2) * 1.0001f + 1e-6f;
+                if (__all_sync(0xffffffffu, kap < 0.6f)) {
+                    const float osz = cmax + __fsqrt_rn(dot3(Oc, Oc));
+                    const float ro = __fsqrt_rn(ro2) * 1.0001f + 1e-6f * osz;
+                    // slack of the exact test (it may report a hit up to ~16 eps B^2 outside the sphere) + this test's own rounding
+                    const float m = 2.5e-5f * (osz + ro) * (osz + ro) + 1e-9f;
+                    const float kk = 1.f - kap * kap;
+                    const int tj = ANY ? j : (MODE == 1 ? sc.L : sc.L + 1);
+                    const float4* gt = pv.tab + (size_t)tj * sc.Spad + c0;
+                    const float2* gr = reinterpret_cast<const float2*>(pv.rad + (size_t)tj * sc.Spad + c0);
+                    auto clear_of_beam = [&](float cx, float cy, float cz, float rad) -> bool {
+                        const float wx = cx - Oc.x, wy = cy - Oc.y, wz = cz - Oc.z;
+                        const float w2 = wx * wx + wy * wy + wz * wz, a = wx * Dc.x + wy * Dc.y + wz * Dc.z;
+                        const float Rp = rad + ro, Rp2 = (Rp * Rp + m) * 1.0002f;
+                        const float tn = a + kap * __fsqrt_rn(Rp2) * 1.0001f;
+                        const float lhs = w2 - Rp2;
+                        return (tn < 0.f) ? (lhs > 0.f) : (lhs * kk > tn * tn * 1.0002f + 1e-3f);
+                    };
+                    uint32_t nsv = 0;
+                    for (int p0 = 0; p0 < npair; p0 += 32) {
+                        const int p = p0 + (int)lane;
+                        bool keep = false;
+                        if (p < npair) {
+                            const float4 uu = __ldg(gt + 2 * p), ww = __ldg(gt + 2 * p + 1);
+                            const float2 rr = __ldg(gr + p);
+                            keep = (c0 + 2 * p < sc.S && !clear_of_beam(uu.x, uu.z, ww.x, rr.x)) ||
+                                   (c0 + 2 * p + 1 < sc.S && !clear_of_beam(uu.y, uu.w, ww.y, rr.y));
+                        }
+                        const uint32_t bal = __ballot_sync(0xffffffffu, keep);
+                        if (keep) slist[nsv + (uint32_t)__popc(bal & ((1u << lane) - 1u))] = (uint16_t)p;
+                        nsv += (uint32_t)__popc(bal);
+                    }
+                    if (__all_sync(0xffffffffu, 2 * (int)nsv <= npair)) {      // worth it (the list path costs ~1.5x per test)
+                        __syncwarp();
+                        const uint16_t padv = nsv ? slist[nsv - 1] : (uint16_t)0;      // padding: the last pair again (never queued twice)
+                        if (lane < (KP - nsv % KP) % KP) slist[nsv + lane] = padv;
+                        nsr = (int)nsv; ns = (int)((nsv + KP - 1) / KP * KP);
+                        __syncwarp();
+                    }
+                }
+            }
+        }
+        if (__all_sync(0xffffffffu, ns >= 0)) {
+            if (q.slow) tests_cnt += (unsigned long long)ns * 2ull * (unsigned long long)NR;
+            for (int pb = 0; pb < ns; pb += KP) {
+                float mk4[KP]; int pi[KP];
+#pragma unroll
+                for (int k = 0; k < KP; ++k) {
+                    pi[k] = slist[pb + k];
+                    const float4 u = c_tab[tb + 2 * pi[k]], w = c_tab[tb + 2 * pi[k] + 1];
+                    float m = -3.0e38f;
+#pragma unroll
+                    for (int r = 0; r < NR; ++r) { const float2 qv = qray(r, u, w); m = fmax3(m, qv.x, qv.y); }
+                    mk4[k] = m;
+                }
+                const float mall = fmaxf(fmaxf(mk4[0], mk4[1]), fmaxf(mk4[2], mk4[3]));
+                if (__any_sync(0xffffffffu, mall >= thr_t)) {
+                    slow_cnt++;
+#pragma unroll 1
+                    for (int k = 0; k < KP; ++k) {
+                        float mv = mk4[0]; int pv_ = pi[0];
+#pragma unroll
+                        for (int kk2 = 1; kk2 < KP; ++kk2) { mv = (k == kk2) ? mk4[kk2] : mv; pv_ = (k == kk2) ? pi[kk2] : pv_; }
+                        if (pb + k < nsr && __any_sync(0xffffffffu, mv >= thr_t)) slow_pair(pv_);
+                    }
+                }
+            }
+        } else {
+        if (q.slow) tests_cnt += (unsigned long long)npair * 2ull * (unsigned long long)NR;
         // ---- scan: KP sphere pairs x NR rays per step, pair-major; the uniform registers of a pair are refilled
         // for the NEXT step as soon as the pair is done (rolling prefetch: LDCU latency never reaches the FMA pipe).
         // The candidate decision of a step is taken one step LATER (software pipelining): the vote/branch never
@@ -326,6 +438,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
             const float mall = fmaxf(fmaxf(mprev[0], mprev[1]), fmaxf(mprev[2], mprev[3]));
             if (__any_sync(0xffffffffu, mall >= thr_t)) slow_step(npair - KP, mprev);            // flush the last step
             break;
+        }
         }
         flush();
 
@@ -388,6 +501,10 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
     if (q.slow) {
         const uint32_t tot = __reduce_add_sync(0xffffffffu, slow_cnt), tot2 = __reduce_add_sync(0xffffffffu, exact_cnt);
         if (lane == 0 && tot) { atomicAdd(q.slow, (unsigned long long)tot); atomicAdd(q.slow + 1, (unsigned long long)tot2); }
+        unsigned long long tt = tests_cnt;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) tt += __shfl_xor_sync(0xffffffffu, tt, d);
+        if (lane == 0 && tt) atomicAdd(q.slow + (PIV ? 2 : 3), tt);
     }
 }
 
