@@ -283,6 +283,7 @@ def run_ours(args, w):
                          "algorithmic_flops_per_ray": fpr, "kernel_ms_per_frame": isect_ms, "kernel_ms_closest": st2["ms_closest"], "kernel_ms_shadow": st2["ms_shadow"], "other_ms": st2["ms_other"], "kernel_share_of_frame": isect_ms / st2["ms_total"],
                          "slow_path_entries_per_ray": st2["slow_path"] / max(1, rays_this_rank), "exact_tests_per_ray": st2["exact_tests"] / max(1, rays_this_rank), "shadow_queries_traced_fraction": st2["shadow_traced"] / max(1, st2["shadow"]),
                          # work actually executed (the early-out shadow passes and the culled shadow queries skip tests):
+                         "executed_tests_pivot_form": st2["tests_pivot"], "executed_tests_general_form": st2["tests_general"],
                          "executed_sphere_tests": st2["tests_pivot"] + st2["tests_general"], "canonical_sphere_tests": rays_this_rank * S,
                          "executed_tflops": (8.0 * st2["tests_pivot"] + 16.0 * st2["tests_general"]) / (isect_ms * 1e-3) / 1e12,
                          "executed_frac": (8.0 * st2["tests_pivot"] + 16.0 * st2["tests_general"]) / (isect_ms * 1e-3) / 1e12 / nominal_tf,

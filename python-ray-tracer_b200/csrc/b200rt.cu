@@ -117,11 +117,23 @@ __constant__ int c_dy[9] = { 0, 0, 0, +1, -1, +1, +1, -1, -1 };
 
 // One thread per (sample k, pixel p) slot.  Primary ray in FP64 (kernels.py:19-23 / :43-55), rounded to FP32,
 // appended to the ray queue.  Slots that the reference never samples (AA border: x == 0 or y == 0) are skipped.
+// Queue position: without anti-aliasing every slot has a ray, so position = slot (the queue is in slot order by
+// construction); with it, border slots are skipped and the queue is compacted IN ORDER (ordered_append8: chunks of
+// 256 slots in ticket order) — the queue order decides which rays share a group in k_isect3 at every later stage.
 __global__ void k_raygen(FrameDev f, float4* __restrict__ rayO, float4* __restrict__ rayD, unsigned long long* __restrict__ hit,
-                         uint32_t* n_live) {
+                         uint32_t* n_live, unsigned long long* ostat, uint32_t* ticket) {
     const uint32_t nslots = f.npix * (uint32_t)f.ns;
-    for (uint32_t base = blockIdx.x * blockDim.x; base < nslots; base += gridDim.x * blockDim.x) {
-        uint32_t slot = base + threadIdx.x;
+    const uint32_t nchunks = (nslots + 255u) / 256u;
+    __shared__ uint32_t s_chunk;
+    for (uint32_t it = blockIdx.x;; it += gridDim.x) {
+        uint32_t c = it;
+        if (f.ns > 1) {
+            if (threadIdx.x == 0) s_chunk = atomicAdd(ticket, 1u);
+            __syncthreads();
+            c = s_chunk;
+        }
+        if (c >= nchunks) break;
+        uint32_t slot = c * 256u + threadIdx.x;
         bool valid = slot < nslots;
         float4 o = make_float4(0, 0, 0, 0), d = make_float4(0, 0, 0, 0);
         if (valid) {
@@ -146,7 +158,9 @@ __global__ void k_raygen(FrameDev f, float4* __restrict__ rayO, float4* __restri
                 o = make_float4((float)f.ox, (float)f.oy, (float)f.oz, __uint_as_float(slot));
             }
         }
-        uint32_t pos = block_append(valid, n_live);
+        uint32_t pos = slot;
+        if (f.ns > 1) { uint32_t pp[8]; ordered_append8(valid ? 1u : 0u, 1, c, ostat, n_live, c == nchunks - 1, pp); pos = pp[0]; }
+        else if (slot == 0) *n_live = nslots;
         if (valid) { rayO[pos] = o; rayD[pos] = d; hit[pos] = kNoHitKey; }
     }
 }
@@ -360,14 +374,22 @@ struct ShadeDev {
     float amb, lamb, weight;             // weight = refl^depth_index (1 for the primary trace), trace.py:131
     int emit_reflection;                 // 0 on the last depth (k_setup)
     unsigned long long* tl;              // diagnostic timeline slot (may be null)
+    unsigned long long* ostat; uint32_t* ticket; size_t ostat_stride;   // k_setup: ordered_append8 status [pass][chunk][8] (zeroed), chunk ticket (zeroed)
 };
 
 // trace.py:56-83: miss -> path ends; hit -> P = O + tD, colour/normal by object type, P += BIAS*N.
 __global__ void k_setup(SceneDev sc, ShadeDev s) {
     if (s.tl && threadIdx.x == 0) atomicMin(s.tl, globaltimer_ns());
     const uint32_t n = *s.n_live;
-    for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {
-        const uint32_t i = base + threadIdx.x;
+    const uint32_t nchunks = (n + 255u) / 256u;
+    __shared__ uint32_t s_chunk;
+    for (;;) {
+        if (threadIdx.x == 0) s_chunk = atomicAdd(s.ticket, 1u);      // chunks in ticket order (ordered_append8 spins on predecessors)
+        __syncthreads();
+        const uint32_t c = s_chunk;
+        if (c >= nchunks) break;
+        const bool is_last = (c == nchunks - 1);
+        const uint32_t i = c * 256u + threadIdx.x;
         bool hit = false; float4 o = make_float4(0, 0, 0, 0), d = o; float t = 0.f; int id = -1;
         if (i < n) {                                 // the three loads go out together (the ray is read even if it missed)
             const unsigned long long key = s.hit[i]; o = s.rayO[i]; d = s.rayD[i];
@@ -386,8 +408,8 @@ __global__ void k_setup(SceneDev sc, ShadeDev s) {
         // One multi-queue append per pass: queue 0 = the hit list (first pass), the others = lights' lists
         // (n_hit and n_sh[] are adjacent counters).
         uint32_t h = 0;
-        if (!s.shidx) h = block_append(hit, s.n_hit);             // dense shadow layout (small scenes): hit list only
-        else for (int j0 = 0, first = 1; first || j0 < sc.L; first = 0) {
+        if (!s.shidx) { uint32_t pos[8]; ordered_append8(hit ? 1u : 0u, 1, c, s.ostat, s.n_hit, is_last, pos); h = pos[0]; }   // dense shadow layout: hit list only
+        else for (int j0 = 0, first = 1, pass = 0; first || j0 < sc.L; first = 0, ++pass) {
             const int nl = min(first ? 7 : 8, sc.L - j0), sh = first ? 1 : 0;
             uint32_t flags = (first && hit) ? 1u : 0u;
             if (hit) {
@@ -398,7 +420,7 @@ __global__ void k_setup(SceneDev sc, ShadeDev s) {
                 }
             }
             uint32_t pos[8];
-            block_append8(flags, nl + sh, first ? s.n_hit : s.n_sh + j0, pos);
+            ordered_append8(flags, nl + sh, c, s.ostat + (size_t)pass * s.ostat_stride, first ? s.n_hit : s.n_sh + j0, is_last, pos);
             if (first) h = pos[0];
 #pragma unroll
             for (int jj = 0; jj < 8; ++jj)
@@ -647,7 +669,7 @@ struct DevCtx {
     Buf stage;                                                     // host-scene / host-pixel_loc staging
     Buf rayO[2], rayD[2], hitKey[2];                               // ray queues, double-buffered by depth parity
     Buf hP[kSets], hN[kSets], occl[kSets], shidx[kSets], shidx2[kSets];   // hit records / shadow state: ring of kSets depths
-    Buf acc, ctr, work, slow, tl;
+    Buf acc, ctr, work, slow, tl, ostat;
     int npre = 2, pre[6] = {128, 256, 0, 0, 0, 0};                  // leading shadow passes (env B200RT_PASSES=a,b,...; multiples of 8)
     bool timeline = false;                                        // env B200RT_TIMELINE: per-launch first-start / last-end (globaltimer) to stderr
     // internal streams (see the launch sequence in render_device): the dependent chain at high priority, one stream per
@@ -660,7 +682,7 @@ struct DevCtx {
     cudaEvent_t done = nullptr; bool has_done = false;
     void release_all() {
         Buf* all[] = { &sphA, &sphB, &sphCol, &plO, &plN, &plNu, &plCol, &lights, &cmax, &pivTab, &pivPos, &pivPerm, &pivRad, &stage, &rayO[0], &rayO[1], &rayD[0], &rayD[1], &hitKey[0], &hitKey[1],
-                       &acc, &tl, &ctr, &work, &slow, &hostResult, &hostPixelLoc, &imgOut, &batchScene };
+                       &acc, &tl, &ostat, &ctr, &work, &slow, &hostResult, &hostPixelLoc, &imgOut, &batchScene };
         for (Buf* b : all) b->release();
         for (int i = 0; i < kSets; ++i) { hP[i].release(); hN[i].release(); occl[i].release(); shidx[i].release(); shidx2[i].release(); }
         if (done) { cudaEventDestroy(done); done = nullptr; } has_done = false; init = false;
@@ -845,18 +867,27 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         if (use_lists) { CK(c.shidx[b].ensure(sizeof(uint32_t) * std::max<size_t>(cap * (size_t)L, 1))); CK(c.shidx2[b].ensure(sizeof(uint32_t) * std::max<size_t>(cap * (size_t)L, 1))); }
     }
     CK(c.acc.ensure(sizeof(float) * 3 * cap));
+    // k_setup's ordered compaction: [pass][chunk of 256 rays][8 queues] status words + the chunk ticket, zeroed before every launch
+    const size_t ostat_stride = ((cap + 255) / 256) * 8;
+    const int ostat_passes = use_lists ? 1 + std::max(0, (L - 7 + 7) / 8) : 1;
+    const size_t ostat_bytes = sizeof(unsigned long long) * (ostat_stride * ostat_passes + 1);
+    CK(c.ostat.ensure(ostat_bytes));
     // Per-light shadow lists pay off when a query is expensive (many spheres); for tiny scenes the dense [light][hit]
     // layout is cheaper than building the lists.
     const int cps = 4 + L;                                       // counters per depth: n_live, n_hit, 2 debug work counters, n_sh[L]
     const int ctr_stride = cps * (depth + 2);
-    CK(c.ctr.ensure(sizeof(uint32_t) * (size_t)ctr_stride * nchunks)); CK(c.slow.ensure(4 * sizeof(unsigned long long)));
+    CK(c.ctr.ensure(sizeof(uint32_t) * (size_t)ctr_stride * nchunks)); CK(c.slow.ensure(24 * sizeof(unsigned long long)));
     CK(cudaMemsetAsync(c.ctr.p, 0, sizeof(uint32_t) * (size_t)ctr_stride * nchunks, st));
     const int nsch = (Spad + kTabCap - 1) / kTabCap;             // sphere chunks of the constant-memory table
-    const size_t work_per_depth = (size_t)nsch + (size_t)2 * L * kMaxPass;   // closest: per chunk; shadow: per (light, pass) group counter + survivor counter
+    int sh_ranges[kMaxPass][2]; const int sh_np = (L > 0 && !nofilter) ? shadow_passes(icfg, Spad, sh_ranges) : 1;
+    if (sh_np < 0) return fail(B200RT_E_SHAPE, "too many spheres for the shadow pass table");
+    const size_t nreg = (cap + kRegion - 1) / kRegion;            // regions of the survivor lists
+    // per depth: closest: group counter per chunk; shadow: group counter per (light, pass), region fill counts per (light, pass < np-1)
+    const size_t work_per_depth = (size_t)nsch + (size_t)L * kMaxPass + (size_t)L * kMaxPass * (sh_np > 1 ? nreg : 0);
     const size_t work_n = work_per_depth * (depth + 1) * nchunks;
     CK(c.work.ensure(sizeof(uint32_t) * work_n));
     CK(cudaMemsetAsync(c.work.p, 0, sizeof(uint32_t) * work_n, st));
-    CK(cudaMemsetAsync(c.slow.p, 0, 4 * sizeof(unsigned long long), st));
+    CK(cudaMemsetAsync(c.slow.p, 0, 24 * sizeof(unsigned long long), st));
 
     {   // persistent grid for the intersection kernels
         int nb = 0; CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_intersect<false, true>, kThreads, isect_smem_bytes(Spad)));
@@ -899,7 +930,9 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         CK(cudaMemsetAsync(accR, 0, sizeof(float) * nslots, cs));
         CK(cudaMemsetAsync(accG, 0, sizeof(float) * nslots, cs));
         CK(cudaMemsetAsync(accB, 0, sizeof(float) * nslots, cs));
-        k_raygen<<<(int)std::min<size_t>((nslots + 255) / 256, (size_t)small_grid), 256, 0, cs>>>(f, c.rayO[0].as<float4>(), c.rayD[0].as<float4>(), c.hitKey[0].as<unsigned long long>(), ctr + 0);
+        if (ns > 1) CK(cudaMemsetAsync(c.ostat.p, 0, ostat_bytes, cs));
+        k_raygen<<<(int)std::min<size_t>((nslots + 255) / 256, (size_t)small_grid), 256, 0, cs>>>(f, c.rayO[0].as<float4>(), c.rayD[0].as<float4>(), c.hitKey[0].as<unsigned long long>(), ctr + 0,
+                                                                                                         c.ostat.as<unsigned long long>(), reinterpret_cast<uint32_t*>(c.ostat.as<unsigned long long>() + ostat_stride * ostat_passes));
         CK(cudaGetLastError());
         tm.end(2);
 
@@ -939,6 +972,8 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             tm.begin(2);
             if (conc && d >= nsets) CK(cudaStreamWaitEvent(cs, c.evShade[hs], 0));        // set hs is free again
             if (tlb) { s.tl = tlb + 2 * (size_t)tln++; tlname.push_back("setup d" + std::to_string(d)); }
+            s.ostat = c.ostat.as<unsigned long long>(); s.ostat_stride = ostat_stride; s.ticket = reinterpret_cast<uint32_t*>(s.ostat + ostat_stride * ostat_passes);
+            CK(cudaMemsetAsync(c.ostat.p, 0, ostat_bytes, cs));
             k_setup<<<small_grid, 256, 0, cs>>>(sc, s); CK(cudaGetLastError());
             if (conc) CK(cudaEventRecord(c.evSetup[hs], cs));
             tm.end(2);
@@ -949,7 +984,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
                     ShadowPlan sp{};
                     sp.list0 = s.shidx; sp.list1 = use_lists ? c.shidx2[hs].as<uint32_t>() : nullptr; sp.cap = cap;
                     sp.n0 = use_lists ? cd + 4 : cd + 3; sp.n0_stride = use_lists ? 1 : 0;      // per-light list lengths n_sh[j], or the hit count
-                    sp.work = wk + nsch; sp.npass = wk + nsch + (size_t)L * kMaxPass;
+                    sp.work = wk + nsch; sp.rn = wk + nsch + (size_t)L * kMaxPass; sp.nreg = sh_np > 1 ? nreg : 0;
                     if (conc) for (int k = 0; k < nls; ++k) CK(cudaStreamWaitEvent(c.lightStream[k], c.evSetup[hs], 0));
                     for (int j = 0; j < L; ++j) {
                         const int f0 = tln;
@@ -1000,7 +1035,9 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
                 if (d == 0) out.primary += cd[0]; else out.bounce += (cd - cps)[3];       // queue of depth d = hit list of depth d-1
                 out.shadow += (uint64_t)cd[3] * (uint64_t)L;
             }
-        unsigned long long slow[4] = {0, 0, 0, 0}; CK(cudaMemcpy(slow, c.slow.p, sizeof(slow), cudaMemcpyDeviceToHost));
+        unsigned long long slow[24] = {}; CK(cudaMemcpy(slow, c.slow.p, sizeof(slow), cudaMemcpyDeviceToHost));
+        if (getenv("B200RT_DEBUG_CULL")) fprintf(stderr, "[cull] shadow first-pass groups %llu, kap<0.1: %llu\n", slow[22], slow[23]);
+        if (getenv("B200RT_DEBUG_CULL")) for (int m = 0; m < 3; ++m) fprintf(stderr, "[cull] mode %d groups %llu beam_ok %llu kept_pairs %llu of %llu  kap<0.1: %llu  and ro<1: %llu\n", m, slow[4 + 6 * m], slow[5 + 6 * m], slow[6 + 6 * m], slow[7 + 6 * m], slow[8 + 6 * m], slow[9 + 6 * m]);
         out.slow_path = slow[0]; out.exact_tests = slow[1]; out.tests_pivot = slow[2]; out.tests_general = slow[3];   // counted by k_isect3
         CK(cudaEventElapsedTime(&out.kernel_ms[0], ev0, ev1));
         out.kernel_ms[1] = tm.total(0); out.kernel_ms[2] = tm.total(1); out.kernel_ms[3] = tm.total(2);

@@ -38,15 +38,18 @@ struct QueueDev {
     const float4* rayO; const float4* rayD;
     // shadow input: hit records
     const float4* hP;                    // (biased hit point, slot)
-    const uint32_t* n_in;                // number of rays (closest) / entries of in_list or hit records (shadow)
+    const uint32_t* n_in;                // number of rays (closest) / entries of the light's list = input of its FIRST pass (shadow)
     uint32_t* work;                      // dynamic group counter (zeroed before the launch)
     unsigned long long* hit;             // closest-hit output, queue order: (float bits of t) << 32 | id; pre-set to kNoHit
     uint8_t* occl; size_t ocap;          // shadow output, [light][hit] with row stride ocap; pre-set to 0 (k_isect3 stores only 1s)
     const uint32_t* in_list;             // k_isect3 shadow input: hit records to query for this light (null: every hit record, identity map)
     // k_isect3 shadow passes: a query scans the light's table (spheres sorted by decreasing solid angle seen from the
     // light) in several launches over consecutive ranges; rays found occluded are done, the others are appended to
-    // out_list (hit-record indices, counter out_n) = the next pass's input.  Null on the last pass.
-    uint32_t* out_list; uint32_t* out_n;
+    // out_list (hit-record indices) = the next pass's input.  To keep neighbouring rays together without a global
+    // ordered compaction, survivors are compacted per REGION: the kRegion consecutive entries [sg*kRegion, (sg+1)*kRegion)
+    // of the first pass's list keep that slot range in every later list, filled from its start (out_rn[sg] = fill
+    // count, zeroed before the frame).  A later pass (in_rn != null) walks the regions' filled parts.  Null on the last pass.
+    uint32_t* out_list; uint32_t* out_rn; const uint32_t* in_rn;
     int last;                            // this launch covers the end of the sphere array: planes are tested here (set by the launcher)
     unsigned long long* slow;            // diagnostic: thread-level slow-path entries (may be null)
     unsigned long long* tl;              // diagnostic (B200RT_TIMELINE): [0] first CTA start, [1] last CTA end, globaltimer ns (may be null)
@@ -106,6 +109,7 @@ __device__ __forceinline__ float fmax3(float a, float b, float c) {
 // (float bits of t << 32 | sphere id) — min t, and on equal t the lowest index, which is the reference's tie-break
 // (first object wins, trace.py:26; planes have ids >= S and so lose ties against spheres, trace.py:36).
 constexpr int KP = 4;                    // sphere pairs per scan step (8 spheres)
+constexpr uint32_t kRegion = 2048;       // entries per survivor-list region (8 ray groups of 256)
 constexpr int kQCap = 768;               // candidate queue entries per warp
 constexpr int kQFlush = kQCap - 32 * 16; // flush before an append (<= 16 per lane) could overflow
 constexpr unsigned long long kNoHit = kNoHitKey;                                                 // (999.0f, id -1)
@@ -132,7 +136,8 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
     const bool last = q.last != 0;
     const uint32_t n_in = *q.n_in;
     const uint32_t* shl = ANY ? q.in_list : nullptr;          // list entry -> hit record
-    const uint32_t ngroups = (n_in + GW - 1) / GW;
+    const bool regions = ANY && q.in_rn != nullptr;
+    const uint32_t ngroups = regions ? ((n_in + kRegion - 1) / kRegion) * (kRegion / GW) : (n_in + GW - 1) / GW;   // work items
     const int npair = cnt >> 1;
     const float cmax = pv.bounds[0], rmax = pv.bounds[1];
     const float kInf = __int_as_float(0x7f800000);
@@ -149,7 +154,12 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
     uint32_t* work = q.work;
 
     auto run_group = [&](const uint32_t g) {
-        const uint32_t gbase = g * (uint32_t)GW;
+        uint32_t gbase = g * (uint32_t)GW, nlim = n_in;       // this group's rays: list entries [gbase, min(gbase + GW, nlim))
+        if (regions) {
+            const uint32_t sg = g / (kRegion / GW), k = g % (kRegion / GW);
+            gbase = sg * kRegion + k * (uint32_t)GW; nlim = sg * kRegion + q.in_rn[sg];
+            if (__all_sync(0xffffffffu, gbase >= nlim)) return;
+        }
 
         // ---- per-ray constants.  Computed ray by ray by ONE copy of the code (iteration k: ray k*32 + lane of the
         // group) and staged in shared memory: unrolled over the thread's rays this prologue was a third of the
@@ -158,7 +168,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
 #pragma unroll 1
         for (int k = 0; k < NR; ++k) {
             const uint32_t rl = (uint32_t)k * 32u + lane, i = gbase + rl;
-            const bool active = i < n_in;
+            const bool active = i < nlim;
             V3 O = mk(0.f, 0.f, 0.f), D = mk(0.f, 0.f, 0.f);
             float th = kInf, no = 0.f;
             uint32_t hrec = 0;
@@ -300,13 +310,20 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
         // the exact test's rounding bound), so the image does not change; B200RT_F_NO_CULL switches it off.  Survivors
         // are listed per PAIR of table positions and scanned through the list (operands from the constant table with a
         // computed index instead of uniform registers); wide beams and poor cull rates take the dense scan. ----
+        if (q.slow && lane == 0) atomicAdd(q.slow + 4 + 6 * MODE, 1ull);                      // dbg: groups
+        if (q.slow && ANY && !regions) {                      // dbg: spread of hit-record indices and pixel slots within a first-pass group
+            uint32_t hmin = 0xffffffffu, hmax = 0, smin = 0xffffffffu, smax = 0;
+            for (int r = 0; r < NR; ++r) { if (gbase + (uint32_t)r * 32u + lane >= nlim) continue; const float4 oo = ws.o[r * 32 + lane]; const uint32_t hr = __float_as_uint(oo.w); const uint32_t sl = __float_as_uint(q.hP[hr].w); hmin = min(hmin, hr); hmax = max(hmax, hr); smin = min(smin, sl); smax = max(smax, sl); }
+            hmin = __reduce_min_sync(0xffffffffu, hmin); hmax = __reduce_max_sync(0xffffffffu, hmax); smin = __reduce_min_sync(0xffffffffu, smin); smax = __reduce_max_sync(0xffffffffu, smax);
+            if (lane == 0) { atomicAdd(q.slow + 20, (unsigned long long)(hmax - hmin)); atomicAdd(q.slow + 21, (unsigned long long)(smax - smin)); }
+        }
         int ns = -1, nsr = 0;                                 // ns >= 0: sparse scan over slist[0..ns), the first nsr entries real
         uint16_t* slist = reinterpret_cast<uint16_t*>(MODE == 2 ? (void*)ws.ki : MODE == 0 ? (void*)ws.thr : (void*)ws.o);   // 1 KB free in every mode
         if (pv.rad && npair <= 32 * NR * 2 && npair >= 64) {
             float ax = 0.f, ay = 0.f, az = 0.f, bx = 0.f, by = 0.f, bz = 0.f, na = 0.f;
 #pragma unroll
             for (int r = 0; r < NR; ++r) {
-                if (gbase + (uint32_t)r * 32u + lane >= n_in) continue;
+                if (gbase + (uint32_t)r * 32u + lane >= nlim) continue;
                 na += 1.f; bx += dx[r]; by += dy[r]; bz += dz[r];
                 if (MODE == 0) { ax += 0.5f * o2x[PIV ? 0 : r]; ay += 0.5f * o2y[PIV ? 0 : r]; az += 0.5f * o2z[PIV ? 0 : r]; }
                 if (MODE == 2) { const float4 oo = ws.o[r * 32 + lane]; ax += oo.x; ay += oo.y; az += oo.z; }
@@ -325,7 +342,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
                 float ro2 = 0.f, kap2 = 0.f;
 #pragma unroll
                 for (int r = 0; r < NR; ++r) {
-                    if (gbase + (uint32_t)r * 32u + lane >= n_in) continue;
+                    if (gbase + (uint32_t)r * 32u + lane >= nlim) continue;
                     const float ex = dx[r] - Dc.x, ey = dy[r] - Dc.y, ez = dz[r] - Dc.z;
                     kap2 = fmaxf(kap2, ex * ex + ey * ey + ez * ez);
                     if (MODE == 0) { const float fx = 0.5f * o2x[PIV ? 0 : r] - Oc.x, fy = 0.5f * o2y[PIV ? 0 : r] - Oc.y, fz = 0.5f * o2z[PIV ? 0 : r] - Oc.z; ro2 = fmaxf(ro2, fx * fx + fy * fy + fz * fz); }
@@ -334,6 +351,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
 #pragma unroll
                 for (int d = 16; d > 0; d >>= 1) { ro2 = fmaxf(ro2, __shfl_xor_sync(0xffffffffu, ro2, d)); kap2 = fmaxf(kap2, __shfl_xor_sync(0xffffffffu, kap2, d)); }
                 const float kap = __fsqrt_rn(kap2) * 1.0001f + 1e-6f;
+                if (q.slow && lane == 0) { atomicAdd(q.slow + 5 + 6 * MODE, 1ull); if (ANY && !regions) { atomicAdd(q.slow + 22, 1ull); if (kap < 0.1f) atomicAdd(q.slow + 23, 1ull); } if (MODE != 2) { if (kap < 0.1f) atomicAdd(q.slow + 8 + 6 * MODE, 1ull); if (kap < 0.1f && ro2 < 1.f) atomicAdd(q.slow + 9 + 6 * MODE, 1ull); } }
                 if (__all_sync(0xffffffffu, kap < 0.6f)) {
                     const float osz = cmax + __fsqrt_rn(dot3(Oc, Oc));
                     const float ro = __fsqrt_rn(ro2) * 1.0001f + 1e-6f * osz;
@@ -365,6 +383,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
                         if (keep) slist[nsv + (uint32_t)__popc(bal & ((1u << lane) - 1u))] = (uint16_t)p;
                         nsv += (uint32_t)__popc(bal);
                     }
+                    if (q.slow && lane == 0) { atomicAdd(q.slow + 6 + 6 * MODE, (unsigned long long)nsv); atomicAdd(q.slow + 7 + 6 * MODE, (unsigned long long)npair); }
                     if (__all_sync(0xffffffffu, 2 * (int)nsv <= npair)) {      // worth it (the list path costs ~1.5x per test)
                         __syncwarp();
                         const uint16_t padv = nsv ? slist[nsv - 1] : (uint16_t)0;      // padding: the last pair again (never queued twice)
@@ -447,7 +466,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
 #pragma unroll 1
         for (int k = 0; k < NR; ++k) {
             const uint32_t rl = (uint32_t)k * 32u + lane, i = gbase + rl;
-            if (i >= n_in) continue;
+            if (i >= nlim) continue;
             const float4 dd = ws.d[rl];
             const V3 D = mk(dd.x, dd.y, dd.z);
             if (ANY) {
@@ -474,10 +493,10 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
                 if (bid >= 0) atomicMin(&q.hit[i], ((unsigned long long)__float_as_uint(best) << 32) | (uint32_t)bid);
             }
         }
-        if (ANY && q.out_list) {                              // survivors -> next pass's list, in queue order
+        if (ANY && q.out_list) {                              // survivors -> next pass's list: appended to their region, in group order
             const uint32_t total = __reduce_add_sync(0xffffffffu, (uint32_t)__popc(surv));
             uint32_t base = 0;
-            if (lane == 0 && total) base = atomicAdd(q.out_n, total);
+            if (lane == 0 && total) base = (gbase / kRegion) * kRegion + atomicAdd(&q.out_rn[gbase / kRegion], total);
             base = __shfl_sync(0xffffffffu, base, 0);
 #pragma unroll 1
             for (int k = 0; k < NR; ++k) {
@@ -572,7 +591,8 @@ constexpr int kMaxPass = 32;
 struct ShadowPlan {                                  // one depth's shadow state (device pointers)
     uint32_t* list0; uint32_t* list1; size_t cap;    // [L][cap] k_setup's lists (null: dense layout, every hit record) and the second buffer
     const uint32_t* n0; int n0_stride;               // list lengths from k_setup: n0[j * n0_stride]  (dense: the hit count, stride 0)
-    uint32_t* npass; uint32_t* work;                 // [L][kMaxPass] zeroed: survivor counters, group counters
+    uint32_t* work;                                  // [L][kMaxPass] zeroed group counters
+    uint32_t* rn; size_t nreg;                       // [L][kMaxPass][nreg] zeroed region fill counts of the survivor lists (nreg = ceil(cap / kRegion))
 };
 
 // Sphere ranges [c0, c0+cnt) of the passes.  Small scenes: one pass.  (resident or not, a pass fits the constant table.)
@@ -604,12 +624,13 @@ static cudaError_t isect3_launch_shadow_light(const IsectCfg& cfg, const SceneDe
         const bool lastp = (p == np - 1);
         q.in_list = in; q.n_in = n_in; q.work = sp.work + (size_t)j * kMaxPass + p; q.last = lastp ? 1 : 0;
         q.out_list = lastp ? nullptr : ((p & 1) ? sp.list0 : sp.list1) + (size_t)j * sp.cap;
-        q.out_n = lastp ? nullptr : sp.npass + (size_t)j * kMaxPass + p;
+        q.in_rn = p == 0 ? nullptr : sp.rn + ((size_t)j * kMaxPass + (p - 1)) * sp.nreg;
+        q.out_rn = lastp ? nullptr : sp.rn + ((size_t)j * kMaxPass + p) * sp.nreg;
         if (!resident && (e = cudaMemcpyToSymbolAsync(c_tab, pv.tab + (size_t)j * sc.Spad + c0, sizeof(float4) * cnt, 0,
                                                       cudaMemcpyDeviceToDevice, st)) != cudaSuccess) return e;
         if (tlbase) q.tl = tlbase + 2 * (size_t)((*tlnext)++);
         if ((e = isect3_launch_one<MODE>(cfg, sc, q, pv, max_rays, c0, cnt, j, resident ? j * sc.Spad + c0 : 0, st)) != cudaSuccess) return e;
-        in = q.out_list; n_in = q.out_n;
+        in = q.out_list;
     }
     return cudaSuccess;
 }

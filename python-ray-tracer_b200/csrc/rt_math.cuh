@@ -131,4 +131,60 @@ __device__ __forceinline__ void block_append8(uint32_t flags, int nq, uint32_t* 
     __syncthreads();
 }
 
+
+// Ordered multi-queue append ("decoupled look-back" compaction).  Chunk c (256 consecutive input items, chunks claimed
+// in ticket order) appends its items to up to 8 queues so that every queue keeps the INPUT order across the whole
+// launch — not just within a CTA as block_append8 does.  Neighbouring pixel tiles then stay neighbours in every
+// compacted list, which is what keeps a ray group of k_isect3 a narrow beam at every depth.
+// status: [chunk][8] 64-bit words, zeroed before the launch; bits 62-63: 1 = this chunk's count, 2 = inclusive prefix.
+// Warp q of the CTA owns queue q: it publishes the chunk's count, sums its predecessors' (32 at a time, spinning only
+// on chunks that are already running — tickets are handed out in order), then publishes the inclusive prefix.
+// The chunk with is_last stores the queue lengths to counters[0..nq).  Contains __syncthreads(); 256-thread CTAs.
+__device__ __forceinline__ void ordered_append8(uint32_t flags, int nq, uint32_t c, unsigned long long* status,
+                                                uint32_t* counters, bool is_last, uint32_t (&pos)[8]) {
+    __shared__ uint32_t s_cnt8[8][8];      // [queue][warp]
+    __shared__ uint32_t s_base8[8];
+    const uint32_t wid = threadIdx.x >> 5, lane = lane_id(), lt = (1u << lane) - 1u;
+    uint32_t mask[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        mask[j] = (j < nq) ? __ballot_sync(0xffffffffu, (flags >> j) & 1u) : 0u;
+        if (j < nq && lane == 0) s_cnt8[j][wid] = (uint32_t)__popc(mask[j]);
+    }
+    __syncthreads();
+    if ((int)wid < nq) {
+        const int qi = (int)wid;
+        const uint32_t v = lane < 8 ? s_cnt8[qi][lane] : 0u;
+        uint32_t x = v;
+#pragma unroll
+        for (int d = 1; d < 8; d <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, d); if ((int)lane >= d) x += y; }
+        const uint32_t total = __shfl_sync(0xffffffffu, x, 7);
+        if (lane < 8) s_cnt8[qi][lane] = x - v;                       // exclusive offset of each warp within the chunk
+        unsigned long long* st = status + (size_t)c * 8 + qi;
+        uint32_t excl = 0;
+        if (c == 0) { if (lane == 0) atomicExch(st, (2ull << 62) | total); }
+        else {
+            if (lane == 0) atomicExch(st, (1ull << 62) | total);
+            for (long long p = (long long)c - 1;; p -= 32) {
+                const long long idx = p - (long long)lane;
+                unsigned long long w = 2ull << 62;                    // before chunk 0: inclusive prefix 0
+                if (idx >= 0) {
+                    const volatile unsigned long long* sp = status + (size_t)idx * 8 + qi;
+                    do { w = *sp; } while ((w >> 62) == 0ull);
+                }
+                const uint32_t incl = __ballot_sync(0xffffffffu, (w >> 62) == 2ull);
+                const int first = incl ? __ffs(incl) - 1 : 32;
+                excl += __reduce_add_sync(0xffffffffu, (int)lane <= first ? (uint32_t)w : 0u);
+                if (incl) break;
+            }
+            if (lane == 0) atomicExch(st, (2ull << 62) | (unsigned long long)(excl + total));
+        }
+        if (lane == 0) { s_base8[qi] = excl; if (is_last) counters[qi] = excl + total; }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < 8; ++j) pos[j] = (j < nq) ? s_base8[j] + s_cnt8[j][wid] + (uint32_t)__popc(mask[j] & lt) : 0u;
+    __syncthreads();
+}
+
 }  // namespace b200rt
