@@ -670,7 +670,7 @@ struct DevCtx {
     Buf rayO[2], rayD[2], hitKey[2];                               // ray queues, double-buffered by depth parity
     Buf hP[kSets], hN[kSets], occl[kSets], shidx[kSets], shidx2[kSets];   // hit records / shadow state: ring of kSets depths
     Buf acc, ctr, work, slow, tl, ostat;
-    int npre = 2, pre[6] = {128, 256, 0, 0, 0, 0};                  // leading shadow passes (env B200RT_PASSES=a,b,...; multiples of 8)
+    int npre = 1, pre[6] = {256, 0, 0, 0, 0, 0};                    // leading shadow passes (env B200RT_PASSES=a,b,...; multiples of 8)
     bool timeline = false;                                        // env B200RT_TIMELINE: per-launch first-start / last-end (globaltimer) to stderr
     // internal streams (see the launch sequence in render_device): the dependent chain at high priority, one stream per
     // light (up to kSide) for the shadow queries, one for the shading
