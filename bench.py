@@ -257,14 +257,17 @@ def run_ours(args, w):
         nominal_tf = 2.0 * 128 * sms * sm_max * 1e6 / 1e12
         fpr = flops_per_ray(S, Pl)
         traffic, traffic_src = None, None          # ncu dram bytes of the k_isect3 launches of one frame (committed capture, 1 GPU, C4)
-        tp = os.path.join(ROOT, "profiles", "r01_v3_traffic.json")
+        tp = os.path.join(ROOT, "profiles", "r01_v6_traffic.json")
         if os.path.exists(tp) and args.workload == "c4" and world == 1:
             tj = json.load(open(tp))
-            traffic, traffic_src = tj["traffic_bytes_per_frame"], "profiles/r01_v3_traffic.json (ncu dram__bytes_read+write, 16 k_isect3 launches of one frame)"
+            traffic, traffic_src = tj["traffic_bytes_per_frame"], "profiles/r01_v6_traffic.json (ncu dram__bytes_read+write, the 28 k_isect3 launches of one frame)"
         ach_tf = rays_this_rank * fpr / (isect_ms * 1e-3) / 1e12
         clocks = sampler.summary()
         depth = w["refl_depth"]
-        launches_per_frame = 3 + (depth + 1) * (3 + L) + 1        # pack, pivot, raygen, per depth closest/setup/shadow/shade, resolve
+        spad = max(8, (S + 7) & ~7)
+        shadow_passes = 2 if spad >= 512 else 1                   # csrc/isect3.cuh shadow_passes(): 256 spheres, then the rest
+        # pack, rank, pivot, raygen; per depth: closest hit, setup, L lights x passes, shade; resolve
+        launches_per_frame = 4 + (depth + 1) * (3 + L * shadow_passes) + 1
         line = {
             "metric": "Mrays/s", "value": rays_total / (ms_step * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
