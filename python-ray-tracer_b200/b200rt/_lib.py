@@ -5,7 +5,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200rt.so")
 
-F_SCENE_ON_HOST, F_NO_FILTER, F_UNSWAP_GB = 0x1, 0x2, 0x4
+F_SCENE_ON_HOST, F_NO_FILTER, F_UNSWAP_GB, F_NO_CULL = 0x1, 0x2, 0x4, 0x8
 
 
 class Grid(C.Structure):

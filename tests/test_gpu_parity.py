@@ -211,3 +211,27 @@ def test_batch_equals_single_frames():
         assert np.array_equal(got[k], render_frame(scene, cam, 0.0, 0.6, 0.3, 2, False)), k
     two = render_batch(scene, cams, 0.0, 0.6, 0.3, 2, False, devices=[0, 0])      # two host threads, one device
     assert np.array_equal(two, got)
+
+
+@pytest.mark.parametrize("S,L,W,H,depth,aa", [(1024, 3, 512, 256, 3, False),    # C4-like: shadow passes, beam culling, look-back over 512 chunks
+                                              (700, 2, 272, 144, 2, True),      # anti-aliased: ordered compaction of the primary queue (border samples skipped)
+                                              (600, 9, 208, 112, 1, False)])    # more than 7 lights: two compaction rounds per chunk
+def test_culling_and_passes_do_not_change_the_image(oracle, S, L, W, H, depth, aa):
+    """Work the kernel proves unnecessary and skips (shadow passes over the sorted light tables, beam culling, the
+    regions of the survivor lists) must leave every byte as the exact-test-on-every-sphere path writes it, at a size
+    where queues span hundreds of 256-ray chunks (ordered compaction with look-back, several regions per list)."""
+    from b200rt import _lib
+    g = _synthetic(S, L, 1, W, H, depth, aa, seed=S + 7 * L)
+    got, st = _cuda(g, stats=True)
+    nocull, st_nc = _cuda(g, flags=_lib.F_NO_CULL, stats=True)
+    assert np.array_equal(got, nocull), "beam culling changed the image"
+    assert np.array_equal(got, _cuda(g, flags=_lib.F_NO_FILTER)), "filtered path differs from exact-test-on-everything"
+    assert st["rays"] == st_nc["rays"]
+    canonical = st["rays"] * S
+    executed, executed_nc = st["tests_pivot"] + st["tests_general"], st_nc["tests_pivot"] + st_nc["tests_general"]
+    print(dict(S=S, L=L, canonical=canonical, executed=executed, executed_no_cull=executed_nc))
+    assert executed < executed_nc <= 1.1 * canonical + 8 * 256 * S        # (padding and partially filled groups count as executed)
+    x0, y0 = W // 3, H // 4
+    ref = oracle.render(None, *_args(g), grid=g["grid"], shape=(W, H), x_range=(x0, x0 + 64), y_range=(y0, y0 + 64))[:, x0:x0 + 64, y0:y0 + 64]
+    rep = parity_report(got[:, x0:x0 + 64, y0:y0 + 64], ref)
+    assert rep["n_bad"] <= _budget(rep["n"]), rep
