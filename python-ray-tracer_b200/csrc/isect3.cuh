@@ -370,18 +370,23 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
                         return (tn < 0.f) ? (lhs > 0.f) : (lhs * kk > tn * tn * 1.0002f + 1e-3f);
                     };
                     uint32_t nsv = 0;
-                    for (int p0 = 0; p0 < npair; p0 += 32) {
-                        const int p = p0 + (int)lane;
-                        bool keep = false;
-                        if (p < npair) {
-                            const float4 uu = __ldg(gt + 2 * p), ww = __ldg(gt + 2 * p + 1);
-                            const float2 rr = __ldg(gr + p);
-                            keep = (c0 + 2 * p < sc.S && !clear_of_beam(uu.x, uu.z, ww.x, rr.x)) ||
-                                   (c0 + 2 * p + 1 < sc.S && !clear_of_beam(uu.y, uu.w, ww.y, rr.y));
+                    for (int p0 = 0; p0 < npair; p0 += 128) {                // 4 pairs per lane per round: their loads go out together
+                        float4 uu[4], ww[4]; float2 rr[4];
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const int p = min(p0 + e * 32 + (int)lane, npair - 1);
+                            uu[e] = __ldg(gt + 2 * p); ww[e] = __ldg(gt + 2 * p + 1); rr[e] = __ldg(gr + p);
                         }
-                        const uint32_t bal = __ballot_sync(0xffffffffu, keep);
-                        if (keep) slist[nsv + (uint32_t)__popc(bal & ((1u << lane) - 1u))] = (uint16_t)p;
-                        nsv += (uint32_t)__popc(bal);
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const int p = p0 + e * 32 + (int)lane;
+                            const bool keep = p < npair &&
+                                ((c0 + 2 * p < sc.S && !clear_of_beam(uu[e].x, uu[e].z, ww[e].x, rr[e].x)) ||
+                                 (c0 + 2 * p + 1 < sc.S && !clear_of_beam(uu[e].y, uu[e].w, ww[e].y, rr[e].y)));
+                            const uint32_t bal = __ballot_sync(0xffffffffu, keep);
+                            if (keep) slist[nsv + (uint32_t)__popc(bal & ((1u << lane) - 1u))] = (uint16_t)p;
+                            nsv += (uint32_t)__popc(bal);
+                        }
                     }
                     if (q.slow && lane == 0) { atomicAdd(q.slow + 6 + 6 * MODE, (unsigned long long)nsv); atomicAdd(q.slow + 7 + 6 * MODE, (unsigned long long)npair); }
                     if (__all_sync(0xffffffffu, 2 * (int)nsv <= npair)) {      // worth it (the list path costs ~1.5x per test)
@@ -396,28 +401,14 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
         }
         if (__all_sync(0xffffffffu, ns >= 0)) {
             if (q.slow) tests_cnt += (unsigned long long)ns * 2ull * (unsigned long long)NR;
-            for (int pb = 0; pb < ns; pb += KP) {
-                float mk4[KP]; int pi[KP];
-#pragma unroll
-                for (int k = 0; k < KP; ++k) {
-                    pi[k] = slist[pb + k];
-                    const float4 u = c_tab[tb + 2 * pi[k]], w = c_tab[tb + 2 * pi[k] + 1];
-                    float m = -3.0e38f;
-#pragma unroll
-                    for (int r = 0; r < NR; ++r) { const float2 qv = qray(r, u, w); m = fmax3(m, qv.x, qv.y); }
-                    mk4[k] = m;
-                }
-                const float mall = fmaxf(fmaxf(mk4[0], mk4[1]), fmaxf(mk4[2], mk4[3]));
-                if (__any_sync(0xffffffffu, mall >= thr_t)) {
-                    slow_cnt++;
 #pragma unroll 1
-                    for (int k = 0; k < KP; ++k) {
-                        float mv = mk4[0]; int pv_ = pi[0];
+            for (int pb = 0; pb < nsr; ++pb) {                 // one listed pair per iteration: small code, the lists are short
+                const int pi = slist[pb];
+                const float4 u = c_tab[tb + 2 * pi], w = c_tab[tb + 2 * pi + 1];
+                float m = -3.0e38f;
 #pragma unroll
-                        for (int kk2 = 1; kk2 < KP; ++kk2) { mv = (k == kk2) ? mk4[kk2] : mv; pv_ = (k == kk2) ? pi[kk2] : pv_; }
-                        if (pb + k < nsr && __any_sync(0xffffffffu, mv >= thr_t)) slow_pair(pv_);
-                    }
-                }
+                for (int r = 0; r < NR; ++r) { const float2 qv = qray(r, u, w); m = fmax3(m, qv.x, qv.y); }
+                if (__any_sync(0xffffffffu, m >= thr_t)) { slow_cnt++; slow_pair(pi); }
             }
         } else {
         if (q.slow) tests_cnt += (unsigned long long)npair * 2ull * (unsigned long long)NR;
