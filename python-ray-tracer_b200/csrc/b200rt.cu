@@ -314,10 +314,11 @@ k_intersect(SceneDev sc, QueueDev q) {
 // (C4: half of all shadow rays are occluded, 90 % of those by one of the first 120-350 spheres of 1024).  Any order
 // gives the same image: a shadow query only asks WHETHER something is hit (trace.py:92-96).  One thread per
 // (light j, sphere s): rank by counting (S is a few thousand at most); padding entries go last.
-__global__ void k_rank(SceneDev sc, int* perm) {
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    const int j = idx / sc.Spad, s = idx - j * sc.Spad;
-    if (j >= sc.L) return;
+__global__ void __launch_bounds__(256) k_rank(SceneDev sc, int* perm) {
+    // grid = (ceil(Spad / 256), L); the keys of 1024 spheres at a time go through shared memory (one division per key
+    // per CTA instead of one per comparison)
+    __shared__ float skey[1024];
+    const int j = blockIdx.y, s = blockIdx.x * blockDim.x + threadIdx.x;
     const float4 v = sc.lights[j];
     auto key = [&](int t) -> float {
         if (t >= sc.S) return -1.f;
@@ -327,8 +328,14 @@ __global__ void k_rank(SceneDev sc, int* perm) {
     };
     const float ks = key(s);
     int rank = 0;
-    for (int t = 0; t < sc.Spad; ++t) { const float kt = key(t); rank += (kt > ks || (kt == ks && t < s)) ? 1 : 0; }
-    perm[(size_t)j * sc.Spad + rank] = s;
+    for (int t0 = 0; t0 < sc.Spad; t0 += 1024) {
+        __syncthreads();
+        for (int t = threadIdx.x; t < 1024; t += blockDim.x) skey[t] = key(t0 + t);      // (t0 + t >= Spad: key -1 and index beyond s: never counted twice)
+        __syncthreads();
+        const int n = min(1024, sc.Spad - t0);
+        for (int t = 0; t < n; ++t) { const float kt = skey[t]; rank += (kt > ks || (kt == ks && t0 + t < s)) ? 1 : 0; }
+    }
+    if (s < sc.Spad) perm[(size_t)j * sc.Spad + rank] = s;
 }
 
 // One thread per (table j, pair i of table positions): k = r^2 - |C-V_j|^2 (j <= L) or r^2 - |C|^2 (j == L+1), float64
@@ -378,7 +385,7 @@ struct ShadeDev {
 };
 
 // trace.py:56-83: miss -> path ends; hit -> P = O + tD, colour/normal by object type, P += BIAS*N.
-__global__ void k_setup(SceneDev sc, ShadeDev s) {
+__global__ void __launch_bounds__(256, 6) k_setup(SceneDev sc, ShadeDev s) {
     if (s.tl && threadIdx.x == 0) atomicMin(s.tl, globaltimer_ns());
     const uint32_t n = *s.n_live;
     const uint32_t nchunks = (n + 255u) / 256u;
@@ -831,7 +838,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     {
         const int n = (L + 2) * (Spad / 2);
         CK(c.pivPerm.ensure(sizeof(int) * std::max<size_t>((size_t)L * Spad, 1))); CK(c.pivRad.ensure(sizeof(float) * (size_t)(L + 2) * Spad));
-        if (L > 0) { k_rank<<<(L * Spad + 255) / 256, 256, 0, st>>>(sc, c.pivPerm.as<int>()); CK(cudaGetLastError()); }
+        if (L > 0) { k_rank<<<dim3((Spad + 255) / 256, L), 256, 0, st>>>(sc, c.pivPerm.as<int>()); CK(cudaGetLastError()); }
         k_pivot<<<(n + 255) / 256, 256, 0, st>>>(sc, (float)a->cam_origin[0], (float)a->cam_origin[1], (float)a->cam_origin[2],
                                                  c.pivPerm.as<int>(), c.pivTab.as<float4>(), c.pivPos.as<float4>(), c.pivRad.as<float>());
         CK(cudaGetLastError());
