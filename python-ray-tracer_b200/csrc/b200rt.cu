@@ -391,7 +391,10 @@ __global__ void __launch_bounds__(256, 6) k_setup(SceneDev sc, ShadeDev s) {
     const uint32_t nchunks = (n + 255u) / 256u;
     __shared__ uint32_t s_chunk;
     for (;;) {
-        if (threadIdx.x == 0) s_chunk = atomicAdd(s.ticket, 1u);      // chunks in ticket order (ordered_append8 spins on predecessors)
+        // Chunks in ticket order (ordered_append8 spins on predecessors).  The ticket is taken only when the CTA is
+        // ready to work on it: prefetching the next ticket during the current chunk tripled the frame time (every
+        // successor then waits for a chunk whose owner is still busy with the one before).
+        if (threadIdx.x == 0) s_chunk = atomicAdd(s.ticket, 1u);
         __syncthreads();
         const uint32_t c = s_chunk;
         if (c >= nchunks) break;
@@ -422,8 +425,15 @@ __global__ void __launch_bounds__(256, 6) k_setup(SceneDev sc, ShadeDev s) {
             if (hit) {
                 for (int jj = 0; jj < nl; ++jj) {
                     const float4 l = __ldg(&sc.lights[j0 + jj]);
-                    const V3 Lv = normalize3(sub3(mk(l.x, l.y, l.z), Pb));
-                    if (__fmul_rn(s.lamb, dot3(Lv, N)) > 0.f) flags |= 1u << (jj + sh);
+                    const V3 dl = sub3(mk(l.x, l.y, l.z), Pb);
+                    // Only the SIGN of k_shade's k = lamb * (normalize(dl) . N) is needed.  It is the sign of dl . N
+                    // whenever that is clearly away from zero (|cos| > 1e-4: the normalised dot differs from
+                    // (dl.N)/|dl| by a few ulp of 1); the rare grazing cases take k_shade's exact arithmetic.
+                    const float dn = dot3(dl, N), dd = dot3(dl, dl);
+                    bool lit;
+                    if (s.lamb > 1e-20f && dn * dn > 1e-8f * dd && dd < 1e30f) lit = dn > 0.f;
+                    else lit = __fmul_rn(s.lamb, dot3(normalize3(dl), N)) > 0.f;
+                    if (lit) flags |= 1u << (jj + sh);
                 }
             }
             uint32_t pos[8];
