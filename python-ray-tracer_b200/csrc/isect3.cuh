@@ -165,17 +165,40 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
         // group) and staged in shared memory: unrolled over the thread's rays this prologue was a third of the
         // kernel's instructions and its instruction-cache misses showed in short launches.  The staged copy also
         // serves the exact tests and the write-back, which therefore read no ray data from global memory. ----
+        // Phase A issues every global load of the group before anything waits on one (two dependent loads per
+        // shadow ray: list entry -> hit record); the raw records pass through the staging arrays to phase B.
+        // The loads are unconditional (index clamped to the group's last ray) so that they are issued back to back.
+        {
+            const uint32_t ilast = nlim - 1u;                  // nlim > gbase here
+            if (MODE == 2) {
+                uint32_t hr[NR]; float4 pp[NR];
+#pragma unroll
+                for (int k = 0; k < NR; ++k) hr[k] = min(gbase + (uint32_t)k * 32u + lane, ilast);
+                if (shl) {
+#pragma unroll
+                    for (int k = 0; k < NR; ++k) hr[k] = shl[hr[k]];
+                }
+#pragma unroll
+                for (int k = 0; k < NR; ++k) pp[k] = q.hP[hr[k]];
+#pragma unroll
+                for (int k = 0; k < NR; ++k) ws.o[k * 32 + lane] = make_float4(pp[k].x, pp[k].y, pp[k].z, __uint_as_float(hr[k]));
+            } else {
+                float4 oo[NR], dd[NR];
+#pragma unroll
+                for (int k = 0; k < NR; ++k) { const uint32_t i = min(gbase + (uint32_t)k * 32u + lane, ilast); oo[k] = q.rayO[i]; dd[k] = q.rayD[i]; }
+#pragma unroll
+                for (int k = 0; k < NR; ++k) { ws.o[k * 32 + lane] = oo[k]; ws.d[k * 32 + lane] = dd[k]; }
+            }
+        }
 #pragma unroll 1
         for (int k = 0; k < NR; ++k) {
             const uint32_t rl = (uint32_t)k * 32u + lane, i = gbase + rl;
             const bool active = i < nlim;
             V3 O = mk(0.f, 0.f, 0.f), D = mk(0.f, 0.f, 0.f);
             float th = kInf, no = 0.f;
-            uint32_t hrec = 0;
             if (active) {
                 if (MODE == 2) {
-                    hrec = shl ? shl[i] : i;
-                    const float4 p = q.hP[hrec];
+                    const float4 p = ws.o[rl];
                     O = mk(p.x, p.y, p.z);
                     const V3 d = sub3(Vp, O);                                   // common.py:84-91
                     const float nrm = __fsqrt_rn(dot3(d, d));
@@ -185,7 +208,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
                     th = -(fmaf(3.8146973e-6f, fmaf(A, A, B * B), fmaf(4.f * e, rmax, 16.f * e * e)) + 1e-12f);
                     no = -dot3(Vp, D);
                 } else {
-                    const float4 o = q.rayO[i], d = q.rayD[i];
+                    const float4 o = ws.o[rl], d = ws.d[rl];
                     O = mk(o.x, o.y, o.z); D = mk(d.x, d.y, d.z);
                     const float oo = dot3(O, O);
                     const float A = cmax + __fsqrt_rn(oo);
@@ -198,8 +221,8 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
             // MODE 0: the per-ray threshold is folded into q (q' = q - thr, one more FFMA2): candidates are q' >= 0
             // (an inactive ray has thr = +inf, so its q' is -inf and never qualifies).
             if (MODE == 0) ws.o[rl] = make_float4(2.f * O.x, 2.f * O.y, 2.f * O.z, -th);
-            if (MODE == 2) ws.o[rl] = make_float4(O.x, O.y, O.z, __uint_as_float(hrec));
-            if (PIV) ws.thr[rl] = th;
+            if (MODE == 2 && !active) ws.o[rl] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (PIV) ws.thr[rl] = th;                          // (MODE 2: ws.o keeps O.xyz and the hit-record index)
             skt[rl] = ANY ? 0u : (uint32_t)(kNoHit >> 32); ski[rl] = 0xffffffffu;
         }
         // the thread's rays r = 0..NR-1 are rays r*32 + lane (32-bit registers, broadcast operands of FFMA2)
@@ -311,12 +334,6 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
         // are listed per PAIR of table positions and scanned through the list (operands from the constant table with a
         // computed index instead of uniform registers); wide beams and poor cull rates take the dense scan. ----
         if (q.slow && lane == 0) atomicAdd(q.slow + 4 + 6 * MODE, 1ull);                      // dbg: groups
-        if (q.slow && ANY && !regions) {                      // dbg: spread of hit-record indices and pixel slots within a first-pass group
-            uint32_t hmin = 0xffffffffu, hmax = 0, smin = 0xffffffffu, smax = 0;
-            for (int r = 0; r < NR; ++r) { if (gbase + (uint32_t)r * 32u + lane >= nlim) continue; const float4 oo = ws.o[r * 32 + lane]; const uint32_t hr = __float_as_uint(oo.w); const uint32_t sl = __float_as_uint(q.hP[hr].w); hmin = min(hmin, hr); hmax = max(hmax, hr); smin = min(smin, sl); smax = max(smax, sl); }
-            hmin = __reduce_min_sync(0xffffffffu, hmin); hmax = __reduce_max_sync(0xffffffffu, hmax); smin = __reduce_min_sync(0xffffffffu, smin); smax = __reduce_max_sync(0xffffffffu, smax);
-            if (lane == 0) { atomicAdd(q.slow + 20, (unsigned long long)(hmax - hmin)); atomicAdd(q.slow + 21, (unsigned long long)(smax - smin)); }
-        }
         int ns = -1, nsr = 0;                                 // ns >= 0: sparse scan over slist[0..ns), the first nsr entries real
         uint16_t* slist = reinterpret_cast<uint16_t*>(MODE == 2 ? (void*)ws.ki : MODE == 0 ? (void*)ws.thr : (void*)ws.o);   // 1 KB free in every mode
         if (pv.rad && npair <= 32 * NR * 2 && npair >= 64) {
