@@ -47,6 +47,7 @@ extern "C" {
 #define B200RT_F_NO_FILTER       0x2u  /* debug: run the exact sphere test on every sphere (must give bit-identical output) */
 #define B200RT_F_UNSWAP_GB       0x4u  /* write channels as R,G,B instead of the reference's R,B,G wiring (common.py:60-63) */
 #define B200RT_F_NO_CULL         0x8u  /* k_isect3 scans every sphere for every ray group (no beam culling); the image is the same */
+#define B200RT_F_NO_SORT         0x10u /* bounce-depth hits stay in pixel order (no regrouping by direction/position bin); the image is the same */
 
 /*
  * Closed form of Camera.generate_pixel_locations() (reference src/scene/camera.py:18-26), evaluated the way

@@ -366,11 +366,146 @@ __global__ void k_pivot(SceneDev sc, float cox, float coy, float coz, const int*
 
 
 // ------------------------------------------------------------------------------------------------
+// Regrouping of the hits of depth >= 1.  The ray queue of a bounce depth is the compacted hit list of the depth
+// before, still in the pixel order of the primary rays: after one reflection neighbouring entries have little in common,
+// their beam (isect3.cuh, beam culling) covers the whole scene and every group scans every sphere.  Before k_setup the
+// hits are therefore binned by (cube-map cell of the REFLECTED direction, grid cell of the hit point): k_setup walks the
+// queue through the resulting permutation, and both its products — the hit records the shadow queries read and the next
+// ray queue — come out in bin order, where 256 consecutive entries share a small region of space and (for the next
+// closest-hit query) a narrow range of directions.  Any order gives the same image: every ray is processed on its
+// own and accumulates into its own slot.  One counting sort per depth: k_key (bin + rank within the bin from a
+// warp-aggregated atomic), k_binsum / k_binscan (exclusive scan of the bin counts), k_perm (scatter).
+// ------------------------------------------------------------------------------------------------
+struct GridDev { float lo[3], inv[3]; int n[3]; int dn; };      // position cells n[0] x n[1] x n[2], direction cells 6 x dn x dn
+struct SortDev {
+    const float4* rayO; const float4* rayD; const unsigned long long* hit; const uint32_t* n_live;
+    const GridDev* grid; uint2* keyb; uint32_t* hist; uint32_t* part; uint32_t* base; uint32_t* perm; uint32_t* n_sorted;
+    int nb; int use_dir;
+};
+
+// Bounding box of the spheres -> position grid with 2^posbits cells, bits handed to the axis with the largest cell.
+__global__ void __launch_bounds__(256) k_grid(SceneDev sc, int posbits, int dn, GridDev* g) {
+    __shared__ float smin[3][256], smax[3][256];
+    float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f};
+    for (int i = threadIdx.x; i < sc.S; i += blockDim.x) {
+        const float4 sp = sc.sphB[i]; const float r = sqrtf(fmaxf(sp.w, 0.f)); const float c[3] = {sp.x, sp.y, sp.z};
+        for (int a = 0; a < 3; ++a) { lo[a] = fminf(lo[a], c[a] - r); hi[a] = fmaxf(hi[a], c[a] + r); }
+    }
+    for (int a = 0; a < 3; ++a) { smin[a][threadIdx.x] = lo[a]; smax[a][threadIdx.x] = hi[a]; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int a = 0; a < 3; ++a) for (int t = 1; t < 256; ++t) { lo[a] = fminf(lo[a], smin[a][t]); hi[a] = fmaxf(hi[a], smax[a][t]); }
+        float ext[3]; int bits[3] = {0, 0, 0};
+        for (int a = 0; a < 3; ++a) { if (!(hi[a] > lo[a])) { lo[a] = 0.f; hi[a] = 1.f; } const float pad = 0.02f * (hi[a] - lo[a]) + 1e-3f; lo[a] -= pad; hi[a] += pad; ext[a] = hi[a] - lo[a]; }
+        for (int b = 0; b < posbits; ++b) {
+            int m = 0; for (int a = 1; a < 3; ++a) if (ext[a] > ext[m]) m = a;
+            bits[m]++; ext[m] *= 0.5f;
+        }
+        for (int a = 0; a < 3; ++a) { g->lo[a] = lo[a]; g->n[a] = 1 << bits[a]; g->inv[a] = (float)(1 << bits[a]) / (hi[a] - lo[a]); }
+        g->dn = dn;
+    }
+}
+
+__global__ void __launch_bounds__(256) k_key(SceneDev sc, SortDev s) {
+    const uint32_t n = *s.n_live;
+    const GridDev g = *s.grid;
+    const uint32_t lane = lane_id();
+    const uint32_t nround = (n + 31u) & ~31u;                     // whole warps stay in the loop (match/shuffle below)
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nround; i += gridDim.x * blockDim.x) {
+        uint32_t b = 0xffffffffu;
+        if (i < n) {
+            const unsigned long long key = s.hit[i];
+            const int id = (int)(uint32_t)key;
+            if (id >= 0) {
+                const float4 o = s.rayO[i], d = s.rayD[i];
+                const float t = __uint_as_float((uint32_t)(key >> 32));
+                const float px = fmaf(t, d.x, o.x), py = fmaf(t, d.y, o.y), pz = fmaf(t, d.z, o.z);
+                uint32_t dc = 0;
+                if (s.use_dir) {                                 // (approximate arithmetic: this only chooses a bin)
+                    float nx, ny, nz;
+                    if (id < sc.S) { const float4 c = __ldg(&sc.sphB[id]); nx = px - c.x; ny = py - c.y; nz = pz - c.z; const float il = rsqrtf(fmaxf(nx * nx + ny * ny + nz * nz, 1e-30f)); nx *= il; ny *= il; nz *= il; }
+                    else           { const float4 nu = __ldg(&sc.plNu[id - sc.S]); nx = nu.x; ny = nu.y; nz = nu.z; }
+                    const float dn2 = 2.f * (d.x * nx + d.y * ny + d.z * nz);
+                    const float rx = d.x - dn2 * nx, ry = d.y - dn2 * ny, rz = d.z - dn2 * nz;
+                    const float ax = fabsf(rx), ay = fabsf(ry), az = fabsf(rz);
+                    float m, u, v; uint32_t face;
+                    if (ax >= ay && ax >= az) { m = ax; u = ry; v = rz; face = rx < 0.f ? 1u : 0u; }
+                    else if (ay >= az)        { m = ay; u = rx; v = rz; face = ry < 0.f ? 3u : 2u; }
+                    else                      { m = az; u = rx; v = ry; face = rz < 0.f ? 5u : 4u; }
+                    const float im = 0.5f * (float)g.dn / fmaxf(m, 1e-30f);
+                    const int iu = min(g.dn - 1, max(0, (int)(u * im + 0.5f * (float)g.dn)));
+                    const int iv = min(g.dn - 1, max(0, (int)(v * im + 0.5f * (float)g.dn)));
+                    dc = (face * (uint32_t)g.dn + (uint32_t)iu) * (uint32_t)g.dn + (uint32_t)iv;
+                }
+                const int ix = min(g.n[0] - 1, max(0, (int)((px - g.lo[0]) * g.inv[0])));
+                const int iy = min(g.n[1] - 1, max(0, (int)((py - g.lo[1]) * g.inv[1])));
+                const int iz = min(g.n[2] - 1, max(0, (int)((pz - g.lo[2]) * g.inv[2])));
+                b = ((dc * (uint32_t)g.n[0] + (uint32_t)ix) * (uint32_t)g.n[1] + (uint32_t)iy) * (uint32_t)g.n[2] + (uint32_t)iz;
+            }
+        }
+        // one atomic per distinct bin of the warp: neighbouring rays often share a bin
+        const uint32_t peers = __match_any_sync(0xffffffffu, b);
+        const uint32_t leader = (uint32_t)__ffs(peers) - 1u;
+        uint32_t base = 0;
+        if (b != 0xffffffffu && lane == leader) base = atomicAdd(&s.hist[b], (uint32_t)__popc(peers));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (i < n) s.keyb[i] = make_uint2(b, base + (uint32_t)__popc(peers & ((1u << lane) - 1u)));
+    }
+}
+
+// Exclusive scan of the bin counts in two launches: sums of 1024-bin blocks, then every block scans its own bins after
+// adding up the block sums before it (nb / 1024 values).  The counts are zeroed for the next use.
+__global__ void __launch_bounds__(1024) k_binsum(SortDev s) {
+    __shared__ uint32_t sw[32];
+    const uint32_t b = blockIdx.x * 1024u + threadIdx.x;
+    uint32_t v = b < (uint32_t)s.nb ? s.hist[b] : 0u;
+    v = __reduce_add_sync(0xffffffffu, v);
+    if (lane_id() == 0) sw[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x < 32) { v = __reduce_add_sync(0xffffffffu, sw[threadIdx.x]); if (threadIdx.x == 0) s.part[blockIdx.x] = v; }
+}
+__global__ void __launch_bounds__(1024) k_binscan(SortDev s) {
+    __shared__ uint32_t sw[32]; __shared__ uint32_t s_off;
+    uint32_t pre = 0;
+    for (uint32_t t = threadIdx.x; t < blockIdx.x; t += 1024u) pre += s.part[t];
+    pre = __reduce_add_sync(0xffffffffu, pre);
+    if (lane_id() == 0) sw[threadIdx.x >> 5] = pre;
+    __syncthreads();
+    if (threadIdx.x < 32) { const uint32_t v = __reduce_add_sync(0xffffffffu, sw[threadIdx.x]); if (threadIdx.x == 0) s_off = v; }
+    __syncthreads();
+    const uint32_t off = s_off;
+    const uint32_t b = blockIdx.x * 1024u + threadIdx.x;
+    const uint32_t v = b < (uint32_t)s.nb ? s.hist[b] : 0u;
+    uint32_t x = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, d); if ((int)lane_id() >= d) x += y; }
+    __syncthreads();
+    if (lane_id() == 31) sw[threadIdx.x >> 5] = x;
+    __syncthreads();
+    if (threadIdx.x < 32) { const uint32_t w = sw[threadIdx.x]; uint32_t y = w;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t z = __shfl_up_sync(0xffffffffu, y, d); if ((int)threadIdx.x >= d) y += z; }
+        sw[threadIdx.x] = y - w; }
+    __syncthreads();
+    const uint32_t excl = off + sw[threadIdx.x >> 5] + x - v;
+    if (b < (uint32_t)s.nb) { s.base[b] = excl; s.hist[b] = 0u; }
+    if (b == (uint32_t)s.nb - 1u) *s.n_sorted = excl + v;
+}
+__global__ void __launch_bounds__(256) k_perm(SortDev s) {
+    const uint32_t n = *s.n_live;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint2 k = s.keyb[i];
+        if (k.x != 0xffffffffu) s.perm[s.base[k.x] + k.y] = i;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // Per-hit shading kernels (trace.py:56-110, :123-131) — <1 % of the work at S=1024
 // ------------------------------------------------------------------------------------------------
 struct ShadeDev {
     const float4* rayO; const float4* rayD;      // this depth's ray queue (k_setup input)
     const unsigned long long* hit;               // packed closest hit per ray (k_setup input)
+    const uint32_t* perm;                        // k_setup walks the queue through this permutation (regrouped hits), or null
     float4* rayO2; float4* rayD2; unsigned long long* hit2;   // next depth's ray queue (k_setup output; hit2 pre-set to "no hit")
     float4* hP; float4* hN;              // hit records: (biased P, slot) (N, id)
     uint8_t* occl; size_t ocap;          // [light][hit], row stride ocap (zeroed by k_setup, set by the shadow query)
@@ -402,7 +537,8 @@ __global__ void __launch_bounds__(256, 6) k_setup(SceneDev sc, ShadeDev s) {
         const uint32_t i = c * 256u + threadIdx.x;
         bool hit = false; float4 o = make_float4(0, 0, 0, 0), d = o; float t = 0.f; int id = -1;
         if (i < n) {                                 // the three loads go out together (the ray is read even if it missed)
-            const unsigned long long key = s.hit[i]; o = s.rayO[i]; d = s.rayD[i];
+            const uint32_t src = s.perm ? s.perm[i] : i;
+            const unsigned long long key = s.hit[src]; o = s.rayO[src]; d = s.rayD[src];
             id = (int)(uint32_t)key; t = __uint_as_float((uint32_t)(key >> 32)); hit = id >= 0;
         }
         V3 Pb = mk(0, 0, 0), N = mk(0, 0, 0);
@@ -687,6 +823,8 @@ struct DevCtx {
     Buf rayO[2], rayD[2], hitKey[2];                               // ray queues, double-buffered by depth parity
     Buf hP[kSets], hN[kSets], occl[kSets], shidx[kSets], shidx2[kSets];   // hit records / shadow state: ring of kSets depths
     Buf acc, ctr, work, slow, tl, ostat;
+    Buf sortKey, sortPerm, sortHist, sortBase, sortPart, sortGrid;   // regrouping of bounce-depth hits (k_key .. k_perm)
+    bool no_sort = false; int sort_posbits = 13, sort_dirn = 4;     // env B200RT_NO_SORT, B200RT_SORT_POSBITS, B200RT_SORT_DIRN
     int npre = 1, pre[6] = {256, 0, 0, 0, 0, 0};                    // leading shadow passes (env B200RT_PASSES=a,b,...; multiples of 8)
     bool timeline = false;                                        // env B200RT_TIMELINE: per-launch first-start / last-end (globaltimer) to stderr
     // internal streams (see the launch sequence in render_device): the dependent chain at high priority, one stream per
@@ -699,7 +837,7 @@ struct DevCtx {
     cudaEvent_t done = nullptr; bool has_done = false;
     void release_all() {
         Buf* all[] = { &sphA, &sphB, &sphCol, &plO, &plN, &plNu, &plCol, &lights, &cmax, &pivTab, &pivPos, &pivPerm, &pivRad, &stage, &rayO[0], &rayO[1], &rayD[0], &rayD[1], &hitKey[0], &hitKey[1],
-                       &acc, &tl, &ostat, &ctr, &work, &slow, &hostResult, &hostPixelLoc, &imgOut, &batchScene };
+                       &acc, &tl, &ostat, &ctr, &work, &slow, &sortKey, &sortPerm, &sortHist, &sortBase, &sortPart, &sortGrid, &hostResult, &hostPixelLoc, &imgOut, &batchScene };
         for (Buf* b : all) b->release();
         for (int i = 0; i < kSets; ++i) { hP[i].release(); hN[i].release(); occl[i].release(); shidx[i].release(); shidx2[i].release(); }
         if (done) { cudaEventDestroy(done); done = nullptr; } has_done = false; init = false;
@@ -779,6 +917,9 @@ int init_ctx(DevCtx& c, int device) {
     { const char* e = getenv("B200RT_NO_CONCURRENCY"); c.no_conc = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_NO_CULL"); c.no_cull = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_TIMELINE"); c.timeline = e && atoi(e) != 0; }
+    { const char* e = getenv("B200RT_NO_SORT"); c.no_sort = e && atoi(e) != 0; }
+    { const char* e = getenv("B200RT_SORT_POSBITS"); if (e) c.sort_posbits = std::min(18, std::max(0, atoi(e))); }
+    { const char* e = getenv("B200RT_SORT_DIRN"); if (e) c.sort_dirn = std::min(16, std::max(1, atoi(e))); }
     if (const char* e = getenv("B200RT_PASSES")) {
         c.npre = 0;
         for (const char* p = e; *p && c.npre < 6; ) { const int v = atoi(p) & ~7; if (v >= 8) c.pre[c.npre++] = v; while (*p && *p != ',') ++p; if (*p == ',') ++p; }
@@ -884,6 +1025,16 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         if (use_lists) { CK(c.shidx[b].ensure(sizeof(uint32_t) * std::max<size_t>(cap * (size_t)L, 1))); CK(c.shidx2[b].ensure(sizeof(uint32_t) * std::max<size_t>(cap * (size_t)L, 1))); }
     }
     CK(c.acc.ensure(sizeof(float) * 3 * cap));
+    // regrouping of the hits of depth >= 1 (see k_key): worth it where beam culling is on and a query is expensive
+    const bool regroup = cull && use_lists && S >= 64 && depth >= 1 && !(a->flags & B200RT_F_NO_SORT) && !c.no_sort;
+    const int sort_nb = 6 * c.sort_dirn * c.sort_dirn << c.sort_posbits, sort_nblk = (sort_nb + 1023) / 1024;
+    if (regroup) {
+        CK(c.sortKey.ensure(sizeof(uint2) * cap)); CK(c.sortPerm.ensure(sizeof(uint32_t) * cap));
+        CK(c.sortHist.ensure(sizeof(uint32_t) * sort_nb)); CK(c.sortBase.ensure(sizeof(uint32_t) * sort_nb));
+        CK(c.sortPart.ensure(sizeof(uint32_t) * sort_nblk)); CK(c.sortGrid.ensure(sizeof(GridDev)));
+        CK(cudaMemsetAsync(c.sortHist.p, 0, sizeof(uint32_t) * sort_nb, st));
+        k_grid<<<1, 256, 0, st>>>(sc, c.sort_posbits, c.sort_dirn, c.sortGrid.as<GridDev>()); CK(cudaGetLastError());
+    }
     // k_setup's ordered compaction: [pass][chunk of 256 rays][8 queues] status words + the chunk ticket, zeroed before every launch
     const size_t ostat_stride = ((cap + 255) / 256) * 8;
     const int ostat_passes = use_lists ? 1 + std::max(0, (L - 7 + 7) / 8) : 1;
@@ -987,6 +1138,15 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             else                              { const int f0 = tln; CK(isect3_launch_closest<0>(icfg, sc, q, pv, nslots, wk, closest_res, cs, tlb, &tln)); tl_mark("closest<0>", d, f0); }
             tm.end(0);
             tm.begin(2);
+            if (regroup && d >= 1) {
+                SortDev so{ q.rayO, q.rayD, q.hit, n_live, c.sortGrid.as<GridDev>(), c.sortKey.as<uint2>(), c.sortHist.as<uint32_t>(), c.sortPart.as<uint32_t>(),
+                            c.sortBase.as<uint32_t>(), c.sortPerm.as<uint32_t>(), cd + 2, sort_nb, d < depth ? 1 : 0 };
+                k_key<<<small_grid, 256, 0, cs>>>(sc, so); CK(cudaGetLastError());
+                k_binsum<<<sort_nblk, 1024, 0, cs>>>(so); CK(cudaGetLastError());
+                k_binscan<<<sort_nblk, 1024, 0, cs>>>(so); CK(cudaGetLastError());
+                k_perm<<<small_grid, 256, 0, cs>>>(so); CK(cudaGetLastError());
+                s.perm = so.perm; s.n_live = cd + 2;                                      // k_setup walks the hits in bin order
+            }
             if (conc && d >= nsets) CK(cudaStreamWaitEvent(cs, c.evShade[hs], 0));        // set hs is free again
             if (tlb) { s.tl = tlb + 2 * (size_t)tln++; tlname.push_back("setup d" + std::to_string(d)); }
             s.ostat = c.ostat.as<unsigned long long>(); s.ostat_stride = ostat_stride; s.ticket = reinterpret_cast<uint32_t*>(s.ostat + ostat_stride * ostat_passes);

@@ -225,6 +225,9 @@ def test_culling_and_passes_do_not_change_the_image(oracle, S, L, W, H, depth, a
     got, st = _cuda(g, stats=True)
     nocull, st_nc = _cuda(g, flags=_lib.F_NO_CULL, stats=True)
     assert np.array_equal(got, nocull), "beam culling changed the image"
+    nosort, st_ns = _cuda(g, flags=_lib.F_NO_SORT, stats=True)
+    assert np.array_equal(got, nosort), "regrouping the bounce-depth hits changed the image"
+    assert st["rays"] == st_ns["rays"] and st["shadow_traced"] == st_ns["shadow_traced"]
     assert np.array_equal(got, _cuda(g, flags=_lib.F_NO_FILTER)), "filtered path differs from exact-test-on-everything"
     assert st["rays"] == st_nc["rays"]
     canonical = st["rays"] * S
