@@ -177,9 +177,9 @@ def run_ours(args, w):
     from b200rt.cuda import pixel_grid
     grids = [pixel_grid(c, local) for c in cams]               # closed-form pixel grid: no 24*W*H-byte array
 
-    def frame(k=0, stats=False):
+    def frame(k=0, stats=False, flags=0):
         c = cams[k % len(cams)]
-        ln = render.configure(stream=stream, strips=strips, stats=stats)
+        ln = render.configure(stream=stream, strips=strips, stats=stats, flags=flags)
         ln(grids[k % len(cams)], result, c.position, c.rotation, spheres, lights, planes, *shade)
         return ln.stats
 
@@ -194,10 +194,12 @@ def run_ours(args, w):
     sampler = ClockSampler(local); sampler.start()
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches0 = _lib.lib().b200rt_launch_count()                # counted by the library at every <<< >>> (this rank)
     e0.record(stream)
     for i in range(args.steps):
         frame(i)
     e1.record(stream)
+    launches = int(_lib.lib().b200rt_launch_count() - launches0)
     barrier()
     ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
     if world > 1:
@@ -206,7 +208,11 @@ def run_ours(args, w):
     sampler.stop_flag = True; sampler.join(timeout=2)
 
     # kernel-class times of an instrumented frame after warm-up (dominant kernel = k_intersect, both variants)
+    # (a) executed-work counters from the diagnostic kernel build; (b) times from the production kernels, launches serialised
     st2 = frame(0, stats=True)
+    st3 = frame(0, stats=True, flags=_lib.F_TIME_ONLY)
+    for k in ("ms_total", "ms_closest", "ms_shadow", "ms_other"):
+        st2[k] = st3[k]
     isect_ms = st2["ms_closest"] + st2["ms_shadow"]
     rays_this_rank = st2["rays"]
 
@@ -263,11 +269,6 @@ def run_ours(args, w):
             traffic, traffic_src = tj["traffic_bytes_per_frame"], "profiles/r01_v6_traffic.json (ncu dram__bytes_read+write, the 28 k_isect3 launches of one frame)"
         ach_tf = rays_this_rank * fpr / (isect_ms * 1e-3) / 1e12
         clocks = sampler.summary()
-        depth = w["refl_depth"]
-        spad = max(8, (S + 7) & ~7)
-        shadow_passes = 2 if spad >= 512 else 1                   # csrc/isect3.cuh shadow_passes(): 256 spheres, then the rest
-        # pack, rank, pivot, raygen; per depth: closest hit, setup, L lights x passes, shade; resolve
-        launches_per_frame = 4 + (depth + 1) * (3 + L * shadow_passes) + 1
         line = {
             "metric": "Mrays/s", "value": rays_total / (ms_step * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
@@ -275,7 +276,7 @@ def run_ours(args, w):
             "config": workload_config(w, world, rays_total),
             "e2e": {"value": rays_total / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": e2e_ms,
                     "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
-            "gpu_launches": int(launches_per_frame * args.steps),
+            "gpu_launches": launches,                         # kernels launched inside the timed region (rank 0; b200rt_launch_count)
             "clocks": clocks,
             "roofline": {"bound": "fp32", "kernel": "k_isect3 (closest + shadow)", "achieved": ach_tf, "peak": nominal_tf,
                          "unit": "TFLOP/s", "frac": ach_tf / nominal_tf, "traffic": traffic, "traffic_source": traffic_src,

@@ -47,6 +47,7 @@ extern "C" {
 #define B200RT_F_NO_FILTER       0x2u  /* debug: run the exact sphere test on every sphere (must give bit-identical output) */
 #define B200RT_F_UNSWAP_GB       0x4u  /* write channels as R,G,B instead of the reference's R,B,G wiring (common.py:60-63) */
 #define B200RT_F_NO_CULL         0x8u  /* k_isect3 scans every sphere for every ray group (no beam culling); the image is the same */
+#define B200RT_F_TIME_ONLY       0x20u /* with `stats`: fill the ray counts and the per-class device times but run the production kernels (no executed-work counters: slow_path, exact_tests, tests_* stay 0) */
 #define B200RT_F_NO_SORT         0x10u /* bounce-depth hits stay in pixel order (no regrouping by direction/position bin); the image is the same */
 
 /*
@@ -141,6 +142,9 @@ B200RT_API int b200rt_to_image_host(int device, const uint8_t* planar, uint8_t* 
 
 B200RT_API int b200rt_device_count(void);
 B200RT_API int b200rt_sm_count(int device);
+/* Kernels launched by this library since it was loaded (host-side count, all devices and threads): the difference
+ * across a timed region is the measured `gpu_launches` of bench.py. */
+B200RT_API unsigned long long b200rt_launch_count(void);
 /* Free the per-device scratch (packed scene, ray queues).  Safe to call at any time between renders. */
 B200RT_API int b200rt_shutdown(void);
 

@@ -5,7 +5,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200rt.so")
 
-F_SCENE_ON_HOST, F_NO_FILTER, F_UNSWAP_GB, F_NO_CULL, F_NO_SORT = 0x1, 0x2, 0x4, 0x8, 0x10
+F_SCENE_ON_HOST, F_NO_FILTER, F_UNSWAP_GB, F_NO_CULL, F_NO_SORT, F_TIME_ONLY = 0x1, 0x2, 0x4, 0x8, 0x10, 0x20
 
 
 class Grid(C.Structure):
@@ -64,6 +64,7 @@ def lib():
         L.b200rt_to_image_host.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint32]; L.b200rt_to_image_host.restype = C.c_int
         L.b200rt_device_count.restype = C.c_int
         L.b200rt_sm_count.argtypes = [C.c_int]; L.b200rt_sm_count.restype = C.c_int
+        L.b200rt_launch_count.restype = C.c_ulonglong
         L.b200rt_shutdown.restype = C.c_int
         if L.b200rt_args_size() != C.sizeof(Args):
             raise ImportError("b200rt_args layout mismatch between _lib.py and libb200rt.so")

@@ -782,6 +782,7 @@ __global__ void __launch_bounds__(256) k_to_image(const uint8_t* __restrict__ in
 // ================================================================================================
 using namespace b200rt;
 
+std::atomic<unsigned long long> b200rt::g_kernel_launches{0};   // declared in isect3.cuh (both modules count into it)
 static thread_local std::string g_err;
 static int fail(int code, const std::string& msg) { g_err = msg; return code; }
 static int cuda_fail(cudaError_t e, const char* what) {
@@ -790,6 +791,7 @@ static int cuda_fail(cudaError_t e, const char* what) {
     return (int)e;
 }
 #define CK(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return cuda_fail(e__, #call); } while (0)
+#define CKL() do { g_kernel_launches.fetch_add(1, std::memory_order_relaxed); CK(cudaGetLastError()); } while (0)   // after every kernel launch
 
 namespace {
 
@@ -898,7 +900,7 @@ int launch_intersect(DevCtx& c, const SceneDev& sc, const QueueDev& q, bool nofi
     const int grid = c.sm_count * c.isect_blocks_per_sm;
     (void)nofilter;                                   // the scalar kernel is kept as the exact-test-on-everything debug path
     k_intersect<ANY, true><<<grid, kThreads, smem, st>>>(sc, q);
-    CK(cudaGetLastError());
+    CKL();
     return 0;
 }
 
@@ -981,7 +983,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         k_pack<<<(nobj + 255) / 256, 256, 0, st>>>(d_sph, S, Spad, d_pla, Pl, d_lig, L, c.sphA.as<float4>(), c.sphB.as<float4>(),
                                                    c.sphCol.as<float4>(), c.plO.as<float4>(), c.plN.as<float4>(), c.plNu.as<float4>(),
                                                    c.plCol.as<float4>(), c.lights.as<float4>(), c.cmax.as<float>());
-        CK(cudaGetLastError());
+        CKL();
     }
     SceneDev sc{ c.sphA.as<float4>(), c.sphB.as<float4>(), c.sphCol.as<float4>(), c.plO.as<float4>(), c.plN.as<float4>(),
                  c.plNu.as<float4>(), c.plCol.as<float4>(), c.lights.as<float4>(), c.cmax.as<float>(), S, Spad, Pl, L };
@@ -989,10 +991,10 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     {
         const int n = (L + 2) * (Spad / 2);
         CK(c.pivPerm.ensure(sizeof(int) * std::max<size_t>((size_t)L * Spad, 1))); CK(c.pivRad.ensure(sizeof(float) * (size_t)(L + 2) * Spad));
-        if (L > 0) { k_rank<<<dim3((Spad + 255) / 256, L), 256, 0, st>>>(sc, c.pivPerm.as<int>()); CK(cudaGetLastError()); }
+        if (L > 0) { k_rank<<<dim3((Spad + 255) / 256, L), 256, 0, st>>>(sc, c.pivPerm.as<int>()); CKL(); }
         k_pivot<<<(n + 255) / 256, 256, 0, st>>>(sc, (float)a->cam_origin[0], (float)a->cam_origin[1], (float)a->cam_origin[2],
                                                  c.pivPerm.as<int>(), c.pivTab.as<float4>(), c.pivPos.as<float4>(), c.pivRad.as<float>());
-        CK(cudaGetLastError());
+        CKL();
     }
     const bool cull = !(a->flags & B200RT_F_NO_CULL) && !c.no_cull;
     const PivotDev pv{ c.pivTab.as<float4>(), c.pivPos.as<float4>(), c.cmax.as<float>(), c.pivPerm.as<int>(), cull ? c.pivRad.as<float>() : nullptr };
@@ -1033,7 +1035,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         CK(c.sortHist.ensure(sizeof(uint32_t) * sort_nb)); CK(c.sortBase.ensure(sizeof(uint32_t) * sort_nb));
         CK(c.sortPart.ensure(sizeof(uint32_t) * sort_nblk)); CK(c.sortGrid.ensure(sizeof(GridDev)));
         CK(cudaMemsetAsync(c.sortHist.p, 0, sizeof(uint32_t) * sort_nb, st));
-        k_grid<<<1, 256, 0, st>>>(sc, c.sort_posbits, c.sort_dirn, c.sortGrid.as<GridDev>()); CK(cudaGetLastError());
+        k_grid<<<1, 256, 0, st>>>(sc, c.sort_posbits, c.sort_dirn, c.sortGrid.as<GridDev>()); CKL();
     }
     // k_setup's ordered compaction: [pass][chunk of 256 rays][8 queues] status words + the chunk ticket, zeroed before every launch
     const size_t ostat_stride = ((cap + 255) / 256) * 8;
@@ -1101,7 +1103,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         if (ns > 1) CK(cudaMemsetAsync(c.ostat.p, 0, ostat_bytes, cs));
         k_raygen<<<(int)std::min<size_t>((nslots + 255) / 256, (size_t)small_grid), 256, 0, cs>>>(f, c.rayO[0].as<float4>(), c.rayD[0].as<float4>(), c.hitKey[0].as<unsigned long long>(), ctr + 0,
                                                                                                          c.ostat.as<unsigned long long>(), reinterpret_cast<uint32_t*>(c.ostat.as<unsigned long long>() + ostat_stride * ostat_passes));
-        CK(cudaGetLastError());
+        CKL();
         tm.end(2);
 
         // Launch sequence.  The dependent chain closest(d) -> setup(d) -> closest(d+1) ... runs on `cs`; the shadow
@@ -1121,7 +1123,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             QueueDev q{};
             q.rayO = c.rayO[b].as<float4>(); q.rayD = c.rayD[b].as<float4>(); q.hP = c.hP[hs].as<float4>();
             q.hit = c.hitKey[b].as<unsigned long long>(); q.occl = c.occl[hs].as<uint8_t>(); q.ocap = cap;
-            q.slow = stats ? c.slow.as<unsigned long long>() : nullptr;
+            q.slow = (stats && !(a->flags & B200RT_F_TIME_ONLY)) ? c.slow.as<unsigned long long>() : nullptr;
             ShadeDev s{};
             s.rayO = q.rayO; s.rayD = q.rayD; s.hit = q.hit;
             s.rayO2 = c.rayO[b ^ 1].as<float4>(); s.rayD2 = c.rayD[b ^ 1].as<float4>(); s.hit2 = c.hitKey[b ^ 1].as<unsigned long long>();
@@ -1141,17 +1143,17 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             if (regroup && d >= 1) {
                 SortDev so{ q.rayO, q.rayD, q.hit, n_live, c.sortGrid.as<GridDev>(), c.sortKey.as<uint2>(), c.sortHist.as<uint32_t>(), c.sortPart.as<uint32_t>(),
                             c.sortBase.as<uint32_t>(), c.sortPerm.as<uint32_t>(), cd + 2, sort_nb, d < depth ? 1 : 0 };
-                k_key<<<small_grid, 256, 0, cs>>>(sc, so); CK(cudaGetLastError());
-                k_binsum<<<sort_nblk, 1024, 0, cs>>>(so); CK(cudaGetLastError());
-                k_binscan<<<sort_nblk, 1024, 0, cs>>>(so); CK(cudaGetLastError());
-                k_perm<<<small_grid, 256, 0, cs>>>(so); CK(cudaGetLastError());
+                k_key<<<small_grid, 256, 0, cs>>>(sc, so); CKL();
+                k_binsum<<<sort_nblk, 1024, 0, cs>>>(so); CKL();
+                k_binscan<<<sort_nblk, 1024, 0, cs>>>(so); CKL();
+                k_perm<<<small_grid, 256, 0, cs>>>(so); CKL();
                 s.perm = so.perm; s.n_live = cd + 2;                                      // k_setup walks the hits in bin order
             }
             if (conc && d >= nsets) CK(cudaStreamWaitEvent(cs, c.evShade[hs], 0));        // set hs is free again
             if (tlb) { s.tl = tlb + 2 * (size_t)tln++; tlname.push_back("setup d" + std::to_string(d)); }
             s.ostat = c.ostat.as<unsigned long long>(); s.ostat_stride = ostat_stride; s.ticket = reinterpret_cast<uint32_t*>(s.ostat + ostat_stride * ostat_passes);
             CK(cudaMemsetAsync(c.ostat.p, 0, ostat_bytes, cs));
-            k_setup<<<small_grid, 256, 0, cs>>>(sc, s); CK(cudaGetLastError());
+            k_setup<<<small_grid, 256, 0, cs>>>(sc, s); CKL();
             if (conc) CK(cudaEventRecord(c.evSetup[hs], cs));
             tm.end(2);
             if (L > 0) {
@@ -1174,7 +1176,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             } else if (conc) CK(cudaStreamWaitEvent(ss, c.evSetup[hs], 0));
             tm.begin(2);
             if (tlb) { s.tl = tlb + 2 * (size_t)tln++; tlname.push_back("shade d" + std::to_string(d)); }
-            k_shade<<<small_grid, 256, 0, ss>>>(sc, s); CK(cudaGetLastError());
+            k_shade<<<small_grid, 256, 0, ss>>>(sc, s); CKL();
             if (conc) CK(cudaEventRecord(c.evShade[hs], ss));
             tm.end(2);
         }
@@ -1187,7 +1189,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         if (al16)      k_resolve<16><<<std::min<int>((f.npix / 16 + 255) / 256, small_grid), 256, 0, cs>>>(f, accR, accG, accB, a->result, a->aliasing, unswap);
         else if (al4)  k_resolve<4><<<std::min<int>((f.npix / 4 + 255) / 256, small_grid), 256, 0, cs>>>(f, accR, accG, accB, a->result, a->aliasing, unswap);
         else           k_resolve<1><<<std::min<int>((f.npix + 255) / 256, small_grid), 256, 0, cs>>>(f, accR, accG, accB, a->result, a->aliasing, unswap);
-        CK(cudaGetLastError());
+        CKL();
         tm.end(2);
     }
     if (conc) { CK(cudaEventRecord(c.evJoin, cs)); CK(cudaStreamWaitEvent(st, c.evJoin, 0)); }
@@ -1238,6 +1240,8 @@ B200RT_API uint32_t b200rt_args_size(void) { return (uint32_t)sizeof(b200rt_args
 B200RT_API int b200rt_device_count(void) {
     int n = 0; if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; } return n;
 }
+B200RT_API unsigned long long b200rt_launch_count(void) { return b200rt::g_kernel_launches.load(std::memory_order_relaxed); }
+
 B200RT_API int b200rt_sm_count(int device) {
     int n = 0; if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) { cudaGetLastError(); return 0; } return n;
 }
@@ -1383,7 +1387,7 @@ B200RT_API int b200rt_to_image(int device, void* stream, const uint8_t* planar, 
     const int vec = (W % 4 == 0) && (H % 4 == 0) && ((uintptr_t)planar % 4 == 0) && ((uintptr_t)rgb % 4 == 0);
     dim3 grid((W + kImgTile - 1) / kImgTile, (H + kImgTile - 1) / kImgTile);
     k_to_image<<<grid, 256, 0, (cudaStream_t)stream>>>(planar, rgb, W, H, (flags & B200RT_F_UNSWAP_GB) ? 1 : 0, vec);
-    CK(cudaGetLastError());
+    CKL();
     return 0;
 }
 

@@ -10,9 +10,12 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <algorithm>
+#include <atomic>
 #include "rt_math.cuh"
 
 namespace b200rt {
+
+extern std::atomic<unsigned long long> g_kernel_launches;   // kernels launched by this library since load (b200rt_launch_count)
 
 // ------------------------------------------------------------------------------------------------
 // Device-side scene (packed once per launch by k_pack from the reference's SoA arrays)
@@ -108,7 +111,22 @@ __device__ __forceinline__ float fmax3(float a, float b, float c) {
 // fills and at the end of the group.  Results meet in shared memory: closest hit = atomicMin on the packed key
 // (float bits of t << 32 | sphere id) — min t, and on equal t the lowest index, which is the reference's tie-break
 // (first object wins, trace.py:26; planes have ids >= S and so lose ties against spheres, trace.py:36).
-constexpr int KP = 4;                    // sphere pairs per scan step (8 spheres)
+#ifndef B200RT_KP
+#define B200RT_KP 2
+#endif
+constexpr int KP = B200RT_KP;            // sphere pairs per scan step, pivot modes
+#ifndef B200RT_KP0
+#define B200RT_KP0 2                     // ... of the 8-FFMA2 form (MODE 0): its step is twice as long, and the unrolled step should fit the L0 instruction cache
+#endif
+#ifndef B200RT_CULL_E
+#define B200RT_CULL_E 2                  // beam culling: sphere pairs per lane per round (code size vs loads in flight; the next round is prefetched)
+#endif
+#ifndef B200RT_ONE_SLOW_SITE
+#define B200RT_ONE_SLOW_SITE 0           // 1: one copy of slow_pair / the exact-test loop behind both scans (smaller code, measured 0.6 ms/frame slower on C4)
+#endif
+#ifndef B200RT_FLUSH_UNROLL
+#define B200RT_FLUSH_UNROLL 1            // 1: #pragma unroll 1 on the exact-test loop (0: the compiler unrolls it by 2 + tail at every inlined site)
+#endif
 constexpr uint32_t kRegion = 2048;       // entries per survivor-list region (8 ray groups of 256)
 constexpr int kQCap = 768;               // candidate queue entries per warp
 constexpr int kQFlush = kQCap - 32 * 16; // flush before an append (<= 16 per lane) could overflow
@@ -124,15 +142,19 @@ template <int NR> struct IsectWarpSmem {               // per warp (no CTA-level
 };
 template <int NR> struct IsectSmem { IsectWarpSmem<NR> w[kThreads / 32]; };   // NR = 8: 14 KB per warp, 112 KB per CTA, 2 CTAs per SM
 
-template <int MODE, int NR>
+// DIAG: the counters / timeline behind q.slow and q.tl (b200rt_stats, B200RT_TIMELINE) exist only in the <.., true>
+// instantiation, which the launcher picks when either pointer is set: in the production kernel they were ~200 cold
+// instructions spread through the hot code, and this kernel's first limiter is instruction fetch (profiles/r01_v7).
+template <int MODE, int NR, bool DIAG>
 __global__ void __launch_bounds__(kThreads, NR == 8 ? 2 : 3)
 k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
     constexpr bool ANY = (MODE == 2), PIV = (MODE != 0);
     constexpr int GW = 32 * NR;                               // rays per warp group
     constexpr int NO = PIV ? 1 : NR;                          // 2*O operands exist only in the 8-FFMA2 form
+    constexpr int KPM = (MODE == 0) ? B200RT_KP0 : KP;        // sphere pairs per scan step of this mode
     extern __shared__ __align__(16) unsigned char s_raw[];
     IsectSmem<NR>& sm = *reinterpret_cast<IsectSmem<NR>*>(s_raw);
-    if (q.tl && threadIdx.x == 0) atomicMin(q.tl, globaltimer_ns());
+    if (DIAG && q.tl && threadIdx.x == 0) atomicMin(q.tl, globaltimer_ns());
     const bool last = q.last != 0;
     const uint32_t n_in = *q.n_in;
     const uint32_t* shl = ANY ? q.in_list : nullptr;          // list entry -> hit record
@@ -259,6 +281,9 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
         // with a divergent loop inside the scan ptxas no longer keeps the table operands in uniform registers.
         auto flush = [&]() {
             __syncwarp();
+#if B200RT_FLUSH_UNROLL
+#pragma unroll 1
+#endif
             for (uint32_t base = 0; base < qcnt; base += 32) {                // warp-uniform trip count
                 const uint32_t idx = base + lane;
                 bool hit = false; uint32_t rl = 0, tbits = 0; int sid = 0;
@@ -283,7 +308,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
                     __syncwarp();
                 }
             }
-            exact_cnt += (qcnt + 31 - lane) / 32;
+            if (DIAG) exact_cnt += (qcnt + 31 - lane) / 32;
             __syncwarp();
             qcnt = 0;
         };
@@ -314,13 +339,13 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
             }
             if (qcnt > (uint32_t)kQFlush) flush();
         };
-        auto slow_step = [&](int pb, const float (&mk4)[KP]) {        // pairs pb .. pb+KP-1, per-pair maxima mk4
-            slow_cnt++;
+        auto slow_step = [&](int pb, const float (&mk4)[KPM]) {        // pairs pb .. pb+KP-1, per-pair maxima mk4
+            if (DIAG) slow_cnt++;
 #pragma unroll 1
-            for (int k = 0; k < KP; ++k) {
+            for (int k = 0; k < KPM; ++k) {
                 float mv = mk4[0];
 #pragma unroll
-                for (int kk = 1; kk < KP; ++kk) mv = (k == kk) ? mk4[kk] : mv;
+                for (int kk = 1; kk < KPM; ++kk) mv = (k == kk) ? mk4[kk] : mv;
                 if (__any_sync(0xffffffffu, mv >= thr_t)) slow_pair(pb + k);
             }
         };
@@ -333,7 +358,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
         // the exact test's rounding bound), so the image does not change; B200RT_F_NO_CULL switches it off.  Survivors
         // are listed per PAIR of table positions and scanned through the list (operands from the constant table with a
         // computed index instead of uniform registers); wide beams and poor cull rates take the dense scan. ----
-        if (q.slow && lane == 0) atomicAdd(q.slow + 4 + 6 * MODE, 1ull);                      // dbg: groups
+        if (DIAG && q.slow && lane == 0) atomicAdd(q.slow + 4 + 6 * MODE, 1ull);                      // dbg: groups
         int ns = -1, nsr = 0;                                 // ns >= 0: sparse scan over slist[0..ns), the first nsr entries real
         uint16_t* slist = reinterpret_cast<uint16_t*>(MODE == 2 ? (void*)ws.ki : MODE == 0 ? (void*)ws.thr : (void*)ws.o);   // 1 KB free in every mode
         if (pv.rad && npair <= 32 * NR * 2 && npair >= 64) {
@@ -368,7 +393,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
 #pragma unroll
                 for (int d = 16; d > 0; d >>= 1) { ro2 = fmaxf(ro2, __shfl_xor_sync(0xffffffffu, ro2, d)); kap2 = fmaxf(kap2, __shfl_xor_sync(0xffffffffu, kap2, d)); }
                 const float kap = __fsqrt_rn(kap2) * 1.0001f + 1e-6f;
-                if (q.slow && lane == 0) { atomicAdd(q.slow + 5 + 6 * MODE, 1ull); if (ANY && !regions) { atomicAdd(q.slow + 22, 1ull); if (kap < 0.1f) atomicAdd(q.slow + 23, 1ull); } if (MODE != 2) { if (kap < 0.1f) atomicAdd(q.slow + 8 + 6 * MODE, 1ull); if (kap < 0.1f && ro2 < 1.f) atomicAdd(q.slow + 9 + 6 * MODE, 1ull); } }
+                if (DIAG && q.slow && lane == 0) { atomicAdd(q.slow + 5 + 6 * MODE, 1ull); if (ANY && !regions) { atomicAdd(q.slow + 22, 1ull); if (kap < 0.1f) atomicAdd(q.slow + 23, 1ull); } if (MODE != 2) { if (kap < 0.1f) atomicAdd(q.slow + 8 + 6 * MODE, 1ull); if (kap < 0.1f && ro2 < 1.f) atomicAdd(q.slow + 9 + 6 * MODE, 1ull); } }
                 if (__all_sync(0xffffffffu, kap < 0.6f)) {
                     const float osz = cmax + __fsqrt_rn(dot3(Oc, Oc));
                     const float ro = __fsqrt_rn(ro2) * 1.0001f + 1e-6f * osz;
@@ -378,46 +403,136 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
                     const int tj = ANY ? j : (MODE == 1 ? sc.L : sc.L + 1);
                     const float4* gt = pv.tab + (size_t)tj * sc.Spad + c0;
                     const float2* gr = reinterpret_cast<const float2*>(pv.rad + (size_t)tj * sc.Spad + c0);
+                    // sqrt(Rp^2 + m) <= Rp + sqrt(m): one square root per group instead of one per sphere (the bound only
+                    // enters through kap * ..., i.e. it loosens the test by a few per cent of a radius for narrow beams)
+                    const float sm_ = __fsqrt_rn(m) * 1.0001f;
                     auto clear_of_beam = [&](float cx, float cy, float cz, float rad) -> bool {
                         const float wx = cx - Oc.x, wy = cy - Oc.y, wz = cz - Oc.z;
                         const float w2 = wx * wx + wy * wy + wz * wz, a = wx * Dc.x + wy * Dc.y + wz * Dc.z;
                         const float Rp = rad + ro, Rp2 = (Rp * Rp + m) * 1.0002f;
-                        const float tn = a + kap * __fsqrt_rn(Rp2) * 1.0001f;
+                        const float tn = a + kap * (Rp + sm_) * 1.0004f;
                         const float lhs = w2 - Rp2;
                         return (tn < 0.f) ? (lhs > 0.f) : (lhs * kk > tn * tn * 1.0002f + 1e-3f);
                     };
                     uint32_t nsv = 0;
-                    for (int p0 = 0; p0 < npair; p0 += 128) {                // 4 pairs per lane per round: their loads go out together
-                        float4 uu[4], ww[4]; float2 rr[4];
+                    // CE pairs per lane per round; the loads of round r+1 are issued before round r is evaluated
+                    constexpr int CE = B200RT_CULL_E;
+                    float4 uu[CE], ww[CE]; float2 rr[CE];
+                    auto load_round = [&](int p0) {
 #pragma unroll
-                        for (int e = 0; e < 4; ++e) {
+                        for (int e = 0; e < CE; ++e) {
                             const int p = min(p0 + e * 32 + (int)lane, npair - 1);
                             uu[e] = __ldg(gt + 2 * p); ww[e] = __ldg(gt + 2 * p + 1); rr[e] = __ldg(gr + p);
                         }
+                    };
+                    load_round(0);
+#pragma unroll 1
+                    for (int p0 = 0; p0 < npair; p0 += 32 * CE) {
+                        float4 cu[CE], cw[CE]; float2 cr[CE];
 #pragma unroll
-                        for (int e = 0; e < 4; ++e) {
+                        for (int e = 0; e < CE; ++e) { cu[e] = uu[e]; cw[e] = ww[e]; cr[e] = rr[e]; }
+                        if (p0 + 32 * CE < npair) load_round(p0 + 32 * CE);
+#pragma unroll
+                        for (int e = 0; e < CE; ++e) {
                             const int p = p0 + e * 32 + (int)lane;
                             const bool keep = p < npair &&
-                                ((c0 + 2 * p < sc.S && !clear_of_beam(uu[e].x, uu[e].z, ww[e].x, rr[e].x)) ||
-                                 (c0 + 2 * p + 1 < sc.S && !clear_of_beam(uu[e].y, uu[e].w, ww[e].y, rr[e].y)));
+                                ((c0 + 2 * p < sc.S && !clear_of_beam(cu[e].x, cu[e].z, cw[e].x, cr[e].x)) ||
+                                 (c0 + 2 * p + 1 < sc.S && !clear_of_beam(cu[e].y, cu[e].w, cw[e].y, cr[e].y)));
                             const uint32_t bal = __ballot_sync(0xffffffffu, keep);
                             if (keep) slist[nsv + (uint32_t)__popc(bal & ((1u << lane) - 1u))] = (uint16_t)p;
                             nsv += (uint32_t)__popc(bal);
                         }
                     }
-                    if (q.slow && lane == 0) { atomicAdd(q.slow + 6 + 6 * MODE, (unsigned long long)nsv); atomicAdd(q.slow + 7 + 6 * MODE, (unsigned long long)npair); }
+                    if (DIAG && q.slow && lane == 0) { atomicAdd(q.slow + 6 + 6 * MODE, (unsigned long long)nsv); atomicAdd(q.slow + 7 + 6 * MODE, (unsigned long long)npair); }
                     if (__all_sync(0xffffffffu, 2 * (int)nsv <= npair)) {      // worth it (the list path costs ~1.5x per test)
                         __syncwarp();
                         const uint16_t padv = nsv ? slist[nsv - 1] : (uint16_t)0;      // padding: the last pair again (never queued twice)
-                        if (lane < (KP - nsv % KP) % KP) slist[nsv + lane] = padv;
-                        nsr = (int)nsv; ns = (int)((nsv + KP - 1) / KP * KP);
+                        if (lane < (KPM - nsv % KPM) % KPM) slist[nsv + lane] = padv;
+                        nsr = (int)nsv; ns = (int)((nsv + KPM - 1) / KPM * KPM);
                         __syncwarp();
                     }
                 }
             }
         }
+#if B200RT_ONE_SLOW_SITE
+        // ---- scan.  Two loops find the sphere pairs in which some ray of the group has a candidate — the list scan
+        // (culled groups: listed pairs, operands by computed index) and the dense scan (all pairs of the launch, operands
+        // through uniform registers) — and ONE handler below them turns those pairs into queue entries: slow_pair and
+        // the exact-test loop exist once in the kernel (they used to be inlined at three / four places, and the
+        // kernel's first limiter is instruction fetch, profiles/r01_v7_summary.md).
+        // Dense scan: KPM sphere pairs x NR rays per step, pair-major; the uniform registers of a pair are refilled
+        // for the NEXT step as soon as the pair is done (rolling prefetch: LDCU latency never reaches the FMA pipe),
+        // and the candidate decision of a step is taken one step LATER (software pipelining): the vote never waits
+        // on the FMA pipe; the last step is drained after the loop.  (The loop keeps the shape ptxas is known to map onto
+        // uniform registers: LDCU -> FFMA2 ..., UR; other equivalent forms of it silently fell back to vector LDC operands.) ----
+        const bool sparse = __all_sync(0xffffffffu, ns >= 0);
+        if (DIAG && q.slow) tests_cnt += (unsigned long long)(sparse ? ns : npair) * 2ull * (unsigned long long)NR;
+        float pm[KPM]; int ppair = 0, pn = 0;                          // pending: pairs ppair .. ppair + pn - 1 with maxima pm[]
+        int li = 0, pb = 0; bool drained = false;
+        float mprev[KPM];
+        float4 u[KPM], w[KPM];
+#pragma unroll
+        for (int k = 0; k < KPM; ++k) { mprev[k] = -3.0e38f; pm[k] = -3.0e38f; u[k] = c_tab[tb + 2 * k]; w[k] = c_tab[tb + 2 * k + 1]; }
+        for (;;) {
+            pn = 0;
+            if (sparse) {
+#pragma unroll 1
+                while (li < nsr) {                                     // one listed pair per iteration: the lists are short
+                    const int pi = slist[li++];
+                    const float4 uu = c_tab[tb + 2 * pi], ww = c_tab[tb + 2 * pi + 1];
+                    float m = -3.0e38f;
+#pragma unroll
+                    for (int r = 0; r < NR; ++r) { const float2 qv = qray(r, uu, ww); m = fmax3(m, qv.x, qv.y); }
+                    if (__any_sync(0xffffffffu, m >= thr_t)) { ppair = pi; pm[0] = m; pn = 1; break; }
+                }
+            } else {
+                for (; pb < npair; pb += KPM) {
+                    float mall = mprev[0];
+#pragma unroll
+                    for (int k = 1; k < KPM; ++k) mall = fmaxf(mall, mprev[k]);
+                    const bool fire = __any_sync(0xffffffffu, mall >= thr_t);   // step pb-KPM
+                    float mk4[KPM];
+#pragma unroll
+                    for (int k = 0; k < KPM; ++k) {
+                        float m = -3.0e38f;
+#pragma unroll
+                        for (int r = 0; r < NR; ++r) { const float2 qv = qray(r, u[k], w[k]); m = fmax3(m, qv.x, qv.y); }
+                        mk4[k] = m;
+                        u[k] = c_tab[tb + 2 * (pb + KPM + k)]; w[k] = c_tab[tb + 2 * (pb + KPM + k) + 1];   // next step (c_tab is over-allocated)
+                    }
+                    if (fire) {                                       // hand step pb-KPM to the handler, keep this step pending
+#pragma unroll
+                        for (int k = 0; k < KPM; ++k) { pm[k] = mprev[k]; mprev[k] = mk4[k]; }
+                        ppair = pb - KPM; pn = KPM; pb += KPM; break;
+                    }
+#pragma unroll
+                    for (int k = 0; k < KPM; ++k) mprev[k] = mk4[k];
+                }
+                if (pn == 0 && !drained) {                            // the last step
+                    drained = true;
+                    float mall = mprev[0];
+#pragma unroll
+                    for (int k = 1; k < KPM; ++k) mall = fmaxf(mall, mprev[k]);
+                    if (__any_sync(0xffffffffu, mall >= thr_t)) {
+#pragma unroll
+                        for (int k = 0; k < KPM; ++k) pm[k] = mprev[k];
+                        ppair = npair - KPM; pn = KPM;
+                    }
+                }
+            }
+            if (pn == 0) break;
+            if (DIAG) slow_cnt++;
+#pragma unroll 1
+            for (int k = 0; k < pn; ++k) {
+                float mv = pm[0];
+#pragma unroll
+                for (int kk = 1; kk < KPM; ++kk) mv = (k == kk) ? pm[kk] : mv;
+                if (__any_sync(0xffffffffu, mv >= thr_t)) slow_pair(ppair + k);
+            }
+        }
+#else
         if (__all_sync(0xffffffffu, ns >= 0)) {
-            if (q.slow) tests_cnt += (unsigned long long)ns * 2ull * (unsigned long long)NR;
+            if (DIAG && q.slow) tests_cnt += (unsigned long long)ns * 2ull * (unsigned long long)NR;
 #pragma unroll 1
             for (int pb = 0; pb < nsr; ++pb) {                 // one listed pair per iteration: small code, the lists are short
                 const int pi = slist[pb];
@@ -425,48 +540,53 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
                 float m = -3.0e38f;
 #pragma unroll
                 for (int r = 0; r < NR; ++r) { const float2 qv = qray(r, u, w); m = fmax3(m, qv.x, qv.y); }
-                if (__any_sync(0xffffffffu, m >= thr_t)) { slow_cnt++; slow_pair(pi); }
+                if (__any_sync(0xffffffffu, m >= thr_t)) { if (DIAG) slow_cnt++; slow_pair(pi); }
             }
         } else {
-        if (q.slow) tests_cnt += (unsigned long long)npair * 2ull * (unsigned long long)NR;
+        if (DIAG && q.slow) tests_cnt += (unsigned long long)npair * 2ull * (unsigned long long)NR;
         // ---- scan: KP sphere pairs x NR rays per step, pair-major; the uniform registers of a pair are refilled
         // for the NEXT step as soon as the pair is done (rolling prefetch: LDCU latency never reaches the FMA pipe).
         // The candidate decision of a step is taken one step LATER (software pipelining): the vote/branch never
         // waits on the FMA pipe. ----
-        float mprev[KP];
-        float4 u[KP], w[KP];
+        float mprev[KPM];
+        float4 u[KPM], w[KPM];
 #pragma unroll
-        for (int k = 0; k < KP; ++k) { mprev[k] = -3.0e38f; u[k] = c_tab[tb + 2 * k]; w[k] = c_tab[tb + 2 * k + 1]; }
+        for (int k = 0; k < KPM; ++k) { mprev[k] = -3.0e38f; u[k] = c_tab[tb + 2 * k]; w[k] = c_tab[tb + 2 * k + 1]; }
         int pb = 0;                                                   // first pair of the step being computed
         for (;;) {
             bool found = false;
-            for (; pb < npair; pb += KP) {
-                const float mall = fmaxf(fmaxf(mprev[0], mprev[1]), fmaxf(mprev[2], mprev[3]));
-                const bool fire = __any_sync(0xffffffffu, mall >= thr_t);       // step pb-KP
-                float mk4[KP];
+            for (; pb < npair; pb += KPM) {
+                float mall = mprev[0];
 #pragma unroll
-                for (int k = 0; k < KP; ++k) {
+                for (int k = 1; k < KPM; ++k) mall = fmaxf(mall, mprev[k]);
+                const bool fire = __any_sync(0xffffffffu, mall >= thr_t);       // step pb-KPM
+                float mk4[KPM];
+#pragma unroll
+                for (int k = 0; k < KPM; ++k) {
                     float m = -3.0e38f;
 #pragma unroll
                     for (int r = 0; r < NR; ++r) { const float2 qv = qray(r, u[k], w[k]); m = fmax3(m, qv.x, qv.y); }
                     mk4[k] = m;
-                    u[k] = c_tab[tb + 2 * (pb + KP + k)]; w[k] = c_tab[tb + 2 * (pb + KP + k) + 1];   // next step (c_tab is over-allocated)
+                    u[k] = c_tab[tb + 2 * (pb + KPM + k)]; w[k] = c_tab[tb + 2 * (pb + KPM + k) + 1];   // next step (c_tab is over-allocated)
                 }
                 if (fire) {                                           // handle step pb-KP first, keep this step pending
-                    slow_step(pb - KP, mprev);
+                    slow_step(pb - KPM, mprev);
 #pragma unroll
-                    for (int k = 0; k < KP; ++k) mprev[k] = mk4[k];
-                    found = true; pb += KP; break;
+                    for (int k = 0; k < KPM; ++k) mprev[k] = mk4[k];
+                    found = true; pb += KPM; break;
                 }
 #pragma unroll
-                for (int k = 0; k < KP; ++k) mprev[k] = mk4[k];
+                for (int k = 0; k < KPM; ++k) mprev[k] = mk4[k];
             }
             if (found) continue;
-            const float mall = fmaxf(fmaxf(mprev[0], mprev[1]), fmaxf(mprev[2], mprev[3]));
-            if (__any_sync(0xffffffffu, mall >= thr_t)) slow_step(npair - KP, mprev);            // flush the last step
+            float mall = mprev[0];
+#pragma unroll
+            for (int k = 1; k < KPM; ++k) mall = fmaxf(mall, mprev[k]);
+            if (__any_sync(0xffffffffu, mall >= thr_t)) slow_step(npair - KPM, mprev);           // flush the last step
             break;
         }
         }
+#endif
         flush();
 
         // ---- planes after the last sphere chunk (trace.py:32-39), then write back (one code copy, ray k*32 + lane) ----
@@ -524,8 +644,8 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
         if (g >= ngroups) break;
         run_group(g);
     }
-    if (q.tl && threadIdx.x == 0) atomicMax(q.tl + 1, globaltimer_ns());
-    if (q.slow) {
+    if (DIAG && q.tl && threadIdx.x == 0) atomicMax(q.tl + 1, globaltimer_ns());
+    if (DIAG && q.slow) {
         const uint32_t tot = __reduce_add_sync(0xffffffffu, slow_cnt), tot2 = __reduce_add_sync(0xffffffffu, exact_cnt);
         if (lane == 0 && tot) { atomicAdd(q.slow, (unsigned long long)tot); atomicAdd(q.slow + 1, (unsigned long long)tot2); }
         unsigned long long tt = tests_cnt;
@@ -542,9 +662,12 @@ struct IsectCfg { int sm_count; int force_nr; int force_nr0; int npre; int pre[6
 
 template <int MODE> static cudaError_t isect3_set_attr() {
     cudaError_t e;
-    if ((e = cudaFuncSetAttribute(k_isect3<MODE, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IsectSmem<8>))) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(k_isect3<MODE, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IsectSmem<4>))) != cudaSuccess) return e;
-    return cudaFuncSetAttribute(k_isect3<MODE, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IsectSmem<2>));
+    if ((e = cudaFuncSetAttribute(k_isect3<MODE, 8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IsectSmem<8>))) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_isect3<MODE, 4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IsectSmem<4>))) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_isect3<MODE, 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IsectSmem<2>))) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_isect3<MODE, 8, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IsectSmem<8>))) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_isect3<MODE, 4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IsectSmem<4>))) != cudaSuccess) return e;
+    return cudaFuncSetAttribute(k_isect3<MODE, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IsectSmem<2>));
 }
 
 // Whole tables tabs[0..n) (each Spad entries) into slots 0..n-1 of THIS module's c_tab: done once per frame when
@@ -566,9 +689,17 @@ static cudaError_t isect3_launch_one(const IsectCfg& cfg, const SceneDev& sc, co
     int nr = cfg.force_nr ? cfg.force_nr : (max_rays >= warps * 256 * 4 ? 8 : (max_rays >= warps * 128 * 4 ? 4 : 2));
     if (MODE == 0 && cfg.force_nr0) nr = cfg.force_nr0;         // (measured: 8 rays/thread wins for the 8-FFMA2 form too)
     const int grid = cfg.sm_count * (nr == 8 ? 2 : 3);
-    if (nr == 8)      k_isect3<MODE, 8><<<grid, kThreads, sizeof(IsectSmem<8>), st>>>(sc, q, pv, c0, cnt, j, tb);
-    else if (nr == 4) k_isect3<MODE, 4><<<grid, kThreads, sizeof(IsectSmem<4>), st>>>(sc, q, pv, c0, cnt, j, tb);
-    else              k_isect3<MODE, 2><<<grid, kThreads, sizeof(IsectSmem<2>), st>>>(sc, q, pv, c0, cnt, j, tb);
+    const bool diag = q.slow != nullptr || q.tl != nullptr;
+    if (diag) {
+        if (nr == 8)      k_isect3<MODE, 8, true><<<grid, kThreads, sizeof(IsectSmem<8>), st>>>(sc, q, pv, c0, cnt, j, tb);
+        else if (nr == 4) k_isect3<MODE, 4, true><<<grid, kThreads, sizeof(IsectSmem<4>), st>>>(sc, q, pv, c0, cnt, j, tb);
+        else              k_isect3<MODE, 2, true><<<grid, kThreads, sizeof(IsectSmem<2>), st>>>(sc, q, pv, c0, cnt, j, tb);
+    } else {
+        if (nr == 8)      k_isect3<MODE, 8, false><<<grid, kThreads, sizeof(IsectSmem<8>), st>>>(sc, q, pv, c0, cnt, j, tb);
+        else if (nr == 4) k_isect3<MODE, 4, false><<<grid, kThreads, sizeof(IsectSmem<4>), st>>>(sc, q, pv, c0, cnt, j, tb);
+        else              k_isect3<MODE, 2, false><<<grid, kThreads, sizeof(IsectSmem<2>), st>>>(sc, q, pv, c0, cnt, j, tb);
+    }
+    g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
     return cudaGetLastError();
 }
 
