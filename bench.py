@@ -196,8 +196,10 @@ def run_ours(args, w):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches0 = _lib.lib().b200rt_launch_count()                # counted by the library at every <<< >>> (this rank)
     e0.record(stream)
+    t_host = time.perf_counter()
     for i in range(args.steps):
         frame(i)
+    host_enqueue_ms = (time.perf_counter() - t_host) * 1e3 / args.steps      # host time to enqueue one frame (no sync inside)
     e1.record(stream)
     launches = int(_lib.lib().b200rt_launch_count() - launches0)
     barrier()
@@ -277,7 +279,7 @@ def run_ours(args, w):
             "e2e": {"value": rays_total / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": e2e_ms,
                     "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
             "gpu_launches": launches,                         # kernels launched inside the timed region (rank 0; b200rt_launch_count)
-            "clocks": clocks,
+            "clocks": clocks, "host_enqueue_ms_per_step": host_enqueue_ms,
             "roofline": {"bound": "fp32", "kernel": "k_isect3 (closest + shadow)", "achieved": ach_tf, "peak": nominal_tf,
                          "unit": "TFLOP/s", "frac": ach_tf / nominal_tf, "traffic": traffic, "traffic_source": traffic_src,
                          "algorithmic_bytes_per_frame": int(rays_this_rank * 40),

@@ -381,6 +381,7 @@ struct SortDev {
     const float4* rayO; const float4* rayD; const unsigned long long* hit; const uint32_t* n_live;
     const GridDev* grid; uint2* keyb; uint32_t* hist; uint32_t* part; uint32_t* base; uint32_t* perm; uint32_t* n_sorted;
     int nb; int use_dir;
+    unsigned long long* tl;      // diagnostic timeline slot: k_key start .. k_perm end (may be null)
 };
 
 // Bounding box of the spheres -> position grid with 2^posbits cells, bits handed to the axis with the largest cell.
@@ -406,7 +407,8 @@ __global__ void __launch_bounds__(256) k_grid(SceneDev sc, int posbits, int dn, 
     }
 }
 
-__global__ void __launch_bounds__(256) k_key(SceneDev sc, SortDev s) {
+__global__ void __launch_bounds__(256, 8) k_key(SceneDev sc, SortDev s) {
+    if (s.tl && threadIdx.x == 0) atomicMin(s.tl, globaltimer_ns());
     const uint32_t n = *s.n_live;
     const GridDev g = *s.grid;
     const uint32_t lane = lane_id();
@@ -454,54 +456,69 @@ __global__ void __launch_bounds__(256) k_key(SceneDev sc, SortDev s) {
 }
 
 // Exclusive scan of the bin counts in two launches: sums of 1024-bin blocks, then every block scans its own bins after
-// adding up the block sums before it (nb / 1024 values).  The counts are zeroed for the next use.
-__global__ void __launch_bounds__(1024) k_binsum(SortDev s) {
-    __shared__ uint32_t sw[32];
-    const uint32_t b = blockIdx.x * 1024u + threadIdx.x;
-    uint32_t v = b < (uint32_t)s.nb ? s.hist[b] : 0u;
+// adding up the block sums before it (nb / 1024 values).  The counts are zeroed for the next use.  256-thread CTAs with
+// 4 bins per thread and <= 32 registers: like k_key / k_perm / k_setup they then fit on an SM NEXT TO two resident
+// k_isect3<shadow> CTAs (8192 registers, 2 KB of shared memory are left), so the dependent chain does not wait for a
+// persistent shadow CTA to retire before each of these small launches (profiles/r01_v8: ~250 us per depth at 1/8 frame).
+__global__ void __launch_bounds__(256, 8) k_binsum(SortDev s) {
+    __shared__ uint32_t sw[8];
+    const uint32_t b0 = blockIdx.x * 1024u + threadIdx.x * 4u;
+    uint32_t v = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) v += (b0 + k < (uint32_t)s.nb) ? s.hist[b0 + k] : 0u;
     v = __reduce_add_sync(0xffffffffu, v);
     if (lane_id() == 0) sw[threadIdx.x >> 5] = v;
     __syncthreads();
-    if (threadIdx.x < 32) { v = __reduce_add_sync(0xffffffffu, sw[threadIdx.x]); if (threadIdx.x == 0) s.part[blockIdx.x] = v; }
+    if (threadIdx.x == 0) { uint32_t t = 0; for (int k = 0; k < 8; ++k) t += sw[k]; s.part[blockIdx.x] = t; }
 }
-__global__ void __launch_bounds__(1024) k_binscan(SortDev s) {
-    __shared__ uint32_t sw[32]; __shared__ uint32_t s_off;
+__global__ void __launch_bounds__(256, 8) k_binscan(SortDev s) {
+    __shared__ uint32_t sw[8]; __shared__ uint32_t s_off;
     uint32_t pre = 0;
-    for (uint32_t t = threadIdx.x; t < blockIdx.x; t += 1024u) pre += s.part[t];
+    for (uint32_t t = threadIdx.x; t < blockIdx.x; t += 256u) pre += s.part[t];
     pre = __reduce_add_sync(0xffffffffu, pre);
     if (lane_id() == 0) sw[threadIdx.x >> 5] = pre;
     __syncthreads();
-    if (threadIdx.x < 32) { const uint32_t v = __reduce_add_sync(0xffffffffu, sw[threadIdx.x]); if (threadIdx.x == 0) s_off = v; }
+    if (threadIdx.x == 0) { uint32_t t = 0; for (int k = 0; k < 8; ++k) t += sw[k]; s_off = t; }
     __syncthreads();
     const uint32_t off = s_off;
-    const uint32_t b = blockIdx.x * 1024u + threadIdx.x;
-    const uint32_t v = b < (uint32_t)s.nb ? s.hist[b] : 0u;
-    uint32_t x = v;
+    const uint32_t b0 = blockIdx.x * 1024u + threadIdx.x * 4u;
+    uint32_t v[4], sum = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { v[k] = (b0 + k < (uint32_t)s.nb) ? s.hist[b0 + k] : 0u; sum += v[k]; }
+    uint32_t x = sum;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, d); if ((int)lane_id() >= d) x += y; }
     __syncthreads();
     if (lane_id() == 31) sw[threadIdx.x >> 5] = x;
     __syncthreads();
-    if (threadIdx.x < 32) { const uint32_t w = sw[threadIdx.x]; uint32_t y = w;
+    uint32_t woff = 0;
+    for (uint32_t k = 0; k < (threadIdx.x >> 5); ++k) woff += sw[k];
+    uint32_t excl = off + woff + x - sum;
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) { const uint32_t z = __shfl_up_sync(0xffffffffu, y, d); if ((int)threadIdx.x >= d) y += z; }
-        sw[threadIdx.x] = y - w; }
-    __syncthreads();
-    const uint32_t excl = off + sw[threadIdx.x >> 5] + x - v;
-    if (b < (uint32_t)s.nb) { s.base[b] = excl; s.hist[b] = 0u; }
-    if (b == (uint32_t)s.nb - 1u) *s.n_sorted = excl + v;
+    for (int k = 0; k < 4; ++k) {
+        if (b0 + k < (uint32_t)s.nb) { s.base[b0 + k] = excl; s.hist[b0 + k] = 0u; }
+        excl += v[k];
+        if (b0 + k == (uint32_t)s.nb - 1u) *s.n_sorted = excl;
+    }
 }
-__global__ void __launch_bounds__(256) k_perm(SortDev s) {
+__global__ void __launch_bounds__(256, 8) k_perm(SortDev s) {
     const uint32_t n = *s.n_live;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const uint2 k = s.keyb[i];
         if (k.x != 0xffffffffu) s.perm[s.base[k.x] + k.y] = i;
     }
+    if (s.tl && threadIdx.x == 0) atomicMax(s.tl + 1, globaltimer_ns());
 }
 
 // ------------------------------------------------------------------------------------------------
 // Per-hit shading kernels (trace.py:56-110, :123-131) — <1 % of the work at S=1024
 // ------------------------------------------------------------------------------------------------
+#ifndef B200RT_SETUP_OCC
+#define B200RT_SETUP_OCC 8      // CTAs per SM the register allocation of k_setup aims at (8 -> 32 registers)
+#endif
+#ifndef B200RT_SHADE_OCC
+#define B200RT_SHADE_OCC 8
+#endif
 struct ShadeDev {
     const float4* rayO; const float4* rayD;      // this depth's ray queue (k_setup input)
     const unsigned long long* hit;               // packed closest hit per ray (k_setup input)
@@ -520,7 +537,7 @@ struct ShadeDev {
 };
 
 // trace.py:56-83: miss -> path ends; hit -> P = O + tD, colour/normal by object type, P += BIAS*N.
-__global__ void __launch_bounds__(256, 6) k_setup(SceneDev sc, ShadeDev s) {
+__global__ void __launch_bounds__(256, B200RT_SETUP_OCC) k_setup(SceneDev sc, ShadeDev s) {   // <= 32 registers: fits beside two resident k_isect3<shadow> CTAs (see k_binsum)
     if (s.tl && threadIdx.x == 0) atomicMin(s.tl, globaltimer_ns());
     const uint32_t n = *s.n_live;
     const uint32_t nchunks = (n + 255u) / 256u;
@@ -600,7 +617,7 @@ __global__ void __launch_bounds__(256, 6) k_setup(SceneDev sc, ShadeDev s) {
 
 // trace.py:77,86-102 and the accumulate of trace.py:131: RGB_trace = amb*col + sum_j [visible_j && k_j>0] k_j*col,
 // acc[slot] += weight * RGB_trace.  (The reflection ray of trace.py:104-110 was queued by k_setup.)
-__global__ void __launch_bounds__(256) k_shade(SceneDev sc, ShadeDev s) {
+__global__ void __launch_bounds__(256, B200RT_SHADE_OCC) k_shade(SceneDev sc, ShadeDev s) {
     if (s.tl && threadIdx.x == 0) atomicMin(s.tl, globaltimer_ns());
     const uint32_t n = *s.n_hit;
     for (uint32_t h = blockIdx.x * blockDim.x + threadIdx.x; h < n; h += gridDim.x * blockDim.x) {
@@ -826,7 +843,7 @@ struct DevCtx {
     Buf hP[kSets], hN[kSets], occl[kSets], shidx[kSets], shidx2[kSets];   // hit records / shadow state: ring of kSets depths
     Buf acc, ctr, work, slow, tl, ostat;
     Buf sortKey, sortPerm, sortHist, sortBase, sortPart, sortGrid;   // regrouping of bounce-depth hits (k_key .. k_perm)
-    bool no_sort = false; int sort_posbits = 13, sort_dirn = 4;     // env B200RT_NO_SORT, B200RT_SORT_POSBITS, B200RT_SORT_DIRN
+    bool no_sort = false; int sort_posbits = -1, sort_dirn = -1;     // env B200RT_NO_SORT, B200RT_SORT_POSBITS, B200RT_SORT_DIRN (-1: chosen from the queue size)
     int npre = 1, pre[6] = {256, 0, 0, 0, 0, 0};                    // leading shadow passes (env B200RT_PASSES=a,b,...; multiples of 8)
     bool timeline = false;                                        // env B200RT_TIMELINE: per-launch first-start / last-end (globaltimer) to stderr
     // internal streams (see the launch sequence in render_device): the dependent chain at high priority, one stream per
@@ -1029,13 +1046,19 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     CK(c.acc.ensure(sizeof(float) * 3 * cap));
     // regrouping of the hits of depth >= 1 (see k_key): worth it where beam culling is on and a query is expensive
     const bool regroup = cull && use_lists && S >= 64 && depth >= 1 && !(a->flags & B200RT_F_NO_SORT) && !c.no_sort;
-    const int sort_nb = 6 * c.sort_dirn * c.sort_dirn << c.sort_posbits, sort_nblk = (sort_nb + 1023) / 1024;
+    // Bin grid of the regrouping: ~40-170 rays per bin measured best at every frame share (C4: 13 position bits and 3x3
+    // direction cells per cube face for the whole 33 M-ray frame, 10 bits / 2x2 for 1/8 of it) — bins much smaller than
+    // a ray group only fragment the groups.
+    int sort_posbits = c.sort_posbits, sort_dirn = c.sort_dirn;
+    if (sort_posbits < 0) { sort_posbits = 6; while (sort_posbits < 15 && ((size_t)5793 << sort_posbits) < cap) ++sort_posbits; }   // round(log2(cap / 4096))
+    if (sort_dirn < 0) sort_dirn = cap >= ((size_t)24 << 20) ? 3 : 2;
+    const int sort_nb = 6 * sort_dirn * sort_dirn << sort_posbits, sort_nblk = (sort_nb + 1023) / 1024;
     if (regroup) {
         CK(c.sortKey.ensure(sizeof(uint2) * cap)); CK(c.sortPerm.ensure(sizeof(uint32_t) * cap));
         CK(c.sortHist.ensure(sizeof(uint32_t) * sort_nb)); CK(c.sortBase.ensure(sizeof(uint32_t) * sort_nb));
         CK(c.sortPart.ensure(sizeof(uint32_t) * sort_nblk)); CK(c.sortGrid.ensure(sizeof(GridDev)));
         CK(cudaMemsetAsync(c.sortHist.p, 0, sizeof(uint32_t) * sort_nb, st));
-        k_grid<<<1, 256, 0, st>>>(sc, c.sort_posbits, c.sort_dirn, c.sortGrid.as<GridDev>()); CKL();
+        k_grid<<<1, 256, 0, st>>>(sc, sort_posbits, sort_dirn, c.sortGrid.as<GridDev>()); CKL();
     }
     // k_setup's ordered compaction: [pass][chunk of 256 rays][8 queues] status words + the chunk ticket, zeroed before every launch
     const size_t ostat_stride = ((cap + 255) / 256) * 8;
@@ -1142,10 +1165,11 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             tm.begin(2);
             if (regroup && d >= 1) {
                 SortDev so{ q.rayO, q.rayD, q.hit, n_live, c.sortGrid.as<GridDev>(), c.sortKey.as<uint2>(), c.sortHist.as<uint32_t>(), c.sortPart.as<uint32_t>(),
-                            c.sortBase.as<uint32_t>(), c.sortPerm.as<uint32_t>(), cd + 2, sort_nb, d < depth ? 1 : 0 };
+                            c.sortBase.as<uint32_t>(), c.sortPerm.as<uint32_t>(), cd + 2, sort_nb, d < depth ? 1 : 0, nullptr };
+                if (tlb) { so.tl = tlb + 2 * (size_t)tln++; tlname.push_back("sort d" + std::to_string(d)); }
                 k_key<<<small_grid, 256, 0, cs>>>(sc, so); CKL();
-                k_binsum<<<sort_nblk, 1024, 0, cs>>>(so); CKL();
-                k_binscan<<<sort_nblk, 1024, 0, cs>>>(so); CKL();
+                k_binsum<<<sort_nblk, 256, 0, cs>>>(so); CKL();
+                k_binscan<<<sort_nblk, 256, 0, cs>>>(so); CKL();
                 k_perm<<<small_grid, 256, 0, cs>>>(so); CKL();
                 s.perm = so.perm; s.n_live = cd + 2;                                      // k_setup walks the hits in bin order
             }

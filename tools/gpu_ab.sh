@@ -12,7 +12,7 @@ import json,sys
 n=sys.argv[1]
 try:
     d=json.loads(open('gpurun_out/ab_%s.json'%n).read().strip().splitlines()[-1]); r=d['roofline']
-    print(n, 'ms', round(d['ms_per_step'],3), 'closest', round(r['kernel_ms_closest'],3), 'shadow', round(r['kernel_ms_shadow'],3), 'other', round(r['other_ms'],3), 'e2e', round(d['e2e']['ms_per_step'],3))
+    print(n, "ms", round(d["ms_per_step"],3), "host", round(d.get("host_enqueue_ms_per_step",0),3), 'closest', round(r['kernel_ms_closest'],3), 'shadow', round(r['kernel_ms_shadow'],3), 'other', round(r['other_ms'],3), 'e2e', round(d['e2e']['ms_per_step'],3))
 except Exception as e: print(n, 'ERR', e, open('gpurun_out/ab_%s.err'%n).read()[-600:])
 PY
 done

@@ -8,7 +8,7 @@ for e in "" "$@"; do
 import json,sys
 try:
     d=json.loads(open('gpurun_out/sweep.json').read().strip().splitlines()[-1]); r=d['roofline']
-    print('[%s]'%sys.argv[1], 'ms', round(d['ms_per_step'],3), 'closest', round(r['kernel_ms_closest'],3), 'shadow', round(r['kernel_ms_shadow'],3), 'other', round(r['other_ms'],3), 'e2e', round(d['e2e']['ms_per_step'],3))
+    print('[%s]'%sys.argv[1], 'ms', round(d['ms_per_step'],3), 'host', round(d.get('host_enqueue_ms_per_step',0),3), 'closest', round(r['kernel_ms_closest'],3), 'shadow', round(r['kernel_ms_shadow'],3), 'other', round(r['other_ms'],3), 'e2e', round(d['e2e']['ms_per_step'],3))
 except Exception as ex: print(sys.argv[1], 'ERR', ex, open('gpurun_out/sweep.err').read()[-400:])
 PY
 done
