@@ -217,6 +217,23 @@ def run_ours(args, w):
         st2[k] = st3[k]
     isect_ms = st2["ms_closest"] + st2["ms_shadow"]
     rays_this_rank = st2["rays"]
+    # (c) the brute-force mode (B200RT_F_DENSE: every specified query scans every sphere, nothing culled): the figure the
+    # FP32-peak target of north_star is about.  Counters from one diagnostic frame, times from production-kernel frames.
+    dense = None
+    if rank == 0 and S >= 64:
+        sd = frame(0, stats=True, flags=_lib.F_DENSE)
+        frame(0, flags=_lib.F_DENSE)
+        torch.cuda.synchronize()
+        d0, d1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n_dense = max(1, min(args.steps, 3))
+        d0.record(stream)
+        for i in range(n_dense):
+            frame(i, flags=_lib.F_DENSE)
+        d1.record(stream)
+        torch.cuda.synchronize()
+        sdt = frame(0, stats=True, flags=_lib.F_DENSE | _lib.F_TIME_ONLY)
+        dense = {"ms_per_frame": d0.elapsed_time(d1) / n_dense, "kernel_ms_per_frame": sdt["ms_closest"] + sdt["ms_shadow"],
+                 "tests_pivot": sd["tests_pivot"], "tests_general": sd["tests_general"], "rays": sd["rays"]}
 
     # end to end: host buffers through b200rt_render_host, copies inside the timed region; N>1: + NCCL gather of strips
     host_out = torch.zeros((3, W, H), dtype=torch.uint8).pin_memory().numpy()      # pinned: the D2H of the framebuffer is a DMA
@@ -294,6 +311,14 @@ def run_ours(args, w):
                          "executed_tflops": (8.0 * st2["tests_pivot"] + 16.0 * st2["tests_general"]) / (isect_ms * 1e-3) / 1e12,
                          "executed_frac": (8.0 * st2["tests_pivot"] + 16.0 * st2["tests_general"]) / (isect_ms * 1e-3) / 1e12 / nominal_tf,
                          "frac_note": "frac = canonical brute-force FLOPs (16 per ray-sphere test, SURVEY 8d) / kernel time / peak; it exceeds the FMA-pipe utilisation because the kernel executes 8 FLOP per test in the pivot form and skips tests that cannot change the image (executed_frac = FLOPs actually issued / peak)",
+                         "dense_mode": None if dense is None else {
+                             "what": "B200RT_F_DENSE: brute force as the reference specifies it - every query scans every sphere (no beam culling, regrouping, shadow passes or lit-pair lists); same image",
+                             "ms_per_frame": dense["ms_per_frame"], "mrays_per_s": dense["rays"] / (dense["ms_per_frame"] * 1e-3) / 1e6,
+                             "kernel_ms_per_frame": dense["kernel_ms_per_frame"],
+                             "algorithmic_tflops": dense["rays"] * fpr / (dense["kernel_ms_per_frame"] * 1e-3) / 1e12,
+                             "frac": dense["rays"] * fpr / (dense["kernel_ms_per_frame"] * 1e-3) / 1e12 / nominal_tf,
+                             "executed_tflops": (8.0 * dense["tests_pivot"] + 16.0 * dense["tests_general"]) / (dense["kernel_ms_per_frame"] * 1e-3) / 1e12,
+                             "executed_frac": (8.0 * dense["tests_pivot"] + 16.0 * dense["tests_general"]) / (dense["kernel_ms_per_frame"] * 1e-3) / 1e12 / nominal_tf},
                          "framebuffer_write_gbs": 3.0 * W * H / world / (st2["ms_total"] * 1e-3) / 1e9,
                          "hbm_peak_gbs": peaks.get("hbm_gbs")},
         }

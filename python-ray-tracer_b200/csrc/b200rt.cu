@@ -514,10 +514,10 @@ __global__ void __launch_bounds__(256, 8) k_perm(SortDev s) {
 // Per-hit shading kernels (trace.py:56-110, :123-131) — <1 % of the work at S=1024
 // ------------------------------------------------------------------------------------------------
 #ifndef B200RT_SETUP_OCC
-#define B200RT_SETUP_OCC 8      // CTAs per SM the register allocation of k_setup aims at (8 -> 32 registers)
+#define B200RT_SETUP_OCC 6      // CTAs per SM the register allocation of k_setup aims at (6 -> 40 registers, no spills; 8 -> 32 with 60 B of spills: no gain measured)
 #endif
 #ifndef B200RT_SHADE_OCC
-#define B200RT_SHADE_OCC 8
+#define B200RT_SHADE_OCC 6
 #endif
 struct ShadeDev {
     const float4* rayO; const float4* rayD;      // this depth's ray queue (k_setup input)
@@ -1013,7 +1013,8 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
                                                  c.pivPerm.as<int>(), c.pivTab.as<float4>(), c.pivPos.as<float4>(), c.pivRad.as<float>());
         CKL();
     }
-    const bool cull = !(a->flags & B200RT_F_NO_CULL) && !c.no_cull;
+    const bool dense = (a->flags & B200RT_F_DENSE) != 0;          // brute force: every specified query scans every sphere
+    const bool cull = !(a->flags & B200RT_F_NO_CULL) && !c.no_cull && !dense;
     const PivotDev pv{ c.pivTab.as<float4>(), c.pivPos.as<float4>(), c.cmax.as<float>(), c.pivPerm.as<int>(), cull ? c.pivRad.as<float>() : nullptr };
     // Constant-memory residency (isect3.cuh): the closest-hit module holds the camera-pivot and origin-free tables,
     // the shadow module one table per light.  When they fit they are uploaded once per frame.
@@ -1021,8 +1022,8 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     const bool closest_res = !nofilter && 2 * Spad <= kTabCap, shadow_res = !nofilter && L > 0 && L * Spad <= kTabCap;
     if (closest_res) { const int tabs[2] = { L, L + 1 }; CK(isect3_upload_resident(pv, Spad, tabs, 2, st)); }
     if (shadow_res) CK(shadow_upload_resident(pv, Spad, L, st));
-    IsectCfg icfg{ c.sm_count, c.force_nr, c.force_nr0, c.npre, {0, 0, 0, 0, 0, 0} };
-    for (int k = 0; k < c.npre; ++k) icfg.pre[k] = c.pre[k];
+    IsectCfg icfg{ c.sm_count, c.force_nr, c.force_nr0, dense ? 0 : c.npre, {0, 0, 0, 0, 0, 0} };
+    for (int k = 0; k < icfg.npre; ++k) icfg.pre[k] = c.pre[k];
 
     // ---- chunking: whole columns, <= max_paths slots per chunk ----
     const size_t per_col = (size_t)ns * H;
@@ -1032,7 +1033,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     if (tiled) cols_per_chunk &= ~(size_t)15;
     const int nchunks = (int)((ncols + cols_per_chunk - 1) / cols_per_chunk);
     const size_t cap = cols_per_chunk * per_col;                 // slots per chunk
-    const bool use_lists = S >= 32 && !(a->flags & B200RT_F_NO_FILTER);
+    const bool use_lists = S >= 32 && !(a->flags & B200RT_F_NO_FILTER) && !dense;
     for (int b = 0; b < 2; ++b) {                                // depth d: ray queue d & 1 (see the launch sequence below)
         CK(c.rayO[b].ensure(sizeof(float4) * cap)); CK(c.rayD[b].ensure(sizeof(float4) * cap));
         CK(c.hitKey[b].ensure(sizeof(unsigned long long) * cap));

@@ -230,6 +230,10 @@ def test_culling_and_passes_do_not_change_the_image(oracle, S, L, W, H, depth, a
     assert st["rays"] == st_ns["rays"] and st["shadow_traced"] == st_ns["shadow_traced"]
     assert np.array_equal(got, _cuda(g, flags=_lib.F_NO_FILTER)), "filtered path differs from exact-test-on-everything"
     assert st["rays"] == st_nc["rays"]
+    dense, st_d = _cuda(g, flags=_lib.F_DENSE, stats=True)            # brute force: the mode bench.py's FP32-peak figure is measured in
+    assert np.array_equal(got, dense), "dense (brute-force) mode differs from the production path"
+    assert st_d["rays"] == st["rays"] and st_d["shadow_traced"] == st_d["shadow"]
+    assert st_d["tests_pivot"] + st_d["tests_general"] >= st["rays"] * S       # every specified test is executed
     canonical = st["rays"] * S
     executed, executed_nc = st["tests_pivot"] + st["tests_general"], st_nc["tests_pivot"] + st_nc["tests_general"]
     print(dict(S=S, L=L, canonical=canonical, executed=executed, executed_no_cull=executed_nc))
