@@ -25,6 +25,7 @@
 #include "../../include/b200rt.h"
 #include "rt_math.cuh"
 #include "isect3.cuh"
+#include "shadow_grid.cuh"
 
 namespace b200rt {
 
@@ -842,8 +843,9 @@ struct DevCtx {
     Buf rayO[2], rayD[2], hitKey[2];                               // ray queues, double-buffered by depth parity
     Buf hP[kSets], hN[kSets], occl[kSets], shidx[kSets], shidx2[kSets];   // hit records / shadow state: ring of kSets depths
     Buf acc, ctr, work, slow, tl, ostat;
+    Buf sgCells, sgTab, sgCone;                                      // per-light direction grids of the shadow queries (shadow_grid.cuh)
     Buf sortKey, sortPerm, sortHist, sortBase, sortPart, sortGrid;   // regrouping of bounce-depth hits (k_key .. k_perm)
-    bool no_sort = false; int sort_posbits = -1, sort_dirn = -1;     // env B200RT_NO_SORT, B200RT_SORT_POSBITS, B200RT_SORT_DIRN (-1: chosen from the queue size)
+    bool no_sgrid = false; bool no_sort = false; int sort_posbits = -1, sort_dirn = -1;     // env B200RT_NO_SORT, B200RT_SORT_POSBITS, B200RT_SORT_DIRN (-1: chosen from the queue size)
     int npre = 1, pre[6] = {256, 0, 0, 0, 0, 0};                    // leading shadow passes (env B200RT_PASSES=a,b,...; multiples of 8)
     bool timeline = false;                                        // env B200RT_TIMELINE: per-launch first-start / last-end (globaltimer) to stderr
     // internal streams (see the launch sequence in render_device): the dependent chain at high priority, one stream per
@@ -856,7 +858,7 @@ struct DevCtx {
     cudaEvent_t done = nullptr; bool has_done = false;
     void release_all() {
         Buf* all[] = { &sphA, &sphB, &sphCol, &plO, &plN, &plNu, &plCol, &lights, &cmax, &pivTab, &pivPos, &pivPerm, &pivRad, &stage, &rayO[0], &rayO[1], &rayD[0], &rayD[1], &hitKey[0], &hitKey[1],
-                       &acc, &tl, &ostat, &ctr, &work, &slow, &sortKey, &sortPerm, &sortHist, &sortBase, &sortPart, &sortGrid, &hostResult, &hostPixelLoc, &imgOut, &batchScene };
+                       &acc, &tl, &ostat, &ctr, &work, &slow, &sortKey, &sortPerm, &sortHist, &sortBase, &sortPart, &sortGrid, &sgCells, &sgTab, &sgCone, &hostResult, &hostPixelLoc, &imgOut, &batchScene };
         for (Buf* b : all) b->release();
         for (int i = 0; i < kSets; ++i) { hP[i].release(); hN[i].release(); occl[i].release(); shidx[i].release(); shidx2[i].release(); }
         if (done) { cudaEventDestroy(done); done = nullptr; } has_done = false; init = false;
@@ -937,6 +939,7 @@ int init_ctx(DevCtx& c, int device) {
     { const char* e = getenv("B200RT_NO_CULL"); c.no_cull = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_TIMELINE"); c.timeline = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_NO_SORT"); c.no_sort = e && atoi(e) != 0; }
+    { const char* e = getenv("B200RT_NO_SGRID"); c.no_sgrid = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_SORT_POSBITS"); if (e) c.sort_posbits = std::min(18, std::max(0, atoi(e))); }
     { const char* e = getenv("B200RT_SORT_DIRN"); if (e) c.sort_dirn = std::min(16, std::max(1, atoi(e))); }
     if (const char* e = getenv("B200RT_PASSES")) {
@@ -1021,7 +1024,17 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     const bool nofilter = (a->flags & B200RT_F_NO_FILTER) != 0;
     const bool closest_res = !nofilter && 2 * Spad <= kTabCap, shadow_res = !nofilter && L > 0 && L * Spad <= kTabCap;
     if (closest_res) { const int tabs[2] = { L, L + 1 }; CK(isect3_upload_resident(pv, Spad, tabs, 2, st)); }
-    if (shadow_res) CK(shadow_upload_resident(pv, Spad, L, st));
+    // Shadow queries through the per-light direction grids (shadow_grid.cuh) wherever work may be skipped at all
+    // (beam culling on) and a query is expensive; k_isect3<shadow> stays for the brute-force / debug modes and tiny scenes.
+    const bool sgrid = cull && !nofilter && S >= 64 && S <= 65535 && L > 0 && !(a->flags & B200RT_F_NO_SGRID) && !c.no_sgrid;
+    ShadowGridDev sg{};
+    if (sgrid) {
+        CK(c.sgCells.ensure(sizeof(uint16_t) * (size_t)L * kSgCells * kSgRec));
+        CK(c.sgTab.ensure(sizeof(float4) * (size_t)L * S)); CK(c.sgCone.ensure(sizeof(float4) * (size_t)L * S));
+        sg = ShadowGridDev{ c.sgCells.as<uint16_t>(), c.sgTab.as<float4>(), c.sgCone.as<float4>() };
+        k_sgrid_tab<<<(L * S + 255) / 256, 256, 0, st>>>(sc, sg); CKL();
+        k_sgrid_build<<<dim3(kSgCells / 256, L), 256, 0, st>>>(sc, sg); CKL();
+    } else if (shadow_res) CK(shadow_upload_resident(pv, Spad, L, st));
     IsectCfg icfg{ c.sm_count, c.force_nr, c.force_nr0, dense ? 0 : c.npre, {0, 0, 0, 0, 0, 0} };
     for (int k = 0; k < icfg.npre; ++k) icfg.pre[k] = c.pre[k];
 
@@ -1097,7 +1110,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     }
     auto tl_mark = [&](const char* nm, int d, int from) { for (int i = from; i < tln; ++i) tlname.push_back(std::string(nm) + " d" + std::to_string(d) + (tln - from > 1 ? " j" + std::to_string(i - from) : "")); };
     // concurrency needs launches that do not touch shared constant memory
-    const bool conc = !stats && !nofilter && S >= 64 && closest_res && (L == 0 || shadow_res) && !c.no_conc;
+    const bool conc = !stats && !nofilter && S >= 64 && closest_res && (L == 0 || shadow_res || sgrid) && !c.no_conc;
     cudaStream_t cs = conc ? c.chainStream : st, ss = conc ? c.shadeStream : st;
     const int nls = std::max(1, std::min(L, kSide));
     if (conc) { CK(cudaEventRecord(c.evFork, st)); CK(cudaStreamWaitEvent(cs, c.evFork, 0)); }
@@ -1184,6 +1197,14 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             if (L > 0) {
                 tm.begin(1);
                 if (nofilter) { q.n_in = cd + 3; q.work = cd + 2; if (int rc = launch_intersect<true>(c, sc, q, true, cs)) return rc; }
+                else if (sgrid) {                       // one launch for all lights of this depth
+                    ShadowGridArgs ga{ q.hP, s.shidx, cap, cd + 4, q.occl, cap, pv.piv, pv.bounds, q.slow, nullptr };
+                    cudaStream_t ls = conc ? c.lightStream[0] : cs;
+                    if (conc) CK(cudaStreamWaitEvent(ls, c.evSetup[hs], 0));
+                    if (tlb) { ga.tl = tlb + 2 * (size_t)tln++; tlname.push_back("shadow grid d" + std::to_string(d)); }
+                    k_shadow_grid<<<dim3(c.sm_count * 6, L), 256, 0, ls>>>(sc, sg, ga); CKL();
+                    if (conc) { CK(cudaEventRecord(c.evLight[0], ls)); CK(cudaStreamWaitEvent(ss, c.evLight[0], 0)); }
+                }
                 else {
                     ShadowPlan sp{};
                     sp.list0 = s.shidx; sp.list1 = use_lists ? c.shidx2[hs].as<uint32_t>() : nullptr; sp.cap = cap;

@@ -1,0 +1,179 @@
+// shadow_grid.cuh — shadow queries through a per-light direction grid (reference trace.py:86-96: "is anything hit by
+// the ray from the biased hit point towards light j?", answered by get_intersection over every sphere and plane).
+//
+// Every shadow ray of light j lies — to within e <= 2^-20 |V-P|, the rounding of its normalised direction — on a line
+// through the light position V.  Seen from V, a sphere (C, r) can only be met by such a line if the line's direction
+// is within alpha = asin(r / |C-V|) of +-(C-V) (the reference's shadow ray does not stop at the light, SURVEY F8, so
+// spheres behind the light count as well: hence both signs).  Once per frame k_sgrid_build lists, for each cell of a
+// cube map of directions around V, the spheres whose cone reaches the cell; a shadow query then looks at the ONE cell
+// its direction falls in and runs, over that cell's few spheres, exactly what k_isect3<shadow> runs over all of them:
+// the 4-FMA pivot filter with the same operands, operation order and per-ray threshold, then sphere_exact on the real
+// ray for the candidates, then the planes.  The grid only removes spheres that provably cannot be hit, so the image is
+// bit-identical to the brute-force path (tests/test_gpu_parity.py compares with B200RT_F_DENSE / B200RT_F_NO_FILTER):
+//   * radius inflated by 2e-3 + 1e-3 r: covers e (<= 2.5e-4), the exact test's rounding (<= 1e-4 in the perpendicular
+//     distance) for |V-P| <= kSgRange and coordinates <= kSgRange; rays from farther away, lights / scenes beyond that
+//     range and cells whose list overflows scan every sphere instead (still through the same filter);
+//   * cell cones widened by 2e-3 rad: covers the rounding of the cell lookup and of the asin / acos used to build.
+#pragma once
+#include "isect3.cuh"
+
+namespace b200rt {
+
+constexpr int kSgN = 32;                          // cells per edge of a cube-map face
+constexpr int kSgCells = 6 * kSgN * kSgN;         // cells per light
+constexpr int kSgRec = 128;                       // uint16 per cell record: [0] count (0xffff: scan every sphere), [4 ..] sphere ids
+constexpr int kSgCap = kSgRec - 4;
+constexpr float kSgRange = 256.f;
+
+struct ShadowGridDev {
+    uint16_t* cells;                              // [L][kSgCells][kSgRec]
+    float4* ltab;                                 // [L][S] (Cx, Cy, Cz, k = r^2 - |C - V_j|^2), k as in k_pivot (float64, rounded once)
+    float4* cone;                                 // [L][S] (unit direction V_j -> C, alpha); alpha >= pi: the sphere reaches every cell
+};
+
+// Cube-map cell of a direction (any length, not all zero): face = 2 * major axis + (negative ? 1 : 0), (u, v) = the other
+// two components over the major one's magnitude.  Approximate arithmetic: the lists carry a margin for a wrong neighbour.
+__device__ __forceinline__ int sg_cell(float x, float y, float z) {
+    const float ax = fabsf(x), ay = fabsf(y), az = fabsf(z);
+    float m, u, v; int face;
+    if (ax >= ay && ax >= az) { m = ax; u = y; v = z; face = x < 0.f ? 1 : 0; }
+    else if (ay >= az)        { m = ay; u = x; v = z; face = y < 0.f ? 3 : 2; }
+    else                      { m = az; u = x; v = y; face = z < 0.f ? 5 : 4; }
+    const float im = 0.5f * (float)kSgN / fmaxf(m, 1e-30f);
+    const int iu = min(kSgN - 1, max(0, (int)(u * im + 0.5f * (float)kSgN)));
+    const int iv = min(kSgN - 1, max(0, (int)(v * im + 0.5f * (float)kSgN)));
+    return (face * kSgN + iu) * kSgN + iv;
+}
+__device__ __forceinline__ V3 sg_dir(int face, float a, float b) {       // un-normalised direction of face coordinates (a, b) in [-1, 1]
+    const float s = (face & 1) ? -1.f : 1.f;
+    return (face >> 1) == 0 ? mk(s, a, b) : (face >> 1) == 1 ? mk(a, s, b) : mk(a, b, s);
+}
+
+// One thread per (light j, sphere s): filter operand k and the sphere's cone seen from the light.
+__global__ void __launch_bounds__(256) k_sgrid_tab(SceneDev sc, ShadowGridDev g) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= sc.L * sc.S) return;
+    const int j = idx / sc.S, s = idx - j * sc.S;
+    const float4 v = sc.lights[j], sp = sc.sphB[s];
+    const double ex = (double)sp.x - v.x, ey = (double)sp.y - v.y, ez = (double)sp.z - v.z;
+    const double d2 = ex * ex + ey * ey + ez * ez;
+    g.ltab[idx] = make_float4(sp.x, sp.y, sp.z, (float)((double)sp.w - d2));
+    const double dist = sqrt(d2), r = sqrt(fmax((double)sp.w, 0.0));
+    const double reff = r * 1.001 + 2e-3;
+    float4 c = make_float4(1.f, 0.f, 0.f, 4.f);                            // alpha = 4 > pi: every cell
+    if (dist > reff * 1.0001 && dist < 1e30) c = make_float4((float)(ex / dist), (float)(ey / dist), (float)(ez / dist), (float)asin(reff / dist));
+    g.cone[idx] = c;
+}
+
+// One thread per (cell, light): the ascending list of the spheres whose cone (either sign) reaches the cell's cone.
+__global__ void __launch_bounds__(256) k_sgrid_build(SceneDev sc, ShadowGridDev g) {
+    __shared__ float4 s_cone[256];
+    const int cell = blockIdx.x * 256 + threadIdx.x, j = blockIdx.y;       // kSgCells % 256 == 0
+    const int face = cell / (kSgN * kSgN), iu = (cell / kSgN) % kSgN, iv = cell % kSgN;
+    const float h = 2.f / (float)kSgN, a0 = -1.f + h * (float)iu, b0 = -1.f + h * (float)iv;
+    const V3 cdir = normalize3(sg_dir(face, a0 + 0.5f * h, b0 + 0.5f * h));
+    float beta = 0.f;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const V3 q = normalize3(sg_dir(face, a0 + ((k & 1) ? h : 0.f), b0 + ((k & 2) ? h : 0.f)));
+        beta = fmaxf(beta, acosf(fminf(1.f, dot3(q, cdir))));
+    }
+    beta += 2e-3f;
+    const float4 v = sc.lights[j];
+    const bool in_range = sc.cmax[0] + sqrtf(v.x * v.x + v.y * v.y + v.z * v.z) <= kSgRange;    // (NaN -> false)
+    uint16_t* rec = g.cells + ((size_t)j * kSgCells + cell) * kSgRec;
+    uint32_t cnt = 0;
+    for (int s0 = 0; s0 < sc.S; s0 += 256) {
+        __syncthreads();
+        if (s0 + (int)threadIdx.x < sc.S) s_cone[threadIdx.x] = g.cone[(size_t)j * sc.S + s0 + threadIdx.x];
+        __syncthreads();
+        const int n = min(256, sc.S - s0);
+        for (int k = 0; k < n; ++k) {
+            const float4 c = s_cone[k];
+            const float ang = acosf(fminf(1.f, fabsf(c.x * cdir.x + c.y * cdir.y + c.z * cdir.z)));
+            if (ang <= c.w + beta) { if (cnt < (uint32_t)kSgCap) rec[4 + cnt] = (uint16_t)(s0 + k); ++cnt; }
+        }
+    }
+    const bool over = cnt > (uint32_t)kSgCap || !in_range;
+    for (uint32_t k = min(cnt, (uint32_t)kSgCap); k < (uint32_t)kSgCap && (k & 3u); ++k) rec[4 + k] = 0;   // pad the last group of four
+    rec[0] = over ? (uint16_t)0xffff : (uint16_t)cnt;
+    rec[1] = (uint16_t)min(cnt, 0xffffu);                                   // diagnostic: the uncapped count
+}
+
+struct ShadowGridArgs {
+    const float4* hP;                    // hit records (biased hit point, slot)
+    const uint32_t* lists; size_t lcap;  // [L][lcap] k_setup's lit-pair lists
+    const uint32_t* n_in;                // [L] list lengths
+    uint8_t* occl; size_t ocap;          // [L][ocap], pre-zeroed; only 1s are stored
+    const float4* piv;                   // [L] light positions (float32)
+    const float* bounds;                 // max |C|, max r
+    unsigned long long* slow;            // diagnostics (b200rt_stats): [1] exact tests, [2] filter tests; may be null
+    unsigned long long* tl;              // diagnostic timeline slot; may be null
+};
+
+// One thread per shadow query; blockIdx.y = light.
+__global__ void __launch_bounds__(256, 6) k_shadow_grid(SceneDev sc, ShadowGridDev g, ShadowGridArgs a) {
+    if (a.tl && threadIdx.x == 0 && blockIdx.y == 0) atomicMin(a.tl, globaltimer_ns());
+    const int j = blockIdx.y;
+    const uint32_t n = a.n_in[j];
+    const uint32_t* list = a.lists + (size_t)j * a.lcap;
+    const float4 vv = __ldg(&a.piv[j]);
+    const V3 Vp = mk(vv.x, vv.y, vv.z);
+    const float cmax = a.bounds[0], rmax = a.bounds[1];
+    const float A = cmax + __fsqrt_rn(dot3(Vp, Vp));
+    const float4* ltab = g.ltab + (size_t)j * sc.S;
+    const uint16_t* cells = g.cells + (size_t)j * kSgCells * kSgRec;
+    unsigned long long n_filter = 0, n_exact = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t hr = list[i];
+        const float4 p = a.hP[hr];
+        // the ray and its filter threshold: the operations of k_isect3<shadow>'s prologue (common.py:84-91)
+        const V3 O = mk(p.x, p.y, p.z);
+        const V3 d = sub3(Vp, O);
+        const float nrm = __fsqrt_rn(dot3(d, d));
+        const V3 D = mk(__fdiv_rn(d.x, nrm), __fdiv_rn(d.y, nrm), __fdiv_rn(d.z, nrm));
+        const float B = cmax + __fsqrt_rn(dot3(O, O));
+        const float e = nrm * 9.5367432e-7f;
+        const float th = -(fmaf(3.8146973e-6f, fmaf(A, A, B * B), fmaf(4.f * e, rmax, 16.f * e * e)) + 1e-12f);
+        const float no = -dot3(Vp, D);
+        const uint16_t* rec = cells + (size_t)sg_cell(D.x, D.y, D.z) * kSgRec;
+        const uint32_t cnt = rec[0];
+        const bool full = cnt == 0xffffu || !(nrm <= kSgRange);            // overflowed cell, far origin or NaN: every sphere
+        const uint32_t ncand = full ? (uint32_t)sc.S : cnt;
+        bool occluded = false;
+        for (uint32_t c = 0; c < ncand && !occluded; c += 4) {
+            uint32_t id[4];
+            if (full) { id[0] = c; id[1] = min(c + 1, (uint32_t)sc.S - 1u); id[2] = min(c + 2, (uint32_t)sc.S - 1u); id[3] = min(c + 3, (uint32_t)sc.S - 1u); }
+            else { const uint2 w = *reinterpret_cast<const uint2*>(rec + 4 + c); id[0] = w.x & 0xffffu; id[1] = w.x >> 16; id[2] = w.y & 0xffffu; id[3] = w.y >> 16; }
+            float4 t4[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) t4[k] = __ldg(&ltab[id[k]]);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if (c + k >= ncand || occluded) continue;
+                const float b = fmaf(t4[k].x, D.x, fmaf(t4[k].y, D.y, fmaf(t4[k].z, D.z, no)));     // k_isect3 qray(), pivot form
+                const float q = fmaf(b, b, t4[k].w);
+                if (a.slow) ++n_filter;
+                if (q >= th) {
+                    const float4 sp = __ldg(&sc.sphB[id[k]]);
+                    const float t = sphere_exact(O, D, sp.x, sp.y, sp.z, sp.w);
+                    occluded = t > 0.f && t < kTMax;                                               // trace.py:26-29, :95
+                    if (a.slow) ++n_exact;
+                }
+            }
+        }
+        for (int pl = 0; pl < sc.Pl && !occluded; ++pl) {                                          // trace.py:32-39
+            const float t = plane_exact(O, D, __ldg(&sc.plO[pl]), __ldg(&sc.plN[pl]));
+            occluded = (t > 0.f && t < kTMax);
+        }
+        if (occluded) a.occl[(size_t)j * a.ocap + hr] = 1;
+    }
+    if (a.slow) {
+#pragma unroll
+        for (int dd = 16; dd > 0; dd >>= 1) { n_filter += __shfl_xor_sync(0xffffffffu, n_filter, dd); n_exact += __shfl_xor_sync(0xffffffffu, n_exact, dd); }
+        if (lane_id() == 0) { if (n_filter) atomicAdd(a.slow + 2, n_filter); if (n_exact) atomicAdd(a.slow + 1, n_exact); }
+    }
+    if (a.tl && threadIdx.x == 0 && blockIdx.y == 0) atomicMax(a.tl + 1, globaltimer_ns());
+}
+
+}  // namespace b200rt

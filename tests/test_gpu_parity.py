@@ -230,6 +230,9 @@ def test_culling_and_passes_do_not_change_the_image(oracle, S, L, W, H, depth, a
     assert st["rays"] == st_ns["rays"] and st["shadow_traced"] == st_ns["shadow_traced"]
     assert np.array_equal(got, _cuda(g, flags=_lib.F_NO_FILTER)), "filtered path differs from exact-test-on-everything"
     assert st["rays"] == st_nc["rays"]
+    nogrid, st_ng = _cuda(g, flags=_lib.F_NO_SGRID, stats=True)       # shadow queries by k_isect3 (passes + beam culling) instead of the light grids
+    assert np.array_equal(got, nogrid), "the lights' direction grids changed the image"
+    assert st_ng["rays"] == st["rays"] and st_ng["shadow_traced"] == st["shadow_traced"]
     dense, st_d = _cuda(g, flags=_lib.F_DENSE, stats=True)            # brute force: the mode bench.py's FP32-peak figure is measured in
     assert np.array_equal(got, dense), "dense (brute-force) mode differs from the production path"
     assert st_d["rays"] == st["rays"] and st_d["shadow_traced"] == st_d["shadow"]
@@ -242,3 +245,38 @@ def test_culling_and_passes_do_not_change_the_image(oracle, S, L, W, H, depth, a
     ref = oracle.render(None, *_args(g), grid=g["grid"], shape=(W, H), x_range=(x0, x0 + 64), y_range=(y0, y0 + 64))[:, x0:x0 + 64, y0:y0 + 64]
     rep = parity_report(got[:, x0:x0 + 64, y0:y0 + 64], ref)
     assert rep["n_bad"] <= _budget(rep["n"]), rep
+
+
+@pytest.mark.parametrize("case", ["light_inside_sphere", "light_touching_sphere", "cluster_in_one_cell", "far_light", "light_below_plane", "grazing"])
+def test_shadow_grid_adversarial_scenes(case):
+    """The per-light direction grids (csrc/shadow_grid.cuh) must never drop a sphere a shadow ray can hit: placements that
+    stress the cone bounds (light inside / on a sphere, hundreds of spheres behind one cell -> list overflow, light outside
+    the grid's coordinate range -> grid disabled, shadow rays leaving from far-away plane points, grazing directions)
+    rendered with the grids and brute force (B200RT_F_DENSE) must give the same bytes."""
+    from b200rt import _lib
+    S, L, W, H = 300, 3, 256, 144
+    g = _synthetic(S, L, 1, W, H, 2, False, seed=11)
+    sp, li = g["spheres"], g["lights"]
+    rng = np.random.default_rng(3)
+    if case == "light_inside_sphere":
+        sp[0:3, 0] = li[:, 0]; sp[3, 0] = 0.8                          # light 0 at the centre of sphere 0
+        sp[0:3, 1] = li[:, 1] + np.float32(0.2); sp[3, 1] = 1.0        # light 1 off-centre inside sphere 1
+    elif case == "light_touching_sphere":
+        sp[0:3, 0] = li[:, 0] + np.array([0.5, 0, 0], np.float32); sp[3, 0] = 0.5          # light exactly on the surface
+        sp[0:3, 1] = li[:, 1] + np.array([0, 0.5004, 0], np.float32); sp[3, 1] = 0.5       # just outside
+        sp[0:3, 2] = li[:, 2] + np.array([0, 0, -0.4996], np.float32); sp[3, 2] = 0.5      # just inside
+    elif case == "cluster_in_one_cell":
+        c = np.array([4.0, 0.5, 0.6], np.float32)                       # 250 small spheres in a 0.4-wide ball: one grid cell of every light
+        sp[0:3, :250] = c[:, None] + rng.uniform(-0.2, 0.2, (3, 250)).astype(np.float32); sp[3, :250] = rng.uniform(0.01, 0.03, 250)
+    elif case == "far_light":
+        li[:, 0] = [300.0, 40.0, 200.0]                                 # beyond the grid's coordinate range: every cell scans all spheres
+        li[:, 1] = [-2.0, 0.0, 260.0]                                   # |V - P| > 256 for every hit: per-ray fallback
+    elif case == "light_below_plane":
+        li[:, 0] = [3.0, 0.0, -2.0]; li[:, 1] = [3.0, 1.0, 0.05]        # light under / just above the ground plane
+    elif case == "grazing":
+        li[:, 0] = [-30.0, 0.0, 0.3]; li[:, 1] = [40.0, 25.0, 0.2]; li[:, 2] = [4.0, 0.0, 0.26]     # lights at sphere height: rays graze the whole field
+    got, st = _cuda(g, stats=True)
+    dense = _cuda(g, flags=_lib.F_DENSE)
+    assert np.array_equal(got, dense), case
+    assert np.array_equal(got, _cuda(g, flags=_lib.F_NO_SGRID)), case
+    assert st["shadow_traced"] > 0
