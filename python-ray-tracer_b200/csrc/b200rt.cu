@@ -1029,11 +1029,11 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     const bool sgrid = cull && !nofilter && S >= 64 && S <= 65535 && L > 0 && !(a->flags & B200RT_F_NO_SGRID) && !c.no_sgrid;
     ShadowGridDev sg{};
     if (sgrid) {
-        CK(c.sgCells.ensure(sizeof(uint16_t) * (size_t)L * kSgCells * kSgRec));
-        CK(c.sgTab.ensure(sizeof(float4) * (size_t)L * S)); CK(c.sgCone.ensure(sizeof(float4) * (size_t)L * S));
-        sg = ShadowGridDev{ c.sgCells.as<uint16_t>(), c.sgTab.as<float4>(), c.sgCone.as<float4>() };
+        CK(c.sgCells.ensure(sizeof(uint16_t) * (size_t)kSgTiers * L * kSgCells * kSgRec));
+        CK(c.sgTab.ensure(sizeof(float4) * (size_t)L * S)); CK(c.sgCone.ensure(sizeof(float4) * (size_t)kSgTiers * L * S));
+        sg = ShadowGridDev{ c.sgCells.as<uint16_t>(), c.sgTab.as<float4>(), c.sgCone.as<float4>(), c.pivPerm.as<int>(), Spad };
         k_sgrid_tab<<<(L * S + 255) / 256, 256, 0, st>>>(sc, sg); CKL();
-        k_sgrid_build<<<dim3(kSgCells / 256, L), 256, 0, st>>>(sc, sg); CKL();
+        k_sgrid_build<<<dim3(kSgCells / 256, L, kSgTiers), 256, 0, st>>>(sc, sg); CKL();
     } else if (shadow_res) CK(shadow_upload_resident(pv, Spad, L, st));
     IsectCfg icfg{ c.sm_count, c.force_nr, c.force_nr0, dense ? 0 : c.npre, {0, 0, 0, 0, 0, 0} };
     for (int k = 0; k < icfg.npre; ++k) icfg.pre[k] = c.pre[k];

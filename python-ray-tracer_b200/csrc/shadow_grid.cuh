@@ -10,9 +10,13 @@
 // the 4-FMA pivot filter with the same operands, operation order and per-ray threshold, then sphere_exact on the real
 // ray for the candidates, then the planes.  The grid only removes spheres that provably cannot be hit, so the image is
 // bit-identical to the brute-force path (tests/test_gpu_parity.py compares with B200RT_F_DENSE / B200RT_F_NO_FILTER):
-//   * radius inflated by 2e-3 + 1e-3 r: covers e (<= 2.5e-4), the exact test's rounding (<= 1e-4 in the perpendicular
-//     distance) for |V-P| <= kSgRange and coordinates <= kSgRange; rays from farther away, lights / scenes beyond that
-//     range and cells whose list overflows scan every sphere instead (still through the same filter);
+//   * radius inflated by 2e-3 + 1e-3 r: covers e (<= 2.5e-4) and the exact test's rounding (<= 1e-4 in the perpendicular
+//     distance) for |V-P| <= 256 and coordinates <= 256.  Shadow rays that start farther away (bounce rays reach the
+//     ground plane up to 999 units out) use a second grid built with 16x the inflation, valid to |V-P| <= 4096; rays
+//     from beyond that, lights / scenes outside the coordinate range and cells whose list overflows scan every sphere
+//     instead (still through the same filter);
+//   * a cell's list is in k_rank's order (decreasing solid angle seen from the light): likely occluders first, and a
+//     query stops at its first hit;
 //   * cell cones widened by 2e-3 rad: covers the rounding of the cell lookup and of the asin / acos used to build.
 #pragma once
 #include "isect3.cuh"
@@ -23,12 +27,16 @@ constexpr int kSgN = 32;                          // cells per edge of a cube-ma
 constexpr int kSgCells = 6 * kSgN * kSgN;         // cells per light
 constexpr int kSgRec = 128;                       // uint16 per cell record: [0] count (0xffff: scan every sphere), [4 ..] sphere ids
 constexpr int kSgCap = kSgRec - 4;
+constexpr int kSgTiers = 2;                       // tier t serves shadow rays with |V-P| <= kSgRange * 16^t
 constexpr float kSgRange = 256.f;
+__host__ __device__ __forceinline__ float sg_range(int t) { return t == 0 ? kSgRange : kSgRange * 16.f; }
+__host__ __device__ __forceinline__ double sg_inflate(int t) { return t == 0 ? 2e-3 : 3.2e-2; }
 
 struct ShadowGridDev {
-    uint16_t* cells;                              // [L][kSgCells][kSgRec]
-    float4* ltab;                                 // [L][S] (Cx, Cy, Cz, k = r^2 - |C - V_j|^2), k as in k_pivot (float64, rounded once)
-    float4* cone;                                 // [L][S] (unit direction V_j -> C, alpha); alpha >= pi: the sphere reaches every cell
+    uint16_t* cells;                              // [kSgTiers][L][kSgCells][kSgRec]
+    float4* ltab;                                 // [L][S] (Cx, Cy, Cz, k = r^2 - |C - V_j|^2), k as in k_pivot (float64, rounded once); by sphere id
+    float4* cone;                                 // [kSgTiers][L][S] (unit direction V_j -> C, alpha) by RANK (k_rank order); alpha >= pi: reaches every cell
+    const int* perm; int Spad;                    // [L][Spad] rank -> sphere id (k_rank)
 };
 
 // Cube-map cell of a direction (any length, not all zero): face = 2 * major axis + (negative ? 1 : 0), (u, v) = the other
@@ -49,26 +57,30 @@ __device__ __forceinline__ V3 sg_dir(int face, float a, float b) {       // un-n
     return (face >> 1) == 0 ? mk(s, a, b) : (face >> 1) == 1 ? mk(a, s, b) : mk(a, b, s);
 }
 
-// One thread per (light j, sphere s): filter operand k and the sphere's cone seen from the light.
+// One thread per (light j, rank pos): filter operand k of the sphere at that rank, and its cone seen from the light per tier.
 __global__ void __launch_bounds__(256) k_sgrid_tab(SceneDev sc, ShadowGridDev g) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= sc.L * sc.S) return;
-    const int j = idx / sc.S, s = idx - j * sc.S;
+    const int j = idx / sc.S, pos = idx - j * sc.S;
+    const int s = g.perm[(size_t)j * g.Spad + pos];
     const float4 v = sc.lights[j], sp = sc.sphB[s];
     const double ex = (double)sp.x - v.x, ey = (double)sp.y - v.y, ez = (double)sp.z - v.z;
     const double d2 = ex * ex + ey * ey + ez * ez;
-    g.ltab[idx] = make_float4(sp.x, sp.y, sp.z, (float)((double)sp.w - d2));
+    g.ltab[(size_t)j * sc.S + s] = make_float4(sp.x, sp.y, sp.z, (float)((double)sp.w - d2));
     const double dist = sqrt(d2), r = sqrt(fmax((double)sp.w, 0.0));
-    const double reff = r * 1.001 + 2e-3;
-    float4 c = make_float4(1.f, 0.f, 0.f, 4.f);                            // alpha = 4 > pi: every cell
-    if (dist > reff * 1.0001 && dist < 1e30) c = make_float4((float)(ex / dist), (float)(ey / dist), (float)(ez / dist), (float)asin(reff / dist));
-    g.cone[idx] = c;
+    for (int t = 0; t < kSgTiers; ++t) {
+        const double reff = r * 1.001 + sg_inflate(t);
+        float4 c = make_float4(1.f, 0.f, 0.f, 4.f);                        // alpha = 4 > pi: every cell
+        if (dist > reff * 1.0001 && dist < 1e30) c = make_float4((float)(ex / dist), (float)(ey / dist), (float)(ez / dist), (float)asin(reff / dist));
+        g.cone[((size_t)t * sc.L + j) * sc.S + pos] = c;
+    }
 }
 
-// One thread per (cell, light): the ascending list of the spheres whose cone (either sign) reaches the cell's cone.
+// One thread per (cell, light, tier): the list, in rank order, of the spheres whose cone (either sign) reaches the cell's cone.
 __global__ void __launch_bounds__(256) k_sgrid_build(SceneDev sc, ShadowGridDev g) {
     __shared__ float4 s_cone[256];
-    const int cell = blockIdx.x * 256 + threadIdx.x, j = blockIdx.y;       // kSgCells % 256 == 0
+    __shared__ int s_id[256];
+    const int cell = blockIdx.x * 256 + threadIdx.x, j = blockIdx.y, tier = blockIdx.z;     // kSgCells % 256 == 0
     const int face = cell / (kSgN * kSgN), iu = (cell / kSgN) % kSgN, iv = cell % kSgN;
     const float h = 2.f / (float)kSgN, a0 = -1.f + h * (float)iu, b0 = -1.f + h * (float)iv;
     const V3 cdir = normalize3(sg_dir(face, a0 + 0.5f * h, b0 + 0.5f * h));
@@ -81,17 +93,18 @@ __global__ void __launch_bounds__(256) k_sgrid_build(SceneDev sc, ShadowGridDev 
     beta += 2e-3f;
     const float4 v = sc.lights[j];
     const bool in_range = sc.cmax[0] + sqrtf(v.x * v.x + v.y * v.y + v.z * v.z) <= kSgRange;    // (NaN -> false)
-    uint16_t* rec = g.cells + ((size_t)j * kSgCells + cell) * kSgRec;
+    uint16_t* rec = g.cells + (((size_t)tier * sc.L + j) * kSgCells + cell) * kSgRec;
+    const float4* cone = g.cone + ((size_t)tier * sc.L + j) * sc.S;
     uint32_t cnt = 0;
     for (int s0 = 0; s0 < sc.S; s0 += 256) {
         __syncthreads();
-        if (s0 + (int)threadIdx.x < sc.S) s_cone[threadIdx.x] = g.cone[(size_t)j * sc.S + s0 + threadIdx.x];
+        if (s0 + (int)threadIdx.x < sc.S) { s_cone[threadIdx.x] = cone[s0 + threadIdx.x]; s_id[threadIdx.x] = g.perm[(size_t)j * g.Spad + s0 + threadIdx.x]; }
         __syncthreads();
         const int n = min(256, sc.S - s0);
         for (int k = 0; k < n; ++k) {
             const float4 c = s_cone[k];
             const float ang = acosf(fminf(1.f, fabsf(c.x * cdir.x + c.y * cdir.y + c.z * cdir.z)));
-            if (ang <= c.w + beta) { if (cnt < (uint32_t)kSgCap) rec[4 + cnt] = (uint16_t)(s0 + k); ++cnt; }
+            if (ang <= c.w + beta) { if (cnt < (uint32_t)kSgCap) rec[4 + cnt] = (uint16_t)s_id[k]; ++cnt; }
         }
     }
     const bool over = cnt > (uint32_t)kSgCap || !in_range;
@@ -122,7 +135,8 @@ __global__ void __launch_bounds__(256, 6) k_shadow_grid(SceneDev sc, ShadowGridD
     const float cmax = a.bounds[0], rmax = a.bounds[1];
     const float A = cmax + __fsqrt_rn(dot3(Vp, Vp));
     const float4* ltab = g.ltab + (size_t)j * sc.S;
-    const uint16_t* cells = g.cells + (size_t)j * kSgCells * kSgRec;
+    const uint16_t* cells0 = g.cells + (size_t)j * kSgCells * kSgRec;
+    const uint16_t* cells1 = g.cells + ((size_t)sc.L + j) * kSgCells * kSgRec;
     unsigned long long n_filter = 0, n_exact = 0;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const uint32_t hr = list[i];
@@ -136,9 +150,10 @@ __global__ void __launch_bounds__(256, 6) k_shadow_grid(SceneDev sc, ShadowGridD
         const float e = nrm * 9.5367432e-7f;
         const float th = -(fmaf(3.8146973e-6f, fmaf(A, A, B * B), fmaf(4.f * e, rmax, 16.f * e * e)) + 1e-12f);
         const float no = -dot3(Vp, D);
-        const uint16_t* rec = cells + (size_t)sg_cell(D.x, D.y, D.z) * kSgRec;
+        const bool near_ = nrm <= sg_range(0);
+        const uint16_t* rec = (near_ ? cells0 : cells1) + (size_t)sg_cell(D.x, D.y, D.z) * kSgRec;
         const uint32_t cnt = rec[0];
-        const bool full = cnt == 0xffffu || !(nrm <= kSgRange);            // overflowed cell, far origin or NaN: every sphere
+        const bool full = cnt == 0xffffu || !(nrm <= sg_range(kSgTiers - 1));      // overflowed cell, origin beyond the last tier or NaN: every sphere
         const uint32_t ncand = full ? (uint32_t)sc.S : cnt;
         bool occluded = false;
         for (uint32_t c = 0; c < ncand && !occluded; c += 4) {
