@@ -47,7 +47,7 @@ extern "C" {
 #define B200RT_F_NO_FILTER       0x2u  /* debug: run the exact sphere test on every sphere (must give bit-identical output) */
 #define B200RT_F_UNSWAP_GB       0x4u  /* write channels as R,G,B instead of the reference's R,B,G wiring (common.py:60-63) */
 #define B200RT_F_NO_CULL         0x8u  /* k_isect3 scans every sphere for every ray group (no beam culling); the image is the same */
-#define B200RT_F_TIME_ONLY       0x20u /* with `stats`: fill the ray counts and the per-class device times but run the production kernels (no executed-work counters: slow_path, exact_tests, tests_* stay 0) */
+#define B200RT_F_TIME_ONLY       0x20u /* with `stats`: fill the ray counts and the per-class device times but run the production kernels (no executed-work counters: slow_path, exact_tests, tests_*, and with the light grids shadow_traced, stay 0) */
 #define B200RT_F_DENSE           0x40u /* brute force as the reference specifies it: every query (shadow queries of unlit pairs included) scans every sphere - no beam culling, regrouping, shadow passes or lit-pair lists; the image is the same.  The FP32-peak figure of bench.py is measured in this mode */
 #define B200RT_F_NO_SGRID        0x80u /* shadow queries scan the light's sphere table (k_isect3, passes + beam culling) instead of looking up the light's direction grid; the image is the same */
 #define B200RT_F_NO_SORT         0x10u /* bounce-depth hits stay in pixel order (no regrouping by direction/position bin); the image is the same */

@@ -601,7 +601,7 @@ __global__ void __launch_bounds__(256, B200RT_SETUP_OCC) k_setup(SceneDev sc, Sh
         if (hit) {
             s.hP[h] = make_float4(Pb.x, Pb.y, Pb.z, o.w);
             s.hN[h] = make_float4(N.x, N.y, N.z, __int_as_float(id));
-            for (int j = 0; j < sc.L; ++j) s.occl[(size_t)j * s.ocap + h] = 0;
+            if (s.occl) for (int j = 0; j < sc.L; ++j) s.occl[(size_t)j * s.ocap + h] = 0;
             if (s.emit_reflection) {                 // the bounce ray does not depend on the shadow queries: queue it now,
                 const V3 D = mk(d.x, d.y, d.z);      // the next closest-hit launch runs beside this depth's shadow launches
                 const float dn = dot3(D, N);
@@ -1054,8 +1054,8 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     const int nsets = std::min(kSets, depth + 1);                // depth d: hit-record set d % nsets
     for (int b = 0; b < nsets; ++b) {
         CK(c.hP[b].ensure(sizeof(float4) * cap)); CK(c.hN[b].ensure(sizeof(float4) * cap));
-        CK(c.occl[b].ensure(std::max<size_t>(cap * (size_t)L, 1)));
-        if (use_lists) { CK(c.shidx[b].ensure(sizeof(uint32_t) * std::max<size_t>(cap * (size_t)L, 1))); CK(c.shidx2[b].ensure(sizeof(uint32_t) * std::max<size_t>(cap * (size_t)L, 1))); }
+        if (!sgrid) CK(c.occl[b].ensure(std::max<size_t>(cap * (size_t)L, 1)));
+        if (use_lists && !sgrid) { CK(c.shidx[b].ensure(sizeof(uint32_t) * std::max<size_t>(cap * (size_t)L, 1))); CK(c.shidx2[b].ensure(sizeof(uint32_t) * std::max<size_t>(cap * (size_t)L, 1))); }
     }
     CK(c.acc.ensure(sizeof(float) * 3 * cap));
     // regrouping of the hits of depth >= 1 (see k_key): worth it where beam culling is on and a query is expensive
@@ -1076,7 +1076,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     }
     // k_setup's ordered compaction: [pass][chunk of 256 rays][8 queues] status words + the chunk ticket, zeroed before every launch
     const size_t ostat_stride = ((cap + 255) / 256) * 8;
-    const int ostat_passes = use_lists ? 1 + std::max(0, (L - 7 + 7) / 8) : 1;
+    const int ostat_passes = (use_lists && !sgrid) ? 1 + std::max(0, (L - 7 + 7) / 8) : 1;
     const size_t ostat_bytes = sizeof(unsigned long long) * (ostat_stride * ostat_passes + 1);
     CK(c.ostat.ensure(ostat_bytes));
     // Per-light shadow lists pay off when a query is expensive (many spheres); for tiny scenes the dense [light][hit]
@@ -1110,7 +1110,8 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     }
     auto tl_mark = [&](const char* nm, int d, int from) { for (int i = from; i < tln; ++i) tlname.push_back(std::string(nm) + " d" + std::to_string(d) + (tln - from > 1 ? " j" + std::to_string(i - from) : "")); };
     // concurrency needs launches that do not touch shared constant memory
-    const bool conc = !stats && !nofilter && S >= 64 && closest_res && (L == 0 || shadow_res || sgrid) && !c.no_conc;
+    const bool conc = !stats && !nofilter && S >= 64 && closest_res && (L == 0 || shadow_res || sgrid) && !c.no_conc
+                      && (!sgrid || cap <= ((size_t)12 << 20));     // with the grids, big frames measured faster in one stream (C4: 14.8 vs 15.9 ms; 1/8 of it: 2.7 vs 2.5)
     cudaStream_t cs = conc ? c.chainStream : st, ss = conc ? c.shadeStream : st;
     const int nls = std::max(1, std::min(L, kSide));
     if (conc) { CK(cudaEventRecord(c.evFork, st)); CK(cudaStreamWaitEvent(cs, c.evFork, 0)); }
@@ -1159,15 +1160,15 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             uint32_t* wk = c.work.as<uint32_t>() + ((size_t)ch * (depth + 1) + d) * work_per_depth;      // k_isect3 group counters
             QueueDev q{};
             q.rayO = c.rayO[b].as<float4>(); q.rayD = c.rayD[b].as<float4>(); q.hP = c.hP[hs].as<float4>();
-            q.hit = c.hitKey[b].as<unsigned long long>(); q.occl = c.occl[hs].as<uint8_t>(); q.ocap = cap;
+            q.hit = c.hitKey[b].as<unsigned long long>(); q.occl = sgrid ? nullptr : c.occl[hs].as<uint8_t>(); q.ocap = cap;
             q.slow = (stats && !(a->flags & B200RT_F_TIME_ONLY)) ? c.slow.as<unsigned long long>() : nullptr;
             ShadeDev s{};
             s.rayO = q.rayO; s.rayD = q.rayD; s.hit = q.hit;
             s.rayO2 = c.rayO[b ^ 1].as<float4>(); s.rayD2 = c.rayD[b ^ 1].as<float4>(); s.hit2 = c.hitKey[b ^ 1].as<unsigned long long>();
-            s.hP = c.hP[hs].as<float4>(); s.hN = c.hN[hs].as<float4>(); s.occl = c.occl[hs].as<uint8_t>(); s.ocap = cap;
+            s.hP = c.hP[hs].as<float4>(); s.hN = c.hN[hs].as<float4>(); s.occl = sgrid ? nullptr : c.occl[hs].as<uint8_t>(); s.ocap = cap;
             s.accR = accR; s.accG = accG; s.accB = accB;
             s.n_live = n_live; s.n_hit = cd + 3;
-            s.shidx = use_lists ? c.shidx[hs].as<uint32_t>() : nullptr; s.shcap = cap; s.n_sh = cd + 4;
+            s.shidx = (use_lists && !sgrid) ? c.shidx[hs].as<uint32_t>() : nullptr; s.shcap = cap; s.n_sh = cd + 4;
             s.amb = (float)a->amb; s.lamb = (float)a->lamb; s.weight = wts[d]; s.emit_reflection = d < depth;
 
             tm.begin(0);
@@ -1197,13 +1198,13 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             if (L > 0) {
                 tm.begin(1);
                 if (nofilter) { q.n_in = cd + 3; q.work = cd + 2; if (int rc = launch_intersect<true>(c, sc, q, true, cs)) return rc; }
-                else if (sgrid) {                       // one launch for all lights of this depth
-                    ShadowGridArgs ga{ q.hP, s.shidx, cap, cd + 4, q.occl, cap, pv.piv, pv.bounds, q.slow, nullptr };
-                    cudaStream_t ls = conc ? c.lightStream[0] : cs;
-                    if (conc) CK(cudaStreamWaitEvent(ls, c.evSetup[hs], 0));
-                    if (tlb) { ga.tl = tlb + 2 * (size_t)tln++; tlname.push_back("shadow grid d" + std::to_string(d)); }
-                    k_shadow_grid<<<dim3(c.sm_count * 6, L), 256, 0, ls>>>(sc, sg, ga); CKL();
-                    if (conc) { CK(cudaEventRecord(c.evLight[0], ls)); CK(cudaStreamWaitEvent(ss, c.evLight[0], 0)); }
+                else if (sgrid) {                       // shadow queries + Lambert sum + accumulate in one kernel (shadow_grid.cuh)
+                    ShadowGridArgs ga{ s.hP, s.hN, s.n_hit, accR, accG, accB, s.amb, s.lamb, s.weight, pv.bounds,
+                                       q.slow ? cd + 4 : nullptr, q.slow, nullptr };        // (counters only in the diagnostic frame: B200RT_F_TIME_ONLY leaves shadow_traced 0)
+                    if (conc) CK(cudaStreamWaitEvent(ss, c.evSetup[hs], 0));
+                    if (tlb) { ga.tl = tlb + 2 * (size_t)tln++; tlname.push_back("shadow+shade d" + std::to_string(d)); }
+                    k_shadow_shade<<<small_grid, 256, 0, ss>>>(sc, sg, ga); CKL();
+                    if (conc) CK(cudaEventRecord(c.evShade[hs], ss));
                 }
                 else {
                     ShadowPlan sp{};
@@ -1220,11 +1221,13 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
                 }
                 tm.end(1);
             } else if (conc) CK(cudaStreamWaitEvent(ss, c.evSetup[hs], 0));
-            tm.begin(2);
-            if (tlb) { s.tl = tlb + 2 * (size_t)tln++; tlname.push_back("shade d" + std::to_string(d)); }
-            k_shade<<<small_grid, 256, 0, ss>>>(sc, s); CKL();
-            if (conc) CK(cudaEventRecord(c.evShade[hs], ss));
-            tm.end(2);
+            if (!(sgrid && L > 0 && !nofilter)) {
+                tm.begin(2);
+                if (tlb) { s.tl = tlb + 2 * (size_t)tln++; tlname.push_back("shade d" + std::to_string(d)); }
+                k_shade<<<small_grid, 256, 0, ss>>>(sc, s); CKL();
+                if (conc) CK(cudaEventRecord(c.evShade[hs], ss));
+                tm.end(2);
+            }
         }
         if (conc) CK(cudaStreamWaitEvent(cs, c.evShade[depth % nsets], 0));               // (ss is in order: every depth is shaded)
 
@@ -1256,7 +1259,8 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         for (int ch = 0; ch < nchunks; ++ch)
             for (int d = 0; d <= depth; ++d) {
                 const uint32_t* cd = h.data() + (size_t)ch * ctr_stride + cps * d;
-                if (use_lists) { for (int j = 0; j < L; ++j) out.shadow_traced += cd[4 + j]; } else out.shadow_traced += (uint64_t)cd[3] * (uint64_t)L;
+                if (use_lists) { for (int j = 0; j < L; ++j) out.shadow_traced += cd[4 + j]; }        // lists: their lengths; grids: counted by k_shadow_shade
+                else out.shadow_traced += (uint64_t)cd[3] * (uint64_t)L;
                 if (d == 0) out.primary += cd[0]; else out.bounce += (cd - cps)[3];       // queue of depth d = hit list of depth d-1
                 out.shadow += (uint64_t)cd[3] * (uint64_t)L;
             }

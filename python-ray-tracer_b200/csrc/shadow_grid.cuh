@@ -5,7 +5,8 @@
 // through the light position V.  Seen from V, a sphere (C, r) can only be met by such a line if the line's direction
 // is within alpha = asin(r / |C-V|) of +-(C-V) (the reference's shadow ray does not stop at the light, SURVEY F8, so
 // spheres behind the light count as well: hence both signs).  Once per frame k_sgrid_build lists, for each cell of a
-// cube map of directions around V, the spheres whose cone reaches the cell; a shadow query then looks at the ONE cell
+// cube map of directions around V, the spheres whose cone reaches the cell; a shadow query (k_shadow_shade, which also
+// does the Lambert sum the query's answer feeds) then looks at the ONE cell
 // its direction falls in and runs, over that cell's few spheres, exactly what k_isect3<shadow> runs over all of them:
 // the 4-FMA pivot filter with the same operands, operation order and per-ray threshold, then sphere_exact on the real
 // ray for the candidates, then the planes.  The grid only removes spheres that provably cannot be hit, so the image is
@@ -23,7 +24,10 @@
 
 namespace b200rt {
 
-constexpr int kSgN = 32;                          // cells per edge of a cube-map face
+#ifndef B200RT_SGN
+#define B200RT_SGN 32
+#endif
+constexpr int kSgN = B200RT_SGN;                          // cells per edge of a cube-map face
 constexpr int kSgCells = 6 * kSgN * kSgN;         // cells per light
 constexpr int kSgRec = 128;                       // uint16 per cell record: [0] count (0xffff: scan every sphere), [4 ..] sphere ids
 constexpr int kSgCap = kSgRec - 4;
@@ -113,82 +117,101 @@ __global__ void __launch_bounds__(256) k_sgrid_build(SceneDev sc, ShadowGridDev 
     rec[1] = (uint16_t)min(cnt, 0xffffu);                                   // diagnostic: the uncapped count
 }
 
+__device__ __forceinline__ void warp_count(uint32_t* ctr) {     // += 1 per calling lane, one atomic per warp
+    const uint32_t m = __activemask();
+    if ((int)lane_id() == __ffs(m) - 1) atomicAdd(ctr, (uint32_t)__popc(m));
+}
+
 struct ShadowGridArgs {
-    const float4* hP;                    // hit records (biased hit point, slot)
-    const uint32_t* lists; size_t lcap;  // [L][lcap] k_setup's lit-pair lists
-    const uint32_t* n_in;                // [L] list lengths
-    uint8_t* occl; size_t ocap;          // [L][ocap], pre-zeroed; only 1s are stored
-    const float4* piv;                   // [L] light positions (float32)
+    const float4* hP; const float4* hN;  // hit records: (biased hit point, slot) (normal, object id)
+    const uint32_t* n_hit;               // number of hit records
+    float* accR; float* accG; float* accB;   // per-slot colour accumulators
+    float amb, lamb, weight;             // weight = refl^depth (trace.py:131)
     const float* bounds;                 // max |C|, max r
-    unsigned long long* slow;            // diagnostics (b200rt_stats): [1] exact tests, [2] filter tests; may be null
+    uint32_t* n_traced;                  // [L] diagnostics (b200rt_stats.shadow_traced): queries run per light; may be null
+    unsigned long long* slow;            // diagnostics: [1] exact tests, [2] filter tests; may be null
     unsigned long long* tl;              // diagnostic timeline slot; may be null
 };
 
-// One thread per shadow query; blockIdx.y = light.
-__global__ void __launch_bounds__(256, 6) k_shadow_grid(SceneDev sc, ShadowGridDev g, ShadowGridArgs a) {
-    if (a.tl && threadIdx.x == 0 && blockIdx.y == 0) atomicMin(a.tl, globaltimer_ns());
-    const int j = blockIdx.y;
-    const uint32_t n = a.n_in[j];
-    const uint32_t* list = a.lists + (size_t)j * a.lcap;
-    const float4 vv = __ldg(&a.piv[j]);
-    const V3 Vp = mk(vv.x, vv.y, vv.z);
+// The lights loop of trace() for one hit record per thread (trace.py:77, 86-102, accumulated as in :131):
+//   RGB = amb * col;  for each light j:  Lv = normalize(light_j - P);  shadowed = query(P, Lv);  k = lamb * (Lv . N);
+//   if not shadowed and k > 0:  RGB += k * col;        acc[slot] += weight * RGB
+// The query is only run where its answer is used (k > 0), through light j's direction grid.  Lights in reference order
+// and one fmaf per channel per light: the sums are those of k_shade.  (k_setup then builds no per-light lists and no
+// occlusion flags exist: this kernel replaces k_isect3<shadow> + k_shade of the scan path.)
+__global__ void __launch_bounds__(256, 4) k_shadow_shade(SceneDev sc, ShadowGridDev g, ShadowGridArgs a) {
+    if (a.tl && threadIdx.x == 0) atomicMin(a.tl, globaltimer_ns());
+    const uint32_t n = *a.n_hit;
     const float cmax = a.bounds[0], rmax = a.bounds[1];
-    const float A = cmax + __fsqrt_rn(dot3(Vp, Vp));
-    const float4* ltab = g.ltab + (size_t)j * sc.S;
-    const uint16_t* cells0 = g.cells + (size_t)j * kSgCells * kSgRec;
-    const uint16_t* cells1 = g.cells + ((size_t)sc.L + j) * kSgCells * kSgRec;
     unsigned long long n_filter = 0, n_exact = 0;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const uint32_t hr = list[i];
-        const float4 p = a.hP[hr];
-        // the ray and its filter threshold: the operations of k_isect3<shadow>'s prologue (common.py:84-91)
-        const V3 O = mk(p.x, p.y, p.z);
-        const V3 d = sub3(Vp, O);
-        const float nrm = __fsqrt_rn(dot3(d, d));
-        const V3 D = mk(__fdiv_rn(d.x, nrm), __fdiv_rn(d.y, nrm), __fdiv_rn(d.z, nrm));
+    for (uint32_t h = blockIdx.x * blockDim.x + threadIdx.x; h < n; h += gridDim.x * blockDim.x) {
+        const float4 p = a.hP[h], nn = a.hN[h];
+        const uint32_t slot = __float_as_uint(p.w);
+        const float ar = a.accR[slot], ag = a.accG[slot], ab = a.accB[slot];
+        const V3 O = mk(p.x, p.y, p.z), N = mk(nn.x, nn.y, nn.z);
+        const int id = __float_as_int(nn.w);
+        const float4 col = (id < sc.S) ? __ldg(&sc.sphCol[id]) : __ldg(&sc.plCol[id - sc.S]);
+        float r = __fmul_rn(a.amb, col.x), gg = __fmul_rn(a.amb, col.y), b = __fmul_rn(a.amb, col.z);   // trace.py:77
         const float B = cmax + __fsqrt_rn(dot3(O, O));
-        const float e = nrm * 9.5367432e-7f;
-        const float th = -(fmaf(3.8146973e-6f, fmaf(A, A, B * B), fmaf(4.f * e, rmax, 16.f * e * e)) + 1e-12f);
-        const float no = -dot3(Vp, D);
-        const bool near_ = nrm <= sg_range(0);
-        const uint16_t* rec = (near_ ? cells0 : cells1) + (size_t)sg_cell(D.x, D.y, D.z) * kSgRec;
-        const uint32_t cnt = rec[0];
-        const bool full = cnt == 0xffffu || !(nrm <= sg_range(kSgTiers - 1));      // overflowed cell, origin beyond the last tier or NaN: every sphere
-        const uint32_t ncand = full ? (uint32_t)sc.S : cnt;
-        bool occluded = false;
-        for (uint32_t c = 0; c < ncand && !occluded; c += 4) {
-            uint32_t id[4];
-            if (full) { id[0] = c; id[1] = min(c + 1, (uint32_t)sc.S - 1u); id[2] = min(c + 2, (uint32_t)sc.S - 1u); id[3] = min(c + 3, (uint32_t)sc.S - 1u); }
-            else { const uint2 w = *reinterpret_cast<const uint2*>(rec + 4 + c); id[0] = w.x & 0xffffu; id[1] = w.x >> 16; id[2] = w.y & 0xffffu; id[3] = w.y >> 16; }
-            float4 t4[4];
+        for (int j = 0; j < sc.L; ++j) {                                                               // trace.py:86
+            const float4 vv = __ldg(&sc.lights[j]);
+            const V3 Vp = mk(vv.x, vv.y, vv.z);
+            // the ray and its filter threshold: the operations of k_isect3<shadow>'s prologue; D is also k_shade's Lv (common.py:84-91)
+            const V3 d = sub3(Vp, O);
+            const float nrm = __fsqrt_rn(dot3(d, d));
+            const V3 D = mk(__fdiv_rn(d.x, nrm), __fdiv_rn(d.y, nrm), __fdiv_rn(d.z, nrm));
+            const float k = __fmul_rn(a.lamb, dot3(D, N));                                             // :99
+            if (!(k > 0.f)) continue;                                                                  // :101 (the query's answer would not be used)
+            if (a.n_traced) warp_count(a.n_traced + j);
+            const float A = cmax + __fsqrt_rn(dot3(Vp, Vp));
+            const float e = nrm * 9.5367432e-7f;
+            const float th = -(fmaf(3.8146973e-6f, fmaf(A, A, B * B), fmaf(4.f * e, rmax, 16.f * e * e)) + 1e-12f);
+            const float no = -dot3(Vp, D);
+            const bool near_ = nrm <= sg_range(0);
+            const uint16_t* rec = g.cells + ((((size_t)(near_ ? 0 : 1) * sc.L + j) * kSgCells) + (size_t)sg_cell(D.x, D.y, D.z)) * kSgRec;
+            const float4* ltab = g.ltab + (size_t)j * sc.S;
+            const uint32_t cnt = rec[0];
+            const bool full = cnt == 0xffffu || !(nrm <= sg_range(kSgTiers - 1));      // overflowed cell, origin beyond the last tier or NaN: every sphere
+            const uint32_t ncand = full ? (uint32_t)sc.S : cnt;
+            bool occluded = false;
+            for (uint32_t c = 0; c < ncand && !occluded; c += 4) {
+                uint32_t cid[4];
+                if (full) { cid[0] = c; cid[1] = min(c + 1, (uint32_t)sc.S - 1u); cid[2] = min(c + 2, (uint32_t)sc.S - 1u); cid[3] = min(c + 3, (uint32_t)sc.S - 1u); }
+                else { const uint2 w = *reinterpret_cast<const uint2*>(rec + 4 + c); cid[0] = w.x & 0xffffu; cid[1] = w.x >> 16; cid[2] = w.y & 0xffffu; cid[3] = w.y >> 16; }
+                float4 t4[4];
 #pragma unroll
-            for (int k = 0; k < 4; ++k) t4[k] = __ldg(&ltab[id[k]]);
+                for (int q = 0; q < 4; ++q) t4[q] = __ldg(&ltab[cid[q]]);
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                if (c + k >= ncand || occluded) continue;
-                const float b = fmaf(t4[k].x, D.x, fmaf(t4[k].y, D.y, fmaf(t4[k].z, D.z, no)));     // k_isect3 qray(), pivot form
-                const float q = fmaf(b, b, t4[k].w);
-                if (a.slow) ++n_filter;
-                if (q >= th) {
-                    const float4 sp = __ldg(&sc.sphB[id[k]]);
-                    const float t = sphere_exact(O, D, sp.x, sp.y, sp.z, sp.w);
-                    occluded = t > 0.f && t < kTMax;                                               // trace.py:26-29, :95
-                    if (a.slow) ++n_exact;
+                for (int q = 0; q < 4; ++q) {
+                    if (c + q >= ncand || occluded) continue;
+                    const float bb = fmaf(t4[q].x, D.x, fmaf(t4[q].y, D.y, fmaf(t4[q].z, D.z, no)));   // k_isect3 qray(), pivot form
+                    const float qq = fmaf(bb, bb, t4[q].w);
+                    if (a.slow) ++n_filter;
+                    if (qq >= th) {
+                        const float4 sp = __ldg(&sc.sphB[cid[q]]);
+                        const float t = sphere_exact(O, D, sp.x, sp.y, sp.z, sp.w);
+                        occluded = t > 0.f && t < kTMax;                                               // trace.py:26-29, :95
+                        if (a.slow) ++n_exact;
+                    }
                 }
             }
+            for (int pl = 0; pl < sc.Pl && !occluded; ++pl) {                                          // trace.py:32-39
+                const float t = plane_exact(O, D, __ldg(&sc.plO[pl]), __ldg(&sc.plN[pl]));
+                occluded = (t > 0.f && t < kTMax);
+            }
+            if (occluded) continue;                                                                    // :95-96
+            r = fmaf(k, col.x, r); gg = fmaf(k, col.y, gg); b = fmaf(k, col.z, b);                     // :102
         }
-        for (int pl = 0; pl < sc.Pl && !occluded; ++pl) {                                          // trace.py:32-39
-            const float t = plane_exact(O, D, __ldg(&sc.plO[pl]), __ldg(&sc.plN[pl]));
-            occluded = (t > 0.f && t < kTMax);
-        }
-        if (occluded) a.occl[(size_t)j * a.ocap + hr] = 1;
+        a.accR[slot] = fmaf(a.weight, r, ar);                                                          // :131
+        a.accG[slot] = fmaf(a.weight, gg, ag);
+        a.accB[slot] = fmaf(a.weight, b, ab);
     }
     if (a.slow) {
 #pragma unroll
         for (int dd = 16; dd > 0; dd >>= 1) { n_filter += __shfl_xor_sync(0xffffffffu, n_filter, dd); n_exact += __shfl_xor_sync(0xffffffffu, n_exact, dd); }
         if (lane_id() == 0) { if (n_filter) atomicAdd(a.slow + 2, n_filter); if (n_exact) atomicAdd(a.slow + 1, n_exact); }
     }
-    if (a.tl && threadIdx.x == 0 && blockIdx.y == 0) atomicMax(a.tl + 1, globaltimer_ns());
+    if (a.tl && threadIdx.x == 0) atomicMax(a.tl + 1, globaltimer_ns());
 }
 
 }  // namespace b200rt
