@@ -220,7 +220,7 @@ def run_ours(args, w):
     # (c) the brute-force mode (B200RT_F_DENSE: every specified query scans every sphere, nothing culled): the figure the
     # FP32-peak target of north_star is about.  Counters from one diagnostic frame, times from production-kernel frames.
     dense = None
-    if rank == 0 and S >= 64:
+    if rank == 0 and S >= 64 and not args.no_dense:
         sd = frame(0, stats=True, flags=_lib.F_DENSE)
         frame(0, flags=_lib.F_DENSE)
         torch.cuda.synchronize()
@@ -282,10 +282,10 @@ def run_ours(args, w):
         nominal_tf = 2.0 * 128 * sms * sm_max * 1e6 / 1e12
         fpr = flops_per_ray(S, Pl)
         traffic, traffic_src = None, None          # ncu dram bytes of the k_isect3 launches of one frame (committed capture, 1 GPU, C4)
-        tp = os.path.join(ROOT, "profiles", "r01_v8_traffic.json")
+        tp = os.path.join(ROOT, "profiles", "r01_v9_traffic.json")
         if os.path.exists(tp) and args.workload == "c4" and world == 1:
             tj = json.load(open(tp))
-            traffic, traffic_src = tj["traffic_bytes_per_frame"], "profiles/r01_v8_traffic.json (ncu dram__bytes_read+write, the 28 k_isect3 launches of one frame)"
+            traffic, traffic_src = tj["traffic_bytes_per_frame"], "profiles/r01_v9_traffic.json (ncu dram__bytes_read+write, the 4 k_isect3 + 4 k_shadow_shade launches of one frame)"
         ach_tf = rays_this_rank * fpr / (isect_ms * 1e-3) / 1e12
         clocks = sampler.summary()
         line = {
@@ -297,7 +297,7 @@ def run_ours(args, w):
                     "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
             "gpu_launches": launches,                         # kernels launched inside the timed region (rank 0; b200rt_launch_count)
             "clocks": clocks, "host_enqueue_ms_per_step": host_enqueue_ms,
-            "roofline": {"bound": "fp32", "kernel": "k_isect3 (closest + shadow)", "achieved": ach_tf, "peak": nominal_tf,
+            "roofline": {"bound": "fp32", "kernel": "k_isect3 (closest-hit queries) + k_shadow_shade (shadow queries through the light grids, with the Lambert sum)", "achieved": ach_tf, "peak": nominal_tf,
                          "unit": "TFLOP/s", "frac": ach_tf / nominal_tf, "traffic": traffic, "traffic_source": traffic_src,
                          "algorithmic_bytes_per_frame": int(rays_this_rank * 40),
                          "peak_def": f"2 FLOP x 128 lanes x {sms} SMs x {sm_max:.0f} MHz (nominal max clock; MEASURED_PEAKS has no FP32 entry)",
@@ -340,6 +340,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c4")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-dense", action="store_true", help="skip the brute-force (B200RT_F_DENSE) measurement")
     args = ap.parse_args()
     from b200rt.workloads import workload
     w = workload(args.workload)

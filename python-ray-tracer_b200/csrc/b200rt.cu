@@ -100,6 +100,11 @@ __device__ __forceinline__ void slot_pixel(const FrameDev& f, uint32_t p, int& l
 // pixel_loc[c, x, y] with the GPU's unchecked C-order flat addressing: elements past the end
 // of the buffer are defined as 0.0.
 __device__ __forceinline__ double pl_at(const FrameDev& f, int c, int x, int y) {
+    if (!f.pixel_loc && x >= 0 && x < f.W && y >= 0 && y < f.H) {           // in-range element of the closed-form grid: no 64-bit divisions
+        if (c == 0) return f.gf;
+        if (c == 1) return __dadd_rn(__dmul_rn((double)x, f.gsy), f.gar);
+        return __dadd_rn(__dmul_rn((double)y, f.gsz), 1.0);
+    }
     const long long W = f.W, H = f.H;
     long long flat = (long long)c * W * H + (long long)x * H + y;
     if (flat < 0 || flat >= 3 * W * H) return 0.0;

@@ -24,6 +24,9 @@
 
 namespace b200rt {
 
+#ifndef B200RT_SS_OCC
+#define B200RT_SS_OCC 4                  // CTAs per SM the register allocation of k_shadow_shade aims at
+#endif
 #ifndef B200RT_SGN
 #define B200RT_SGN 32
 #endif
@@ -51,7 +54,7 @@ __device__ __forceinline__ int sg_cell(float x, float y, float z) {
     if (ax >= ay && ax >= az) { m = ax; u = y; v = z; face = x < 0.f ? 1 : 0; }
     else if (ay >= az)        { m = ay; u = x; v = z; face = y < 0.f ? 3 : 2; }
     else                      { m = az; u = x; v = y; face = z < 0.f ? 5 : 4; }
-    const float im = 0.5f * (float)kSgN / fmaxf(m, 1e-30f);
+    const float im = 0.5f * (float)kSgN * __frcp_rn(fmaxf(m, 1e-30f));
     const int iu = min(kSgN - 1, max(0, (int)(u * im + 0.5f * (float)kSgN)));
     const int iv = min(kSgN - 1, max(0, (int)(v * im + 0.5f * (float)kSgN)));
     return (face * kSgN + iu) * kSgN + iv;
@@ -139,7 +142,7 @@ struct ShadowGridArgs {
 // The query is only run where its answer is used (k > 0), through light j's direction grid.  Lights in reference order
 // and one fmaf per channel per light: the sums are those of k_shade.  (k_setup then builds no per-light lists and no
 // occlusion flags exist: this kernel replaces k_isect3<shadow> + k_shade of the scan path.)
-__global__ void __launch_bounds__(256, 4) k_shadow_shade(SceneDev sc, ShadowGridDev g, ShadowGridArgs a) {
+__global__ void __launch_bounds__(256, B200RT_SS_OCC) k_shadow_shade(SceneDev sc, ShadowGridDev g, ShadowGridArgs a) {
     if (a.tl && threadIdx.x == 0) atomicMin(a.tl, globaltimer_ns());
     const uint32_t n = *a.n_hit;
     const float cmax = a.bounds[0], rmax = a.bounds[1];

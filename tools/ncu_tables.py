@@ -50,14 +50,14 @@ for i, d in L.items():
     g = gb(*d["dram__bytes_read.sum"]) + gb(*d["dram__bytes_write.sum"])
     if d["k"].startswith("k_raygen"):
         seen_raygen += 1
-    if seen_raygen == 2 and "k_isect3" in d["k"]:          # second frame of the process = the TIME_ONLY frame: production kernels, launches serialised
+    if seen_raygen == 2 and ("k_isect3" in d["k"] or "k_shadow_shade" in d["k"]):          # second frame of the process = the TIME_ONLY frame: production kernels, launches serialised
         first_frame_isect.append((t, g))
     if seen_raygen == 2:
         print(f"| {i} | `{d['k']}` | {t:.3f} | {d['sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_elapsed'][0]:.1f} | "
               f"{d['smsp__issue_active.avg.pct_of_peak_sustained_active'][0]:.1f} | {g:.3f} | {d['smsp__inst_executed.sum'][0] / 1e6:.1f} |")
 if first_frame_isect:
     out = {"traffic_bytes_per_frame": sum(g for _, g in first_frame_isect) * 1e9, "launches": len(first_frame_isect),
-           "source": "ncu dram__bytes_read.sum + dram__bytes_write.sum over the k_isect3 launches of one production C4 frame (" + pre.split('/')[-1] + "_frame.csv)",
+           "source": "ncu dram__bytes_read.sum + dram__bytes_write.sum over the k_isect3 + k_shadow_shade launches (closest-hit and shadow queries) of one production C4 frame (" + pre.split('/')[-1] + "_frame.csv)",
            "kernel_ms_under_ncu": sum(t for t, _ in first_frame_isect)}
     json.dump(out, open(pre + "_traffic.json", "w"), indent=1)
     print("\n", json.dumps(out))
