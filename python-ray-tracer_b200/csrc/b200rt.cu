@@ -850,7 +850,7 @@ struct DevCtx {
     Buf acc, ctr, work, slow, tl, ostat;
     Buf sgCells, sgTab, sgCone;                                      // per-light direction grids of the shadow queries (shadow_grid.cuh)
     Buf sortKey, sortPerm, sortHist, sortBase, sortPart, sortGrid;   // regrouping of bounce-depth hits (k_key .. k_perm)
-    bool no_sgrid = false; bool no_sort = false; int sort_posbits = -1, sort_dirn = -1;     // env B200RT_NO_SORT, B200RT_SORT_POSBITS, B200RT_SORT_DIRN (-1: chosen from the queue size)
+    bool no_sgrid = false; int sgrid_min_s = 1; bool no_sort = false; int sort_posbits = -1, sort_dirn = -1;     // env B200RT_NO_SORT, B200RT_SORT_POSBITS, B200RT_SORT_DIRN (-1: chosen from the queue size)
     int npre = 1, pre[6] = {256, 0, 0, 0, 0, 0};                    // leading shadow passes (env B200RT_PASSES=a,b,...; multiples of 8)
     bool timeline = false;                                        // env B200RT_TIMELINE: per-launch first-start / last-end (globaltimer) to stderr
     // internal streams (see the launch sequence in render_device): the dependent chain at high priority, one stream per
@@ -945,6 +945,7 @@ int init_ctx(DevCtx& c, int device) {
     { const char* e = getenv("B200RT_TIMELINE"); c.timeline = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_NO_SORT"); c.no_sort = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_NO_SGRID"); c.no_sgrid = e && atoi(e) != 0; }
+    { const char* e = getenv("B200RT_SGRID_MIN_S"); if (e) c.sgrid_min_s = std::max(1, atoi(e)); }
     { const char* e = getenv("B200RT_SORT_POSBITS"); if (e) c.sort_posbits = std::min(18, std::max(0, atoi(e))); }
     { const char* e = getenv("B200RT_SORT_DIRN"); if (e) c.sort_dirn = std::min(16, std::max(1, atoi(e))); }
     if (const char* e = getenv("B200RT_PASSES")) {
@@ -1030,8 +1031,9 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     const bool closest_res = !nofilter && 2 * Spad <= kTabCap, shadow_res = !nofilter && L > 0 && L * Spad <= kTabCap;
     if (closest_res) { const int tabs[2] = { L, L + 1 }; CK(isect3_upload_resident(pv, Spad, tabs, 2, st)); }
     // Shadow queries through the per-light direction grids (shadow_grid.cuh) wherever work may be skipped at all
-    // (beam culling on) and a query is expensive; k_isect3<shadow> stays for the brute-force / debug modes and tiny scenes.
-    const bool sgrid = cull && !nofilter && S >= 64 && S <= 65535 && L > 0 && !(a->flags & B200RT_F_NO_SGRID) && !c.no_sgrid;
+    // (beam culling on); k_isect3<shadow> + k_shade stay for the brute-force / debug modes.  (Also for the 6-sphere default
+    // scene: C3 3.95 -> 2.58 ms, C5 1.78 -> 1.40 ms per frame against the dense [light][hit] scan.)
+    const bool sgrid = cull && !nofilter && S >= c.sgrid_min_s && S <= 65535 && L > 0 && !(a->flags & B200RT_F_NO_SGRID) && !c.no_sgrid;
     ShadowGridDev sg{};
     if (sgrid) {
         CK(c.sgCells.ensure(sizeof(uint16_t) * (size_t)kSgTiers * L * kSgCells * kSgRec));

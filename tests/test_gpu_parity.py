@@ -75,6 +75,19 @@ def test_filter_is_exact(name):
     assert np.array_equal(_cuda(g), _cuda(g, flags=_lib.F_NO_FILTER))
 
 
+@pytest.mark.parametrize("name", ["c1_aa1", "rand_a", "rand_c", "c4_small", "edge_l0", "edge_p0", "edge_d0"])
+def test_scan_path_equals_grid_path(name):
+    """Shadow queries by k_isect3<shadow> + k_shade (B200RT_F_NO_SGRID, the path of rounds before the light grids) and
+    brute force (B200RT_F_DENSE) write the same bytes as the default path on the reference's golden scenes."""
+    from b200rt import _lib
+    if not have_golden(name):
+        pytest.skip("golden missing")
+    g = load_golden(name)
+    got = _cuda(g)
+    assert np.array_equal(got, _cuda(g, flags=_lib.F_NO_SGRID))
+    assert np.array_equal(got, _cuda(g, flags=_lib.F_DENSE))
+
+
 def test_deterministic_and_tiled_equals_whole():
     g = load_golden("c4_small")
     a, b = _cuda(g), _cuda(g)

@@ -1,10 +1,10 @@
 cd $GRAFT_REPO_ROOT
 mkdir -p gpurun_out
 NG=${1:-8}
-timeout 300 python bench.py --steps 10 --warmup 3 --no-cpu > gpurun_out/scale_n1.json 2> gpurun_out/scale_n1.err
+timeout 300 python bench.py --steps 10 --warmup 3 --no-cpu --no-dense > gpurun_out/scale_n1.json 2> gpurun_out/scale_n1.err
 for n in 2 4 8; do
   if [ $n -le $NG ]; then
-    timeout 400 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 2950$n bench.py --gpus $n --steps 10 --warmup 3 --no-cpu > gpurun_out/scale_n$n.json 2> gpurun_out/scale_n$n.err
+    timeout 400 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 2950$n bench.py --gpus $n --steps 10 --warmup 3 --no-cpu --no-dense > gpurun_out/scale_n$n.json 2> gpurun_out/scale_n$n.err
   fi
 done
 python - <<'PY'
