@@ -152,6 +152,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
     constexpr int GW = 32 * NR;                               // rays per warp group
     constexpr int NO = PIV ? 1 : NR;                          // 2*O operands exist only in the 8-FFMA2 form
     constexpr int KPM = (MODE == 0) ? B200RT_KP0 : KP;        // sphere pairs per scan step of this mode
+    constexpr uint32_t kQFl = (NR == 8) ? (uint32_t)kQFlush : 512u - 64u * NR;   // flush threshold of the candidate queue (see slist)
     extern __shared__ __align__(16) unsigned char s_raw[];
     IsectSmem<NR>& sm = *reinterpret_cast<IsectSmem<NR>*>(s_raw);
     if (DIAG && q.tl && threadIdx.x == 0) atomicMin(q.tl, globaltimer_ns());
@@ -337,7 +338,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
                 cand &= cand - 1;
                 sq[pos++] = ((uint32_t)(bit >> 1) * 32u + lane) | ((uint32_t)(2 * pair + (bit & 1)) << 8);
             }
-            if (qcnt > (uint32_t)kQFlush) flush();
+            if (qcnt > kQFl) flush();
         };
         auto slow_step = [&](int pb, const float (&mk4)[KPM]) {        // pairs pb .. pb+KP-1, per-pair maxima mk4
             if (DIAG) slow_cnt++;
@@ -360,8 +361,12 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
         // computed index instead of uniform registers); wide beams and poor cull rates take the dense scan. ----
         if (DIAG && q.slow && lane == 0) atomicAdd(q.slow + 4 + 6 * MODE, 1ull);                      // dbg: groups
         int ns = -1, nsr = 0;                                 // ns >= 0: sparse scan over slist[0..ns), the first nsr entries real
-        uint16_t* slist = reinterpret_cast<uint16_t*>(MODE == 2 ? (void*)ws.ki : MODE == 0 ? (void*)ws.thr : (void*)ws.o);   // 1 KB free in every mode
-        if (pv.rad && npair <= 32 * NR * 2 && npair >= 64) {
+        // The pair list needs 2 B x npair (<= 1 KB).  NR = 8: an array that is free in the mode (1 KB each).  Fewer rays per
+        // thread: those arrays are smaller, so the list takes the top third of the candidate queue, whose remaining
+        // 512 entries still hold one slow_pair's worst case (32 lanes x 2 NR) beyond the flush threshold.
+        uint16_t* slist = (NR == 8) ? reinterpret_cast<uint16_t*>(MODE == 2 ? (void*)ws.ki : MODE == 0 ? (void*)ws.thr : (void*)ws.o)
+                                    : reinterpret_cast<uint16_t*>(ws.q + 512);
+        if (pv.rad && npair <= 512 && npair >= 64) {
             float ax = 0.f, ay = 0.f, az = 0.f, bx = 0.f, by = 0.f, bz = 0.f, na = 0.f;
 #pragma unroll
             for (int r = 0; r < NR; ++r) {
@@ -686,7 +691,10 @@ template <int MODE>
 static cudaError_t isect3_launch_one(const IsectCfg& cfg, const SceneDev& sc, const QueueDev& q, const PivotDev& pv, size_t max_rays,
                                      int c0, int cnt, int j, int tb, cudaStream_t st) {
     const size_t warps = (size_t)cfg.sm_count * 2 * (kThreads / 32);
-    int nr = cfg.force_nr ? cfg.force_nr : (max_rays >= warps * 256 * 4 ? 8 : (max_rays >= warps * 128 * 4 ? 4 : 2));
+    // 4 rays per thread (groups of 128 rays, 3 CTAs = 24 warps per SM) measured best at every size once the 4-ray build
+    // could cull 512 pairs (C4: 13.06 -> 12.78 ms; 1/8 of it 2.29 -> 2.17: shorter groups, shorter tails); 8 rays per
+    // thread (B200RT_NR=8) amortise the uniform loads better but run 16 warps per SM.
+    int nr = cfg.force_nr ? cfg.force_nr : (max_rays >= warps * 128 * 4 ? 4 : 2);
     if (MODE == 0 && cfg.force_nr0) nr = cfg.force_nr0;         // (measured: 8 rays/thread wins for the 8-FFMA2 form too)
     const int grid = cfg.sm_count * (nr == 8 ? 2 : 3);
     const bool diag = q.slow != nullptr || q.tl != nullptr;
