@@ -167,7 +167,7 @@ __global__ void k_raygen(FrameDev f, float4* __restrict__ rayO, float4* __restri
         uint32_t pos = slot;
         if (f.ns > 1) { uint32_t pp[8]; ordered_append8(valid ? 1u : 0u, 1, c, ostat, n_live, c == nchunks - 1, pp); pos = pp[0]; }
         else if (slot == 0) *n_live = nslots;
-        if (valid) { rayO[pos] = o; rayD[pos] = d; hit[pos] = kNoHitKey; }
+        if (valid) { rayO[pos] = o; rayD[pos] = d; if (hit) hit[pos] = kNoHitKey; }
     }
 }
 
@@ -614,7 +614,7 @@ __global__ void __launch_bounds__(256, B200RT_SETUP_OCC) k_setup(SceneDev sc, Sh
                 const V3 O2 = madd3(Pb, kBias, R);                                             // trace.py:110
                 s.rayO2[h] = make_float4(O2.x, O2.y, O2.z, o.w);                               // the hit list IS the next queue
                 s.rayD2[h] = make_float4(R.x, R.y, R.z, 0.f);
-                s.hit2[h] = kNoHit;
+                if (s.hit2) s.hit2[h] = kNoHit;     // (null: the next closest-hit query is a single k_isect3 launch that stores its keys)
             }
         }
     }
@@ -1093,6 +1093,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     CK(c.ctr.ensure(sizeof(uint32_t) * (size_t)ctr_stride * nchunks)); CK(c.slow.ensure(24 * sizeof(unsigned long long)));
     CK(cudaMemsetAsync(c.ctr.p, 0, sizeof(uint32_t) * (size_t)ctr_stride * nchunks, st));
     const int nsch = (Spad + kTabCap - 1) / kTabCap;             // sphere chunks of the constant-memory table
+    const bool store_keys = !nofilter && nsch == 1;              // one k_isect3 launch per closest-hit query: it stores the keys, nobody pre-sets them
     int sh_ranges[kMaxPass][2]; const int sh_np = (L > 0 && !nofilter) ? shadow_passes(icfg, Spad, sh_ranges) : 1;
     if (sh_np < 0) return fail(B200RT_E_SHAPE, "too many spheres for the shadow pass table");
     const size_t nreg = (cap + kRegion - 1) / kRegion;            // regions of the survivor lists
@@ -1146,7 +1147,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         CK(cudaMemsetAsync(accG, 0, sizeof(float) * nslots, cs));
         CK(cudaMemsetAsync(accB, 0, sizeof(float) * nslots, cs));
         if (ns > 1) CK(cudaMemsetAsync(c.ostat.p, 0, ostat_bytes, cs));
-        k_raygen<<<(int)std::min<size_t>((nslots + 255) / 256, (size_t)small_grid), 256, 0, cs>>>(f, c.rayO[0].as<float4>(), c.rayD[0].as<float4>(), c.hitKey[0].as<unsigned long long>(), ctr + 0,
+        k_raygen<<<(int)std::min<size_t>((nslots + 255) / 256, (size_t)small_grid), 256, 0, cs>>>(f, c.rayO[0].as<float4>(), c.rayD[0].as<float4>(), store_keys ? nullptr : c.hitKey[0].as<unsigned long long>(), ctr + 0,
                                                                                                          c.ostat.as<unsigned long long>(), reinterpret_cast<uint32_t*>(c.ostat.as<unsigned long long>() + ostat_stride * ostat_passes));
         CKL();
         tm.end(2);
@@ -1171,7 +1172,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             q.slow = (stats && !(a->flags & B200RT_F_TIME_ONLY)) ? c.slow.as<unsigned long long>() : nullptr;
             ShadeDev s{};
             s.rayO = q.rayO; s.rayD = q.rayD; s.hit = q.hit;
-            s.rayO2 = c.rayO[b ^ 1].as<float4>(); s.rayD2 = c.rayD[b ^ 1].as<float4>(); s.hit2 = c.hitKey[b ^ 1].as<unsigned long long>();
+            s.rayO2 = c.rayO[b ^ 1].as<float4>(); s.rayD2 = c.rayD[b ^ 1].as<float4>(); s.hit2 = store_keys ? nullptr : c.hitKey[b ^ 1].as<unsigned long long>();
             s.hP = c.hP[hs].as<float4>(); s.hN = c.hN[hs].as<float4>(); s.occl = sgrid ? nullptr : c.occl[hs].as<uint8_t>(); s.ocap = cap;
             s.accR = accR; s.accG = accG; s.accB = accB;
             s.n_live = n_live; s.n_hit = cd + 3;

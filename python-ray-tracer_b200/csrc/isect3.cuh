@@ -54,6 +54,7 @@ struct QueueDev {
     // count, zeroed before the frame).  A later pass (in_rn != null) walks the regions' filled parts.  Null on the last pass.
     uint32_t* out_list; uint32_t* out_rn; const uint32_t* in_rn;
     int last;                            // this launch covers the end of the sphere array: planes are tested here (set by the launcher)
+    int only;                            // closest hit: this launch covers ALL spheres, so it stores the key (no pre-set "no hit", no atomic merge)
     unsigned long long* slow;            // diagnostic: thread-level slow-path entries (may be null)
     unsigned long long* tl;              // diagnostic (B200RT_TIMELINE): [0] first CTA start, [1] last CTA end, globaltimer ns (may be null)
 };
@@ -119,7 +120,8 @@ constexpr int KP = B200RT_KP;            // sphere pairs per scan step, pivot mo
 #define B200RT_KP0 2                     // ... of the 8-FFMA2 form (MODE 0): its step is twice as long, and the unrolled step should fit the L0 instruction cache
 #endif
 #ifndef B200RT_CULL_E
-#define B200RT_CULL_E 2                  // beam culling: sphere pairs per lane per round (code size vs loads in flight; the next round is prefetched)
+#define B200RT_CULL_E 0                  // beam culling: sphere pairs per lane per round (code size / registers vs loads in flight; the next round is
+                                         // prefetched).  0: 2 with 8 rays per thread, 1 with fewer (85 registers: C4 12.78 -> 12.69 ms; 3 and 4 spill)
 #endif
 #ifndef B200RT_ONE_SLOW_SITE
 #define B200RT_ONE_SLOW_SITE 0           // 1: one copy of slow_pair / the exact-test loop behind both scans (smaller code, measured 0.6 ms/frame slower on C4)
@@ -421,7 +423,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
                     };
                     uint32_t nsv = 0;
                     // CE pairs per lane per round; the loads of round r+1 are issued before round r is evaluated
-                    constexpr int CE = B200RT_CULL_E;
+                    constexpr int CE = B200RT_CULL_E ? B200RT_CULL_E : (NR == 8 ? 2 : 1);
                     float4 uu[CE], ww[CE]; float2 rr[CE];
                     auto load_round = [&](int p0) {
 #pragma unroll
@@ -623,7 +625,9 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
                         if (t > 0.f && t < best) { best = t; bid = sc.S + pl; }
                     }
                 }
-                if (bid >= 0) atomicMin(&q.hit[i], ((unsigned long long)__float_as_uint(best) << 32) | (uint32_t)bid);
+                const unsigned long long key = ((unsigned long long)__float_as_uint(best) << 32) | (uint32_t)bid;     // nothing hit: (999.0f, -1) = kNoHit
+                if (q.only) q.hit[i] = key;
+                else if (bid >= 0) atomicMin(&q.hit[i], key);
             }
         }
         if (ANY && q.out_list) {                              // survivors -> next pass's list: appended to their region, in group order
@@ -725,7 +729,7 @@ static cudaError_t isect3_launch_closest(const IsectCfg& cfg, const SceneDev& sc
         const int cnt = std::min(chunk, sc.Spad - c0);
         if (!resident && (e = cudaMemcpyToSymbolAsync(c_tab, pv.tab + (size_t)tj * sc.Spad + c0, sizeof(float4) * cnt, 0,
                                                       cudaMemcpyDeviceToDevice, st)) != cudaSuccess) return e;
-        q.work = work + k; q.last = (c0 + cnt >= sc.Spad) ? 1 : 0;
+        q.work = work + k; q.last = (c0 + cnt >= sc.Spad) ? 1 : 0; q.only = (c0 == 0 && cnt >= sc.Spad) ? 1 : 0;
         if (tlbase) q.tl = tlbase + 2 * (size_t)((*tlnext)++);
         if ((e = isect3_launch_one<MODE>(cfg, sc, q, pv, max_rays, c0, cnt, L, resident ? (MODE == 1 ? 0 : sc.Spad) : 0, st)) != cudaSuccess) return e;
     }
