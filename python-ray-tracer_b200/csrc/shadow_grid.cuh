@@ -146,6 +146,9 @@ __global__ void __launch_bounds__(256, B200RT_SS_OCC) k_shadow_shade(SceneDev sc
     if (a.tl && threadIdx.x == 0) atomicMin(a.tl, globaltimer_ns());
     const uint32_t n = *a.n_hit;
     const float cmax = a.bounds[0], rmax = a.bounds[1];
+    __shared__ float s_A[64];                                  // per light: cmax + |V_j| (the filter threshold's A), first 64 lights
+    if ((int)threadIdx.x < min(sc.L, 64)) { const float4 vv = __ldg(&sc.lights[threadIdx.x]); s_A[threadIdx.x] = cmax + __fsqrt_rn(dot3(mk(vv.x, vv.y, vv.z), mk(vv.x, vv.y, vv.z))); }
+    __syncthreads();
     unsigned long long n_filter = 0, n_exact = 0;
     for (uint32_t h = blockIdx.x * blockDim.x + threadIdx.x; h < n; h += gridDim.x * blockDim.x) {
         const float4 p = a.hP[h], nn = a.hN[h];
@@ -166,7 +169,7 @@ __global__ void __launch_bounds__(256, B200RT_SS_OCC) k_shadow_shade(SceneDev sc
             const float k = __fmul_rn(a.lamb, dot3(D, N));                                             // :99
             if (!(k > 0.f)) continue;                                                                  // :101 (the query's answer would not be used)
             if (a.n_traced) warp_count(a.n_traced + j);
-            const float A = cmax + __fsqrt_rn(dot3(Vp, Vp));
+            const float A = j < 64 ? s_A[j] : cmax + __fsqrt_rn(dot3(Vp, Vp));
             const float e = nrm * 9.5367432e-7f;
             const float th = -(fmaf(3.8146973e-6f, fmaf(A, A, B * B), fmaf(4.f * e, rmax, 16.f * e * e)) + 1e-12f);
             const float no = -dot3(Vp, D);
@@ -199,7 +202,13 @@ __global__ void __launch_bounds__(256, B200RT_SS_OCC) k_shadow_shade(SceneDev sc
                 }
             }
             for (int pl = 0; pl < sc.Pl && !occluded; ++pl) {                                          // trace.py:32-39
-                const float t = plane_exact(O, D, __ldg(&sc.plO[pl]), __ldg(&sc.plN[pl]));
+                const float4 po = __ldg(&sc.plO[pl]), pn = __ldg(&sc.plN[pl]);
+                // t = num / den > 0 needs num and den of the same sign: where they differ (or num is 0) the quotient is <= 0
+                // and plane_exact's division is skipped — the usual case for a point on the plane looking up at a light
+                const float den = dot3(D, mk(pn.x, pn.y, pn.z));
+                const float num = dot3(mk(__fsub_rn(po.x, O.x), __fsub_rn(po.y, O.y), __fsub_rn(po.z, O.z)), mk(pn.x, pn.y, pn.z));
+                if ((num > 0.f) != (den > 0.f) || num == 0.f) continue;
+                const float t = plane_exact(O, D, po, pn);
                 occluded = (t > 0.f && t < kTMax);
             }
             if (occluded) continue;                                                                    // :95-96
