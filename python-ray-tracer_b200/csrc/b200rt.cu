@@ -344,6 +344,56 @@ __global__ void __launch_bounds__(256) k_rank(SceneDev sc, int* perm) {
     if (s < sc.Spad) perm[(size_t)j * sc.Spad + rank] = s;
 }
 
+// Order of the two closest-hit tables (row L of perm): spheres along a Morton curve through their centres, padding last.
+// Any order gives the same image (the closest hit is the minimum over (t, sphere id), and ids are mapped back through
+// perm); a spatial order makes 64 consecutive table positions a compact cluster, which k_isect3's beam culling tests as
+// a whole before it looks at the cluster's pairs (k_clus, isect3.cuh).
+__device__ __forceinline__ uint32_t morton10(uint32_t v) {          // spread the low 10 bits: ..9876543210 -> 9..8..7.. (every third bit)
+    v &= 1023u; v = (v | (v << 16)) & 0x030000ffu; v = (v | (v << 8)) & 0x0300f00fu; v = (v | (v << 4)) & 0x030c30c3u; v = (v | (v << 2)) & 0x09249249u;
+    return v;
+}
+__global__ void __launch_bounds__(256) k_mrank(SceneDev sc, int* perm) {
+    __shared__ uint32_t skey[1024];
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    const float cm = fmaxf(sc.cmax[0], 1e-20f);
+    auto key = [&](int t) -> uint32_t {
+        if (t >= sc.S) return 0xffffffffu;
+        const float4 sp = sc.sphB[t];
+        const uint32_t qx = (uint32_t)min(1023, max(0, (int)((sp.x / cm * 0.5f + 0.5f) * 1023.f)));
+        const uint32_t qy = (uint32_t)min(1023, max(0, (int)((sp.y / cm * 0.5f + 0.5f) * 1023.f)));
+        const uint32_t qz = (uint32_t)min(1023, max(0, (int)((sp.z / cm * 0.5f + 0.5f) * 1023.f)));
+        return morton10(qx) | (morton10(qy) << 1) | (morton10(qz) << 2);
+    };
+    const uint32_t ks = key(s);
+    int rank = 0;
+    for (int t0 = 0; t0 < sc.Spad; t0 += 1024) {
+        __syncthreads();
+        for (int t = threadIdx.x; t < 1024; t += blockDim.x) skey[t] = key(t0 + t);
+        __syncthreads();
+        const int n = min(1024, sc.Spad - t0);
+        for (int t = 0; t < n; ++t) { const uint32_t kt = skey[t]; rank += (kt < ks || (kt == ks && t0 + t < s)) ? 1 : 0; }
+    }
+    if (s < sc.Spad) perm[(size_t)sc.L * sc.Spad + rank] = s;
+}
+// One thread per cluster of 64 consecutive positions of the closest-hit tables: bounding sphere (centre = mean of the
+// centres, radius = max |C - centre| + r, rounded up); a cluster of padding only gets radius -1 (never kept).
+__global__ void __launch_bounds__(64) k_clus(SceneDev sc, const int* perm, float4* clus) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c * 64 >= sc.Spad) return;
+    const int* pr = perm + (size_t)sc.L * sc.Spad;
+    float mx = 0.f, my = 0.f, mz = 0.f; int n = 0;
+    for (int k = 0; k < 64 && c * 64 + k < sc.Spad; ++k) { const int s = pr[c * 64 + k]; if (s < sc.S) { const float4 sp = sc.sphB[s]; mx += sp.x; my += sp.y; mz += sp.z; ++n; } }
+    if (n == 0) { clus[c] = make_float4(0.f, 0.f, 0.f, -1.f); return; }
+    mx /= (float)n; my /= (float)n; mz /= (float)n;
+    float rad = 0.f;
+    for (int k = 0; k < 64 && c * 64 + k < sc.Spad; ++k) {
+        const int s = pr[c * 64 + k];
+        if (s < sc.S) { const float4 sp = sc.sphB[s]; const float ex = sp.x - mx, ey = sp.y - my, ez = sp.z - mz;
+                        rad = fmaxf(rad, __fsqrt_ru(ex * ex + ey * ey + ez * ez) * 1.00001f + __fsqrt_ru(fmaxf(sp.w, 0.f))); }
+    }
+    clus[c] = make_float4(mx, my, mz, rad * 1.00001f + 1e-6f);
+}
+
 // One thread per (table j, pair i of table positions): k = r^2 - |C-V_j|^2 (j <= L) or r^2 - |C|^2 (j == L+1), float64
 // rounded once.  Light tables (j < L) are in k_rank's order, the two closest-hit tables in array order (ids matter there).
 __global__ void k_pivot(SceneDev sc, float cox, float coy, float coz, const int* perm, float4* tab, float4* piv, float* rad) {
@@ -357,7 +407,7 @@ __global__ void k_pivot(SceneDev sc, float cox, float coy, float coz, const int*
     float c[2][4];
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
-        const int s = (j < sc.L) ? perm[(size_t)j * sc.Spad + 2 * i + h] : 2 * i + h;
+        const int s = perm[(size_t)min(j, sc.L) * sc.Spad + 2 * i + h];         // light j's order, or the closest-hit tables' (row L)
         if (s < sc.S) {
             const float4 sp = sc.sphB[s];
             const double ex = (double)sp.x - v.x, ey = (double)sp.y - v.y, ez = (double)sp.z - v.z;
@@ -843,14 +893,14 @@ struct DevCtx {
     int isect_blocks_per_sm = 2;
     int force_nr = 0, force_nr0 = 0; bool no_pivot = false, no_conc = false, no_cull = false;                       // tuning overrides (env B200RT_NR, B200RT_NO_PIVOT)
     Buf sphA, sphB, sphCol, plO, plN, plNu, plCol, lights, cmax;   // packed scene
-    Buf pivTab, pivPos, pivPerm, pivRad;                                   // pivot tables (k_pivot), light-table order (k_rank)
+    Buf pivTab, pivPos, pivPerm, pivRad, pivClus;                                   // pivot tables (k_pivot), light-table order (k_rank)
     Buf stage;                                                     // host-scene / host-pixel_loc staging
     Buf rayO[2], rayD[2], hitKey[2];                               // ray queues, double-buffered by depth parity
     Buf hP[kSets], hN[kSets], occl[kSets], shidx[kSets], shidx2[kSets];   // hit records / shadow state: ring of kSets depths
     Buf acc, ctr, work, slow, tl, ostat;
     Buf sgCells, sgTab, sgCone;                                      // per-light direction grids of the shadow queries (shadow_grid.cuh)
     Buf sortKey, sortPerm, sortHist, sortBase, sortPart, sortGrid;   // regrouping of bounce-depth hits (k_key .. k_perm)
-    bool no_sgrid = false; int sgrid_min_s = 1; bool no_sort = false; int sort_posbits = -1, sort_dirn = -1;     // env B200RT_NO_SORT, B200RT_SORT_POSBITS, B200RT_SORT_DIRN (-1: chosen from the queue size)
+    bool no_sgrid = false, no_clus = false; int sgrid_min_s = 1; bool no_sort = false; int sort_posbits = -1, sort_dirn = -1;     // env B200RT_NO_SORT, B200RT_SORT_POSBITS, B200RT_SORT_DIRN (-1: chosen from the queue size)
     int npre = 1, pre[6] = {256, 0, 0, 0, 0, 0};                    // leading shadow passes (env B200RT_PASSES=a,b,...; multiples of 8)
     bool timeline = false;                                        // env B200RT_TIMELINE: per-launch first-start / last-end (globaltimer) to stderr
     // internal streams (see the launch sequence in render_device): the dependent chain at high priority, one stream per
@@ -862,7 +912,7 @@ struct DevCtx {
     Buf hostResult, hostPixelLoc, imgOut;                          // b200rt_render_host / b200rt_to_image_host device copies
     cudaEvent_t done = nullptr; bool has_done = false;
     void release_all() {
-        Buf* all[] = { &sphA, &sphB, &sphCol, &plO, &plN, &plNu, &plCol, &lights, &cmax, &pivTab, &pivPos, &pivPerm, &pivRad, &stage, &rayO[0], &rayO[1], &rayD[0], &rayD[1], &hitKey[0], &hitKey[1],
+        Buf* all[] = { &sphA, &sphB, &sphCol, &plO, &plN, &plNu, &plCol, &lights, &cmax, &pivTab, &pivPos, &pivPerm, &pivRad, &pivClus, &stage, &rayO[0], &rayO[1], &rayD[0], &rayD[1], &hitKey[0], &hitKey[1],
                        &acc, &tl, &ostat, &ctr, &work, &slow, &sortKey, &sortPerm, &sortHist, &sortBase, &sortPart, &sortGrid, &sgCells, &sgTab, &sgCone, &hostResult, &hostPixelLoc, &imgOut, &batchScene };
         for (Buf* b : all) b->release();
         for (int i = 0; i < kSets; ++i) { hP[i].release(); hN[i].release(); occl[i].release(); shidx[i].release(); shidx2[i].release(); }
@@ -944,6 +994,7 @@ int init_ctx(DevCtx& c, int device) {
     { const char* e = getenv("B200RT_NO_CULL"); c.no_cull = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_TIMELINE"); c.timeline = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_NO_SORT"); c.no_sort = e && atoi(e) != 0; }
+    { const char* e = getenv("B200RT_NO_CLUS"); c.no_clus = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_NO_SGRID"); c.no_sgrid = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_SGRID_MIN_S"); if (e) c.sgrid_min_s = std::max(1, atoi(e)); }
     { const char* e = getenv("B200RT_SORT_POSBITS"); if (e) c.sort_posbits = std::min(18, std::max(0, atoi(e))); }
@@ -1016,15 +1067,18 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     CK(c.pivTab.ensure(sizeof(float4) * (size_t)(L + 2) * Spad)); CK(c.pivPos.ensure(sizeof(float4) * (L + 1)));
     {
         const int n = (L + 2) * (Spad / 2);
-        CK(c.pivPerm.ensure(sizeof(int) * std::max<size_t>((size_t)L * Spad, 1))); CK(c.pivRad.ensure(sizeof(float) * (size_t)(L + 2) * Spad));
+        CK(c.pivPerm.ensure(sizeof(int) * (size_t)(L + 1) * Spad)); CK(c.pivRad.ensure(sizeof(float) * (size_t)(L + 2) * Spad));
+        CK(c.pivClus.ensure(sizeof(float4) * (size_t)((Spad + 63) / 64)));
         if (L > 0) { k_rank<<<dim3((Spad + 255) / 256, L), 256, 0, st>>>(sc, c.pivPerm.as<int>()); CKL(); }
+        k_mrank<<<(Spad + 255) / 256, 256, 0, st>>>(sc, c.pivPerm.as<int>()); CKL();
+        k_clus<<<((Spad + 63) / 64 + 63) / 64, 64, 0, st>>>(sc, c.pivPerm.as<int>(), c.pivClus.as<float4>()); CKL();
         k_pivot<<<(n + 255) / 256, 256, 0, st>>>(sc, (float)a->cam_origin[0], (float)a->cam_origin[1], (float)a->cam_origin[2],
                                                  c.pivPerm.as<int>(), c.pivTab.as<float4>(), c.pivPos.as<float4>(), c.pivRad.as<float>());
         CKL();
     }
     const bool dense = (a->flags & B200RT_F_DENSE) != 0;          // brute force: every specified query scans every sphere
     const bool cull = !(a->flags & B200RT_F_NO_CULL) && !c.no_cull && !dense;
-    const PivotDev pv{ c.pivTab.as<float4>(), c.pivPos.as<float4>(), c.cmax.as<float>(), c.pivPerm.as<int>(), cull ? c.pivRad.as<float>() : nullptr };
+    const PivotDev pv{ c.pivTab.as<float4>(), c.pivPos.as<float4>(), c.cmax.as<float>(), c.pivPerm.as<int>(), cull ? c.pivRad.as<float>() : nullptr, (cull && !c.no_clus) ? c.pivClus.as<float4>() : nullptr };
     // Constant-memory residency (isect3.cuh): the closest-hit module holds the camera-pivot and origin-free tables,
     // the shadow module one table per light.  When they fit they are uploaded once per frame.
     const bool nofilter = (a->flags & B200RT_F_NO_FILTER) != 0;

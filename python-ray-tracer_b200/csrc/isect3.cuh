@@ -90,8 +90,9 @@ struct PivotDev {
     const float4* tab;                   // [(L+2)][Spad] pair layout; table j < L: light j, j == L: camera, j == L+1: origin-free
     const float4* piv;                   // [(L+1)]       pivot positions (float32)
     const float*  bounds;                // [2]           max |C|, max r
-    const int*    perm;                  // [L][Spad]     light tables only: table position -> sphere index (k_rank), or null
+    const int*    perm;                  // [L+1][Spad]   table position -> sphere index: rows 0..L-1 the lights' tables (k_rank), row L both closest-hit tables (k_mrank)
     const float*  rad;                   // [(L+2)][Spad] radius of the sphere at each table position (beam culling), or null = no culling
+    const float4* clus;                  // [ceil(Spad/64)] bounding spheres of 64 consecutive positions of the closest-hit tables (k_clus), or null
 };
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
@@ -293,7 +294,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
                 if (idx < qcnt) {
                     const uint32_t item = sq[idx];
                     rl = item & 255u; sid = c0 + (int)(item >> 8);
-                    if (ANY && pv.perm) sid = __ldg(&pv.perm[(size_t)j * sc.Spad + sid]);          // sorted table position -> sphere
+                    sid = __ldg(&pv.perm[(size_t)(ANY ? j : sc.L) * sc.Spad + sid]);               // table position -> sphere
                     const float4 dd = ws.d[rl];                // the ray as staged by the prologue (2*O halves exactly)
                     const V3 D = mk(dd.x, dd.y, dd.z);
                     V3 O = Vp;
@@ -432,13 +433,28 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
                             uu[e] = __ldg(gt + 2 * p); ww[e] = __ldg(gt + 2 * p + 1); rr[e] = __ldg(gr + p);
                         }
                     };
-                    load_round(0);
+                    // Closest-hit tables are in Morton order (k_mrank): 64 consecutive positions = 32 pairs form a compact
+                    // cluster with a bounding sphere (k_clus).  Lane c tests cluster c against the beam first; rounds whose
+                    // clusters are all clear of it are skipped entirely (no loads, no per-sphere tests).
+                    uint32_t rmask = 0xffffffffu;                              // bit r: round r (pairs [32 CE r, 32 CE (r+1))) has to be looked at
+                    if (!ANY && pv.clus && c0 == 0) {
+                        const int ncl = (npair + 31) >> 5;                     // <= 16 (npair <= 512)
+                        bool keepc = false;
+                        if ((int)lane < ncl) { const float4 cb = __ldg(&pv.clus[lane]); keepc = cb.w >= 0.f && !clear_of_beam(cb.x, cb.y, cb.z, cb.w); }
+                        const uint32_t cm = __ballot_sync(0xffffffffu, keepc);
+                        rmask = (CE == 1) ? cm : 0u;
+                        if (CE > 1) for (int r = 0; r * CE < ncl; ++r) if ((cm >> (r * CE)) & ((1u << CE) - 1u)) rmask |= 1u << r;
+                    }
+                    rmask &= (npair + 32 * CE - 1) / (32 * CE) >= 32 ? 0xffffffffu : (1u << ((npair + 32 * CE - 1) / (32 * CE))) - 1u;
+                    if (rmask) load_round((__ffs(rmask) - 1) * 32 * CE);
 #pragma unroll 1
-                    for (int p0 = 0; p0 < npair; p0 += 32 * CE) {
+                    while (rmask) {
+                        const int p0 = (__ffs(rmask) - 1) * 32 * CE;
+                        rmask &= rmask - 1u;
                         float4 cu[CE], cw[CE]; float2 cr[CE];
 #pragma unroll
                         for (int e = 0; e < CE; ++e) { cu[e] = uu[e]; cw[e] = ww[e]; cr[e] = rr[e]; }
-                        if (p0 + 32 * CE < npair) load_round(p0 + 32 * CE);
+                        if (rmask) load_round((__ffs(rmask) - 1) * 32 * CE);
 #pragma unroll
                         for (int e = 0; e < CE; ++e) {
                             const int p = p0 + e * 32 + (int)lane;
