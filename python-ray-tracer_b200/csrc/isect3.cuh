@@ -714,7 +714,9 @@ static cudaError_t isect3_launch_one(const IsectCfg& cfg, const SceneDev& sc, co
     // 4 rays per thread (groups of 128 rays, 3 CTAs = 24 warps per SM) measured best at every size once the 4-ray build
     // could cull 512 pairs (C4: 13.06 -> 12.78 ms; 1/8 of it 2.29 -> 2.17: shorter groups, shorter tails); 8 rays per
     // thread (B200RT_NR=8) amortise the uniform loads better but run 16 warps per SM.
-    int nr = cfg.force_nr ? cfg.force_nr : (max_rays >= warps * 128 * 4 ? 4 : 2);
+    // Without culling (brute-force mode, B200RT_F_NO_CULL) the launch is one long dense scan and 8 rays per thread win
+    // (C4 dense mode: 60.8 vs 69.5 ms per frame).
+    int nr = cfg.force_nr ? cfg.force_nr : (max_rays >= warps * 128 * 4 ? ((pv.rad || max_rays < warps * 256 * 4) ? 4 : 8) : 2);
     if (MODE == 0 && cfg.force_nr0) nr = cfg.force_nr0;         // (measured: 8 rays/thread wins for the 8-FFMA2 form too)
     const int grid = cfg.sm_count * (nr == 8 ? 2 : 3);
     const bool diag = q.slow != nullptr || q.tl != nullptr;
