@@ -32,7 +32,7 @@ for p in (ROOT, os.path.join(ROOT, "python-ray-tracer_b200")):
 
 import numpy as np  # noqa: E402
 
-STRIP = 16           # columns per interleaved strip (multi-GPU load balance)
+STRIP = int(os.environ.get("B200RT_STRIP", "16"))    # columns per interleaved strip (multi-GPU load balance); multiple of 16
 
 
 class ClockSampler(threading.Thread):
@@ -170,7 +170,7 @@ def run_ours(args, w):
     strips = (STRIP, rank, world) if world > 1 else None
     emu = int(os.environ.get("B200RT_EMULATE_WORLD", "0"))      # tuning aid: render rank 0's share of an N-GPU frame on one GPU
     if world == 1 and emu > 1:
-        strips = (STRIP, 0, emu)
+        strips = (STRIP, int(os.environ.get("B200RT_EMULATE_RANK", "0")), emu)
     shade = (w["amb"], w["lamb"], w["refl"], w["refl_depth"], w["aliasing"])
     stream = torch.cuda.current_stream(dev)
 
