@@ -85,7 +85,8 @@ __global__ void __launch_bounds__(256) k_sgrid_tab(SceneDev sc, ShadowGridDev g)
 
 // One thread per (cell, light, tier): the list, in rank order, of the spheres whose cone (either sign) reaches the cell's cone.
 __global__ void __launch_bounds__(256) k_sgrid_build(SceneDev sc, ShadowGridDev g) {
-    __shared__ float4 s_cone[256];
+    __shared__ float4 s_cone[256];                                         // (unit direction, cos alpha)
+    __shared__ float s_sin[256];                                           // sin alpha; alpha + beta >= pi: cos = -2 (always listed)
     __shared__ int s_id[256];
     const int cell = blockIdx.x * 256 + threadIdx.x, j = blockIdx.y, tier = blockIdx.z;     // kSgCells % 256 == 0
     const int face = cell / (kSgN * kSgN), iu = (cell / kSgN) % kSgN, iv = cell % kSgN;
@@ -98,6 +99,7 @@ __global__ void __launch_bounds__(256) k_sgrid_build(SceneDev sc, ShadowGridDev 
         beta = fmaxf(beta, acosf(fminf(1.f, dot3(q, cdir))));
     }
     beta += 2e-3f;
+    const float cb = cosf(beta), sb = sinf(beta);
     const float4 v = sc.lights[j];
     const bool in_range = sc.cmax[0] + sqrtf(v.x * v.x + v.y * v.y + v.z * v.z) <= kSgRange;    // (NaN -> false)
     uint16_t* rec = g.cells + (((size_t)tier * sc.L + j) * kSgCells + cell) * kSgRec;
@@ -105,13 +107,19 @@ __global__ void __launch_bounds__(256) k_sgrid_build(SceneDev sc, ShadowGridDev 
     uint32_t cnt = 0;
     for (int s0 = 0; s0 < sc.S; s0 += 256) {
         __syncthreads();
-        if (s0 + (int)threadIdx.x < sc.S) { s_cone[threadIdx.x] = cone[s0 + threadIdx.x]; s_id[threadIdx.x] = g.perm[(size_t)j * g.Spad + s0 + threadIdx.x]; }
+        if (s0 + (int)threadIdx.x < sc.S) {
+            const float4 c = cone[s0 + threadIdx.x];
+            // angle(u, cell) <= alpha + beta  <=>  u . cdir >= cos(alpha + beta) = cos a cos b - sin a sin b  (alpha + beta < pi; beta <= 0.8)
+            const bool all = c.w >= 3.1415927f - 0.9f;
+            s_cone[threadIdx.x] = make_float4(c.x, c.y, c.z, all ? -2.f : cosf(c.w)); s_sin[threadIdx.x] = all ? 0.f : sinf(c.w);
+            s_id[threadIdx.x] = g.perm[(size_t)j * g.Spad + s0 + threadIdx.x];
+        }
         __syncthreads();
         const int n = min(256, sc.S - s0);
         for (int k = 0; k < n; ++k) {
             const float4 c = s_cone[k];
-            const float ang = acosf(fminf(1.f, fabsf(c.x * cdir.x + c.y * cdir.y + c.z * cdir.z)));
-            if (ang <= c.w + beta) { if (cnt < (uint32_t)kSgCap) rec[4 + cnt] = (uint16_t)s_id[k]; ++cnt; }
+            const float dt = fabsf(c.x * cdir.x + c.y * cdir.y + c.z * cdir.z);
+            if (dt >= fmaf(c.w, cb, -s_sin[k] * sb) - 1e-6f) { if (cnt < (uint32_t)kSgCap) rec[4 + cnt] = (uint16_t)s_id[k]; ++cnt; }
         }
     }
     const bool over = cnt > (uint32_t)kSgCap || !in_range;
