@@ -28,7 +28,7 @@ namespace b200rt {
 #define B200RT_SS_OCC 4                  // CTAs per SM the register allocation of k_shadow_shade aims at
 #endif
 #ifndef B200RT_SGN
-#define B200RT_SGN 32
+#define B200RT_SGN 64                   // (32: shadow kernel +8 %; 48: +1.5 %; measured with the cosine-comparison build)
 #endif
 constexpr int kSgN = B200RT_SGN;                          // cells per edge of a cube-map face
 constexpr int kSgCells = 6 * kSgN * kSgN;         // cells per light
