@@ -7,9 +7,8 @@ sys.path.insert(0, os.path.join(ROOT, "python-ray-tracer_b200")); sys.path.inser
 from b200rt import render_host, _lib
 from b200rt.scene import Camera
 
-n = int(sys.argv[1]) if len(sys.argv) > 1 else 40
-bad = 0
-for seed in range(n):
+def scene(seed):
+    """Random scene `seed` -> (args of render_host after pixel_loc, grid, (W, H), description)."""
     rng = np.random.default_rng(1000 + seed)
     S = int(rng.choice([1, 3, 17, 64, 200, 700, 1500])); L = int(rng.integers(1, 6)); Pl = int(rng.integers(0, 3))
     W, H = 16 * int(rng.integers(6, 14)), 16 * int(rng.integers(4, 9))
@@ -32,11 +31,23 @@ for seed in range(n):
     cam = Camera(resolution=(W, H), position=[-2, 0, 2.0], euler=[0, -30, 0])
     depth = int(rng.integers(0, 4)); aa = bool(rng.integers(0, 4) == 0)
     args = (cam.position, cam.rotation, sp, li, pl, 0.05, 0.6, 0.3, depth, aa)
-    a = render_host(None, *args, grid=np.array(cam.grid()), shape=(W, H))
-    b = render_host(None, *args, grid=np.array(cam.grid()), shape=(W, H), flags=_lib.F_DENSE)
-    c = render_host(None, *args, grid=np.array(cam.grid()), shape=(W, H), flags=_lib.F_NO_SGRID)
-    ok = np.array_equal(a, b) and np.array_equal(a, c)
-    bad += 0 if ok else 1
-    print(f"seed {seed}: S={S} L={L} Pl={Pl} {W}x{H} depth={depth} aa={aa} sum={int(a.sum())} -> {'ok' if ok else 'MISMATCH ' + str(int((a != b).sum())) + ' / ' + str(int((a != c).sum()))}", flush=True)
-print("mismatching scenes:", bad)
-sys.exit(1 if bad else 0)
+    return args, np.array(cam.grid()), (W, H), f"S={S} L={L} Pl={Pl} {W}x{H} depth={depth} aa={aa}"
+
+
+def check(seed):
+    args, grid, shape, desc = scene(seed)
+    a = render_host(None, *args, grid=grid, shape=shape)
+    b = render_host(None, *args, grid=grid, shape=shape, flags=_lib.F_DENSE)
+    c = render_host(None, *args, grid=grid, shape=shape, flags=_lib.F_NO_SGRID)
+    return np.array_equal(a, b) and np.array_equal(a, c), desc, int(a.sum()), int((a != b).sum()), int((a != c).sum())
+
+
+if __name__ == "__main__":
+    n = int(sys.argv[1]) if len(sys.argv) > 1 else 40
+    bad = 0
+    for seed in range(n):
+        ok, desc, chk, d1, d2 = check(seed)
+        bad += 0 if ok else 1
+        print(f"seed {seed}: {desc} sum={chk} -> {'ok' if ok else f'MISMATCH {d1} / {d2}'}", flush=True)
+    print("mismatching scenes:", bad)
+    sys.exit(1 if bad else 0)
