@@ -1088,7 +1088,9 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     // Shadow queries through the per-light direction grids (shadow_grid.cuh) wherever work may be skipped at all
     // (beam culling on); k_isect3<shadow> + k_shade stay for the brute-force / debug modes.  (Also for the 6-sphere default
     // scene: C3 3.95 -> 2.58 ms, C5 1.78 -> 1.40 ms per frame against the dense [light][hit] scan.)
-    const bool sgrid = cull && !nofilter && S >= c.sgrid_min_s && S <= 65535 && L > 0 && !(a->flags & B200RT_F_NO_SGRID) && !c.no_sgrid;
+    const bool sgrid = cull && !nofilter && S >= c.sgrid_min_s && S <= 65535 && L > 0 &&
+                       sizeof(uint16_t) * (size_t)kSgTiers * L * kSgCells * kSgRec <= ((size_t)8 << 30) &&      // 12.6 MB per light; beyond 8 GB of grids: scan path
+                       !(a->flags & B200RT_F_NO_SGRID) && !c.no_sgrid;
     ShadowGridDev sg{};
     if (sgrid) {
         CK(c.sgCells.ensure(sizeof(uint16_t) * (size_t)kSgTiers * L * kSgCells * kSgRec));
