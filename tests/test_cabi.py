@@ -68,3 +68,14 @@ def test_missing_library_fails_loudly(monkeypatch):
     monkeypatch.setattr(_lib, "LIB_PATH", "/nonexistent/libb200rt.so")
     with pytest.raises(ImportError):
         _lib.lib()
+
+
+def test_flag_constants_match_header():
+    """The B200RT_F_* values of include/b200rt.h and the constants the Python binding passes are the same numbers."""
+    import re
+    from b200rt import _lib
+    hdr = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include", "b200rt.h")).read()
+    flags = {m.group(1): int(m.group(2), 16) for m in re.finditer(r"#define\s+B200RT_F_(\w+)\s+0x([0-9a-fA-F]+)u", hdr)}
+    assert len(flags) >= 8 and len(set(flags.values())) == len(flags)          # distinct bits
+    for name, val in flags.items():
+        assert getattr(_lib, "F_" + name) == val, name
