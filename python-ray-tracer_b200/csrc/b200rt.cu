@@ -900,7 +900,7 @@ struct DevCtx {
     Buf acc, ctr, work, slow, tl, ostat;
     Buf sgCells, sgTab, sgCone;                                      // per-light direction grids of the shadow queries (shadow_grid.cuh)
     Buf sortKey, sortPerm, sortHist, sortBase, sortPart, sortGrid;   // regrouping of bounce-depth hits (k_key .. k_perm)
-    bool no_sgrid = false, no_clus = false, no_sort_last = true; int sgrid_min_s = 1; bool no_sort = false; int sort_posbits = -1, sort_dirn = -1;     // env B200RT_NO_SORT, B200RT_SORT_POSBITS, B200RT_SORT_DIRN (-1: chosen from the queue size)
+    bool no_sgrid = false, no_clus = false, no_sort_last = true; int ss_grid = 0; int sgrid_min_s = 1; bool no_sort = false; int sort_posbits = -1, sort_dirn = -1;     // env B200RT_NO_SORT, B200RT_SORT_POSBITS, B200RT_SORT_DIRN (-1: chosen from the queue size)
     int npre = 1, pre[6] = {256, 0, 0, 0, 0, 0};                    // leading shadow passes (env B200RT_PASSES=a,b,...; multiples of 8)
     bool timeline = false;                                        // env B200RT_TIMELINE: per-launch first-start / last-end (globaltimer) to stderr
     // internal streams (see the launch sequence in render_device): the dependent chain at high priority, one stream per
@@ -995,6 +995,7 @@ int init_ctx(DevCtx& c, int device) {
     { const char* e = getenv("B200RT_TIMELINE"); c.timeline = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_NO_SORT"); c.no_sort = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_SORT_LAST"); if (e) c.no_sort_last = atoi(e) == 0; }   // the last depth has no next bounce to regroup for: skipping its sort measured 0.08 ms faster at C4
+    { const char* e = getenv("B200RT_SS_GRID"); if (e) c.ss_grid = std::max(0, atoi(e)); }     // CTAs per SM of the k_shadow_shade grid (0: sized from the queue)
     { const char* e = getenv("B200RT_NO_CLUS"); c.no_clus = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_NO_SGRID"); c.no_sgrid = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_SGRID_MIN_S"); if (e) c.sgrid_min_s = std::max(1, atoi(e)); }
@@ -1268,7 +1269,10 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
                                        q.slow ? cd + 4 : nullptr, q.slow, nullptr };        // (counters only in the diagnostic frame: B200RT_F_TIME_ONLY leaves shadow_traced 0)
                     if (conc) CK(cudaStreamWaitEvent(ss, c.evSetup[hs], 0));
                     if (tlb) { ga.tl = tlb + 2 * (size_t)tln++; tlname.push_back("shadow+shade d" + std::to_string(d)); }
-                    k_shadow_shade<<<small_grid, 256, 0, ss>>>(sc, sg, ga); CKL();
+                    // grid: ~16 hits per thread, between 8 and 64 CTAs per SM (C4: 55 per SM measured 0.12 ms faster than 8; 1/8 of it stays at 8)
+                    const int ssg = c.ss_grid > 0 ? c.sm_count * c.ss_grid
+                                                  : (int)std::min<size_t>((size_t)c.sm_count * 64, std::max<size_t>((size_t)c.sm_count * 8, cap / (256 * 16)));
+                    k_shadow_shade<<<ssg, 256, 0, ss>>>(sc, sg, ga); CKL();
                     if (conc) CK(cudaEventRecord(c.evShade[hs], ss));
                 }
                 else {
