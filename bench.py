@@ -282,10 +282,10 @@ def run_ours(args, w):
         nominal_tf = 2.0 * 128 * sms * sm_max * 1e6 / 1e12
         fpr = flops_per_ray(S, Pl)
         traffic, traffic_src = None, None          # ncu dram bytes of the k_isect3 launches of one frame (committed capture, 1 GPU, C4)
-        tp = os.path.join(ROOT, "profiles", "r01_v11_traffic.json")
+        tp = os.path.join(ROOT, "profiles", "r01_v12_traffic.json")
         if os.path.exists(tp) and args.workload == "c4" and world == 1:
             tj = json.load(open(tp))
-            traffic, traffic_src = tj["traffic_bytes_per_frame"], "profiles/r01_v11_traffic.json (ncu dram__bytes_read+write, the 4 k_isect3 + 4 k_shadow_shade launches of one frame)"
+            traffic, traffic_src = tj["traffic_bytes_per_frame"], "profiles/r01_v12_traffic.json (ncu dram__bytes_read+write, the 4 k_isect3 + 4 k_shadow_shade launches of one frame)"
         ach_tf = rays_this_rank * fpr / (isect_ms * 1e-3) / 1e12
         clocks = sampler.summary()
         line = {
