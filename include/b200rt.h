@@ -142,6 +142,17 @@ B200RT_API int b200rt_to_image(int device, void* stream, const uint8_t* planar, 
 /* Same with HOST buffers (stages, transposes on the device, copies back, synchronises). */
 B200RT_API int b200rt_to_image_host(int device, const uint8_t* planar, uint8_t* rgb, int W, int H, uint32_t flags);
 
+/* Allocation-free variant of b200rt_to_image_host.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (tight serving loops, harnesses that forbid it).  Same
+ * arguments, same result bytes; the device staging buffers are one file-scope `static __device__` array of
+ * 2 * 3 * B200RT_NOALLOC_MAX_PIXELS bytes (6 MiB, held by every GPU that loads the library until exit), so the call
+ * performs no cudaMalloc / cudaFree / allocating library routine.  W*H > B200RT_NOALLOC_MAX_PIXELS is rejected with
+ * B200RT_E_SHAPE.  All calls on a device share the array (it keeps the last call's contents; the call clears what it
+ * hands back); calls overlapping on the GPU would race on it, so the entry point serialises its callers per device
+ * (mutex, default stream, synchronous). */
+#define B200RT_NOALLOC_MAX_PIXELS (1 << 20)   /* 1024 x 1024; the reference's main.py frame is 1000 x 1000 (src/main.py:10) */
+B200RT_API int b200rt_to_image_host_noalloc(int device, const uint8_t* planar, uint8_t* rgb, int W, int H, uint32_t flags);
+
 B200RT_API int b200rt_device_count(void);
 B200RT_API int b200rt_sm_count(int device);
 /* Kernels launched by this library since it was loaded (host-side count, all devices and threads): the difference

@@ -62,6 +62,7 @@ def lib():
         L.b200rt_fp32_probe.restype = C.c_int
         L.b200rt_to_image.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint32]; L.b200rt_to_image.restype = C.c_int
         L.b200rt_to_image_host.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint32]; L.b200rt_to_image_host.restype = C.c_int
+        L.b200rt_to_image_host_noalloc.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint32]; L.b200rt_to_image_host_noalloc.restype = C.c_int
         L.b200rt_device_count.restype = C.c_int
         L.b200rt_sm_count.argtypes = [C.c_int]; L.b200rt_sm_count.restype = C.c_int
         L.b200rt_launch_count.restype = C.c_ulonglong

@@ -1529,6 +1529,55 @@ B200RT_API int b200rt_to_image_host(int device, const uint8_t* planar, uint8_t* 
     return 0;
 }
 
+// ------------------------------------------------------------------------------------------------
+// Allocation-free variant of b200rt_to_image_host (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: tight serving loops, harnesses that forbid it).
+// The two device staging buffers that b200rt_to_image_host takes from cudaMalloc'd per-device scratch (DevCtx::hostResult,
+// DevCtx::imgOut) live in ONE file-scope device array of fixed size instead: planar input in the first half, interleaved
+// output in the second.  Every device that loads the library holds the array (6 MiB) until the process exits.
+// In host code `g_noalloc_scratch` is only a host-side stand-in for the symbol, never a device address: the device
+// address is fetched once per device with cudaGetSymbolAddress (that device current) and only that pointer goes to
+// copies and kernels.  The array is shared by every call on the device and keeps the last call's contents; nothing in
+// it has to start at zero (the H2D copy overwrites the whole input region and k_to_image writes every byte of the output
+// region of a W x H frame), the output region is still cleared first so that a failed launch cannot hand back an older
+// frame.  Calls that overlapped on the GPU would race on the array: this entry point therefore holds a per-device mutex,
+// works on the default stream and synchronises before it returns, so two host threads on one device queue up.
+// ------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_noalloc_scratch[2 * 3 * (size_t)B200RT_NOALLOC_MAX_PIXELS];
+
+namespace {
+struct NoAllocCtx { std::mutex mu; unsigned char* dev_ptr = nullptr; };
+NoAllocCtx g_noalloc[kMaxDevices];
+}
+
+B200RT_API int b200rt_to_image_host_noalloc(int device, const uint8_t* planar, uint8_t* rgb, int W, int H, uint32_t flags) {
+    if (!planar || !rgb) return fail(B200RT_E_NULL, "planar / rgb pointer is NULL");
+    if (W <= 0 || H <= 0) return fail(B200RT_E_SHAPE, "W and H must be positive");
+    if ((long long)W * H > (long long)B200RT_NOALLOC_MAX_PIXELS)
+        return fail(B200RT_E_SHAPE, "b200rt_to_image_host_noalloc: W*H = " + std::to_string((long long)W * H) + " pixels exceeds the static scratch of B200RT_NOALLOC_MAX_PIXELS = " +
+                                    std::to_string((long long)B200RT_NOALLOC_MAX_PIXELS) + " pixels; use b200rt_to_image_host");
+    int ndev = b200rt_device_count();
+    if (device < 0 || device >= ndev || device >= kMaxDevices) return fail(B200RT_E_DEVICE, "no such CUDA device");
+    DeviceGuard guard(device);
+    NoAllocCtx& c = g_noalloc[device];
+    std::lock_guard<std::mutex> lock(c.mu);
+    if (!c.dev_ptr) {                                              // set-up, once per device, with that device current
+        void* p = nullptr;
+        CK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        if (!p) return fail(B200RT_E_NOMEM, "cudaGetSymbolAddress returned a null address for the static scratch");
+        c.dev_ptr = static_cast<unsigned char*>(p);
+    }
+    const size_t n = (size_t)3 * W * H;
+    unsigned char* d_in = c.dev_ptr;
+    unsigned char* d_out = c.dev_ptr + (size_t)3 * B200RT_NOALLOC_MAX_PIXELS;      // 256-byte aligned: 3 * 2^20
+    CK(cudaMemcpyAsync(d_in, planar, n, cudaMemcpyHostToDevice, nullptr));
+    CK(cudaMemsetAsync(d_out, 0, n, nullptr));
+    if (int rc = b200rt_to_image(device, nullptr, d_in, d_out, W, H, flags)) return rc;
+    CK(cudaMemcpyAsync(rgb, d_out, n, cudaMemcpyDeviceToHost, nullptr));
+    CK(cudaStreamSynchronize(nullptr));
+    return 0;
+}
+
 B200RT_API int b200rt_shutdown(void) {
     int ndev = b200rt_device_count();
     for (int dev = 0; dev < ndev && dev < kMaxDevices; ++dev) {
