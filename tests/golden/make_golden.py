@@ -228,6 +228,12 @@ def main():
                                        regions=random_regions(rng, 3840, 2160, 8, 32), procs=p),
         "c4_crops": lambda: frame_case("c4_crops", c4_scene(), Camera((7680, 4320), [-6, 0, 5.0], [0, -25, 0]), 0.0, 0.6, 0.3, 3, False,
                                        regions=random_regions(rng, 7680, 4320, 16, 12), procs=p, cols_per_job=1),
+        # round 2: the simulator pin of the full-size C4 frame grown 4x (28 more crops of 16x16 = 7168 px, ~2.4 core-s per pixel
+        # at S=1024: ~5 core-hours), and C4 WITH anti-aliasing (9 samples per pixel: ~22 core-s per pixel), incl. the flat-wrap corner
+        "c4_crops_b": lambda: frame_case("c4_crops_b", c4_scene(), Camera((7680, 4320), [-6, 0, 5.0], [0, -25, 0]), 0.0, 0.6, 0.3, 3, False,
+                                         regions=random_regions(np.random.default_rng(4102), 7680, 4320, 28, 16, include_edges=False), procs=p, cols_per_job=1),
+        "c4_aa1_crops": lambda: frame_case("c4_aa1_crops", c4_scene(), Camera((7680, 4320), [-6, 0, 5.0], [0, -25, 0]), 0.0, 0.6, 0.3, 3, True,
+                                           regions=random_regions(np.random.default_rng(4103), 7680, 4320, 5, 8), procs=p, cols_per_job=1),
         "c4_small": lambda: frame_case("c4_small", c4_scene(), Camera((64, 36), [-6, 0, 5.0], [0, -25, 0]), 0.0, 0.6, 0.3, 3, False,
                                        procs=p, cols_per_job=1),
         "c5_crops_k0": lambda: frame_case("c5_crops_k0", default, c5_camera(0), 0.0, 0.6, 0.3, 2, False,

@@ -307,3 +307,129 @@ def test_fuzz_default_equals_brute_force_and_scan_path():
         assert ok, (seed, desc, d1, d2)
         total += chk                       # (a single scene may be all black: spheres off camera, no plane)
     assert total > 0
+
+
+@pytest.fixture
+def max_paths():
+    """Sets B200RT_MAX_PATHS (read by the library at every call) and restores it."""
+    import os
+    old = os.environ.get("B200RT_MAX_PATHS")
+
+    def set_(v):
+        if v is None:
+            os.environ.pop("B200RT_MAX_PATHS", None)
+        else:
+            os.environ["B200RT_MAX_PATHS"] = str(v)
+    yield set_
+    set_(old)
+
+
+@pytest.mark.parametrize("name", ["c1_aa1", "rand_b", "c4_small", "synthetic_512x256", "synthetic_aa_272x144"])
+def test_multi_chunk_wavefront_equals_one_chunk(max_paths, name):
+    """A frame whose paths exceed the chunk capacity is rendered as several wavefronts over column ranges (C4 with
+    anti-aliasing: 7 chunks of <= 48 Mi paths).  Forced here with B200RT_MAX_PATHS: every byte equals the one-chunk render,
+    with tiled (16-column multiples) and column-major slot orders, anti-aliased (ordered compaction per chunk) or not."""
+    if name.startswith("synthetic_aa"):
+        g = _synthetic(700, 2, 1, 272, 144, 2, True, seed=91)
+    elif name.startswith("synthetic"):
+        g = _synthetic(1024, 3, 1, 512, 256, 3, False, seed=90)
+    else:
+        g = load_golden(name)
+    max_paths(None)
+    one, st1 = _cuda(g, stats=True)
+    H, ns = int(g["H"]), 9 if bool(g["aliasing"]) else 1
+    for paths in (4096, 16 * H * ns + 5, 40 * H * ns):           # 1-2 columns per chunk (untiled), exactly 16, 32 (tiled: rounded down to 16s)
+        max_paths(max(1024, paths))
+        many, stn = _cuda(g, stats=True)
+        assert np.array_equal(one, many), (name, paths)
+        assert stn["rays"] == st1["rays"] and stn["primary"] == st1["primary"], (name, paths)
+        assert np.array_equal(one, _cuda(g)), (name, paths, "production kernels")
+    max_paths(None)
+
+
+def test_c4_antialiased_crops_vs_simulator_golden():
+    """C4 with anti-aliasing (SURVEY §8(d) 'secondary'): crops of the full 7680x4320 frame, 9 samples per pixel, against the
+    reference itself under the simulator — including the flat-wrap corner x = W-1 / y = H-1."""
+    if not have_golden("c4_aa1_crops"):
+        pytest.skip("golden not generated")
+    g = load_golden("c4_aa1_crops")
+    assert bool(g["aliasing"])
+    tot = dict(n=0, n_bad=0, max=0)
+    for (x0, x1, y0, y1, ref) in golden_regions(g):
+        xa = (x0 // 16) * 16
+        got = _cuda(g, tile=(xa, min(int(g["W"]), xa + 16)))[:, x0:x1, y0:y1]
+        rep = parity_report(got, ref)
+        tot["n"] += rep["n"]; tot["n_bad"] += rep["n_bad"]; tot["max"] = max(tot["max"], rep["max"])
+    print("c4 AA crops", tot)
+    assert tot["n_bad"] <= _budget(tot["n"]), tot
+
+
+def test_c4_second_simulator_pin():
+    """28 more 16x16 crops of the full-size C4 frame rendered by the reference under the simulator (round 2: the pin grown 4x)."""
+    if not have_golden("c4_crops_b"):
+        pytest.skip("golden not generated")
+    g = load_golden("c4_crops_b")
+    tot = dict(n=0, n_bad=0, max=0)
+    for (x0, x1, y0, y1, ref) in golden_regions(g):
+        xa = (x0 // 16) * 16
+        got = _cuda(g, tile=(xa, min(int(g["W"]), xa + 32)))[:, x0:x1, y0:y1]
+        rep = parity_report(got, ref)
+        tot["n"] += rep["n"]; tot["n_bad"] += rep["n_bad"]; tot["max"] = max(tot["max"], rep["max"])
+    print("c4 crops b", tot)
+    assert tot["n_bad"] <= _budget(tot["n"]), tot
+
+
+def test_bit_stable_on_multi_stream_frame_sizes():
+    """Determinism where the launch sequence runs on several streams (S >= 64, <= 12 Mi paths: chain / shade streams) and
+    on a strip-sharded share of the full-size C4 frame: repeated renders are byte-identical."""
+    g = _synthetic(1024, 3, 1, 1024, 512, 3, False, seed=5)
+    a = _cuda(g)
+    for _ in range(3):
+        assert np.array_equal(a, _cuda(g))
+    from b200rt import render_host
+    from b200rt.workloads import workload
+    w = workload("c4"); cam = w["cameras"][0]; W, H = cam.resolution
+    sp, li, pl = w["scene"].generate_scene()
+    args = (cam.position, cam.rotation, sp, li, pl, w["amb"], w["lamb"], w["refl"], w["refl_depth"], w["aliasing"])
+    outs = [render_host(None, *args, grid=cam.grid(), shape=(W, H), strips=(16, 5, 8)) for _ in range(3)]
+    assert np.array_equal(outs[0], outs[1]) and np.array_equal(outs[0], outs[2])
+    assert outs[0][:, 80:96].any() and not outs[0][:, 0:80].any()           # only rank 5's strips were written
+
+
+@pytest.mark.parametrize("case", ["far_plane_origins", "tiny_radii", "coords_near_250", "camera_inside_sphere", "huge_and_tiny"])
+def test_filter_margin_stress_scenes(case):
+    """Scenes that stress the hand-derived margins of the conservative FFMA2 filter (isect3.cuh): the default path, the scan
+    path and brute force all run that filter, so they are compared here with B200RT_F_NO_FILTER — sphere_exact on EVERY
+    sphere, no filter at all.  A margin that is too tight would drop a hit and change a byte."""
+    from b200rt import _lib
+    from b200rt.scene import Camera
+    S, L, W, H = 400, 3, 256, 144
+    g = _synthetic(S, L, 1, W, H, 3, False, seed=23)
+    sp, li = g["spheres"], g["lights"]
+    rng = np.random.default_rng(17)
+    if case == "far_plane_origins":             # camera almost parallel to the plane: bounce / shadow origins up to ~900 units out
+        cam = Camera(resolution=(W, H), position=[-2, 0, 0.6], euler=[0, -0.05, 0])
+        g.update(grid=np.array(cam.grid()), cam_origin=cam.position, cam_rotation=cam.rotation)
+        sp[0] = rng.uniform(5, 900, S); sp[1] = rng.uniform(-60, 60, S); sp[3] = rng.uniform(0.3, 6.0, S); sp[2] = sp[3] + rng.uniform(0, 3, S)
+    elif case == "tiny_radii":
+        sp[3] = rng.uniform(1e-3, 4e-3, S); sp[2] = sp[3] + rng.uniform(0, 0.02, S)
+        sp[0] = rng.uniform(0.5, 3.0, S); sp[1] = rng.uniform(-1, 1, S)
+    elif case == "coords_near_250":             # |C| close to the light grids' coordinate range, camera and lights moved along
+        off = np.array([240.0, -230.0, 0.0], np.float32)
+        sp[0] += off[0]; sp[1] += off[1]; li[0] += off[0]; li[1] += off[1]
+        cam = Camera(resolution=(W, H), position=[-2 + 240.0, -230.0, 2.0], euler=[0, -30, 0])
+        g.update(grid=np.array(cam.grid()), cam_origin=cam.position, cam_rotation=cam.rotation)
+        for p in range(g["planes"].shape[1]):
+            g["planes"][0, p] += 240.0; g["planes"][1, p] -= 230.0
+    elif case == "camera_inside_sphere":        # the far root is taken (intersections.py:33-36) for every primary ray
+        sp[0:3, 0] = [-2.0, 0.0, 2.0]; sp[3, 0] = 6.0
+        sp[0:3, 1] = [-1.5, 0.2, 1.8]; sp[3, 1] = 0.45      # and a small sphere just in front of the camera, inside the big one
+    elif case == "huge_and_tiny":
+        sp[3, :20] = rng.uniform(20, 120, 20); sp[0, :20] = rng.uniform(100, 400, 20); sp[2, :20] = sp[3, :20] * rng.uniform(0.2, 1.0, 20)
+        sp[3, 20:200] = rng.uniform(2e-3, 1e-2, 180)
+    got = _cuda(g)
+    assert got.any()
+    exact = _cuda(g, flags=_lib.F_NO_FILTER)
+    assert np.array_equal(got, exact), (case, int((got != exact).sum()))
+    assert np.array_equal(got, _cuda(g, flags=_lib.F_DENSE)), case
+    assert np.array_equal(got, _cuda(g, flags=_lib.F_NO_SGRID)), case

@@ -1,5 +1,6 @@
 """Fuzz the exact-culling paths: random scenes (lights among the spheres, inside them, far away; clustered and huge spheres),
-default path vs brute force (B200RT_F_DENSE) must be byte-identical.  usage: python tools/gpu_fuzz.py [n_scenes]"""
+default path vs brute force (B200RT_F_DENSE), the scan path (B200RT_F_NO_SGRID) and - for S <= 700 - the exact test on every
+sphere without any filter (B200RT_F_NO_FILTER) must be byte-identical.  usage: python tools/gpu_fuzz.py [n_scenes]"""
 import os, sys
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -39,7 +40,11 @@ def check(seed):
     a = render_host(None, *args, grid=grid, shape=shape)
     b = render_host(None, *args, grid=grid, shape=shape, flags=_lib.F_DENSE)
     c = render_host(None, *args, grid=grid, shape=shape, flags=_lib.F_NO_SGRID)
-    return np.array_equal(a, b) and np.array_equal(a, c), desc, int(a.sum()), int((a != b).sum()), int((a != c).sum())
+    # a, b and c all run the conservative FFMA2 filter; B200RT_F_NO_FILTER runs sphere_exact on every sphere (scalar debug
+    # kernel, slow: S <= 700 only) and is the check that the filter's margins never drop a hit
+    d = render_host(None, *args, grid=grid, shape=shape, flags=_lib.F_NO_FILTER) if args[2].shape[1] <= 700 else a
+    return (np.array_equal(a, b) and np.array_equal(a, c) and np.array_equal(a, d), desc, int(a.sum()), int((a != b).sum()),
+            int((a != c).sum()) + int((a != d).sum()))
 
 
 if __name__ == "__main__":
