@@ -153,6 +153,16 @@ B200RT_API int b200rt_to_image_host(int device, const uint8_t* planar, uint8_t* 
 #define B200RT_NOALLOC_MAX_PIXELS (1 << 20)   /* 1024 x 1024; the reference's main.py frame is 1000 x 1000 (src/main.py:10) */
 B200RT_API int b200rt_to_image_host_noalloc(int device, const uint8_t* planar, uint8_t* rgb, int W, int H, uint32_t flags);
 
+/* Page-locked host memory for the framebuffer: the destination of `result.copy_to_host()` (reference src/main.py:51; numba's
+ * counterpart of b200rt_alloc_host is cuda.pinned_array).  b200rt_render_host / _batch_host copy into whatever `result`
+ * points at; when that memory is pinned the copy is one DMA at PCIe rate.  b200rt_host_register pins memory the caller
+ * owns, e.g. a shared-memory mapping of the (3,W,H) frame that the ranks of a multi-GPU job copy their strips into — the
+ * "direct device-to-host gather" of the tiles (north_star).  CUDA runtime must be usable (a GPU present). */
+B200RT_API int b200rt_alloc_host(size_t bytes, void** out);
+B200RT_API int b200rt_free_host(void* p);
+B200RT_API int b200rt_host_register(void* p, size_t bytes);
+B200RT_API int b200rt_host_unregister(void* p);
+
 B200RT_API int b200rt_device_count(void);
 B200RT_API int b200rt_sm_count(int device);
 /* Kernels launched by this library since it was loaded (host-side count, all devices and threads): the difference

@@ -63,6 +63,10 @@ def lib():
         L.b200rt_to_image.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint32]; L.b200rt_to_image.restype = C.c_int
         L.b200rt_to_image_host.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint32]; L.b200rt_to_image_host.restype = C.c_int
         L.b200rt_to_image_host_noalloc.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint32]; L.b200rt_to_image_host_noalloc.restype = C.c_int
+        L.b200rt_alloc_host.argtypes = [C.c_size_t, C.POINTER(C.c_void_p)]; L.b200rt_alloc_host.restype = C.c_int
+        L.b200rt_free_host.argtypes = [C.c_void_p]; L.b200rt_free_host.restype = C.c_int
+        L.b200rt_host_register.argtypes = [C.c_void_p, C.c_size_t]; L.b200rt_host_register.restype = C.c_int
+        L.b200rt_host_unregister.argtypes = [C.c_void_p]; L.b200rt_host_unregister.restype = C.c_int
         L.b200rt_device_count.restype = C.c_int
         L.b200rt_sm_count.argtypes = [C.c_int]; L.b200rt_sm_count.restype = C.c_int
         L.b200rt_launch_count.restype = C.c_ulonglong

@@ -112,5 +112,38 @@ def device_array(shape, dtype=np.float64, device=None):
     return DeviceArray(torch.zeros(tuple(shape), dtype=tdt, device=f"cuda:{dev}"), shape=shape, dtype=dtype, device=dev)
 
 
+class _PinnedOwner:
+    """Frees a b200rt_alloc_host block when the last numpy view of it goes away."""
+
+    def __init__(self, ptr, nbytes):
+        self.ptr, self.nbytes = ptr, nbytes
+
+    def __del__(self):
+        try:
+            from . import _lib
+            _lib.lib().b200rt_free_host(self.ptr)
+        except Exception:
+            pass
+
+
+def pinned_array(shape, dtype=np.float64):
+    """numba.cuda.pinned_array equivalent: a page-locked host ndarray (b200rt_alloc_host).  Passing one as `out=` of
+    render_host / render_frame / render_batch makes the framebuffer's device-to-host copy a single DMA (reference
+    src/main.py:51 `result.copy_to_host()`); allocate it once and reuse it across frames (pinning 100 MB costs tens of ms)."""
+    import ctypes as C
+    from . import _lib
+    shape = (int(shape),) if np.isscalar(shape) else tuple(int(v) for v in shape)
+    dt = np.dtype(dtype)
+    nbytes = max(1, int(np.prod(shape)) * dt.itemsize)
+    p = C.c_void_p()
+    _lib.check(_lib.lib().b200rt_alloc_host(nbytes, C.byref(p)))
+    owner = _PinnedOwner(p.value, nbytes)
+    buf = (C.c_uint8 * nbytes).from_address(p.value)
+    buf._owner = owner                                   # the ctypes buffer keeps the block alive; numpy keeps the buffer
+    arr = np.frombuffer(buf, dtype=dt, count=int(np.prod(shape))).reshape(shape)
+    arr[...] = 0
+    return arr
+
+
 def synchronize():
     _torch().cuda.synchronize()

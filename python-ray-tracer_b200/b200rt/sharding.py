@@ -68,3 +68,40 @@ def allgather_frame(result, rank, world, strip=DEFAULT_STRIP, group=None):
         if r != rank:
             result.index_copy_(1, cols[r], parts[r][:, :len(cols[r]), :])
     return result
+
+
+class SharedFrame:
+    """One (3,W,H) uint8 host frame shared by the ranks of a multi-GPU job: the direct device-to-host gather of SURVEY
+    §8(e) across PROCESSES.  Every rank maps the same /dev/shm file and pins the mapping (b200rt_host_register); its
+    b200rt_render_host call then copies its strips straight into the frame, so after a barrier the creating rank (and
+    every other) holds the assembled frame — the `result.copy_to_host()` of reference src/main.py:51 for N GPUs, with no
+    extra copy and no collective.
+
+        fr = SharedFrame(name, W, H, create=(rank == 0)); barrier()         # rank 0 creates, then everyone attaches
+        render_host(..., out=fr.array, strips=(16, rank, world)); barrier()  # fr.array is now the whole frame
+    """
+
+    def __init__(self, name, W, H, create, pin=True, directory="/dev/shm"):
+        import os
+        self.path = os.path.join(directory, name)
+        self.created = bool(create)
+        n = 3 * int(W) * int(H)
+        if create:
+            with open(self.path, "wb") as f:
+                f.truncate(n)
+        self.array = np.memmap(self.path, dtype=np.uint8, mode="r+", shape=(3, int(W), int(H)))
+        self.pinned = False
+        if pin:
+            from . import _lib
+            _lib.check(_lib.lib().b200rt_host_register(self.array.ctypes.data, n))
+            self.pinned = True
+
+    def close(self):
+        import os
+        if self.pinned:
+            from . import _lib
+            _lib.lib().b200rt_host_unregister(self.array.ctypes.data)
+            self.pinned = False
+        self.array = None
+        if self.created and os.path.exists(self.path):
+            os.unlink(self.path)

@@ -1578,6 +1578,27 @@ B200RT_API int b200rt_to_image_host_noalloc(int device, const uint8_t* planar, u
     return 0;
 }
 
+// Page-locked host memory for the framebuffer (the destination of `result.copy_to_host()`, reference src/main.py:51; numba's
+// counterpart is cuda.pinned_array): a D2H copy into pinned memory is one DMA at PCIe rate (~52 GB/s measured for the 99.5 MB
+// C4 frame), into pageable memory it is staged through a driver bounce buffer at a fraction of that.
+B200RT_API int b200rt_alloc_host(size_t bytes, void** out) {
+    if (!out) return fail(B200RT_E_NULL, "out is NULL");
+    *out = nullptr;
+    if (bytes == 0) return fail(B200RT_E_SHAPE, "bytes must be positive");
+    CK(cudaHostAlloc(out, bytes, cudaHostAllocPortable));
+    return 0;
+}
+B200RT_API int b200rt_free_host(void* p) { if (p) CK(cudaFreeHost(p)); return 0; }
+// Pin memory the caller already owns (a numpy array, a shared-memory mapping that several ranks D2H their strips into: the
+// "direct device-to-host gather" of SURVEY §8(e)).  The range stays pinned until b200rt_host_unregister.
+B200RT_API int b200rt_host_register(void* p, size_t bytes) {
+    if (!p) return fail(B200RT_E_NULL, "pointer is NULL");
+    if (bytes == 0) return fail(B200RT_E_SHAPE, "bytes must be positive");
+    CK(cudaHostRegister(p, bytes, cudaHostRegisterPortable));
+    return 0;
+}
+B200RT_API int b200rt_host_unregister(void* p) { if (p) CK(cudaHostUnregister(p)); return 0; }
+
 B200RT_API int b200rt_shutdown(void) {
     int ndev = b200rt_device_count();
     for (int dev = 0; dev < ndev && dev < kMaxDevices; ++dev) {

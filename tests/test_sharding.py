@@ -113,3 +113,20 @@ def test_multi_device_frame_equals_single_device():
     n = torch.cuda.device_count()
     devs = list(range(n)) if n > 1 else [0, 0]           # one GPU: two host threads share the device (serialised by the library)
     assert np.array_equal(render_frame(scene, cam, 0.0, 0.6, 0.3, 2, True, devices=devs), one)
+
+
+def test_shared_frame_assembles_strips_across_mappings(tmp_path):
+    """SharedFrame without pinning (no GPU here): two mappings of one /dev/shm-style file, each 'rank' writes its strips,
+    the creator sees the assembled frame (the multi-process direct device-to-host gather of bench.py --gpus N)."""
+    from b200rt.sharding import SharedFrame, columns_of_rank
+    W, H = 100, 24
+    whole = np.random.default_rng(0).integers(0, 256, (3, W, H), dtype=np.uint8)
+    a = SharedFrame("frame_test", W, H, create=True, pin=False, directory=str(tmp_path))
+    b = SharedFrame("frame_test", W, H, create=False, pin=False, directory=str(tmp_path))
+    for rank, fr in enumerate((a, b)):
+        cols = columns_of_rank(W, rank, 2, 16)
+        fr.array[:, cols, :] = whole[:, cols, :]
+    assert np.array_equal(np.asarray(a.array), whole)
+    b.close(); a.close()
+    import os
+    assert not os.path.exists(os.path.join(str(tmp_path), "frame_test"))
