@@ -50,6 +50,8 @@ extern "C" {
 #define B200RT_F_TIME_ONLY       0x20u /* with `stats`: fill the ray counts and the per-class device times but run the production kernels (no executed-work counters: slow_path, exact_tests, tests_*, and with the light grids shadow_traced, stay 0) */
 #define B200RT_F_DENSE           0x40u /* brute force as the reference specifies it: every query (shadow queries of unlit pairs included) scans every sphere - no beam culling, regrouping, shadow passes or lit-pair lists; the image is the same.  The FP32-peak figure of bench.py is measured in this mode */
 #define B200RT_F_NO_SGRID        0x80u /* shadow queries scan the light's sphere table (k_isect3, passes + beam culling) instead of looking up the light's direction grid; the image is the same */
+#define B200RT_F_NO_GRAPH        0x100u /* launch the frame's kernels one by one instead of replaying the captured CUDA graph of the sequence (A/B, debugging); the image is the same */
+#define B200RT_F_NO_CACHE        0x200u /* rebuild every scene-derived table in this call (the resident-scene tables are normally rebuilt only when the scene arrays change); implies NO_GRAPH; the image is the same */
 #define B200RT_F_NO_SORT         0x10u /* bounce-depth hits stay in pixel order (no regrouping by direction/position bin); the image is the same */
 
 /*
@@ -168,6 +170,9 @@ B200RT_API int b200rt_sm_count(int device);
 /* Kernels launched by this library since it was loaded (host-side count, all devices and threads): the difference
  * across a timed region is the measured `gpu_launches` of bench.py. */
 B200RT_API unsigned long long b200rt_launch_count(void);
+/* Frames on `device` that were replayed from a captured CUDA graph of their launch sequence (diagnostic; the second call with
+ * the same shapes / buffers / flags captures, later ones replay; the camera pose is not part of the key). */
+B200RT_API unsigned long long b200rt_graph_replays(int device);
 /* Free the per-device scratch (packed scene, ray queues).  Safe to call at any time between renders. */
 B200RT_API int b200rt_shutdown(void);
 

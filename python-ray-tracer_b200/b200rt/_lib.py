@@ -6,6 +6,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200rt.so")
 
 F_SCENE_ON_HOST, F_NO_FILTER, F_UNSWAP_GB, F_NO_CULL, F_NO_SORT, F_TIME_ONLY, F_DENSE, F_NO_SGRID = 0x1, 0x2, 0x4, 0x8, 0x10, 0x20, 0x40, 0x80
+F_NO_GRAPH, F_NO_CACHE = 0x100, 0x200
 
 
 class Grid(C.Structure):
@@ -70,6 +71,7 @@ def lib():
         L.b200rt_device_count.restype = C.c_int
         L.b200rt_sm_count.argtypes = [C.c_int]; L.b200rt_sm_count.restype = C.c_int
         L.b200rt_launch_count.restype = C.c_ulonglong
+        L.b200rt_graph_replays.argtypes = [C.c_int]; L.b200rt_graph_replays.restype = C.c_ulonglong
         L.b200rt_shutdown.restype = C.c_int
         if L.b200rt_args_size() != C.sizeof(Args):
             raise ImportError("b200rt_args layout mismatch between _lib.py and libb200rt.so")

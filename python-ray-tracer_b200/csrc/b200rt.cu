@@ -29,12 +29,63 @@
 
 namespace b200rt {
 
+// ------------------------------------------------------------------------------------------------
+// Resident scene.  Everything that depends only on the scene arrays (packed float4 tables, the lights' solid-angle orders,
+// the Morton order and cluster bounds of the closest-hit tables, the pivot tables of the lights and the origin-free table, the
+// lights' direction grids, the bounding box of the regrouping) is kept on the device between calls and rebuilt only when
+// the scene changes.  "Changes" is decided ON THE DEVICE, so it holds for device-resident scene arrays too and the launch
+// sequence of a frame is the same whether or not anything is rebuilt (it can be captured in a CUDA graph): k_scene_cmp
+// compares the caller's arrays bit for bit with the copy of the arrays the tables were built from and bumps a version
+// counter when they differ; every builder kernel returns at once when its table group already carries that version, and
+// k_cache_commit stamps the groups built in this call.  Only the camera pivot table (k_pivot, j == L) is per frame.
+//   cs[0] scene version   cs[1..3] version the groups {base tables, light grids, regrouping box} were built from
+//   cs[4] key of the regrouping box (position bits, direction cells)   cs[5..7] S, L, Pl of the saved copy   cs[8] CTA ticket
+// ------------------------------------------------------------------------------------------------
+enum { kCsVersion = 0, kCsBase = 1, kCsSgrid = 2, kCsGrid = 3, kCsGridKey = 4, kCsS = 5, kCsL = 6, kCsPl = 7, kCsTicket = 8, kCsWords = 16 };
+
+__global__ void __launch_bounds__(256) k_scene_cmp(const float* __restrict__ spheres, int S, const float* __restrict__ lights, int L,
+                                                  const float* __restrict__ planes, int Pl, uint32_t* saved, uint32_t* cs, float* cmax) {
+    __shared__ int s_diff, s_last;
+    const int nS = 7 * S, nL = 3 * L, n = nS + nL + 9 * Pl;
+    if (threadIdx.x == 0) s_diff = (cs[kCsS] != (uint32_t)S || cs[kCsL] != (uint32_t)L || cs[kCsPl] != (uint32_t)Pl) ? 1 : 0;
+    __syncthreads();
+    bool diff = false;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float v = i < nS ? spheres[i] : (i < nS + nL ? lights[i - nS] : planes[i - nS - nL]);
+        const uint32_t b = __float_as_uint(v);
+        if (saved[i] != b) { saved[i] = b; diff = true; }            // compare and update in one pass (bit patterns: NaNs and -0 count)
+    }
+    if (__syncthreads_or(diff ? 1 : 0) && threadIdx.x == 0) s_diff = 1;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        if (s_diff) atomicOr(&cs[kCsTicket], 0x80000000u);
+        __threadfence();
+        const uint32_t t = atomicAdd(&cs[kCsTicket], 1u);
+        s_last = ((t & 0x7fffffffu) == gridDim.x - 1) ? 1 : 0;
+        if (s_last) {                                                 // last CTA: publish
+            __threadfence();
+            const uint32_t all = atomicExch(&cs[kCsTicket], 0u);
+            if (all & 0x80000000u) { cs[kCsVersion] += 1u; cs[kCsS] = (uint32_t)S; cs[kCsL] = (uint32_t)L; cs[kCsPl] = (uint32_t)Pl; }
+            // k_pack's atomicMax bounds start from zero when (and only when) the base tables are about to be rebuilt
+            if (cs[kCsBase] != cs[kCsVersion]) { cmax[0] = 0.f; cmax[1] = 0.f; }
+        }
+    }
+}
+__global__ void k_cache_commit(uint32_t* cs, int base, int sgrid, int grid, uint32_t gridkey) {
+    const uint32_t v = cs[kCsVersion];
+    if (base) cs[kCsBase] = v;
+    if (sgrid) cs[kCsSgrid] = v;
+    if (grid) { cs[kCsGrid] = v; cs[kCsGridKey] = gridkey; }
+}
+__device__ __forceinline__ bool cache_fresh(const uint32_t* cs, int group) { return cs[group] == cs[kCsVersion]; }
+
 // (7,S) / (9,Pl) / (3,L) float32 SoA  ->  packed float4 arrays.  One thread per object.
 __global__ void k_pack(const float* __restrict__ spheres, int S, int Spad,
                        const float* __restrict__ planes, int Pl,
                        const float* __restrict__ lights, int L,
                        float4* sphA, float4* sphB, float4* sphCol,
-                       float4* plO, float4* plN, float4* plNu, float4* plCol, float4* lightsOut, float* cmax) {
+                       float4* plO, float4* plN, float4* plNu, float4* plCol, float4* lightsOut, float* cmax, const uint32_t* cs) {
+    if (cache_fresh(cs, kCsBase)) return;
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < Spad) {
         if (i < S) {
@@ -66,11 +117,17 @@ __global__ void k_pack(const float* __restrict__ spheres, int S, int Spad,
 // ------------------------------------------------------------------------------------------------
 // Frame / tile description shared by k_raygen and k_resolve
 // ------------------------------------------------------------------------------------------------
-struct FrameDev {
-    const double* pixel_loc;       // (3,W,H) or nullptr
+// Per-frame camera: read through a device pointer so that a captured launch sequence (CUDA graph) can be replayed for a new
+// camera pose by updating this block alone.
+struct CamDev {
     double gf, gar, gsy, gsz;      // affine grid (camera.py:18-26)
     double ox, oy, oz;             // camera origin
     double rot[9];                 // camera rotation, row-major
+    float cox, coy, coz, pad;      // camera origin rounded to float32 (pivot of the primary rays)
+};
+struct FrameDev {
+    const double* pixel_loc;       // (3,W,H) or nullptr
+    const CamDev* cam;
     int W, H;
     int x0, x1;                    // chunk LOCAL columns [x0, x1) (local = index among the columns this call renders)
     int xb;                        // tile origin: global x of local column 0
@@ -99,11 +156,11 @@ __device__ __forceinline__ void slot_pixel(const FrameDev& f, uint32_t p, int& l
 
 // pixel_loc[c, x, y] with the GPU's unchecked C-order flat addressing: elements past the end
 // of the buffer are defined as 0.0.
-__device__ __forceinline__ double pl_at(const FrameDev& f, int c, int x, int y) {
+__device__ __forceinline__ double pl_at(const FrameDev& f, const CamDev& cm, int c, int x, int y) {
     if (!f.pixel_loc && x >= 0 && x < f.W && y >= 0 && y < f.H) {           // in-range element of the closed-form grid: no 64-bit divisions
-        if (c == 0) return f.gf;
-        if (c == 1) return __dadd_rn(__dmul_rn((double)x, f.gsy), f.gar);
-        return __dadd_rn(__dmul_rn((double)y, f.gsz), 1.0);
+        if (c == 0) return cm.gf;
+        if (c == 1) return __dadd_rn(__dmul_rn((double)x, cm.gsy), cm.gar);
+        return __dadd_rn(__dmul_rn((double)y, cm.gsz), 1.0);
     }
     const long long W = f.W, H = f.H;
     long long flat = (long long)c * W * H + (long long)x * H + y;
@@ -111,9 +168,9 @@ __device__ __forceinline__ double pl_at(const FrameDev& f, int c, int x, int y) 
     if (f.pixel_loc) return f.pixel_loc[flat];
     int cc = (int)(flat / (W * H)); long long rem = flat - (long long)cc * W * H;
     int xx = (int)(rem / H), yy = (int)(rem - (long long)xx * H);
-    if (cc == 0) return f.gf;
-    if (cc == 1) return __dadd_rn(__dmul_rn((double)xx, f.gsy), f.gar);
-    return __dadd_rn(__dmul_rn((double)yy, f.gsz), 1.0);
+    if (cc == 0) return cm.gf;
+    if (cc == 1) return __dadd_rn(__dmul_rn((double)xx, cm.gsy), cm.gar);
+    return __dadd_rn(__dmul_rn((double)yy, cm.gsz), 1.0);
 }
 
 
@@ -131,6 +188,10 @@ __global__ void k_raygen(FrameDev f, float4* __restrict__ rayO, float4* __restri
     const uint32_t nslots = f.npix * (uint32_t)f.ns;
     const uint32_t nchunks = (nslots + 255u) / 256u;
     __shared__ uint32_t s_chunk;
+    __shared__ CamDev s_cam;
+    if (threadIdx.x < sizeof(CamDev) / 8) reinterpret_cast<double*>(&s_cam)[threadIdx.x] = reinterpret_cast<const double*>(f.cam)[threadIdx.x];
+    __syncthreads();
+    const CamDev& cm = s_cam;
     for (uint32_t it = blockIdx.x;; it += gridDim.x) {
         uint32_t c = it;
         if (f.ns > 1) {
@@ -148,20 +209,20 @@ __global__ void k_raygen(FrameDev f, float4* __restrict__ rayO, float4* __restri
             int x = col_x(f, f.x0 + lc);
             if (k > 0 && !(x >= 1 && y >= 1)) valid = false;          // kernels.py:29
             if (valid) {
-                double px = pl_at(f, 0, x, y), py = pl_at(f, 1, x, y), pz = pl_at(f, 2, x, y);
+                double px = pl_at(f, cm, 0, x, y), py = pl_at(f, cm, 1, x, y), pz = pl_at(f, cm, 2, x, y);
                 if (k > 0) {                                          // kernels.py:43-50  0.5*P + 0.5*P'
                     int xn = x + c_dx[k], yn = y + c_dy[k];
-                    px = __dadd_rn(__dmul_rn(0.5, px), __dmul_rn(0.5, pl_at(f, 0, xn, yn)));
-                    py = __dadd_rn(__dmul_rn(0.5, py), __dmul_rn(0.5, pl_at(f, 1, xn, yn)));
-                    pz = __dadd_rn(__dmul_rn(0.5, pz), __dmul_rn(0.5, pl_at(f, 2, xn, yn)));
+                    px = __dadd_rn(__dmul_rn(0.5, px), __dmul_rn(0.5, pl_at(f, cm, 0, xn, yn)));
+                    py = __dadd_rn(__dmul_rn(0.5, py), __dmul_rn(0.5, pl_at(f, cm, 1, xn, yn)));
+                    pz = __dadd_rn(__dmul_rn(0.5, pz), __dmul_rn(0.5, pl_at(f, cm, 2, xn, yn)));
                 }
                 // matmul (common.py:40-49) then normalize (common.py:28-32), float64
-                double bx = f.rot[0] * px + f.rot[1] * py + f.rot[2] * pz;
-                double by = f.rot[3] * px + f.rot[4] * py + f.rot[5] * pz;
-                double bz = f.rot[6] * px + f.rot[7] * py + f.rot[8] * pz;
+                double bx = cm.rot[0] * px + cm.rot[1] * py + cm.rot[2] * pz;
+                double by = cm.rot[3] * px + cm.rot[4] * py + cm.rot[5] * pz;
+                double bz = cm.rot[6] * px + cm.rot[7] * py + cm.rot[8] * pz;
                 double n = sqrt(bx * bx + by * by + bz * bz);
                 d = make_float4((float)(bx / n), (float)(by / n), (float)(bz / n), 0.f);
-                o = make_float4((float)f.ox, (float)f.oy, (float)f.oz, __uint_as_float(slot));
+                o = make_float4((float)cm.ox, (float)cm.oy, (float)cm.oz, __uint_as_float(slot));
             }
         }
         uint32_t pos = slot;
@@ -320,7 +381,8 @@ k_intersect(SceneDev sc, QueueDev q) {
 // (C4: half of all shadow rays are occluded, 90 % of those by one of the first 120-350 spheres of 1024).  Any order
 // gives the same image: a shadow query only asks WHETHER something is hit (trace.py:92-96).  One thread per
 // (light j, sphere s): rank by counting (S is a few thousand at most); padding entries go last.
-__global__ void __launch_bounds__(256) k_rank(SceneDev sc, int* perm) {
+__global__ void __launch_bounds__(256) k_rank(SceneDev sc, int* perm, const uint32_t* cs) {
+    if (cache_fresh(cs, kCsBase)) return;
     // grid = (ceil(Spad / 256), L); the keys of 1024 spheres at a time go through shared memory (one division per key
     // per CTA instead of one per comparison)
     __shared__ float skey[1024];
@@ -352,7 +414,8 @@ __device__ __forceinline__ uint32_t morton10(uint32_t v) {          // spread th
     v &= 1023u; v = (v | (v << 16)) & 0x030000ffu; v = (v | (v << 8)) & 0x0300f00fu; v = (v | (v << 4)) & 0x030c30c3u; v = (v | (v << 2)) & 0x09249249u;
     return v;
 }
-__global__ void __launch_bounds__(256) k_mrank(SceneDev sc, int* perm) {
+__global__ void __launch_bounds__(256) k_mrank(SceneDev sc, int* perm, const uint32_t* cs) {
+    if (cache_fresh(cs, kCsBase)) return;
     __shared__ uint32_t skey[1024];
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     const float cm = fmaxf(sc.cmax[0], 1e-20f);
@@ -377,7 +440,8 @@ __global__ void __launch_bounds__(256) k_mrank(SceneDev sc, int* perm) {
 }
 // One thread per cluster of 64 consecutive positions of the closest-hit tables: bounding sphere (centre = mean of the
 // centres, radius = max |C - centre| + r, rounded up); a cluster of padding only gets radius -1 (never kept).
-__global__ void __launch_bounds__(64) k_clus(SceneDev sc, const int* perm, float4* clus) {
+__global__ void __launch_bounds__(64) k_clus(SceneDev sc, const int* perm, float4* clus, const uint32_t* cs) {
+    if (cache_fresh(cs, kCsBase)) return;
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c * 64 >= sc.Spad) return;
     const int* pr = perm + (size_t)sc.L * sc.Spad;
@@ -396,13 +460,15 @@ __global__ void __launch_bounds__(64) k_clus(SceneDev sc, const int* perm, float
 
 // One thread per (table j, pair i of table positions): k = r^2 - |C-V_j|^2 (j <= L) or r^2 - |C|^2 (j == L+1), float64
 // rounded once.  Light tables (j < L) are in k_rank's order, the two closest-hit tables in array order (ids matter there).
-__global__ void k_pivot(SceneDev sc, float cox, float coy, float coz, const int* perm, float4* tab, float4* piv, float* rad) {
+// The camera's table (j == L) is rebuilt every frame, the others only with the scene.
+__global__ void k_pivot(SceneDev sc, const CamDev* cam, const int* perm, float4* tab, float4* piv, float* rad, const uint32_t* cs) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     const int npair = sc.Spad / 2;
     const int j = idx / npair, i = idx - j * npair;
     if (j > sc.L + 1) return;
+    if (j != sc.L && cache_fresh(cs, kCsBase)) return;
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (j < sc.L) v = sc.lights[j]; else if (j == sc.L) v = make_float4(cox, coy, coz, 0.f);
+    if (j < sc.L) v = sc.lights[j]; else if (j == sc.L) v = make_float4(cam->cox, cam->coy, cam->coz, 0.f);
     if (i == 0 && j <= sc.L) piv[j] = v;
     float c[2][4];
 #pragma unroll
@@ -441,7 +507,8 @@ struct SortDev {
 };
 
 // Bounding box of the spheres -> position grid with 2^posbits cells, bits handed to the axis with the largest cell.
-__global__ void __launch_bounds__(256) k_grid(SceneDev sc, int posbits, int dn, GridDev* g) {
+__global__ void __launch_bounds__(256) k_grid(SceneDev sc, int posbits, int dn, GridDev* g, const uint32_t* cs, uint32_t gridkey) {
+    if (cache_fresh(cs, kCsGrid) && cs[kCsGridKey] == gridkey) return;
     __shared__ float smin[3][256], smax[3][256];
     float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f};
     for (int i = threadIdx.x; i < sc.S; i += blockDim.x) {
@@ -582,7 +649,7 @@ struct ShadeDev {
     float4* rayO2; float4* rayD2; unsigned long long* hit2;   // next depth's ray queue (k_setup output; hit2 pre-set to "no hit")
     float4* hP; float4* hN;              // hit records: (biased P, slot) (N, id)
     uint8_t* occl; size_t ocap;          // [light][hit], row stride ocap (zeroed by k_setup, set by the shadow query)
-    float* accR; float* accG; float* accB;   // per-slot colour accumulators
+    float4* acc;                         // per-slot colour accumulators (R, G, B, -): one 16-byte read-modify-write per hit
     const uint32_t* n_live;              // rays in the queue (k_setup input)
     uint32_t* n_hit;                     // hit records (k_setup output, k_shade input)
     uint32_t* shidx; size_t shcap; uint32_t* n_sh;   // per light: list of hit records to shadow-test, and its length (k_setup output)
@@ -627,7 +694,8 @@ __global__ void __launch_bounds__(256, B200RT_SETUP_OCC) k_setup(SceneDev sc, Sh
         // One multi-queue append per pass: queue 0 = the hit list (first pass), the others = lights' lists
         // (n_hit and n_sh[] are adjacent counters).
         uint32_t h = 0;
-        if (!s.shidx) { uint32_t pos[8]; ordered_append8(hit ? 1u : 0u, 1, c, s.ostat, s.n_hit, is_last, pos); h = pos[0]; }   // dense shadow layout: hit list only
+        if (!s.shidx && s.perm) { h = i; if (is_last && threadIdx.x == 0) *s.n_hit = n; }            // regrouped: the permutation lists hits only, in their final order
+        else if (!s.shidx) { uint32_t pos[8]; ordered_append8(hit ? 1u : 0u, 1, c, s.ostat, s.n_hit, is_last, pos); h = pos[0]; }   // dense shadow layout: hit list only
         else for (int j0 = 0, first = 1, pass = 0; first || j0 < sc.L; first = 0, ++pass) {
             const int nl = min(first ? 7 : 8, sc.L - j0), sh = first ? 1 : 0;
             uint32_t flags = (first && hit) ? 1u : 0u;
@@ -671,6 +739,41 @@ __global__ void __launch_bounds__(256, B200RT_SETUP_OCC) k_setup(SceneDev sc, Sh
     if (s.tl && threadIdx.x == 0) atomicMax(s.tl + 1, globaltimer_ns());
 }
 
+// k_setup for regrouped depths on the light-grid path.  The counting sort already gives every hit its position in bin order
+// (base[bin] + rank within the bin, k_key / k_binscan), and that position IS its index in the compacted hit list = next ray queue
+// (misses have no bin and are not counted).  So the queue is read in its own order — coalesced — and the records are scattered to
+// their final positions: no permutation array, no gather through it, no ordered compaction (nothing to compact).  Arithmetic as k_setup.
+__global__ void __launch_bounds__(256, B200RT_SETUP_OCC) k_setup_scatter(SceneDev sc, ShadeDev s, const uint2* __restrict__ keyb, const uint32_t* __restrict__ base,
+                                                                         const uint32_t* __restrict__ n_sorted) {
+    if (s.tl && threadIdx.x == 0) atomicMin(s.tl, globaltimer_ns());
+    const uint32_t n = *s.n_live;
+    if (blockIdx.x == 0 && threadIdx.x == 0) *s.n_hit = *n_sorted;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint2 kb = keyb[i];
+        if (kb.x == 0xffffffffu) continue;                                           // miss: the path ends (trace.py:56-58)
+        const unsigned long long key = s.hit[i]; const float4 o = s.rayO[i], d = s.rayD[i];
+        const uint32_t h = base[kb.x] + kb.y;
+        const int id = (int)(uint32_t)key; const float t = __uint_as_float((uint32_t)(key >> 32));
+        V3 N;
+        const V3 P = madd3(mk(o.x, o.y, o.z), t, mk(d.x, d.y, d.z));                 // trace.py:60
+        if (id < sc.S) { const float4 c = __ldg(&sc.sphB[id]); N = normalize3(sub3(P, mk(c.x, c.y, c.z))); }   // common.py:94-101
+        else           { const float4 nu = __ldg(&sc.plNu[id - sc.S]); N = mk(nu.x, nu.y, nu.z); }             // common.py:104-110
+        const V3 Pb = madd3(P, kBias, N);                                            // trace.py:82-83
+        s.hP[h] = make_float4(Pb.x, Pb.y, Pb.z, o.w);
+        s.hN[h] = make_float4(N.x, N.y, N.z, __int_as_float(id));
+        if (s.emit_reflection) {
+            const V3 D = mk(d.x, d.y, d.z);
+            const float dn = dot3(D, N);
+            const V3 R = normalize3(madd3(D, -2.0f * dn, N));                        // common.py:113-120
+            const V3 O2 = madd3(Pb, kBias, R);                                       // trace.py:110
+            s.rayO2[h] = make_float4(O2.x, O2.y, O2.z, o.w);
+            s.rayD2[h] = make_float4(R.x, R.y, R.z, 0.f);
+            if (s.hit2) s.hit2[h] = kNoHit;
+        }
+    }
+    if (s.tl && threadIdx.x == 0) atomicMax(s.tl + 1, globaltimer_ns());
+}
+
 // trace.py:77,86-102 and the accumulate of trace.py:131: RGB_trace = amb*col + sum_j [visible_j && k_j>0] k_j*col,
 // acc[slot] += weight * RGB_trace.  (The reflection ray of trace.py:104-110 was queued by k_setup.)
 __global__ void __launch_bounds__(256, B200RT_SHADE_OCC) k_shade(SceneDev sc, ShadeDev s) {
@@ -682,7 +785,7 @@ __global__ void __launch_bounds__(256, B200RT_SHADE_OCC) k_shade(SceneDev sc, Sh
         // query is only looked at when k > 0 fails first, so reading it early is harmless).
         const float4 p = s.hP[h], nn = s.hN[h];
         const uint32_t slot = __float_as_uint(p.w);
-        const float ar = s.accR[slot], ag = s.accG[slot], ab = s.accB[slot];
+        const float4 a0 = s.acc[slot]; const float ar = a0.x, ag = a0.y, ab = a0.z;
         uint32_t occ8 = 0;
 #pragma unroll
         for (int j = 0; j < 8; ++j) if (j < sc.L && s.occl[(size_t)j * s.ocap + h]) occ8 |= 1u << j;
@@ -699,9 +802,7 @@ __global__ void __launch_bounds__(256, B200RT_SHADE_OCC) k_shade(SceneDev sc, Sh
             if (!(k > 0.f)) continue;                                                                  // :101
             r = fmaf(k, col.x, r); g = fmaf(k, col.y, g); b = fmaf(k, col.z, b);                       // :102
         }
-        s.accR[slot] = fmaf(s.weight, r, ar);                                                          // :131
-        s.accG[slot] = fmaf(s.weight, g, ag);
-        s.accB[slot] = fmaf(s.weight, b, ab);
+        s.acc[slot] = make_float4(fmaf(s.weight, r, ar), fmaf(s.weight, g, ag), fmaf(s.weight, b, ab), 0.f);      // :131
     }
     if (s.tl && threadIdx.x == 0) atomicMax(s.tl + 1, globaltimer_ns());
 }
@@ -709,8 +810,7 @@ __global__ void __launch_bounds__(256, B200RT_SHADE_OCC) k_shade(SceneDev sc, Sh
 // kernels.py:58-73: sum the samples in reference order with the G/B cross-wiring (F6), /9, quantise with
 // round-half-even, swap G/B on output (F5), and store VEC pixels (consecutive y = contiguous bytes) per thread.
 template <int VEC>
-__global__ void k_resolve(FrameDev f, const float* __restrict__ accR, const float* __restrict__ accG,
-                          const float* __restrict__ accB, uint8_t* __restrict__ result, int aliasing, int unswap) {
+__global__ void k_resolve(FrameDev f, const float4* __restrict__ acc, uint8_t* __restrict__ result, int aliasing, int unswap) {
     const uint32_t nvec = f.npix / VEC;
     const size_t WH = (size_t)f.W * f.H;
     for (uint32_t v = blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += gridDim.x * blockDim.x) {
@@ -720,11 +820,12 @@ __global__ void k_resolve(FrameDev f, const float* __restrict__ accR, const floa
             const uint32_t p = v * VEC + e;
             int lc, y; slot_pixel(f, p, lc, y);
             const int x = col_x(f, f.x0 + lc);
-            float R = accR[p], G = accG[p], B = accB[p];
+            const float4 a0 = acc[p]; float R = a0.x, G = a0.y, B = a0.z;
             if (aliasing && x >= 1 && y >= 1) {                                        // kernels.py:29
                 for (int k = 1; k < 9; ++k) {
                     const size_t sl = (size_t)k * f.npix + p;
-                    R = __fadd_rn(R, accR[sl]); G = __fadd_rn(G, accB[sl]); B = __fadd_rn(B, accG[sl]);   // :58-60
+                    const float4 ak = acc[sl];
+                    R = __fadd_rn(R, ak.x); G = __fadd_rn(G, ak.z); B = __fadd_rn(B, ak.y);               // :58-60 (G += B_s, B += G_s)
                 }
                 R = __fdiv_rn(R, 9.0f); G = __fdiv_rn(G, 9.0f); B = __fdiv_rn(B, 9.0f);                  // :63-65
             }
@@ -868,10 +969,13 @@ static int cuda_fail(cudaError_t e, const char* what) {
 
 namespace {
 
+std::atomic<unsigned long long> g_alloc_gen{1};      // bumped whenever any scratch buffer moves: captured graphs hold raw pointers
+
 struct Buf {
     void* p = nullptr; size_t cap = 0;
     cudaError_t ensure(size_t bytes) {
         if (bytes <= cap) return cudaSuccess;
+        g_alloc_gen.fetch_add(1, std::memory_order_relaxed);
         if (p) { cudaError_t e = cudaFree(p); p = nullptr; cap = 0; if (e != cudaSuccess) return e; }   // cudaFree waits for the device
         size_t want = bytes + bytes / 8;
         cudaError_t e = cudaMalloc(&p, want);
@@ -879,7 +983,7 @@ struct Buf {
         if (e == cudaSuccess) cap = want;
         return e;
     }
-    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    void release() { if (p) { cudaFree(p); g_alloc_gen.fetch_add(1, std::memory_order_relaxed); } p = nullptr; cap = 0; }
     template <class T> T* as() const { return reinterpret_cast<T*>(p); }
 };
 
@@ -907,11 +1011,23 @@ struct DevCtx {
     // light (up to kSide) for the shadow queries, one for the shading
     cudaStream_t chainStream = nullptr, lightStream[kSide] = {}, shadeStream = nullptr;
     cudaEvent_t evFork = nullptr, evJoin = nullptr, evSetup[kSets] = {}, evShade[kSets] = {}, evLight[kSide] = {};
-    Buf batchScene;                                                // b200rt_render_batch_host: the scene, staged once
+    // resident scene (k_scene_cmp): the raw arrays the tables were built from, the version words, the per-frame camera block
+    Buf rawScene, cacheState, camDev; size_t rawCap = 0;
+    std::vector<float> hostScene; int hostS = -1, hostL = -1, hostPl = -1; unsigned long long hostStageGen = 0;   // host-side copy of the last staged host scene
+    // captured launch sequences (CUDA graphs), keyed by everything that shapes the sequence except the camera
+    struct GraphEntry { std::vector<unsigned char> key; cudaGraphExec_t exec = nullptr; unsigned long long gen = 0; unsigned long long last_use = 0; bool failed = false; unsigned kernels = 0; };
+    std::vector<GraphEntry> graphs; unsigned long long graph_clock = 0; cudaStream_t captureStream = nullptr;
+    bool no_graph = false, no_cache = false, no_scatter = false, graph_all = false;                       // env B200RT_NO_GRAPH, B200RT_NO_CACHE
+    unsigned long long n_graph_launches = 0, n_plain_frames = 0;
+    Buf batchScene;                                                // (unused since the resident scene; kept for release_all)
     cudaStream_t copyStream = nullptr; cudaEvent_t evRender[2] = {nullptr, nullptr}, evCopy[2] = {nullptr, nullptr};
     Buf hostResult, hostPixelLoc, imgOut;                          // b200rt_render_host / b200rt_to_image_host device copies
     cudaEvent_t done = nullptr; bool has_done = false;
     void release_all() {
+        for (auto& g : graphs) if (g.exec) cudaGraphExecDestroy(g.exec);
+        graphs.clear(); hostS = hostL = hostPl = -1; hostScene.clear(); rawCap = 0;
+        if (captureStream) { cudaStreamDestroy(captureStream); captureStream = nullptr; }
+        rawScene.release(); cacheState.release(); camDev.release();
         Buf* all[] = { &sphA, &sphB, &sphCol, &plO, &plN, &plNu, &plCol, &lights, &cmax, &pivTab, &pivPos, &pivPerm, &pivRad, &pivClus, &stage, &rayO[0], &rayO[1], &rayD[0], &rayD[1], &hitKey[0], &hitKey[1],
                        &acc, &tl, &ostat, &ctr, &work, &slow, &sortKey, &sortPerm, &sortHist, &sortBase, &sortPart, &sortGrid, &sgCells, &sgTab, &sgCone, &hostResult, &hostPixelLoc, &imgOut, &batchScene };
         for (Buf* b : all) b->release();
@@ -998,6 +1114,10 @@ int init_ctx(DevCtx& c, int device) {
     { const char* e = getenv("B200RT_SS_GRID"); if (e) c.ss_grid = std::max(0, atoi(e)); }     // CTAs per SM of the k_shadow_shade grid (0: sized from the queue)
     { const char* e = getenv("B200RT_NO_CLUS"); c.no_clus = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_NO_SGRID"); c.no_sgrid = e && atoi(e) != 0; }
+    { const char* e = getenv("B200RT_NO_GRAPH"); c.no_graph = e && atoi(e) != 0; }
+    { const char* e = getenv("B200RT_NO_CACHE"); c.no_cache = e && atoi(e) != 0; }
+    { const char* e = getenv("B200RT_NO_SCATTER"); c.no_scatter = e && atoi(e) != 0; }
+    { const char* e = getenv("B200RT_GRAPH_ALL"); c.graph_all = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_SGRID_MIN_S"); if (e) c.sgrid_min_s = std::max(1, atoi(e)); }
     { const char* e = getenv("B200RT_SORT_POSBITS"); if (e) c.sort_posbits = std::min(18, std::max(0, atoi(e))); }
     { const char* e = getenv("B200RT_SORT_DIRN"); if (e) c.sort_dirn = std::min(16, std::max(1, atoi(e))); }
@@ -1006,6 +1126,7 @@ int init_ctx(DevCtx& c, int device) {
         for (const char* p = e; *p && c.npre < 6; ) { const int v = atoi(p) & ~7; if (v >= 8) c.pre[c.npre++] = v; while (*p && *p != ',') ++p; if (*p == ',') ++p; }
     }
     CK(cudaEventCreateWithFlags(&c.done, cudaEventDisableTiming));
+    CK(cudaStreamCreateWithFlags(&c.captureStream, cudaStreamNonBlocking));
     {
         int lo = 0, hi = 0; CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));         // hi = greatest priority (numerically lowest)
         CK(cudaStreamCreateWithPriority(&c.chainStream, cudaStreamNonBlocking, hi));
@@ -1039,43 +1160,34 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     }
     if (ncols == 0) { if (stats) memset(a->stats, 0, sizeof(*a->stats)); return 0; }
 
-    if (c.has_done) CK(cudaStreamWaitEvent(st, c.done, 0));      // serialise users of the shared scratch
-
-    // ---- scene: stage (if on host) and pack ----
+    // ---- scene: resident tables, rebuilt only when k_scene_cmp finds the arrays changed (see "Resident scene" above) ----
     CK(c.sphA.ensure(sizeof(float4) * Spad)); CK(c.sphB.ensure(sizeof(float4) * std::max(S, 1))); CK(c.sphCol.ensure(sizeof(float4) * std::max(S, 1)));
     CK(c.plO.ensure(sizeof(float4) * std::max(Pl, 1))); CK(c.plN.ensure(sizeof(float4) * std::max(Pl, 1)));
     CK(c.plNu.ensure(sizeof(float4) * std::max(Pl, 1))); CK(c.plCol.ensure(sizeof(float4) * std::max(Pl, 1)));
     CK(c.lights.ensure(sizeof(float4) * std::max(L, 1))); CK(c.cmax.ensure(2 * sizeof(float)));
-    const float *d_sph = a->spheres, *d_lig = a->lights, *d_pla = a->planes;
-    if (a->flags & B200RT_F_SCENE_ON_HOST) {
-        const size_t nS = (size_t)7 * S, nL = (size_t)3 * L, nP = (size_t)9 * Pl;
-        CK(c.stage.ensure(sizeof(float) * std::max<size_t>(nS + nL + nP, 1)));
-        float* sg = c.stage.as<float>();
-        if (nS) CK(cudaMemcpyAsync(sg, a->spheres, sizeof(float) * nS, cudaMemcpyHostToDevice, st));
-        if (nL) CK(cudaMemcpyAsync(sg + nS, a->lights, sizeof(float) * nL, cudaMemcpyHostToDevice, st));
-        if (nP) CK(cudaMemcpyAsync(sg + nS + nL, a->planes, sizeof(float) * nP, cudaMemcpyHostToDevice, st));
-        d_sph = sg; d_lig = sg + nS; d_pla = sg + nS + nL;
-    }
-    CK(cudaMemsetAsync(c.cmax.p, 0, 2 * sizeof(float), st));
+    const float *d_sph = a->spheres, *d_lig = a->lights, *d_pla = a->planes;      // DEVICE arrays (run_frame staged a host scene)
+    const size_t nraw = (size_t)7 * S + (size_t)3 * L + (size_t)9 * Pl;
+    CK(c.pivTab.ensure(sizeof(float4) * (size_t)(L + 2) * Spad)); CK(c.pivPos.ensure(sizeof(float4) * (L + 1)));
+    CK(c.pivPerm.ensure(sizeof(int) * (size_t)(L + 1) * Spad)); CK(c.pivRad.ensure(sizeof(float) * (size_t)(L + 2) * Spad));
+    CK(c.pivClus.ensure(sizeof(float4) * (size_t)((Spad + 63) / 64)));
+    uint32_t* cst = c.cacheState.as<uint32_t>();                 // (allocated and initialised by run_frame, with rawScene and camDev)
     {
+        const int nb = (int)std::min<size_t>((nraw + 255) / 256 + 1, 64);
+        k_scene_cmp<<<nb, 256, 0, st>>>(d_sph, S, d_lig, L, d_pla, Pl, c.rawScene.as<uint32_t>(), cst, c.cmax.as<float>()); CKL();
         const int nobj = std::max(std::max(Spad, Pl), L);
         k_pack<<<(nobj + 255) / 256, 256, 0, st>>>(d_sph, S, Spad, d_pla, Pl, d_lig, L, c.sphA.as<float4>(), c.sphB.as<float4>(),
                                                    c.sphCol.as<float4>(), c.plO.as<float4>(), c.plN.as<float4>(), c.plNu.as<float4>(),
-                                                   c.plCol.as<float4>(), c.lights.as<float4>(), c.cmax.as<float>());
+                                                   c.plCol.as<float4>(), c.lights.as<float4>(), c.cmax.as<float>(), cst);
         CKL();
     }
     SceneDev sc{ c.sphA.as<float4>(), c.sphB.as<float4>(), c.sphCol.as<float4>(), c.plO.as<float4>(), c.plN.as<float4>(),
                  c.plNu.as<float4>(), c.plCol.as<float4>(), c.lights.as<float4>(), c.cmax.as<float>(), S, Spad, Pl, L };
-    CK(c.pivTab.ensure(sizeof(float4) * (size_t)(L + 2) * Spad)); CK(c.pivPos.ensure(sizeof(float4) * (L + 1)));
     {
         const int n = (L + 2) * (Spad / 2);
-        CK(c.pivPerm.ensure(sizeof(int) * (size_t)(L + 1) * Spad)); CK(c.pivRad.ensure(sizeof(float) * (size_t)(L + 2) * Spad));
-        CK(c.pivClus.ensure(sizeof(float4) * (size_t)((Spad + 63) / 64)));
-        if (L > 0) { k_rank<<<dim3((Spad + 255) / 256, L), 256, 0, st>>>(sc, c.pivPerm.as<int>()); CKL(); }
-        k_mrank<<<(Spad + 255) / 256, 256, 0, st>>>(sc, c.pivPerm.as<int>()); CKL();
-        k_clus<<<((Spad + 63) / 64 + 63) / 64, 64, 0, st>>>(sc, c.pivPerm.as<int>(), c.pivClus.as<float4>()); CKL();
-        k_pivot<<<(n + 255) / 256, 256, 0, st>>>(sc, (float)a->cam_origin[0], (float)a->cam_origin[1], (float)a->cam_origin[2],
-                                                 c.pivPerm.as<int>(), c.pivTab.as<float4>(), c.pivPos.as<float4>(), c.pivRad.as<float>());
+        if (L > 0) { k_rank<<<dim3((Spad + 255) / 256, L), 256, 0, st>>>(sc, c.pivPerm.as<int>(), cst); CKL(); }
+        k_mrank<<<(Spad + 255) / 256, 256, 0, st>>>(sc, c.pivPerm.as<int>(), cst); CKL();
+        k_clus<<<((Spad + 63) / 64 + 63) / 64, 64, 0, st>>>(sc, c.pivPerm.as<int>(), c.pivClus.as<float4>(), cst); CKL();
+        k_pivot<<<(n + 255) / 256, 256, 0, st>>>(sc, c.camDev.as<CamDev>(), c.pivPerm.as<int>(), c.pivTab.as<float4>(), c.pivPos.as<float4>(), c.pivRad.as<float>(), cst);
         CKL();
     }
     const bool dense = (a->flags & B200RT_F_DENSE) != 0;          // brute force: every specified query scans every sphere
@@ -1097,8 +1209,8 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         CK(c.sgCells.ensure(sizeof(uint16_t) * (size_t)kSgTiers * L * kSgCells * kSgRec));
         CK(c.sgTab.ensure(sizeof(float4) * (size_t)L * S)); CK(c.sgCone.ensure(sizeof(float4) * (size_t)kSgTiers * L * S));
         sg = ShadowGridDev{ c.sgCells.as<uint16_t>(), c.sgTab.as<float4>(), c.sgCone.as<float4>(), c.pivPerm.as<int>(), Spad };
-        k_sgrid_tab<<<(L * S + 255) / 256, 256, 0, st>>>(sc, sg); CKL();
-        k_sgrid_build<<<dim3(kSgCells / 256, L, kSgTiers), 256, 0, st>>>(sc, sg); CKL();
+        k_sgrid_tab<<<(L * S + 255) / 256, 256, 0, st>>>(sc, sg, cst); CKL();
+        k_sgrid_build<<<dim3(kSgCells / 256, L, kSgTiers), 256, 0, st>>>(sc, sg, cst); CKL();
     } else if (shadow_res) CK(shadow_upload_resident(pv, Spad, L, st));
     IsectCfg icfg{ c.sm_count, c.force_nr, c.force_nr0, dense ? 0 : c.npre, {0, 0, 0, 0, 0, 0} };
     for (int k = 0; k < icfg.npre; ++k) icfg.pre[k] = c.pre[k];
@@ -1122,7 +1234,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         if (!sgrid) CK(c.occl[b].ensure(std::max<size_t>(cap * (size_t)L, 1)));
         if (use_lists && !sgrid) { CK(c.shidx[b].ensure(sizeof(uint32_t) * std::max<size_t>(cap * (size_t)L, 1))); CK(c.shidx2[b].ensure(sizeof(uint32_t) * std::max<size_t>(cap * (size_t)L, 1))); }
     }
-    CK(c.acc.ensure(sizeof(float) * 3 * cap));
+    CK(c.acc.ensure(sizeof(float4) * cap));
     // regrouping of the hits of depth >= 1 (see k_key): worth it where beam culling is on and a query is expensive
     const bool regroup = cull && use_lists && S >= 64 && depth >= 1 && !(a->flags & B200RT_F_NO_SORT) && !c.no_sort;
     // Bin grid of the regrouping: ~40-170 rays per bin measured best at every frame share (C4: 13 position bits and 3x3
@@ -1137,8 +1249,9 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         CK(c.sortHist.ensure(sizeof(uint32_t) * sort_nb)); CK(c.sortBase.ensure(sizeof(uint32_t) * sort_nb));
         CK(c.sortPart.ensure(sizeof(uint32_t) * sort_nblk)); CK(c.sortGrid.ensure(sizeof(GridDev)));
         CK(cudaMemsetAsync(c.sortHist.p, 0, sizeof(uint32_t) * sort_nb, st));
-        k_grid<<<1, 256, 0, st>>>(sc, sort_posbits, sort_dirn, c.sortGrid.as<GridDev>()); CKL();
+        k_grid<<<1, 256, 0, st>>>(sc, sort_posbits, sort_dirn, c.sortGrid.as<GridDev>(), cst, (uint32_t)(sort_posbits * 64 + sort_dirn)); CKL();
     }
+    k_cache_commit<<<1, 1, 0, st>>>(cst, 1, sgrid ? 1 : 0, regroup ? 1 : 0, (uint32_t)(sort_posbits * 64 + sort_dirn)); CKL();
     // k_setup's ordered compaction: [pass][chunk of 256 rays][8 queues] status words + the chunk ticket, zeroed before every launch
     const size_t ostat_stride = ((cap + 255) / 256) * 8;
     const int ostat_passes = (use_lists && !sgrid) ? 1 + std::max(0, (L - 7 + 7) / 8) : 1;
@@ -1162,7 +1275,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     CK(cudaMemsetAsync(c.work.p, 0, sizeof(uint32_t) * work_n, st));
     CK(cudaMemsetAsync(c.slow.p, 0, 24 * sizeof(unsigned long long), st));
 
-    {   // persistent grid for the intersection kernels
+    if (a->flags & B200RT_F_NO_FILTER) {   // persistent grid of the scalar debug kernel
         int nb = 0; CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_intersect<false, true>, kThreads, isect_smem_bytes(Spad)));
         c.isect_blocks_per_sm = std::max(1, nb);
     }
@@ -1189,21 +1302,17 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
 
     for (int ch = 0; ch < nchunks; ++ch) {
         FrameDev f{};
-        f.pixel_loc = a->pixel_loc; f.gf = a->grid.f; f.gar = a->grid.ar; f.gsy = a->grid.sy; f.gsz = a->grid.sz;
-        f.ox = a->cam_origin[0]; f.oy = a->cam_origin[1]; f.oz = a->cam_origin[2];
-        for (int i = 0; i < 9; ++i) f.rot[i] = a->cam_rot[i];
+        f.pixel_loc = a->pixel_loc; f.cam = c.camDev.as<CamDev>();
         f.W = W; f.H = H; f.ns = ns;
         f.x0 = (int)(ch * cols_per_chunk); f.x1 = std::min(ncols, f.x0 + (int)cols_per_chunk);
         f.xb = a->x_begin; f.sw = a->strip_width; f.srank = a->strip_rank; f.sworld = a->strip_world;
         f.npix = (uint32_t)(f.x1 - f.x0) * (uint32_t)H; f.tiled = tiled ? 1 : 0;
         const size_t nslots = (size_t)f.npix * ns;
         uint32_t* ctr = c.ctr.as<uint32_t>() + (size_t)ch * ctr_stride;
-        float* accR = c.acc.as<float>(); float* accG = accR + cap; float* accB = accG + cap;
+        float4* acc = c.acc.as<float4>();
 
         tm.begin(2);
-        CK(cudaMemsetAsync(accR, 0, sizeof(float) * nslots, cs));
-        CK(cudaMemsetAsync(accG, 0, sizeof(float) * nslots, cs));
-        CK(cudaMemsetAsync(accB, 0, sizeof(float) * nslots, cs));
+        CK(cudaMemsetAsync(acc, 0, sizeof(float4) * nslots, cs));
         if (ns > 1) CK(cudaMemsetAsync(c.ostat.p, 0, ostat_bytes, cs));
         k_raygen<<<(int)std::min<size_t>((nslots + 255) / 256, (size_t)small_grid), 256, 0, cs>>>(f, c.rayO[0].as<float4>(), c.rayD[0].as<float4>(), store_keys ? nullptr : c.hitKey[0].as<unsigned long long>(), ctr + 0,
                                                                                                          c.ostat.as<unsigned long long>(), reinterpret_cast<uint32_t*>(c.ostat.as<unsigned long long>() + ostat_stride * ostat_passes));
@@ -1232,7 +1341,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             s.rayO = q.rayO; s.rayD = q.rayD; s.hit = q.hit;
             s.rayO2 = c.rayO[b ^ 1].as<float4>(); s.rayD2 = c.rayD[b ^ 1].as<float4>(); s.hit2 = store_keys ? nullptr : c.hitKey[b ^ 1].as<unsigned long long>();
             s.hP = c.hP[hs].as<float4>(); s.hN = c.hN[hs].as<float4>(); s.occl = sgrid ? nullptr : c.occl[hs].as<uint8_t>(); s.ocap = cap;
-            s.accR = accR; s.accG = accG; s.accB = accB;
+            s.acc = acc;
             s.n_live = n_live; s.n_hit = cd + 3;
             s.shidx = (use_lists && !sgrid) ? c.shidx[hs].as<uint32_t>() : nullptr; s.shcap = cap; s.n_sh = cd + 4;
             s.amb = (float)a->amb; s.lamb = (float)a->lamb; s.weight = wts[d]; s.emit_reflection = d < depth;
@@ -1244,6 +1353,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             else                              { const int f0 = tln; CK(isect3_launch_closest<0>(icfg, sc, q, pv, nslots, wk, closest_res, cs, tlb, &tln)); tl_mark("closest<0>", d, f0); }
             tm.end(0);
             tm.begin(2);
+            bool scatter = false;
             if (regroup && d >= 1 && (d < depth || !c.no_sort_last)) {
                 SortDev so{ q.rayO, q.rayD, q.hit, n_live, c.sortGrid.as<GridDev>(), c.sortKey.as<uint2>(), c.sortHist.as<uint32_t>(), c.sortPart.as<uint32_t>(),
                             c.sortBase.as<uint32_t>(), c.sortPerm.as<uint32_t>(), cd + 2, sort_nb, d < depth ? 1 : 0, nullptr };
@@ -1251,21 +1361,29 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
                 k_key<<<small_grid, 256, 0, cs>>>(sc, so); CKL();
                 k_binsum<<<sort_nblk, 256, 0, cs>>>(so); CKL();
                 k_binscan<<<sort_nblk, 256, 0, cs>>>(so); CKL();
-                k_perm<<<small_grid, 256, 0, cs>>>(so); CKL();
-                s.perm = so.perm; s.n_live = cd + 2;                                      // k_setup walks the hits in bin order
+                // (the scan path's per-light lists need the ordered append; at a full C4 frame the 16-byte scattered stores cost more
+                // than the gather through the permutation: "other" 3.20 -> 3.71 ms, at 1/8 of it 0.471 -> 0.453)
+                scatter = sgrid && L > 0 && !c.no_scatter && cap <= ((size_t)12 << 20);
+                if (!scatter) {
+                    k_perm<<<small_grid, 256, 0, cs>>>(so); CKL();
+                    s.perm = so.perm; s.n_live = cd + 2;                                  // k_setup walks the hits in bin order
+                }
             }
             if (conc && d >= nsets) CK(cudaStreamWaitEvent(cs, c.evShade[hs], 0));        // set hs is free again
             if (tlb) { s.tl = tlb + 2 * (size_t)tln++; tlname.push_back("setup d" + std::to_string(d)); }
             s.ostat = c.ostat.as<unsigned long long>(); s.ostat_stride = ostat_stride; s.ticket = reinterpret_cast<uint32_t*>(s.ostat + ostat_stride * ostat_passes);
-            CK(cudaMemsetAsync(c.ostat.p, 0, ostat_bytes, cs));
-            k_setup<<<small_grid, 256, 0, cs>>>(sc, s); CKL();
+            if (scatter) { k_setup_scatter<<<small_grid, 256, 0, cs>>>(sc, s, c.sortKey.as<uint2>(), c.sortBase.as<uint32_t>(), cd + 2); CKL(); }
+            else {
+                CK(cudaMemsetAsync(c.ostat.p, 0, ostat_bytes, cs));
+                k_setup<<<small_grid, 256, 0, cs>>>(sc, s); CKL();
+            }
             if (conc) CK(cudaEventRecord(c.evSetup[hs], cs));
             tm.end(2);
             if (L > 0) {
                 tm.begin(1);
                 if (nofilter) { q.n_in = cd + 3; q.work = cd + 2; if (int rc = launch_intersect<true>(c, sc, q, true, cs)) return rc; }
                 else if (sgrid) {                       // shadow queries + Lambert sum + accumulate in one kernel (shadow_grid.cuh)
-                    ShadowGridArgs ga{ s.hP, s.hN, s.n_hit, accR, accG, accB, s.amb, s.lamb, s.weight, pv.bounds,
+                    ShadowGridArgs ga{ s.hP, s.hN, s.n_hit, acc, s.amb, s.lamb, s.weight, pv.bounds,
                                        q.slow ? cd + 4 : nullptr, q.slow, nullptr };        // (counters only in the diagnostic frame: B200RT_F_TIME_ONLY leaves shadow_traced 0)
                     if (conc) CK(cudaStreamWaitEvent(ss, c.evSetup[hs], 0));
                     if (tlb) { ga.tl = tlb + 2 * (size_t)tln++; tlname.push_back("shadow+shade d" + std::to_string(d)); }
@@ -1304,14 +1422,13 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         const int unswap = (a->flags & B200RT_F_UNSWAP_GB) ? 1 : 0;
         const bool al16 = (H % 16 == 0) && (((uintptr_t)a->result) % 16 == 0);     // every column start is then 16-byte aligned
         const bool al4 = (H % 4 == 0) && (((uintptr_t)a->result) % 4 == 0);
-        if (al16)      k_resolve<16><<<std::min<int>((f.npix / 16 + 255) / 256, small_grid), 256, 0, cs>>>(f, accR, accG, accB, a->result, a->aliasing, unswap);
-        else if (al4)  k_resolve<4><<<std::min<int>((f.npix / 4 + 255) / 256, small_grid), 256, 0, cs>>>(f, accR, accG, accB, a->result, a->aliasing, unswap);
-        else           k_resolve<1><<<std::min<int>((f.npix + 255) / 256, small_grid), 256, 0, cs>>>(f, accR, accG, accB, a->result, a->aliasing, unswap);
+        if (al16)      k_resolve<16><<<std::min<int>((f.npix / 16 + 255) / 256, small_grid), 256, 0, cs>>>(f, acc, a->result, a->aliasing, unswap);
+        else if (al4)  k_resolve<4><<<std::min<int>((f.npix / 4 + 255) / 256, small_grid), 256, 0, cs>>>(f, acc, a->result, a->aliasing, unswap);
+        else           k_resolve<1><<<std::min<int>((f.npix + 255) / 256, small_grid), 256, 0, cs>>>(f, acc, a->result, a->aliasing, unswap);
         CKL();
         tm.end(2);
     }
     if (conc) { CK(cudaEventRecord(c.evJoin, cs)); CK(cudaStreamWaitEvent(st, c.evJoin, 0)); }
-    CK(cudaEventRecord(c.done, st)); c.has_done = true;
     if (tlb) {
         CK(cudaStreamSynchronize(st));
         std::vector<unsigned long long> h(2 * (size_t)tln); CK(cudaMemcpy(h.data(), tlb, sizeof(unsigned long long) * h.size(), cudaMemcpyDeviceToHost));
@@ -1347,6 +1464,131 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
 
 }  // namespace
 
+namespace {
+
+__global__ void k_set_cam(CamDev v, CamDev* dst) { if (threadIdx.x == 0) *dst = v; }
+
+// Host scene arrays -> the device staging buffer, skipped when the arrays equal the ones staged last (compared on the host:
+// 28 KB at C4).  Afterwards d->spheres / lights / planes are DEVICE pointers into the staging buffer.
+int stage_host_scene(DevCtx& c, const b200rt_args* a, cudaStream_t st, b200rt_args* d) {
+    const size_t nS = (size_t)7 * a->S, nL = (size_t)3 * a->L, nP = (size_t)9 * a->Pl, n = nS + nL + nP;
+    CK(c.stage.ensure(sizeof(float) * std::max<size_t>(n, 1)));
+    bool same = c.hostS == a->S && c.hostL == a->L && c.hostPl == a->Pl && c.hostScene.size() == n && c.hostStageGen == g_alloc_gen.load() && !c.no_cache;
+    if (same && n) same = (!nS || !memcmp(c.hostScene.data(), a->spheres, sizeof(float) * nS)) &&
+                          (!nL || !memcmp(c.hostScene.data() + nS, a->lights, sizeof(float) * nL)) &&
+                          (!nP || !memcmp(c.hostScene.data() + nS + nL, a->planes, sizeof(float) * nP));
+    float* sg = c.stage.as<float>();
+    if (!same) {
+        c.hostScene.resize(n);
+        if (nS) memcpy(c.hostScene.data(), a->spheres, sizeof(float) * nS);
+        if (nL) memcpy(c.hostScene.data() + nS, a->lights, sizeof(float) * nL);
+        if (nP) memcpy(c.hostScene.data() + nS + nL, a->planes, sizeof(float) * nP);
+        c.hostS = a->S; c.hostL = a->L; c.hostPl = a->Pl;
+        if (n) CK(cudaMemcpyAsync(sg, c.hostScene.data(), sizeof(float) * n, cudaMemcpyHostToDevice, st));
+        c.hostStageGen = g_alloc_gen.load();
+    }
+    d->spheres = sg; d->lights = sg + nS; d->planes = sg + nS + nL;
+    d->flags &= ~B200RT_F_SCENE_ON_HOST;
+    return 0;
+}
+
+// One frame tile: resident-scene bookkeeping, the per-frame camera block, then the launch sequence — replayed from a
+// captured CUDA graph when the same sequence (same shapes, buffers, flags, shader scalars) has been run before.
+int run_frame(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
+    b200rt_args d = *a;
+    if (c.has_done) CK(cudaStreamWaitEvent(st, c.done, 0));      // serialise users of the shared scratch
+    if (a->flags & B200RT_F_SCENE_ON_HOST) { if (int rc = stage_host_scene(c, a, st, &d)) return rc; }
+    // resident-scene state
+    const size_t nraw = (size_t)7 * a->S + (size_t)3 * a->L + (size_t)9 * a->Pl;
+    const bool fresh_state = c.cacheState.p == nullptr;
+    CK(c.cacheState.ensure(sizeof(uint32_t) * kCsWords)); CK(c.camDev.ensure(sizeof(CamDev)));
+    const void* raw_before = c.rawScene.p;
+    CK(c.rawScene.ensure(sizeof(uint32_t) * std::max<size_t>(nraw, 1)));
+    if (fresh_state || c.rawScene.p != raw_before || c.no_cache || (a->flags & B200RT_F_NO_CACHE)) {
+        uint32_t init[kCsWords] = {};                             // version 1, nothing built, shape unknown
+        init[kCsVersion] = 1u; init[kCsS] = init[kCsL] = init[kCsPl] = 0xffffffffu;
+        CK(cudaMemcpyAsync(c.cacheState.p, init, sizeof(init), cudaMemcpyHostToDevice, st));
+    }
+    CamDev cam{};
+    cam.gf = a->grid.f; cam.gar = a->grid.ar; cam.gsy = a->grid.sy; cam.gsz = a->grid.sz;
+    cam.ox = a->cam_origin[0]; cam.oy = a->cam_origin[1]; cam.oz = a->cam_origin[2];
+    for (int i = 0; i < 9; ++i) cam.rot[i] = a->cam_rot[i];
+    cam.cox = (float)a->cam_origin[0]; cam.coy = (float)a->cam_origin[1]; cam.coz = (float)a->cam_origin[2];
+    k_set_cam<<<1, 32, 0, st>>>(cam, c.camDev.as<CamDev>()); CKL();
+
+    // Replay pays where the frame is launch-bound and runs in one stream (the 6-sphere configs: C1 0.243 -> 0.190 ms) or is big
+    // (C4: 10.85 -> 10.77 ms).  Frames on the multi-stream schedule (S >= 64, <= 12 Mi paths: one GPU's share of a sharded frame)
+    // keep plain launches: stream priorities are not part of a captured graph and the replay measured slower (1.83 vs 1.78 ms).
+    bool multistream = false;
+    {
+        int ncols = a->x_end - a->x_begin;
+        if (a->strip_width > 0) { const int sw = a->strip_width, period = sw * a->strip_world, span = ncols; ncols = span / period * sw + std::max(0, std::min(sw, span % period - a->strip_rank * sw)); }
+        const size_t paths = std::min<size_t>((size_t)ncols * a->H * (a->aliasing ? 9 : 1), max_paths_per_chunk());
+        multistream = a->S >= 64 && !(a->flags & B200RT_F_NO_FILTER) && !c.no_conc && paths <= ((size_t)12 << 20);
+    }
+    const bool can_graph = !c.no_graph && !a->stats && !c.timeline && !(a->flags & (B200RT_F_NO_GRAPH | B200RT_F_NO_CACHE)) && !c.no_cache && (!multistream || c.graph_all);
+    int rc = 0;
+    bool done = false;
+    if (can_graph) {
+        // key: every argument except the camera block, plus the per-call tuning value and the allocation generation
+        b200rt_args k = d;
+        memset(k.cam_origin, 0, sizeof(k.cam_origin)); memset(k.cam_rot, 0, sizeof(k.cam_rot)); memset(&k.grid, 0, sizeof(k.grid));
+        k.stream = nullptr; k.stats = nullptr;
+        const size_t mp = max_paths_per_chunk();
+        std::vector<unsigned char> key(sizeof(k) + sizeof(mp));
+        memcpy(key.data(), &k, sizeof(k)); memcpy(key.data() + sizeof(k), &mp, sizeof(mp));
+        DevCtx::GraphEntry* e = nullptr;
+        for (auto& g : c.graphs) if (g.key == key) { e = &g; break; }
+        const unsigned long long gen = g_alloc_gen.load();
+        if (e && e->exec && e->gen != gen) { cudaGraphExecDestroy(e->exec); e->exec = nullptr; }      // scratch moved: pointers in the graph are stale
+        if (e && !e->exec && !e->failed) {                        // second use of this sequence: capture it
+            cudaGraph_t graph = nullptr;
+            cudaError_t ce = cudaStreamBeginCapture(c.captureStream, cudaStreamCaptureModeRelaxed);
+            if (ce == cudaSuccess) {
+                const unsigned long long launches0 = g_kernel_launches.load();
+                const int rcap = render_device(c, &d, c.captureStream);
+                g_kernel_launches.store(launches0);                // (captured, not launched: counted per graph launch below)
+                ce = cudaStreamEndCapture(c.captureStream, &graph);
+                if (rcap != 0 && ce == cudaSuccess) ce = cudaErrorUnknown;
+                if (ce == cudaSuccess) {
+                    size_t nn = 0; cudaGraphGetNodes(graph, nullptr, &nn);
+                    ce = cudaGraphInstantiate(&e->exec, graph, 0);
+                    if (ce == cudaSuccess) {
+                        cudaGraphNode_t* nodes = new cudaGraphNode_t[nn ? nn : 1]; cudaGraphGetNodes(graph, nodes, &nn);
+                        unsigned kn = 0; for (size_t i = 0; i < nn; ++i) { cudaGraphNodeType t; if (cudaGraphNodeGetType(nodes[i], &t) == cudaSuccess && t == cudaGraphNodeTypeKernel) ++kn; }
+                        delete[] nodes;
+                        e->kernels = kn;                           // kernel nodes of the graph = launches per replay
+                    }
+                }
+                if (graph) cudaGraphDestroy(graph);
+            }
+            if (ce != cudaSuccess) {
+                cudaGetLastError();
+                e->failed = true; e->exec = nullptr;
+                fprintf(stderr, "[b200rt] CUDA graph capture failed (%s); this launch sequence keeps running as plain launches\n", cudaGetErrorName(ce));
+            } else e->gen = g_alloc_gen.load();
+        }
+        if (e && e->exec) {
+            CK(cudaGraphLaunch(e->exec, st));
+            g_kernel_launches.fetch_add(e->kernels, std::memory_order_relaxed);
+            e->last_use = ++c.graph_clock; ++c.n_graph_launches; done = true;
+        } else if (!e) {                                          // first use: remember the key, run plainly (this allocates the scratch)
+            if (c.graphs.size() >= 16) {
+                size_t lru = 0; for (size_t i = 1; i < c.graphs.size(); ++i) if (c.graphs[i].last_use < c.graphs[lru].last_use) lru = i;
+                if (c.graphs[lru].exec) cudaGraphExecDestroy(c.graphs[lru].exec);
+                c.graphs.erase(c.graphs.begin() + lru);
+            }
+            DevCtx::GraphEntry ne; ne.key = key; ne.last_use = ++c.graph_clock; c.graphs.push_back(ne);
+        }
+    }
+    if (!done) { rc = render_device(c, &d, st); ++c.n_plain_frames; }
+    if (rc) return rc;
+    CK(cudaEventRecord(c.done, st)); c.has_done = true;
+    return 0;
+}
+
+}  // namespace
+
 // ================================================================================================
 // C ABI (include/b200rt.h)
 // ================================================================================================
@@ -1361,6 +1603,11 @@ B200RT_API int b200rt_device_count(void) {
 }
 B200RT_API unsigned long long b200rt_launch_count(void) { return b200rt::g_kernel_launches.load(std::memory_order_relaxed); }
 
+B200RT_API unsigned long long b200rt_graph_replays(int device) {
+    if (device < 0 || device >= kMaxDevices) return 0;
+    return g_ctx[device].n_graph_launches;
+}
+
 B200RT_API int b200rt_sm_count(int device) {
     int n = 0; if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) { cudaGetLastError(); return 0; } return n;
 }
@@ -1371,7 +1618,7 @@ B200RT_API int b200rt_render(const b200rt_args* a) {
     DevCtx& c = g_ctx[a->device];
     std::lock_guard<std::mutex> lock(c.mu);
     if (int rc = init_ctx(c, a->device)) return rc;
-    return render_device(c, a, (cudaStream_t)a->stream);
+    return run_frame(c, a, (cudaStream_t)a->stream);
 }
 
 B200RT_API int b200rt_render_host(const b200rt_args* a) {
@@ -1392,7 +1639,7 @@ B200RT_API int b200rt_render_host(const b200rt_args* a) {
     }
     CK(c.hostResult.ensure(3 * WH));                              // src/main.py:32 (only the tile is written / read back)
     d.result = c.hostResult.as<uint8_t>();
-    if (int rc = render_device(c, &d, st)) return rc;
+    if (int rc = run_frame(c, &d, st)) return rc;
     const int sw = a->strip_width > 0 ? a->strip_width : std::max(1, a->x_end - a->x_begin);
     const int world = a->strip_width > 0 ? a->strip_world : 1, srank = a->strip_width > 0 ? a->strip_rank : 0;
     if (a->x_end - a->x_begin == a->W && world == 1) {
@@ -1435,16 +1682,9 @@ B200RT_API int b200rt_render_batch_host(const b200rt_args* a, int n_frames, cons
     CK(c.hostResult.ensure(2 * fb));
     b200rt_args d = *a;
     d.stats = nullptr;
-    // scene: stage once, then treat as device-resident
-    const size_t nS = (size_t)7 * a->S, nL = (size_t)3 * a->L, nP = (size_t)9 * a->Pl;
-    CK(c.batchScene.ensure(sizeof(float) * std::max<size_t>(nS + nL + nP, 1)));
-    float* sg = c.batchScene.as<float>();
+    // scene: host arrays every frame; run_frame stages them once (they compare equal afterwards) and the tables stay resident
+    d.flags |= B200RT_F_SCENE_ON_HOST;
     if (c.has_done) CK(cudaStreamWaitEvent(st, c.done, 0));
-    if (nS) CK(cudaMemcpyAsync(sg, a->spheres, sizeof(float) * nS, cudaMemcpyHostToDevice, st));
-    if (nL) CK(cudaMemcpyAsync(sg + nS, a->lights, sizeof(float) * nL, cudaMemcpyHostToDevice, st));
-    if (nP) CK(cudaMemcpyAsync(sg + nS + nL, a->planes, sizeof(float) * nP, cudaMemcpyHostToDevice, st));
-    d.spheres = sg; d.lights = sg + nS; d.planes = sg + nS + nL;
-    d.flags &= ~B200RT_F_SCENE_ON_HOST;
     if (a->pixel_loc) {
         CK(c.hostPixelLoc.ensure(sizeof(double) * 3 * WH));
         CK(cudaMemcpyAsync(c.hostPixelLoc.p, a->pixel_loc, sizeof(double) * 3 * WH, cudaMemcpyHostToDevice, st));
@@ -1456,7 +1696,7 @@ B200RT_API int b200rt_render_batch_host(const b200rt_args* a, int n_frames, cons
         for (int i = 0; i < 9; ++i) d.cam_rot[i] = cam_rots[9 * k + i];
         d.result = c.hostResult.as<uint8_t>() + (size_t)b * fb;
         if (k >= 2) CK(cudaStreamWaitEvent(st, c.evCopy[b], 0));                 // frame k-2 has left this framebuffer
-        if (int rc = render_device(c, &d, st)) return rc;
+        if (int rc = run_frame(c, &d, st)) return rc;
         CK(cudaEventRecord(c.evRender[b], st));
         CK(cudaStreamWaitEvent(c.copyStream, c.evRender[b], 0));
         CK(cudaMemcpyAsync(results + (size_t)k * fb, d.result, fb, cudaMemcpyDeviceToHost, c.copyStream));

@@ -65,7 +65,8 @@ __device__ __forceinline__ V3 sg_dir(int face, float a, float b) {       // un-n
 }
 
 // One thread per (light j, rank pos): filter operand k of the sphere at that rank, and its cone seen from the light per tier.
-__global__ void __launch_bounds__(256) k_sgrid_tab(SceneDev sc, ShadowGridDev g) {
+__global__ void __launch_bounds__(256) k_sgrid_tab(SceneDev sc, ShadowGridDev g, const uint32_t* cs) {
+    if (cs[2] == cs[0]) return;                                            // resident scene (b200rt.cu: kCsSgrid / kCsVersion): grids already built from this scene
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= sc.L * sc.S) return;
     const int j = idx / sc.S, pos = idx - j * sc.S;
@@ -84,7 +85,8 @@ __global__ void __launch_bounds__(256) k_sgrid_tab(SceneDev sc, ShadowGridDev g)
 }
 
 // One thread per (cell, light, tier): the list, in rank order, of the spheres whose cone (either sign) reaches the cell's cone.
-__global__ void __launch_bounds__(256) k_sgrid_build(SceneDev sc, ShadowGridDev g) {
+__global__ void __launch_bounds__(256) k_sgrid_build(SceneDev sc, ShadowGridDev g, const uint32_t* cs) {
+    if (cs[2] == cs[0]) return;
     __shared__ float4 s_cone[256];                                         // (unit direction, cos alpha)
     __shared__ float s_sin[256];                                           // sin alpha; alpha + beta >= pi: cos = -2 (always listed)
     __shared__ int s_id[256];
@@ -136,7 +138,7 @@ __device__ __forceinline__ void warp_count(uint32_t* ctr) {     // += 1 per call
 struct ShadowGridArgs {
     const float4* hP; const float4* hN;  // hit records: (biased hit point, slot) (normal, object id)
     const uint32_t* n_hit;               // number of hit records
-    float* accR; float* accG; float* accB;   // per-slot colour accumulators
+    float4* acc;                         // per-slot colour accumulators (R, G, B, -)
     float amb, lamb, weight;             // weight = refl^depth (trace.py:131)
     const float* bounds;                 // max |C|, max r
     uint32_t* n_traced;                  // [L] diagnostics (b200rt_stats.shadow_traced): queries run per light; may be null
@@ -161,7 +163,7 @@ __global__ void __launch_bounds__(256, B200RT_SS_OCC) k_shadow_shade(SceneDev sc
     for (uint32_t h = blockIdx.x * blockDim.x + threadIdx.x; h < n; h += gridDim.x * blockDim.x) {
         const float4 p = a.hP[h], nn = a.hN[h];
         const uint32_t slot = __float_as_uint(p.w);
-        const float ar = a.accR[slot], ag = a.accG[slot], ab = a.accB[slot];
+        const float4 a0 = a.acc[slot]; const float ar = a0.x, ag = a0.y, ab = a0.z;
         const V3 O = mk(p.x, p.y, p.z), N = mk(nn.x, nn.y, nn.z);
         const int id = __float_as_int(nn.w);
         const float4 col = (id < sc.S) ? __ldg(&sc.sphCol[id]) : __ldg(&sc.plCol[id - sc.S]);
@@ -222,9 +224,7 @@ __global__ void __launch_bounds__(256, B200RT_SS_OCC) k_shadow_shade(SceneDev sc
             if (occluded) continue;                                                                    // :95-96
             r = fmaf(k, col.x, r); gg = fmaf(k, col.y, gg); b = fmaf(k, col.z, b);                     // :102
         }
-        a.accR[slot] = fmaf(a.weight, r, ar);                                                          // :131
-        a.accG[slot] = fmaf(a.weight, gg, ag);
-        a.accB[slot] = fmaf(a.weight, b, ab);
+        a.acc[slot] = make_float4(fmaf(a.weight, r, ar), fmaf(a.weight, gg, ag), fmaf(a.weight, b, ab), 0.f);     // :131
     }
     if (a.slow) {
 #pragma unroll

@@ -357,7 +357,7 @@ def test_c4_antialiased_crops_vs_simulator_golden():
     tot = dict(n=0, n_bad=0, max=0)
     for (x0, x1, y0, y1, ref) in golden_regions(g):
         xa = (x0 // 16) * 16
-        got = _cuda(g, tile=(xa, min(int(g["W"]), xa + 16)))[:, x0:x1, y0:y1]
+        got = _cuda(g, tile=(xa, min(int(g["W"]), xa + 32)))[:, x0:x1, y0:y1]
         rep = parity_report(got, ref)
         tot["n"] += rep["n"]; tot["n_bad"] += rep["n_bad"]; tot["max"] = max(tot["max"], rep["max"])
     print("c4 AA crops", tot)
