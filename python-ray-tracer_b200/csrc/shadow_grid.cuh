@@ -32,8 +32,9 @@ namespace b200rt {
 #endif
 constexpr int kSgN = B200RT_SGN;                          // cells per edge of a cube-map face
 constexpr int kSgCells = 6 * kSgN * kSgN;         // cells per light
-constexpr int kSgRec = 128;                       // uint16 per cell record: [0] count (0xffff: scan every sphere), [4 ..] sphere ids
-constexpr int kSgCap = kSgRec - 4;
+constexpr int kSgRec = 128;                       // uint16 per cell record: [0] count (0xffff: scan every sphere), [1 ..] sphere ids: the first
+                                                  // 16-byte load of a record brings the count and 7 ids, every further one 8 ids
+constexpr int kSgCap = kSgRec - 1;
 constexpr int kSgTiers = 2;                       // tier t serves shadow rays with |V-P| <= kSgRange * 16^t
 constexpr float kSgRange = 256.f;
 __host__ __device__ __forceinline__ float sg_range(int t) { return t == 0 ? kSgRange : kSgRange * 16.f; }
@@ -121,13 +122,12 @@ __global__ void __launch_bounds__(256) k_sgrid_build(SceneDev sc, ShadowGridDev 
         for (int k = 0; k < n; ++k) {
             const float4 c = s_cone[k];
             const float dt = fabsf(c.x * cdir.x + c.y * cdir.y + c.z * cdir.z);
-            if (dt >= fmaf(c.w, cb, -s_sin[k] * sb) - 1e-6f) { if (cnt < (uint32_t)kSgCap) rec[4 + cnt] = (uint16_t)s_id[k]; ++cnt; }
+            if (dt >= fmaf(c.w, cb, -s_sin[k] * sb) - 1e-6f) { if (cnt < (uint32_t)kSgCap) rec[1 + cnt] = (uint16_t)s_id[k]; ++cnt; }
         }
     }
     const bool over = cnt > (uint32_t)kSgCap || !in_range;
-    for (uint32_t k = min(cnt, (uint32_t)kSgCap); k < (uint32_t)kSgCap && (k & 3u); ++k) rec[4 + k] = 0;   // pad the last group of four
+    for (uint32_t k = min(cnt, (uint32_t)kSgCap); k < (uint32_t)kSgCap && ((k + 1u) & 7u); ++k) rec[1 + k] = 0;   // pad the last 16-byte group (a valid id: S >= 1)
     rec[0] = over ? (uint16_t)0xffff : (uint16_t)cnt;
-    rec[1] = (uint16_t)min(cnt, 0xffffu);                                   // diagnostic: the uncapped count
 }
 
 __device__ __forceinline__ void warp_count(uint32_t* ctr) {     // += 1 per calling lane, one atomic per warp
@@ -174,55 +174,71 @@ __global__ void __launch_bounds__(256, B200RT_SS_OCC) k_shadow_shade(SceneDev sc
             const V3 Vp = mk(vv.x, vv.y, vv.z);
             // the ray and its filter threshold: the operations of k_isect3<shadow>'s prologue; D is also k_shade's Lv (common.py:84-91)
             const V3 d = sub3(Vp, O);
-            const float nrm = __fsqrt_rn(dot3(d, d));
-            const V3 D = mk(__fdiv_rn(d.x, nrm), __fdiv_rn(d.y, nrm), __fdiv_rn(d.z, nrm));
-            const float k = __fmul_rn(a.lamb, dot3(D, N));                                             // :99
-            if (!(k > 0.f)) continue;                                                                  // :101 (the query's answer would not be used)
+            const float nrmc = __fsqrt_rn(dot3(d, d));
+            const V3 Dc = mk(__fdiv_rn(d.x, nrmc), __fdiv_rn(d.y, nrmc), __fdiv_rn(d.z, nrmc));
+            const float kc = __fmul_rn(a.lamb, dot3(Dc, N));                                           // :99
+            if (!(kc > 0.f)) continue;                                                                 // :101 (the query's answer would not be used)
+            // the first 16 bytes of the cell's record: count + 7 ids (one load where count and ids used to be two dependent ones)
+            const uint16_t* recc = g.cells + ((((size_t)(nrmc <= sg_range(0) ? 0 : 1) * sc.L + j) * kSgCells) + (size_t)sg_cell(Dc.x, Dc.y, Dc.z)) * kSgRec;
+            const uint4 hc = __ldg(reinterpret_cast<const uint4*>(recc));
             if (a.n_traced) warp_count(a.n_traced + j);
             const float A = j < 64 ? s_A[j] : cmax + __fsqrt_rn(dot3(Vp, Vp));
-            const float e = nrm * 9.5367432e-7f;
+            const float e = nrmc * 9.5367432e-7f;
             const float th = -(fmaf(3.8146973e-6f, fmaf(A, A, B * B), fmaf(4.f * e, rmax, 16.f * e * e)) + 1e-12f);
-            const float no = -dot3(Vp, D);
-            const bool near_ = nrm <= sg_range(0);
-            const uint16_t* rec = g.cells + ((((size_t)(near_ ? 0 : 1) * sc.L + j) * kSgCells) + (size_t)sg_cell(D.x, D.y, D.z)) * kSgRec;
+            const float no = -dot3(Vp, Dc);
             const float4* ltab = g.ltab + (size_t)j * sc.S;
-            const uint32_t cnt = rec[0];
-            const bool full = cnt == 0xffffu || !(nrm <= sg_range(kSgTiers - 1));      // overflowed cell, origin beyond the last tier or NaN: every sphere
-            const uint32_t ncand = full ? (uint32_t)sc.S : cnt;
+            const uint32_t cnt = hc.x & 0xffffu;
+            const bool full = cnt == 0xffffu || !(nrmc <= sg_range(kSgTiers - 1));     // overflowed cell, origin beyond the last tier or NaN: every sphere
             bool occluded = false;
-            for (uint32_t c = 0; c < ncand && !occluded; c += 4) {
-                uint32_t cid[4];
-                if (full) { cid[0] = c; cid[1] = min(c + 1, (uint32_t)sc.S - 1u); cid[2] = min(c + 2, (uint32_t)sc.S - 1u); cid[3] = min(c + 3, (uint32_t)sc.S - 1u); }
-                else { const uint2 w = *reinterpret_cast<const uint2*>(rec + 4 + c); cid[0] = w.x & 0xffffu; cid[1] = w.x >> 16; cid[2] = w.y & 0xffffu; cid[3] = w.y >> 16; }
+            // four candidates: their filter operands are requested together, then tested in order (a query stops at its first hit)
+            auto test4 = [&](const uint32_t (&cid)[4], uint32_t nvalid) {
                 float4 t4[4];
 #pragma unroll
                 for (int q = 0; q < 4; ++q) t4[q] = __ldg(&ltab[cid[q]]);
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
-                    if (c + q >= ncand || occluded) continue;
-                    const float bb = fmaf(t4[q].x, D.x, fmaf(t4[q].y, D.y, fmaf(t4[q].z, D.z, no)));   // k_isect3 qray(), pivot form
+                    if ((uint32_t)q >= nvalid || occluded) continue;
+                    const float bb = fmaf(t4[q].x, Dc.x, fmaf(t4[q].y, Dc.y, fmaf(t4[q].z, Dc.z, no)));   // k_isect3 qray(), pivot form
                     const float qq = fmaf(bb, bb, t4[q].w);
                     if (a.slow) ++n_filter;
                     if (qq >= th) {
                         const float4 sp = __ldg(&sc.sphB[cid[q]]);
-                        const float t = sphere_exact(O, D, sp.x, sp.y, sp.z, sp.w);
+                        const float t = sphere_exact(O, Dc, sp.x, sp.y, sp.z, sp.w);
                         occluded = t > 0.f && t < kTMax;                                               // trace.py:26-29, :95
                         if (a.slow) ++n_exact;
                     }
+                }
+            };
+            if (full) {
+                for (uint32_t c = 0; c < (uint32_t)sc.S && !occluded; c += 4) {
+                    const uint32_t cid[4] = { c, min(c + 1, (uint32_t)sc.S - 1u), min(c + 2, (uint32_t)sc.S - 1u), min(c + 3, (uint32_t)sc.S - 1u) };
+                    test4(cid, (uint32_t)sc.S - c);
+                }
+            } else if (cnt) {
+                {   // candidates 0..6 came with the header
+                    const uint32_t c0[4] = { hc.x >> 16, hc.y & 0xffffu, hc.y >> 16, hc.z & 0xffffu };
+                    test4(c0, cnt);
+                    if (cnt > 4u && !occluded) { const uint32_t c1[4] = { hc.z >> 16, hc.w & 0xffffu, hc.w >> 16, hc.w >> 16 }; test4(c1, min(cnt - 4u, 3u)); }
+                }
+                for (uint32_t c = 7; c < cnt && !occluded; c += 8) {                                   // candidates c .. c+7 = rec[c+1 .. c+8]
+                    const uint4 w = __ldg(reinterpret_cast<const uint4*>(recc + 1 + c));
+                    const uint32_t c0[4] = { w.x & 0xffffu, w.x >> 16, w.y & 0xffffu, w.y >> 16 };
+                    test4(c0, cnt - c);
+                    if (cnt > c + 4u && !occluded) { const uint32_t c1[4] = { w.z & 0xffffu, w.z >> 16, w.w & 0xffffu, w.w >> 16 }; test4(c1, cnt - c - 4u); }
                 }
             }
             for (int pl = 0; pl < sc.Pl && !occluded; ++pl) {                                          // trace.py:32-39
                 const float4 po = __ldg(&sc.plO[pl]), pn = __ldg(&sc.plN[pl]);
                 // t = num / den > 0 needs num and den of the same sign: where they differ (or num is 0) the quotient is <= 0
                 // and plane_exact's division is skipped — the usual case for a point on the plane looking up at a light
-                const float den = dot3(D, mk(pn.x, pn.y, pn.z));
+                const float den = dot3(Dc, mk(pn.x, pn.y, pn.z));
                 const float num = dot3(mk(__fsub_rn(po.x, O.x), __fsub_rn(po.y, O.y), __fsub_rn(po.z, O.z)), mk(pn.x, pn.y, pn.z));
                 if ((num > 0.f) != (den > 0.f) || num == 0.f) continue;
-                const float t = plane_exact(O, D, po, pn);
+                const float t = plane_exact(O, Dc, po, pn);
                 occluded = (t > 0.f && t < kTMax);
             }
             if (occluded) continue;                                                                    // :95-96
-            r = fmaf(k, col.x, r); gg = fmaf(k, col.y, gg); b = fmaf(k, col.z, b);                     // :102
+            r = fmaf(kc, col.x, r); gg = fmaf(kc, col.y, gg); b = fmaf(kc, col.z, b);                  // :102
         }
         a.acc[slot] = make_float4(fmaf(a.weight, r, ar), fmaf(a.weight, gg, ag), fmaf(a.weight, b, ab), 0.f);     // :131
     }
