@@ -990,8 +990,36 @@ struct Buf {
 constexpr int kSets = 4;      // depths whose hit records are alive at once
 constexpr int kSide = 4;      // shadow streams
 
+constexpr int kLanes = 2;     // wavefronts of one call that may be in flight at once (each with its own queues and streams)
+
+// Per-wavefront scratch and streams.  A call renders its columns as one wavefront (lane 0), or — for one GPU's share of a
+// sharded frame, where a single wavefront leaves the SMs idle in the tails of its persistent kernels and between its ~30
+// dependent small launches — as two half-width wavefronts in two lanes whose launch sequences interleave on the device.
+struct Lane {
+    Buf rayO[2], rayD[2], hitKey[2];                               // ray queues, double-buffered by depth parity
+    Buf hP[kSets], hN[kSets], occl[kSets], shidx[kSets], shidx2[kSets];   // hit records / shadow state: ring of kSets depths
+    Buf acc, ostat;
+    Buf sortKey, sortPerm, sortHist, sortBase, sortPart;           // regrouping of bounce-depth hits (k_key .. k_perm)
+    // streams (see the launch sequence in render_device): the dependent chain at high priority, one stream per light (up to
+    // kSide) for the shadow queries of the scan path, one for the shading
+    cudaStream_t chainStream = nullptr, lightStream[kSide] = {}, shadeStream = nullptr;
+    cudaEvent_t evFork = nullptr, evJoin = nullptr, evSetup[kSets] = {}, evShade[kSets] = {}, evLight[kSide] = {};
+    void release() {
+        Buf* all[] = { &rayO[0], &rayO[1], &rayD[0], &rayD[1], &hitKey[0], &hitKey[1], &acc, &ostat, &sortKey, &sortPerm, &sortHist, &sortBase, &sortPart };
+        for (Buf* b : all) b->release();
+        for (int i = 0; i < kSets; ++i) { hP[i].release(); hN[i].release(); occl[i].release(); shidx[i].release(); shidx2[i].release(); }
+        if (chainStream) {
+            cudaStreamDestroy(chainStream); chainStream = nullptr; cudaStreamDestroy(shadeStream);
+            for (int i = 0; i < kSide; ++i) { cudaStreamDestroy(lightStream[i]); cudaEventDestroy(evLight[i]); }
+            for (int i = 0; i < kSets; ++i) { cudaEventDestroy(evSetup[i]); cudaEventDestroy(evShade[i]); }
+            cudaEventDestroy(evFork); cudaEventDestroy(evJoin);
+        }
+    }
+};
+
 struct DevCtx {
     std::mutex mu;
+    Lane lane[kLanes];
     bool init = false;
     int sm_count = 0;
     int isect_blocks_per_sm = 2;
@@ -999,18 +1027,13 @@ struct DevCtx {
     Buf sphA, sphB, sphCol, plO, plN, plNu, plCol, lights, cmax;   // packed scene
     Buf pivTab, pivPos, pivPerm, pivRad, pivClus;                                   // pivot tables (k_pivot), light-table order (k_rank)
     Buf stage;                                                     // host-scene / host-pixel_loc staging
-    Buf rayO[2], rayD[2], hitKey[2];                               // ray queues, double-buffered by depth parity
-    Buf hP[kSets], hN[kSets], occl[kSets], shidx[kSets], shidx2[kSets];   // hit records / shadow state: ring of kSets depths
-    Buf acc, ctr, work, slow, tl, ostat;
+    Buf ctr, work, slow, tl;
     Buf sgCells, sgTab, sgCone;                                      // per-light direction grids of the shadow queries (shadow_grid.cuh)
-    Buf sortKey, sortPerm, sortHist, sortBase, sortPart, sortGrid;   // regrouping of bounce-depth hits (k_key .. k_perm)
+    Buf sortGrid;                                                    // bounding box / cell counts of the regrouping (scene-level)
+    bool no_lanes = false, lane_conc = false;                        // env B200RT_NO_LANES, B200RT_LANE_CONC
     bool no_sgrid = false, no_clus = false, no_sort_last = true; int ss_grid = 0; int sgrid_min_s = 1; bool no_sort = false; int sort_posbits = -1, sort_dirn = -1;     // env B200RT_NO_SORT, B200RT_SORT_POSBITS, B200RT_SORT_DIRN (-1: chosen from the queue size)
     int npre = 1, pre[6] = {256, 0, 0, 0, 0, 0};                    // leading shadow passes (env B200RT_PASSES=a,b,...; multiples of 8)
     bool timeline = false;                                        // env B200RT_TIMELINE: per-launch first-start / last-end (globaltimer) to stderr
-    // internal streams (see the launch sequence in render_device): the dependent chain at high priority, one stream per
-    // light (up to kSide) for the shadow queries, one for the shading
-    cudaStream_t chainStream = nullptr, lightStream[kSide] = {}, shadeStream = nullptr;
-    cudaEvent_t evFork = nullptr, evJoin = nullptr, evSetup[kSets] = {}, evShade[kSets] = {}, evLight[kSide] = {};
     // resident scene (k_scene_cmp): the raw arrays the tables were built from, the version words, the per-frame camera block
     Buf rawScene, cacheState, camDev; size_t rawCap = 0;
     std::vector<float> hostScene; int hostS = -1, hostL = -1, hostPl = -1; unsigned long long hostStageGen = 0;   // host-side copy of the last staged host scene
@@ -1028,17 +1051,11 @@ struct DevCtx {
         graphs.clear(); hostS = hostL = hostPl = -1; hostScene.clear(); rawCap = 0;
         if (captureStream) { cudaStreamDestroy(captureStream); captureStream = nullptr; }
         rawScene.release(); cacheState.release(); camDev.release();
-        Buf* all[] = { &sphA, &sphB, &sphCol, &plO, &plN, &plNu, &plCol, &lights, &cmax, &pivTab, &pivPos, &pivPerm, &pivRad, &pivClus, &stage, &rayO[0], &rayO[1], &rayD[0], &rayD[1], &hitKey[0], &hitKey[1],
-                       &acc, &tl, &ostat, &ctr, &work, &slow, &sortKey, &sortPerm, &sortHist, &sortBase, &sortPart, &sortGrid, &sgCells, &sgTab, &sgCone, &hostResult, &hostPixelLoc, &imgOut, &batchScene };
+        Buf* all[] = { &sphA, &sphB, &sphCol, &plO, &plN, &plNu, &plCol, &lights, &cmax, &pivTab, &pivPos, &pivPerm, &pivRad, &pivClus, &stage,
+                       &tl, &ctr, &work, &slow, &sortGrid, &sgCells, &sgTab, &sgCone, &hostResult, &hostPixelLoc, &imgOut, &batchScene };
         for (Buf* b : all) b->release();
-        for (int i = 0; i < kSets; ++i) { hP[i].release(); hN[i].release(); occl[i].release(); shidx[i].release(); shidx2[i].release(); }
+        for (int l = 0; l < kLanes; ++l) lane[l].release();
         if (done) { cudaEventDestroy(done); done = nullptr; } has_done = false; init = false;
-        if (chainStream) {
-            cudaStreamDestroy(chainStream); chainStream = nullptr; cudaStreamDestroy(shadeStream);
-            for (int i = 0; i < kSide; ++i) { cudaStreamDestroy(lightStream[i]); cudaEventDestroy(evLight[i]); }
-            for (int i = 0; i < kSets; ++i) { cudaEventDestroy(evSetup[i]); cudaEventDestroy(evShade[i]); }
-            cudaEventDestroy(evFork); cudaEventDestroy(evJoin);
-        }
         if (copyStream) { cudaStreamDestroy(copyStream); copyStream = nullptr; for (int i = 0; i < 2; ++i) { cudaEventDestroy(evRender[i]); cudaEventDestroy(evCopy[i]); } }
     }
 };
@@ -1119,6 +1136,8 @@ int init_ctx(DevCtx& c, int device) {
     { const char* e = getenv("B200RT_NO_SCATTER"); c.no_scatter = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_GRAPH_ALL"); c.graph_all = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_NO_SPLIT"); c.no_split = e && atoi(e) != 0; }
+    { const char* e = getenv("B200RT_NO_LANES"); c.no_lanes = e && atoi(e) != 0; }
+    { const char* e = getenv("B200RT_LANE_CONC"); c.lane_conc = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_SGRID_MIN_S"); if (e) c.sgrid_min_s = std::max(1, atoi(e)); }
     { const char* e = getenv("B200RT_SORT_POSBITS"); if (e) c.sort_posbits = std::min(18, std::max(0, atoi(e))); }
     { const char* e = getenv("B200RT_SORT_DIRN"); if (e) c.sort_dirn = std::min(16, std::max(1, atoi(e))); }
@@ -1130,11 +1149,14 @@ int init_ctx(DevCtx& c, int device) {
     CK(cudaStreamCreateWithFlags(&c.captureStream, cudaStreamNonBlocking));
     {
         int lo = 0, hi = 0; CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));         // hi = greatest priority (numerically lowest)
-        CK(cudaStreamCreateWithPriority(&c.chainStream, cudaStreamNonBlocking, hi));
-        CK(cudaStreamCreateWithPriority(&c.shadeStream, cudaStreamNonBlocking, hi));
-        for (int i = 0; i < kSide; ++i) { CK(cudaStreamCreateWithPriority(&c.lightStream[i], cudaStreamNonBlocking, lo)); CK(cudaEventCreateWithFlags(&c.evLight[i], cudaEventDisableTiming)); }
-        for (int i = 0; i < kSets; ++i) { CK(cudaEventCreateWithFlags(&c.evSetup[i], cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&c.evShade[i], cudaEventDisableTiming)); }
-        CK(cudaEventCreateWithFlags(&c.evFork, cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&c.evJoin, cudaEventDisableTiming));
+        for (int l = 0; l < kLanes; ++l) {
+            Lane& ln = c.lane[l];
+            CK(cudaStreamCreateWithPriority(&ln.chainStream, cudaStreamNonBlocking, hi));
+            CK(cudaStreamCreateWithPriority(&ln.shadeStream, cudaStreamNonBlocking, hi));
+            for (int i = 0; i < kSide; ++i) { CK(cudaStreamCreateWithPriority(&ln.lightStream[i], cudaStreamNonBlocking, lo)); CK(cudaEventCreateWithFlags(&ln.evLight[i], cudaEventDisableTiming)); }
+            for (int i = 0; i < kSets; ++i) { CK(cudaEventCreateWithFlags(&ln.evSetup[i], cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&ln.evShade[i], cudaEventDisableTiming)); }
+            CK(cudaEventCreateWithFlags(&ln.evFork, cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&ln.evJoin, cudaEventDisableTiming));
+        }
     }
     c.init = true;
     return 0;
@@ -1220,22 +1242,33 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     const size_t per_col = (size_t)ns * H;
     size_t cols_per_chunk = std::max<size_t>(1, max_paths_per_chunk() / per_col);
     cols_per_chunk = std::min<size_t>(cols_per_chunk, (size_t)ncols);
+    // Two lanes (see struct Lane): frames that would run on the multi-stream schedule — many spheres, at most 12 Mi paths, i.e.
+    // one GPU's share of a sharded frame — are cut into two half-width wavefronts that run side by side.  Measured on 1/8 of
+    // C4: one wavefront on three streams 1.72 ms, two lanes 1.5x ms.  Tiles are bit-identical to the whole (tested).
+    const bool lanes_ok = !stats && !c.timeline && !c.no_lanes && !(a->flags & B200RT_F_NO_FILTER) && S >= 64 && 2 * Spad <= kTabCap &&
+                          (L == 0 || sgrid) && !c.no_conc && (size_t)ncols * per_col <= ((size_t)12 << 20) && (size_t)ncols * per_col >= ((size_t)1 << 20) &&
+                          ncols >= 64 && cols_per_chunk == (size_t)ncols;
+    const int nlanes = lanes_ok ? 2 : 1;
+    if (nlanes == 2) cols_per_chunk = (((size_t)ncols + 1) / 2 + 15) & ~(size_t)15;
     const bool tiled = (H % 16 == 0) && (ncols % 16 == 0) && (cols_per_chunk >= 16);
     if (tiled) cols_per_chunk &= ~(size_t)15;
     const int nchunks = (int)((ncols + cols_per_chunk - 1) / cols_per_chunk);
     const size_t cap = cols_per_chunk * per_col;                 // slots per chunk
     const bool use_lists = S >= 32 && !(a->flags & B200RT_F_NO_FILTER) && !dense;
-    for (int b = 0; b < 2; ++b) {                                // depth d: ray queue d & 1 (see the launch sequence below)
-        CK(c.rayO[b].ensure(sizeof(float4) * cap)); CK(c.rayD[b].ensure(sizeof(float4) * cap));
-        CK(c.hitKey[b].ensure(sizeof(unsigned long long) * cap));
-    }
     const int nsets = std::min(kSets, depth + 1);                // depth d: hit-record set d % nsets
-    for (int b = 0; b < nsets; ++b) {
-        CK(c.hP[b].ensure(sizeof(float4) * cap)); CK(c.hN[b].ensure(sizeof(float4) * cap));
-        if (!sgrid) CK(c.occl[b].ensure(std::max<size_t>(cap * (size_t)L, 1)));
-        if (use_lists && !sgrid) { CK(c.shidx[b].ensure(sizeof(uint32_t) * std::max<size_t>(cap * (size_t)L, 1))); CK(c.shidx2[b].ensure(sizeof(uint32_t) * std::max<size_t>(cap * (size_t)L, 1))); }
+    for (int l = 0; l < nlanes; ++l) {
+        Lane& ln = c.lane[l];
+        for (int b = 0; b < 2; ++b) {                            // depth d: ray queue d & 1 (see the launch sequence below)
+            CK(ln.rayO[b].ensure(sizeof(float4) * cap)); CK(ln.rayD[b].ensure(sizeof(float4) * cap));
+            CK(ln.hitKey[b].ensure(sizeof(unsigned long long) * cap));
+        }
+        for (int b = 0; b < nsets; ++b) {
+            CK(ln.hP[b].ensure(sizeof(float4) * cap)); CK(ln.hN[b].ensure(sizeof(float4) * cap));
+            if (!sgrid) CK(ln.occl[b].ensure(std::max<size_t>(cap * (size_t)L, 1)));
+            if (use_lists && !sgrid) { CK(ln.shidx[b].ensure(sizeof(uint32_t) * std::max<size_t>(cap * (size_t)L, 1))); CK(ln.shidx2[b].ensure(sizeof(uint32_t) * std::max<size_t>(cap * (size_t)L, 1))); }
+        }
+        CK(ln.acc.ensure(sizeof(float4) * cap));
     }
-    CK(c.acc.ensure(sizeof(float4) * cap));
     // regrouping of the hits of depth >= 1 (see k_key): worth it where beam culling is on and a query is expensive
     const bool regroup = cull && use_lists && S >= 64 && depth >= 1 && !(a->flags & B200RT_F_NO_SORT) && !c.no_sort;
     // Bin grid of the regrouping: ~40-170 rays per bin measured best at every frame share (C4: 13 position bits and 3x3
@@ -1246,10 +1279,14 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     if (sort_dirn < 0) sort_dirn = cap >= ((size_t)24 << 20) ? 3 : 2;
     const int sort_nb = 6 * sort_dirn * sort_dirn << sort_posbits, sort_nblk = (sort_nb + 1023) / 1024;
     if (regroup) {
-        CK(c.sortKey.ensure(sizeof(uint2) * cap)); CK(c.sortPerm.ensure(sizeof(uint32_t) * cap));
-        CK(c.sortHist.ensure(sizeof(uint32_t) * sort_nb)); CK(c.sortBase.ensure(sizeof(uint32_t) * sort_nb));
-        CK(c.sortPart.ensure(sizeof(uint32_t) * sort_nblk)); CK(c.sortGrid.ensure(sizeof(GridDev)));
-        CK(cudaMemsetAsync(c.sortHist.p, 0, sizeof(uint32_t) * sort_nb, st));
+        for (int l = 0; l < nlanes; ++l) {
+            Lane& ln = c.lane[l];
+            CK(ln.sortKey.ensure(sizeof(uint2) * cap)); CK(ln.sortPerm.ensure(sizeof(uint32_t) * cap));
+            CK(ln.sortHist.ensure(sizeof(uint32_t) * sort_nb)); CK(ln.sortBase.ensure(sizeof(uint32_t) * sort_nb));
+            CK(ln.sortPart.ensure(sizeof(uint32_t) * sort_nblk));
+            CK(cudaMemsetAsync(ln.sortHist.p, 0, sizeof(uint32_t) * sort_nb, st));
+        }
+        CK(c.sortGrid.ensure(sizeof(GridDev)));
         k_grid<<<1, 256, 0, st>>>(sc, sort_posbits, sort_dirn, c.sortGrid.as<GridDev>(), cst, (uint32_t)(sort_posbits * 64 + sort_dirn)); CKL();
     }
     k_cache_commit<<<1, 1, 0, st>>>(cst, 1, sgrid ? 1 : 0, regroup ? 1 : 0, (uint32_t)(sort_posbits * 64 + sort_dirn)); CKL();
@@ -1257,7 +1294,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     const size_t ostat_stride = ((cap + 255) / 256) * 8;
     const int ostat_passes = (use_lists && !sgrid) ? 1 + std::max(0, (L - 7 + 7) / 8) : 1;
     const size_t ostat_bytes = sizeof(unsigned long long) * (ostat_stride * ostat_passes + 1);
-    CK(c.ostat.ensure(ostat_bytes));
+    for (int l = 0; l < nlanes; ++l) CK(c.lane[l].ostat.ensure(ostat_bytes));
     // Per-light shadow lists pay off when a query is expensive (many spheres); for tiny scenes the dense [light][hit]
     // layout is cheaper than building the lists.
     const int cps = 4 + L;                                       // counters per depth: n_live, n_hit, 2 debug work counters, n_sh[L]
@@ -1291,10 +1328,14 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     auto tl_mark = [&](const char* nm, int d, int from) { for (int i = from; i < tln; ++i) tlname.push_back(std::string(nm) + " d" + std::to_string(d) + (tln - from > 1 ? " j" + std::to_string(i - from) : "")); };
     // concurrency needs launches that do not touch shared constant memory
     const bool conc = !stats && !nofilter && S >= 64 && closest_res && (L == 0 || shadow_res || sgrid) && !c.no_conc
-                      && (!sgrid || cap <= ((size_t)12 << 20));     // with the grids, big frames measured faster in one stream (C4: 14.8 vs 15.9 ms; 1/8 of it: 2.7 vs 2.5)
-    cudaStream_t cs = conc ? c.chainStream : st, ss = conc ? c.shadeStream : st;
+                      && (!sgrid || cap <= ((size_t)12 << 20))      // with the grids, big frames measured faster in one stream (C4: 14.8 vs 15.9 ms; 1/8 of it: 2.7 vs 2.5)
+                      && (nlanes == 1 || c.lane_conc);              // two lanes: each lane's sequence in one stream unless B200RT_LANE_CONC=1
+    const bool forked = conc || nlanes > 1;                      // the frame's launches run on internal streams, forked from / joined to `st`
     const int nls = std::max(1, std::min(L, kSide));
-    if (conc) { CK(cudaEventRecord(c.evFork, st)); CK(cudaStreamWaitEvent(cs, c.evFork, 0)); }
+    if (forked) {
+        CK(cudaEventRecord(c.lane[0].evFork, st));
+        for (int l = 0; l < nlanes; ++l) CK(cudaStreamWaitEvent(c.lane[l].chainStream, c.lane[0].evFork, 0));
+    }
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     if (stats) { CK(cudaEventCreate(&ev0)); CK(cudaEventCreate(&ev1)); CK(cudaEventRecord(ev0, st)); }
 
@@ -1302,6 +1343,8 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     for (int d = 0; d <= depth; ++d) wts[d] = d == 0 ? 1.0f : (float)pow(a->refl, (double)d);     // trace.py:131 refl ** (i+1)
 
     for (int ch = 0; ch < nchunks; ++ch) {
+        Lane& ln = c.lane[ch % nlanes];
+        cudaStream_t cs = forked ? ln.chainStream : st, ss = conc ? ln.shadeStream : cs;
         FrameDev f{};
         f.pixel_loc = a->pixel_loc; f.cam = c.camDev.as<CamDev>();
         f.W = W; f.H = H; f.ns = ns;
@@ -1310,13 +1353,13 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         f.npix = (uint32_t)(f.x1 - f.x0) * (uint32_t)H; f.tiled = tiled ? 1 : 0;
         const size_t nslots = (size_t)f.npix * ns;
         uint32_t* ctr = c.ctr.as<uint32_t>() + (size_t)ch * ctr_stride;
-        float4* acc = c.acc.as<float4>();
+        float4* acc = ln.acc.as<float4>();
 
         tm.begin(2);
         CK(cudaMemsetAsync(acc, 0, sizeof(float4) * nslots, cs));
-        if (ns > 1) CK(cudaMemsetAsync(c.ostat.p, 0, ostat_bytes, cs));
-        k_raygen<<<(int)std::min<size_t>((nslots + 255) / 256, (size_t)small_grid), 256, 0, cs>>>(f, c.rayO[0].as<float4>(), c.rayD[0].as<float4>(), store_keys ? nullptr : c.hitKey[0].as<unsigned long long>(), ctr + 0,
-                                                                                                         c.ostat.as<unsigned long long>(), reinterpret_cast<uint32_t*>(c.ostat.as<unsigned long long>() + ostat_stride * ostat_passes));
+        if (ns > 1) CK(cudaMemsetAsync(ln.ostat.p, 0, ostat_bytes, cs));
+        k_raygen<<<(int)std::min<size_t>((nslots + 255) / 256, (size_t)small_grid), 256, 0, cs>>>(f, ln.rayO[0].as<float4>(), ln.rayD[0].as<float4>(), store_keys ? nullptr : ln.hitKey[0].as<unsigned long long>(), ctr + 0,
+                                                                                                         ln.ostat.as<unsigned long long>(), reinterpret_cast<uint32_t*>(ln.ostat.as<unsigned long long>() + ostat_stride * ostat_passes));
         CKL();
         tm.end(2);
 
@@ -1335,16 +1378,16 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             uint32_t* n_live = d == 0 ? ctr + 0 : ctr + cps * (d - 1) + 3;       // the hit list of depth d-1 is the ray queue of depth d
             uint32_t* wk = c.work.as<uint32_t>() + ((size_t)ch * (depth + 1) + d) * work_per_depth;      // k_isect3 group counters
             QueueDev q{};
-            q.rayO = c.rayO[b].as<float4>(); q.rayD = c.rayD[b].as<float4>(); q.hP = c.hP[hs].as<float4>();
-            q.hit = c.hitKey[b].as<unsigned long long>(); q.occl = sgrid ? nullptr : c.occl[hs].as<uint8_t>(); q.ocap = cap;
+            q.rayO = ln.rayO[b].as<float4>(); q.rayD = ln.rayD[b].as<float4>(); q.hP = ln.hP[hs].as<float4>();
+            q.hit = ln.hitKey[b].as<unsigned long long>(); q.occl = sgrid ? nullptr : ln.occl[hs].as<uint8_t>(); q.ocap = cap;
             q.slow = (stats && !(a->flags & B200RT_F_TIME_ONLY)) ? c.slow.as<unsigned long long>() : nullptr;
             ShadeDev s{};
             s.rayO = q.rayO; s.rayD = q.rayD; s.hit = q.hit;
-            s.rayO2 = c.rayO[b ^ 1].as<float4>(); s.rayD2 = c.rayD[b ^ 1].as<float4>(); s.hit2 = store_keys ? nullptr : c.hitKey[b ^ 1].as<unsigned long long>();
-            s.hP = c.hP[hs].as<float4>(); s.hN = c.hN[hs].as<float4>(); s.occl = sgrid ? nullptr : c.occl[hs].as<uint8_t>(); s.ocap = cap;
+            s.rayO2 = ln.rayO[b ^ 1].as<float4>(); s.rayD2 = ln.rayD[b ^ 1].as<float4>(); s.hit2 = store_keys ? nullptr : ln.hitKey[b ^ 1].as<unsigned long long>();
+            s.hP = ln.hP[hs].as<float4>(); s.hN = ln.hN[hs].as<float4>(); s.occl = sgrid ? nullptr : ln.occl[hs].as<uint8_t>(); s.ocap = cap;
             s.acc = acc;
             s.n_live = n_live; s.n_hit = cd + 3;
-            s.shidx = (use_lists && !sgrid) ? c.shidx[hs].as<uint32_t>() : nullptr; s.shcap = cap; s.n_sh = cd + 4;
+            s.shidx = (use_lists && !sgrid) ? ln.shidx[hs].as<uint32_t>() : nullptr; s.shcap = cap; s.n_sh = cd + 4;
             s.amb = (float)a->amb; s.lamb = (float)a->lamb; s.weight = wts[d]; s.emit_reflection = d < depth;
 
             tm.begin(0);
@@ -1356,8 +1399,8 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             tm.begin(2);
             bool scatter = false;
             if (regroup && d >= 1 && (d < depth || !c.no_sort_last)) {
-                SortDev so{ q.rayO, q.rayD, q.hit, n_live, c.sortGrid.as<GridDev>(), c.sortKey.as<uint2>(), c.sortHist.as<uint32_t>(), c.sortPart.as<uint32_t>(),
-                            c.sortBase.as<uint32_t>(), c.sortPerm.as<uint32_t>(), cd + 2, sort_nb, d < depth ? 1 : 0, nullptr };
+                SortDev so{ q.rayO, q.rayD, q.hit, n_live, c.sortGrid.as<GridDev>(), ln.sortKey.as<uint2>(), ln.sortHist.as<uint32_t>(), ln.sortPart.as<uint32_t>(),
+                            ln.sortBase.as<uint32_t>(), ln.sortPerm.as<uint32_t>(), cd + 2, sort_nb, d < depth ? 1 : 0, nullptr };
                 if (tlb) { so.tl = tlb + 2 * (size_t)tln++; tlname.push_back("sort d" + std::to_string(d)); }
                 k_key<<<small_grid, 256, 0, cs>>>(sc, so); CKL();
                 k_binsum<<<sort_nblk, 256, 0, cs>>>(so); CKL();
@@ -1370,15 +1413,15 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
                     s.perm = so.perm; s.n_live = cd + 2;                                  // k_setup walks the hits in bin order
                 }
             }
-            if (conc && d >= nsets) CK(cudaStreamWaitEvent(cs, c.evShade[hs], 0));        // set hs is free again
+            if (conc && d >= nsets) CK(cudaStreamWaitEvent(cs, ln.evShade[hs], 0));        // set hs is free again
             if (tlb) { s.tl = tlb + 2 * (size_t)tln++; tlname.push_back("setup d" + std::to_string(d)); }
-            s.ostat = c.ostat.as<unsigned long long>(); s.ostat_stride = ostat_stride; s.ticket = reinterpret_cast<uint32_t*>(s.ostat + ostat_stride * ostat_passes);
-            if (scatter) { k_setup_scatter<<<small_grid, 256, 0, cs>>>(sc, s, c.sortKey.as<uint2>(), c.sortBase.as<uint32_t>(), cd + 2); CKL(); }
+            s.ostat = ln.ostat.as<unsigned long long>(); s.ostat_stride = ostat_stride; s.ticket = reinterpret_cast<uint32_t*>(s.ostat + ostat_stride * ostat_passes);
+            if (scatter) { k_setup_scatter<<<small_grid, 256, 0, cs>>>(sc, s, ln.sortKey.as<uint2>(), ln.sortBase.as<uint32_t>(), cd + 2); CKL(); }
             else {
-                CK(cudaMemsetAsync(c.ostat.p, 0, ostat_bytes, cs));
+                CK(cudaMemsetAsync(ln.ostat.p, 0, ostat_bytes, cs));
                 k_setup<<<small_grid, 256, 0, cs>>>(sc, s); CKL();
             }
-            if (conc) CK(cudaEventRecord(c.evSetup[hs], cs));
+            if (conc) CK(cudaEventRecord(ln.evSetup[hs], cs));
             tm.end(2);
             if (L > 0) {
                 tm.begin(1);
@@ -1386,38 +1429,38 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
                 else if (sgrid) {                       // shadow queries + Lambert sum + accumulate in one kernel (shadow_grid.cuh)
                     ShadowGridArgs ga{ s.hP, s.hN, s.n_hit, acc, s.amb, s.lamb, s.weight, pv.bounds,
                                        q.slow ? cd + 4 : nullptr, q.slow, nullptr };        // (counters only in the diagnostic frame: B200RT_F_TIME_ONLY leaves shadow_traced 0)
-                    if (conc) CK(cudaStreamWaitEvent(ss, c.evSetup[hs], 0));
+                    if (conc) CK(cudaStreamWaitEvent(ss, ln.evSetup[hs], 0));
                     if (tlb) { ga.tl = tlb + 2 * (size_t)tln++; tlname.push_back("shadow+shade d" + std::to_string(d)); }
                     // grid: ~16 hits per thread, between 8 and 64 CTAs per SM (C4: 55 per SM measured 0.12 ms faster than 8; 1/8 of it stays at 8)
                     const int ssg = c.ss_grid > 0 ? c.sm_count * c.ss_grid
                                                   : (int)std::min<size_t>((size_t)c.sm_count * 64, std::max<size_t>((size_t)c.sm_count * 8, cap / (256 * 16)));
                     k_shadow_shade<<<ssg, 256, 0, ss>>>(sc, sg, ga); CKL();
-                    if (conc) CK(cudaEventRecord(c.evShade[hs], ss));
+                    if (conc) CK(cudaEventRecord(ln.evShade[hs], ss));
                 }
                 else {
                     ShadowPlan sp{};
-                    sp.list0 = s.shidx; sp.list1 = use_lists ? c.shidx2[hs].as<uint32_t>() : nullptr; sp.cap = cap;
+                    sp.list0 = s.shidx; sp.list1 = use_lists ? ln.shidx2[hs].as<uint32_t>() : nullptr; sp.cap = cap;
                     sp.n0 = use_lists ? cd + 4 : cd + 3; sp.n0_stride = use_lists ? 1 : 0;      // per-light list lengths n_sh[j], or the hit count
                     sp.work = wk + nsch; sp.rn = wk + nsch + (size_t)L * kMaxPass; sp.nreg = sh_np > 1 ? nreg : 0;
-                    if (conc) for (int k = 0; k < nls; ++k) CK(cudaStreamWaitEvent(c.lightStream[k], c.evSetup[hs], 0));
+                    if (conc) for (int k = 0; k < nls; ++k) CK(cudaStreamWaitEvent(ln.lightStream[k], ln.evSetup[hs], 0));
                     for (int j = 0; j < L; ++j) {
                         const int f0 = tln;
-                        CK(shadow_launch_light(icfg, sc, q, pv, nslots, sp, j, shadow_res, conc ? c.lightStream[j % nls] : cs, tlb, &tln));
+                        CK(shadow_launch_light(icfg, sc, q, pv, nslots, sp, j, shadow_res, conc ? ln.lightStream[j % nls] : cs, tlb, &tln));
                         for (int k = f0; k < tln; ++k) tlname.push_back("shadow d" + std::to_string(d) + " j" + std::to_string(j) + " p" + std::to_string(k - f0));
                     }
-                    if (conc) for (int k = 0; k < nls; ++k) { CK(cudaEventRecord(c.evLight[k], c.lightStream[k])); CK(cudaStreamWaitEvent(ss, c.evLight[k], 0)); }
+                    if (conc) for (int k = 0; k < nls; ++k) { CK(cudaEventRecord(ln.evLight[k], ln.lightStream[k])); CK(cudaStreamWaitEvent(ss, ln.evLight[k], 0)); }
                 }
                 tm.end(1);
-            } else if (conc) CK(cudaStreamWaitEvent(ss, c.evSetup[hs], 0));
+            } else if (conc) CK(cudaStreamWaitEvent(ss, ln.evSetup[hs], 0));
             if (!(sgrid && L > 0 && !nofilter)) {
                 tm.begin(2);
                 if (tlb) { s.tl = tlb + 2 * (size_t)tln++; tlname.push_back("shade d" + std::to_string(d)); }
                 k_shade<<<small_grid, 256, 0, ss>>>(sc, s); CKL();
-                if (conc) CK(cudaEventRecord(c.evShade[hs], ss));
+                if (conc) CK(cudaEventRecord(ln.evShade[hs], ss));
                 tm.end(2);
             }
         }
-        if (conc) CK(cudaStreamWaitEvent(cs, c.evShade[depth % nsets], 0));               // (ss is in order: every depth is shaded)
+        if (conc) CK(cudaStreamWaitEvent(cs, ln.evShade[depth % nsets], 0));               // (ss is in order: every depth is shaded)
 
         tm.begin(2);
         const int unswap = (a->flags & B200RT_F_UNSWAP_GB) ? 1 : 0;
@@ -1429,7 +1472,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         CKL();
         tm.end(2);
     }
-    if (conc) { CK(cudaEventRecord(c.evJoin, cs)); CK(cudaStreamWaitEvent(st, c.evJoin, 0)); }
+    if (forked) for (int l = 0; l < nlanes; ++l) { CK(cudaEventRecord(c.lane[l].evJoin, c.lane[l].chainStream)); CK(cudaStreamWaitEvent(st, c.lane[l].evJoin, 0)); }
     if (tlb) {
         CK(cudaStreamSynchronize(st));
         std::vector<unsigned long long> h(2 * (size_t)tln); CK(cudaMemcpy(h.data(), tlb, sizeof(unsigned long long) * h.size(), cudaMemcpyDeviceToHost));

@@ -1,0 +1,7 @@
+#!/bin/bash
+cd "$(dirname "$0")/.."
+run() { env "$@" python bench.py --no-cpu --no-dense --steps 20 --warmup 3 2>/dev/null | python -c "import json,sys; j=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('  ms', round(j['ms_per_step'],4), 'e2e', round(j['e2e']['ms_per_step'],4), {k: round(v,3) for k,v in j['roofline']['exact_culled']['kernel_ms'].items()})"; }
+for w in 8 4 2; do
+  echo "== world $w"
+  for knobs in "X=1" "B200RT_NO_LANES=1" "B200RT_LANE_CONC=1"; do echo " $knobs"; run B200RT_EMULATE_WORLD=$w $knobs; done
+done
