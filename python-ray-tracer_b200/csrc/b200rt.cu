@@ -26,6 +26,7 @@
 #include "rt_math.cuh"
 #include "isect3.cuh"
 #include "shadow_grid.cuh"
+#include "closest_grid.cuh"
 
 namespace b200rt {
 
@@ -40,8 +41,9 @@ namespace b200rt {
 // k_cache_commit stamps the groups built in this call.  Only the camera pivot table (k_pivot, j == L) is per frame.
 //   cs[0] scene version   cs[1..3] version the groups {base tables, light grids, regrouping box} were built from
 //   cs[4] key of the regrouping box (position bits, direction cells)   cs[5..7] S, L, Pl of the saved copy   cs[8] CTA ticket
+//   cs[9] version the closest-hit grid (closest_grid.cuh) was built from
 // ------------------------------------------------------------------------------------------------
-enum { kCsVersion = 0, kCsBase = 1, kCsSgrid = 2, kCsGrid = 3, kCsGridKey = 4, kCsS = 5, kCsL = 6, kCsPl = 7, kCsTicket = 8, kCsWords = 16 };
+enum { kCsVersion = 0, kCsBase = 1, kCsSgrid = 2, kCsGrid = 3, kCsGridKey = 4, kCsS = 5, kCsL = 6, kCsPl = 7, kCsTicket = 8, kCsCgrid = 9, kCsWords = 16 };
 
 __global__ void __launch_bounds__(256) k_scene_cmp(const float* __restrict__ spheres, int S, const float* __restrict__ lights, int L,
                                                   const float* __restrict__ planes, int Pl, uint32_t* saved, uint32_t* cs, float* cmax) {
@@ -71,8 +73,9 @@ __global__ void __launch_bounds__(256) k_scene_cmp(const float* __restrict__ sph
         }
     }
 }
-__global__ void k_cache_commit(uint32_t* cs, int base, int sgrid, int grid, uint32_t gridkey) {
+__global__ void k_cache_commit(uint32_t* cs, int base, int sgrid, int grid, uint32_t gridkey, int cgrid) {
     const uint32_t v = cs[kCsVersion];
+    if (cgrid) cs[kCsCgrid] = v;
     if (base) cs[kCsBase] = v;
     if (sgrid) cs[kCsSgrid] = v;
     if (grid) { cs[kCsGrid] = v; cs[kCsGridKey] = gridkey; }
@@ -1030,6 +1033,8 @@ struct DevCtx {
     Buf ctr, work, slow, tl;
     Buf sgCells, sgTab, sgCone;                                      // per-light direction grids of the shadow queries (shadow_grid.cuh)
     Buf sortGrid;                                                    // bounding box / cell counts of the regrouping (scene-level)
+    Buf cgHdr, cgStart, cgCursor, cgIds, cgBig;                      // uniform grid of the spheres for per-ray closest-hit queries (closest_grid.cuh)
+    int cgrid_from = 1; size_t cgrid_max_paths = (size_t)12 << 20;   // env B200RT_CGRID_FROM (first depth served by the grid; 99: never), B200RT_CGRID_MAX_PATHS
     bool no_lanes = false, lane_conc = false;                        // env B200RT_NO_LANES, B200RT_LANE_CONC
     bool no_sgrid = false, no_clus = false, no_sort_last = true; int ss_grid = 0; int sgrid_min_s = 1; bool no_sort = false; int sort_posbits = -1, sort_dirn = -1;     // env B200RT_NO_SORT, B200RT_SORT_POSBITS, B200RT_SORT_DIRN (-1: chosen from the queue size)
     int npre = 1, pre[6] = {256, 0, 0, 0, 0, 0};                    // leading shadow passes (env B200RT_PASSES=a,b,...; multiples of 8)
@@ -1052,7 +1057,7 @@ struct DevCtx {
         if (captureStream) { cudaStreamDestroy(captureStream); captureStream = nullptr; }
         rawScene.release(); cacheState.release(); camDev.release();
         Buf* all[] = { &sphA, &sphB, &sphCol, &plO, &plN, &plNu, &plCol, &lights, &cmax, &pivTab, &pivPos, &pivPerm, &pivRad, &pivClus, &stage,
-                       &tl, &ctr, &work, &slow, &sortGrid, &sgCells, &sgTab, &sgCone, &hostResult, &hostPixelLoc, &imgOut, &batchScene };
+                       &tl, &ctr, &work, &slow, &sortGrid, &cgHdr, &cgStart, &cgCursor, &cgIds, &cgBig, &sgCells, &sgTab, &sgCone, &hostResult, &hostPixelLoc, &imgOut, &batchScene };
         for (Buf* b : all) b->release();
         for (int l = 0; l < kLanes; ++l) lane[l].release();
         if (done) { cudaEventDestroy(done); done = nullptr; } has_done = false; init = false;
@@ -1136,7 +1141,9 @@ int init_ctx(DevCtx& c, int device) {
     { const char* e = getenv("B200RT_NO_SCATTER"); c.no_scatter = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_GRAPH_ALL"); c.graph_all = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_NO_SPLIT"); c.no_split = e && atoi(e) != 0; }
-    { const char* e = getenv("B200RT_NO_LANES"); c.no_lanes = e && atoi(e) != 0; }
+    { const char* e = getenv("B200RT_LANES"); c.no_lanes = !(e && atoi(e) != 0); }       // two-lane wavefronts: measured slower, opt-in
+    { const char* e = getenv("B200RT_CGRID_FROM"); if (e) c.cgrid_from = std::max(1, atoi(e)); }
+    { const char* e = getenv("B200RT_CGRID_MAX_PATHS"); if (e) c.cgrid_max_paths = (size_t)std::max(0ll, atoll(e)); }
     { const char* e = getenv("B200RT_LANE_CONC"); c.lane_conc = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_SGRID_MIN_S"); if (e) c.sgrid_min_s = std::max(1, atoi(e)); }
     { const char* e = getenv("B200RT_SORT_POSBITS"); if (e) c.sort_posbits = std::min(18, std::max(0, atoi(e))); }
@@ -1235,6 +1242,23 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         k_sgrid_tab<<<(L * S + 255) / 256, 256, 0, st>>>(sc, sg, cst); CKL();
         k_sgrid_build<<<dim3(kSgCells / 256, L, kSgTiers), 256, 0, st>>>(sc, sg, cst); CKL();
     } else if (shadow_res) CK(shadow_upload_resident(pv, Spad, L, st));
+    // Closest-hit queries of bounce rays through a uniform grid of the spheres, one ray per thread (closest_grid.cuh), where
+    // the beam method loses its edge: small queues (one GPU's share of a sharded frame).
+    const size_t frame_paths = (size_t)ncols * H * ns;
+    const bool cgrid = cull && !nofilter && S >= 64 && S <= 65535 && depth >= 1 && c.cgrid_from <= depth && frame_paths <= c.cgrid_max_paths &&
+                       !(a->flags & B200RT_F_NO_CGRID);
+    CGridDev cg{};
+    const int cg_max_cells = (int)std::min<size_t>((size_t)1 << 21, (size_t)32 * S + 4096);
+    if (cgrid) {
+        const size_t ids_cap = (size_t)64 * S + 4096;
+        CK(c.cgHdr.ensure(sizeof(CGridHdr))); CK(c.cgStart.ensure(sizeof(uint32_t) * ((size_t)cg_max_cells + 1))); CK(c.cgCursor.ensure(sizeof(uint32_t) * (size_t)cg_max_cells));
+        CK(c.cgIds.ensure(sizeof(uint16_t) * ids_cap)); CK(c.cgBig.ensure(sizeof(uint32_t) * kCgMaxBig));
+        cg = CGridDev{ c.cgHdr.as<CGridHdr>(), c.cgStart.as<uint32_t>(), c.cgCursor.as<uint32_t>(), c.cgIds.as<uint16_t>(), c.cgBig.as<uint32_t>(), ids_cap };
+        k_cg_setup<<<1, 256, 0, st>>>(sc, cg, cg_max_cells, cst, kCsCgrid); CKL();
+        k_cg_bin<<<(S + 255) / 256, 256, 0, st>>>(sc, cg, 0, cst, kCsCgrid); CKL();
+        k_cg_scan<<<1, 1024, 0, st>>>(cg, cg_max_cells, cst, kCsCgrid); CKL();
+        k_cg_bin<<<(S + 255) / 256, 256, 0, st>>>(sc, cg, 1, cst, kCsCgrid); CKL();
+    }
     IsectCfg icfg{ c.sm_count, c.force_nr, c.force_nr0, dense ? 0 : c.npre, {0, 0, 0, 0, 0, 0} };
     for (int k = 0; k < icfg.npre; ++k) icfg.pre[k] = c.pre[k];
 
@@ -1289,7 +1313,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         CK(c.sortGrid.ensure(sizeof(GridDev)));
         k_grid<<<1, 256, 0, st>>>(sc, sort_posbits, sort_dirn, c.sortGrid.as<GridDev>(), cst, (uint32_t)(sort_posbits * 64 + sort_dirn)); CKL();
     }
-    k_cache_commit<<<1, 1, 0, st>>>(cst, 1, sgrid ? 1 : 0, regroup ? 1 : 0, (uint32_t)(sort_posbits * 64 + sort_dirn)); CKL();
+    k_cache_commit<<<1, 1, 0, st>>>(cst, 1, sgrid ? 1 : 0, regroup ? 1 : 0, (uint32_t)(sort_posbits * 64 + sort_dirn), cgrid ? 1 : 0); CKL();
     // k_setup's ordered compaction: [pass][chunk of 256 rays][8 queues] status words + the chunk ticket, zeroed before every launch
     const size_t ostat_stride = ((cap + 255) / 256) * 8;
     const int ostat_passes = (use_lists && !sgrid) ? 1 + std::max(0, (L - 7 + 7) / 8) : 1;
@@ -1394,7 +1418,16 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             q.n_in = n_live; q.work = cd + 1;
             if (nofilter)                     { if (int rc = launch_intersect<false>(c, sc, q, true, cs)) return rc; }
             else if (d == 0 && !c.no_pivot)   { const int f0 = tln; CK(isect3_launch_closest<1>(icfg, sc, q, pv, nslots, wk, closest_res, cs, tlb, &tln)); tl_mark("closest<1>", d, f0); }
-            else                              { const int f0 = tln; CK(isect3_launch_closest<0>(icfg, sc, q, pv, nslots, wk, closest_res, cs, tlb, &tln)); tl_mark("closest<0>", d, f0); }
+            else {
+                if (cgrid && d >= c.cgrid_from) {               // per-ray grid walk; k_isect3 below only takes the queue if the grid turned out unusable (cd[1] stays 0 otherwise)
+                    CGridArgs ca{ q.rayO, q.rayD, n_live, q.hit, nullptr, q.slow, cd + 1 };
+                    if (tlb) { ca.tl = tlb + 2 * (size_t)tln++; tlname.push_back("closest<grid> d" + std::to_string(d)); }
+                    const int cgg = (int)std::min<size_t>((size_t)c.sm_count * 32, std::max<size_t>((size_t)c.sm_count * 8, cap / (256 * 4)));
+                    k_closest_grid<<<cgg, 256, 0, cs>>>(sc, cg, ca); CKL();
+                    q.n_in = cd + 1;
+                }
+                const int f0 = tln; CK(isect3_launch_closest<0>(icfg, sc, q, pv, nslots, wk, closest_res, cs, tlb, &tln)); tl_mark("closest<0>", d, f0);
+            }
             tm.end(0);
             tm.begin(2);
             bool scatter = false;

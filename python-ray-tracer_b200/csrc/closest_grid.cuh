@@ -1,0 +1,231 @@
+// closest_grid.cuh — closest-hit queries of incoherent (bounce) rays through a uniform 3-D grid of the spheres, one ray
+// per thread (reference trace.py:7-41, called at :53 for the reflection traces of :128).
+//
+// Why a second closest-hit kernel.  k_isect3 (isect3.cuh) is a beam method: 128 rays share one culled sphere list, which is
+// what makes primary rays cost 0.6 % of the brute-force tests.  Its cost per ray rises as the rays of a group diverge — deeper
+// bounces, and above all SMALLER queues: the regrouping bins hold a fixed number of rays, so at 1/8 of the rays (one GPU of
+// eight) a bin spans 8x the volume of ray space and the groups keep 1.6x the sphere pairs, 2x as many take the dense scan
+// (profiles/r02_cullstats.txt; second bounce: 68 ns per ray at the full C4 frame, 149 ns at 1/8 of it).  A per-ray traversal
+// costs the same per ray at any queue size.
+//
+// Exactness (the image stays byte-identical to brute force; tests compare with B200RT_F_DENSE / B200RT_F_NO_FILTER):
+//   * every candidate is decided by sphere_exact() on the real ray — the function every other path uses — and the closest hit
+//     is the minimum over (t, sphere id), i.e. "smallest t, lowest index on a tie" (trace.py:26); planes afterwards with a
+//     strict `<`, so they lose ties against spheres (trace.py:36);
+//   * the grid only has to offer every sphere the ray can hit, in a cell the walk visits before it stops.  A sphere is listed in
+//     every cell its box, inflated by eps = 2e-3 + 1e-3 r, overlaps: eps covers the exact test's slack (it may report a hit up to
+//     ~1e-4 outside the sphere while coordinates stay below 256) and the rounding of the walk (a cell grazed within ~1e-5 of a
+//     corner may be skipped: whatever is hit there is also listed in the neighbouring cell that is visited);
+//   * the walk stops after a cell only when the best hit so far lies clearly before the cell's exit (margin 1e-3 + 1e-5 t): every
+//     sphere not yet offered can only be hit beyond that exit;
+//   * spheres whose inflated box covers more than kCgBigCells cells are kept on a short list that every ray tests;
+//     scenes outside the coordinate range (max |C| + max r > 256) do not use the grid at all (the launcher falls back to k_isect3).
+#pragma once
+#include "isect3.cuh"
+
+namespace b200rt {
+
+constexpr int kCgMaxDim = 128;            // cells per axis, at most
+constexpr int kCgBigCells = 512;          // a sphere covering more cells than this goes on the "big" list
+constexpr int kCgMaxBig = 256;            // capacity of the big list; more big spheres than that: the grid is not used
+constexpr float kCgRange = 256.f;
+
+struct CGridHdr {                         // device-resident description of the grid (written by k_cg_setup)
+    float lo[3], inv[3], edge[3];         // cell (x,y,z) = floor((p - lo) * inv); edge = 1 / inv
+    int n[3]; int ncells;
+    int nbig; int ok;                     // ok = 0: grid unusable for this scene (range / big-list overflow): use k_isect3
+    uint32_t total;                       // entries of the id list
+};
+
+struct CGridDev {
+    CGridHdr* hdr;
+    uint32_t* start;                      // [ncells + 1] exclusive prefix of the cells' list lengths (counts before the scan)
+    uint32_t* cursor;                     // [ncells] fill cursors
+    uint16_t* ids;                        // [total] sphere ids, cell by cell
+    uint32_t* big;                        // [kCgMaxBig] ids of the big spheres
+    size_t ids_cap;                       // capacity of `ids` (entries)
+};
+
+// Scene bounds -> grid dimensions.  One CTA.  ~2 spheres per cell: n_target = 4 S cells, cubic cells, <= kCgMaxDim per axis.
+__global__ void __launch_bounds__(256) k_cg_setup(SceneDev sc, CGridDev g, int max_cells, const uint32_t* cs, int cs_group) {
+    if (cs[cs_group] == cs[0]) return;
+    __shared__ int s_ncells;
+    __shared__ float smin[3][256], smax[3][256];
+    float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f};
+    for (int i = threadIdx.x; i < sc.S; i += blockDim.x) {
+        const float4 sp = sc.sphB[i]; const float r = sqrtf(fmaxf(sp.w, 0.f)) * 1.001f + 2e-3f; const float c[3] = {sp.x, sp.y, sp.z};
+        for (int a = 0; a < 3; ++a) { lo[a] = fminf(lo[a], c[a] - r); hi[a] = fmaxf(hi[a], c[a] + r); }
+    }
+    for (int a = 0; a < 3; ++a) { smin[a][threadIdx.x] = lo[a]; smax[a][threadIdx.x] = hi[a]; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int a = 0; a < 3; ++a) for (int t = 1; t < 256; ++t) { lo[a] = fminf(lo[a], smin[a][t]); hi[a] = fmaxf(hi[a], smax[a][t]); }
+        CGridHdr h{};
+        float ext[3]; float vol = 1.f;
+        for (int a = 0; a < 3; ++a) { if (!(hi[a] > lo[a])) { lo[a] = 0.f; hi[a] = 1.f; } const float pad = 1e-3f * (hi[a] - lo[a]) + 1e-3f; lo[a] -= pad; hi[a] += pad; ext[a] = hi[a] - lo[a]; vol *= ext[a]; }
+        const float target = fminf(fmaxf(4.f * (float)sc.S, 64.f), 262144.f);
+        const float edge = cbrtf(vol / target);
+        h.ncells = 1;
+        for (int a = 0; a < 3; ++a) {
+            h.n[a] = max(1, min(kCgMaxDim, (int)ceilf(ext[a] / fmaxf(edge, 1e-20f))));
+            h.lo[a] = lo[a]; h.edge[a] = ext[a] / (float)h.n[a]; h.inv[a] = (float)h.n[a] / ext[a];
+            h.ncells *= h.n[a];
+        }
+        h.ok = (sc.S > 0 && sc.cmax[0] + sc.cmax[1] <= kCgRange && vol > 0.f && vol < 3e38f && h.ncells <= max_cells) ? 1 : 0;       // (NaN -> 0)
+        h.nbig = 0; h.total = 0;
+        *g.hdr = h;
+        s_ncells = h.ok ? h.ncells : 0;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i <= s_ncells; i += blockDim.x) g.start[i] = 0u;       // the counts of pass 0 start from zero
+}
+
+__device__ __forceinline__ void cg_cell_range(const CGridHdr& h, float4 sp, int (&c0)[3], int (&c1)[3]) {
+    const float r = sqrtf(fmaxf(sp.w, 0.f)) * 1.001f + 2e-3f;                 // r + eps, rounded generously
+    const float c[3] = {sp.x, sp.y, sp.z};
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        c0[a] = max(0, min(h.n[a] - 1, (int)floorf((c[a] - r - h.lo[a]) * h.inv[a] - 1e-3f)));
+        c1[a] = max(0, min(h.n[a] - 1, (int)floorf((c[a] + r - h.lo[a]) * h.inv[a] + 1e-3f)));
+    }
+}
+
+// pass 0: count the cells' list lengths (and collect the big spheres); pass 1: fill the lists.  One thread per sphere.
+__global__ void __launch_bounds__(256) k_cg_bin(SceneDev sc, CGridDev g, int pass, const uint32_t* cs, int cs_group) {
+    if (cs[cs_group] == cs[0]) return;
+    const CGridHdr h = *g.hdr;
+    if (!h.ok) return;
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= sc.S) return;
+    int c0[3], c1[3]; cg_cell_range(h, sc.sphB[s], c0, c1);
+    const long long ncov = (long long)(c1[0] - c0[0] + 1) * (c1[1] - c0[1] + 1) * (c1[2] - c0[2] + 1);
+    if (ncov > kCgBigCells) {
+        if (pass == 0) { const int k = atomicAdd(&g.hdr->nbig, 1); if (k < kCgMaxBig) g.big[k] = (uint32_t)s; }
+        return;
+    }
+    for (int z = c0[2]; z <= c1[2]; ++z) for (int y = c0[1]; y <= c1[1]; ++y) for (int x = c0[0]; x <= c1[0]; ++x) {
+        const int cell = (z * h.n[1] + y) * h.n[0] + x;
+        if (pass == 0) atomicAdd(&g.start[cell], 1u);
+        else { const uint32_t k = atomicAdd(&g.cursor[cell], 1u); if ((size_t)k < g.ids_cap) g.ids[k] = (uint16_t)s; }
+    }
+}
+
+// Exclusive scan of the counts (one CTA; <= 2^21 cells, a few per thread) and validation.  cursor[cell] = start[cell].
+__global__ void __launch_bounds__(1024) k_cg_scan(CGridDev g, int max_cells, const uint32_t* cs, int cs_group) {
+    if (cs[cs_group] == cs[0]) return;
+    __shared__ uint32_t swarp[32]; __shared__ uint32_t s_carry;
+    const CGridHdr h = *g.hdr;
+    if (!h.ok) return;
+    if (threadIdx.x == 0) s_carry = 0;
+    __syncthreads();
+    const int n = min(h.ncells, max_cells);
+    for (int base = 0; base < n; base += 1024) {
+        const int i = base + (int)threadIdx.x;
+        const uint32_t v = i < n ? g.start[i] : 0u;
+        uint32_t x = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, d); if ((int)(threadIdx.x & 31) >= d) x += y; }
+        if ((threadIdx.x & 31) == 31) swarp[threadIdx.x >> 5] = x;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            uint32_t w = swarp[threadIdx.x], y2 = w;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, y2, d); if ((int)threadIdx.x >= d) y2 += y; }
+            swarp[threadIdx.x] = y2 - w;                         // exclusive offset of each warp
+        }
+        __syncthreads();
+        const uint32_t excl = s_carry + swarp[threadIdx.x >> 5] + x - v;
+        if (i < n) { g.start[i] = excl; g.cursor[i] = excl; }
+        __syncthreads();
+        if (threadIdx.x == 1023) s_carry = excl + v;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        g.start[n] = s_carry;
+        g.hdr->total = s_carry;
+        if ((size_t)s_carry > g.ids_cap || h.nbig > kCgMaxBig || h.ncells > max_cells) g.hdr->ok = 0;      // does not fit: the launcher's kernels fall back
+    }
+}
+
+struct CGridArgs {
+    const float4* rayO; const float4* rayD; const uint32_t* n_in;
+    unsigned long long* hit;                 // (float bits of t) << 32 | id per ray; written for every ray
+    unsigned long long* tl;                  // diagnostic timeline slot; may be null
+    unsigned long long* slow;                // diagnostics: [1] exact tests, [10] cell steps; may be null
+    uint32_t* fallback;                      // stays 0 when the grid served the queue; grid unusable (hdr.ok == 0): set to the queue length, which is
+                                             // the ray count of the k_isect3 launch that follows (an empty launch otherwise)
+};
+
+// One thread per ray: Amanatides-Woo walk through the cells, sphere_exact on every listed sphere, planes last.
+__global__ void __launch_bounds__(256) k_closest_grid(SceneDev sc, CGridDev g, CGridArgs a) {
+    if (a.tl && threadIdx.x == 0) atomicMin(a.tl, globaltimer_ns());
+    const CGridHdr h = *g.hdr;
+    const uint32_t n = *a.n_in;
+    if (!h.ok) { if (blockIdx.x == 0 && threadIdx.x == 0) *a.fallback = n; return; }       // the caller's k_isect3 launch then takes the whole queue
+    unsigned long long n_exact = 0, n_steps = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float4 o4 = a.rayO[i], d4 = a.rayD[i];
+        const V3 O = mk(o4.x, o4.y, o4.z), D = mk(d4.x, d4.y, d4.z);
+        float best = kTMax; uint32_t bid = 0xffffffffu;
+        auto offer = [&](uint32_t sid) {
+            const float4 sp = __ldg(&sc.sphB[sid]);
+            const float t = sphere_exact(O, D, sp.x, sp.y, sp.z, sp.w);
+            if (a.slow) ++n_exact;
+            if (t > 0.f && (t < best || (t == best && sid < bid))) { best = t; bid = sid; }             // trace.py:26-29: smallest t, lowest index on a tie
+        };
+        for (int k = 0; k < h.nbig; ++k) offer(g.big[k]);
+        // clip the ray to the grid's box (slab test, conservative: box grown by a cell fraction)
+        const float o[3] = {O.x, O.y, O.z}, d[3] = {D.x, D.y, D.z};
+        float t0 = 0.f, t1 = kTMax;
+        bool miss = false;
+#pragma unroll
+        for (int ax = 0; ax < 3; ++ax) {
+            const float lo = h.lo[ax] - 1e-3f * h.edge[ax], hi = h.lo[ax] + (float)h.n[ax] * h.edge[ax] + 1e-3f * h.edge[ax];
+            if (fabsf(d[ax]) < 1e-20f) { if (o[ax] < lo || o[ax] > hi) miss = true; }
+            else {
+                const float inv = 1.f / d[ax];
+                float ta = (lo - o[ax]) * inv, tb = (hi - o[ax]) * inv;
+                if (ta > tb) { const float tt = ta; ta = tb; tb = tt; }
+                t0 = fmaxf(t0, ta - 1e-4f * fabsf(ta)); t1 = fminf(t1, tb + 1e-4f * fabsf(tb));
+            }
+        }
+        if (!miss && t0 <= t1) {
+            int c[3], step[3]; float tmax[3], tdel[3];
+#pragma unroll
+            for (int ax = 0; ax < 3; ++ax) {
+                const float p = fmaf(t0, d[ax], o[ax]);
+                c[ax] = max(0, min(h.n[ax] - 1, (int)floorf((p - h.lo[ax]) * h.inv[ax])));
+                if (d[ax] > 1e-20f)       { step[ax] = 1;  tdel[ax] = h.edge[ax] / d[ax];  tmax[ax] = (h.lo[ax] + (float)(c[ax] + 1) * h.edge[ax] - o[ax]) / d[ax]; }
+                else if (d[ax] < -1e-20f) { step[ax] = -1; tdel[ax] = -h.edge[ax] / d[ax]; tmax[ax] = (h.lo[ax] + (float)c[ax] * h.edge[ax] - o[ax]) / d[ax]; }
+                else                      { step[ax] = 0;  tdel[ax] = 3e38f; tmax[ax] = 3e38f; }
+            }
+            for (;;) {
+                const int cell = (c[2] * h.n[1] + c[1]) * h.n[0] + c[0];
+                const uint32_t s0 = __ldg(&g.start[cell]), s1 = __ldg(&g.start[cell + 1]);
+                for (uint32_t k = s0; k < s1; ++k) offer((uint32_t)__ldg(&g.ids[k]));
+                if (a.slow) ++n_steps;
+                const float texit = fminf(tmax[0], fminf(tmax[1], tmax[2]));
+                if (best < texit - (1e-3f + 1e-5f * texit) || texit > t1) break;       // nothing beyond this cell can be closer / the ray has left the box
+                const int ax = (tmax[0] <= tmax[1] && tmax[0] <= tmax[2]) ? 0 : (tmax[1] <= tmax[2] ? 1 : 2);
+                // (written without dynamic indexing: the three axes stay in registers)
+                if (ax == 0) { c[0] += step[0]; tmax[0] += tdel[0]; if (c[0] < 0 || c[0] >= h.n[0]) break; }
+                else if (ax == 1) { c[1] += step[1]; tmax[1] += tdel[1]; if (c[1] < 0 || c[1] >= h.n[1]) break; }
+                else { c[2] += step[2]; tmax[2] += tdel[2]; if (c[2] < 0 || c[2] >= h.n[2]) break; }
+            }
+        }
+        int id = (int)bid;
+        for (int pl = 0; pl < sc.Pl; ++pl) {                                                             // trace.py:32-39
+            const float t = plane_exact(O, D, __ldg(&sc.plO[pl]), __ldg(&sc.plN[pl]));
+            if (t > 0.f && t < best) { best = t; id = sc.S + pl; }
+        }
+        a.hit[i] = ((unsigned long long)__float_as_uint(best) << 32) | (uint32_t)id;                    // nothing hit: (999.0f, -1) = kNoHit
+    }
+    if (a.slow) {
+#pragma unroll
+        for (int dd = 16; dd > 0; dd >>= 1) { n_exact += __shfl_xor_sync(0xffffffffu, n_exact, dd); n_steps += __shfl_xor_sync(0xffffffffu, n_steps, dd); }
+        if (lane_id() == 0) { if (n_exact) atomicAdd(a.slow + 1, n_exact); if (n_steps) atomicAdd(a.slow + 10, n_steps); }
+    }
+    if (a.tl && threadIdx.x == 0) atomicMax(a.tl + 1, globaltimer_ns());
+}
+
+}  // namespace b200rt

@@ -433,3 +433,40 @@ def test_filter_margin_stress_scenes(case):
     assert np.array_equal(got, exact), (case, int((got != exact).sum()))
     assert np.array_equal(got, _cuda(g, flags=_lib.F_DENSE)), case
     assert np.array_equal(got, _cuda(g, flags=_lib.F_NO_SGRID)), case
+
+
+@pytest.mark.parametrize("S,W,H,depth,aa,seed", [(1024, 512, 256, 3, False, 31), (300, 256, 144, 2, True, 32), (2500, 192, 128, 2, False, 33), (64, 128, 96, 4, False, 34)])
+def test_closest_hit_grid_equals_beam_scan_and_brute_force(S, W, H, depth, aa, seed):
+    """Bounce rays of small frames find their closest hit by a per-ray walk through a uniform grid of the spheres
+    (csrc/closest_grid.cuh).  Same bytes as the beam-culled scan (B200RT_F_NO_CGRID), brute force and the unfiltered exact test."""
+    from b200rt import _lib
+    g = _synthetic(S, 3, 1, W, H, depth, aa, seed=seed)
+    got, st = _cuda(g, stats=True)
+    scan, st_scan = _cuda(g, flags=_lib.F_NO_CGRID, stats=True)
+    assert np.array_equal(got, scan), "grid walk differs from the beam-culled scan"
+    assert st["rays"] == st_scan["rays"]
+    assert st["tests_general"] < st_scan["tests_general"]            # the bounce queries did not run through k_isect3
+    assert np.array_equal(got, _cuda(g, flags=_lib.F_DENSE))
+    if S <= 1024:
+        assert np.array_equal(got, _cuda(g, flags=_lib.F_NO_FILTER))
+
+
+@pytest.mark.parametrize("case", ["huge_sphere_on_big_list", "out_of_range_falls_back", "flat_scene", "camera_inside_sphere"])
+def test_closest_hit_grid_edge_cases(case):
+    from b200rt import _lib
+    from b200rt.scene import Camera
+    g = _synthetic(200, 2, 1, 256, 144, 3, False, seed=41)
+    sp = g["spheres"]
+    if case == "huge_sphere_on_big_list":
+        sp[0:3, 0] = [6.0, 0.0, -40.0]; sp[3, 0] = 41.0             # a dome under the scene: covers most cells
+        sp[0:3, 1] = [4.0, 1.0, 3.0]; sp[3, 1] = 2.5
+    elif case == "out_of_range_falls_back":
+        sp[0:3, 5] = [300.0, 10.0, 2.0]; sp[3, 5] = 1.0              # max |C| > 256: the grid is unusable, k_isect3 takes the queue
+    elif case == "flat_scene":
+        sp[2] = sp[3]                                                # all spheres resting on the plane: one layer of cells
+    elif case == "camera_inside_sphere":
+        sp[0:3, 0] = [-2.0, 0.0, 2.0]; sp[3, 0] = 5.0
+    got = _cuda(g)
+    assert got.any()
+    assert np.array_equal(got, _cuda(g, flags=_lib.F_NO_CGRID)), case
+    assert np.array_equal(got, _cuda(g, flags=_lib.F_NO_FILTER)), case
