@@ -1033,8 +1033,10 @@ struct DevCtx {
     Buf ctr, work, slow, tl;
     Buf sgCells, sgTab, sgCone;                                      // per-light direction grids of the shadow queries (shadow_grid.cuh)
     Buf sortGrid;                                                    // bounding box / cell counts of the regrouping (scene-level)
-    Buf cgHdr, cgStart, cgCursor, cgIds, cgBig;                      // uniform grid of the spheres for per-ray closest-hit queries (closest_grid.cuh)
-    int cgrid_from = 1; size_t cgrid_max_paths = (size_t)12 << 20;   // env B200RT_CGRID_FROM (first depth served by the grid; 99: never), B200RT_CGRID_MAX_PATHS
+    Buf cgHdr, cgStart, cgCursor, cgIds, cgBig, cgRec;                      // uniform grid of the spheres for per-ray closest-hit queries (closest_grid.cuh)
+    int cgrid_ctas = 8;                                              // env B200RT_CGRID_CTAS: CTAs per SM of k_closest_grid
+    float cgrid_density = 2.f;                                       // env B200RT_CGRID_DENSITY: cells per sphere the grid aims at
+    int cgrid_from = 1; size_t cgrid_max_paths = (size_t)20 << 20, cgrid_nosort_paths = (size_t)10 << 20;   // env B200RT_CGRID_FROM (first depth served by the grid; 99: never), B200RT_CGRID_MAX_PATHS
     bool no_lanes = false, lane_conc = false;                        // env B200RT_NO_LANES, B200RT_LANE_CONC
     bool no_sgrid = false, no_clus = false, no_sort_last = true; int ss_grid = 0; int sgrid_min_s = 1; bool no_sort = false; int sort_posbits = -1, sort_dirn = -1;     // env B200RT_NO_SORT, B200RT_SORT_POSBITS, B200RT_SORT_DIRN (-1: chosen from the queue size)
     int npre = 1, pre[6] = {256, 0, 0, 0, 0, 0};                    // leading shadow passes (env B200RT_PASSES=a,b,...; multiples of 8)
@@ -1057,7 +1059,7 @@ struct DevCtx {
         if (captureStream) { cudaStreamDestroy(captureStream); captureStream = nullptr; }
         rawScene.release(); cacheState.release(); camDev.release();
         Buf* all[] = { &sphA, &sphB, &sphCol, &plO, &plN, &plNu, &plCol, &lights, &cmax, &pivTab, &pivPos, &pivPerm, &pivRad, &pivClus, &stage,
-                       &tl, &ctr, &work, &slow, &sortGrid, &cgHdr, &cgStart, &cgCursor, &cgIds, &cgBig, &sgCells, &sgTab, &sgCone, &hostResult, &hostPixelLoc, &imgOut, &batchScene };
+                       &tl, &ctr, &work, &slow, &sortGrid, &cgHdr, &cgStart, &cgCursor, &cgIds, &cgBig, &cgRec, &sgCells, &sgTab, &sgCone, &hostResult, &hostPixelLoc, &imgOut, &batchScene };
         for (Buf* b : all) b->release();
         for (int l = 0; l < kLanes; ++l) lane[l].release();
         if (done) { cudaEventDestroy(done); done = nullptr; } has_done = false; init = false;
@@ -1143,7 +1145,10 @@ int init_ctx(DevCtx& c, int device) {
     { const char* e = getenv("B200RT_NO_SPLIT"); c.no_split = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_LANES"); c.no_lanes = !(e && atoi(e) != 0); }       // two-lane wavefronts: measured slower, opt-in
     { const char* e = getenv("B200RT_CGRID_FROM"); if (e) c.cgrid_from = std::max(1, atoi(e)); }
+    { const char* e = getenv("B200RT_CGRID_DENSITY"); if (e) c.cgrid_density = std::max(0.25f, (float)atof(e)); }
+    { const char* e = getenv("B200RT_CGRID_CTAS"); if (e) c.cgrid_ctas = std::max(1, std::min(32, atoi(e))); }
     { const char* e = getenv("B200RT_CGRID_MAX_PATHS"); if (e) c.cgrid_max_paths = (size_t)std::max(0ll, atoll(e)); }
+    { const char* e = getenv("B200RT_CGRID_NOSORT_PATHS"); if (e) c.cgrid_nosort_paths = (size_t)std::max(0ll, atoll(e)); }
     { const char* e = getenv("B200RT_LANE_CONC"); c.lane_conc = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_SGRID_MIN_S"); if (e) c.sgrid_min_s = std::max(1, atoi(e)); }
     { const char* e = getenv("B200RT_SORT_POSBITS"); if (e) c.sort_posbits = std::min(18, std::max(0, atoi(e))); }
@@ -1252,12 +1257,13 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     if (cgrid) {
         const size_t ids_cap = (size_t)64 * S + 4096;
         CK(c.cgHdr.ensure(sizeof(CGridHdr))); CK(c.cgStart.ensure(sizeof(uint32_t) * ((size_t)cg_max_cells + 1))); CK(c.cgCursor.ensure(sizeof(uint32_t) * (size_t)cg_max_cells));
-        CK(c.cgIds.ensure(sizeof(uint16_t) * ids_cap)); CK(c.cgBig.ensure(sizeof(uint32_t) * kCgMaxBig));
-        cg = CGridDev{ c.cgHdr.as<CGridHdr>(), c.cgStart.as<uint32_t>(), c.cgCursor.as<uint32_t>(), c.cgIds.as<uint16_t>(), c.cgBig.as<uint32_t>(), ids_cap };
-        k_cg_setup<<<1, 256, 0, st>>>(sc, cg, cg_max_cells, cst, kCsCgrid); CKL();
+        CK(c.cgIds.ensure(sizeof(uint16_t) * ids_cap)); CK(c.cgBig.ensure(sizeof(uint32_t) * kCgMaxBig)); CK(c.cgRec.ensure(sizeof(uint4) * (size_t)cg_max_cells));
+        cg = CGridDev{ c.cgHdr.as<CGridHdr>(), c.cgStart.as<uint32_t>(), c.cgCursor.as<uint32_t>(), c.cgIds.as<uint16_t>(), c.cgRec.as<uint4>(), c.cgBig.as<uint32_t>(), ids_cap };
+        k_cg_setup<<<1, 256, 0, st>>>(sc, cg, cg_max_cells, c.cgrid_density, cst, kCsCgrid); CKL();
         k_cg_bin<<<(S + 255) / 256, 256, 0, st>>>(sc, cg, 0, cst, kCsCgrid); CKL();
         k_cg_scan<<<1, 1024, 0, st>>>(cg, cg_max_cells, cst, kCsCgrid); CKL();
         k_cg_bin<<<(S + 255) / 256, 256, 0, st>>>(sc, cg, 1, cst, kCsCgrid); CKL();
+        k_cg_pack<<<(cg_max_cells + 255) / 256, 256, 0, st>>>(cg, cst, kCsCgrid); CKL();
     }
     IsectCfg icfg{ c.sm_count, c.force_nr, c.force_nr0, dense ? 0 : c.npre, {0, 0, 0, 0, 0, 0} };
     for (int k = 0; k < icfg.npre; ++k) icfg.pre[k] = c.pre[k];
@@ -1294,7 +1300,10 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         CK(ln.acc.ensure(sizeof(float4) * cap));
     }
     // regrouping of the hits of depth >= 1 (see k_key): worth it where beam culling is on and a query is expensive
-    const bool regroup = cull && use_lists && S >= 64 && depth >= 1 && !(a->flags & B200RT_F_NO_SORT) && !c.no_sort;
+    // (not where the grid walk serves every bounce depth of a small frame: it needs no coherent groups, and the order it leaves to
+    // k_shadow_shade costs less than the sort — 1/8 of C4: 1.578 -> 1.526 ms, 1/4: 2.90 -> 2.83)
+    const bool regroup = cull && use_lists && S >= 64 && depth >= 1 && !(a->flags & B200RT_F_NO_SORT) && !c.no_sort &&
+                         !(cgrid && c.cgrid_from <= 1 && frame_paths <= c.cgrid_nosort_paths);
     // Bin grid of the regrouping: ~40-170 rays per bin measured best at every frame share (C4: 13 position bits and 3x3
     // direction cells per cube face for the whole 33 M-ray frame, 10 bits / 2x2 for 1/8 of it) — bins much smaller than
     // a ray group only fragment the groups.
@@ -1321,7 +1330,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     for (int l = 0; l < nlanes; ++l) CK(c.lane[l].ostat.ensure(ostat_bytes));
     // Per-light shadow lists pay off when a query is expensive (many spheres); for tiny scenes the dense [light][hit]
     // layout is cheaper than building the lists.
-    const int cps = 4 + L;                                       // counters per depth: n_live, n_hit, 2 debug work counters, n_sh[L]
+    const int cps = 5 + L;                                       // counters per depth: n_live, n_hit, 2 debug work counters, n_sh[L], ray-fetch counter of the grid walk
     const int ctr_stride = cps * (depth + 2);
     CK(c.ctr.ensure(sizeof(uint32_t) * (size_t)ctr_stride * nchunks)); CK(c.slow.ensure(24 * sizeof(unsigned long long)));
     CK(cudaMemsetAsync(c.ctr.p, 0, sizeof(uint32_t) * (size_t)ctr_stride * nchunks, st));
@@ -1528,6 +1537,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
                 out.shadow += (uint64_t)cd[3] * (uint64_t)L;
             }
         unsigned long long slow[24] = {}; CK(cudaMemcpy(slow, c.slow.p, sizeof(slow), cudaMemcpyDeviceToHost));
+        if (getenv("B200RT_DEBUG_CULL")) fprintf(stderr, "[cgrid] bounce rays %llu cell steps %llu exact tests %llu\n", (unsigned long long)out.bounce, slow[10], slow[11]);
         if (getenv("B200RT_DEBUG_CULL")) fprintf(stderr, "[cull] shadow first-pass groups %llu, kap<0.1: %llu\n", slow[22], slow[23]);
         if (getenv("B200RT_DEBUG_CULL")) for (int m = 0; m < 3; ++m) fprintf(stderr, "[cull] mode %d groups %llu beam_ok %llu kept_pairs %llu of %llu  kap<0.1: %llu  and ro<1: %llu\n", m, slow[4 + 6 * m], slow[5 + 6 * m], slow[6 + 6 * m], slow[7 + 6 * m], slow[8 + 6 * m], slow[9 + 6 * m]);
         out.slow_path = slow[0]; out.exact_tests = slow[1]; out.tests_pivot = slow[2]; out.tests_general = slow[3];   // counted by k_isect3

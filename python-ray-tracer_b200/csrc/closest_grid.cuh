@@ -42,12 +42,15 @@ struct CGridDev {
     uint32_t* start;                      // [ncells + 1] exclusive prefix of the cells' list lengths (counts before the scan)
     uint32_t* cursor;                     // [ncells] fill cursors
     uint16_t* ids;                        // [total] sphere ids, cell by cell
+    uint4* rec;                           // [ncells] per cell 8 x uint16: [0] list length, [1..7] the first seven ids — one 16-byte load serves
+                                          // a cell (average list: 2-3 spheres); longer lists continue in `ids`
     uint32_t* big;                        // [kCgMaxBig] ids of the big spheres
     size_t ids_cap;                       // capacity of `ids` (entries)
 };
 
-// Scene bounds -> grid dimensions.  One CTA.  ~2 spheres per cell: n_target = 4 S cells, cubic cells, <= kCgMaxDim per axis.
-__global__ void __launch_bounds__(256) k_cg_setup(SceneDev sc, CGridDev g, int max_cells, const uint32_t* cs, int cs_group) {
+// Scene bounds -> grid dimensions.  One CTA.  n_target = cells_per_sphere * S cubic cells (2 per sphere measured best:
+// profiles/r02_cgrid*.txt), <= kCgMaxDim per axis.
+__global__ void __launch_bounds__(256) k_cg_setup(SceneDev sc, CGridDev g, int max_cells, float cells_per_sphere, const uint32_t* cs, int cs_group) {
     if (cs[cs_group] == cs[0]) return;
     __shared__ int s_ncells;
     __shared__ float smin[3][256], smax[3][256];
@@ -63,7 +66,7 @@ __global__ void __launch_bounds__(256) k_cg_setup(SceneDev sc, CGridDev g, int m
         CGridHdr h{};
         float ext[3]; float vol = 1.f;
         for (int a = 0; a < 3; ++a) { if (!(hi[a] > lo[a])) { lo[a] = 0.f; hi[a] = 1.f; } const float pad = 1e-3f * (hi[a] - lo[a]) + 1e-3f; lo[a] -= pad; hi[a] += pad; ext[a] = hi[a] - lo[a]; vol *= ext[a]; }
-        const float target = fminf(fmaxf(4.f * (float)sc.S, 64.f), 262144.f);
+        const float target = fminf(fmaxf(cells_per_sphere * (float)sc.S, 64.f), 262144.f);
         const float edge = cbrtf(vol / target);
         h.ncells = 1;
         for (int a = 0; a < 3; ++a) {
@@ -147,6 +150,20 @@ __global__ void __launch_bounds__(1024) k_cg_scan(CGridDev g, int max_cells, con
     }
 }
 
+// One thread per cell: the cell's 16-byte record from its list.
+__global__ void __launch_bounds__(256) k_cg_pack(CGridDev g, const uint32_t* cs, int cs_group) {
+    if (cs[cs_group] == cs[0]) return;
+    const CGridHdr h = *g.hdr;
+    if (!h.ok) return;
+    const int cell = blockIdx.x * blockDim.x + threadIdx.x;
+    if (cell >= h.ncells) return;
+    const uint32_t s0 = g.start[cell], cnt = g.start[cell + 1] - s0;
+    uint32_t v[8]; v[0] = min(cnt, 0xffffu);
+#pragma unroll
+    for (int k = 0; k < 7; ++k) v[k + 1] = (uint32_t)k < cnt ? (uint32_t)g.ids[s0 + k] : 0u;
+    g.rec[cell] = make_uint4(v[0] | (v[1] << 16), v[2] | (v[3] << 16), v[4] | (v[5] << 16), v[6] | (v[7] << 16));
+}
+
 struct CGridArgs {
     const float4* rayO; const float4* rayD; const uint32_t* n_in;
     unsigned long long* hit;                 // (float bits of t) << 32 | id per ray; written for every ray
@@ -157,6 +174,8 @@ struct CGridArgs {
 };
 
 // One thread per ray: Amanatides-Woo walk through the cells, sphere_exact on every listed sphere, planes last.
+// (Measured and dropped, profiles/r02_cgrid*.txt: a mailbox of the last two spheres offered, 0.70 -> 0.75 ms for 1/8 of C4; persistent
+// lanes with dynamic ray fetch — one cell step per loop iteration, idle lanes refill from the queue — 0.73 -> 0.87 ms.)
 __global__ void __launch_bounds__(256) k_closest_grid(SceneDev sc, CGridDev g, CGridArgs a) {
     if (a.tl && threadIdx.x == 0) atomicMin(a.tl, globaltimer_ns());
     const CGridHdr h = *g.hdr;
@@ -199,18 +218,34 @@ __global__ void __launch_bounds__(256) k_closest_grid(SceneDev sc, CGridDev g, C
                 else if (d[ax] < -1e-20f) { step[ax] = -1; tdel[ax] = -h.edge[ax] / d[ax]; tmax[ax] = (h.lo[ax] + (float)c[ax] * h.edge[ax] - o[ax]) / d[ax]; }
                 else                      { step[ax] = 0;  tdel[ax] = 3e38f; tmax[ax] = 3e38f; }
             }
+            int cell = (c[2] * h.n[1] + c[1]) * h.n[0] + c[0];
+            const int cstride[3] = { step[0], step[1] * h.n[0], step[2] * h.n[0] * h.n[1] };
+            uint4 rec = __ldg(&g.rec[cell]);
             for (;;) {
-                const int cell = (c[2] * h.n[1] + c[1]) * h.n[0] + c[0];
-                const uint32_t s0 = __ldg(&g.start[cell]), s1 = __ldg(&g.start[cell + 1]);
-                for (uint32_t k = s0; k < s1; ++k) offer((uint32_t)__ldg(&g.ids[k]));
-                if (a.slow) ++n_steps;
+                // where the walk goes next is known before this cell's spheres are looked at: the next cell's record is requested
+                // first, so its latency overlaps the tests (record -> sphB[id] is the only dependent chain left)
                 const float texit = fminf(tmax[0], fminf(tmax[1], tmax[2]));
-                if (best < texit - (1e-3f + 1e-5f * texit) || texit > t1) break;       // nothing beyond this cell can be closer / the ray has left the box
                 const int ax = (tmax[0] <= tmax[1] && tmax[0] <= tmax[2]) ? 0 : (tmax[1] <= tmax[2] ? 1 : 2);
-                // (written without dynamic indexing: the three axes stay in registers)
-                if (ax == 0) { c[0] += step[0]; tmax[0] += tdel[0]; if (c[0] < 0 || c[0] >= h.n[0]) break; }
-                else if (ax == 1) { c[1] += step[1]; tmax[1] += tdel[1]; if (c[1] < 0 || c[1] >= h.n[1]) break; }
-                else { c[2] += step[2]; tmax[2] += tdel[2]; if (c[2] < 0 || c[2] >= h.n[2]) break; }
+                const int cn = (ax == 0 ? c[0] + step[0] : ax == 1 ? c[1] + step[1] : c[2] + step[2]);
+                const bool inside = cn >= 0 && cn < (ax == 0 ? h.n[0] : ax == 1 ? h.n[1] : h.n[2]) && texit <= t1;
+                const int ncell = cell + (ax == 0 ? cstride[0] : ax == 1 ? cstride[1] : cstride[2]);
+                uint4 nrec = make_uint4(0u, 0u, 0u, 0u);
+                if (inside) nrec = __ldg(&g.rec[ncell]);
+                const uint32_t cnt = rec.x & 0xffffu;
+                if (cnt) {
+                    offer(rec.x >> 16);
+                    if (cnt > 1) { offer(rec.y & 0xffffu);
+                    if (cnt > 2) { offer(rec.y >> 16);
+                    if (cnt > 3) { offer(rec.z & 0xffffu);
+                    if (cnt > 4) { offer(rec.z >> 16);
+                    if (cnt > 5) { offer(rec.w & 0xffffu);
+                    if (cnt > 6) { offer(rec.w >> 16);
+                    if (cnt > 7) { const uint32_t s0 = __ldg(&g.start[cell]); for (uint32_t k = 7; k < cnt; ++k) offer((uint32_t)__ldg(&g.ids[s0 + k])); } } } } } } }
+                }
+                if (a.slow) ++n_steps;
+                if (best < texit - (1e-3f + 1e-5f * texit) || !inside) break;         // nothing beyond this cell can be closer / the ray leaves the grid
+                if (ax == 0) { c[0] = cn; tmax[0] += tdel[0]; } else if (ax == 1) { c[1] = cn; tmax[1] += tdel[1]; } else { c[2] = cn; tmax[2] += tdel[2]; }
+                cell = ncell; rec = nrec;
             }
         }
         int id = (int)bid;
@@ -223,7 +258,7 @@ __global__ void __launch_bounds__(256) k_closest_grid(SceneDev sc, CGridDev g, C
     if (a.slow) {
 #pragma unroll
         for (int dd = 16; dd > 0; dd >>= 1) { n_exact += __shfl_xor_sync(0xffffffffu, n_exact, dd); n_steps += __shfl_xor_sync(0xffffffffu, n_steps, dd); }
-        if (lane_id() == 0) { if (n_exact) atomicAdd(a.slow + 1, n_exact); if (n_steps) atomicAdd(a.slow + 10, n_steps); }
+        if (lane_id() == 0) { if (n_exact) { atomicAdd(a.slow + 1, n_exact); atomicAdd(a.slow + 11, n_exact); } if (n_steps) atomicAdd(a.slow + 10, n_steps); }
     }
     if (a.tl && threadIdx.x == 0) atomicMax(a.tl + 1, globaltimer_ns());
 }
