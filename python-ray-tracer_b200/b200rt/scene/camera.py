@@ -25,9 +25,10 @@ class Camera:
         width, height = self.resolution
         ar = int(width / height)                                   # camera.py:22 (sic: integer aspect ratio)
         f = 1 / np.tan(np.radians(self.field_of_view) / 2)
-        with np.errstate(divide="ignore", invalid="ignore"):
-            sy = np.float64(-ar - ar) / np.float64(width - 1)
-            sz = np.float64(-1 - 1) / np.float64(height - 1)
+        # a one-point axis: mgrid leaves its step at 1 (`if step != 1: step = (stop - start) / (step - 1)`) and the only
+        # index is 0, so the value is `start`; any finite step reproduces that (a division by W-1 = 0 would give NaN)
+        sy = np.float64(-ar - ar) / np.float64(width - 1) if width > 1 else np.float64(1.0)
+        sz = np.float64(-1 - 1) / np.float64(height - 1) if height > 1 else np.float64(1.0)
         return float(f), float(ar), float(sy), float(sz)
 
     def generate_pixel_locations(self):

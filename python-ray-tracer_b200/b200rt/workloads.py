@@ -51,6 +51,10 @@ def workload(name):
     if name == "c5":
         return dict(scene=Scene.default_scene(), cameras=[c5_camera(k) for k in range(64)], **SHADER, refl_depth=2,
                     aliasing=False, label="C5 64-frame orbit of the default scene 3840x2160 depth 2")
+    if name in ("c4_s2048", "c4_s4096"):          # not a BASELINE config: the C4 generator with more spheres, for the S > 1024 path (grid walk at every depth)
+        n = int(name.split("_s")[1])
+        return dict(scene=c4_scene(n=n, seed=n), cameras=[Camera((3840, 2160), [-6, 0, 5.0], [0, -25, 0])], **SHADER, refl_depth=3,
+                    aliasing=False, label=f"C4-like: {n} random spheres 3840x2160 depth 3")
     raise ValueError(name)
 
 

@@ -1037,6 +1037,7 @@ struct DevCtx {
     int cgrid_ctas = 8;                                              // env B200RT_CGRID_CTAS: CTAs per SM of k_closest_grid
     float cgrid_density = 2.f;                                       // env B200RT_CGRID_DENSITY: cells per sphere the grid aims at
     int cgrid_from = 1; size_t cgrid_max_paths = (size_t)20 << 20, cgrid_nosort_paths = (size_t)10 << 20;   // env B200RT_CGRID_FROM (first depth served by the grid; 99: never), B200RT_CGRID_MAX_PATHS
+    bool no_cgrid_all = false;                                       // env B200RT_NO_CGRID_ALL
     bool no_lanes = false, lane_conc = false;                        // env B200RT_NO_LANES, B200RT_LANE_CONC
     bool no_sgrid = false, no_clus = false, no_sort_last = true; int ss_grid = 0; int sgrid_min_s = 1; bool no_sort = false; int sort_posbits = -1, sort_dirn = -1;     // env B200RT_NO_SORT, B200RT_SORT_POSBITS, B200RT_SORT_DIRN (-1: chosen from the queue size)
     int npre = 1, pre[6] = {256, 0, 0, 0, 0, 0};                    // leading shadow passes (env B200RT_PASSES=a,b,...; multiples of 8)
@@ -1148,6 +1149,7 @@ int init_ctx(DevCtx& c, int device) {
     { const char* e = getenv("B200RT_CGRID_DENSITY"); if (e) c.cgrid_density = std::max(0.25f, (float)atof(e)); }
     { const char* e = getenv("B200RT_CGRID_CTAS"); if (e) c.cgrid_ctas = std::max(1, std::min(32, atoi(e))); }
     { const char* e = getenv("B200RT_CGRID_MAX_PATHS"); if (e) c.cgrid_max_paths = (size_t)std::max(0ll, atoll(e)); }
+    { const char* e = getenv("B200RT_NO_CGRID_ALL"); c.no_cgrid_all = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_CGRID_NOSORT_PATHS"); if (e) c.cgrid_nosort_paths = (size_t)std::max(0ll, atoll(e)); }
     { const char* e = getenv("B200RT_LANE_CONC"); c.lane_conc = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_SGRID_MIN_S"); if (e) c.sgrid_min_s = std::max(1, atoi(e)); }
@@ -1250,7 +1252,11 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     // Closest-hit queries of bounce rays through a uniform grid of the spheres, one ray per thread (closest_grid.cuh), where
     // the beam method loses its edge: small queues (one GPU's share of a sharded frame).
     const size_t frame_paths = (size_t)ncols * H * ns;
-    const bool cgrid = cull && !nofilter && S >= 64 && S <= 65535 && depth >= 1 && c.cgrid_from <= depth && frame_paths <= c.cgrid_max_paths &&
+    // Beyond 512 sphere pairs (S > 1024) k_isect3's per-group pair list does not hold a launch's pairs and its groups fall back to
+    // the dense scan of every sphere, primary rays included: there the grid walk serves every depth at any frame size.
+    const bool cgrid_all = Spad / 2 > 512 && !c.no_cgrid_all;
+    const int cgrid_from = cgrid_all ? 0 : c.cgrid_from;
+    const bool cgrid = cull && !nofilter && S >= 64 && S <= 65535 && cgrid_from <= depth && (cgrid_all || (depth >= 1 && frame_paths <= c.cgrid_max_paths)) &&
                        !(a->flags & B200RT_F_NO_CGRID);
     CGridDev cg{};
     const int cg_max_cells = (int)std::min<size_t>((size_t)1 << 21, (size_t)32 * S + 4096);
@@ -1303,7 +1309,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     // (not where the grid walk serves every bounce depth of a small frame: it needs no coherent groups, and the order it leaves to
     // k_shadow_shade costs less than the sort — 1/8 of C4: 1.578 -> 1.526 ms, 1/4: 2.90 -> 2.83)
     const bool regroup = cull && use_lists && S >= 64 && depth >= 1 && !(a->flags & B200RT_F_NO_SORT) && !c.no_sort &&
-                         !(cgrid && c.cgrid_from <= 1 && frame_paths <= c.cgrid_nosort_paths);
+                         !(cgrid && cgrid_from <= 1 && frame_paths <= c.cgrid_nosort_paths);
     // Bin grid of the regrouping: ~40-170 rays per bin measured best at every frame share (C4: 13 position bits and 3x3
     // direction cells per cube face for the whole 33 M-ray frame, 10 bits / 2x2 for 1/8 of it) — bins much smaller than
     // a ray group only fragment the groups.
@@ -1425,16 +1431,16 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
 
             tm.begin(0);
             q.n_in = n_live; q.work = cd + 1;
+            if (cgrid && d >= cgrid_from) {                     // per-ray grid walk; k_isect3 below only takes the queue if the grid turned out unusable (cd[1] stays 0 otherwise)
+                CGridArgs ca{ q.rayO, q.rayD, n_live, q.hit, nullptr, q.slow, cd + 1 };
+                if (tlb) { ca.tl = tlb + 2 * (size_t)tln++; tlname.push_back("closest<grid> d" + std::to_string(d)); }
+                const int cgg = (int)std::min<size_t>((size_t)c.sm_count * 32, std::max<size_t>((size_t)c.sm_count * 8, cap / (256 * 4)));
+                k_closest_grid<<<cgg, 256, 0, cs>>>(sc, cg, ca); CKL();
+                q.n_in = cd + 1;
+            }
             if (nofilter)                     { if (int rc = launch_intersect<false>(c, sc, q, true, cs)) return rc; }
             else if (d == 0 && !c.no_pivot)   { const int f0 = tln; CK(isect3_launch_closest<1>(icfg, sc, q, pv, nslots, wk, closest_res, cs, tlb, &tln)); tl_mark("closest<1>", d, f0); }
             else {
-                if (cgrid && d >= c.cgrid_from) {               // per-ray grid walk; k_isect3 below only takes the queue if the grid turned out unusable (cd[1] stays 0 otherwise)
-                    CGridArgs ca{ q.rayO, q.rayD, n_live, q.hit, nullptr, q.slow, cd + 1 };
-                    if (tlb) { ca.tl = tlb + 2 * (size_t)tln++; tlname.push_back("closest<grid> d" + std::to_string(d)); }
-                    const int cgg = (int)std::min<size_t>((size_t)c.sm_count * 32, std::max<size_t>((size_t)c.sm_count * 8, cap / (256 * 4)));
-                    k_closest_grid<<<cgg, 256, 0, cs>>>(sc, cg, ca); CKL();
-                    q.n_in = cd + 1;
-                }
                 const int f0 = tln; CK(isect3_launch_closest<0>(icfg, sc, q, pv, nslots, wk, closest_res, cs, tlb, &tln)); tl_mark("closest<0>", d, f0);
             }
             tm.end(0);
@@ -1531,7 +1537,9 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         for (int ch = 0; ch < nchunks; ++ch)
             for (int d = 0; d <= depth; ++d) {
                 const uint32_t* cd = h.data() + (size_t)ch * ctr_stride + cps * d;
-                if (use_lists) { for (int j = 0; j < L; ++j) out.shadow_traced += cd[4 + j]; }        // lists: their lengths; grids: counted by k_shadow_shade
+                // lists (scan path, S >= 32): their lengths; light grids: counted per light by k_shadow_shade in the diagnostic frame (left 0 by
+                // B200RT_F_TIME_ONLY); dense [light][hit] layout: every pair is traced
+                if (use_lists || sgrid) { for (int j = 0; j < L; ++j) out.shadow_traced += cd[4 + j]; }
                 else out.shadow_traced += (uint64_t)cd[3] * (uint64_t)L;
                 if (d == 0) out.primary += cd[0]; else out.bounce += (cd - cps)[3];       // queue of depth d = hit list of depth d-1
                 out.shadow += (uint64_t)cd[3] * (uint64_t)L;

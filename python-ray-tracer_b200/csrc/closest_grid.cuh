@@ -193,17 +193,20 @@ __global__ void __launch_bounds__(256) k_closest_grid(SceneDev sc, CGridDev g, C
             if (t > 0.f && (t < best || (t == best && sid < bid))) { best = t; bid = sid; }             // trace.py:26-29: smallest t, lowest index on a tie
         };
         for (int k = 0; k < h.nbig; ++k) offer(g.big[k]);
-        // clip the ray to the grid's box (slab test, conservative: box grown by a cell fraction)
+        // clip the ray to the grid's box (slab test, conservative: box grown by a cell fraction).  One reciprocal per axis serves the
+        // slab test and the walk's increments: these parameters only steer the walk (margins below), the hits come from sphere_exact.
         const float o[3] = {O.x, O.y, O.z}, d[3] = {D.x, D.y, D.z};
+        float inv[3];
         float t0 = 0.f, t1 = kTMax;
         bool miss = false;
 #pragma unroll
         for (int ax = 0; ax < 3; ++ax) {
             const float lo = h.lo[ax] - 1e-3f * h.edge[ax], hi = h.lo[ax] + (float)h.n[ax] * h.edge[ax] + 1e-3f * h.edge[ax];
+            inv[ax] = 0.f;
             if (fabsf(d[ax]) < 1e-20f) { if (o[ax] < lo || o[ax] > hi) miss = true; }
             else {
-                const float inv = 1.f / d[ax];
-                float ta = (lo - o[ax]) * inv, tb = (hi - o[ax]) * inv;
+                inv[ax] = __frcp_rn(d[ax]);
+                float ta = (lo - o[ax]) * inv[ax], tb = (hi - o[ax]) * inv[ax];
                 if (ta > tb) { const float tt = ta; ta = tb; tb = tt; }
                 t0 = fmaxf(t0, ta - 1e-4f * fabsf(ta)); t1 = fminf(t1, tb + 1e-4f * fabsf(tb));
             }
@@ -214,8 +217,8 @@ __global__ void __launch_bounds__(256) k_closest_grid(SceneDev sc, CGridDev g, C
             for (int ax = 0; ax < 3; ++ax) {
                 const float p = fmaf(t0, d[ax], o[ax]);
                 c[ax] = max(0, min(h.n[ax] - 1, (int)floorf((p - h.lo[ax]) * h.inv[ax])));
-                if (d[ax] > 1e-20f)       { step[ax] = 1;  tdel[ax] = h.edge[ax] / d[ax];  tmax[ax] = (h.lo[ax] + (float)(c[ax] + 1) * h.edge[ax] - o[ax]) / d[ax]; }
-                else if (d[ax] < -1e-20f) { step[ax] = -1; tdel[ax] = -h.edge[ax] / d[ax]; tmax[ax] = (h.lo[ax] + (float)c[ax] * h.edge[ax] - o[ax]) / d[ax]; }
+                if (d[ax] > 1e-20f)       { step[ax] = 1;  tdel[ax] = h.edge[ax] * inv[ax];  tmax[ax] = (h.lo[ax] + (float)(c[ax] + 1) * h.edge[ax] - o[ax]) * inv[ax]; }
+                else if (d[ax] < -1e-20f) { step[ax] = -1; tdel[ax] = -h.edge[ax] * inv[ax]; tmax[ax] = (h.lo[ax] + (float)c[ax] * h.edge[ax] - o[ax]) * inv[ax]; }
                 else                      { step[ax] = 0;  tdel[ax] = 3e38f; tmax[ax] = 3e38f; }
             }
             int cell = (c[2] * h.n[1] + c[1]) * h.n[0] + c[0];

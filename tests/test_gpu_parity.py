@@ -470,3 +470,18 @@ def test_closest_hit_grid_edge_cases(case):
     assert got.any()
     assert np.array_equal(got, _cuda(g, flags=_lib.F_NO_CGRID)), case
     assert np.array_equal(got, _cuda(g, flags=_lib.F_NO_FILTER)), case
+
+
+@pytest.mark.parametrize("res", [(1, 1), (5, 1), (1, 5), (2, 3)])
+def test_one_point_axes_render_like_the_oracle(oracle, res):
+    """W == 1 or H == 1: the closed-form grid has no step to divide by (Camera.grid: mgrid returns `start`)."""
+    from b200rt import render_frame
+    from b200rt.scene import Scene, Camera
+    scene = Scene.default_scene()
+    for aa in (False, True):
+        cam = Camera(resolution=res, position=[-2, 0, 2.0], euler=[0, -30, 0])
+        got = render_frame(scene, cam, 0.1, 0.6, 0.3, 2, aa)
+        sp, li, pl = scene.generate_scene()
+        ref = oracle.render(np.asarray(cam.generate_pixel_locations()), cam.position, cam.rotation, sp, li, pl, 0.1, 0.6, 0.3, 2, aa)
+        assert got.shape == (3, *res)
+        assert np.abs(got.astype(int) - ref.astype(int)).max() <= 1, (res, aa)

@@ -84,6 +84,11 @@ def test_against_reference_package_in_place():
         a, b = ref.Camera(res, list(pos), list(e), fov), Camera(res, list(pos), list(e), fov)
         assert np.array_equal(a.rotation, b.rotation) and np.array_equal(a.position, b.position)
         assert np.array_equal(a.generate_pixel_locations(), np.asarray(b.generate_pixel_locations()))
+    for res in ((1, 1), (5, 1), (1, 5), (2, 1)):                    # one-point axes: mgrid returns `start`, no division by W-1 = 0
+        a, b = ref.Camera(res, [0, 0, 1.0], [0, 0, 0]), Camera(res, [0, 0, 1.0], [0, 0, 0])
+        Pa, Pb = a.generate_pixel_locations(), np.asarray(b.generate_pixel_locations())
+        assert np.all(np.isfinite(Pb)) and np.array_equal(Pa, Pb), res
+        assert np.all(np.isfinite(b.grid()))
     sa = ref.Scene([ref.Light([1, 2, 3])], [ref.Sphere([0.1, 0.2, 0.3], 0.7, [1, 2, 3])], [ref.Plane([0, 0, 1], [1, 2, 3], [9, 8, 7])])
     sb = Scene([Light([1, 2, 3])], [Sphere([0.1, 0.2, 0.3], 0.7, [1, 2, 3])], [Plane([0, 0, 1], [1, 2, 3], [9, 8, 7])])
     for x, y in zip(sa.generate_scene(), sb.generate_scene()):

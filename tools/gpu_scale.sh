@@ -15,6 +15,6 @@ for n in (1,2,4,8):
     try:
         d=json.loads(open(f).read().strip().splitlines()[-1])
         if n==1: base=d['ms_per_step']; be=d['e2e']['ms_per_step']
-        print(n, 'ms', round(d['ms_per_step'],3), 'x', round(base/d['ms_per_step'],2), 'e2e ms', round(d['e2e']['ms_per_step'],3), 'x', round(be/d['e2e']['ms_per_step'],2), d['clocks'])
+        print(n, "ms", round(d["ms_per_step"],3), "x", round(base/d["ms_per_step"],2), "e2e ms", round(d["e2e"]["ms_per_step"],3), "x", round(be/d["e2e"]["ms_per_step"],2), "assembled", d["e2e"].get("assembled"), "checksum ok", d["e2e"].get("checksum_matches_one_gpu_frame"), d["clocks"])
     except Exception as e: print(f,'ERR',e, open(f.replace('.json','.err')).read()[-1500:] if glob.glob(f.replace('.json','.err')) else '')
 PY
