@@ -243,15 +243,10 @@ constexpr int kGroup   = kThreads * kRays;
 constexpr int kChunkS  = 4096;           // spheres staged in shared memory per pass (64 KB + 16 KB)
 
 
-// Per ray, per sphere the loop evaluates the discriminant of intersections.py:23 in expanded form
-//     disc = b^2 - c,  b = (C-O).D = C.D - O.D,  c = |C-O|^2 - r^2 = (|C|^2 - r^2) - 2 C.O + |O|^2
-//     q = b^2 + 2 C.O + (r^2 - |C|^2)   and   disc >= 0  <=>  q >= |O|^2
-// = 7 FFMA per test with per-ray constants (D, 2O, -O.D) and one float4 per sphere.  The expanded form
-// cancels badly in FP32, so it is used ONLY as a conservative filter: q >= |O|^2 - margin, with margin a
-// rigorous bound on its rounding error (64 * 2^-24 * (max|C| + |O|)^2).  Spheres that pass
-// (a few per ray out of S) go through sphere_exact() — the robust form — which alone decides hit/miss and t.
-// With B200RT_F_NO_FILTER every sphere takes the exact test; outputs must be bit-identical (tested).
-template <bool ANY, bool NOFILTER>
+// Debug / proof kernel (B200RT_F_NO_FILTER): sphere_exact() on EVERY sphere for every ray, no conservative filter, no culling,
+// no grids — the statement every production path must reproduce byte for byte (tests/test_gpu_parity.py).  Scalar, spheres
+// staged through shared memory chunk by chunk.
+template <bool ANY>
 __global__ void __launch_bounds__(kThreads, 2)
 k_intersect(SceneDev sc, QueueDev q) {
     extern __shared__ float4 s_sph[];                        // [chunk] filter operands
@@ -273,7 +268,7 @@ k_intersect(SceneDev sc, QueueDev q) {
         if (g >= ngroups) break;
 
         // ---- load / build this thread's rays ----
-        float dx[kRays], dy[kRays], dz[kRays], o2x[kRays], o2y[kRays], o2z[kRays], nod[kRays], thr[kRays];
+        float dx[kRays], dy[kRays], dz[kRays], o2x[kRays], o2y[kRays], o2z[kRays], thr[kRays];
         float best[kRays]; int bid[kRays];
 #pragma unroll
         for (int r = 0; r < kRays; ++r) {
@@ -293,7 +288,6 @@ k_intersect(SceneDev sc, QueueDev q) {
             }
             dx[r] = D.x; dy[r] = D.y; dz[r] = D.z;
             o2x[r] = 2.f * O.x; o2y[r] = 2.f * O.y; o2z[r] = 2.f * O.z;
-            nod[r] = -dot3(O, D);
             const float oo = dot3(O, O);
             const float A = cmax + __fsqrt_rn(oo);
             const float margin = fmaf(3.8146973e-6f /* 64 * 2^-24 */, A * A, 1e-12f);
@@ -319,14 +313,7 @@ k_intersect(SceneDev sc, QueueDev q) {
                 bool p0[kRays], p1[kRays]; bool any = false;
 #pragma unroll
                 for (int r = 0; r < kRays; ++r) {
-                    if (NOFILTER) { p0[r] = thr[r] < 3e38f && (c0 + s < sc.S); p1[r] = thr[r] < 3e38f && (c0 + s + 1 < sc.S); }
-                    else {
-                        const float b0 = fmaf(a0.x, dx[r], fmaf(a0.y, dy[r], fmaf(a0.z, dz[r], nod[r])));
-                        const float b1 = fmaf(a1.x, dx[r], fmaf(a1.y, dy[r], fmaf(a1.z, dz[r], nod[r])));
-                        const float q0 = fmaf(b0, b0, fmaf(a0.x, o2x[r], fmaf(a0.y, o2y[r], fmaf(a0.z, o2z[r], a0.w))));
-                        const float q1 = fmaf(b1, b1, fmaf(a1.x, o2x[r], fmaf(a1.y, o2y[r], fmaf(a1.z, o2z[r], a1.w))));
-                        p0[r] = q0 >= thr[r]; p1[r] = q1 >= thr[r];
-                    }
+                    p0[r] = thr[r] < 3e38f && (c0 + s < sc.S); p1[r] = thr[r] < 3e38f && (c0 + s + 1 < sc.S);       // every sphere of every active ray
                     any |= p0[r] | p1[r];
                 }
                 if (any) {                                                // rare: a few spheres per ray
@@ -1110,11 +1097,10 @@ int validate(const b200rt_args* a) {
 }
 
 template <bool ANY>
-int launch_intersect(DevCtx& c, const SceneDev& sc, const QueueDev& q, bool nofilter, cudaStream_t st) {
+int launch_intersect(DevCtx& c, const SceneDev& sc, const QueueDev& q, cudaStream_t st) {
     const size_t smem = isect_smem_bytes(sc.Spad);
     const int grid = c.sm_count * c.isect_blocks_per_sm;
-    (void)nofilter;                                   // the scalar kernel is kept as the exact-test-on-everything debug path
-    k_intersect<ANY, true><<<grid, kThreads, smem, st>>>(sc, q);
+    k_intersect<ANY><<<grid, kThreads, smem, st>>>(sc, q);
     CKL();
     return 0;
 }
@@ -1125,8 +1111,8 @@ int init_ctx(DevCtx& c, int device) {
     if (prop.major != 10) return fail(B200RT_E_DEVICE, "libb200rt is built for sm_100a (B200) only; device is sm_" + std::to_string(prop.major * 10 + prop.minor));
     c.sm_count = prop.multiProcessorCount;
     const int smem_max = (int)isect_smem_bytes(kChunkS);
-    CK(cudaFuncSetAttribute(k_intersect<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
-    CK(cudaFuncSetAttribute(k_intersect<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
+    CK(cudaFuncSetAttribute(k_intersect<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
+    CK(cudaFuncSetAttribute(k_intersect<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
     CK(isect3_set_attr<0>()); CK(isect3_set_attr<1>()); CK(shadow_set_attr());
     { const char* e = getenv("B200RT_NR"); c.force_nr = e ? atoi(e) : 0; if (c.force_nr != 2 && c.force_nr != 4 && c.force_nr != 8) c.force_nr = 0; }
     { const char* e = getenv("B200RT_NR0"); c.force_nr0 = e ? atoi(e) : 0; if (c.force_nr0 != 2 && c.force_nr0 != 4 && c.force_nr0 != 8) c.force_nr0 = 0; }
@@ -1353,7 +1339,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     CK(cudaMemsetAsync(c.slow.p, 0, 24 * sizeof(unsigned long long), st));
 
     if (a->flags & B200RT_F_NO_FILTER) {   // persistent grid of the scalar debug kernel
-        int nb = 0; CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_intersect<false, true>, kThreads, isect_smem_bytes(Spad)));
+        int nb = 0; CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_intersect<false>, kThreads, isect_smem_bytes(Spad)));
         c.isect_blocks_per_sm = std::max(1, nb);
     }
     const int small_grid = c.sm_count * 8;
@@ -1438,7 +1424,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
                 k_closest_grid<<<cgg, 256, 0, cs>>>(sc, cg, ca); CKL();
                 q.n_in = cd + 1;
             }
-            if (nofilter)                     { if (int rc = launch_intersect<false>(c, sc, q, true, cs)) return rc; }
+            if (nofilter)                     { if (int rc = launch_intersect<false>(c, sc, q, cs)) return rc; }
             else if (d == 0 && !c.no_pivot)   { const int f0 = tln; CK(isect3_launch_closest<1>(icfg, sc, q, pv, nslots, wk, closest_res, cs, tlb, &tln)); tl_mark("closest<1>", d, f0); }
             else {
                 const int f0 = tln; CK(isect3_launch_closest<0>(icfg, sc, q, pv, nslots, wk, closest_res, cs, tlb, &tln)); tl_mark("closest<0>", d, f0);
@@ -1473,7 +1459,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             tm.end(2);
             if (L > 0) {
                 tm.begin(1);
-                if (nofilter) { q.n_in = cd + 3; q.work = cd + 2; if (int rc = launch_intersect<true>(c, sc, q, true, cs)) return rc; }
+                if (nofilter) { q.n_in = cd + 3; q.work = cd + 2; if (int rc = launch_intersect<true>(c, sc, q, cs)) return rc; }
                 else if (sgrid) {                       // shadow queries + Lambert sum + accumulate in one kernel (shadow_grid.cuh)
                     ShadowGridArgs ga{ s.hP, s.hN, s.n_hit, acc, s.amb, s.lamb, s.weight, pv.bounds,
                                        q.slow ? cd + 4 : nullptr, q.slow, nullptr };        // (counters only in the diagnostic frame: B200RT_F_TIME_ONLY leaves shadow_traced 0)

@@ -124,9 +124,6 @@ constexpr int KP = B200RT_KP;            // sphere pairs per scan step, pivot mo
 #define B200RT_CULL_E 0                  // beam culling: sphere pairs per lane per round (code size / registers vs loads in flight; the next round is
                                          // prefetched).  0: 2 with 8 rays per thread, 1 with fewer (85 registers: C4 12.78 -> 12.69 ms; 3 and 4 spill)
 #endif
-#ifndef B200RT_ONE_SLOW_SITE
-#define B200RT_ONE_SLOW_SITE 0           // 1: one copy of slow_pair / the exact-test loop behind both scans (smaller code, measured 0.6 ms/frame slower on C4)
-#endif
 #ifndef B200RT_FLUSH_UNROLL
 #define B200RT_FLUSH_UNROLL 1            // 1: #pragma unroll 1 on the exact-test loop (0: the compiler unrolls it by 2 + tail at every inlined site)
 #endif
@@ -477,83 +474,6 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
                 }
             }
         }
-#if B200RT_ONE_SLOW_SITE
-        // ---- scan.  Two loops find the sphere pairs in which some ray of the group has a candidate — the list scan
-        // (culled groups: listed pairs, operands by computed index) and the dense scan (all pairs of the launch, operands
-        // through uniform registers) — and ONE handler below them turns those pairs into queue entries: slow_pair and
-        // the exact-test loop exist once in the kernel (they used to be inlined at three / four places, and the
-        // kernel's first limiter is instruction fetch, profiles/r01_v7_summary.md).
-        // Dense scan: KPM sphere pairs x NR rays per step, pair-major; the uniform registers of a pair are refilled
-        // for the NEXT step as soon as the pair is done (rolling prefetch: LDCU latency never reaches the FMA pipe),
-        // and the candidate decision of a step is taken one step LATER (software pipelining): the vote never waits
-        // on the FMA pipe; the last step is drained after the loop.  (The loop keeps the shape ptxas is known to map onto
-        // uniform registers: LDCU -> FFMA2 ..., UR; other equivalent forms of it silently fell back to vector LDC operands.) ----
-        const bool sparse = __all_sync(0xffffffffu, ns >= 0);
-        if (DIAG && q.slow) tests_cnt += (unsigned long long)(sparse ? ns : npair) * 2ull * (unsigned long long)NR;
-        float pm[KPM]; int ppair = 0, pn = 0;                          // pending: pairs ppair .. ppair + pn - 1 with maxima pm[]
-        int li = 0, pb = 0; bool drained = false;
-        float mprev[KPM];
-        float4 u[KPM], w[KPM];
-#pragma unroll
-        for (int k = 0; k < KPM; ++k) { mprev[k] = -3.0e38f; pm[k] = -3.0e38f; u[k] = c_tab[tb + 2 * k]; w[k] = c_tab[tb + 2 * k + 1]; }
-        for (;;) {
-            pn = 0;
-            if (sparse) {
-#pragma unroll 1
-                while (li < nsr) {                                     // one listed pair per iteration: the lists are short
-                    const int pi = slist[li++];
-                    const float4 uu = c_tab[tb + 2 * pi], ww = c_tab[tb + 2 * pi + 1];
-                    float m = -3.0e38f;
-#pragma unroll
-                    for (int r = 0; r < NR; ++r) { const float2 qv = qray(r, uu, ww); m = fmax3(m, qv.x, qv.y); }
-                    if (__any_sync(0xffffffffu, m >= thr_t)) { ppair = pi; pm[0] = m; pn = 1; break; }
-                }
-            } else {
-                for (; pb < npair; pb += KPM) {
-                    float mall = mprev[0];
-#pragma unroll
-                    for (int k = 1; k < KPM; ++k) mall = fmaxf(mall, mprev[k]);
-                    const bool fire = __any_sync(0xffffffffu, mall >= thr_t);   // step pb-KPM
-                    float mk4[KPM];
-#pragma unroll
-                    for (int k = 0; k < KPM; ++k) {
-                        float m = -3.0e38f;
-#pragma unroll
-                        for (int r = 0; r < NR; ++r) { const float2 qv = qray(r, u[k], w[k]); m = fmax3(m, qv.x, qv.y); }
-                        mk4[k] = m;
-                        u[k] = c_tab[tb + 2 * (pb + KPM + k)]; w[k] = c_tab[tb + 2 * (pb + KPM + k) + 1];   // next step (c_tab is over-allocated)
-                    }
-                    if (fire) {                                       // hand step pb-KPM to the handler, keep this step pending
-#pragma unroll
-                        for (int k = 0; k < KPM; ++k) { pm[k] = mprev[k]; mprev[k] = mk4[k]; }
-                        ppair = pb - KPM; pn = KPM; pb += KPM; break;
-                    }
-#pragma unroll
-                    for (int k = 0; k < KPM; ++k) mprev[k] = mk4[k];
-                }
-                if (pn == 0 && !drained) {                            // the last step
-                    drained = true;
-                    float mall = mprev[0];
-#pragma unroll
-                    for (int k = 1; k < KPM; ++k) mall = fmaxf(mall, mprev[k]);
-                    if (__any_sync(0xffffffffu, mall >= thr_t)) {
-#pragma unroll
-                        for (int k = 0; k < KPM; ++k) pm[k] = mprev[k];
-                        ppair = npair - KPM; pn = KPM;
-                    }
-                }
-            }
-            if (pn == 0) break;
-            if (DIAG) slow_cnt++;
-#pragma unroll 1
-            for (int k = 0; k < pn; ++k) {
-                float mv = pm[0];
-#pragma unroll
-                for (int kk = 1; kk < KPM; ++kk) mv = (k == kk) ? pm[kk] : mv;
-                if (__any_sync(0xffffffffu, mv >= thr_t)) slow_pair(ppair + k);
-            }
-        }
-#else
         if (__all_sync(0xffffffffu, ns >= 0)) {
             if (DIAG && q.slow) tests_cnt += (unsigned long long)ns * 2ull * (unsigned long long)NR;
 #pragma unroll 1
@@ -609,7 +529,6 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
             break;
         }
         }
-#endif
         flush();
 
         // ---- planes after the last sphere chunk (trace.py:32-39), then write back (one code copy, ray k*32 + lane) ----

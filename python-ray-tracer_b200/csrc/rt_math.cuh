@@ -68,73 +68,9 @@ __device__ __forceinline__ float plane_exact(V3 O, V3 D, float4 po, float4 pn) {
 
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
 
-// Warp-aggregated append: returns this lane's slot in a queue whose length lives at *counter.
-__device__ __forceinline__ uint32_t warp_append(bool valid, uint32_t* counter) {
-    uint32_t mask = __ballot_sync(0xffffffffu, valid);
-    uint32_t base = 0;
-    if (mask) {
-        int leader = __ffs(mask) - 1;
-        if ((int)lane_id() == leader) base = atomicAdd(counter, (uint32_t)__popc(mask));
-        base = __shfl_sync(0xffffffffu, base, leader);
-    }
-    return base + __popc(mask & ((1u << lane_id()) - 1u));
-}
-
-
-// CTA-aggregated append for 256-thread CTAs whose threads hold CONSECUTIVE items: the CTA's valid items land in one
-// contiguous, order-preserving run of the queue (one atomic per CTA).  Keeps neighbouring pixels neighbouring in
-// the ray queues, which is what makes a warp's rays pass the sphere filter at the same spheres.
-// Must be called by every thread of the CTA (contains __syncthreads()).
-__device__ __forceinline__ uint32_t block_append(bool valid, uint32_t* counter) {
-    __shared__ uint32_t s_cnt[8];
-    __shared__ uint32_t s_base;
-    const uint32_t mask = __ballot_sync(0xffffffffu, valid);
-    const uint32_t wid = threadIdx.x >> 5;
-    if (lane_id() == 0) s_cnt[wid] = (uint32_t)__popc(mask);
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        uint32_t total = 0;
-#pragma unroll
-        for (int w = 0; w < 8; ++w) { const uint32_t t = s_cnt[w]; s_cnt[w] = total; total += t; }
-        s_base = total ? atomicAdd(counter, total) : 0u;
-    }
-    __syncthreads();
-    const uint32_t pos = s_base + s_cnt[wid] + (uint32_t)__popc(mask & ((1u << lane_id()) - 1u));
-    __syncthreads();                                   // s_cnt / s_base are reused by the caller's next iteration
-    return pos;
-}
-
-
-// block_append for up to 8 queues at once (bit j of `flags` = this item goes on queue j; counters[j] = its length):
-// one pair of barriers for all of them.  pos[j] is valid where bit j is set.
-__device__ __forceinline__ void block_append8(uint32_t flags, int nq, uint32_t* counters, uint32_t (&pos)[8]) {
-    __shared__ uint32_t s_cnt8[8][8];      // [queue][warp]
-    __shared__ uint32_t s_base8[8];
-    const uint32_t wid = threadIdx.x >> 5, lt = (1u << lane_id()) - 1u;
-    uint32_t mask[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-        mask[j] = (j < nq) ? __ballot_sync(0xffffffffu, (flags >> j) & 1u) : 0u;
-        if (j < nq && lane_id() == 0) s_cnt8[j][wid] = (uint32_t)__popc(mask[j]);
-    }
-    __syncthreads();
-    if ((int)threadIdx.x < nq) {
-        const int j = threadIdx.x;
-        uint32_t total = 0;
-#pragma unroll
-        for (int w = 0; w < 8; ++w) { const uint32_t t = s_cnt8[j][w]; s_cnt8[j][w] = total; total += t; }
-        s_base8[j] = total ? atomicAdd(counters + j, total) : 0u;
-    }
-    __syncthreads();
-#pragma unroll
-    for (int j = 0; j < 8; ++j) pos[j] = (j < nq) ? s_base8[j] + s_cnt8[j][wid] + (uint32_t)__popc(mask[j] & lt) : 0u;
-    __syncthreads();
-}
-
-
 // Ordered multi-queue append ("decoupled look-back" compaction).  Chunk c (256 consecutive input items, chunks claimed
 // in ticket order) appends its items to up to 8 queues so that every queue keeps the INPUT order across the whole
-// launch — not just within a CTA as block_append8 does.  Neighbouring pixel tiles then stay neighbours in every
+// launch — not just within a CTA, as an atomic append per CTA would.  Neighbouring pixel tiles then stay neighbours in every
 // compacted list, which is what keeps a ray group of k_isect3 a narrow beam at every depth.
 // status: [chunk][8] 64-bit words, zeroed before the launch; bits 62-63: 1 = this chunk's count, 2 = inclusive prefix.
 // Warp q of the CTA owns queue q: it publishes the chunk's count, sums its predecessors' (32 at a time, spinning only
