@@ -18,7 +18,7 @@ case $MODE in
   dense)
     BENCH="python tools/one_frame.py dense"
     $BENCH > gpurun_out/${T}_plain.log 2>&1 &&
-    ncu --set full --clock-control none --import-source on -k regex:"k_isect3" -s 8 -c 8 -o gpurun_out/${T}_dense $BENCH > gpurun_out/${T}_ncu.log 2>&1 ;;
+    ncu --set full --clock-control none --import-source on -k regex:"k_isect3" -s 16 -c 8 -o gpurun_out/${T}_dense $BENCH > gpurun_out/${T}_ncu.log 2>&1 ;;
   culled)
     BENCH="python tools/one_frame.py culled"
     B200RT_NO_GRAPH=1 $BENCH > gpurun_out/${T}_plain.log 2>&1 &&

@@ -1,5 +1,6 @@
-"""Summarise the ncu CSVs of tools/gpu_prof8.sh: launch list (per kernel totals / shares) and per-launch frame metrics.
-usage: python tools/ncu_tables.py gpurun_out/v8   ->  prints markdown tables, writes <prefix>_traffic.json"""
+"""Summarise the ncu CSVs of tools/gpu_profile.sh: launch list (per-kernel totals / shares) and the per-launch metrics of one
+production frame, with per-class DRAM traffic.
+usage: python tools/ncu_tables.py gpurun_out/r02   ->  prints markdown tables, writes <prefix>_traffic.json"""
 import csv, re, sys, json, collections
 
 pre = sys.argv[1]
@@ -20,7 +21,20 @@ def gb(v, u):
 
 
 def short(k):
-    return re.sub(r"\(.*", "", k).replace("void ", "").replace("b200rt::", "")
+    m = re.search(r"\b(k_\w+(?:<[^>]*>)?)", k)
+    if m:
+        return m.group(1).replace("(bool)", "")
+    k = k.replace("void ", "")
+    m = re.match(r"([\w:]+)", k)
+    return m.group(1) if m else k
+
+
+def klass(k):
+    if k.startswith("k_isect3") or k.startswith("k_closest_grid") or k.startswith("k_intersect"):
+        return "closest_hit"
+    if k.startswith("k_shadow_shade"):
+        return "shadow_shade"
+    return "other"
 
 
 agg = collections.defaultdict(lambda: [0, 0.0])
@@ -42,22 +56,31 @@ L = collections.OrderedDict()
 for r in rows(pre + "_frame.csv"):
     d = L.setdefault(int(r["ID"]), {"k": short(r["Kernel Name"])})
     d[r["Metric Name"]] = (float(r["Metric Value"].replace(",", "")), r["Metric Unit"])
-print("| # | kernel | ms | FMA pipe % | issue % | DRAM GB | warp instr M |\n|---|---|---|---|---|---|---|")
-first_frame_isect = []
-seen_raygen = 0
+# frames = runs of launches starting at k_scene_cmp; a production frame has no diagnostic (<..., 1>) k_isect3 instantiation
+frames, cur = [], []
 for i, d in L.items():
+    if d["k"].startswith("k_set_cam") and cur:
+        frames.append(cur); cur = []
+    cur.append((i, d))
+if cur:
+    frames.append(cur)
+prod = [f for f in frames if any(d["k"].startswith("k_resolve") for _, d in f) and not any(re.search(r"k_isect3<\d, \d, 1>", d["k"]) for _, d in f)]
+frame = prod[0] if prod else frames[0]
+print(f"production frame: launches {frame[0][0]}..{frame[-1][0]} of the process ({len(frames)} frames / tiles captured)\n")
+print("| # | kernel | ms | FMA pipe % | issue % | threads / instr | DRAM GB | warp instr M |\n|---|---|---|---|---|---|---|---|")
+per = collections.defaultdict(lambda: [0.0, 0.0])
+for i, d in frame:
     t = ms(*d["gpu__time_duration.sum"])
     g = gb(*d["dram__bytes_read.sum"]) + gb(*d["dram__bytes_write.sum"])
-    if d["k"].startswith("k_raygen"):
-        seen_raygen += 1
-    if seen_raygen == 2 and ("k_isect3" in d["k"] or "k_shadow_shade" in d["k"]):          # second frame of the process = the TIME_ONLY frame: production kernels, launches serialised
-        first_frame_isect.append((t, g))
-    if seen_raygen == 2:
-        print(f"| {i} | `{d['k']}` | {t:.3f} | {d['sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_elapsed'][0]:.1f} | "
-              f"{d['smsp__issue_active.avg.pct_of_peak_sustained_active'][0]:.1f} | {g:.3f} | {d['smsp__inst_executed.sum'][0] / 1e6:.1f} |")
-if first_frame_isect:
-    out = {"traffic_bytes_per_frame": sum(g for _, g in first_frame_isect) * 1e9, "launches": len(first_frame_isect),
-           "source": "ncu dram__bytes_read.sum + dram__bytes_write.sum over the k_isect3 + k_shadow_shade launches (closest-hit and shadow queries) of one production C4 frame (" + pre.split('/')[-1] + "_frame.csv)",
-           "kernel_ms_under_ncu": sum(t for t, _ in first_frame_isect)}
-    json.dump(out, open(pre + "_traffic.json", "w"), indent=1)
-    print("\n", json.dumps(out))
+    per[klass(d["k"])][0] += t; per[klass(d["k"])][1] += g
+    if t < 0.004 or d["k"].startswith("at::"):
+        continue
+    print(f"| {i} | `{d['k']}` | {t:.3f} | {d['sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_elapsed'][0]:.1f} | "
+          f"{d['smsp__issue_active.avg.pct_of_peak_sustained_active'][0]:.1f} | {d.get('smsp__thread_inst_executed_per_inst_executed.ratio', (0,))[0]:.1f} | {g:.3f} | {d['smsp__inst_executed.sum'][0] / 1e6:.1f} |")
+print("\n| class | ms (under ncu, cold) | DRAM GB |\n|---|---|---|")
+for k, v in per.items():
+    print(f"| {k} | {v[0]:.3f} | {v[1]:.3f} |")
+print(f"| frame | {sum(v[0] for v in per.values()):.3f} | {sum(v[1] for v in per.values()):.3f} |")
+out = {"traffic_bytes_per_frame": sum(v[1] for v in per.values()) * 1e9, "dram_bytes_per_class": {k: v[1] * 1e9 for k, v in per.items()},
+       "launches": len(frame), "what": "ncu dram__bytes_read.sum + dram__bytes_write.sum of every launch of one production tile/frame (" + pre.split('/')[-1] + "_frame.csv)"}
+json.dump(out, open(pre + "_traffic.json", "w"))
