@@ -174,6 +174,9 @@ B200RT_API unsigned long long b200rt_launch_count(void);
 /* Frames on `device` that were replayed from a captured CUDA graph of their launch sequence (diagnostic; the second call with
  * the same shapes / buffers / flags captures, later ones replay; the camera pose is not part of the key). */
 B200RT_API unsigned long long b200rt_graph_replays(int device);
+/* Checked build only (-DB200RT_CHECK, tools/gpu_check.sh): number of failed index assertions of the library's kernels since load on the
+ * current device; ~0 when the library was not built with the checks. */
+B200RT_API unsigned long long b200rt_debug_check_failures(void);
 /* Free the per-device scratch (packed scene, ray queues).  Safe to call at any time between renders. */
 B200RT_API int b200rt_shutdown(void);
 

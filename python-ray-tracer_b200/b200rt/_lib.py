@@ -71,6 +71,7 @@ def lib():
         L.b200rt_device_count.restype = C.c_int
         L.b200rt_sm_count.argtypes = [C.c_int]; L.b200rt_sm_count.restype = C.c_int
         L.b200rt_launch_count.restype = C.c_ulonglong
+        L.b200rt_debug_check_failures.restype = C.c_ulonglong
         L.b200rt_graph_replays.argtypes = [C.c_int]; L.b200rt_graph_replays.restype = C.c_ulonglong
         L.b200rt_shutdown.restype = C.c_int
         if L.b200rt_args_size() != C.sizeof(Args):

@@ -618,6 +618,7 @@ __global__ void __launch_bounds__(256, 8) k_perm(SortDev s) {
     const uint32_t n = *s.n_live;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const uint2 k = s.keyb[i];
+        RT_CHECK(5, k.x == 0xffffffffu || (k.x < (uint32_t)s.nb && s.base[k.x] + k.y < n));
         if (k.x != 0xffffffffu) s.perm[s.base[k.x] + k.y] = i;
     }
     if (s.tl && threadIdx.x == 0) atomicMax(s.tl + 1, globaltimer_ns());
@@ -708,10 +709,11 @@ __global__ void __launch_bounds__(256, B200RT_SETUP_OCC) k_setup(SceneDev sc, Sh
             if (first) h = pos[0];
 #pragma unroll
             for (int jj = 0; jj < 8; ++jj)
-                if (jj >= sh && ((flags >> jj) & 1u)) s.shidx[(size_t)(j0 + jj - sh) * s.shcap + pos[jj]] = h;
+                if (jj >= sh && ((flags >> jj) & 1u)) { RT_CHECK(3, pos[jj] < s.shcap); s.shidx[(size_t)(j0 + jj - sh) * s.shcap + pos[jj]] = h; }
             j0 += nl;
         }
         if (hit) {
+            RT_CHECK(2, h < s.shcap && h < n);
             s.hP[h] = make_float4(Pb.x, Pb.y, Pb.z, o.w);
             s.hN[h] = make_float4(N.x, N.y, N.z, __int_as_float(id));
             if (s.occl) for (int j = 0; j < sc.L; ++j) s.occl[(size_t)j * s.ocap + h] = 0;
@@ -1687,6 +1689,16 @@ B200RT_API unsigned long long b200rt_launch_count(void) { return b200rt::g_kerne
 B200RT_API unsigned long long b200rt_graph_replays(int device) {
     if (device < 0 || device >= kMaxDevices) return 0;
     return g_ctx[device].n_graph_launches;
+}
+
+B200RT_API unsigned long long b200rt_debug_check_failures(void) {
+#ifdef B200RT_CHECK
+    unsigned int h[8] = {}; unsigned long long t = b200rt::shadow_check_failures();
+    if (cudaMemcpyFromSymbol(h, g_check_fail, sizeof(h)) == cudaSuccess) for (unsigned int v : h) t += v;
+    return t;
+#else
+    return ~0ull;                                               // not a checked build
+#endif
 }
 
 B200RT_API int b200rt_sm_count(int device) {

@@ -109,7 +109,7 @@ __global__ void __launch_bounds__(256) k_cg_bin(SceneDev sc, CGridDev g, int pas
     for (int z = c0[2]; z <= c1[2]; ++z) for (int y = c0[1]; y <= c1[1]; ++y) for (int x = c0[0]; x <= c1[0]; ++x) {
         const int cell = (z * h.n[1] + y) * h.n[0] + x;
         if (pass == 0) atomicAdd(&g.start[cell], 1u);
-        else { const uint32_t k = atomicAdd(&g.cursor[cell], 1u); if ((size_t)k < g.ids_cap) g.ids[k] = (uint16_t)s; }
+        else { const uint32_t k = atomicAdd(&g.cursor[cell], 1u); RT_CHECK(6, k < g.start[cell + 1]); if ((size_t)k < g.ids_cap) g.ids[k] = (uint16_t)s; }
     }
 }
 
@@ -235,6 +235,7 @@ __global__ void __launch_bounds__(256) k_closest_grid(SceneDev sc, CGridDev g, C
                 uint4 nrec = make_uint4(0u, 0u, 0u, 0u);
                 if (inside) nrec = __ldg(&g.rec[ncell]);
                 const uint32_t cnt = rec.x & 0xffffu;
+                RT_CHECK(6, cell >= 0 && cell < h.ncells && (!inside || (ncell >= 0 && ncell < h.ncells)));
                 if (cnt) {
                     offer(rec.x >> 16);
                     if (cnt > 1) { offer(rec.y & 0xffffu);

@@ -336,6 +336,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
             while (cand) {
                 const int bit = __ffs(cand) - 1;
                 cand &= cand - 1;
+                RT_CHECK(0, pos < (NR == 8 ? (uint32_t)kQCap : 512u));
                 sq[pos++] = ((uint32_t)(bit >> 1) * 32u + lane) | ((uint32_t)(2 * pair + (bit & 1)) << 8);
             }
             if (qcnt > kQFl) flush();
@@ -459,6 +460,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
                                 ((c0 + 2 * p < sc.S && !clear_of_beam(cu[e].x, cu[e].z, cw[e].x, cr[e].x)) ||
                                  (c0 + 2 * p + 1 < sc.S && !clear_of_beam(cu[e].y, cu[e].w, cw[e].y, cr[e].y)));
                             const uint32_t bal = __ballot_sync(0xffffffffu, keep);
+                            RT_CHECK(1, !keep || nsv + (uint32_t)__popc(bal & ((1u << lane) - 1u)) < 512u);
                             if (keep) slist[nsv + (uint32_t)__popc(bal & ((1u << lane) - 1u))] = (uint16_t)p;
                             nsv += (uint32_t)__popc(bal);
                         }
@@ -574,6 +576,7 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
             for (int k = 0; k < NR; ++k) {
                 const bool sv = (surv >> k) & 1u;
                 const uint32_t bal = __ballot_sync(0xffffffffu, sv);
+                RT_CHECK(4, !sv || base + (uint32_t)__popc(bal & ((1u << lane) - 1u)) < (gbase / kRegion + 1u) * kRegion);
                 if (sv) q.out_list[base + (uint32_t)__popc(bal & ((1u << lane) - 1u))] = __float_as_uint(ws.o[(uint32_t)k * 32u + lane].w);
                 base += (uint32_t)__popc(bal);
             }
@@ -725,6 +728,7 @@ static cudaError_t isect3_launch_shadow_light(const IsectCfg& cfg, const SceneDe
 
 // The shadow mode lives in isect_shadow.cu (its own module / constant bank):
 cudaError_t shadow_set_attr();
+unsigned long long shadow_check_failures();
 cudaError_t shadow_upload_resident(const PivotDev& pv, int Spad, int L, cudaStream_t st);
 cudaError_t shadow_launch_light(const IsectCfg& cfg, const SceneDev& sc, const QueueDev& q, const PivotDev& pv, size_t max_rays,
                                 const ShadowPlan& sp, int j, bool resident, cudaStream_t st,

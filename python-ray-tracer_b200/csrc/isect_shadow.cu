@@ -8,6 +8,16 @@ namespace b200rt {
 
 cudaError_t shadow_set_attr() { return isect3_set_attr<2>(); }
 
+unsigned long long shadow_check_failures() {            // RT_CHECK failures counted in this translation unit (checked build only)
+#ifdef B200RT_CHECK
+    unsigned int h[8] = {}; unsigned long long t = 0;
+    if (cudaMemcpyFromSymbol(h, g_check_fail, sizeof(h)) == cudaSuccess) for (unsigned int v : h) t += v;
+    return t;
+#else
+    return 0;
+#endif
+}
+
 cudaError_t shadow_upload_resident(const PivotDev& pv, int Spad, int L, cudaStream_t st) {
     std::vector<int> tabs(L);
     for (int j = 0; j < L; ++j) tabs[j] = j;                 // slot j = light j

@@ -16,6 +16,18 @@ constexpr float kBias  = 0.0002f;   // trace.py:82
 constexpr float kEps   = 0.001f;    // intersections.py:46
 constexpr float kTMax  = 999.0f;    // trace.py:17
 
+// Checked build (-DB200RT_CHECK; tools/gpu_check.sh): index assertions at the places where a wrong index would write outside
+// a buffer — compute-sanitizer is closed on this GPU pool (profiles/r02_sanitizer.log), so the checks are the library's own.
+// Every translation unit counts into its own copy; b200rt_debug_check_failures() sums them.  Compiled out otherwise.
+#ifdef B200RT_CHECK
+static __device__ unsigned int g_check_fail[8];
+#define RT_CHECK(slot, cond) do { if (!(cond)) atomicAdd(&g_check_fail[slot], 1u); } while (0)
+#else
+#define RT_CHECK(slot, cond) do { } while (0)
+#endif
+// slots: 0 candidate queue of k_isect3, 1 pair list of the beam culling, 2 hit list / next queue (k_setup), 3 per-light lists,
+//        4 survivor lists, 5 regrouping (bins / permutation), 6 closest-hit grid (cells / ids), 7 light grids (cells)
+
 struct V3 { float x, y, z; };
 
 __device__ __forceinline__ V3 mk(float x, float y, float z) { V3 v; v.x = x; v.y = y; v.z = z; return v; }

@@ -180,6 +180,7 @@ __global__ void __launch_bounds__(256, B200RT_SS_OCC) k_shadow_shade(SceneDev sc
             if (!(kc > 0.f)) continue;                                                                 // :101 (the query's answer would not be used)
             // the first 16 bytes of the cell's record: count + 7 ids (one load where count and ids used to be two dependent ones)
             const uint16_t* recc = g.cells + ((((size_t)(nrmc <= sg_range(0) ? 0 : 1) * sc.L + j) * kSgCells) + (size_t)sg_cell(Dc.x, Dc.y, Dc.z)) * kSgRec;
+            RT_CHECK(7, sg_cell(Dc.x, Dc.y, Dc.z) >= 0 && sg_cell(Dc.x, Dc.y, Dc.z) < kSgCells);
             const uint4 hc = __ldg(reinterpret_cast<const uint4*>(recc));
             if (a.n_traced) warp_count(a.n_traced + j);
             const float A = j < 64 ? s_A[j] : cmax + __fsqrt_rn(dot3(Vp, Vp));

@@ -15,6 +15,17 @@ def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (B200); run with -m gpu")
 
 
+def pytest_sessionfinish(session, exitstatus):
+    """Checked build of the library (tools/gpu_check.sh): report the index-assertion failures of the whole session."""
+    if os.environ.get("B200RT_REPORT_CHECKS"):
+        from b200rt import _lib
+        if _lib._lib is not None:
+            f = int(_lib._lib.b200rt_debug_check_failures())
+            print("\n[b200rt checked build] index-assertion failures in this session:", "not a checked build" if f == 2**64 - 1 else f)
+            if f not in (0, 2**64 - 1):
+                session.exitstatus = 3
+
+
 def load_golden(name):
     z = np.load(os.path.join(GOLDEN, name + ".npz"))
     return {k: z[k] for k in z.files}
