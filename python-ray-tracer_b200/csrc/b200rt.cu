@@ -1025,7 +1025,7 @@ struct DevCtx {
     Buf cgHdr, cgStart, cgCursor, cgIds, cgBig, cgRec;                      // uniform grid of the spheres for per-ray closest-hit queries (closest_grid.cuh)
     int cgrid_ctas = 8;                                              // env B200RT_CGRID_CTAS: CTAs per SM of k_closest_grid
     float cgrid_density = 2.f;                                       // env B200RT_CGRID_DENSITY: cells per sphere the grid aims at
-    int cgrid_from = 1; size_t cgrid_max_paths = (size_t)20 << 20, cgrid_nosort_paths = (size_t)10 << 20;   // env B200RT_CGRID_FROM (first depth served by the grid; 99: never), B200RT_CGRID_MAX_PATHS
+    int cgrid_from = 1; size_t cgrid_max_paths = (size_t)1 << 40, cgrid_nosort_paths = (size_t)10 << 20;   // env B200RT_CGRID_FROM (first depth served by the grid; 99: never), B200RT_CGRID_MAX_PATHS
     bool no_cgrid_all = false;                                       // env B200RT_NO_CGRID_ALL
     bool no_lanes = false, lane_conc = false;                        // env B200RT_NO_LANES, B200RT_LANE_CONC
     bool no_sgrid = false, no_clus = false, no_sort_last = true; int ss_grid = 0; int sgrid_min_s = 1; bool no_sort = false; int sort_posbits = -1, sort_dirn = -1;     // env B200RT_NO_SORT, B200RT_SORT_POSBITS, B200RT_SORT_DIRN (-1: chosen from the queue size)
@@ -1419,14 +1419,13 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
 
             tm.begin(0);
             q.n_in = n_live; q.work = cd + 1;
-            if (cgrid && d >= cgrid_from) {                     // per-ray grid walk; k_isect3 below only takes the queue if the grid turned out unusable (cd[1] stays 0 otherwise)
+            if (cgrid && d >= cgrid_from) {                     // per-ray grid walk (an unusable grid is handled inside the kernel)
                 CGridArgs ca{ q.rayO, q.rayD, n_live, q.hit, nullptr, q.slow, cd + 1 };
                 if (tlb) { ca.tl = tlb + 2 * (size_t)tln++; tlname.push_back("closest<grid> d" + std::to_string(d)); }
                 const int cgg = (int)std::min<size_t>((size_t)c.sm_count * 32, std::max<size_t>((size_t)c.sm_count * 8, cap / (256 * 4)));
                 k_closest_grid<<<cgg, 256, 0, cs>>>(sc, cg, ca); CKL();
-                q.n_in = cd + 1;
             }
-            if (nofilter)                     { if (int rc = launch_intersect<false>(c, sc, q, cs)) return rc; }
+            else if (nofilter)                { if (int rc = launch_intersect<false>(c, sc, q, cs)) return rc; }
             else if (d == 0 && !c.no_pivot)   { const int f0 = tln; CK(isect3_launch_closest<1>(icfg, sc, q, pv, nslots, wk, closest_res, cs, tlb, &tln)); tl_mark("closest<1>", d, f0); }
             else {
                 const int f0 = tln; CK(isect3_launch_closest<0>(icfg, sc, q, pv, nslots, wk, closest_res, cs, tlb, &tln)); tl_mark("closest<0>", d, f0);

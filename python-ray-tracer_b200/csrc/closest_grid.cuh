@@ -19,7 +19,8 @@
 //   * the walk stops after a cell only when the best hit so far lies clearly before the cell's exit (margin 1e-3 + 1e-5 t): every
 //     sphere not yet offered can only be hit beyond that exit;
 //   * spheres whose inflated box covers more than kCgBigCells cells are kept on a short list that every ray tests;
-//     scenes outside the coordinate range (max |C| + max r > 256) do not use the grid at all (the launcher falls back to k_isect3).
+//     beyond coordinates of 256 the inflation and the stop margin grow in proportion (cg_eps_scale); a scene whose lists overflow the
+//     grid's capacity (ids, big list, cells) marks the grid unusable on the device and every ray then tests every sphere in this kernel.
 #pragma once
 #include "isect3.cuh"
 
@@ -33,7 +34,7 @@ constexpr float kCgRange = 256.f;
 struct CGridHdr {                         // device-resident description of the grid (written by k_cg_setup)
     float lo[3], inv[3], edge[3];         // cell (x,y,z) = floor((p - lo) * inv); edge = 1 / inv
     int n[3]; int ncells;
-    int nbig; int ok;                     // ok = 0: grid unusable for this scene (range / big-list overflow): use k_isect3
+    int nbig; int ok;                     // ok = 0: grid unusable for this scene (lists overflow its capacity): k_closest_grid tests every sphere
     uint32_t total;                       // entries of the id list
 };
 
@@ -48,6 +49,9 @@ struct CGridDev {
     size_t ids_cap;                       // capacity of `ids` (entries)
 };
 
+// eps = (2e-3 + 1e-3 r) * max(1, B / 256), B = max |C| + max r: the exact test's slack and the walk's rounding grow linearly with the coordinates
+__device__ __forceinline__ float cg_eps_scale(const float* cmax) { return fmaxf(1.f, (cmax[0] + cmax[1]) * (1.f / kCgRange)); }
+
 // Scene bounds -> grid dimensions.  One CTA.  n_target = cells_per_sphere * S cubic cells (2 per sphere measured best:
 // profiles/r02_cgrid*.txt), <= kCgMaxDim per axis.
 __global__ void __launch_bounds__(256) k_cg_setup(SceneDev sc, CGridDev g, int max_cells, float cells_per_sphere, const uint32_t* cs, int cs_group) {
@@ -56,7 +60,7 @@ __global__ void __launch_bounds__(256) k_cg_setup(SceneDev sc, CGridDev g, int m
     __shared__ float smin[3][256], smax[3][256];
     float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f};
     for (int i = threadIdx.x; i < sc.S; i += blockDim.x) {
-        const float4 sp = sc.sphB[i]; const float r = sqrtf(fmaxf(sp.w, 0.f)) * 1.001f + 2e-3f; const float c[3] = {sp.x, sp.y, sp.z};
+        const float4 sp = sc.sphB[i]; const float r = sqrtf(fmaxf(sp.w, 0.f)) * (1.f + 1e-3f * cg_eps_scale(sc.cmax)) + 2e-3f * cg_eps_scale(sc.cmax); const float c[3] = {sp.x, sp.y, sp.z};
         for (int a = 0; a < 3; ++a) { lo[a] = fminf(lo[a], c[a] - r); hi[a] = fmaxf(hi[a], c[a] + r); }
     }
     for (int a = 0; a < 3; ++a) { smin[a][threadIdx.x] = lo[a]; smax[a][threadIdx.x] = hi[a]; }
@@ -74,7 +78,7 @@ __global__ void __launch_bounds__(256) k_cg_setup(SceneDev sc, CGridDev g, int m
             h.lo[a] = lo[a]; h.edge[a] = ext[a] / (float)h.n[a]; h.inv[a] = (float)h.n[a] / ext[a];
             h.ncells *= h.n[a];
         }
-        h.ok = (sc.S > 0 && sc.cmax[0] + sc.cmax[1] <= kCgRange && vol > 0.f && vol < 3e38f && h.ncells <= max_cells) ? 1 : 0;       // (NaN -> 0)
+        h.ok = (sc.S > 0 && vol > 0.f && vol < 3e38f && h.ncells <= max_cells) ? 1 : 0;       // (NaN -> 0)
         h.nbig = 0; h.total = 0;
         *g.hdr = h;
         s_ncells = h.ok ? h.ncells : 0;
@@ -83,8 +87,8 @@ __global__ void __launch_bounds__(256) k_cg_setup(SceneDev sc, CGridDev g, int m
     for (int i = threadIdx.x; i <= s_ncells; i += blockDim.x) g.start[i] = 0u;       // the counts of pass 0 start from zero
 }
 
-__device__ __forceinline__ void cg_cell_range(const CGridHdr& h, float4 sp, int (&c0)[3], int (&c1)[3]) {
-    const float r = sqrtf(fmaxf(sp.w, 0.f)) * 1.001f + 2e-3f;                 // r + eps, rounded generously
+__device__ __forceinline__ void cg_cell_range(const CGridHdr& h, float4 sp, float escale, int (&c0)[3], int (&c1)[3]) {
+    const float r = sqrtf(fmaxf(sp.w, 0.f)) * (1.f + 1e-3f * escale) + 2e-3f * escale;      // r + eps, rounded generously
     const float c[3] = {sp.x, sp.y, sp.z};
 #pragma unroll
     for (int a = 0; a < 3; ++a) {
@@ -100,7 +104,7 @@ __global__ void __launch_bounds__(256) k_cg_bin(SceneDev sc, CGridDev g, int pas
     if (!h.ok) return;
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= sc.S) return;
-    int c0[3], c1[3]; cg_cell_range(h, sc.sphB[s], c0, c1);
+    int c0[3], c1[3]; cg_cell_range(h, sc.sphB[s], cg_eps_scale(sc.cmax), c0, c1);
     const long long ncov = (long long)(c1[0] - c0[0] + 1) * (c1[1] - c0[1] + 1) * (c1[2] - c0[2] + 1);
     if (ncov > kCgBigCells) {
         if (pass == 0) { const int k = atomicAdd(&g.hdr->nbig, 1); if (k < kCgMaxBig) g.big[k] = (uint32_t)s; }
@@ -146,7 +150,7 @@ __global__ void __launch_bounds__(1024) k_cg_scan(CGridDev g, int max_cells, con
     if (threadIdx.x == 0) {
         g.start[n] = s_carry;
         g.hdr->total = s_carry;
-        if ((size_t)s_carry > g.ids_cap || h.nbig > kCgMaxBig || h.ncells > max_cells) g.hdr->ok = 0;      // does not fit: the launcher's kernels fall back
+        if ((size_t)s_carry > g.ids_cap || h.nbig > kCgMaxBig || h.ncells > max_cells) g.hdr->ok = 0;      // does not fit: k_closest_grid tests every sphere
     }
 }
 
@@ -169,8 +173,7 @@ struct CGridArgs {
     unsigned long long* hit;                 // (float bits of t) << 32 | id per ray; written for every ray
     unsigned long long* tl;                  // diagnostic timeline slot; may be null
     unsigned long long* slow;                // diagnostics: [1] exact tests, [10] cell steps; may be null
-    uint32_t* fallback;                      // stays 0 when the grid served the queue; grid unusable (hdr.ok == 0): set to the queue length, which is
-                                             // the ray count of the k_isect3 launch that follows (an empty launch otherwise)
+    uint32_t* unused;
 };
 
 // One thread per ray: Amanatides-Woo walk through the cells, sphere_exact on every listed sphere, planes last.
@@ -180,7 +183,26 @@ __global__ void __launch_bounds__(256) k_closest_grid(SceneDev sc, CGridDev g, C
     if (a.tl && threadIdx.x == 0) atomicMin(a.tl, globaltimer_ns());
     const CGridHdr h = *g.hdr;
     const uint32_t n = *a.n_in;
-    if (!h.ok) { if (blockIdx.x == 0 && threadIdx.x == 0) *a.fallback = n; return; }       // the caller's k_isect3 launch then takes the whole queue
+    if (!h.ok) {            // grid unusable for this scene (capacity: see k_cg_scan): every ray tests every sphere, in order — slow, correct, rare
+        for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+            const float4 o4 = a.rayO[i], d4 = a.rayD[i];
+            const V3 O = mk(o4.x, o4.y, o4.z), D = mk(d4.x, d4.y, d4.z);
+            float best = kTMax; int id = -1;
+            for (int sid = 0; sid < sc.S; ++sid) {
+                const float4 sp = __ldg(&sc.sphB[sid]);
+                const float t = sphere_exact(O, D, sp.x, sp.y, sp.z, sp.w);
+                if (t > 0.f && t < best) { best = t; id = sid; }                                           // trace.py:26-29
+            }
+            for (int pl = 0; pl < sc.Pl; ++pl) {
+                const float t = plane_exact(O, D, __ldg(&sc.plO[pl]), __ldg(&sc.plN[pl]));
+                if (t > 0.f && t < best) { best = t; id = sc.S + pl; }
+            }
+            a.hit[i] = ((unsigned long long)__float_as_uint(best) << 32) | (uint32_t)id;
+        }
+        return;
+    }
+    const float mscale = cg_eps_scale(sc.cmax);                 // the walk's stop margin grows with the coordinate range like the lists' inflation
+    const float marg0 = 1e-3f * mscale, marg1 = 1e-5f * mscale;
     unsigned long long n_exact = 0, n_steps = 0;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const float4 o4 = a.rayO[i], d4 = a.rayD[i];
@@ -247,7 +269,7 @@ __global__ void __launch_bounds__(256) k_closest_grid(SceneDev sc, CGridDev g, C
                     if (cnt > 7) { const uint32_t s0 = __ldg(&g.start[cell]); for (uint32_t k = 7; k < cnt; ++k) offer((uint32_t)__ldg(&g.ids[s0 + k])); } } } } } } }
                 }
                 if (a.slow) ++n_steps;
-                if (best < texit - (1e-3f + 1e-5f * texit) || !inside) break;         // nothing beyond this cell can be closer / the ray leaves the grid
+                if (best < texit - fmaf(marg1, texit, marg0) || !inside) break;   // nothing beyond this cell can be closer / the ray leaves the grid
                 if (ax == 0) { c[0] = cn; tmax[0] += tdel[0]; } else if (ax == 1) { c[1] = cn; tmax[1] += tdel[1]; } else { c[2] = cn; tmax[2] += tdel[2]; }
                 cell = ncell; rec = nrec;
             }
