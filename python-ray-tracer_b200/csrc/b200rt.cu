@@ -186,7 +186,7 @@ __constant__ int c_dy[9] = { 0, 0, 0, +1, -1, +1, +1, -1, -1 };
 // Queue position: without anti-aliasing every slot has a ray, so position = slot (the queue is in slot order by
 // construction); with it, border slots are skipped and the queue is compacted IN ORDER (ordered_append8: chunks of
 // 256 slots in ticket order) — the queue order decides which rays share a group in k_isect3 at every later stage.
-__global__ void k_raygen(FrameDev f, float4* __restrict__ rayO, float4* __restrict__ rayD, unsigned long long* __restrict__ hit,
+__global__ void k_raygen(FrameDev f, float4* __restrict__ rayD, unsigned long long* __restrict__ hit,
                          uint32_t* n_live, unsigned long long* ostat, uint32_t* ticket) {
     const uint32_t nslots = f.npix * (uint32_t)f.ns;
     const uint32_t nchunks = (nslots + 255u) / 256u;
@@ -205,7 +205,7 @@ __global__ void k_raygen(FrameDev f, float4* __restrict__ rayO, float4* __restri
         if (c >= nchunks) break;
         uint32_t slot = c * 256u + threadIdx.x;
         bool valid = slot < nslots;
-        float4 o = make_float4(0, 0, 0, 0), d = make_float4(0, 0, 0, 0);
+        float4 d = make_float4(0, 0, 0, 0);
         if (valid) {
             uint32_t k = slot / f.npix, p = slot - k * f.npix;
             int lc, y; slot_pixel(f, p, lc, y);
@@ -224,14 +224,13 @@ __global__ void k_raygen(FrameDev f, float4* __restrict__ rayO, float4* __restri
                 double by = cm.rot[3] * px + cm.rot[4] * py + cm.rot[5] * pz;
                 double bz = cm.rot[6] * px + cm.rot[7] * py + cm.rot[8] * pz;
                 double n = sqrt(bx * bx + by * by + bz * bz);
-                d = make_float4((float)(bx / n), (float)(by / n), (float)(bz / n), 0.f);
-                o = make_float4((float)cm.ox, (float)cm.oy, (float)cm.oz, __uint_as_float(slot));
+                d = make_float4((float)(bx / n), (float)(by / n), (float)(bz / n), __uint_as_float(slot));     // origin = the camera (CamDev.cox..coz = (float)ox..oz): not stored
             }
         }
         uint32_t pos = slot;
         if (f.ns > 1) { uint32_t pp[8]; ordered_append8(valid ? 1u : 0u, 1, c, ostat, n_live, c == nchunks - 1, pp); pos = pp[0]; }
         else if (slot == 0) *n_live = nslots;
-        if (valid) { rayO[pos] = o; rayD[pos] = d; if (hit) hit[pos] = kNoHitKey; }
+        if (valid) { rayD[pos] = d; if (hit) hit[pos] = kNoHitKey; }
     }
 }
 
@@ -282,8 +281,9 @@ k_intersect(SceneDev sc, QueueDev q) {
                     O = mk(p.x, p.y, p.z);
                     D = normalize3(sub3(mk(l.x, l.y, l.z), O));            // common.py:84-91
                 } else {
-                    const float4 o = q.rayO[i], d = q.rayD[i];
-                    O = mk(o.x, o.y, o.z); D = mk(d.x, d.y, d.z);
+                    const float4 d = q.rayD[i];
+                    D = mk(d.x, d.y, d.z);
+                    uint32_t slot_; O = ray_origin(q.rayO, q.camo, i, D, d.w, slot_);
                 }
             }
             dx[r] = D.x; dy[r] = D.y; dz[r] = D.z;
@@ -490,7 +490,7 @@ __global__ void k_pivot(SceneDev sc, const CamDev* cam, const int* perm, float4*
 // ------------------------------------------------------------------------------------------------
 struct GridDev { float lo[3], inv[3]; int n[3]; int dn; };      // position cells n[0] x n[1] x n[2], direction cells 6 x dn x dn
 struct SortDev {
-    const float4* rayO; const float4* rayD; const unsigned long long* hit; const uint32_t* n_live;
+    const float4* rayO; const float4* rayD; const float* camo; const unsigned long long* hit; const uint32_t* n_live;
     const GridDev* grid; uint2* keyb; uint32_t* hist; uint32_t* part; uint32_t* base; uint32_t* perm; uint32_t* n_sorted;
     int nb; int use_dir;
     unsigned long long* tl;      // diagnostic timeline slot: k_key start .. k_perm end (may be null)
@@ -532,7 +532,8 @@ __global__ void __launch_bounds__(256, 8) k_key(SceneDev sc, SortDev s) {
             const unsigned long long key = s.hit[i];
             const int id = (int)(uint32_t)key;
             if (id >= 0) {
-                const float4 o = s.rayO[i], d = s.rayD[i];
+                const float4 d = s.rayD[i];
+                uint32_t slot_; const V3 o = ray_origin(s.rayO, s.camo, i, mk(d.x, d.y, d.z), d.w, slot_);
                 const float t = __uint_as_float((uint32_t)(key >> 32));
                 const float px = fmaf(t, d.x, o.x), py = fmaf(t, d.y, o.y), pz = fmaf(t, d.z, o.z);
                 uint32_t dc = 0;
@@ -634,10 +635,10 @@ __global__ void __launch_bounds__(256, 8) k_perm(SortDev s) {
 #define B200RT_SHADE_OCC 6
 #endif
 struct ShadeDev {
-    const float4* rayO; const float4* rayD;      // this depth's ray queue (k_setup input)
+    const float4* rayO; const float4* rayD; const float* camo;      // this depth's ray queue (k_setup input; rt_math.cuh: ray_origin)
     const unsigned long long* hit;               // packed closest hit per ray (k_setup input)
     const uint32_t* perm;                        // k_setup walks the queue through this permutation (regrouped hits), or null
-    float4* rayO2; float4* rayD2; unsigned long long* hit2;   // next depth's ray queue (k_setup output; hit2 pre-set to "no hit")
+    float4* rayD2; unsigned long long* hit2;     // next depth's ray queue: directions (the origins are derived from hP); hit2 pre-set to "no hit"
     float4* hP; float4* hN;              // hit records: (biased P, slot) (N, id)
     uint8_t* occl; size_t ocap;          // [light][hit], row stride ocap (zeroed by k_setup, set by the shadow query)
     float4* acc;                         // per-slot colour accumulators (R, G, B, -): one 16-byte read-modify-write per hit
@@ -667,9 +668,11 @@ __global__ void __launch_bounds__(256, B200RT_SETUP_OCC) k_setup(SceneDev sc, Sh
         const bool is_last = (c == nchunks - 1);
         const uint32_t i = c * 256u + threadIdx.x;
         bool hit = false; float4 o = make_float4(0, 0, 0, 0), d = o; float t = 0.f; int id = -1;
-        if (i < n) {                                 // the three loads go out together (the ray is read even if it missed)
+        if (i < n) {                                 // the loads go out together (the ray is read even if it missed)
             const uint32_t src = s.perm ? s.perm[i] : i;
-            const unsigned long long key = s.hit[src]; o = s.rayO[src]; d = s.rayD[src];
+            const unsigned long long key = s.hit[src]; d = s.rayD[src];
+            uint32_t slot; const V3 O = ray_origin(s.rayO, s.camo, src, mk(d.x, d.y, d.z), d.w, slot);
+            o = make_float4(O.x, O.y, O.z, __uint_as_float(slot));
             id = (int)(uint32_t)key; t = __uint_as_float((uint32_t)(key >> 32)); hit = id >= 0;
         }
         V3 Pb = mk(0, 0, 0), N = mk(0, 0, 0);
@@ -721,9 +724,7 @@ __global__ void __launch_bounds__(256, B200RT_SETUP_OCC) k_setup(SceneDev sc, Sh
                 const V3 D = mk(d.x, d.y, d.z);      // the next closest-hit launch runs beside this depth's shadow launches
                 const float dn = dot3(D, N);
                 const V3 R = normalize3(madd3(D, -2.0f * dn, N));                              // common.py:113-120
-                const V3 O2 = madd3(Pb, kBias, R);                                             // trace.py:110
-                s.rayO2[h] = make_float4(O2.x, O2.y, O2.z, o.w);                               // the hit list IS the next queue
-                s.rayD2[h] = make_float4(R.x, R.y, R.z, 0.f);
+                s.rayD2[h] = make_float4(R.x, R.y, R.z, 0.f);                                  // the hit list IS the next queue: origin = Pb + BIAS * R (trace.py:110), derived by the readers
                 if (s.hit2) s.hit2[h] = kNoHit;     // (null: the next closest-hit query is a single k_isect3 launch that stores its keys)
             }
         }
@@ -743,7 +744,9 @@ __global__ void __launch_bounds__(256, B200RT_SETUP_OCC) k_setup_scatter(SceneDe
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const uint2 kb = keyb[i];
         if (kb.x == 0xffffffffu) continue;                                           // miss: the path ends (trace.py:56-58)
-        const unsigned long long key = s.hit[i]; const float4 o = s.rayO[i], d = s.rayD[i];
+        const unsigned long long key = s.hit[i]; const float4 d = s.rayD[i];
+        uint32_t slot; const V3 O = ray_origin(s.rayO, s.camo, i, mk(d.x, d.y, d.z), d.w, slot);
+        const float4 o = make_float4(O.x, O.y, O.z, __uint_as_float(slot));
         const uint32_t h = base[kb.x] + kb.y;
         const int id = (int)(uint32_t)key; const float t = __uint_as_float((uint32_t)(key >> 32));
         V3 N;
@@ -757,9 +760,7 @@ __global__ void __launch_bounds__(256, B200RT_SETUP_OCC) k_setup_scatter(SceneDe
             const V3 D = mk(d.x, d.y, d.z);
             const float dn = dot3(D, N);
             const V3 R = normalize3(madd3(D, -2.0f * dn, N));                        // common.py:113-120
-            const V3 O2 = madd3(Pb, kBias, R);                                       // trace.py:110
-            s.rayO2[h] = make_float4(O2.x, O2.y, O2.z, o.w);
-            s.rayD2[h] = make_float4(R.x, R.y, R.z, 0.f);
+            s.rayD2[h] = make_float4(R.x, R.y, R.z, 0.f);                            // origin = Pb + BIAS * R (trace.py:110), derived by the readers
             if (s.hit2) s.hit2[h] = kNoHit;
         }
     }
@@ -988,7 +989,7 @@ constexpr int kLanes = 2;     // wavefronts of one call that may be in flight at
 // sharded frame, where a single wavefront leaves the SMs idle in the tails of its persistent kernels and between its ~30
 // dependent small launches — as two half-width wavefronts in two lanes whose launch sequences interleave on the device.
 struct Lane {
-    Buf rayO[2], rayD[2], hitKey[2];                               // ray queues, double-buffered by depth parity
+    Buf rayD[2], hitKey[2];                                        // ray queues (directions; origins are derived: rt_math.cuh ray_origin), double-buffered by depth parity
     Buf hP[kSets], hN[kSets], occl[kSets], shidx[kSets], shidx2[kSets];   // hit records / shadow state: ring of kSets depths
     Buf acc, ostat;
     Buf sortKey, sortPerm, sortHist, sortBase, sortPart;           // regrouping of bounce-depth hits (k_key .. k_perm)
@@ -997,7 +998,7 @@ struct Lane {
     cudaStream_t chainStream = nullptr, lightStream[kSide] = {}, shadeStream = nullptr;
     cudaEvent_t evFork = nullptr, evJoin = nullptr, evSetup[kSets] = {}, evShade[kSets] = {}, evLight[kSide] = {};
     void release() {
-        Buf* all[] = { &rayO[0], &rayO[1], &rayD[0], &rayD[1], &hitKey[0], &hitKey[1], &acc, &ostat, &sortKey, &sortPerm, &sortHist, &sortBase, &sortPart };
+        Buf* all[] = { &rayD[0], &rayD[1], &hitKey[0], &hitKey[1], &acc, &ostat, &sortKey, &sortPerm, &sortHist, &sortBase, &sortPart };
         for (Buf* b : all) b->release();
         for (int i = 0; i < kSets; ++i) { hP[i].release(); hN[i].release(); occl[i].release(); shidx[i].release(); shidx2[i].release(); }
         if (chainStream) {
@@ -1283,7 +1284,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     for (int l = 0; l < nlanes; ++l) {
         Lane& ln = c.lane[l];
         for (int b = 0; b < 2; ++b) {                            // depth d: ray queue d & 1 (see the launch sequence below)
-            CK(ln.rayO[b].ensure(sizeof(float4) * cap)); CK(ln.rayD[b].ensure(sizeof(float4) * cap));
+            CK(ln.rayD[b].ensure(sizeof(float4) * cap));
             CK(ln.hitKey[b].ensure(sizeof(unsigned long long) * cap));
         }
         for (int b = 0; b < nsets; ++b) {
@@ -1385,7 +1386,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         tm.begin(2);
         CK(cudaMemsetAsync(acc, 0, sizeof(float4) * nslots, cs));
         if (ns > 1) CK(cudaMemsetAsync(ln.ostat.p, 0, ostat_bytes, cs));
-        k_raygen<<<(int)std::min<size_t>((nslots + 255) / 256, (size_t)small_grid), 256, 0, cs>>>(f, ln.rayO[0].as<float4>(), ln.rayD[0].as<float4>(), store_keys ? nullptr : ln.hitKey[0].as<unsigned long long>(), ctr + 0,
+        k_raygen<<<(int)std::min<size_t>((nslots + 255) / 256, (size_t)small_grid), 256, 0, cs>>>(f, ln.rayD[0].as<float4>(), store_keys ? nullptr : ln.hitKey[0].as<unsigned long long>(), ctr + 0,
                                                                                                          ln.ostat.as<unsigned long long>(), reinterpret_cast<uint32_t*>(ln.ostat.as<unsigned long long>() + ostat_stride * ostat_passes));
         CKL();
         tm.end(2);
@@ -1405,12 +1406,14 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             uint32_t* n_live = d == 0 ? ctr + 0 : ctr + cps * (d - 1) + 3;       // the hit list of depth d-1 is the ray queue of depth d
             uint32_t* wk = c.work.as<uint32_t>() + ((size_t)ch * (depth + 1) + d) * work_per_depth;      // k_isect3 group counters
             QueueDev q{};
-            q.rayO = ln.rayO[b].as<float4>(); q.rayD = ln.rayD[b].as<float4>(); q.hP = ln.hP[hs].as<float4>();
+            q.rayO = d == 0 ? nullptr : ln.hP[(d - 1) % nsets].as<float4>();     // depth >= 1: the hit records of the depth before are the queue
+            q.camo = &c.camDev.as<CamDev>()->cox;
+            q.rayD = ln.rayD[b].as<float4>(); q.hP = ln.hP[hs].as<float4>();
             q.hit = ln.hitKey[b].as<unsigned long long>(); q.occl = sgrid ? nullptr : ln.occl[hs].as<uint8_t>(); q.ocap = cap;
             q.slow = (stats && !(a->flags & B200RT_F_TIME_ONLY)) ? c.slow.as<unsigned long long>() : nullptr;
             ShadeDev s{};
-            s.rayO = q.rayO; s.rayD = q.rayD; s.hit = q.hit;
-            s.rayO2 = ln.rayO[b ^ 1].as<float4>(); s.rayD2 = ln.rayD[b ^ 1].as<float4>(); s.hit2 = store_keys ? nullptr : ln.hitKey[b ^ 1].as<unsigned long long>();
+            s.rayO = q.rayO; s.rayD = q.rayD; s.camo = q.camo; s.hit = q.hit;
+            s.rayD2 = ln.rayD[b ^ 1].as<float4>(); s.hit2 = store_keys ? nullptr : ln.hitKey[b ^ 1].as<unsigned long long>();
             s.hP = ln.hP[hs].as<float4>(); s.hN = ln.hN[hs].as<float4>(); s.occl = sgrid ? nullptr : ln.occl[hs].as<uint8_t>(); s.ocap = cap;
             s.acc = acc;
             s.n_live = n_live; s.n_hit = cd + 3;
@@ -1420,7 +1423,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             tm.begin(0);
             q.n_in = n_live; q.work = cd + 1;
             if (cgrid && d >= cgrid_from) {                     // per-ray grid walk (an unusable grid is handled inside the kernel)
-                CGridArgs ca{ q.rayO, q.rayD, n_live, q.hit, nullptr, q.slow, cd + 1 };
+                CGridArgs ca{ q.rayO, q.rayD, q.camo, n_live, q.hit, nullptr, q.slow, cd + 1 };
                 if (tlb) { ca.tl = tlb + 2 * (size_t)tln++; tlname.push_back("closest<grid> d" + std::to_string(d)); }
                 const int cgg = (int)std::min<size_t>((size_t)c.sm_count * 32, std::max<size_t>((size_t)c.sm_count * 8, cap / (256 * 4)));
                 k_closest_grid<<<cgg, 256, 0, cs>>>(sc, cg, ca); CKL();
@@ -1434,7 +1437,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             tm.begin(2);
             bool scatter = false;
             if (regroup && d >= 1 && (d < depth || !c.no_sort_last)) {
-                SortDev so{ q.rayO, q.rayD, q.hit, n_live, c.sortGrid.as<GridDev>(), ln.sortKey.as<uint2>(), ln.sortHist.as<uint32_t>(), ln.sortPart.as<uint32_t>(),
+                SortDev so{ q.rayO, q.rayD, q.camo, q.hit, n_live, c.sortGrid.as<GridDev>(), ln.sortKey.as<uint2>(), ln.sortHist.as<uint32_t>(), ln.sortPart.as<uint32_t>(),
                             ln.sortBase.as<uint32_t>(), ln.sortPerm.as<uint32_t>(), cd + 2, sort_nb, d < depth ? 1 : 0, nullptr };
                 if (tlb) { so.tl = tlb + 2 * (size_t)tln++; tlname.push_back("sort d" + std::to_string(d)); }
                 k_key<<<small_grid, 256, 0, cs>>>(sc, so); CKL();

@@ -169,7 +169,7 @@ __global__ void __launch_bounds__(256) k_cg_pack(CGridDev g, const uint32_t* cs,
 }
 
 struct CGridArgs {
-    const float4* rayO; const float4* rayD; const uint32_t* n_in;
+    const float4* rayO; const float4* rayD; const float* camo; const uint32_t* n_in;      // ray queue (rt_math.cuh: ray_origin)
     unsigned long long* hit;                 // (float bits of t) << 32 | id per ray; written for every ray
     unsigned long long* tl;                  // diagnostic timeline slot; may be null
     unsigned long long* slow;                // diagnostics: [1] exact tests, [10] cell steps; may be null
@@ -185,8 +185,9 @@ __global__ void __launch_bounds__(256) k_closest_grid(SceneDev sc, CGridDev g, C
     const uint32_t n = *a.n_in;
     if (!h.ok) {            // grid unusable for this scene (capacity: see k_cg_scan): every ray tests every sphere, in order — slow, correct, rare
         for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-            const float4 o4 = a.rayO[i], d4 = a.rayD[i];
-            const V3 O = mk(o4.x, o4.y, o4.z), D = mk(d4.x, d4.y, d4.z);
+            const float4 d4 = a.rayD[i];
+            const V3 D = mk(d4.x, d4.y, d4.z);
+            uint32_t slot_; const V3 O = ray_origin(a.rayO, a.camo, i, D, d4.w, slot_);
             float best = kTMax; int id = -1;
             for (int sid = 0; sid < sc.S; ++sid) {
                 const float4 sp = __ldg(&sc.sphB[sid]);
@@ -205,8 +206,9 @@ __global__ void __launch_bounds__(256) k_closest_grid(SceneDev sc, CGridDev g, C
     const float marg0 = 1e-3f * mscale, marg1 = 1e-5f * mscale;
     unsigned long long n_exact = 0, n_steps = 0;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const float4 o4 = a.rayO[i], d4 = a.rayD[i];
-        const V3 O = mk(o4.x, o4.y, o4.z), D = mk(d4.x, d4.y, d4.z);
+        const float4 d4 = a.rayD[i];
+        const V3 D = mk(d4.x, d4.y, d4.z);
+        uint32_t slot_; const V3 O = ray_origin(a.rayO, a.camo, i, D, d4.w, slot_);
         float best = kTMax; uint32_t bid = 0xffffffffu;
         auto offer = [&](uint32_t sid) {
             const float4 sp = __ldg(&sc.sphB[sid]);

@@ -37,8 +37,9 @@ constexpr unsigned long long kNoHitKey = ((unsigned long long)0x4479c000u << 32)
 constexpr int kThreads = 256;            // threads per CTA
 
 struct QueueDev {
-    // closest-hit input: ray queue (O.xyz, slot) / (D.xyz, -)
-    const float4* rayO; const float4* rayD;
+    // closest-hit input: ray queue.  rayD = (D.xyz, slot bits at depth 0); rayO = the biased hit points (Pb.xyz, slot) of the depth before, from
+    // which the origin is Pb + BIAS * D, or null at depth 0: origin = the camera constant camo[0..2] (rt_math.cuh: ray_origin)
+    const float4* rayO; const float4* rayD; const float* camo;
     // shadow input: hit records
     const float4* hP;                    // (biased hit point, slot)
     const uint32_t* n_in;                // number of rays (closest) / entries of the light's list = input of its FIRST pass (shadow)
@@ -208,7 +209,15 @@ k_isect3(SceneDev sc, QueueDev q, PivotDev pv, int c0, int cnt, int j, int tb) {
             } else {
                 float4 oo[NR], dd[NR];
 #pragma unroll
-                for (int k = 0; k < NR; ++k) { const uint32_t i = min(gbase + (uint32_t)k * 32u + lane, ilast); oo[k] = q.rayO[i]; dd[k] = q.rayD[i]; }
+                for (int k = 0; k < NR; ++k) {
+                    const uint32_t i = min(gbase + (uint32_t)k * 32u + lane, ilast);
+                    dd[k] = q.rayD[i];
+                    oo[k] = q.rayO ? q.rayO[i] : make_float4(q.camo[0], q.camo[1], q.camo[2], 0.f);
+                }
+                if (q.rayO) {                                  // bounce origin from the hit record: Pb + BIAS * R (trace.py:110; ray_origin())
+#pragma unroll
+                    for (int k = 0; k < NR; ++k) { const V3 o2 = madd3(mk(oo[k].x, oo[k].y, oo[k].z), kBias, mk(dd[k].x, dd[k].y, dd[k].z)); oo[k].x = o2.x; oo[k].y = o2.y; oo[k].z = o2.z; }
+                }
 #pragma unroll
                 for (int k = 0; k < NR; ++k) { ws.o[k * 32 + lane] = oo[k]; ws.d[k * 32 + lane] = dd[k]; }
             }
