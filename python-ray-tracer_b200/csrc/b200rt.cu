@@ -488,7 +488,6 @@ __global__ void k_pivot(SceneDev sc, const CamDev* cam, const int* perm, float4*
 // own and accumulates into its own slot.  One counting sort per depth: k_key (bin + rank within the bin from a
 // warp-aggregated atomic), k_binsum / k_binscan (exclusive scan of the bin counts), k_perm (scatter).
 // ------------------------------------------------------------------------------------------------
-struct GridDev { float lo[3], inv[3]; int n[3]; int dn; };      // position cells n[0] x n[1] x n[2], direction cells 6 x dn x dn
 struct SortDev {
     const float4* rayO; const float4* rayD; const float* camo; const unsigned long long* hit; const uint32_t* n_live;
     const GridDev* grid; uint2* keyb; uint32_t* hist; uint32_t* part; uint32_t* base; uint32_t* perm; uint32_t* n_sorted;
@@ -534,29 +533,7 @@ __global__ void __launch_bounds__(256, 8) k_key(SceneDev sc, SortDev s) {
             if (id >= 0) {
                 const float4 d = s.rayD[i];
                 uint32_t slot_; const V3 o = ray_origin(s.rayO, s.camo, i, mk(d.x, d.y, d.z), d.w, slot_);
-                const float t = __uint_as_float((uint32_t)(key >> 32));
-                const float px = fmaf(t, d.x, o.x), py = fmaf(t, d.y, o.y), pz = fmaf(t, d.z, o.z);
-                uint32_t dc = 0;
-                if (s.use_dir) {                                 // (approximate arithmetic: this only chooses a bin)
-                    float nx, ny, nz;
-                    if (id < sc.S) { const float4 c = __ldg(&sc.sphB[id]); nx = px - c.x; ny = py - c.y; nz = pz - c.z; const float il = rsqrtf(fmaxf(nx * nx + ny * ny + nz * nz, 1e-30f)); nx *= il; ny *= il; nz *= il; }
-                    else           { const float4 nu = __ldg(&sc.plNu[id - sc.S]); nx = nu.x; ny = nu.y; nz = nu.z; }
-                    const float dn2 = 2.f * (d.x * nx + d.y * ny + d.z * nz);
-                    const float rx = d.x - dn2 * nx, ry = d.y - dn2 * ny, rz = d.z - dn2 * nz;
-                    const float ax = fabsf(rx), ay = fabsf(ry), az = fabsf(rz);
-                    float m, u, v; uint32_t face;
-                    if (ax >= ay && ax >= az) { m = ax; u = ry; v = rz; face = rx < 0.f ? 1u : 0u; }
-                    else if (ay >= az)        { m = ay; u = rx; v = rz; face = ry < 0.f ? 3u : 2u; }
-                    else                      { m = az; u = rx; v = ry; face = rz < 0.f ? 5u : 4u; }
-                    const float im = 0.5f * (float)g.dn / fmaxf(m, 1e-30f);
-                    const int iu = min(g.dn - 1, max(0, (int)(u * im + 0.5f * (float)g.dn)));
-                    const int iv = min(g.dn - 1, max(0, (int)(v * im + 0.5f * (float)g.dn)));
-                    dc = (face * (uint32_t)g.dn + (uint32_t)iu) * (uint32_t)g.dn + (uint32_t)iv;
-                }
-                const int ix = min(g.n[0] - 1, max(0, (int)((px - g.lo[0]) * g.inv[0])));
-                const int iy = min(g.n[1] - 1, max(0, (int)((py - g.lo[1]) * g.inv[1])));
-                const int iz = min(g.n[2] - 1, max(0, (int)((pz - g.lo[2]) * g.inv[2])));
-                b = ((dc * (uint32_t)g.n[0] + (uint32_t)ix) * (uint32_t)g.n[1] + (uint32_t)iy) * (uint32_t)g.n[2] + (uint32_t)iz;
+                b = sort_bin(sc, g, o, mk(d.x, d.y, d.z), __uint_as_float((uint32_t)(key >> 32)), id, s.use_dir);
             }
         }
         // one atomic per distinct bin of the warp: neighbouring rays often share a bin
@@ -1027,6 +1004,7 @@ struct DevCtx {
     int cgrid_ctas = 8;                                              // env B200RT_CGRID_CTAS: CTAs per SM of k_closest_grid
     float cgrid_density = 2.f;                                       // env B200RT_CGRID_DENSITY: cells per sphere the grid aims at
     int cgrid_from = 1; size_t cgrid_max_paths = (size_t)1 << 40, cgrid_nosort_paths = (size_t)10 << 20;   // env B200RT_CGRID_FROM (first depth served by the grid; 99: never), B200RT_CGRID_MAX_PATHS
+    bool no_fold_key = false;                                        // env B200RT_NO_FOLD_KEY: separate k_key launch
     bool no_cgrid_all = false;                                       // env B200RT_NO_CGRID_ALL
     bool no_lanes = false, lane_conc = false;                        // env B200RT_NO_LANES, B200RT_LANE_CONC
     bool no_sgrid = false, no_clus = false, no_sort_last = true; int ss_grid = 0; int sgrid_min_s = 1; bool no_sort = false; int sort_posbits = -1, sort_dirn = -1;     // env B200RT_NO_SORT, B200RT_SORT_POSBITS, B200RT_SORT_DIRN (-1: chosen from the queue size)
@@ -1138,6 +1116,7 @@ int init_ctx(DevCtx& c, int device) {
     { const char* e = getenv("B200RT_CGRID_DENSITY"); if (e) c.cgrid_density = std::max(0.25f, (float)atof(e)); }
     { const char* e = getenv("B200RT_CGRID_CTAS"); if (e) c.cgrid_ctas = std::max(1, std::min(32, atoi(e))); }
     { const char* e = getenv("B200RT_CGRID_MAX_PATHS"); if (e) c.cgrid_max_paths = (size_t)std::max(0ll, atoll(e)); }
+    { const char* e = getenv("B200RT_NO_FOLD_KEY"); c.no_fold_key = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_NO_CGRID_ALL"); c.no_cgrid_all = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_CGRID_NOSORT_PATHS"); if (e) c.cgrid_nosort_paths = (size_t)std::max(0ll, atoll(e)); }
     { const char* e = getenv("B200RT_LANE_CONC"); c.lane_conc = e && atoi(e) != 0; }
@@ -1421,12 +1400,16 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             s.amb = (float)a->amb; s.lamb = (float)a->lamb; s.weight = wts[d]; s.emit_reflection = d < depth;
 
             tm.begin(0);
+            bool key_folded = false;                            // the regrouping keys of this depth's hits were computed by the closest-hit kernel
             q.n_in = n_live; q.work = cd + 1;
             if (cgrid && d >= cgrid_from) {                     // per-ray grid walk (an unusable grid is handled inside the kernel)
-                CGridArgs ca{ q.rayO, q.rayD, q.camo, n_live, q.hit, nullptr, q.slow, cd + 1 };
+                CGridArgs ca{ q.rayO, q.rayD, q.camo, n_live, q.hit, nullptr, q.slow, cd + 1, nullptr, nullptr, nullptr, 0 };
+                const bool sort_here = regroup && d >= 1 && (d < depth || !c.no_sort_last);
+                if (sort_here && !c.no_fold_key) { ca.sgrid = c.sortGrid.as<GridDev>(); ca.hist = ln.sortHist.as<uint32_t>(); ca.keyb = ln.sortKey.as<uint2>(); ca.use_dir = d < depth ? 1 : 0; key_folded = true; }
                 if (tlb) { ca.tl = tlb + 2 * (size_t)tln++; tlname.push_back("closest<grid> d" + std::to_string(d)); }
                 const int cgg = (int)std::min<size_t>((size_t)c.sm_count * 32, std::max<size_t>((size_t)c.sm_count * 8, cap / (256 * 4)));
-                k_closest_grid<<<cgg, 256, 0, cs>>>(sc, cg, ca); CKL();
+                if (key_folded) k_closest_grid_key<<<cgg, 256, 0, cs>>>(sc, cg, ca); else k_closest_grid<<<cgg, 256, 0, cs>>>(sc, cg, ca);
+                CKL();
             }
             else if (nofilter)                { if (int rc = launch_intersect<false>(c, sc, q, cs)) return rc; }
             else if (d == 0 && !c.no_pivot)   { const int f0 = tln; CK(isect3_launch_closest<1>(icfg, sc, q, pv, nslots, wk, closest_res, cs, tlb, &tln)); tl_mark("closest<1>", d, f0); }
@@ -1440,7 +1423,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
                 SortDev so{ q.rayO, q.rayD, q.camo, q.hit, n_live, c.sortGrid.as<GridDev>(), ln.sortKey.as<uint2>(), ln.sortHist.as<uint32_t>(), ln.sortPart.as<uint32_t>(),
                             ln.sortBase.as<uint32_t>(), ln.sortPerm.as<uint32_t>(), cd + 2, sort_nb, d < depth ? 1 : 0, nullptr };
                 if (tlb) { so.tl = tlb + 2 * (size_t)tln++; tlname.push_back("sort d" + std::to_string(d)); }
-                k_key<<<small_grid, 256, 0, cs>>>(sc, so); CKL();
+                if (!key_folded) { k_key<<<small_grid, 256, 0, cs>>>(sc, so); CKL(); }
                 k_binsum<<<sort_nblk, 256, 0, cs>>>(so); CKL();
                 k_binscan<<<sort_nblk, 256, 0, cs>>>(so); CKL();
                 // (the scan path's per-light lists need the ordered append; at a full C4 frame the 16-byte scattered stores cost more

@@ -26,6 +26,45 @@
 
 namespace b200rt {
 
+// ---- regrouping key of a hit (see "Regrouping of the hits of depth >= 1" in b200rt.cu): bin = (cube-map cell of the REFLECTED direction, grid
+// cell of the hit point).  Shared by k_key and by k_closest_grid, which computes it in its epilogue where (O, D, t, id) are still in registers
+// (one launch and 40 bytes of reads per ray less).  Approximate arithmetic: this only chooses a bin.
+struct GridDev { float lo[3], inv[3]; int n[3]; int dn; };      // position cells n[0] x n[1] x n[2], direction cells 6 x dn x dn
+__device__ __forceinline__ uint32_t sort_bin(const SceneDev& sc, const GridDev& g, V3 o, V3 d, float t, int id, int use_dir) {
+    const float px = fmaf(t, d.x, o.x), py = fmaf(t, d.y, o.y), pz = fmaf(t, d.z, o.z);
+    uint32_t dc = 0;
+    if (use_dir) {
+        float nx, ny, nz;
+        if (id < sc.S) { const float4 c = __ldg(&sc.sphB[id]); nx = px - c.x; ny = py - c.y; nz = pz - c.z; const float il = rsqrtf(fmaxf(nx * nx + ny * ny + nz * nz, 1e-30f)); nx *= il; ny *= il; nz *= il; }
+        else           { const float4 nu = __ldg(&sc.plNu[id - sc.S]); nx = nu.x; ny = nu.y; nz = nu.z; }
+        const float dn2 = 2.f * (d.x * nx + d.y * ny + d.z * nz);
+        const float rx = d.x - dn2 * nx, ry = d.y - dn2 * ny, rz = d.z - dn2 * nz;
+        const float ax = fabsf(rx), ay = fabsf(ry), az = fabsf(rz);
+        float m, u, v; uint32_t face;
+        if (ax >= ay && ax >= az) { m = ax; u = ry; v = rz; face = rx < 0.f ? 1u : 0u; }
+        else if (ay >= az)        { m = ay; u = rx; v = rz; face = ry < 0.f ? 3u : 2u; }
+        else                      { m = az; u = rx; v = ry; face = rz < 0.f ? 5u : 4u; }
+        const float im = 0.5f * (float)g.dn / fmaxf(m, 1e-30f);
+        const int iu = min(g.dn - 1, max(0, (int)(u * im + 0.5f * (float)g.dn)));
+        const int iv = min(g.dn - 1, max(0, (int)(v * im + 0.5f * (float)g.dn)));
+        dc = (face * (uint32_t)g.dn + (uint32_t)iu) * (uint32_t)g.dn + (uint32_t)iv;
+    }
+    const int ix = min(g.n[0] - 1, max(0, (int)((px - g.lo[0]) * g.inv[0])));
+    const int iy = min(g.n[1] - 1, max(0, (int)((py - g.lo[1]) * g.inv[1])));
+    const int iz = min(g.n[2] - 1, max(0, (int)((pz - g.lo[2]) * g.inv[2])));
+    return ((dc * (uint32_t)g.n[0] + (uint32_t)ix) * (uint32_t)g.n[1] + (uint32_t)iy) * (uint32_t)g.n[2] + (uint32_t)iz;
+}
+// bin + rank within the bin (one atomic per distinct bin among the calling lanes) -> keyb[i]; b == 0xffffffff: a miss, not counted
+__device__ __forceinline__ void sort_key_store(uint32_t b, uint32_t i, uint32_t* hist, uint2* keyb) {
+    const uint32_t act = __activemask(), lane = lane_id();
+    const uint32_t peers = __match_any_sync(act, b);
+    const uint32_t leader = (uint32_t)__ffs(peers) - 1u;
+    uint32_t base = 0;
+    if (b != 0xffffffffu && lane == leader) base = atomicAdd(&hist[b], (uint32_t)__popc(peers));
+    base = __shfl_sync(peers, base, leader);
+    keyb[i] = make_uint2(b, base + (uint32_t)__popc(peers & ((1u << lane) - 1u)));
+}
+
 constexpr int kCgMaxDim = 128;            // cells per axis, at most
 constexpr int kCgBigCells = 512;          // a sphere covering more cells than this goes on the "big" list
 constexpr int kCgMaxBig = 256;            // capacity of the big list; more big spheres than that: the grid is not used
@@ -174,12 +213,14 @@ struct CGridArgs {
     unsigned long long* tl;                  // diagnostic timeline slot; may be null
     unsigned long long* slow;                // diagnostics: [1] exact tests, [10] cell steps; may be null
     uint32_t* unused;
+    const GridDev* sgrid; uint32_t* hist; uint2* keyb; int use_dir;      // non-null keyb: also compute the hits' regrouping keys (k_key folded in)
 };
 
 // One thread per ray: Amanatides-Woo walk through the cells, sphere_exact on every listed sphere, planes last.
 // (Measured and dropped, profiles/r02_cgrid*.txt: a mailbox of the last two spheres offered, 0.70 -> 0.75 ms for 1/8 of C4; persistent
 // lanes with dynamic ray fetch — one cell step per loop iteration, idle lanes refill from the queue — 0.73 -> 0.87 ms.)
-__global__ void __launch_bounds__(256) k_closest_grid(SceneDev sc, CGridDev g, CGridArgs a) {
+template <bool KEY>      // KEY: also compute the regrouping keys of the hits (a separate kernel: the key code must not cost the plain walk registers)
+__device__ __forceinline__ void closest_grid_body(const SceneDev& sc, const CGridDev& g, const CGridArgs& a) {
     if (a.tl && threadIdx.x == 0) atomicMin(a.tl, globaltimer_ns());
     const CGridHdr h = *g.hdr;
     const uint32_t n = *a.n_in;
@@ -199,6 +240,7 @@ __global__ void __launch_bounds__(256) k_closest_grid(SceneDev sc, CGridDev g, C
                 if (t > 0.f && t < best) { best = t; id = sc.S + pl; }
             }
             a.hit[i] = ((unsigned long long)__float_as_uint(best) << 32) | (uint32_t)id;
+            if (KEY) sort_key_store(id >= 0 ? sort_bin(sc, *a.sgrid, O, D, best, id, a.use_dir) : 0xffffffffu, i, a.hist, a.keyb);
         }
         return;
     }
@@ -282,6 +324,7 @@ __global__ void __launch_bounds__(256) k_closest_grid(SceneDev sc, CGridDev g, C
             if (t > 0.f && t < best) { best = t; id = sc.S + pl; }
         }
         a.hit[i] = ((unsigned long long)__float_as_uint(best) << 32) | (uint32_t)id;                    // nothing hit: (999.0f, -1) = kNoHit
+        if (KEY) sort_key_store(id >= 0 ? sort_bin(sc, *a.sgrid, O, D, best, id, a.use_dir) : 0xffffffffu, i, a.hist, a.keyb);
     }
     if (a.slow) {
 #pragma unroll
@@ -290,5 +333,10 @@ __global__ void __launch_bounds__(256) k_closest_grid(SceneDev sc, CGridDev g, C
     }
     if (a.tl && threadIdx.x == 0) atomicMax(a.tl + 1, globaltimer_ns());
 }
+
+// Both at 64 registers = 4 CTAs per SM (the walk lives on occupancy: 76 registers measured 16 % slower).  The plain walk is left to ptxas'
+// own choice (64 registers, 16 B of spills), which measured 3 % faster than the explicit bound.
+__global__ void __launch_bounds__(256) k_closest_grid(SceneDev sc, CGridDev g, CGridArgs a) { closest_grid_body<false>(sc, g, a); }
+__global__ void __launch_bounds__(256, 4) k_closest_grid_key(SceneDev sc, CGridDev g, CGridArgs a) { closest_grid_body<true>(sc, g, a); }
 
 }  // namespace b200rt
