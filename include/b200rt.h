@@ -53,6 +53,7 @@ extern "C" {
 #define B200RT_F_NO_GRAPH        0x100u /* launch the frame's kernels one by one instead of replaying the captured CUDA graph of the sequence (A/B, debugging); the image is the same */
 #define B200RT_F_NO_CACHE        0x200u /* rebuild every scene-derived table in this call (the resident-scene tables are normally rebuilt only when the scene arrays change); implies NO_GRAPH; the image is the same */
 #define B200RT_F_NO_CGRID        0x400u /* closest-hit queries of bounce rays always by the beam-culled scan (k_isect3), never by the per-ray walk through the uniform grid of the spheres (closest_grid.cuh); the image is the same */
+#define B200RT_F_NO_FUSED        0x800u /* scenes with fewer than 64 spheres run through the wavefront kernels (k_isect3, k_setup, k_shadow_shade) instead of the one-kernel-per-depth path (fused_small.cuh); the image is the same */
 #define B200RT_F_NO_SORT         0x10u /* bounce-depth hits stay in pixel order (no regrouping by direction/position bin); the image is the same */
 
 /*

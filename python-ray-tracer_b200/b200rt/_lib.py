@@ -6,7 +6,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200rt.so")
 
 F_SCENE_ON_HOST, F_NO_FILTER, F_UNSWAP_GB, F_NO_CULL, F_NO_SORT, F_TIME_ONLY, F_DENSE, F_NO_SGRID = 0x1, 0x2, 0x4, 0x8, 0x10, 0x20, 0x40, 0x80
-F_NO_GRAPH, F_NO_CACHE, F_NO_CGRID = 0x100, 0x200, 0x400
+F_NO_GRAPH, F_NO_CACHE, F_NO_CGRID, F_NO_FUSED = 0x100, 0x200, 0x400, 0x800
 
 
 class Grid(C.Structure):

@@ -27,6 +27,7 @@
 #include "isect3.cuh"
 #include "shadow_grid.cuh"
 #include "closest_grid.cuh"
+#include "fused_small.cuh"
 
 namespace b200rt {
 
@@ -41,9 +42,9 @@ namespace b200rt {
 // k_cache_commit stamps the groups built in this call.  Only the camera pivot table (k_pivot, j == L) is per frame.
 //   cs[0] scene version   cs[1..3] version the groups {base tables, light grids, regrouping box} were built from
 //   cs[4] key of the regrouping box (position bits, direction cells)   cs[5..7] S, L, Pl of the saved copy   cs[8] CTA ticket
-//   cs[9] version the closest-hit grid (closest_grid.cuh) was built from
+//   cs[9] version the closest-hit grid (closest_grid.cuh) was built from   cs[10] version of the packed arrays (k_pack; the small-scene path builds nothing else)
 // ------------------------------------------------------------------------------------------------
-enum { kCsVersion = 0, kCsBase = 1, kCsSgrid = 2, kCsGrid = 3, kCsGridKey = 4, kCsS = 5, kCsL = 6, kCsPl = 7, kCsTicket = 8, kCsCgrid = 9, kCsWords = 16 };
+enum { kCsVersion = 0, kCsBase = 1, kCsSgrid = 2, kCsGrid = 3, kCsGridKey = 4, kCsS = 5, kCsL = 6, kCsPl = 7, kCsTicket = 8, kCsCgrid = 9, kCsPack = 10, kCsWords = 16 };
 
 __global__ void __launch_bounds__(256) k_scene_cmp(const float* __restrict__ spheres, int S, const float* __restrict__ lights, int L,
                                                   const float* __restrict__ planes, int Pl, uint32_t* saved, uint32_t* cs, float* cmax) {
@@ -69,12 +70,13 @@ __global__ void __launch_bounds__(256) k_scene_cmp(const float* __restrict__ sph
             const uint32_t all = atomicExch(&cs[kCsTicket], 0u);
             if (all & 0x80000000u) { cs[kCsVersion] += 1u; cs[kCsS] = (uint32_t)S; cs[kCsL] = (uint32_t)L; cs[kCsPl] = (uint32_t)Pl; }
             // k_pack's atomicMax bounds start from zero when (and only when) the base tables are about to be rebuilt
-            if (cs[kCsBase] != cs[kCsVersion]) { cmax[0] = 0.f; cmax[1] = 0.f; }
+            if (cs[kCsPack] != cs[kCsVersion]) { cmax[0] = 0.f; cmax[1] = 0.f; }
         }
     }
 }
 __global__ void k_cache_commit(uint32_t* cs, int base, int sgrid, int grid, uint32_t gridkey, int cgrid) {
     const uint32_t v = cs[kCsVersion];
+    cs[kCsPack] = v;                                             // k_pack runs in every call
     if (cgrid) cs[kCsCgrid] = v;
     if (base) cs[kCsBase] = v;
     if (sgrid) cs[kCsSgrid] = v;
@@ -88,7 +90,7 @@ __global__ void k_pack(const float* __restrict__ spheres, int S, int Spad,
                        const float* __restrict__ lights, int L,
                        float4* sphA, float4* sphB, float4* sphCol,
                        float4* plO, float4* plN, float4* plNu, float4* plCol, float4* lightsOut, float* cmax, const uint32_t* cs) {
-    if (cache_fresh(cs, kCsBase)) return;
+    if (cache_fresh(cs, kCsPack)) return;
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < Spad) {
         if (i < S) {
@@ -181,6 +183,29 @@ __device__ __forceinline__ double pl_at(const FrameDev& f, const CamDev& cm, int
 __constant__ int c_dx[9] = { 0, -1, +1, 0, 0, -1, +1, -1, +1 };
 __constant__ int c_dy[9] = { 0, 0, 0, +1, -1, +1, +1, -1, -1 };
 
+// Primary ray of sample slot `slot` = (sample k, pixel p): direction in FP64 (kernels.py:19-23 / :43-55) rounded once to FP32, slot bits in .w.
+// False for the slots the reference never samples (AA border: x == 0 or y == 0, kernels.py:29).
+__device__ __forceinline__ bool primary_dir(const FrameDev& f, const CamDev& cm, uint32_t slot, float4& d) {
+    const uint32_t k = slot / f.npix, p = slot - k * f.npix;
+    int lc, y; slot_pixel(f, p, lc, y);
+    const int x = col_x(f, f.x0 + lc);
+    if (k > 0 && !(x >= 1 && y >= 1)) return false;                       // kernels.py:29
+    double px = pl_at(f, cm, 0, x, y), py = pl_at(f, cm, 1, x, y), pz = pl_at(f, cm, 2, x, y);
+    if (k > 0) {                                                          // kernels.py:43-50  0.5*P + 0.5*P'
+        const int xn = x + c_dx[k], yn = y + c_dy[k];
+        px = __dadd_rn(__dmul_rn(0.5, px), __dmul_rn(0.5, pl_at(f, cm, 0, xn, yn)));
+        py = __dadd_rn(__dmul_rn(0.5, py), __dmul_rn(0.5, pl_at(f, cm, 1, xn, yn)));
+        pz = __dadd_rn(__dmul_rn(0.5, pz), __dmul_rn(0.5, pl_at(f, cm, 2, xn, yn)));
+    }
+    // matmul (common.py:40-49) then normalize (common.py:28-32), float64
+    const double bx = cm.rot[0] * px + cm.rot[1] * py + cm.rot[2] * pz;
+    const double by = cm.rot[3] * px + cm.rot[4] * py + cm.rot[5] * pz;
+    const double bz = cm.rot[6] * px + cm.rot[7] * py + cm.rot[8] * pz;
+    const double n = sqrt(bx * bx + by * by + bz * bz);
+    d = make_float4((float)(bx / n), (float)(by / n), (float)(bz / n), __uint_as_float(slot));     // origin = the camera (CamDev.cox..coz = (float)ox..oz): not stored
+    return true;
+}
+
 // One thread per (sample k, pixel p) slot.  Primary ray in FP64 (kernels.py:19-23 / :43-55), rounded to FP32,
 // appended to the ray queue.  Slots that the reference never samples (AA border: x == 0 or y == 0) are skipped.
 // Queue position: without anti-aliasing every slot has a ray, so position = slot (the queue is in slot order by
@@ -204,34 +229,28 @@ __global__ void k_raygen(FrameDev f, float4* __restrict__ rayD, unsigned long lo
         }
         if (c >= nchunks) break;
         uint32_t slot = c * 256u + threadIdx.x;
-        bool valid = slot < nslots;
         float4 d = make_float4(0, 0, 0, 0);
-        if (valid) {
-            uint32_t k = slot / f.npix, p = slot - k * f.npix;
-            int lc, y; slot_pixel(f, p, lc, y);
-            int x = col_x(f, f.x0 + lc);
-            if (k > 0 && !(x >= 1 && y >= 1)) valid = false;          // kernels.py:29
-            if (valid) {
-                double px = pl_at(f, cm, 0, x, y), py = pl_at(f, cm, 1, x, y), pz = pl_at(f, cm, 2, x, y);
-                if (k > 0) {                                          // kernels.py:43-50  0.5*P + 0.5*P'
-                    int xn = x + c_dx[k], yn = y + c_dy[k];
-                    px = __dadd_rn(__dmul_rn(0.5, px), __dmul_rn(0.5, pl_at(f, cm, 0, xn, yn)));
-                    py = __dadd_rn(__dmul_rn(0.5, py), __dmul_rn(0.5, pl_at(f, cm, 1, xn, yn)));
-                    pz = __dadd_rn(__dmul_rn(0.5, pz), __dmul_rn(0.5, pl_at(f, cm, 2, xn, yn)));
-                }
-                // matmul (common.py:40-49) then normalize (common.py:28-32), float64
-                double bx = cm.rot[0] * px + cm.rot[1] * py + cm.rot[2] * pz;
-                double by = cm.rot[3] * px + cm.rot[4] * py + cm.rot[5] * pz;
-                double bz = cm.rot[6] * px + cm.rot[7] * py + cm.rot[8] * pz;
-                double n = sqrt(bx * bx + by * by + bz * bz);
-                d = make_float4((float)(bx / n), (float)(by / n), (float)(bz / n), __uint_as_float(slot));     // origin = the camera (CamDev.cox..coz = (float)ox..oz): not stored
-            }
-        }
+        const bool valid = slot < nslots && primary_dir(f, cm, slot, d);
         uint32_t pos = slot;
         if (f.ns > 1) { uint32_t pp[8]; ordered_append8(valid ? 1u : 0u, 1, c, ostat, n_live, c == nchunks - 1, pp); pos = pp[0]; }
         else if (slot == 0) *n_live = nslots;
         if (valid) { rayD[pos] = d; if (hit) hit[pos] = kNoHitKey; }
     }
+}
+
+// Small scenes (S < 64): one kernel per depth does the whole `trace` of every live path (fused_small.cuh); depth 0 also generates the ray.
+__global__ void __launch_bounds__(256) k_fused_primary(SceneDev sc, FusedArgs a, FrameDev f) {
+    __shared__ CamDev s_cam;
+    if (threadIdx.x < sizeof(CamDev) / 8) reinterpret_cast<double*>(&s_cam)[threadIdx.x] = reinterpret_cast<const double*>(f.cam)[threadIdx.x];
+    __syncthreads();
+    if (a.tl && threadIdx.x == 0) atomicMin(a.tl, globaltimer_ns());
+    fused_depth_body<true>(sc, a, f.npix * (uint32_t)f.ns, [&](uint32_t slot, V3& D) { float4 d; const bool v = primary_dir(f, s_cam, slot, d); D = mk(d.x, d.y, d.z); return v; });
+    if (a.tl && threadIdx.x == 0) atomicMax(a.tl + 1, globaltimer_ns());
+}
+__global__ void __launch_bounds__(256) k_fused_bounce(SceneDev sc, FusedArgs a) {
+    if (a.tl && threadIdx.x == 0) atomicMin(a.tl, globaltimer_ns());
+    fused_depth_body<false>(sc, a, *a.n_in, [](uint32_t, V3&) { return false; });
+    if (a.tl && threadIdx.x == 0) atomicMax(a.tl + 1, globaltimer_ns());
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1004,6 +1023,7 @@ struct DevCtx {
     int cgrid_ctas = 8;                                              // env B200RT_CGRID_CTAS: CTAs per SM of k_closest_grid
     float cgrid_density = 2.f;                                       // env B200RT_CGRID_DENSITY: cells per sphere the grid aims at
     int cgrid_from = 1; size_t cgrid_max_paths = (size_t)1 << 40, cgrid_nosort_paths = (size_t)10 << 20;   // env B200RT_CGRID_FROM (first depth served by the grid; 99: never), B200RT_CGRID_MAX_PATHS
+    bool no_fused = false;                                           // env B200RT_NO_FUSED: small scenes through the wavefront kernels
     bool no_fold_key = false;                                        // env B200RT_NO_FOLD_KEY: separate k_key launch
     bool no_cgrid_all = false;                                       // env B200RT_NO_CGRID_ALL
     bool no_lanes = false, lane_conc = false;                        // env B200RT_NO_LANES, B200RT_LANE_CONC
@@ -1116,6 +1136,7 @@ int init_ctx(DevCtx& c, int device) {
     { const char* e = getenv("B200RT_CGRID_DENSITY"); if (e) c.cgrid_density = std::max(0.25f, (float)atof(e)); }
     { const char* e = getenv("B200RT_CGRID_CTAS"); if (e) c.cgrid_ctas = std::max(1, std::min(32, atoi(e))); }
     { const char* e = getenv("B200RT_CGRID_MAX_PATHS"); if (e) c.cgrid_max_paths = (size_t)std::max(0ll, atoll(e)); }
+    { const char* e = getenv("B200RT_NO_FUSED"); c.no_fused = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_NO_FOLD_KEY"); c.no_fold_key = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_NO_CGRID_ALL"); c.no_cgrid_all = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_CGRID_NOSORT_PATHS"); if (e) c.cgrid_nosort_paths = (size_t)std::max(0ll, atoll(e)); }
@@ -1147,6 +1168,99 @@ int init_ctx(DevCtx& c, int device) {
 }  // namespace
 
 namespace {
+
+// Small scenes (S < 64, default flags): the frame is k_fused_primary, k_fused_bounce x refl_depth, k_resolve (fused_small.cuh).
+// Only k_pack's arrays are needed — no pivot tables, grids or constant banks.
+int render_fused_small(DevCtx& c, const b200rt_args* a, cudaStream_t st, const SceneDev& sc, uint32_t* cst, int ncols) {
+    const bool stats = a->stats != nullptr;
+    const int L = a->L, depth = (int)a->refl_depth, ns = a->aliasing ? 9 : 1, W = a->W, H = a->H;
+    k_cache_commit<<<1, 1, 0, st>>>(cst, 0, 0, 0, 0u, 0); CKL();
+    const size_t per_col = (size_t)ns * H;
+    size_t cols_per_chunk = std::min<size_t>(std::max<size_t>(1, max_paths_per_chunk() / per_col), (size_t)ncols);
+    const bool tiled = (H % 16 == 0) && (ncols % 16 == 0) && (cols_per_chunk >= 16);
+    if (tiled) cols_per_chunk &= ~(size_t)15;
+    const int nchunks = (int)((ncols + cols_per_chunk - 1) / cols_per_chunk);
+    const size_t cap = cols_per_chunk * per_col;
+    Lane& ln = c.lane[0];
+    for (int b = 0; b < 2; ++b) { CK(ln.rayD[b].ensure(sizeof(float4) * cap)); CK(ln.hP[b].ensure(sizeof(float4) * cap)); }
+    CK(ln.acc.ensure(sizeof(float4) * cap));
+    const int cps = 5 + L, ctr_stride = cps * (depth + 2);
+    CK(c.ctr.ensure(sizeof(uint32_t) * (size_t)ctr_stride * nchunks));
+    CK(cudaMemsetAsync(c.ctr.p, 0, sizeof(uint32_t) * (size_t)ctr_stride * nchunks, st));
+    unsigned long long* tlb = nullptr; int tln = 0; std::vector<std::string> tlname;
+    if (c.timeline) {
+        CK(c.tl.ensure(sizeof(unsigned long long) * 2 * 1024)); tlb = c.tl.as<unsigned long long>();
+        std::vector<unsigned long long> init(2048); for (int i = 0; i < 1024; ++i) { init[2 * i] = ~0ull; init[2 * i + 1] = 0; }
+        CK(cudaMemcpyAsync(tlb, init.data(), sizeof(unsigned long long) * 2048, cudaMemcpyHostToDevice, st)); CK(cudaStreamSynchronize(st));
+    }
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, evA = nullptr, evB = nullptr;
+    if (stats) { CK(cudaEventCreate(&ev0)); CK(cudaEventCreate(&ev1)); CK(cudaEventCreate(&evA)); CK(cudaEventCreate(&evB)); CK(cudaEventRecord(ev0, st)); }
+    float fused_ms = 0.f;
+    const bool diag = stats && !(a->flags & B200RT_F_TIME_ONLY);
+    for (int ch = 0; ch < nchunks; ++ch) {
+        FrameDev f{};
+        f.pixel_loc = a->pixel_loc; f.cam = c.camDev.as<CamDev>();
+        f.W = W; f.H = H; f.ns = ns;
+        f.x0 = (int)(ch * cols_per_chunk); f.x1 = std::min(ncols, f.x0 + (int)cols_per_chunk);
+        f.xb = a->x_begin; f.sw = a->strip_width; f.srank = a->strip_rank; f.sworld = a->strip_world;
+        f.npix = (uint32_t)(f.x1 - f.x0) * (uint32_t)H; f.tiled = tiled ? 1 : 0;
+        const size_t nslots = (size_t)f.npix * ns;
+        uint32_t* ctr = c.ctr.as<uint32_t>() + (size_t)ch * ctr_stride;
+        float4* acc = ln.acc.as<float4>();
+        CK(cudaMemsetAsync(acc, 0, sizeof(float4) * nslots, st));
+        // grid: ~4 paths per thread, at least 2 CTAs per SM
+        const int grid = (int)std::min<size_t>((size_t)c.sm_count * 32, std::max<size_t>((size_t)c.sm_count * 2, (nslots + 1023) / 1024));
+        if (stats) CK(cudaEventRecord(evA, st));
+        for (int d = 0; d <= depth; ++d) {
+            uint32_t* cd = ctr + cps * d;
+            FusedArgs fa{};
+            fa.rayO = d == 0 ? nullptr : ln.hP[(d - 1) & 1].as<float4>(); fa.rayD = ln.rayD[d & 1].as<float4>(); fa.camo = &c.camDev.as<CamDev>()->cox;
+            fa.n_in = d == 0 ? nullptr : ctr + cps * (d - 1) + 3;
+            fa.hP2 = ln.hP[d & 1].as<float4>(); fa.rayD2 = ln.rayD[(d + 1) & 1].as<float4>();
+            fa.n_hit = cd + 3; fa.n_primary = ctr + 0; fa.acc = acc;
+            fa.amb = (float)a->amb; fa.lamb = (float)a->lamb; fa.weight = d == 0 ? 1.0f : (float)pow(a->refl, (double)d);     // trace.py:131 refl ** (i+1)
+            fa.emit_reflection = d < depth; fa.n_traced = diag ? cd + 4 : nullptr;
+            if (tlb) { fa.tl = tlb + 2 * (size_t)tln++; tlname.push_back("fused d" + std::to_string(d)); }
+            if (d == 0) k_fused_primary<<<grid, 256, 0, st>>>(sc, fa, f); else k_fused_bounce<<<grid, 256, 0, st>>>(sc, fa);
+            CKL();
+        }
+        if (stats) { CK(cudaEventRecord(evB, st)); }
+        const int unswap = (a->flags & B200RT_F_UNSWAP_GB) ? 1 : 0;
+        const int small_grid = c.sm_count * 8;
+        const bool al16 = (H % 16 == 0) && (((uintptr_t)a->result) % 16 == 0);
+        const bool al4 = (H % 4 == 0) && (((uintptr_t)a->result) % 4 == 0);
+        if (al16)      k_resolve<16><<<std::min<int>((f.npix / 16 + 255) / 256, small_grid), 256, 0, st>>>(f, acc, a->result, a->aliasing, unswap);
+        else if (al4)  k_resolve<4><<<std::min<int>((f.npix / 4 + 255) / 256, small_grid), 256, 0, st>>>(f, acc, a->result, a->aliasing, unswap);
+        else           k_resolve<1><<<std::min<int>((f.npix + 255) / 256, small_grid), 256, 0, st>>>(f, acc, a->result, a->aliasing, unswap);
+        CKL();
+        if (stats) { CK(cudaStreamSynchronize(st)); float ms = 0; CK(cudaEventElapsedTime(&ms, evA, evB)); fused_ms += ms; }
+    }
+    if (tlb) {
+        CK(cudaStreamSynchronize(st));
+        std::vector<unsigned long long> h(2 * (size_t)tln); CK(cudaMemcpy(h.data(), tlb, sizeof(unsigned long long) * h.size(), cudaMemcpyDeviceToHost));
+        unsigned long long t0 = ~0ull; for (int i = 0; i < tln; ++i) t0 = std::min(t0, h[2 * i]);
+        for (int i = 0; i < tln; ++i) fprintf(stderr, "[b200rt timeline] %-16s start %9.1f us  end %9.1f us  dur %8.1f us\n", tlname[i].c_str(), (h[2 * i] - t0) * 1e-3, (h[2 * i + 1] - t0) * 1e-3, (h[2 * i + 1] - h[2 * i]) * 1e-3);
+    }
+    if (stats) {
+        CK(cudaEventRecord(ev1, st));
+        CK(cudaStreamSynchronize(st));
+        std::vector<uint32_t> h((size_t)ctr_stride * nchunks);
+        CK(cudaMemcpy(h.data(), c.ctr.p, sizeof(uint32_t) * h.size(), cudaMemcpyDeviceToHost));
+        b200rt_stats out{};
+        for (int ch = 0; ch < nchunks; ++ch)
+            for (int d = 0; d <= depth; ++d) {
+                const uint32_t* cd = h.data() + (size_t)ch * ctr_stride + cps * d;
+                for (int j = 0; j < L; ++j) out.shadow_traced += cd[4 + j];
+                if (d == 0) out.primary += cd[0]; else out.bounce += (cd - cps)[3];
+                out.shadow += (uint64_t)cd[3] * (uint64_t)L;
+            }
+        CK(cudaEventElapsedTime(&out.kernel_ms[0], ev0, ev1));
+        out.kernel_ms[1] = fused_ms; out.kernel_ms[2] = 0.f; out.kernel_ms[3] = std::max(0.f, out.kernel_ms[0] - fused_ms);   // class "closest hit" = the fused trace kernels
+        cudaEventDestroy(ev0); cudaEventDestroy(ev1); cudaEventDestroy(evA); cudaEventDestroy(evB);
+        *a->stats = out;
+    }
+    return 0;
+}
 
 // The launch sequence.  `a` has DEVICE pointers for pixel_loc/result; scene pointers are host or device per flags.
 int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
@@ -1187,6 +1301,8 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     }
     SceneDev sc{ c.sphA.as<float4>(), c.sphB.as<float4>(), c.sphCol.as<float4>(), c.plO.as<float4>(), c.plN.as<float4>(),
                  c.plNu.as<float4>(), c.plCol.as<float4>(), c.lights.as<float4>(), c.cmax.as<float>(), S, Spad, Pl, L };
+    if (S < 64 && !c.no_fused && !(a->flags & (B200RT_F_NO_FILTER | B200RT_F_DENSE | B200RT_F_NO_CULL | B200RT_F_NO_SGRID | B200RT_F_NO_FUSED)))
+        return render_fused_small(c, a, st, sc, cst, ncols);
     {
         const int n = (L + 2) * (Spad / 2);
         if (L > 0) { k_rank<<<dim3((Spad + 255) / 256, L), 256, 0, st>>>(sc, c.pivPerm.as<int>(), cst); CKL(); }

@@ -485,3 +485,25 @@ def test_one_point_axes_render_like_the_oracle(oracle, res):
         ref = oracle.render(np.asarray(cam.generate_pixel_locations()), cam.position, cam.rotation, sp, li, pl, 0.1, 0.6, 0.3, 2, aa)
         assert got.shape == (3, *res)
         assert np.abs(got.astype(int) - ref.astype(int)).max() <= 1, (res, aa)
+
+
+@pytest.mark.parametrize("name", ["c1_aa0", "c1_aa1", "rand_a", "rand_b", "rand_c", "edge_s0", "edge_l0", "edge_p0", "edge_d0", "synthetic_13_17_2", "synthetic_63_3_1_aa"])
+def test_fused_small_scene_path_equals_wavefront(name):
+    """Scenes with fewer than 64 spheres run one fused kernel per depth (csrc/fused_small.cuh): same bytes and the same ray counts as the
+    wavefront kernels (B200RT_F_NO_FUSED), brute force and the unfiltered exact test."""
+    from b200rt import _lib
+    if name == "synthetic_13_17_2":
+        g = _synthetic(13, 17, 2, 192, 112, 3, False, seed=77)
+    elif name == "synthetic_63_3_1_aa":
+        g = _synthetic(63, 3, 1, 160, 96, 2, True, seed=78)
+    else:
+        g = load_golden(name)
+    got, st = _cuda(g, stats=True)
+    wave, st_w = _cuda(g, flags=_lib.F_NO_FUSED, stats=True)
+    assert np.array_equal(got, wave), "fused small-scene path differs from the wavefront kernels"
+    for k in ("primary", "shadow", "bounce", "rays", "shadow_traced"):
+        assert st[k] == st_w[k], (k, st[k], st_w[k])
+    assert np.array_equal(got, _cuda(g, flags=_lib.F_DENSE))
+    assert np.array_equal(got, _cuda(g, flags=_lib.F_NO_FILTER))
+    assert np.array_equal(got, _cuda(g))                                    # production launch (no stats), replayed graph on the repeat
+    assert np.array_equal(got, _cuda(g))
