@@ -85,13 +85,10 @@ __global__ void k_cache_commit(uint32_t* cs, int base, int sgrid, int grid, uint
 __device__ __forceinline__ bool cache_fresh(const uint32_t* cs, int group) { return cs[group] == cs[kCsVersion]; }
 
 // (7,S) / (9,Pl) / (3,L) float32 SoA  ->  packed float4 arrays.  One thread per object.
-__global__ void k_pack(const float* __restrict__ spheres, int S, int Spad,
-                       const float* __restrict__ planes, int Pl,
-                       const float* __restrict__ lights, int L,
-                       float4* sphA, float4* sphB, float4* sphCol,
-                       float4* plO, float4* plN, float4* plNu, float4* plCol, float4* lightsOut, float* cmax, const uint32_t* cs) {
-    if (cache_fresh(cs, kCsPack)) return;
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
+struct PackOut { float4 *sphA, *sphB, *sphCol, *plO, *plN, *plNu, *plCol, *lightsOut; float* cmax; };
+__device__ __forceinline__ void pack_item(int i, const float* __restrict__ spheres, int S, int Spad, const float* __restrict__ planes, int Pl,
+                                          const float* __restrict__ lights, int L, const PackOut& o) {
+    float4 *sphA = o.sphA, *sphB = o.sphB, *sphCol = o.sphCol, *plO = o.plO, *plN = o.plN, *plNu = o.plNu, *plCol = o.plCol, *lightsOut = o.lightsOut; float* cmax = o.cmax;
     if (i < Spad) {
         if (i < S) {
             float cx = spheres[0 * S + i], cy = spheres[1 * S + i], cz = spheres[2 * S + i], r = spheres[3 * S + i];
@@ -116,7 +113,40 @@ __global__ void k_pack(const float* __restrict__ spheres, int S, int Spad,
         plNu[i] = make_float4(__fdiv_rn(nx, nn), __fdiv_rn(ny, nn), __fdiv_rn(nz, nn), 0.f);
         plCol[i] = make_float4(planes[6 * Pl + i], planes[7 * Pl + i], planes[8 * Pl + i], 0.f);
     }
-    if (i < L) lightsOut[i] = make_float4(lights[0 * L + i], lights[1 * L + i], lights[2 * L + i], 0.f);
+    if (i < L) lightsOut[i] = make_float4(lights[0 * L + i], lights[1 * L + i], lights[2 * L + i], 0.f);}
+__global__ void k_pack(const float* __restrict__ spheres, int S, int Spad,
+                       const float* __restrict__ planes, int Pl,
+                       const float* __restrict__ lights, int L,
+                       float4* sphA, float4* sphB, float4* sphCol,
+                       float4* plO, float4* plN, float4* plNu, float4* plCol, float4* lightsOut, float* cmax, const uint32_t* cs) {
+    if (cache_fresh(cs, kCsPack)) return;
+    pack_item(blockIdx.x * blockDim.x + threadIdx.x, spheres, S, Spad, planes, Pl, lights, L, PackOut{ sphA, sphB, sphCol, plO, plN, plNu, plCol, lightsOut, cmax });
+}
+
+// Small scenes (the fused path needs nothing but the packed arrays): k_scene_cmp + k_pack + k_cache_commit as ONE single-CTA launch.
+__global__ void __launch_bounds__(256) k_small_prep(const float* __restrict__ spheres, int S, int Spad, const float* __restrict__ lights, int L,
+                                                   const float* __restrict__ planes, int Pl, uint32_t* saved, uint32_t* cs, PackOut o) {
+    __shared__ int s_diff;
+    const int nS = 7 * S, nL = 3 * L, n = nS + nL + 9 * Pl;
+    if (threadIdx.x == 0) s_diff = (cs[kCsS] != (uint32_t)S || cs[kCsL] != (uint32_t)L || cs[kCsPl] != (uint32_t)Pl) ? 1 : 0;
+    __syncthreads();
+    bool diff = false;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const float v = i < nS ? spheres[i] : (i < nS + nL ? lights[i - nS] : planes[i - nS - nL]);
+        const uint32_t b = __float_as_uint(v);
+        if (saved[i] != b) { saved[i] = b; diff = true; }
+    }
+    if (__syncthreads_or(diff ? 1 : 0) && threadIdx.x == 0) s_diff = 1;
+    __syncthreads();
+    if (threadIdx.x == 0 && s_diff) { cs[kCsVersion] += 1u; cs[kCsS] = (uint32_t)S; cs[kCsL] = (uint32_t)L; cs[kCsPl] = (uint32_t)Pl; }
+    __syncthreads();
+    if (cs[kCsPack] == cs[kCsVersion]) return;                                   // (uniform: every thread reads the same words after the barrier)
+    if (threadIdx.x == 0) { o.cmax[0] = 0.f; o.cmax[1] = 0.f; }
+    __syncthreads();
+    const int nobj = max(max(Spad, Pl), L);
+    for (int i = threadIdx.x; i < nobj; i += blockDim.x) pack_item(i, spheres, S, Spad, planes, Pl, lights, L, o);
+    __syncthreads();
+    if (threadIdx.x == 0) cs[kCsPack] = cs[kCsVersion];
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1171,10 +1201,9 @@ namespace {
 
 // Small scenes (S < 64, default flags): the frame is k_fused_primary, k_fused_bounce x refl_depth, k_resolve (fused_small.cuh).
 // Only k_pack's arrays are needed — no pivot tables, grids or constant banks.
-int render_fused_small(DevCtx& c, const b200rt_args* a, cudaStream_t st, const SceneDev& sc, uint32_t* cst, int ncols) {
+int render_fused_small(DevCtx& c, const b200rt_args* a, cudaStream_t st, const SceneDev& sc, int ncols) {
     const bool stats = a->stats != nullptr;
     const int L = a->L, depth = (int)a->refl_depth, ns = a->aliasing ? 9 : 1, W = a->W, H = a->H;
-    k_cache_commit<<<1, 1, 0, st>>>(cst, 0, 0, 0, 0u, 0); CKL();
     const size_t per_col = (size_t)ns * H;
     size_t cols_per_chunk = std::min<size_t>(std::max<size_t>(1, max_paths_per_chunk() / per_col), (size_t)ncols);
     const bool tiled = (H % 16 == 0) && (ncols % 16 == 0) && (cols_per_chunk >= 16);
@@ -1291,6 +1320,12 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     CK(c.pivClus.ensure(sizeof(float4) * (size_t)((Spad + 63) / 64)));
     uint32_t* cst = c.cacheState.as<uint32_t>();                 // (allocated and initialised by run_frame, with rawScene and camDev)
     {
+        const bool small = S < 64 && !c.no_fused && !(a->flags & (B200RT_F_NO_FILTER | B200RT_F_DENSE | B200RT_F_NO_CULL | B200RT_F_NO_SGRID | B200RT_F_NO_FUSED));
+        const PackOut po{ c.sphA.as<float4>(), c.sphB.as<float4>(), c.sphCol.as<float4>(), c.plO.as<float4>(), c.plN.as<float4>(), c.plNu.as<float4>(),
+                          c.plCol.as<float4>(), c.lights.as<float4>(), c.cmax.as<float>() };
+        if (small && nraw <= 16384) {                             // (the fused small-scene path; one launch instead of three)
+            k_small_prep<<<1, 256, 0, st>>>(d_sph, S, Spad, d_lig, L, d_pla, Pl, c.rawScene.as<uint32_t>(), cst, po); CKL();
+        } else {
         const int nb = (int)std::min<size_t>((nraw + 255) / 256 + 1, 64);
         k_scene_cmp<<<nb, 256, 0, st>>>(d_sph, S, d_lig, L, d_pla, Pl, c.rawScene.as<uint32_t>(), cst, c.cmax.as<float>()); CKL();
         const int nobj = std::max(std::max(Spad, Pl), L);
@@ -1298,11 +1333,13 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
                                                    c.sphCol.as<float4>(), c.plO.as<float4>(), c.plN.as<float4>(), c.plNu.as<float4>(),
                                                    c.plCol.as<float4>(), c.lights.as<float4>(), c.cmax.as<float>(), cst);
         CKL();
+        if (small) { k_cache_commit<<<1, 1, 0, st>>>(cst, 0, 0, 0, 0u, 0); CKL(); }
+        }
     }
     SceneDev sc{ c.sphA.as<float4>(), c.sphB.as<float4>(), c.sphCol.as<float4>(), c.plO.as<float4>(), c.plN.as<float4>(),
                  c.plNu.as<float4>(), c.plCol.as<float4>(), c.lights.as<float4>(), c.cmax.as<float>(), S, Spad, Pl, L };
     if (S < 64 && !c.no_fused && !(a->flags & (B200RT_F_NO_FILTER | B200RT_F_DENSE | B200RT_F_NO_CULL | B200RT_F_NO_SGRID | B200RT_F_NO_FUSED)))
-        return render_fused_small(c, a, st, sc, cst, ncols);
+        return render_fused_small(c, a, st, sc, ncols);
     {
         const int n = (L + 2) * (Spad / 2);
         if (L > 0) { k_rank<<<dim3((Spad + 255) / 256, L), 256, 0, st>>>(sc, c.pivPerm.as<int>(), cst); CKL(); }
