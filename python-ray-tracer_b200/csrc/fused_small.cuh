@@ -73,7 +73,12 @@ __device__ __forceinline__ void fused_depth_body(const SceneDev& sc, const Fused
                 for (int j = 0; j < sc.L; ++j) {
                     const float4 vv = __ldg(&sc.lights[j]);
                     const V3 dl = sub3(mk(vv.x, vv.y, vv.z), Pb);
-                    const float nrm = __fsqrt_rn(dot3(dl, dl));
+                    // Only lights with k = lamb * (Lv . N) > 0 matter (:101).  The sign of k is the sign of dl . N whenever that is clearly away from
+                    // zero (|cos| > 1e-4: the normalised dot differs from (dl.N)/|dl| by a few ulp of 1), so clearly unlit lights skip the
+                    // square root and the three divisions; grazing cases take the exact arithmetic below.
+                    const float dn_ = dot3(dl, N), dd_ = dot3(dl, dl);
+                    if (a.lamb > 1e-20f && dn_ * dn_ > 1e-8f * dd_ && dd_ < 1e30f && !(dn_ > 0.f)) continue;
+                    const float nrm = __fsqrt_rn(dd_);
                     const V3 Lv = mk(__fdiv_rn(dl.x, nrm), __fdiv_rn(dl.y, nrm), __fdiv_rn(dl.z, nrm));
                     const float k = __fmul_rn(a.lamb, dot3(Lv, N));
                     if (!(k > 0.f)) continue;                                                        // :101 (the query's answer would not be used)
@@ -85,7 +90,12 @@ __device__ __forceinline__ void fused_depth_body(const SceneDev& sc, const Fused
                         occluded = t > 0.f && t < kTMax;                                             // :92-96
                     }
                     for (int pl = 0; pl < sc.Pl && !occluded; ++pl) {
-                        const float t = plane_exact(Pb, Lv, __ldg(&sc.plO[pl]), __ldg(&sc.plN[pl]));
+                        const float4 po = __ldg(&sc.plO[pl]), pn = __ldg(&sc.plN[pl]);
+                        // t = num / den > 0 needs num and den of the same sign: otherwise plane_exact's division is skipped (a point on the plane looking up at a light)
+                        const float den = dot3(Lv, mk(pn.x, pn.y, pn.z));
+                        const float num = dot3(mk(__fsub_rn(po.x, Pb.x), __fsub_rn(po.y, Pb.y), __fsub_rn(po.z, Pb.z)), mk(pn.x, pn.y, pn.z));
+                        if ((num > 0.f) != (den > 0.f) || num == 0.f) continue;
+                        const float t = plane_exact(Pb, Lv, po, pn);
                         occluded = t > 0.f && t < kTMax;
                     }
                     if (occluded) continue;
