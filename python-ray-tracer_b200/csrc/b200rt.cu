@@ -793,6 +793,66 @@ __global__ void __launch_bounds__(256, B200RT_SETUP_OCC) k_setup_scatter(SceneDe
     if (s.tl && threadIdx.x == 0) atomicMax(s.tl + 1, globaltimer_ns());
 }
 
+// k_setup + k_shadow_shade in one kernel (light-grid path, single-stream frames): the thread that builds a hit's record shades it at once, from
+// registers.  The record's normal / object id (16 B written, 16 B read) never go through memory, and the biased hit point is written once (it is
+// the next depth's queue entry) but not read back: 48 bytes less per hit of the ~90 k_setup and k_shadow_shade move together.  Order of the hit
+// list and arithmetic as in the two kernels (same device functions), so the image is the same bytes.
+__global__ void __launch_bounds__(256, B200RT_SS_OCC) k_setup_shade(SceneDev sc, ShadeDev s, ShadowGridDev g, ShadowGridArgs a) {
+    if (a.tl && threadIdx.x == 0) atomicMin(a.tl, globaltimer_ns());
+    const uint32_t n = *s.n_live;
+    const uint32_t nchunks = (n + 255u) / 256u;
+    const float cmax = a.bounds[0], rmax = a.bounds[1];
+    __shared__ float s_A[64];
+    __shared__ uint32_t s_chunk;
+    if ((int)threadIdx.x < min(sc.L, 64)) { const float4 vv = __ldg(&sc.lights[threadIdx.x]); s_A[threadIdx.x] = cmax + __fsqrt_rn(dot3(mk(vv.x, vv.y, vv.z), mk(vv.x, vv.y, vv.z))); }
+    __syncthreads();
+    unsigned long long n_filter = 0, n_exact = 0;
+    for (;;) {
+        __syncthreads();
+        if (threadIdx.x == 0) s_chunk = atomicAdd(s.ticket, 1u);          // chunks in ticket order (ordered_append8 spins on predecessors)
+        __syncthreads();
+        const uint32_t c = s_chunk;
+        if (c >= nchunks) break;
+        const bool is_last = (c == nchunks - 1);
+        const uint32_t i = c * 256u + threadIdx.x;
+        bool hit = false; float4 d = make_float4(0, 0, 0, 0); V3 O = mk(0, 0, 0); uint32_t slot = 0; float t = 0.f; int id = -1;
+        if (i < n) {
+            const uint32_t src = s.perm ? s.perm[i] : i;
+            const unsigned long long key = s.hit[src]; d = s.rayD[src];
+            O = ray_origin(s.rayO, s.camo, src, mk(d.x, d.y, d.z), d.w, slot);
+            id = (int)(uint32_t)key; t = __uint_as_float((uint32_t)(key >> 32)); hit = id >= 0;
+        }
+        V3 Pb = mk(0, 0, 0), N = mk(0, 0, 0);
+        if (hit) {
+            const V3 P = madd3(O, t, mk(d.x, d.y, d.z));                            // trace.py:60
+            if (id < sc.S) { const float4 cc = __ldg(&sc.sphB[id]); N = normalize3(sub3(P, mk(cc.x, cc.y, cc.z))); }   // common.py:94-101
+            else           { const float4 nu = __ldg(&sc.plNu[id - sc.S]); N = mk(nu.x, nu.y, nu.z); }                 // common.py:104-110
+            Pb = madd3(P, kBias, N);                                                 // trace.py:82-83
+        }
+        uint32_t h = 0;
+        if (s.perm) { h = i; if (is_last && threadIdx.x == 0) *s.n_hit = n; }        // regrouped: the permutation lists hits only, in their final order
+        else { uint32_t pos[8]; ordered_append8(hit ? 1u : 0u, 1, c, s.ostat, s.n_hit, is_last, pos); h = pos[0]; }
+        if (hit) {
+            RT_CHECK(2, h < s.shcap && h < n);
+            if (s.emit_reflection) {
+                s.hP[h] = make_float4(Pb.x, Pb.y, Pb.z, __uint_as_float(slot));      // = the next depth's queue entry (origin Pb + BIAS * R by the readers)
+                const V3 D = mk(d.x, d.y, d.z);
+                const float dn = dot3(D, N);
+                const V3 R = normalize3(madd3(D, -2.0f * dn, N));                    // common.py:113-120
+                s.rayD2[h] = make_float4(R.x, R.y, R.z, 0.f);
+                if (s.hit2) s.hit2[h] = kNoHit;
+            }
+            shadow_shade_hit(sc, g, a, s_A, cmax, rmax, Pb, N, id, slot, n_filter, n_exact);      // trace.py:77, 86-102, 131
+        }
+    }
+    if (a.slow) {
+#pragma unroll
+        for (int dd = 16; dd > 0; dd >>= 1) { n_filter += __shfl_xor_sync(0xffffffffu, n_filter, dd); n_exact += __shfl_xor_sync(0xffffffffu, n_exact, dd); }
+        if (lane_id() == 0) { if (n_filter) atomicAdd(a.slow + 2, n_filter); if (n_exact) atomicAdd(a.slow + 1, n_exact); }
+    }
+    if (a.tl && threadIdx.x == 0) atomicMax(a.tl + 1, globaltimer_ns());
+}
+
 // trace.py:77,86-102 and the accumulate of trace.py:131: RGB_trace = amb*col + sum_j [visible_j && k_j>0] k_j*col,
 // acc[slot] += weight * RGB_trace.  (The reflection ray of trace.py:104-110 was queued by k_setup.)
 __global__ void __launch_bounds__(256, B200RT_SHADE_OCC) k_shade(SceneDev sc, ShadeDev s) {
@@ -1053,6 +1113,7 @@ struct DevCtx {
     int cgrid_ctas = 8;                                              // env B200RT_CGRID_CTAS: CTAs per SM of k_closest_grid
     float cgrid_density = 2.f;                                       // env B200RT_CGRID_DENSITY: cells per sphere the grid aims at
     int cgrid_from = 1; size_t cgrid_max_paths = (size_t)1 << 40, cgrid_nosort_paths = (size_t)10 << 20;   // env B200RT_CGRID_FROM (first depth served by the grid; 99: never), B200RT_CGRID_MAX_PATHS
+    int fuse_ss = 1;                                                 // env B200RT_FUSE_SS: 0 never, 1 single-stream frames (default), 2 always
     bool no_fused = false;                                           // env B200RT_NO_FUSED: small scenes through the wavefront kernels
     bool no_fold_key = false;                                        // env B200RT_NO_FOLD_KEY: separate k_key launch
     bool no_cgrid_all = false;                                       // env B200RT_NO_CGRID_ALL
@@ -1166,6 +1227,7 @@ int init_ctx(DevCtx& c, int device) {
     { const char* e = getenv("B200RT_CGRID_DENSITY"); if (e) c.cgrid_density = std::max(0.25f, (float)atof(e)); }
     { const char* e = getenv("B200RT_CGRID_CTAS"); if (e) c.cgrid_ctas = std::max(1, std::min(32, atoi(e))); }
     { const char* e = getenv("B200RT_CGRID_MAX_PATHS"); if (e) c.cgrid_max_paths = (size_t)std::max(0ll, atoll(e)); }
+    { const char* e = getenv("B200RT_FUSE_SS"); if (e) c.fuse_ss = std::max(0, std::min(2, atoi(e))); }
     { const char* e = getenv("B200RT_NO_FUSED"); c.no_fused = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_NO_FOLD_KEY"); c.no_fold_key = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_NO_CGRID_ALL"); c.no_cgrid_all = e && atoi(e) != 0; }
@@ -1590,6 +1652,20 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             if (conc && d >= nsets) CK(cudaStreamWaitEvent(cs, ln.evShade[hs], 0));        // set hs is free again
             if (tlb) { s.tl = tlb + 2 * (size_t)tln++; tlname.push_back("setup d" + std::to_string(d)); }
             s.ostat = ln.ostat.as<unsigned long long>(); s.ostat_stride = ostat_stride; s.ticket = reinterpret_cast<uint32_t*>(s.ostat + ostat_stride * ostat_passes);
+            // light-grid path in one stream: k_setup and k_shadow_shade as one kernel (k_setup_shade); with the multi-stream schedule they stay
+            // apart, the shading of depth d running beside the closest-hit query of depth d+1
+            const bool fuse_ss = sgrid && L > 0 && !scatter && (c.fuse_ss == 2 || (c.fuse_ss == 1 && !conc));
+            if (fuse_ss) {
+                tm.end(2);
+                tm.begin(1);
+                ShadowGridArgs ga{ nullptr, nullptr, s.n_hit, acc, s.amb, s.lamb, s.weight, pv.bounds, q.slow ? cd + 4 : nullptr, q.slow, s.tl };
+                CK(cudaMemsetAsync(ln.ostat.p, 0, ostat_bytes, cs));
+                const int ssg = c.ss_grid > 0 ? c.sm_count * c.ss_grid : c.sm_count * B200RT_SS_OCC * 2;
+                k_setup_shade<<<ssg, 256, 0, cs>>>(sc, s, sg, ga); CKL();
+                if (conc) { CK(cudaEventRecord(ln.evSetup[hs], cs)); CK(cudaEventRecord(ln.evShade[hs], cs)); CK(cudaStreamWaitEvent(ss, ln.evShade[hs], 0)); }
+                tm.end(1);
+                continue;
+            }
             if (scatter) { k_setup_scatter<<<small_grid, 256, 0, cs>>>(sc, s, ln.sortKey.as<uint2>(), ln.sortBase.as<uint32_t>(), cd + 2); CKL(); }
             else {
                 CK(cudaMemsetAsync(ln.ostat.p, 0, ostat_bytes, cs));

@@ -146,6 +146,89 @@ struct ShadowGridArgs {
     unsigned long long* tl;              // diagnostic timeline slot; may be null
 };
 
+// The lights loop of trace() for ONE hit record (biased hit point O, normal N, object id, accumulator slot): see k_shadow_shade below.  Also called by
+// k_setup_shade (b200rt.cu), which shades a hit in the thread that has just built its record.
+__device__ __forceinline__ void shadow_shade_hit(const SceneDev& sc, const ShadowGridDev& g, const ShadowGridArgs& a, const float* s_A, float cmax, float rmax,
+                                                 V3 O, V3 N, int id, uint32_t slot, unsigned long long& n_filter, unsigned long long& n_exact) {
+    const float4 a0 = a.acc[slot]; const float ar = a0.x, ag = a0.y, ab = a0.z;
+    const float4 col = (id < sc.S) ? __ldg(&sc.sphCol[id]) : __ldg(&sc.plCol[id - sc.S]);
+    float r = __fmul_rn(a.amb, col.x), gg = __fmul_rn(a.amb, col.y), b = __fmul_rn(a.amb, col.z);   // trace.py:77
+    const float B = cmax + __fsqrt_rn(dot3(O, O));
+    for (int j = 0; j < sc.L; ++j) {                                                               // trace.py:86
+        const float4 vv = __ldg(&sc.lights[j]);
+        const V3 Vp = mk(vv.x, vv.y, vv.z);
+        // the ray and its filter threshold: the operations of k_isect3<shadow>'s prologue; D is also k_shade's Lv (common.py:84-91)
+        const V3 d = sub3(Vp, O);
+        const float nrmc = __fsqrt_rn(dot3(d, d));
+        const V3 Dc = mk(__fdiv_rn(d.x, nrmc), __fdiv_rn(d.y, nrmc), __fdiv_rn(d.z, nrmc));
+        const float kc = __fmul_rn(a.lamb, dot3(Dc, N));                                           // :99
+        if (!(kc > 0.f)) continue;                                                                 // :101 (the query's answer would not be used)
+        // the first 16 bytes of the cell's record: count + 7 ids (one load where count and ids used to be two dependent ones)
+        const uint16_t* recc = g.cells + ((((size_t)(nrmc <= sg_range(0) ? 0 : 1) * sc.L + j) * kSgCells) + (size_t)sg_cell(Dc.x, Dc.y, Dc.z)) * kSgRec;
+        RT_CHECK(7, sg_cell(Dc.x, Dc.y, Dc.z) >= 0 && sg_cell(Dc.x, Dc.y, Dc.z) < kSgCells);
+        const uint4 hc = __ldg(reinterpret_cast<const uint4*>(recc));
+        if (a.n_traced) warp_count(a.n_traced + j);
+        const float A = j < 64 ? s_A[j] : cmax + __fsqrt_rn(dot3(Vp, Vp));
+        const float e = nrmc * 9.5367432e-7f;
+        const float th = -(fmaf(3.8146973e-6f, fmaf(A, A, B * B), fmaf(4.f * e, rmax, 16.f * e * e)) + 1e-12f);
+        const float no = -dot3(Vp, Dc);
+        const float4* ltab = g.ltab + (size_t)j * sc.S;
+        const uint32_t cnt = hc.x & 0xffffu;
+        const bool full = cnt == 0xffffu || !(nrmc <= sg_range(kSgTiers - 1));     // overflowed cell, origin beyond the last tier or NaN: every sphere
+        bool occluded = false;
+        // four candidates: their filter operands are requested together, then tested in order (a query stops at its first hit)
+        auto test4 = [&](const uint32_t (&cid)[4], uint32_t nvalid) {
+            float4 t4[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) t4[q] = __ldg(&ltab[cid[q]]);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                if ((uint32_t)q >= nvalid || occluded) continue;
+                const float bb = fmaf(t4[q].x, Dc.x, fmaf(t4[q].y, Dc.y, fmaf(t4[q].z, Dc.z, no)));   // k_isect3 qray(), pivot form
+                const float qq = fmaf(bb, bb, t4[q].w);
+                if (a.slow) ++n_filter;
+                if (qq >= th) {
+                    const float4 sp = __ldg(&sc.sphB[cid[q]]);
+                    const float t = sphere_exact(O, Dc, sp.x, sp.y, sp.z, sp.w);
+                    occluded = t > 0.f && t < kTMax;                                               // trace.py:26-29, :95
+                    if (a.slow) ++n_exact;
+                }
+            }
+        };
+        if (full) {
+            for (uint32_t c = 0; c < (uint32_t)sc.S && !occluded; c += 4) {
+                const uint32_t cid[4] = { c, min(c + 1, (uint32_t)sc.S - 1u), min(c + 2, (uint32_t)sc.S - 1u), min(c + 3, (uint32_t)sc.S - 1u) };
+                test4(cid, (uint32_t)sc.S - c);
+            }
+        } else if (cnt) {
+            {   // candidates 0..6 came with the header
+                const uint32_t c0[4] = { hc.x >> 16, hc.y & 0xffffu, hc.y >> 16, hc.z & 0xffffu };
+                test4(c0, cnt);
+                if (cnt > 4u && !occluded) { const uint32_t c1[4] = { hc.z >> 16, hc.w & 0xffffu, hc.w >> 16, hc.w >> 16 }; test4(c1, min(cnt - 4u, 3u)); }
+            }
+            for (uint32_t c = 7; c < cnt && !occluded; c += 8) {                                   // candidates c .. c+7 = rec[c+1 .. c+8]
+                const uint4 w = __ldg(reinterpret_cast<const uint4*>(recc + 1 + c));
+                const uint32_t c0[4] = { w.x & 0xffffu, w.x >> 16, w.y & 0xffffu, w.y >> 16 };
+                test4(c0, cnt - c);
+                if (cnt > c + 4u && !occluded) { const uint32_t c1[4] = { w.z & 0xffffu, w.z >> 16, w.w & 0xffffu, w.w >> 16 }; test4(c1, cnt - c - 4u); }
+            }
+        }
+        for (int pl = 0; pl < sc.Pl && !occluded; ++pl) {                                          // trace.py:32-39
+            const float4 po = __ldg(&sc.plO[pl]), pn = __ldg(&sc.plN[pl]);
+            // t = num / den > 0 needs num and den of the same sign: where they differ (or num is 0) the quotient is <= 0
+            // and plane_exact's division is skipped — the usual case for a point on the plane looking up at a light
+            const float den = dot3(Dc, mk(pn.x, pn.y, pn.z));
+            const float num = dot3(mk(__fsub_rn(po.x, O.x), __fsub_rn(po.y, O.y), __fsub_rn(po.z, O.z)), mk(pn.x, pn.y, pn.z));
+            if ((num > 0.f) != (den > 0.f) || num == 0.f) continue;
+            const float t = plane_exact(O, Dc, po, pn);
+            occluded = (t > 0.f && t < kTMax);
+        }
+        if (occluded) continue;                                                                    // :95-96
+        r = fmaf(kc, col.x, r); gg = fmaf(kc, col.y, gg); b = fmaf(kc, col.z, b);                  // :102
+    }
+    a.acc[slot] = make_float4(fmaf(a.weight, r, ar), fmaf(a.weight, gg, ag), fmaf(a.weight, b, ab), 0.f);     // :131
+}
+
 // The lights loop of trace() for one hit record per thread (trace.py:77, 86-102, accumulated as in :131):
 //   RGB = amb * col;  for each light j:  Lv = normalize(light_j - P);  shadowed = query(P, Lv);  k = lamb * (Lv . N);
 //   if not shadowed and k > 0:  RGB += k * col;        acc[slot] += weight * RGB
@@ -162,86 +245,7 @@ __global__ void __launch_bounds__(256, B200RT_SS_OCC) k_shadow_shade(SceneDev sc
     unsigned long long n_filter = 0, n_exact = 0;
     for (uint32_t h = blockIdx.x * blockDim.x + threadIdx.x; h < n; h += gridDim.x * blockDim.x) {
         const float4 p = a.hP[h], nn = a.hN[h];
-        const uint32_t slot = __float_as_uint(p.w);
-        const float4 a0 = a.acc[slot]; const float ar = a0.x, ag = a0.y, ab = a0.z;
-        const V3 O = mk(p.x, p.y, p.z), N = mk(nn.x, nn.y, nn.z);
-        const int id = __float_as_int(nn.w);
-        const float4 col = (id < sc.S) ? __ldg(&sc.sphCol[id]) : __ldg(&sc.plCol[id - sc.S]);
-        float r = __fmul_rn(a.amb, col.x), gg = __fmul_rn(a.amb, col.y), b = __fmul_rn(a.amb, col.z);   // trace.py:77
-        const float B = cmax + __fsqrt_rn(dot3(O, O));
-        for (int j = 0; j < sc.L; ++j) {                                                               // trace.py:86
-            const float4 vv = __ldg(&sc.lights[j]);
-            const V3 Vp = mk(vv.x, vv.y, vv.z);
-            // the ray and its filter threshold: the operations of k_isect3<shadow>'s prologue; D is also k_shade's Lv (common.py:84-91)
-            const V3 d = sub3(Vp, O);
-            const float nrmc = __fsqrt_rn(dot3(d, d));
-            const V3 Dc = mk(__fdiv_rn(d.x, nrmc), __fdiv_rn(d.y, nrmc), __fdiv_rn(d.z, nrmc));
-            const float kc = __fmul_rn(a.lamb, dot3(Dc, N));                                           // :99
-            if (!(kc > 0.f)) continue;                                                                 // :101 (the query's answer would not be used)
-            // the first 16 bytes of the cell's record: count + 7 ids (one load where count and ids used to be two dependent ones)
-            const uint16_t* recc = g.cells + ((((size_t)(nrmc <= sg_range(0) ? 0 : 1) * sc.L + j) * kSgCells) + (size_t)sg_cell(Dc.x, Dc.y, Dc.z)) * kSgRec;
-            RT_CHECK(7, sg_cell(Dc.x, Dc.y, Dc.z) >= 0 && sg_cell(Dc.x, Dc.y, Dc.z) < kSgCells);
-            const uint4 hc = __ldg(reinterpret_cast<const uint4*>(recc));
-            if (a.n_traced) warp_count(a.n_traced + j);
-            const float A = j < 64 ? s_A[j] : cmax + __fsqrt_rn(dot3(Vp, Vp));
-            const float e = nrmc * 9.5367432e-7f;
-            const float th = -(fmaf(3.8146973e-6f, fmaf(A, A, B * B), fmaf(4.f * e, rmax, 16.f * e * e)) + 1e-12f);
-            const float no = -dot3(Vp, Dc);
-            const float4* ltab = g.ltab + (size_t)j * sc.S;
-            const uint32_t cnt = hc.x & 0xffffu;
-            const bool full = cnt == 0xffffu || !(nrmc <= sg_range(kSgTiers - 1));     // overflowed cell, origin beyond the last tier or NaN: every sphere
-            bool occluded = false;
-            // four candidates: their filter operands are requested together, then tested in order (a query stops at its first hit)
-            auto test4 = [&](const uint32_t (&cid)[4], uint32_t nvalid) {
-                float4 t4[4];
-#pragma unroll
-                for (int q = 0; q < 4; ++q) t4[q] = __ldg(&ltab[cid[q]]);
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    if ((uint32_t)q >= nvalid || occluded) continue;
-                    const float bb = fmaf(t4[q].x, Dc.x, fmaf(t4[q].y, Dc.y, fmaf(t4[q].z, Dc.z, no)));   // k_isect3 qray(), pivot form
-                    const float qq = fmaf(bb, bb, t4[q].w);
-                    if (a.slow) ++n_filter;
-                    if (qq >= th) {
-                        const float4 sp = __ldg(&sc.sphB[cid[q]]);
-                        const float t = sphere_exact(O, Dc, sp.x, sp.y, sp.z, sp.w);
-                        occluded = t > 0.f && t < kTMax;                                               // trace.py:26-29, :95
-                        if (a.slow) ++n_exact;
-                    }
-                }
-            };
-            if (full) {
-                for (uint32_t c = 0; c < (uint32_t)sc.S && !occluded; c += 4) {
-                    const uint32_t cid[4] = { c, min(c + 1, (uint32_t)sc.S - 1u), min(c + 2, (uint32_t)sc.S - 1u), min(c + 3, (uint32_t)sc.S - 1u) };
-                    test4(cid, (uint32_t)sc.S - c);
-                }
-            } else if (cnt) {
-                {   // candidates 0..6 came with the header
-                    const uint32_t c0[4] = { hc.x >> 16, hc.y & 0xffffu, hc.y >> 16, hc.z & 0xffffu };
-                    test4(c0, cnt);
-                    if (cnt > 4u && !occluded) { const uint32_t c1[4] = { hc.z >> 16, hc.w & 0xffffu, hc.w >> 16, hc.w >> 16 }; test4(c1, min(cnt - 4u, 3u)); }
-                }
-                for (uint32_t c = 7; c < cnt && !occluded; c += 8) {                                   // candidates c .. c+7 = rec[c+1 .. c+8]
-                    const uint4 w = __ldg(reinterpret_cast<const uint4*>(recc + 1 + c));
-                    const uint32_t c0[4] = { w.x & 0xffffu, w.x >> 16, w.y & 0xffffu, w.y >> 16 };
-                    test4(c0, cnt - c);
-                    if (cnt > c + 4u && !occluded) { const uint32_t c1[4] = { w.z & 0xffffu, w.z >> 16, w.w & 0xffffu, w.w >> 16 }; test4(c1, cnt - c - 4u); }
-                }
-            }
-            for (int pl = 0; pl < sc.Pl && !occluded; ++pl) {                                          // trace.py:32-39
-                const float4 po = __ldg(&sc.plO[pl]), pn = __ldg(&sc.plN[pl]);
-                // t = num / den > 0 needs num and den of the same sign: where they differ (or num is 0) the quotient is <= 0
-                // and plane_exact's division is skipped — the usual case for a point on the plane looking up at a light
-                const float den = dot3(Dc, mk(pn.x, pn.y, pn.z));
-                const float num = dot3(mk(__fsub_rn(po.x, O.x), __fsub_rn(po.y, O.y), __fsub_rn(po.z, O.z)), mk(pn.x, pn.y, pn.z));
-                if ((num > 0.f) != (den > 0.f) || num == 0.f) continue;
-                const float t = plane_exact(O, Dc, po, pn);
-                occluded = (t > 0.f && t < kTMax);
-            }
-            if (occluded) continue;                                                                    // :95-96
-            r = fmaf(kc, col.x, r); gg = fmaf(kc, col.y, gg); b = fmaf(kc, col.z, b);                  // :102
-        }
-        a.acc[slot] = make_float4(fmaf(a.weight, r, ar), fmaf(a.weight, gg, ag), fmaf(a.weight, b, ab), 0.f);     // :131
+        shadow_shade_hit(sc, g, a, s_A, cmax, rmax, mk(p.x, p.y, p.z), mk(nn.x, nn.y, nn.z), __float_as_int(nn.w), __float_as_uint(p.w), n_filter, n_exact);
     }
     if (a.slow) {
 #pragma unroll
