@@ -22,6 +22,6 @@ case $MODE in
   culled)
     BENCH="python tools/one_frame.py culled"
     B200RT_NO_GRAPH=1 $BENCH > gpurun_out/${T}_plain.log 2>&1 &&
-    B200RT_NO_GRAPH=1 ncu --set full --clock-control none --import-source on -k regex:"k_shadow_shade|k_closest_grid|k_setup|k_isect3|k_key|k_raygen" -s 11 -c 12 -o gpurun_out/${T}_culled $BENCH > gpurun_out/${T}_ncu.log 2>&1 ;;
+    B200RT_NO_GRAPH=1 ncu --set full --clock-control none --import-source on -k regex:"k_shadow_shade|k_closest_grid|k_setup|k_isect3|k_key|k_raygen" -s 9 -c 10 -o gpurun_out/${T}_culled $BENCH > gpurun_out/${T}_ncu.log 2>&1 ;;
 esac
 echo "rc=$?"; tail -3 gpurun_out/${T}_ncu.log | cut -c1-200

@@ -32,7 +32,7 @@ def short(k):
 def klass(k):
     if k.startswith("k_isect3") or k.startswith("k_closest_grid") or k.startswith("k_intersect"):
         return "closest_hit"
-    if k.startswith("k_shadow_shade"):
+    if k.startswith("k_shadow_shade") or k.startswith("k_setup_shade"):      # (bench.py's live class "shadow_shade" times k_setup_shade as a whole)
         return "shadow_shade"
     return "other"
 
