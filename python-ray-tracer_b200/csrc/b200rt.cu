@@ -1112,7 +1112,7 @@ struct DevCtx {
     Buf cgHdr, cgStart, cgCursor, cgIds, cgBig, cgRec;                      // uniform grid of the spheres for per-ray closest-hit queries (closest_grid.cuh)
     int cgrid_ctas = 8;                                              // env B200RT_CGRID_CTAS: CTAs per SM of k_closest_grid
     float cgrid_density = 2.f;                                       // env B200RT_CGRID_DENSITY: cells per sphere the grid aims at
-    int cgrid_from = 1; size_t cgrid_max_paths = (size_t)1 << 40, cgrid_nosort_paths = (size_t)10 << 20;   // env B200RT_CGRID_FROM (first depth served by the grid; 99: never), B200RT_CGRID_MAX_PATHS
+    int cgrid_from = 1; size_t cgrid_max_paths = (size_t)1 << 40, cgrid_nosort_paths = 0;   // env B200RT_CGRID_FROM (first depth served by the grid; 99: never), B200RT_CGRID_MAX_PATHS
     int fuse_ss = 1;                                                 // env B200RT_FUSE_SS: 0 never, 1 single-stream frames (default), 2 always
     bool no_fused = false;                                           // env B200RT_NO_FUSED: small scenes through the wavefront kernels
     bool no_fold_key = false;                                        // env B200RT_NO_FOLD_KEY: separate k_key launch
@@ -1489,8 +1489,8 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
         CK(ln.acc.ensure(sizeof(float4) * cap));
     }
     // regrouping of the hits of depth >= 1 (see k_key): worth it where beam culling is on and a query is expensive
-    // (not where the grid walk serves every bounce depth of a small frame: it needs no coherent groups, and the order it leaves to
-    // k_shadow_shade costs less than the sort — 1/8 of C4: 1.578 -> 1.526 ms, 1/4: 2.90 -> 2.83)
+    // (B200RT_CGRID_NOSORT_PATHS: frames up to that many paths skip it where the grid walk serves every bounce depth.  It paid while the keys
+    // were a separate pass — 1/8 of C4: 1.578 -> 1.526 ms — but not since the walk computes them in its epilogue: 1.468 -> 1.446 with the sort; default 0)
     const bool regroup = cull && use_lists && S >= 64 && depth >= 1 && !(a->flags & B200RT_F_NO_SORT) && !c.no_sort &&
                          !(cgrid && cgrid_from <= 1 && frame_paths <= c.cgrid_nosort_paths);
     // Bin grid of the regrouping: ~40-170 rays per bin measured best at every frame share (C4: 13 position bits and 3x3
