@@ -11,8 +11,9 @@ synchronize on both sides, max over ranks.  One JSON line on rank 0.
     value     whole-job Mrays/s with scene and camera resident in HBM (ray = one get_intersection query)
     e2e       the same metric through the host-buffer C-ABI call (b200rt_render_host): H2D of the scene arrays
               and D2H of the uint8 framebuffer inside the timed region
-    roofline  FP32 CUDA-core roofline of the dominant kernel (k_intersect): algorithmic FLOPs = rays x (16 S + 14 Pl)
-    cpu_baseline  the float64 oracle port (OpenMP, all host threads) on a bounded sample of the same frame
+    roofline  two labelled objects: `brute_force` (B200RT_F_DENSE: every query scans every sphere; roofline.frac = its executed FP32 FLOPs / kernel time /
+              FP32 peak) and `exact_culled` (the shipped default: per-class times, executed fraction, DRAM bytes, Mrays/s as specified and as traced)
+    cpu_baseline  the float64 oracle port (OpenMP, all host threads) on a fixed, representative sample of the same frame (every n-th 16-column strip)
 
 `--impl reference` times that CPU port alone (the reference itself is a numba-CUDA Python kernel whose only
 CPU-executable form is the ~160 px/s simulator; it cannot travel to the GPU box — DESIGN.md).
