@@ -1,6 +1,7 @@
 """Fuzz the exact-culling paths: random scenes (lights among the spheres, inside them, far away; clustered and huge spheres),
-default path vs brute force (B200RT_F_DENSE), the scan path (B200RT_F_NO_SGRID) and - for S <= 700 - the exact test on every
-sphere without any filter (B200RT_F_NO_FILTER) must be byte-identical.  usage: python tools/gpu_fuzz.py [n_scenes]"""
+default path vs brute force (B200RT_F_DENSE), the scan path (B200RT_F_NO_SGRID), the path without the closest-hit grid / the fused
+small-scene kernels (B200RT_F_NO_CGRID | B200RT_F_NO_FUSED), a repeated (cached, graph-replayed) call and - for S <= 700 - the exact
+test on every sphere without any filter (B200RT_F_NO_FILTER) must be byte-identical.  usage: python tools/gpu_fuzz.py [n_scenes]"""
 import os, sys
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -11,7 +12,7 @@ from b200rt.scene import Camera
 def scene(seed):
     """Random scene `seed` -> (args of render_host after pixel_loc, grid, (W, H), description)."""
     rng = np.random.default_rng(1000 + seed)
-    S = int(rng.choice([1, 3, 17, 64, 200, 700, 1500])); L = int(rng.integers(1, 6)); Pl = int(rng.integers(0, 3))
+    S = int(rng.choice([1, 3, 17, 63, 64, 200, 700, 1500, 2600])); L = int(rng.integers(1, 6)); Pl = int(rng.integers(0, 3))
     W, H = 16 * int(rng.integers(6, 14)), 16 * int(rng.integers(4, 9))
     sp = np.zeros((7, S), np.float32)
     spread = float(rng.choice([1.0, 4.0, 12.0]))
@@ -43,8 +44,12 @@ def check(seed):
     # a, b and c all run the conservative FFMA2 filter; B200RT_F_NO_FILTER runs sphere_exact on every sphere (scalar debug
     # kernel, slow: S <= 700 only) and is the check that the filter's margins never drop a hit
     d = render_host(None, *args, grid=grid, shape=shape, flags=_lib.F_NO_FILTER) if args[2].shape[1] <= 700 else a
-    return (np.array_equal(a, b) and np.array_equal(a, c) and np.array_equal(a, d), desc, int(a.sum()), int((a != b).sum()),
-            int((a != c).sum()) + int((a != d).sum()))
+    # the structures of round 2 one by one: the per-ray grid walk off (beam-culled scan instead), the fused small-scene kernels off (wavefront instead),
+    # and the cached / graph-replayed second call of the same arguments
+    e = render_host(None, *args, grid=grid, shape=shape, flags=_lib.F_NO_CGRID | _lib.F_NO_FUSED)
+    f = render_host(None, *args, grid=grid, shape=shape)
+    return (np.array_equal(a, b) and np.array_equal(a, c) and np.array_equal(a, d) and np.array_equal(a, e) and np.array_equal(a, f), desc, int(a.sum()), int((a != b).sum()),
+            int((a != c).sum()) + int((a != d).sum()) + int((a != e).sum()) + int((a != f).sum()))
 
 
 if __name__ == "__main__":
