@@ -1114,12 +1114,13 @@ struct DevCtx {
     float cgrid_density = 2.f;                                       // env B200RT_CGRID_DENSITY: cells per sphere the grid aims at
     int cgrid_from = 1; size_t cgrid_max_paths = (size_t)1 << 40, cgrid_nosort_paths = 0;   // env B200RT_CGRID_FROM (first depth served by the grid; 99: never), B200RT_CGRID_MAX_PATHS
     int fuse_ss = 1;                                                 // env B200RT_FUSE_SS: 0 never, 1 single-stream frames (default), 2 always
+    int sort_max_depth = 1 << 20;                                    // env B200RT_SORT_MAX_DEPTH: deepest depth whose hits are regrouped
     int split_num = 7, split_den = 8;                                // env B200RT_SPLIT=num/den: share of the columns in the first tile of b200rt_render_host's two-tile overlap
     bool no_fused = false;                                           // env B200RT_NO_FUSED: small scenes through the wavefront kernels
     bool no_fold_key = false;                                        // env B200RT_NO_FOLD_KEY: separate k_key launch
     bool no_cgrid_all = false;                                       // env B200RT_NO_CGRID_ALL
     bool no_lanes = false, lane_conc = false;                        // env B200RT_NO_LANES, B200RT_LANE_CONC
-    bool no_sgrid = false, no_clus = false, no_sort_last = true; int ss_grid = 0; int sgrid_min_s = 1; bool no_sort = false; int sort_posbits = -1, sort_dirn = -1;     // env B200RT_NO_SORT, B200RT_SORT_POSBITS, B200RT_SORT_DIRN (-1: chosen from the queue size)
+    bool no_sgrid = false, no_clus = false, no_sort_last = false; int ss_grid = 0; int sgrid_min_s = 1; bool no_sort = false; int sort_posbits = -1, sort_dirn = -1;     // env B200RT_NO_SORT, B200RT_SORT_POSBITS, B200RT_SORT_DIRN (-1: chosen from the queue size)
     int npre = 1, pre[6] = {256, 0, 0, 0, 0, 0};                    // leading shadow passes (env B200RT_PASSES=a,b,...; multiples of 8)
     bool timeline = false;                                        // env B200RT_TIMELINE: per-launch first-start / last-end (globaltimer) to stderr
     // resident scene (k_scene_cmp): the raw arrays the tables were built from, the version words, the per-frame camera block
@@ -1214,7 +1215,9 @@ int init_ctx(DevCtx& c, int device) {
     { const char* e = getenv("B200RT_NO_CULL"); c.no_cull = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_TIMELINE"); c.timeline = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_NO_SORT"); c.no_sort = e && atoi(e) != 0; }
-    { const char* e = getenv("B200RT_SORT_LAST"); if (e) c.no_sort_last = atoi(e) == 0; }   // the last depth has no next bounce to regroup for: skipping its sort measured 0.08 ms faster at C4
+    // The last depth has no next bounce to regroup for, but its shading profits from the order: round 1 (separate k_key pass, ordered compaction in k_setup) measured the
+    // sort 0.08 ms slower at C4; with the keys from the walk's epilogue and k_setup_shade it is 0.2 ms faster (10.03 -> 9.83 ms).  B200RT_SORT_LAST=0 skips it.
+    { const char* e = getenv("B200RT_SORT_LAST"); if (e) c.no_sort_last = atoi(e) == 0; }
     { const char* e = getenv("B200RT_SS_GRID"); if (e) c.ss_grid = std::max(0, atoi(e)); }     // CTAs per SM of the k_shadow_shade grid (0: sized from the queue)
     { const char* e = getenv("B200RT_NO_CLUS"); c.no_clus = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_NO_SGRID"); c.no_sgrid = e && atoi(e) != 0; }
@@ -1230,6 +1233,7 @@ int init_ctx(DevCtx& c, int device) {
     { const char* e = getenv("B200RT_CGRID_MAX_PATHS"); if (e) c.cgrid_max_paths = (size_t)std::max(0ll, atoll(e)); }
     { const char* e = getenv("B200RT_FUSE_SS"); if (e) c.fuse_ss = std::max(0, std::min(2, atoi(e))); }
     { const char* e = getenv("B200RT_SPLIT"); int n_ = 0, d_ = 0; if (e && sscanf(e, "%d/%d", &n_, &d_) == 2 && n_ > 0 && d_ > n_) { c.split_num = n_; c.split_den = d_; } }
+    { const char* e = getenv("B200RT_SORT_MAX_DEPTH"); if (e) c.sort_max_depth = std::max(0, atoi(e)); }
     { const char* e = getenv("B200RT_NO_FUSED"); c.no_fused = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_NO_FOLD_KEY"); c.no_fold_key = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_NO_CGRID_ALL"); c.no_cgrid_all = e && atoi(e) != 0; }
@@ -1621,7 +1625,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             q.n_in = n_live; q.work = cd + 1;
             if (cgrid && d >= cgrid_from) {                     // per-ray grid walk (an unusable grid is handled inside the kernel)
                 CGridArgs ca{ q.rayO, q.rayD, q.camo, n_live, q.hit, nullptr, q.slow, cd + 1, nullptr, nullptr, nullptr, 0 };
-                const bool sort_here = regroup && d >= 1 && (d < depth || !c.no_sort_last);
+                const bool sort_here = regroup && d >= 1 && d <= c.sort_max_depth && (d < depth || !c.no_sort_last);
                 if (sort_here && !c.no_fold_key) { ca.sgrid = c.sortGrid.as<GridDev>(); ca.hist = ln.sortHist.as<uint32_t>(); ca.keyb = ln.sortKey.as<uint2>(); ca.use_dir = d < depth ? 1 : 0; key_folded = true; }
                 if (tlb) { ca.tl = tlb + 2 * (size_t)tln++; tlname.push_back("closest<grid> d" + std::to_string(d)); }
                 const int cgg = (int)std::min<size_t>((size_t)c.sm_count * 32, std::max<size_t>((size_t)c.sm_count * 8, cap / (256 * 4)));
@@ -1636,7 +1640,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
             tm.end(0);
             tm.begin(2);
             bool scatter = false;
-            if (regroup && d >= 1 && (d < depth || !c.no_sort_last)) {
+            if (regroup && d >= 1 && d <= c.sort_max_depth && (d < depth || !c.no_sort_last)) {
                 SortDev so{ q.rayO, q.rayD, q.camo, q.hit, n_live, c.sortGrid.as<GridDev>(), ln.sortKey.as<uint2>(), ln.sortHist.as<uint32_t>(), ln.sortPart.as<uint32_t>(),
                             ln.sortBase.as<uint32_t>(), ln.sortPerm.as<uint32_t>(), cd + 2, sort_nb, d < depth ? 1 : 0, nullptr };
                 if (tlb) { so.tl = tlb + 2 * (size_t)tln++; tlname.push_back("sort d" + std::to_string(d)); }
