@@ -98,8 +98,12 @@ __device__ __forceinline__ void pack_item(int i, const float* __restrict__ spher
             sphB[i] = make_float4(cx, cy, cz, r2);
             sphCol[i] = make_float4(spheres[4 * S + i], spheres[5 * S + i], spheres[6 * S + i], 0.f);
             // scene bound for the filter margin: max |C| (atomicMax on the bit pattern of a non-negative float)
-            atomicMax(reinterpret_cast<int*>(cmax), __float_as_int((float)sqrt(cc) * 1.0000002f));
-            atomicMax(reinterpret_cast<int*>(cmax) + 1, __float_as_int(fabsf(r)));          // bounds[1] = max r
+            // (a sphere with a NaN / infinite coordinate or radius is never hit by any path, like in the reference — intersections.py:25-36 with NaN —
+            // and must not poison the bounds every other sphere's margins are computed from)
+            if (isfinite(cc) && isfinite(r)) {
+                atomicMax(reinterpret_cast<int*>(cmax), __float_as_int((float)sqrt(cc) * 1.0000002f));
+                atomicMax(reinterpret_cast<int*>(cmax) + 1, __float_as_int(fabsf(r)));      // bounds[1] = max r
+            }
         } else {
             sphA[i] = make_float4(0.f, 0.f, 0.f, -3.0e38f);               // padding: q = -3e38 never reaches a threshold
         }
@@ -431,7 +435,8 @@ __global__ void __launch_bounds__(256) k_rank(SceneDev sc, int* perm, const uint
         if (t >= sc.S) return -1.f;
         const float4 sp = sc.sphB[t];
         const float ex = sp.x - v.x, ey = sp.y - v.y, ez = sp.z - v.z;
-        return sp.w / fmaxf(ex * ex + ey * ey + ez * ez, 1e-30f);
+        const float k = sp.w / fmaxf(ex * ex + ey * ey + ez * ez, 1e-30f);
+        return (k == k) ? k : -0.5f;                          // NaN sphere: after every valid one (keys >= 0), before the padding (-1); the order must stay total
     };
     const float ks = key(s);
     int rank = 0;
@@ -485,13 +490,14 @@ __global__ void __launch_bounds__(64) k_clus(SceneDev sc, const int* perm, float
     if (c * 64 >= sc.Spad) return;
     const int* pr = perm + (size_t)sc.L * sc.Spad;
     float mx = 0.f, my = 0.f, mz = 0.f; int n = 0;
-    for (int k = 0; k < 64 && c * 64 + k < sc.Spad; ++k) { const int s = pr[c * 64 + k]; if (s < sc.S) { const float4 sp = sc.sphB[s]; mx += sp.x; my += sp.y; mz += sp.z; ++n; } }
+    auto finite4 = [](const float4& v) { return isfinite(v.x) && isfinite(v.y) && isfinite(v.z) && isfinite(v.w); };      // (a non-finite sphere is never hit: it needs no bound)
+    for (int k = 0; k < 64 && c * 64 + k < sc.Spad; ++k) { const int s = pr[c * 64 + k]; if (s < sc.S) { const float4 sp = sc.sphB[s]; if (!finite4(sp)) continue; mx += sp.x; my += sp.y; mz += sp.z; ++n; } }
     if (n == 0) { clus[c] = make_float4(0.f, 0.f, 0.f, -1.f); return; }
     mx /= (float)n; my /= (float)n; mz /= (float)n;
     float rad = 0.f;
     for (int k = 0; k < 64 && c * 64 + k < sc.Spad; ++k) {
         const int s = pr[c * 64 + k];
-        if (s < sc.S) { const float4 sp = sc.sphB[s]; const float ex = sp.x - mx, ey = sp.y - my, ez = sp.z - mz;
+        if (s < sc.S) { const float4 sp = sc.sphB[s]; if (!finite4(sp)) continue; const float ex = sp.x - mx, ey = sp.y - my, ez = sp.z - mz;
                         rad = fmaxf(rad, __fsqrt_ru(ex * ex + ey * ey + ez * ez) * 1.00001f + __fsqrt_ru(fmaxf(sp.w, 0.f))); }
     }
     clus[c] = make_float4(mx, my, mz, rad * 1.00001f + 1e-6f);

@@ -451,7 +451,7 @@ def test_closest_hit_grid_equals_beam_scan_and_brute_force(S, W, H, depth, aa, s
         assert np.array_equal(got, _cuda(g, flags=_lib.F_NO_FILTER))
 
 
-@pytest.mark.parametrize("case", ["huge_sphere_on_big_list", "out_of_range_falls_back", "flat_scene", "camera_inside_sphere"])
+@pytest.mark.parametrize("case", ["huge_sphere_on_big_list", "out_of_range_falls_back", "flat_scene", "camera_inside_sphere", "lists_overflow_capacity", "nan_sphere"])
 def test_closest_hit_grid_edge_cases(case):
     from b200rt import _lib
     from b200rt.scene import Camera
@@ -466,6 +466,11 @@ def test_closest_hit_grid_edge_cases(case):
         sp[2] = sp[3]                                                # all spheres resting on the plane: one layer of cells
     elif case == "camera_inside_sphere":
         sp[0:3, 0] = [-2.0, 0.0, 2.0]; sp[3, 0] = 5.0
+    elif case == "lists_overflow_capacity":                          # every sphere covers hundreds of cells: the id lists exceed the grid's capacity ->
+        sp[3] = np.random.default_rng(4).uniform(1.0, 1.3, sp.shape[1])  # the grid marks itself unusable on the device and every ray tests every sphere
+        sp[2] = sp[3] + 0.1
+    elif case == "nan_sphere":
+        sp[0, 3] = np.nan; sp[3, 7] = np.nan                          # never hit, by any path
     got = _cuda(g)
     assert got.any()
     assert np.array_equal(got, _cuda(g, flags=_lib.F_NO_CGRID)), case
