@@ -1117,7 +1117,7 @@ struct DevCtx {
     Buf sortGrid;                                                    // bounding box / cell counts of the regrouping (scene-level)
     Buf cgHdr, cgStart, cgCursor, cgIds, cgBig, cgRec;                      // uniform grid of the spheres for per-ray closest-hit queries (closest_grid.cuh)
     int cgrid_ctas = 8;                                              // env B200RT_CGRID_CTAS: CTAs per SM of k_closest_grid
-    float cgrid_density = 2.f;                                       // env B200RT_CGRID_DENSITY: cells per sphere the grid aims at
+    float cgrid_density = 1.5f;                                       // env B200RT_CGRID_DENSITY: cells per sphere the grid aims at
     int cgrid_from = 1; size_t cgrid_max_paths = (size_t)1 << 40, cgrid_nosort_paths = 0;   // env B200RT_CGRID_FROM (first depth served by the grid; 99: never), B200RT_CGRID_MAX_PATHS
     int fuse_ss = 1;                                                 // env B200RT_FUSE_SS: 0 never, 1 single-stream frames (default), 2 always
     int sort_max_depth = 1 << 20;                                    // env B200RT_SORT_MAX_DEPTH: deepest depth whose hits are regrouped

@@ -91,7 +91,7 @@ struct CGridDev {
 // eps = (2e-3 + 1e-3 r) * max(1, B / 256), B = max |C| + max r: the exact test's slack and the walk's rounding grow linearly with the coordinates
 __device__ __forceinline__ float cg_eps_scale(const float* cmax) { return fmaxf(1.f, (cmax[0] + cmax[1]) * (1.f / kCgRange)); }
 
-// Scene bounds -> grid dimensions.  One CTA.  n_target = cells_per_sphere * S cubic cells (2 per sphere measured best:
+// Scene bounds -> grid dimensions.  One CTA.  n_target = cells_per_sphere * S cubic cells (1 - 2 per sphere measured within 1 % of each other, default 1.5:
 // profiles/r02_cgrid*.txt), <= kCgMaxDim per axis.
 __global__ void __launch_bounds__(256) k_cg_setup(SceneDev sc, CGridDev g, int max_cells, float cells_per_sphere, const uint32_t* cs, int cs_group) {
     if (cs[cs_group] == cs[0]) return;
