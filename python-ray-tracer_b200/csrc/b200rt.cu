@@ -1116,7 +1116,7 @@ struct DevCtx {
     Buf sgCells, sgTab, sgCone;                                      // per-light direction grids of the shadow queries (shadow_grid.cuh)
     Buf sortGrid;                                                    // bounding box / cell counts of the regrouping (scene-level)
     Buf cgHdr, cgStart, cgCursor, cgIds, cgBig, cgRec;                      // uniform grid of the spheres for per-ray closest-hit queries (closest_grid.cuh)
-    int cgrid_ctas = 8;                                              // env B200RT_CGRID_CTAS: CTAs per SM of k_closest_grid
+    int cgrid_ctas = 64;                                             // env B200RT_CGRID_CTAS: CTAs per SM of the walk's grid, at most
     float cgrid_density = 1.5f;                                       // env B200RT_CGRID_DENSITY: cells per sphere the grid aims at
     int cgrid_from = 1; size_t cgrid_max_paths = (size_t)1 << 40, cgrid_nosort_paths = 0;   // env B200RT_CGRID_FROM (first depth served by the grid; 99: never), B200RT_CGRID_MAX_PATHS
     int fuse_ss = 1;                                                 // env B200RT_FUSE_SS: 0 never, 1 single-stream frames (default), 2 always
@@ -1234,8 +1234,8 @@ int init_ctx(DevCtx& c, int device) {
     { const char* e = getenv("B200RT_NO_SPLIT"); c.no_split = e && atoi(e) != 0; }
     { const char* e = getenv("B200RT_LANES"); c.no_lanes = !(e && atoi(e) != 0); }       // two-lane wavefronts: measured slower, opt-in
     { const char* e = getenv("B200RT_CGRID_FROM"); if (e) c.cgrid_from = std::max(1, atoi(e)); }
+    { const char* e = getenv("B200RT_CGRID_CTAS"); if (e) c.cgrid_ctas = std::max(1, std::min(1024, atoi(e))); }
     { const char* e = getenv("B200RT_CGRID_DENSITY"); if (e) c.cgrid_density = std::max(0.25f, (float)atof(e)); }
-    { const char* e = getenv("B200RT_CGRID_CTAS"); if (e) c.cgrid_ctas = std::max(1, std::min(32, atoi(e))); }
     { const char* e = getenv("B200RT_CGRID_MAX_PATHS"); if (e) c.cgrid_max_paths = (size_t)std::max(0ll, atoll(e)); }
     { const char* e = getenv("B200RT_FUSE_SS"); if (e) c.fuse_ss = std::max(0, std::min(2, atoi(e))); }
     { const char* e = getenv("B200RT_SPLIT"); int n_ = 0, d_ = 0; if (e && sscanf(e, "%d/%d", &n_, &d_) == 2 && n_ > 0 && d_ > n_) { c.split_num = n_; c.split_den = d_; } }
@@ -1634,7 +1634,7 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
                 const bool sort_here = regroup && d >= 1 && d <= c.sort_max_depth && (d < depth || !c.no_sort_last);
                 if (sort_here && !c.no_fold_key) { ca.sgrid = c.sortGrid.as<GridDev>(); ca.hist = ln.sortHist.as<uint32_t>(); ca.keyb = ln.sortKey.as<uint2>(); ca.use_dir = d < depth ? 1 : 0; key_folded = true; }
                 if (tlb) { ca.tl = tlb + 2 * (size_t)tln++; tlname.push_back("closest<grid> d" + std::to_string(d)); }
-                const int cgg = (int)std::min<size_t>((size_t)c.sm_count * 32, std::max<size_t>((size_t)c.sm_count * 8, cap / (256 * 4)));
+                const int cgg = (int)std::min<size_t>((size_t)c.sm_count * c.cgrid_ctas, std::max<size_t>((size_t)c.sm_count * 8, cap / (256 * 4)));
                 if (key_folded) k_closest_grid_key<<<cgg, 256, 0, cs>>>(sc, cg, ca); else k_closest_grid<<<cgg, 256, 0, cs>>>(sc, cg, ca);
                 CKL();
             }
