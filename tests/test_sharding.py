@@ -130,3 +130,52 @@ def test_shared_frame_assembles_strips_across_mappings(tmp_path):
     b.close(); a.close()
     import os
     assert not os.path.exists(os.path.join(str(tmp_path), "frame_test"))
+
+
+def _shared_worker(rank, world, port, q, name, directory):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from oracle import oracle_f64 as O
+        g = load_golden("rand_a")
+        W, H = int(g["W"]), int(g["H"])
+        args = (g["cam_origin"], g["cam_rotation"], g["spheres"], g["lights"], g["planes"], float(g["amb"]), float(g["lamb"]),
+                float(g["refl"]), int(g["refl_depth"]), bool(g["aliasing"]))
+        fr = None
+        if rank == 0:                                                    # bench.py's sequence: rank 0 creates, barrier, the others attach
+            fr = sharding.SharedFrame(name, W, H, create=True, pin=False, directory=directory)
+        dist.barrier()
+        if rank != 0:
+            fr = sharding.SharedFrame(name, W, H, create=False, pin=False, directory=directory)
+        for a, b in sharding.strip_ranges(W, rank, world, 4):            # every rank writes its strips straight into the one frame
+            fr.array[:, a:b, :] = O.render(None, *args, grid=g["grid"], shape=(W, H), x_range=(a, b))[:, a:b, :]
+        fr.array.flush()
+        dist.barrier()
+        if rank == 0:
+            q.put(np.array(fr.array))                                    # the creating rank holds the assembled frame
+        dist.barrier()
+        fr.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_gloo_world2_shared_frame_is_assembled_on_rank0(oracle, tmp_path):
+    """The multi-process direct gather of bench.py --gpus N (SharedFrame: one mapping, every rank writes its strips, no collective on the
+    data path) with two gloo processes on CPU: rank 0 ends up holding the whole frame."""
+    g = load_golden("rand_a")
+    W, H = int(g["W"]), int(g["H"])
+    args = (g["cam_origin"], g["cam_rotation"], g["spheres"], g["lights"], g["planes"], float(g["amb"]), float(g["lamb"]),
+            float(g["refl"]), int(g["refl_depth"]), bool(g["aliasing"]))
+    whole = oracle.render(None, *args, grid=g["grid"], shape=(W, H))
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_shared_worker, args=(r, 2, port, q, "shared_frame_gloo", str(tmp_path))) for r in range(2)]
+    for p in procs:
+        p.start()
+    frame = q.get(timeout=180)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert np.array_equal(frame, whole)
+    assert not os.path.exists(os.path.join(str(tmp_path), "shared_frame_gloo"))
