@@ -1,7 +1,7 @@
 """Fuzz the exact-culling paths: random scenes (lights among the spheres, inside them, far away; clustered and huge spheres),
 default path vs brute force (B200RT_F_DENSE), the scan path (B200RT_F_NO_SGRID), the path without the closest-hit grid / the fused
 small-scene kernels (B200RT_F_NO_CGRID | B200RT_F_NO_FUSED), a repeated (cached, graph-replayed) call and - for S <= 700 - the exact
-test on every sphere without any filter (B200RT_F_NO_FILTER) must be byte-identical.  usage: python tools/gpu_fuzz.py [n_scenes]"""
+test on every sphere without any filter (B200RT_F_NO_FILTER) must be byte-identical.  usage: python tools/gpu_fuzz.py [n_scenes] [first_seed]"""
 import os, sys
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -54,8 +54,9 @@ def check(seed):
 
 if __name__ == "__main__":
     n = int(sys.argv[1]) if len(sys.argv) > 1 else 40
+    first = int(sys.argv[2]) if len(sys.argv) > 2 else 0
     bad = 0
-    for seed in range(n):
+    for seed in range(first, first + n):
         ok, desc, chk, d1, d2 = check(seed)
         bad += 0 if ok else 1
         print(f"seed {seed}: {desc} sum={chk} -> {'ok' if ok else f'MISMATCH {d1} / {d2}'}", flush=True)
