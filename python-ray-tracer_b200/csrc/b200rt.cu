@@ -1433,13 +1433,17 @@ int render_device(DevCtx& c, const b200rt_args* a, cudaStream_t st) {
     // Shadow queries through the per-light direction grids (shadow_grid.cuh) wherever work may be skipped at all
     // (beam culling on); k_isect3<shadow> + k_shade stay for the brute-force / debug modes.  (Also for the 6-sphere default
     // scene: C3 3.95 -> 2.58 ms, C5 1.78 -> 1.40 ms per frame against the dense [light][hit] scan.)
-    const bool sgrid = cull && !nofilter && S >= c.sgrid_min_s && S <= 65535 && L > 0 &&
-                       sizeof(uint16_t) * (size_t)kSgTiers * L * kSgCells * kSgRec <= ((size_t)8 << 30) &&      // 12.6 MB per light; beyond 8 GB of grids: scan path
-                       !(a->flags & B200RT_F_NO_SGRID) && !c.no_sgrid;
+    bool sgrid = cull && !nofilter && S >= c.sgrid_min_s && S <= 65535 && L > 0 &&
+                 sizeof(uint16_t) * (size_t)kSgTiers * L * kSgCells * kSgRec <= ((size_t)2 << 30) &&      // 12.6 MB per light; beyond 2 GB of grids (81 lights): scan path
+                 !(a->flags & B200RT_F_NO_SGRID) && !c.no_sgrid;
     ShadowGridDev sg{};
+    if (sgrid) {                                                 // no memory for the grids: the scan path needs none
+        const cudaError_t e1 = c.sgCells.ensure(sizeof(uint16_t) * (size_t)kSgTiers * L * kSgCells * kSgRec);
+        const cudaError_t e2 = e1 == cudaSuccess ? c.sgTab.ensure(sizeof(float4) * (size_t)L * S) : e1;
+        const cudaError_t e3 = e2 == cudaSuccess ? c.sgCone.ensure(sizeof(float4) * (size_t)kSgTiers * L * S) : e2;
+        if (e3 != cudaSuccess) { cudaGetLastError(); sgrid = false; }
+    }
     if (sgrid) {
-        CK(c.sgCells.ensure(sizeof(uint16_t) * (size_t)kSgTiers * L * kSgCells * kSgRec));
-        CK(c.sgTab.ensure(sizeof(float4) * (size_t)L * S)); CK(c.sgCone.ensure(sizeof(float4) * (size_t)kSgTiers * L * S));
         sg = ShadowGridDev{ c.sgCells.as<uint16_t>(), c.sgTab.as<float4>(), c.sgCone.as<float4>(), c.pivPerm.as<int>(), Spad };
         k_sgrid_tab<<<(L * S + 255) / 256, 256, 0, st>>>(sc, sg, cst); CKL();
         k_sgrid_build<<<dim3(kSgCells / 256, L, kSgTiers), 256, 0, st>>>(sc, sg, cst); CKL();
